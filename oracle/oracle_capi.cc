@@ -1,0 +1,308 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see towr_oracle.h header).
+#include "oracle_capi.h"
+
+#include <cstring>
+#include <exception>
+#include <stdexcept>
+#include <string>
+
+#include "constraints.h"
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+using namespace orc;
+
+static thread_local std::string g_err;
+
+struct orc_problem {
+  NlpFormulation formulation;
+  SplineHolder splines;
+  Problem nlp;
+  Vec x0;
+};
+
+static NlpFormulation MakeFormulation(const orc_spec& s) {
+  NlpFormulation f;
+  const int E = s.n_ee;
+  f.model_.dynamic_model_ = std::make_shared<SingleRigidBodyDynamics>(s.mass, s.inertia[0], s.inertia[1], s.inertia[2],
+                                                                      s.inertia[3], s.inertia[4], s.inertia[5], E);
+  auto kin = std::make_shared<KinematicModel>();
+  for (int e = 0; e < E; ++e) {
+    kin->nominal_stance_.push_back(V3(s.nominal_stance[e][0], s.nominal_stance[e][1], s.nominal_stance[e][2]));
+    kin->max_dev_.push_back(V3(s.max_dev[e][0], s.max_dev[e][1], s.max_dev[e][2]));
+    kin->min_dev_.push_back(V3(s.min_dev[e][0], s.min_dev[e][1], s.min_dev[e][2]));
+  }
+  f.model_.kinematic_model_ = kin;
+  f.terrain_ = HeightMap::MakeTerrain(s.terrain_id);
+
+  Parameters& p = f.params_;
+  p.constraints_.clear();
+  for (int i = 0; i < s.n_constraints; ++i) p.constraints_.push_back(static_cast<Parameters::ConstraintName>(s.constraints[i]));
+  for (int e = 0; e < E; ++e) {
+    p.ee_phase_durations_.push_back(Vec(s.phase_durations[e], s.phase_durations[e] + s.n_phases[e]));
+    p.ee_in_contact_at_start_.push_back(s.in_contact_at_start[e] != 0);
+  }
+  p.dt_constraint_dynamic_ = s.dt_constraint_dynamic;
+  p.dt_constraint_range_of_motion_ = s.dt_constraint_range_of_motion;
+  p.dt_constraint_base_motion_ = s.dt_constraint_base_motion;
+  p.dt_constraint_force_ = s.dt_constraint_force;
+  p.dt_constraint_torque_ = s.dt_constraint_torque;
+  p.duration_base_polynomial_ = s.duration_base_polynomial;
+  p.ee_polynomials_per_swing_phase_ = s.ee_polynomials_per_swing_phase;
+  p.force_polynomials_per_stance_phase_ = s.force_polynomials_per_stance_phase;
+  p.torque_polynomials_per_stance_phase_ = s.torque_polynomials_per_stance_phase;
+  p.force_limit_in_normal_direction_ = s.force_limit_in_normal_direction;
+  p.torque_tx_min_ = s.torque_tx_min; p.torque_tx_max_ = s.torque_tx_max;
+  p.torque_ty_min_ = s.torque_ty_min; p.torque_ty_max_ = s.torque_ty_max;
+  p.torque_k_friction_ = s.torque_k_friction;
+  p.bound_phase_duration_ = {s.bound_phase_duration[0], s.bound_phase_duration[1]};
+  p.enable_stance_tracking = false;
+  auto dims = [](const int* flags) { std::vector<int> d; for (int i = 0; i < 3; ++i) if (flags[i]) d.push_back(i); return d; };
+  p.bounds_final_lin_pos_ = dims(s.bounds_final_lin_pos);
+  p.bounds_final_lin_vel_ = dims(s.bounds_final_lin_vel);
+  p.bounds_final_ang_pos_ = dims(s.bounds_final_ang_pos);
+  p.bounds_final_ang_vel_ = dims(s.bounds_final_ang_vel);
+
+  auto node = [](const double* a) { Node n; n.p = V3(a[0], a[1], a[2]); n.v = V3(a[3], a[4], a[5]); return n; };
+  f.initial_base_.lin = node(s.initial_base_lin);
+  f.initial_base_.ang = node(s.initial_base_ang);
+  f.final_base_.lin = node(s.final_base_lin);
+  f.final_base_.ang = node(s.final_base_ang);
+  for (int e = 0; e < E; ++e) f.initial_ee_W_.push_back(V3(s.initial_ee_W[e][0], s.initial_ee_W[e][1], s.initial_ee_W[e][2]));
+  return f;
+}
+
+static void Build(orc_problem* p, const orc_spec& s) {
+  p->formulation = MakeFormulation(s);
+  for (auto& v : p->formulation.GetVariableSets(p->splines)) p->nlp.AddVariableSet(v);
+  for (auto& c : p->formulation.GetConstraints(p->splines)) p->nlp.AddConstraintSet(c);
+  p->x0 = p->nlp.GetVariableValues();
+}
+
+extern "C" {
+
+void orc_spec_defaults(orc_spec* s) {
+  std::memset(s, 0, sizeof(*s));
+  Parameters d;
+  s->n_constraints = static_cast<int>(d.constraints_.size());
+  for (int i = 0; i < s->n_constraints; ++i) s->constraints[i] = d.constraints_[i];
+  s->dt_constraint_dynamic = d.dt_constraint_dynamic_;
+  s->dt_constraint_range_of_motion = d.dt_constraint_range_of_motion_;
+  s->dt_constraint_base_motion = d.dt_constraint_base_motion_;
+  s->dt_constraint_force = d.dt_constraint_force_;
+  s->dt_constraint_torque = d.dt_constraint_torque_;
+  s->duration_base_polynomial = d.duration_base_polynomial_;
+  s->ee_polynomials_per_swing_phase = d.ee_polynomials_per_swing_phase_;
+  s->force_polynomials_per_stance_phase = d.force_polynomials_per_stance_phase_;
+  s->torque_polynomials_per_stance_phase = d.torque_polynomials_per_stance_phase_;
+  s->force_limit_in_normal_direction = d.force_limit_in_normal_direction_;
+  s->torque_tx_min = d.torque_tx_min_; s->torque_tx_max = d.torque_tx_max_;
+  s->torque_ty_min = d.torque_ty_min_; s->torque_ty_max = d.torque_ty_max_;
+  s->torque_k_friction = d.torque_k_friction_;
+  s->bound_phase_duration[0] = d.bound_phase_duration_.first;
+  s->bound_phase_duration[1] = d.bound_phase_duration_.second;
+  for (int i = 0; i < 3; ++i) s->bounds_final_lin_pos[i] = s->bounds_final_lin_vel[i] = s->bounds_final_ang_pos[i] = s->bounds_final_ang_vel[i] = 1;
+}
+
+int orc_spec_robot(orc_spec* s, int robot) {
+  try {
+    RobotModel rm = RobotModel::Make(static_cast<RobotModel::Robot>(robot));
+    static const double inertia[4][7] = {   // models/examples/*_model.h
+        {20, 1.2, 5.5, 6.0, 0.0, -0.2, -0.01},
+        {20, 1.209, 5.583, 6.056, 0.005, -0.190, -0.012},
+        {83, 4.26, 8.97, 9.88, -0.0063, 0.193, 0.0126},
+        {29.5, 0.946438, 1.94478, 2.01835, 0.000938112, -0.00595386, -0.00146328}};
+    s->mass = inertia[robot][0];
+    for (int i = 0; i < 6; ++i) s->inertia[i] = inertia[robot][1 + i];
+    s->n_ee = static_cast<int>(rm.kinematic_model_->nominal_stance_.size());
+    for (int e = 0; e < s->n_ee; ++e)
+      for (int d = 0; d < 3; ++d) {
+        s->nominal_stance[e][d] = rm.kinematic_model_->nominal_stance_[e](d);
+        s->max_dev[e][d] = rm.kinematic_model_->max_dev_[e](d);
+        s->min_dev[e][d] = rm.kinematic_model_->min_dev_[e](d);
+      }
+    return 0;
+  } catch (const std::exception& e) { g_err = e.what(); return -1; }
+}
+
+int orc_spec_gait(orc_spec* s, int combo, double T) {
+  try {
+    auto gen = GaitGenerator::MakeGaitGenerator(s->n_ee);
+    gen->SetCombo(static_cast<GaitGenerator::Combos>(combo));
+    for (int e = 0; e < s->n_ee; ++e) {
+      Vec d = gen->GetPhaseDurations(T, e);
+      if (d.size() > ORC_MAX_PHASES) throw std::runtime_error("too many phases");
+      s->n_phases[e] = static_cast<int>(d.size());
+      for (size_t i = 0; i < d.size(); ++i) s->phase_durations[e][i] = d[i];
+      s->in_contact_at_start[e] = gen->IsInContactAtStart(e) ? 1 : 0;
+    }
+    return 0;
+  } catch (const std::exception& e) { g_err = e.what(); return -1; }
+}
+
+void orc_spec_nominal_states(orc_spec* s, double goal_x, double goal_y, double goal_yaw) {
+  double z_ground = 0.0;
+  for (int e = 0; e < s->n_ee; ++e) {
+    s->initial_ee_W[e][0] = s->nominal_stance[e][0];
+    s->initial_ee_W[e][1] = s->nominal_stance[e][1];
+    s->initial_ee_W[e][2] = z_ground;
+  }
+  for (int i = 0; i < 6; ++i) s->initial_base_lin[i] = s->initial_base_ang[i] = s->final_base_lin[i] = s->final_base_ang[i] = 0.0;
+  s->initial_base_lin[2] = -s->nominal_stance[0][2] + z_ground;
+  s->final_base_lin[0] = goal_x;
+  s->final_base_lin[1] = goal_y;
+  s->final_base_lin[2] = s->initial_base_lin[2];
+  s->final_base_ang[2] = goal_yaw;
+}
+
+orc_problem* orc_create(const orc_spec* s) {
+  orc_problem* p = nullptr;
+  try {
+    p = new orc_problem();
+    Build(p, *s);
+    return p;
+  } catch (const std::exception& e) {
+    g_err = e.what();
+    delete p;
+    return nullptr;
+  }
+}
+void orc_destroy(orc_problem* p) { delete p; }
+const char* orc_last_error(void) { return g_err.c_str(); }
+
+int orc_n_vars(const orc_problem* p) { return p->nlp.GetNumberOfOptimizationVariables(); }
+int orc_n_rows(const orc_problem* p) { return p->nlp.GetNumberOfConstraints(); }
+int orc_n_var_sets(const orc_problem* p) { return static_cast<int>(p->nlp.Vars()->GetComponents().size()); }
+int orc_n_con_sets(const orc_problem* p) { return static_cast<int>(p->nlp.Constraints().size()); }
+const char* orc_var_set_name(const orc_problem* p, int i) { return p->nlp.Vars()->GetComponents().at(i)->GetName().c_str(); }
+int orc_var_set_rows(const orc_problem* p, int i) { return p->nlp.Vars()->GetComponents().at(i)->GetRows(); }
+const char* orc_con_set_name(const orc_problem* p, int i) { return p->nlp.Constraints().at(i)->GetName().c_str(); }
+int orc_con_set_rows(const orc_problem* p, int i) { return p->nlp.Constraints().at(i)->GetRows(); }
+
+void orc_x0(const orc_problem* p, double* x) { std::memcpy(x, p->x0.data(), p->x0.size() * sizeof(double)); }
+void orc_var_bounds(const orc_problem* p, double* lower, double* upper) {
+  VecBound b = p->nlp.GetBoundsOnOptimizationVariables();
+  for (size_t i = 0; i < b.size(); ++i) { lower[i] = b[i].lower; upper[i] = b[i].upper; }
+}
+void orc_con_bounds(const orc_problem* p, double* lower, double* upper) {
+  VecBound b = p->nlp.GetBoundsOnConstraints();
+  for (size_t i = 0; i < b.size(); ++i) { lower[i] = b[i].lower; upper[i] = b[i].upper; }
+}
+void orc_eval_g(orc_problem* p, const double* x, double* g) {
+  Vec v = p->nlp.EvaluateConstraints(x);
+  std::memcpy(g, v.data(), v.size() * sizeof(double));
+}
+int orc_eval_jac(orc_problem* p, const double* x, int* rows, int* cols, double* vals) {
+  std::vector<int> r, c;
+  std::vector<double> v;
+  Vec cur;
+  if (!x) { cur = p->nlp.GetVariableValues(); x = cur.data(); }
+  p->nlp.EvalJacobian(x, &r, &c, &v);
+  if (rows) std::memcpy(rows, r.data(), r.size() * sizeof(int));
+  if (cols) std::memcpy(cols, c.data(), c.size() * sizeof(int));
+  if (vals) std::memcpy(vals, v.data(), v.size() * sizeof(double));
+  return static_cast<int>(v.size());
+}
+int orc_nnz(orc_problem* p, const double* x) { return orc_eval_jac(p, x, nullptr, nullptr, nullptr); }
+
+}  // extern "C"
+
+extern "C" {
+
+int orc_batch_eval(const orc_spec* s, int n, const double* x, double* g, double* vals, int n_threads) {
+  int status = 0;
+  int nv = 0, nr = 0, nnz = 0;
+  {
+    orc_problem probe;
+    Build(&probe, *s);
+    nv = probe.nlp.GetNumberOfOptimizationVariables();
+    nr = probe.nlp.GetNumberOfConstraints();
+    nnz = orc_nnz(&probe, nullptr);
+  }
+#ifdef _OPENMP
+  if (n_threads > 0) omp_set_num_threads(n_threads);
+#endif
+#pragma omp parallel
+  {
+    orc_problem local;              // one object graph per thread (instances are not thread-safe)
+    Build(&local, *s);
+    std::vector<double> v;
+#pragma omp for schedule(dynamic)
+    for (int i = 0; i < n; ++i) {
+      const double* xi = x + static_cast<size_t>(i) * nv;
+      if (g) {
+        Vec gi = local.nlp.EvaluateConstraints(xi);
+        std::memcpy(g + static_cast<size_t>(i) * nr, gi.data(), nr * sizeof(double));
+      }
+      if (vals) {
+        local.nlp.EvalJacobian(xi, nullptr, nullptr, &v);
+        if (static_cast<int>(v.size()) != nnz) {
+#pragma omp atomic write
+          status = -1;
+        } else {
+          std::memcpy(vals + static_cast<size_t>(i) * nnz, v.data(), nnz * sizeof(double));
+        }
+      }
+    }
+  }
+  return status;
+}
+
+static Node MakeNode(const double* p, const double* v) { Node n; n.p = V3(p[0], p[1], p[2]); n.v = V3(v[0], v[1], v[2]); return n; }
+
+void orc_hermite_point(const double* p0, const double* v0, const double* p1, const double* v1, double T, double t,
+                       double* pos, double* vel, double* acc) {
+  CubicHermitePolynomial poly;
+  poly.SetNodes(MakeNode(p0, v0), MakeNode(p1, v1));
+  poly.SetDuration(T);
+  poly.UpdateCoeff();
+  State3 s = poly.GetPoint(t);
+  for (int d = 0; d < 3; ++d) { pos[d] = s.p(d); vel[d] = s.v(d); acc[d] = s.a(d); }
+}
+void orc_hermite_basis(double T, double t, double* out12) {
+  CubicHermitePolynomial poly;
+  poly.SetDuration(T);
+  int k = 0;
+  for (Dx dxdt : {kPos, kVel, kAcc}) {
+    out12[k++] = poly.GetDerivativeWrtStartNode(dxdt, kPos, t);
+    out12[k++] = poly.GetDerivativeWrtStartNode(dxdt, kVel, t);
+    out12[k++] = poly.GetDerivativeWrtEndNode(dxdt, kPos, t);
+    out12[k++] = poly.GetDerivativeWrtEndNode(dxdt, kVel, t);
+  }
+}
+void orc_hermite_dpos_dT(const double* p0, const double* v0, const double* p1, const double* v1, double T, double t, double* out3) {
+  CubicHermitePolynomial poly;
+  poly.SetNodes(MakeNode(p0, v0), MakeNode(p1, v1));
+  poly.SetDuration(T);
+  poly.UpdateCoeff();
+  V3 d = poly.GetDerivativeOfPosWrtDuration(t);
+  for (int i = 0; i < 3; ++i) out3[i] = d(i);
+}
+void orc_terrain(int terrain_id, double x, double y, double* height, double* dh, double* basis, double* dbasis) {
+  auto t = HeightMap::MakeTerrain(terrain_id);
+  *height = t->GetHeight(x, y);
+  dh[0] = t->GetDerivativeOfHeightWrt(0, x, y);
+  dh[1] = t->GetDerivativeOfHeightWrt(1, x, y);
+  HeightMap::Direction dirs[3] = {HeightMap::Normal, HeightMap::Tangent1, HeightMap::Tangent2};
+  for (int b = 0; b < 3; ++b) {
+    V3 v = t->GetNormalizedBasis(dirs[b], x, y);
+    for (int i = 0; i < 3; ++i) basis[b * 3 + i] = v(i);
+    for (int dim = 0; dim < 2; ++dim) {
+      V3 dv = t->GetDerivativeOfNormalizedBasisWrt(dirs[b], dim, x, y);
+      for (int i = 0; i < 3; ++i) dbasis[(b * 2 + dim) * 3 + i] = dv(i);
+    }
+  }
+}
+void orc_sample_times(double T, double dt, double* out, int* n) {
+  struct Probe : TimeDiscretizationConstraint {
+    Probe(double T_, double dt_) : TimeDiscretizationConstraint(T_, dt_, "probe") {}
+    void UpdateConstraintAtInstance(double, int, Vec&) const override {}
+    void UpdateBoundsAtInstance(double, int, VecBound&) const override {}
+    void UpdateJacobianAtInstance(double, int, const std::string&, SpMat&) const override {}
+  } probe(T, dt);
+  *n = static_cast<int>(probe.SampleTimes().size());
+  if (out) for (int i = 0; i < *n; ++i) out[i] = probe.SampleTimes()[i];
+}
+
+}  // extern "C"

@@ -1,0 +1,96 @@
+/* ORACLE — TEST INFRASTRUCTURE ONLY (see towr_oracle.h header).
+ * Plain-C surface of the CPU oracle, loaded with ctypes by tests/, smoke() and
+ * bench.py's cpu_baseline / --impl reference legs.  Not part of the product ABI
+ * (that one is include/towr_b200.h). */
+#ifndef ORACLE_CAPI_H_
+#define ORACLE_CAPI_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORC_MAX_EE 4
+#define ORC_MAX_PHASES 32
+#define ORC_MAX_CONSTRAINTS 16
+
+/* The public members of towr::NlpFormulation (nlp_formulation.h:100-105) plus the
+ * fields of towr::Parameters (parameters.h:135-336) the hot path reads. */
+typedef struct orc_spec {
+  int n_ee;
+  /* RobotModel: SingleRigidBodyDynamics(mass, Ixx,Iyy,Izz,Ixy,Ixz,Iyz) + KinematicModel */
+  double mass;
+  double inertia[6];
+  double nominal_stance[ORC_MAX_EE][3];
+  double max_dev[ORC_MAX_EE][3];
+  double min_dev[ORC_MAX_EE][3];
+  int terrain_id;                         /* HeightMap::TerrainID, 7 = FiveStepStairs of hopper_example.cc */
+  /* Parameters */
+  int n_phases[ORC_MAX_EE];
+  double phase_durations[ORC_MAX_EE][ORC_MAX_PHASES];
+  int in_contact_at_start[ORC_MAX_EE];
+  int n_constraints;
+  int constraints[ORC_MAX_CONSTRAINTS];   /* Parameters::ConstraintName values, in order */
+  double dt_constraint_dynamic, dt_constraint_range_of_motion, dt_constraint_base_motion;
+  double dt_constraint_force, dt_constraint_torque;
+  double duration_base_polynomial;
+  int ee_polynomials_per_swing_phase, force_polynomials_per_stance_phase, torque_polynomials_per_stance_phase;
+  double force_limit_in_normal_direction;
+  double torque_tx_min, torque_tx_max, torque_ty_min, torque_ty_max, torque_k_friction;
+  double bound_phase_duration[2];
+  int bounds_final_lin_pos[3], bounds_final_lin_vel[3], bounds_final_ang_pos[3], bounds_final_ang_vel[3]; /* flag per dim */
+  /* BaseState initial/final: p(3) then v(3); initial_ee_W_ */
+  double initial_base_lin[6], initial_base_ang[6], final_base_lin[6], final_base_ang[6];
+  double initial_ee_W[ORC_MAX_EE][3];
+} orc_spec;
+
+/* Parameters::Parameters() defaults (parameters.cc:40-105), enable_stance_tracking=false. */
+void orc_spec_defaults(orc_spec* s);
+/* RobotModel(robot) constants: 0 Monoped, 1 Biped, 2 Hyq, 3 Anymal.  Sets n_ee. */
+int orc_spec_robot(orc_spec* s, int robot);
+/* GaitGenerator::MakeGaitGenerator(n_ee)->SetCombo(combo); phase durations scaled to T (towr_ros_app.cc:71-77). */
+int orc_spec_gait(orc_spec* s, int combo, double T);
+/* towr_ros_app.cc:47-58: feet at nominal xy on z=0, base above; goal (x,y,yaw), final z = initial z. */
+void orc_spec_nominal_states(orc_spec* s, double goal_x, double goal_y, double goal_yaw);
+
+typedef struct orc_problem orc_problem;
+orc_problem* orc_create(const orc_spec* s);
+void orc_destroy(orc_problem* p);
+const char* orc_last_error(void);
+
+int orc_n_vars(const orc_problem* p);
+int orc_n_rows(const orc_problem* p);
+int orc_n_var_sets(const orc_problem* p);
+int orc_n_con_sets(const orc_problem* p);
+const char* orc_var_set_name(const orc_problem* p, int i);
+int orc_var_set_rows(const orc_problem* p, int i);
+const char* orc_con_set_name(const orc_problem* p, int i);
+int orc_con_set_rows(const orc_problem* p, int i);
+
+void orc_x0(const orc_problem* p, double* x);                       /* initial guess = GetVariableValues() at set-up */
+void orc_var_bounds(const orc_problem* p, double* lower, double* upper);
+void orc_con_bounds(const orc_problem* p, double* lower, double* upper);
+/* eval_g */
+void orc_eval_g(orc_problem* p, const double* x, double* g);
+/* number of stored Jacobian entries at x (x == NULL: at the current variables) */
+int orc_nnz(orc_problem* p, const double* x);
+/* eval_jac_g: rows/cols/vals may each be NULL; returns the number of stored entries */
+int orc_eval_jac(orc_problem* p, const double* x, int* rows, int* cols, double* vals);
+
+/* CPU baseline: n problems of ONE spec, x is n x n_vars row-major, g n x n_rows, vals n x nnz (nnz at x0).
+ * OpenMP over problems, one object graph per thread.  Returns 0, or -1 on a pattern-size mismatch. */
+int orc_batch_eval(const orc_spec* s, int n, const double* x, double* g, double* vals, int n_threads);
+
+/* unit hooks for known-answer tests */
+void orc_hermite_point(const double* p0, const double* v0, const double* p1, const double* v1, double T, double t,
+                       double* pos, double* vel, double* acc);
+/* out[dxdt*4 + {start_p,start_v,end_p,end_v}] for dxdt in pos,vel,acc */
+void orc_hermite_basis(double T, double t, double* out12);
+void orc_hermite_dpos_dT(const double* p0, const double* v0, const double* p1, const double* v1, double T, double t, double* out3);
+void orc_terrain(int terrain_id, double x, double y, double* height, double* dh /*2*/, double* basis /*3x3 n,t1,t2*/,
+                 double* dbasis /*3x2x3: [basis][dim][xyz]*/);
+void orc_sample_times(double T, double dt, double* out, int* n);    /* time_discretization_constraint.cc:41-49 */
+
+#ifdef __cplusplus
+}
+#endif
+#endif
