@@ -1,0 +1,154 @@
+/* towr_b200.h — C ABI of the batched B200 evaluation backend for TOWR's NLP.
+ *
+ * One eval = for one trajectory-optimisation problem, given its variable vector x,
+ * all constraint values g and all stored values of the sparse constraint Jacobian.
+ * This library evaluates many problems of one *structure class* per launch on a B200.
+ *
+ * What each entry point replaces in the reference (paths relative to towr/):
+ *   - the callbacks ifopt::Problem makes per Ipopt iteration:
+ *     VariableSet::SetVariables      src/variables/nodes_variables.cc:68-76, phase_durations.cc:79-100
+ *     ConstraintSet::GetValues       src/constraints/time_discretization_constraint.cc:65-75 (+ node-based sets)
+ *     ConstraintSet::FillJacobianBlock  src/constraints/time_discretization_constraint.cc:89-96 (+ node-based sets)
+ *     -> towr_b200_batch_eval / towr_b200_batch_eval_device
+ *   - ConstraintSet::GetBounds / VariableSet::GetBounds / GetValues (initial guess)
+ *     src/nlp_formulation.cc:121-363, nodes_variables.cc:118-122,219-263
+ *     -> towr_b200_problem_x0 / _var_bounds / _con_bounds   (host, set-up only)
+ *   - the first eval_jac_g(values == NULL) walk that defines the sparsity pattern
+ *     -> towr_b200_structure_pattern
+ *   - NlpFormulation's public members + Parameters    include/towr/nlp_formulation.h:100-105,
+ *     include/towr/parameters.h:135-336   -> towr_b200_spec
+ *
+ * Conventions: every function returns 0 on success and a negative towr_b200_status
+ * otherwise (never throws across the boundary); towr_b200_last_error() gives the text
+ * for the calling thread.  Buffers are caller-owned.  There is NO CPU fallback: the
+ * eval entry points fail with TOWR_B200_ERR_CUDA when no CUDA device is usable.
+ */
+#ifndef TOWR_B200_H_
+#define TOWR_B200_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TOWR_B200_MAX_EE 4
+#define TOWR_B200_MAX_PHASES 32
+#define TOWR_B200_MAX_CONSTRAINTS 16
+
+typedef enum towr_b200_status {
+  TOWR_B200_OK = 0,
+  TOWR_B200_ERR_ARG = -1,        /* bad argument / inconsistent spec (std::runtime_error in the reference) */
+  TOWR_B200_ERR_UNSUPPORTED = -2,/* valid in the reference, not built here yet */
+  TOWR_B200_ERR_CUDA = -3,       /* CUDA runtime error or no device */
+  TOWR_B200_ERR_STRUCTURE = -4   /* problem does not belong to the batch's structure class */
+} towr_b200_status;
+
+/* towr::Parameters::ConstraintName, include/towr/parameters.h:142-153 */
+enum { TOWR_B200_C_DYNAMIC = 0, TOWR_B200_C_ENDEFFECTOR_ROM, TOWR_B200_C_TOTAL_TIME, TOWR_B200_C_TERRAIN,
+       TOWR_B200_C_TERRAIN_HARD, TOWR_B200_C_FORCE, TOWR_B200_C_TORQUE, TOWR_B200_C_SWING, TOWR_B200_C_BASE_ROM,
+       TOWR_B200_C_BASE_ACC, TOWR_B200_C_BASE_HEIGHT };
+/* towr::RobotModel::Robot, include/towr/models/robot_model.h */
+enum { TOWR_B200_MONOPED = 0, TOWR_B200_BIPED, TOWR_B200_HYQ, TOWR_B200_ANYMAL };
+/* towr::HeightMap::TerrainID, include/towr/terrain/height_map.h; 7 = FiveStepStairs of test/hopper_example.cc:53-86 */
+enum { TOWR_B200_FLAT = 0, TOWR_B200_BLOCK, TOWR_B200_STAIRS, TOWR_B200_GAP, TOWR_B200_SLOPE, TOWR_B200_CHIMNEY,
+       TOWR_B200_CHIMNEY_LR, TOWR_B200_FIVE_STEP_STAIRS, TOWR_B200_TERRAIN_COUNT };
+/* what to evaluate */
+enum { TOWR_B200_EVAL_G = 1, TOWR_B200_EVAL_JAC = 2, TOWR_B200_EVAL_BOTH = 3 };
+
+/* One NlpFormulation: the six public members of towr::NlpFormulation plus the Parameters fields
+ * the path reads.  Same meaning as the reference fields of the same name. */
+typedef struct towr_b200_spec {
+  int n_ee;
+  /* model_: SingleRigidBodyDynamics(mass, Ixx,Iyy,Izz,Ixy,Ixz,Iyz) + KinematicModel */
+  double mass;
+  double inertia[6];
+  double nominal_stance[TOWR_B200_MAX_EE][3];
+  double max_dev[TOWR_B200_MAX_EE][3];
+  double min_dev[TOWR_B200_MAX_EE][3];
+  int terrain_id;
+  /* params_ */
+  int n_phases[TOWR_B200_MAX_EE];
+  double phase_durations[TOWR_B200_MAX_EE][TOWR_B200_MAX_PHASES];
+  int in_contact_at_start[TOWR_B200_MAX_EE];
+  int n_constraints;
+  int constraints[TOWR_B200_MAX_CONSTRAINTS];
+  double dt_constraint_dynamic, dt_constraint_range_of_motion, dt_constraint_base_motion;
+  double dt_constraint_force, dt_constraint_torque;
+  double duration_base_polynomial;
+  int ee_polynomials_per_swing_phase, force_polynomials_per_stance_phase, torque_polynomials_per_stance_phase;
+  double force_limit_in_normal_direction;
+  double torque_tx_min, torque_tx_max, torque_ty_min, torque_ty_max, torque_k_friction;
+  double bound_phase_duration[2];
+  int bounds_final_lin_pos[3], bounds_final_lin_vel[3], bounds_final_ang_pos[3], bounds_final_ang_vel[3];
+  /* initial_base_, final_base_ (p xyz then v xyz), initial_ee_W_ */
+  double initial_base_lin[6], initial_base_ang[6], final_base_lin[6], final_base_ang[6];
+  double initial_ee_W[TOWR_B200_MAX_EE][3];
+} towr_b200_spec;
+
+const char* towr_b200_last_error(void);
+/* 1 when a CUDA device is visible to this process */
+int towr_b200_device_count(void);
+
+/* ---- formulation helpers (host; mirror the reference's set-up code) --------------------------- */
+/* Parameters::Parameters() defaults, src/parameters.cc:40-105 (enable_stance_tracking off) */
+int towr_b200_spec_defaults(towr_b200_spec* s);
+/* RobotModel(robot): include/towr/models/examples/{monoped,biped,hyq,anymal}_model.h */
+int towr_b200_spec_robot(towr_b200_spec* s, int robot);
+/* GaitGenerator::MakeGaitGenerator(n_ee)->SetCombo(combo), durations scaled to T
+ * (src/initialization/gait_generator.cc:54-105, towr_ros/src/towr_ros_app.cc:71-77) */
+int towr_b200_spec_gait(towr_b200_spec* s, int combo, double total_time);
+/* towr_ros/src/towr_ros_app.cc:47-58: feet at nominal xy on z = 0, base above them; goal pose */
+int towr_b200_spec_nominal_states(towr_b200_spec* s, double goal_x, double goal_y, double goal_yaw);
+/* Parameters::OptimizePhaseDurations(), src/parameters.cc:109-112 */
+int towr_b200_spec_optimize_durations(towr_b200_spec* s);
+
+/* ---- structure class: everything the sparsity pattern depends on ----------------------------- */
+typedef struct towr_b200_structure towr_b200_structure;
+int towr_b200_structure_create(const towr_b200_spec* s, towr_b200_structure** out);
+void towr_b200_structure_destroy(towr_b200_structure* st);
+int towr_b200_structure_n_vars(const towr_b200_structure* st);
+int towr_b200_structure_n_rows(const towr_b200_structure* st);
+int towr_b200_structure_nnz(const towr_b200_structure* st);
+int towr_b200_structure_n_var_sets(const towr_b200_structure* st);
+int towr_b200_structure_n_con_sets(const towr_b200_structure* st);
+const char* towr_b200_structure_var_set_name(const towr_b200_structure* st, int i);
+int towr_b200_structure_var_set_rows(const towr_b200_structure* st, int i);
+const char* towr_b200_structure_con_set_name(const towr_b200_structure* st, int i);
+int towr_b200_structure_con_set_rows(const towr_b200_structure* st, int i);
+/* row-major sorted (row, col) of every stored Jacobian entry, ifopt order; arrays of nnz ints */
+int towr_b200_structure_pattern(const towr_b200_structure* st, int* rows, int* cols);
+/* 0 when `s` has the same structure class as `st`, TOWR_B200_ERR_STRUCTURE otherwise */
+int towr_b200_structure_accepts(const towr_b200_structure* st, const towr_b200_spec* s);
+
+/* ---- per-problem host quantities (set-up only) ------------------------------------------------ */
+int towr_b200_problem_x0(const towr_b200_structure* st, const towr_b200_spec* s, double* x);
+int towr_b200_problem_var_bounds(const towr_b200_structure* st, const towr_b200_spec* s, double* lower, double* upper);
+int towr_b200_problem_con_bounds(const towr_b200_structure* st, const towr_b200_spec* s, double* lower, double* upper);
+
+/* ---- a batch of problems of one structure class, resident on one GPU -------------------------- */
+typedef struct towr_b200_batch towr_b200_batch;
+int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int device, towr_b200_batch** out);
+void towr_b200_batch_destroy(towr_b200_batch* b);
+int towr_b200_batch_size(const towr_b200_batch* b);
+/* per-problem constants the kernels read: mass, inertia, terrain id (from `s`; structure must match) */
+int towr_b200_batch_set_problem(towr_b200_batch* b, int i, const towr_b200_spec* s);
+/* same constants for all problems */
+int towr_b200_batch_set_all_problems(towr_b200_batch* b, const towr_b200_spec* s);
+
+/* Host-buffer evaluation (what an Ipopt callback sees).  problem_ids may be NULL (= 0..n-1).
+ * x: n x n_vars row-major.  g_out: n x n_rows, jac_values_out: n x nnz; each may be NULL when
+ * `what` does not ask for it.  Copies H2D, launches, copies D2H, synchronises. */
+int towr_b200_batch_eval(towr_b200_batch* b, const int* problem_ids, int n, int what, const double* x,
+                         double* g_out, double* jac_values_out);
+/* Device-buffer evaluation of problems 0..n-1: pointers are device memory on the batch's GPU,
+ * same shapes; `stream` is a cudaStream_t (NULL = the batch's own stream).  Asynchronous. */
+int towr_b200_batch_eval_device(towr_b200_batch* b, int n, int what, const double* d_x, double* d_g,
+                                double* d_jac_values, void* stream);
+/* per-problem status of the last eval: bit 0 = non-finite value in g, bit 1 = non-finite Jacobian value */
+int towr_b200_batch_status(towr_b200_batch* b, int n, int* status_out);
+/* kernel launches issued by this batch so far (for bench.py's gpu_launches) */
+long long towr_b200_batch_launch_count(const towr_b200_batch* b);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TOWR_B200_H_ */

@@ -1,0 +1,282 @@
+"""towr2025_b200 — batched B200 evaluation backend for TOWR's NLP (constraint values + sparse-Jacobian values).
+
+Python here is plumbing only: a ctypes view of the C ABI in include/towr_b200.h (libtowr_b200.so, built from
+towr2025_b200/csrc by `make` / build()).  The product is the CUDA library; there is no CPU evaluation path —
+every eval call fails loudly when the library or a GPU is missing.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_HERE)
+LIB_PATH = os.path.join(_HERE, "libtowr_b200.so")
+CSRC = os.path.join(_HERE, "csrc")
+
+MAX_EE, MAX_PHASES, MAX_CONSTRAINTS = 4, 32, 16
+
+# towr::Parameters::ConstraintName
+Dynamic, EndeffectorRom, TotalTime, Terrain, TerrainHard, Force, Torque, Swing, BaseRom, BaseAcc, BaseHeight = range(11)
+Monoped, Biped, Hyq, Anymal = range(4)
+FlatID, BlockID, StairsID, GapID, SlopeID, ChimneyID, ChimneyLRID, FiveStepStairsID = range(8)
+EVAL_G, EVAL_JAC, EVAL_BOTH = 1, 2, 3
+C0, C1, C2, C3, C4 = range(5)
+
+
+class Spec(C.Structure):
+    """towr_b200_spec (include/towr_b200.h)."""
+    _fields_ = [
+        ("n_ee", C.c_int),
+        ("mass", C.c_double),
+        ("inertia", C.c_double * 6),
+        ("nominal_stance", (C.c_double * 3) * MAX_EE),
+        ("max_dev", (C.c_double * 3) * MAX_EE),
+        ("min_dev", (C.c_double * 3) * MAX_EE),
+        ("terrain_id", C.c_int),
+        ("n_phases", C.c_int * MAX_EE),
+        ("phase_durations", (C.c_double * MAX_PHASES) * MAX_EE),
+        ("in_contact_at_start", C.c_int * MAX_EE),
+        ("n_constraints", C.c_int),
+        ("constraints", C.c_int * MAX_CONSTRAINTS),
+        ("dt_constraint_dynamic", C.c_double),
+        ("dt_constraint_range_of_motion", C.c_double),
+        ("dt_constraint_base_motion", C.c_double),
+        ("dt_constraint_force", C.c_double),
+        ("dt_constraint_torque", C.c_double),
+        ("duration_base_polynomial", C.c_double),
+        ("ee_polynomials_per_swing_phase", C.c_int),
+        ("force_polynomials_per_stance_phase", C.c_int),
+        ("torque_polynomials_per_stance_phase", C.c_int),
+        ("force_limit_in_normal_direction", C.c_double),
+        ("torque_tx_min", C.c_double), ("torque_tx_max", C.c_double),
+        ("torque_ty_min", C.c_double), ("torque_ty_max", C.c_double),
+        ("torque_k_friction", C.c_double),
+        ("bound_phase_duration", C.c_double * 2),
+        ("bounds_final_lin_pos", C.c_int * 3), ("bounds_final_lin_vel", C.c_int * 3),
+        ("bounds_final_ang_pos", C.c_int * 3), ("bounds_final_ang_vel", C.c_int * 3),
+        ("initial_base_lin", C.c_double * 6), ("initial_base_ang", C.c_double * 6),
+        ("final_base_lin", C.c_double * 6), ("final_base_ang", C.c_double * 6),
+        ("initial_ee_W", (C.c_double * 3) * MAX_EE),
+    ]
+
+    def copy(self):
+        s = Spec()
+        C.memmove(C.byref(s), C.byref(self), C.sizeof(Spec))
+        return s
+
+
+class TowrB200Error(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("towr_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+def build(verbose=False):
+    """Compile libtowr_b200.so in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    env = dict(os.environ)
+    out = None if verbose else subprocess.DEVNULL
+    subprocess.check_call(["make", "-C", CSRC, "-j4"], env=env, stdout=out)
+    return LIB_PATH
+
+
+_lib = None
+
+_EXPORTS = """towr_b200_last_error towr_b200_device_count towr_b200_spec_defaults towr_b200_spec_robot towr_b200_spec_gait
+towr_b200_spec_nominal_states towr_b200_spec_optimize_durations towr_b200_structure_create towr_b200_structure_destroy
+towr_b200_structure_n_vars towr_b200_structure_n_rows towr_b200_structure_nnz towr_b200_structure_n_var_sets
+towr_b200_structure_n_con_sets towr_b200_structure_var_set_name towr_b200_structure_var_set_rows
+towr_b200_structure_con_set_name towr_b200_structure_con_set_rows towr_b200_structure_pattern towr_b200_structure_accepts
+towr_b200_problem_x0 towr_b200_problem_var_bounds towr_b200_problem_con_bounds towr_b200_batch_create
+towr_b200_batch_destroy towr_b200_batch_size towr_b200_batch_set_problem towr_b200_batch_set_all_problems
+towr_b200_batch_eval towr_b200_batch_eval_device towr_b200_batch_status towr_b200_batch_launch_count""".split()
+
+
+def lib():
+    """The loaded C-ABI library.  Raises if it has not been built: there is no fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise TowrB200Error(-3, "libtowr_b200.so is not built (run towr2025_b200.build() or make -C towr2025_b200/csrc)")
+    L = C.CDLL(LIB_PATH)
+    dp, ip, sp, vp = C.POINTER(C.c_double), C.POINTER(C.c_int), C.POINTER(Spec), C.c_void_p
+    L.towr_b200_last_error.restype = C.c_char_p
+    L.towr_b200_spec_defaults.argtypes = [sp]
+    L.towr_b200_spec_robot.argtypes = [sp, C.c_int]
+    L.towr_b200_spec_gait.argtypes = [sp, C.c_int, C.c_double]
+    L.towr_b200_spec_nominal_states.argtypes = [sp, C.c_double, C.c_double, C.c_double]
+    L.towr_b200_spec_optimize_durations.argtypes = [sp]
+    L.towr_b200_structure_create.argtypes = [sp, C.POINTER(vp)]
+    L.towr_b200_structure_destroy.argtypes = [vp]
+    L.towr_b200_structure_destroy.restype = None
+    for f in ("n_vars", "n_rows", "nnz", "n_var_sets", "n_con_sets"):
+        getattr(L, "towr_b200_structure_" + f).argtypes = [vp]
+    for f in ("var_set_name", "con_set_name"):
+        getattr(L, "towr_b200_structure_" + f).argtypes = [vp, C.c_int]
+        getattr(L, "towr_b200_structure_" + f).restype = C.c_char_p
+    for f in ("var_set_rows", "con_set_rows"):
+        getattr(L, "towr_b200_structure_" + f).argtypes = [vp, C.c_int]
+    L.towr_b200_structure_pattern.argtypes = [vp, ip, ip]
+    L.towr_b200_structure_accepts.argtypes = [vp, sp]
+    L.towr_b200_problem_x0.argtypes = [vp, sp, dp]
+    L.towr_b200_problem_var_bounds.argtypes = [vp, sp, dp, dp]
+    L.towr_b200_problem_con_bounds.argtypes = [vp, sp, dp, dp]
+    L.towr_b200_batch_create.argtypes = [vp, C.c_int, C.c_int, C.POINTER(vp)]
+    L.towr_b200_batch_destroy.argtypes = [vp]
+    L.towr_b200_batch_destroy.restype = None
+    L.towr_b200_batch_size.argtypes = [vp]
+    L.towr_b200_batch_set_problem.argtypes = [vp, C.c_int, sp]
+    L.towr_b200_batch_set_all_problems.argtypes = [vp, sp]
+    L.towr_b200_batch_eval.argtypes = [vp, ip, C.c_int, C.c_int, dp, dp, dp]
+    L.towr_b200_batch_eval_device.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp]
+    L.towr_b200_batch_status.argtypes = [vp, C.c_int, ip]
+    L.towr_b200_batch_launch_count.argtypes = [vp]
+    L.towr_b200_batch_launch_count.restype = C.c_longlong
+    _lib = L
+    return L
+
+
+def exported_symbols():
+    return list(_EXPORTS)
+
+
+def _check(rc):
+    if rc != 0:
+        raise TowrB200Error(rc, lib().towr_b200_last_error().decode())
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double)) if a is not None else None
+
+
+def _ip(a):
+    return a.ctypes.data_as(C.POINTER(C.c_int)) if a is not None else None
+
+
+def make_spec(robot, combo, total_time, goal=(1.0, 0.0, 0.0), terrain=FlatID, optimize_durations=False,
+              extra_constraints=()):
+    """An NlpFormulation set up the way towr_ros_app.cc:47-117 does it."""
+    L = lib()
+    s = Spec()
+    _check(L.towr_b200_spec_defaults(C.byref(s)))
+    _check(L.towr_b200_spec_robot(C.byref(s), robot))
+    _check(L.towr_b200_spec_gait(C.byref(s), combo, total_time))
+    _check(L.towr_b200_spec_nominal_states(C.byref(s), *goal))
+    s.terrain_id = terrain
+    for c in extra_constraints:
+        s.constraints[s.n_constraints] = c
+        s.n_constraints += 1
+    if optimize_durations:
+        _check(L.towr_b200_spec_optimize_durations(C.byref(s)))
+    return s
+
+
+class Structure:
+    """A structure class: sizes, names and the device-independent sparsity pattern."""
+
+    def __init__(self, spec):
+        self._L = lib()
+        h = C.c_void_p()
+        _check(self._L.towr_b200_structure_create(C.byref(spec), C.byref(h)))
+        self._h = h
+        self.n_vars = self._L.towr_b200_structure_n_vars(h)
+        self.n_rows = self._L.towr_b200_structure_n_rows(h)
+        self.nnz = self._L.towr_b200_structure_nnz(h)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._L.towr_b200_structure_destroy(self._h)
+            self._h = None
+
+    def var_sets(self):
+        L, h = self._L, self._h
+        return [(L.towr_b200_structure_var_set_name(h, i).decode(), L.towr_b200_structure_var_set_rows(h, i))
+                for i in range(L.towr_b200_structure_n_var_sets(h))]
+
+    def con_sets(self):
+        L, h = self._L, self._h
+        return [(L.towr_b200_structure_con_set_name(h, i).decode(), L.towr_b200_structure_con_set_rows(h, i))
+                for i in range(L.towr_b200_structure_n_con_sets(h))]
+
+    def pattern(self):
+        r, c = np.empty(self.nnz, np.int32), np.empty(self.nnz, np.int32)
+        _check(self._L.towr_b200_structure_pattern(self._h, _ip(r), _ip(c)))
+        return r, c
+
+    def accepts(self, spec):
+        return self._L.towr_b200_structure_accepts(self._h, C.byref(spec)) == 0
+
+    def x0(self, spec):
+        x = np.empty(self.n_vars)
+        _check(self._L.towr_b200_problem_x0(self._h, C.byref(spec), _dp(x)))
+        return x
+
+    def var_bounds(self, spec):
+        lo, up = np.empty(self.n_vars), np.empty(self.n_vars)
+        _check(self._L.towr_b200_problem_var_bounds(self._h, C.byref(spec), _dp(lo), _dp(up)))
+        return lo, up
+
+    def con_bounds(self, spec):
+        lo, up = np.empty(self.n_rows), np.empty(self.n_rows)
+        _check(self._L.towr_b200_problem_con_bounds(self._h, C.byref(spec), _dp(lo), _dp(up)))
+        return lo, up
+
+    @property
+    def bytes_per_eval(self):
+        """Algorithmic HBM bytes of one eval: read x, write g, write every stored Jacobian value."""
+        return 8 * (self.n_vars + self.n_rows + self.nnz)
+
+
+class Batch:
+    """n problems of one structure class resident on one GPU."""
+
+    def __init__(self, structure, n_problems, device=0):
+        self._L = lib()
+        self.structure = structure
+        self.n = n_problems
+        h = C.c_void_p()
+        _check(self._L.towr_b200_batch_create(structure._h, n_problems, device, C.byref(h)))
+        self._h = h
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._L.towr_b200_batch_destroy(self._h)
+            self._h = None
+
+    def set_problem(self, i, spec):
+        _check(self._L.towr_b200_batch_set_problem(self._h, i, C.byref(spec)))
+
+    def set_all(self, spec):
+        _check(self._L.towr_b200_batch_set_all_problems(self._h, C.byref(spec)))
+
+    def eval(self, x, what=EVAL_BOTH, ids=None, g_out=None, jac_out=None):
+        """Host-buffer evaluation through the C ABI (copies in, launches, copies out)."""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        n = x.shape[0]
+        st = self.structure
+        assert x.shape[1] == st.n_vars
+        g = (g_out if g_out is not None else np.empty((n, st.n_rows))) if what & EVAL_G else None
+        v = (jac_out if jac_out is not None else np.empty((n, st.nnz))) if what & EVAL_JAC else None
+        idp = None
+        if ids is not None:
+            ids = np.ascontiguousarray(ids, dtype=np.int32)
+            idp = _ip(ids)
+        _check(self._L.towr_b200_batch_eval(self._h, idp, n, what, _dp(x), _dp(g), _dp(v)))
+        return g, v
+
+    def eval_device(self, n, what, d_x, d_g, d_vals, stream=None):
+        """Device-pointer evaluation (ints from tensor.data_ptr()); asynchronous on `stream` (a cudaStream_t int)."""
+        _check(self._L.towr_b200_batch_eval_device(self._h, n, what, C.c_void_p(d_x), C.c_void_p(d_g or 0),
+                                                    C.c_void_p(d_vals or 0), C.c_void_p(stream or 0)))
+
+    def status(self, n=None):
+        n = self.n if n is None else n
+        s = np.empty(n, np.int32)
+        _check(self._L.towr_b200_batch_status(self._h, n, _ip(s)))
+        return s
+
+    @property
+    def launches(self):
+        return int(self._L.towr_b200_batch_launch_count(self._h))

@@ -1,0 +1,313 @@
+// capi.cu — the extern "C" boundary declared in include/towr_b200.h.
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <exception>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+#include "structure.h"
+
+namespace tb {
+void SpecDefaults(towr_b200_spec* s);
+void SpecRobot(towr_b200_spec* s, int robot);
+void SpecGait(towr_b200_spec* s, int combo, double total_time);
+void SpecNominalStates(towr_b200_spec* s, double gx, double gy, double gyaw);
+}  // namespace tb
+
+struct towr_b200_structure {
+  tb::HostProgram hp;
+};
+
+namespace {
+thread_local std::string g_err;
+
+struct CudaError : std::runtime_error {
+  explicit CudaError(const std::string& m) : std::runtime_error(m) {}
+};
+struct StructureError : std::runtime_error {
+  explicit StructureError(const std::string& m) : std::runtime_error(m) {}
+};
+
+void Check(cudaError_t e, const char* what) {
+  if (e != cudaSuccess) throw CudaError(std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+template <class F>
+int Guard(F&& f) {
+  try {
+    f();
+    return TOWR_B200_OK;
+  } catch (const CudaError& e) {
+    g_err = e.what();
+    return TOWR_B200_ERR_CUDA;
+  } catch (const StructureError& e) {
+    g_err = e.what();
+    return TOWR_B200_ERR_STRUCTURE;
+  } catch (const std::exception& e) {
+    g_err = e.what();
+    return g_err.rfind("unsupported", 0) == 0 ? TOWR_B200_ERR_UNSUPPORTED : TOWR_B200_ERR_ARG;
+  } catch (...) {
+    g_err = "unknown error";
+    return TOWR_B200_ERR_ARG;
+  }
+}
+
+template <class T>
+T* Upload(const std::vector<T>& v) {
+  T* d = nullptr;
+  size_t bytes = sizeof(T) * (v.empty() ? 1 : v.size());
+  Check(cudaMalloc(&d, bytes), "cudaMalloc(table)");
+  if (!v.empty()) Check(cudaMemcpy(d, v.data(), sizeof(T) * v.size(), cudaMemcpyHostToDevice), "cudaMemcpy(table)");
+  return d;
+}
+}  // namespace
+
+struct towr_b200_batch {
+  const towr_b200_structure* st = nullptr;
+  int n = 0, device = 0;
+  cudaStream_t stream = nullptr;
+  tb::DeviceProgram dp{};
+  std::vector<void*> owned;            // device allocations
+  std::vector<tb::ProblemConst> pc_host;
+  tb::ProblemConst* pc_dev = nullptr;
+  bool pc_dirty = true;
+  int* status_dev = nullptr;
+  // staging for the host-buffer path
+  double *x_dev = nullptr, *g_dev = nullptr, *v_dev = nullptr;
+  tb::ProblemConst* pc_gather_dev = nullptr;
+  int max_ctas = 0;
+  long long launches = 0;
+
+  void SyncConsts() {
+    if (!pc_dirty) return;
+    Check(cudaMemcpyAsync(pc_dev, pc_host.data(), sizeof(tb::ProblemConst) * n, cudaMemcpyHostToDevice, stream), "H2D consts");
+    pc_dirty = false;
+  }
+  ~towr_b200_batch() {
+    cudaSetDevice(device);
+    for (void* p : owned) cudaFree(p);
+    if (stream) cudaStreamDestroy(stream);
+  }
+};
+
+extern "C" {
+
+const char* towr_b200_last_error(void) { return g_err.c_str(); }
+
+int towr_b200_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+int towr_b200_spec_defaults(towr_b200_spec* s) { return Guard([&] { if (!s) throw std::runtime_error("null spec"); tb::SpecDefaults(s); }); }
+int towr_b200_spec_robot(towr_b200_spec* s, int robot) { return Guard([&] { if (!s) throw std::runtime_error("null spec"); tb::SpecRobot(s, robot); }); }
+int towr_b200_spec_gait(towr_b200_spec* s, int combo, double T) { return Guard([&] { if (!s) throw std::runtime_error("null spec"); tb::SpecGait(s, combo, T); }); }
+int towr_b200_spec_nominal_states(towr_b200_spec* s, double gx, double gy, double gyaw) {
+  return Guard([&] { if (!s) throw std::runtime_error("null spec"); tb::SpecNominalStates(s, gx, gy, gyaw); });
+}
+int towr_b200_spec_optimize_durations(towr_b200_spec* s) {
+  return Guard([&] {
+    if (!s) throw std::runtime_error("null spec");
+    if (s->n_constraints >= TOWR_B200_MAX_CONSTRAINTS) throw std::runtime_error("constraint list full");
+    s->constraints[s->n_constraints++] = TOWR_B200_C_TOTAL_TIME;
+  });
+}
+
+int towr_b200_structure_create(const towr_b200_spec* s, towr_b200_structure** out) {
+  return Guard([&] {
+    if (!s || !out) throw std::runtime_error("null argument");
+    auto st = std::make_unique<towr_b200_structure>();
+    tb::BuildProgram(*s, st->hp);
+    *out = st.release();
+  });
+}
+void towr_b200_structure_destroy(towr_b200_structure* st) { delete st; }
+int towr_b200_structure_n_vars(const towr_b200_structure* st) { return st->hp.n_vars; }
+int towr_b200_structure_n_rows(const towr_b200_structure* st) { return st->hp.n_rows; }
+int towr_b200_structure_nnz(const towr_b200_structure* st) { return st->hp.nnz; }
+int towr_b200_structure_n_var_sets(const towr_b200_structure* st) { return static_cast<int>(st->hp.var_sets.size()); }
+int towr_b200_structure_n_con_sets(const towr_b200_structure* st) { return static_cast<int>(st->hp.con_sets.size()); }
+const char* towr_b200_structure_var_set_name(const towr_b200_structure* st, int i) { return st->hp.var_sets.at(i).name.c_str(); }
+int towr_b200_structure_var_set_rows(const towr_b200_structure* st, int i) { return st->hp.var_sets.at(i).n_vars; }
+const char* towr_b200_structure_con_set_name(const towr_b200_structure* st, int i) { return st->hp.con_sets.at(i).name.c_str(); }
+int towr_b200_structure_con_set_rows(const towr_b200_structure* st, int i) { return st->hp.con_sets.at(i).n_rows; }
+int towr_b200_structure_pattern(const towr_b200_structure* st, int* rows, int* cols) {
+  return Guard([&] {
+    if (!st) throw std::runtime_error("null structure");
+    if (rows) std::memcpy(rows, st->hp.pat_rows.data(), sizeof(int) * st->hp.nnz);
+    if (cols) std::memcpy(cols, st->hp.pat_cols.data(), sizeof(int) * st->hp.nnz);
+  });
+}
+int towr_b200_structure_accepts(const towr_b200_structure* st, const towr_b200_spec* s) {
+  return Guard([&] {
+    if (!st || !s) throw std::runtime_error("null argument");
+    tb::ValidateSpec(*s);
+    if (tb::StructureSignature(*s) != st->hp.signature) throw StructureError("spec belongs to a different structure class");
+  });
+}
+
+int towr_b200_problem_x0(const towr_b200_structure* st, const towr_b200_spec* s, double* x) {
+  return Guard([&] {
+    if (towr_b200_structure_accepts(st, s) != 0) throw StructureError(g_err);
+    tb::ProblemX0(st->hp, *s, x);
+  });
+}
+int towr_b200_problem_var_bounds(const towr_b200_structure* st, const towr_b200_spec* s, double* lo, double* up) {
+  return Guard([&] {
+    if (towr_b200_structure_accepts(st, s) != 0) throw StructureError(g_err);
+    tb::ProblemVarBounds(st->hp, *s, lo, up);
+  });
+}
+int towr_b200_problem_con_bounds(const towr_b200_structure* st, const towr_b200_spec* s, double* lo, double* up) {
+  return Guard([&] {
+    if (towr_b200_structure_accepts(st, s) != 0) throw StructureError(g_err);
+    tb::ProblemConBounds(st->hp, *s, lo, up);
+  });
+}
+
+int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int device, towr_b200_batch** out) {
+  return Guard([&] {
+    if (!st || !out || n_problems < 1) throw std::runtime_error("bad argument to batch_create");
+    if (towr_b200_device_count() < 1) throw CudaError("no CUDA device visible: this backend has no CPU fallback");
+    Check(cudaSetDevice(device), "cudaSetDevice");
+    auto b = std::make_unique<towr_b200_batch>();
+    b->st = st;
+    b->n = n_problems;
+    b->device = device;
+    Check(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    const tb::HostProgram& hp = st->hp;
+    tb::DeviceProgram& dp = b->dp;
+    dp.n_vars = hp.n_vars; dp.n_rows = hp.n_rows; dp.nnz = hp.nnz; dp.n_ee = hp.n_ee;
+    dp.n_node_values = hp.n_node_values;
+    dp.n_polys = static_cast<int>(hp.polys.size());
+    dp.n_segments = static_cast<int>(hp.segments.size());
+    dp.g_capacity = hp.g_capacity;
+    auto keep = [&](auto* p) { b->owned.push_back(const_cast<void*>(static_cast<const void*>(p))); return p; };
+    dp.node_src = keep(Upload(hp.node_src));
+    dp.polys = keep(Upload(hp.polys));
+    dp.samples = keep(Upload(hp.samples));
+    dp.items = keep(Upload(hp.items));
+    dp.entries = keep(Upload(hp.entries));
+    dp.B = keep(Upload(hp.B));
+    dp.segments = keep(Upload(hp.segments));
+    b->pc_host.assign(n_problems, tb::ProblemConst{});
+    Check(cudaMalloc(&b->pc_dev, sizeof(tb::ProblemConst) * n_problems), "cudaMalloc(consts)");
+    keep(b->pc_dev);
+    Check(cudaMalloc(&b->status_dev, sizeof(int) * n_problems), "cudaMalloc(status)");
+    keep(b->status_dev);
+    Check(cudaMemset(b->status_dev, 0, sizeof(int) * n_problems), "cudaMemset(status)");
+    cudaDeviceProp prop;
+    Check(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
+    if (tb::EvalSharedBytes(dp) > static_cast<size_t>(prop.sharedMemPerBlockOptin))
+      throw std::runtime_error("unsupported: structure class needs more shared memory per CTA than the device has");
+    int occ = tb::EvalOccupancy(dp);
+    if (occ < 1) throw CudaError("evaluation kernel cannot be resident on this device");
+    b->max_ctas = prop.multiProcessorCount * occ * 8;
+    *out = b.release();
+  });
+}
+void towr_b200_batch_destroy(towr_b200_batch* b) { delete b; }
+int towr_b200_batch_size(const towr_b200_batch* b) { return b ? b->n : 0; }
+
+int towr_b200_batch_set_problem(towr_b200_batch* b, int i, const towr_b200_spec* s) {
+  return Guard([&] {
+    if (!b || i < 0 || i >= b->n) throw std::runtime_error("problem index out of range");
+    if (towr_b200_structure_accepts(b->st, s) != 0) throw StructureError(g_err);
+    tb::FillProblemConst(*s, b->pc_host[i]);
+    b->pc_dirty = true;
+  });
+}
+int towr_b200_batch_set_all_problems(towr_b200_batch* b, const towr_b200_spec* s) {
+  return Guard([&] {
+    if (!b) throw std::runtime_error("null batch");
+    if (towr_b200_structure_accepts(b->st, s) != 0) throw StructureError(g_err);
+    tb::ProblemConst pc;
+    tb::FillProblemConst(*s, pc);
+    for (auto& p : b->pc_host) p = pc;
+    b->pc_dirty = true;
+  });
+}
+
+int towr_b200_batch_eval_device(towr_b200_batch* b, int n, int what, const double* d_x, double* d_g,
+                                double* d_jac_values, void* stream) {
+  return Guard([&] {
+    if (!b || n < 0 || n > b->n) throw std::runtime_error("bad problem count");
+    if (what < 1 || what > 3) throw std::runtime_error("what must be EVAL_G, EVAL_JAC or EVAL_BOTH");
+    if (!d_x || ((what & TOWR_B200_EVAL_G) && !d_g) || ((what & TOWR_B200_EVAL_JAC) && !d_jac_values))
+      throw std::runtime_error("null device buffer");
+    Check(cudaSetDevice(b->device), "cudaSetDevice");
+    cudaStream_t s = stream ? static_cast<cudaStream_t>(stream) : b->stream;
+    if (b->pc_dirty) {
+      b->SyncConsts();
+      Check(cudaStreamSynchronize(b->stream), "sync consts");
+    }
+    Check(tb::LaunchEval(b->dp, b->pc_dev, what, d_x, d_g, d_jac_values, b->status_dev, n, b->max_ctas, s), "launch");
+    b->launches += 1;
+  });
+}
+
+int towr_b200_batch_eval(towr_b200_batch* b, const int* ids, int n, int what, const double* x, double* g_out,
+                         double* jac_out) {
+  return Guard([&] {
+    if (!b || n < 0 || n > b->n) throw std::runtime_error("bad problem count");
+    if (what < 1 || what > 3) throw std::runtime_error("what must be EVAL_G, EVAL_JAC or EVAL_BOTH");
+    if (!x || ((what & TOWR_B200_EVAL_G) && !g_out) || ((what & TOWR_B200_EVAL_JAC) && !jac_out))
+      throw std::runtime_error("null host buffer");
+    if (n == 0) return;
+    Check(cudaSetDevice(b->device), "cudaSetDevice");
+    const tb::DeviceProgram& dp = b->dp;
+    auto ensure = [&](auto*& p, size_t per) {
+      if (!p) {
+        Check(cudaMalloc(&p, sizeof(*p) * per * b->n), "cudaMalloc(staging)");
+        b->owned.push_back(p);
+      }
+    };
+    ensure(b->x_dev, dp.n_vars);
+    if (what & TOWR_B200_EVAL_G) ensure(b->g_dev, dp.n_rows);
+    if (what & TOWR_B200_EVAL_JAC) ensure(b->v_dev, dp.nnz);
+    const tb::ProblemConst* pcs = b->pc_dev;
+    if (ids) {
+      // gather the constants of the requested problems (the callers' x rows are already in request order)
+      ensure(b->pc_gather_dev, 1);
+      std::vector<tb::ProblemConst> sel(n);
+      for (int i = 0; i < n; ++i) {
+        if (ids[i] < 0 || ids[i] >= b->n) throw std::runtime_error("problem id out of range");
+        sel[i] = b->pc_host[ids[i]];
+      }
+      Check(cudaMemcpyAsync(b->pc_gather_dev, sel.data(), sizeof(tb::ProblemConst) * n, cudaMemcpyHostToDevice, b->stream), "H2D consts");
+      Check(cudaStreamSynchronize(b->stream), "sync consts");
+      pcs = b->pc_gather_dev;
+    } else {
+      b->SyncConsts();
+    }
+    Check(cudaMemcpyAsync(b->x_dev, x, sizeof(double) * dp.n_vars * n, cudaMemcpyHostToDevice, b->stream), "H2D x");
+    Check(tb::LaunchEval(dp, pcs, what, b->x_dev, b->g_dev, b->v_dev, b->status_dev, n, b->max_ctas, b->stream), "launch");
+    b->launches += 1;
+    if (what & TOWR_B200_EVAL_G)
+      Check(cudaMemcpyAsync(g_out, b->g_dev, sizeof(double) * dp.n_rows * n, cudaMemcpyDeviceToHost, b->stream), "D2H g");
+    if (what & TOWR_B200_EVAL_JAC)
+      Check(cudaMemcpyAsync(jac_out, b->v_dev, sizeof(double) * dp.nnz * n, cudaMemcpyDeviceToHost, b->stream), "D2H values");
+    Check(cudaStreamSynchronize(b->stream), "eval");
+  });
+}
+
+int towr_b200_batch_status(towr_b200_batch* b, int n, int* status_out) {
+  return Guard([&] {
+    if (!b || n < 0 || n > b->n || !status_out) throw std::runtime_error("bad argument");
+    Check(cudaSetDevice(b->device), "cudaSetDevice");
+    Check(cudaMemcpy(status_out, b->status_dev, sizeof(int) * n, cudaMemcpyDeviceToHost), "D2H status");
+    Check(cudaMemset(b->status_dev, 0, sizeof(int) * n), "reset status");
+  });
+}
+
+long long towr_b200_batch_launch_count(const towr_b200_batch* b) { return b ? b->launches : 0; }
+
+}  // extern "C"

@@ -1,0 +1,84 @@
+// device_math.cuh — per-sample math of the hot path (FP64, CUDA cores; nothing here is a dense contraction).
+//
+//   spline point evaluation      towr/src/helpers/polynomial.cc:47-61 (same association: sum_c t^c * coeff_c)
+//   Euler ZYX kinematics         towr/src/helpers/euler_converter.cc:133-221,241-304
+//   single-rigid-body residual   towr/src/models/single_rigid_body_dynamics.cc:76-102
+// The Jacobian side does not replay Eigen's sparse row algebra: it forms the dense 3x3 partial derivatives of a
+// constraint w.r.t. the spline's (pos, vel, acc) once per sample; stage B multiplies them with Hermite basis values.
+#pragma once
+#include "program.h"
+#include "terrain.h"
+
+namespace tb {
+
+struct Pt3 { double p[3], v[3], a[3]; };
+
+enum { kNeedPos = 1, kNeedVel = 2, kNeedAcc = 4 };
+
+// nodes[slot*6 + deriv*3 + dim], coef[poly*6 + {0:c,3:d} + dim]
+template <int NEED>
+__device__ __forceinline__ void EvalSpline(const DeviceProgram& P, const double* __restrict__ nodes,
+                                           const double* __restrict__ coef, int sample, Pt3& o) {
+  const SampleRec* sr = P.samples + sample;
+  const int poly = __ldg(&sr->poly);
+  const double t = __ldg(&sr->t), t2 = __ldg(&sr->t2), t3 = __ldg(&sr->t3);
+  const int n0 = __ldg(&P.polys[poly].node0);
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    const double a = nodes[n0 * 6 + d], b = nodes[n0 * 6 + 3 + d];
+    const double c = coef[poly * 6 + d], dd = coef[poly * 6 + 3 + d];
+    if (NEED & kNeedPos) o.p[d] = ((a + t * b) + t2 * c) + t3 * dd;
+    if (NEED & kNeedVel) o.v[d] = (b + (2 * t) * c) + (3 * t2) * dd;
+    if (NEED & kNeedAcc) o.a[d] = 2.0 * c + (6 * t) * dd;
+  }
+}
+
+struct Trig { double sx, cx, sy, cy, sz, cz; };
+
+__device__ __forceinline__ Trig MakeTrig(const double e[3]) {
+  Trig t;
+  sincos(e[0], &t.sx, &t.cx);
+  sincos(e[1], &t.sy, &t.cy);
+  sincos(e[2], &t.sz, &t.cz);
+  return t;
+}
+
+// base-to-world rotation (euler_converter.cc:207-221), row-major R[3*i+j]
+__device__ __forceinline__ void RotationMatrix(const Trig& t, double R[9]) {
+  R[0] = t.cy * t.cz; R[1] = t.cz * t.sx * t.sy - t.cx * t.sz; R[2] = t.sx * t.sz + t.cx * t.cz * t.sy;
+  R[3] = t.cy * t.sz; R[4] = t.cx * t.cz + t.sx * t.sy * t.sz; R[5] = t.cx * t.sy * t.sz - t.cz * t.sx;
+  R[6] = -t.sy;       R[7] = t.cy * t.sx;                      R[8] = t.cx * t.cy;
+}
+
+// dR/d(euler c), c = 0 roll, 1 pitch, 2 yaw (coefficients of jac_x, jac_y, jac_z in euler_converter.cc:241-268)
+__device__ __forceinline__ void RotationMatrixDeriv(const Trig& t, int c, double D[9]) {
+  if (c == 0) {
+    D[0] = 0.0; D[1] = t.sx * t.sz + t.cx * t.cz * t.sy;  D[2] = t.cx * t.sz - t.cz * t.sx * t.sy;
+    D[3] = 0.0; D[4] = t.cx * t.sy * t.sz - t.cz * t.sx;  D[5] = -t.cx * t.cz - t.sx * t.sy * t.sz;
+    D[6] = 0.0; D[7] = t.cx * t.cy;                       D[8] = -t.cy * t.sx;
+  } else if (c == 1) {
+    D[0] = -t.cz * t.sy; D[1] = t.cy * t.cz * t.sx; D[2] = t.cx * t.cy * t.cz;
+    D[3] = -t.sy * t.sz; D[4] = t.cy * t.sx * t.sz; D[5] = t.cx * t.cy * t.sz;
+    D[6] = -t.cy;        D[7] = -t.sx * t.sy;       D[8] = -t.cx * t.sy;
+  } else {
+    D[0] = -t.cy * t.sz; D[1] = -t.cx * t.cz - t.sx * t.sy * t.sz; D[2] = t.cz * t.sx - t.cx * t.sy * t.sz;
+    D[3] = t.cy * t.cz;  D[4] = t.cz * t.sx * t.sy - t.cx * t.sz;  D[5] = t.sx * t.sz + t.cx * t.cz * t.sy;
+    D[6] = 0.0;          D[7] = 0.0;                               D[8] = 0.0;
+  }
+}
+
+__device__ __forceinline__ void MatVec3(const double A[9], const double v[3], double o[3]) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) o[i] = (A[3 * i] * v[0] + A[3 * i + 1] * v[1]) + A[3 * i + 2] * v[2];
+}
+__device__ __forceinline__ void MatTVec3(const double A[9], const double v[3], double o[3]) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) o[i] = (A[i] * v[0] + A[3 + i] * v[1]) + A[6 + i] * v[2];
+}
+__device__ __forceinline__ void Cross3(const double a[3], const double b[3], double o[3]) {
+  o[0] = a[1] * b[2] - a[2] * b[1];
+  o[1] = a[2] * b[0] - a[0] * b[2];
+  o[2] = a[0] * b[1] - a[1] * b[0];
+}
+
+}  // namespace tb

@@ -1,0 +1,15 @@
+// kernels.h — launcher interface between capi.cu and kernels.cu
+#pragma once
+#include <cuda_runtime.h>
+
+#include "../../include/towr_b200.h"
+#include "program.h"
+
+namespace tb {
+size_t EvalSharedBytes(const DeviceProgram& P);
+// evaluates problems 0..n_problems-1; x, g, vals, status are device pointers on the current device
+cudaError_t LaunchEval(const DeviceProgram& P, const ProblemConst* pcs, int what, const double* x, double* g,
+                       double* vals, int* status, int n_problems, int max_ctas, cudaStream_t stream);
+// resident CTAs per SM of the evaluation kernel for this program
+int EvalOccupancy(const DeviceProgram& P);
+}  // namespace tb

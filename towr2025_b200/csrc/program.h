@@ -1,0 +1,153 @@
+// program.h — the "evaluation program" of one structure class.
+//
+// A structure class fixes everything the sparsity pattern of TOWR's constraint Jacobian depends on
+// (robot leg count, phase counts, contact-at-start, fixed phase durations, sampling dt's, constraint
+// list).  The host builder (structure.cc) turns a towr_b200_spec into flat tables; the kernel
+// (kernels.cu) interprets them for every problem of a batch:
+//
+//   stage N  gather node values (pos/vel per spline node) from x            -> smem nodes[]
+//   stage C  Hermite coefficients c,d per (polynomial, dim)                 -> smem coef[]
+//   per segment:
+//     stage A  one thread per *item* (a time sample or a node of one constraint family):
+//              writes its constraint rows g and its partial-derivative slots -> smem G[]
+//     stage B  one thread per stored Jacobian entry: val = sum_t G[g+t*gs] * B[b+t*bs],
+//              coalesced store into the problem's value array
+//
+// B[] holds class constants (Hermite basis values at the fixed sample times, signs, 1/t_swing ...),
+// G[] holds per-problem quantities (forces, lever arms, rotation matrices, terrain slopes ...).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace tb {
+
+// ---- device-visible records (plain data, shared by host and device code) ---------------------------------------
+struct PolyRec {        // one cubic-Hermite polynomial of one spline
+  int node0;            // slot of its start node in nodes[] (end node = node0 + 1)
+  int pad;
+  double T, T2, T3;     // duration and std::pow(T,2), std::pow(T,3) (host-evaluated, polynomial.cc:97-104)
+};
+
+struct SampleRec {      // "spline S evaluated at global time t" for fixed durations (spline.cc:48-78)
+  int poly;             // global polynomial index
+  int pad;
+  double t, t2, t3;     // local time and std::pow(t,2), std::pow(t,3)
+};
+
+enum ItemType : int {
+  kItemDynamic = 0,     // dynamic_constraint.cc:63-148            6 rows per sample
+  kItemRom,             // range_of_motion_constraint.cc:72-131    3 rows per (sample, foot); one item serves all feet
+  kItemForce,           // force_constraint_discretized.cc:97-221  5 rows per (sample, foot)
+  kItemTerrainNode,     // terrain_constraint.cc:61-111            1 row per ee-motion node
+  kItemBaseHeightNode,  // base_height_constraint.cc:58-110        1 row per base-lin node
+  kItemSwingNode,       // swing_constraint.cc:54-108              4 rows per swing node
+  kItemSplineAcc,       // spline_acc_constraint.cc:48-80          3 rows per junction
+  kItemTotalDuration,   // total_duration_constraint.cc:48-72
+};
+
+constexpr int kMaxEE = 4;
+// indices into ItemRec::s
+enum { kSBaseLin = 0, kSBaseAng = 1, kSMotion = 2, kSForce = 2 + kMaxEE, kSTorque = 2 + 2 * kMaxEE, kSCount = 2 + 3 * kMaxEE };
+
+struct ItemRec {
+  int type;
+  int gslot;            // first G slot of this item (segment-relative)
+  int ee;               // foot (force / terrain / swing) ; splineacc: unused
+  int n_ee;
+  int row[kMaxEE];      // first constraint row written (absolute in g); RoM: one per foot
+  int s[kSCount];       // SampleRec indices; node-based items: node slot / polynomial index in s[0]
+};
+
+struct EntryRec {       // one stored Jacobian entry, in storage (row-major) order
+  uint32_t w0;          // g (16 bits) | gs (12 bits) << 16 | (nt-1) (2 bits) << 28
+  uint32_t w1;          // b (30 bits) | bs (1 bit) << 31
+};
+
+struct SegmentRec {
+  int item0, n_items;   // items of this segment
+  int entry0, n_entries;// entries fed by this segment (contiguous in storage order)
+  int g_size;           // G slots used
+  int pad;
+};
+
+// slots 0.. of every segment's G buffer
+enum { kGOne = 0, kGMass = 1, kGReserved = 2 };
+
+struct DeviceProgram {  // pointers into device memory (one copy per GPU)
+  int n_vars, n_rows, nnz, n_ee;
+  int n_node_values;    // 6 per node
+  int n_polys;
+  int n_segments;
+  int g_capacity;       // max g_size over segments
+  const int* node_src;  // [n_node_values] column of x, or -1 for a value pinned to 0
+  const PolyRec* polys;
+  const SampleRec* samples;
+  const ItemRec* items;
+  const EntryRec* entries;
+  const double* B;
+  const SegmentRec* segments;
+};
+
+struct ProblemConst {   // per-problem constants read by the kernels
+  double mass;
+  double I[9];          // body inertia tensor, row-major, off-diagonals negated (single_rigid_body_dynamics.cc:36-44)
+  int terrain_id;
+  int pad;
+};
+
+// ---- host-side description ------------------------------------------------------------------------------------
+struct NodeRef { int node, deriv, dim; };
+
+enum SetKind { kBaseLin = 0, kBaseAng, kEEMotion, kEEAng, kEEForce, kEETorque, kEESchedule };
+
+struct VarSet {         // one ifopt variable set = one column block
+  std::string name;
+  int kind = 0;
+  int ee = -1;
+  int col0 = 0, n_vars = 0;
+  int n_nodes = 0;
+  int node_slot0 = -1;  // first node slot in the device nodes[] array (-1: not staged)
+  int poly0 = -1;       // first global polynomial index (-1: no spline staged)
+  bool in_nlp = true;   // ee-schedule sets exist always but are columns only when durations are optimised
+  std::vector<std::vector<NodeRef>> refs;      // per variable: the node values it writes
+  std::vector<int> poly_phase, poly_in_phase, polys_in_phase;
+  std::vector<char> poly_const;
+  std::vector<double> poly_T;
+  int n_polys() const { return n_nodes - 1; }
+  bool IsConstantNode(int node) const;
+  std::vector<int> NonConstantNodes() const;
+  int PolyAtStartOfPhase(int phase) const;
+  int PhaseOfNode(int node) const;
+  int OptIndex(int node, int deriv, int dim) const;   // nodes_variables.cc:44-54 (-1 if not optimised)
+};
+
+struct ConSet { std::string name; int row0, n_rows; };
+
+// what ConstraintSet::GetBounds returns for one row (values depend on per-problem model data)
+enum RowBoundKind { kBoundZero = 0, kBoundTerrainSwing, kBoundRom, kBoundForceNormal, kBoundLE0, kBoundGE0,
+                    kBoundBaseHeight, kBoundTotalDuration };
+struct RowBound { int kind, ee, dim; };
+
+struct HostProgram {
+  int n_vars = 0, n_rows = 0, nnz = 0, n_ee = 0;
+  bool optimize_durations = false;
+  double total_time = 0.0;
+  std::vector<VarSet> var_sets;      // NLP column order (base-lin, base-ang, ee-motion.., ee-ang.., ee-force.., ee-torque.., [ee-schedule..])
+  std::vector<ConSet> con_sets;
+  std::vector<RowBound> row_bounds;  // one per constraint row
+  std::vector<int> pat_rows, pat_cols;
+  std::vector<int> node_src;
+  std::vector<PolyRec> polys;
+  std::vector<SampleRec> samples;
+  std::vector<ItemRec> items;
+  std::vector<EntryRec> entries;
+  std::vector<double> B;
+  std::vector<SegmentRec> segments;
+  int g_capacity = 0;
+  int n_node_values = 0;
+  std::string signature;   // canonical text of every structural field (structure_accepts compares it)
+  const VarSet* Find(int kind, int ee = -1) const;
+};
+
+}  // namespace tb

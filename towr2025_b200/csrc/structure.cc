@@ -1,0 +1,579 @@
+// structure.cc — builds the evaluation program (pattern + item/entry tables) of a structure class.
+//
+// The stored-entry rules restate, per constraint family, which coefficients the reference's Eigen
+// code stores: coeffRef inserts, sparse products keep structural unions, Cross() has
+// six off-diagonal entries (single_rigid_body_dynamics.cc:47-57), DerivOfRotVecMult(inverse) has no
+// roll column in its first row (euler_converter.cc:223-268).  Row order = constraint-set order of
+// nlp_formulation.cc:365-378, column order = variable-set order of nlp_formulation.cc:81-101; inside a
+// row entries are sorted by column (ifopt's setFromTriplets on a row-major matrix).
+#include "structure.h"
+
+#include <algorithm>
+#include <array>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <sstream>
+#include <stdexcept>
+
+namespace tb {
+
+std::vector<double> SampleTimes(double T, double dt) {
+  std::vector<double> ts;
+  double t = 0.0;
+  ts.push_back(t);
+  const int n = static_cast<int>(std::floor(T / dt));
+  for (int i = 0; i < n; ++i) {
+    t += dt;                 // repeated addition, not i*dt
+    ts.push_back(t);
+  }
+  ts.push_back(T);           // may duplicate the last sample
+  return ts;
+}
+
+void HermiteBasis(double T, double t, double o[12]) {
+  const double t2 = std::pow(t, 2), t3 = std::pow(t, 3);
+  const double T2 = std::pow(T, 2), T3 = std::pow(T, 3);
+  // position
+  o[0] = (2 * t3) / T3 - (3 * t2) / T2 + 1;   o[1] = t - (2 * t2) / T + t3 / T2;
+  o[2] = (3 * t2) / T2 - (2 * t3) / T3;       o[3] = t3 / T2 - t2 / T;
+  // velocity
+  o[4] = (6 * t2) / T3 - (6 * t) / T2;        o[5] = (3 * t2) / T2 - (4 * t) / T + 1;
+  o[6] = (6 * t) / T2 - (6 * t2) / T3;        o[7] = (3 * t2) / T2 - (2 * t) / T;
+  // acceleration
+  o[8] = (12 * t) / T3 - 6 / T2;              o[9] = (6 * t) / T2 - 4 / T;
+  o[10] = 6 / T2 - (12 * t) / T3;             o[11] = (6 * t) / T2 - 2 / T;
+}
+
+int SegmentId(double t_global, const std::vector<double>& durations) {
+  double acc = 0.0;
+  for (size_t i = 0; i < durations.size(); ++i) {
+    acc += durations[i];
+    if (acc >= t_global - 1e-10) return static_cast<int>(i);
+  }
+  return static_cast<int>(durations.size()) - 1;
+}
+
+double LocalTime(double t_global, int id, const std::vector<double>& durations) {
+  double t = t_global;
+  for (int i = 0; i < id; ++i) t -= durations[i];
+  return t;
+}
+
+namespace {
+
+struct Term { int g = 0, gs = 0, nt = 1, b = 0, bs = 0; };
+struct ColBasis { int idx, dim; double v[3]; };   // v[dx]: d{pos,vel,acc}/d(variable idx)
+struct SplineAt { int sample; int poly; double t_local; };
+
+class Builder {
+ public:
+  Builder(const towr_b200_spec& s, HostProgram& hp, const std::vector<char>* new_segment_before_group)
+      : s_(s), hp_(hp), plan_(new_segment_before_group) {}
+
+  void Run();
+  std::vector<int> group_g_size;    // filled by Run(): G slots each group allocated
+
+ private:
+  // ---- tables
+  int AddB(double v) {
+    uint64_t bits;
+    std::memcpy(&bits, &v, 8);
+    auto it = b1_.find(bits);
+    if (it != b1_.end()) return it->second;
+    int i = static_cast<int>(hp_.B.size());
+    hp_.B.push_back(v);
+    b1_[bits] = i;
+    return i;
+  }
+  int AddB3(double a, double b, double c) {
+    std::array<uint64_t, 3> key;
+    std::memcpy(&key[0], &a, 8); std::memcpy(&key[1], &b, 8); std::memcpy(&key[2], &c, 8);
+    auto it = b3_.find(key);
+    if (it != b3_.end()) return it->second;
+    int i = static_cast<int>(hp_.B.size());
+    hp_.B.push_back(a); hp_.B.push_back(b); hp_.B.push_back(c);
+    b3_[key] = i;
+    return i;
+  }
+  SplineAt At(const VarSet& set, double t_global) {
+    SplineAt a;
+    a.poly = SegmentId(t_global, set.poly_T);
+    a.t_local = LocalTime(t_global, a.poly, set.poly_T);
+    SampleRec r;
+    r.poly = set.poly0 + a.poly;
+    r.pad = 0;
+    r.t = a.t_local;
+    r.t2 = std::pow(a.t_local, 2);
+    r.t3 = std::pow(a.t_local, 3);
+    a.sample = static_cast<int>(hp_.samples.size());
+    hp_.samples.push_back(r);
+    return a;
+  }
+  // stored columns of NodeSpline::GetJacobianWrtNodes(poly, t_local, *) with their values for all three dx
+  // (node_spline.cc:84-112): ascending idx, start side before end side, contributions added from 0.0
+  std::vector<ColBasis> Columns(const VarSet& set, int poly, double t_local) const {
+    double hb[12];
+    HermiteBasis(set.poly_T[poly], t_local, hb);
+    std::vector<ColBasis> cols;
+    for (int idx = 0; idx < set.n_vars; ++idx) {
+      ColBasis cb{idx, -1, {0.0, 0.0, 0.0}};
+      for (const NodeRef& r : set.refs[idx])
+        for (int side = 0; side < 2; ++side)
+          if (poly + side == r.node) {
+            cb.dim = r.dim;
+            for (int dx = 0; dx < 3; ++dx) cb.v[dx] += hb[dx * 4 + side * 2 + r.deriv];
+          }
+      if (cb.dim >= 0) cols.push_back(cb);
+    }
+    return cols;
+  }
+
+  // ---- segments / groups
+  void BeginGroup() {
+    int gi = static_cast<int>(group_g_size.size());
+    bool new_seg = hp_.segments.empty() || (plan_ ? (*plan_)[gi] != 0 : true);
+    if (new_seg) {
+      CloseSegment();
+      SegmentRec sg{};
+      sg.item0 = static_cast<int>(hp_.items.size());
+      sg.entry0 = static_cast<int>(hp_.entries.size());
+      sg.g_size = kGReserved;
+      hp_.segments.push_back(sg);
+    }
+    group_g_size.push_back(0);
+  }
+  void CloseSegment() {
+    if (hp_.segments.empty()) return;
+    SegmentRec& sg = hp_.segments.back();
+    sg.n_items = static_cast<int>(hp_.items.size()) - sg.item0;
+    sg.n_entries = static_cast<int>(hp_.entries.size()) - sg.entry0;
+    hp_.g_capacity = std::max(hp_.g_capacity, sg.g_size);
+  }
+  int AllocG(int n) {
+    SegmentRec& sg = hp_.segments.back();
+    int g = sg.g_size;
+    sg.g_size += n;
+    group_g_size.back() += n;
+    if (sg.g_size > 65535) throw std::runtime_error("segment needs more than 65535 G slots");
+    return g;
+  }
+
+  // ---- rows of the constraint set being emitted
+  void BeginSet(const std::string& name, int n_rows) {
+    set_row0_ = hp_.n_rows;
+    hp_.con_sets.push_back(ConSet{name, hp_.n_rows, n_rows});
+    hp_.n_rows += n_rows;
+    rows_.assign(n_rows, {});
+    hp_.row_bounds.resize(hp_.n_rows, RowBound{kBoundZero, 0, 0});
+  }
+  void Bound(int row_local, int kind, int ee = 0, int dim = 0) { hp_.row_bounds.at(set_row0_ + row_local) = RowBound{kind, ee, dim}; }
+  void Add(int row_local, int col, const Term& t, bool overwrite = false) {
+    auto& r = rows_.at(row_local);
+    for (auto& e : r)
+      if (e.first == col) {
+        if (!overwrite) throw std::runtime_error("duplicate Jacobian entry emitted");
+        e.second = t;
+        return;
+      }
+    r.emplace_back(col, t);
+  }
+  void EndSet() {
+    for (size_t r = 0; r < rows_.size(); ++r) {
+      auto& row = rows_[r];
+      std::stable_sort(row.begin(), row.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+      for (auto& e : row) {
+        const Term& t = e.second;
+        if (t.g < 0 || t.g > 65535 || t.gs < 0 || t.gs > 4095 || t.nt < 1 || t.nt > 4 || t.b < 0 || t.b >= (1 << 30))
+          throw std::runtime_error("entry descriptor out of range");
+        EntryRec er;
+        er.w0 = static_cast<uint32_t>(t.g) | (static_cast<uint32_t>(t.gs) << 16) | (static_cast<uint32_t>(t.nt - 1) << 28);
+        er.w1 = static_cast<uint32_t>(t.b) | (static_cast<uint32_t>(t.bs) << 31);
+        hp_.entries.push_back(er);
+        hp_.pat_rows.push_back(set_row0_ + static_cast<int>(r));
+        hp_.pat_cols.push_back(e.first);
+      }
+    }
+    rows_.clear();
+  }
+  ItemRec NewItem(int type) const {
+    ItemRec it;
+    std::memset(&it, 0, sizeof(it));
+    it.type = type;
+    it.n_ee = s_.n_ee;
+    return it;
+  }
+  const VarSet& Set(int kind, int ee = -1) const {
+    const VarSet* v = hp_.Find(kind, ee);
+    if (!v) throw std::runtime_error("variable set missing");
+    return *v;
+  }
+
+  void EmitTerrain(int ee);
+  void EmitDynamic();
+  void EmitSplineAcc();
+  void EmitRom();
+  void EmitForceDisc(int ee);
+  void EmitSwing(int ee);
+  void EmitBaseHeight();
+  void EmitHeightRows(const VarSet& set, int item_type, int ee);
+
+  const towr_b200_spec& s_;
+  HostProgram& hp_;
+  const std::vector<char>* plan_;
+  std::map<uint64_t, int> b1_;
+  std::map<std::array<uint64_t, 3>, int> b3_;
+  std::vector<std::vector<std::pair<int, Term>>> rows_;
+  int set_row0_ = 0;
+};
+
+// Cross(v)(r,d) = sign * v[k] for r != d (single_rigid_body_dynamics.cc:47-57)
+inline void CrossEntry(int r, int d, int* k, double* sign) {
+  *k = 3 - r - d;
+  *sign = ((d - r + 3) % 3 == 2) ? 1.0 : -1.0;
+}
+
+// TerrainConstraint / BaseHeightConstraint: one row per node id >= 1: z - h(x,y) [- offset];
+// entries (row, z) = 1, (row, x) = -h_x, (row, y) = -h_y  (terrain_constraint.cc:93-111, base_height_constraint.cc:90-110)
+void Builder::EmitHeightRows(const VarSet& set, int item_type, int ee) {
+  const int one = AddB(1.0);
+  for (int node = 1; node < set.n_nodes; ++node) {
+    ItemRec it = NewItem(item_type);
+    it.ee = ee;
+    it.row[0] = set_row0_ + node - 1;
+    it.s[0] = set.node_slot0 + node;
+    it.gslot = AllocG(2);
+    hp_.items.push_back(it);
+    if (item_type == kItemBaseHeightNode) Bound(node - 1, kBoundBaseHeight);
+    else Bound(node - 1, set.IsConstantNode(node) ? kBoundZero : kBoundTerrainSwing, ee);
+    Term tz; tz.g = kGOne; tz.b = one;
+    Add(node - 1, set.col0 + set.OptIndex(node, 0, 2), tz, true);
+    for (int dim = 0; dim < 2; ++dim) {
+      Term t; t.g = it.gslot + dim; t.b = one;
+      Add(node - 1, set.col0 + set.OptIndex(node, 0, dim), t, true);
+    }
+  }
+}
+
+void Builder::EmitTerrain(int ee) {
+  const VarSet& m = Set(kEEMotion, ee);
+  BeginGroup();
+  BeginSet("terrain-" + m.name, m.n_nodes - 1);
+  EmitHeightRows(m, kItemTerrainNode, ee);
+  EndSet();
+}
+
+void Builder::EmitBaseHeight() {
+  const VarSet& lin = Set(kBaseLin);
+  BeginGroup();
+  BeginSet("base-height-" + lin.name, lin.n_nodes - 1);
+  EmitHeightRows(lin, kItemBaseHeightNode, 0);
+  EndSet();
+}
+
+// DynamicConstraint, 6 rows per sample (dynamic_constraint.cc:57-126 with single_rigid_body_dynamics.cc:104-204)
+void Builder::EmitDynamic() {
+  const int E = s_.n_ee;
+  const VarSet& lin = Set(kBaseLin);
+  const VarSet& ang = Set(kBaseAng);
+  const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_dynamic);
+  BeginGroup();
+  BeginSet("dynamic", static_cast<int>(ts.size()) * 6);
+  for (size_t k = 0; k < ts.size(); ++k) {
+    const double t = ts[k];
+    const int r0 = static_cast<int>(k) * 6;
+    ItemRec it = NewItem(kItemDynamic);
+    it.row[0] = set_row0_ + r0;
+    const int g0 = AllocG(27 + 6 * E);
+    it.gslot = g0;
+    const int gAp = g0, gF = g0 + 27, gR = g0 + 27 + 3 * E;
+
+    SplineAt al = At(lin, t), aa = At(ang, t);
+    it.s[kSBaseLin] = al.sample;
+    it.s[kSBaseAng] = aa.sample;
+    // base-lin: angular rows -sum_e Cross(f_e) J_pos, linear rows m J_acc
+    for (const ColBasis& c : Columns(lin, al.poly, al.t_local)) {
+      for (int r = 0; r < 3; ++r) {
+        if (r == c.dim) continue;
+        int kk; double sg;
+        CrossEntry(r, c.dim, &kk, &sg);
+        Term tm; tm.g = gF + kk; tm.gs = 3; tm.nt = E; tm.b = AddB(-(sg * c.v[0]));
+        Add(r0 + r, lin.col0 + c.idx, tm);
+      }
+      Term tm; tm.g = kGMass; tm.b = AddB(c.v[2]);
+      Add(r0 + 3 + c.dim, lin.col0 + c.idx, tm);
+    }
+    // base-ang: full 3 x 12 block, value = A_pos*Bp + A_vel*Bv + A_acc*Ba
+    for (const ColBasis& c : Columns(ang, aa.poly, aa.t_local))
+      for (int r = 0; r < 3; ++r) {
+        Term tm; tm.g = gAp + r * 3 + c.dim; tm.gs = 9; tm.nt = 3; tm.b = AddB3(c.v[0], c.v[1], c.v[2]); tm.bs = 1;
+        Add(r0 + r, ang.col0 + c.idx, tm);
+      }
+    for (int e = 0; e < E; ++e) {
+      const VarSet& mo = Set(kEEMotion, e);
+      const VarSet& fo = Set(kEEForce, e);
+      const VarSet& to = Set(kEETorque, e);
+      SplineAt am = At(mo, t), af = At(fo, t), at = At(to, t);
+      it.s[kSMotion + e] = am.sample;
+      it.s[kSForce + e] = af.sample;
+      it.s[kSTorque + e] = at.sample;
+      // ee-motion: Cross(f_e) J_p on the angular rows
+      for (const ColBasis& c : Columns(mo, am.poly, am.t_local))
+        for (int r = 0; r < 3; ++r) {
+          if (r == c.dim) continue;
+          int kk; double sg;
+          CrossEntry(r, c.dim, &kk, &sg);
+          Term tm; tm.g = gF + 3 * e + kk; tm.b = AddB(sg * c.v[0]);
+          Add(r0 + r, mo.col0 + c.idx, tm);
+        }
+      // ee-force: Cross(c - p_e) J_f on the angular rows, -J_f on the linear rows
+      for (const ColBasis& c : Columns(fo, af.poly, af.t_local)) {
+        for (int r = 0; r < 3; ++r) {
+          if (r == c.dim) continue;
+          int kk; double sg;
+          CrossEntry(r, c.dim, &kk, &sg);
+          Term tm; tm.g = gR + 3 * e + kk; tm.b = AddB(sg * c.v[0]);
+          Add(r0 + r, fo.col0 + c.idx, tm);
+        }
+        Term tm; tm.g = kGOne; tm.b = AddB(-c.v[0]);
+        Add(r0 + 3 + c.dim, fo.col0 + c.idx, tm);
+      }
+      // ee-torque: -J_tau on the angular rows
+      for (const ColBasis& c : Columns(to, at.poly, at.t_local)) {
+        Term tm; tm.g = kGOne; tm.b = AddB(-c.v[0]);
+        Add(r0 + c.dim, to.col0 + c.idx, tm);
+      }
+    }
+    hp_.items.push_back(it);
+  }
+  EndSet();
+}
+
+// SplineAccConstraint for base-lin and base-ang: acc at the end of poly j minus acc at the start of poly j+1
+// (spline_acc_constraint.cc:48-80); the Jacobian is constant
+void Builder::EmitSplineAcc() {
+  BeginGroup();
+  for (int which = 0; which < 2; ++which) {
+    const VarSet& set = Set(which == 0 ? kBaseLin : kBaseAng);
+    const int nj = set.n_polys() - 1;
+    BeginSet("splineacc-" + set.name, 3 * nj);
+    for (int j = 0; j < nj; ++j) {
+      ItemRec it = NewItem(kItemSplineAcc);
+      it.row[0] = set_row0_ + 3 * j;
+      it.s[0] = set.poly0 + j;
+      it.gslot = 0;
+      hp_.items.push_back(it);
+      std::vector<ColBasis> prev = Columns(set, j, set.poly_T[j]);
+      std::vector<ColBasis> next = Columns(set, j + 1, 0.0);
+      struct Pair { int dim = 0; double prev = 0.0, next = 0.0; };   // missing side contributes 0.0
+      std::map<int, Pair> merged;
+      for (const ColBasis& c : prev) { merged[c.idx].dim = c.dim; merged[c.idx].prev = c.v[2]; }
+      for (const ColBasis& c : next) { merged[c.idx].dim = c.dim; merged[c.idx].next = c.v[2]; }
+      for (auto& m : merged) {
+        Term tm; tm.g = kGOne; tm.b = AddB(m.second.prev - m.second.next);
+        Add(3 * j + m.second.dim, set.col0 + m.first, tm);
+      }
+    }
+    EndSet();
+  }
+}
+
+// RangeOfMotionConstraint, one set per foot, 3 rows per sample (range_of_motion_constraint.cc:66-131).
+// One item per sample serves all feet: G = R^T (9) then d(R^T r_e)/d(euler) (9) per foot.
+void Builder::EmitRom() {
+  const int E = s_.n_ee;
+  const VarSet& lin = Set(kBaseLin);
+  const VarSet& ang = Set(kBaseAng);
+  const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_range_of_motion);
+  const int K = static_cast<int>(ts.size());
+  BeginGroup();
+  const int item0 = static_cast<int>(hp_.items.size());
+  struct PerSample { int g0; SplineAt al, aa; };
+  std::vector<PerSample> ps(K);
+  for (int k = 0; k < K; ++k) {
+    ItemRec it = NewItem(kItemRom);
+    ps[k].g0 = AllocG(9 + 9 * E);
+    it.gslot = ps[k].g0;
+    ps[k].al = At(lin, ts[k]);
+    ps[k].aa = At(ang, ts[k]);
+    it.s[kSBaseLin] = ps[k].al.sample;
+    it.s[kSBaseAng] = ps[k].aa.sample;
+    hp_.items.push_back(it);
+  }
+  for (int e = 0; e < E; ++e) {
+    const VarSet& mo = Set(kEEMotion, e);
+    BeginSet("rangeofmotion-" + std::to_string(e), 3 * K);
+    for (int k = 0; k < K; ++k) {
+      ItemRec& it = hp_.items[item0 + k];
+      it.row[e] = set_row0_ + 3 * k;
+      SplineAt am = At(mo, ts[k]);
+      it.s[kSMotion + e] = am.sample;
+      for (int r = 0; r < 3; ++r) Bound(3 * k + r, kBoundRom, e, r);
+      const int gRT = ps[k].g0, gD = ps[k].g0 + 9 + 9 * e;
+      for (const ColBasis& c : Columns(lin, ps[k].al.poly, ps[k].al.t_local))
+        for (int r = 0; r < 3; ++r) {            // (-1 * R^T) J_c
+          Term tm; tm.g = gRT + r * 3 + c.dim; tm.b = AddB(-c.v[0]);
+          Add(3 * k + r, lin.col0 + c.idx, tm);
+        }
+      for (const ColBasis& c : Columns(ang, ps[k].aa.poly, ps[k].aa.t_local))
+        for (int r = 0; r < 3; ++r) {            // DerivOfRotVecMult(t, r_W, inverse): no roll column in row X
+          if (r == 0 && c.dim == 0) continue;
+          Term tm; tm.g = gD + r * 3 + c.dim; tm.b = AddB(c.v[0]);
+          Add(3 * k + r, ang.col0 + c.idx, tm);
+        }
+      for (const ColBasis& c : Columns(mo, am.poly, am.t_local))
+        for (int r = 0; r < 3; ++r) {            // R^T J_p
+          Term tm; tm.g = gRT + r * 3 + c.dim; tm.b = AddB(c.v[0]);
+          Add(3 * k + r, mo.col0 + c.idx, tm);
+        }
+    }
+    EndSet();
+  }
+}
+
+// ForceConstraintDiscretized, 5 rows per sample (force_constraint_discretized.cc:97-221)
+void Builder::EmitForceDisc(int ee) {
+  const VarSet& mo = Set(kEEMotion, ee);
+  const VarSet& fo = Set(kEEForce, ee);
+  const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_force);
+  BeginGroup();
+  BeginSet("force-disc-" + fo.name, static_cast<int>(ts.size()) * 5);
+  for (size_t k = 0; k < ts.size(); ++k) {
+    ItemRec it = NewItem(kItemForce);
+    it.ee = ee;
+    it.row[0] = set_row0_ + static_cast<int>(k) * 5;
+    it.gslot = AllocG(15);
+    SplineAt am = At(mo, ts[k]), af = At(fo, ts[k]);
+    it.s[kSMotion + ee] = am.sample;
+    it.s[kSForce + ee] = af.sample;
+    hp_.items.push_back(it);
+    const int bk[5] = {kBoundForceNormal, kBoundLE0, kBoundGE0, kBoundLE0, kBoundGE0};
+    for (int i = 0; i < 5; ++i) Bound(static_cast<int>(k) * 5 + i, bk[i], ee);
+    for (const ColBasis& c : Columns(fo, af.poly, af.t_local))
+      for (int i = 0; i < 5; ++i) {              // b_i . J_f
+        Term tm; tm.g = it.gslot + 3 * i + c.dim; tm.b = AddB(c.v[0]);
+        Add(static_cast<int>(k) * 5 + i, fo.col0 + c.idx, tm);
+      }
+    // the ee-motion block is stored only where the terrain's second derivatives are non-zero
+    // (force_constraint_discretized.cc:58): never for the terrains a curvature-free class admits.
+  }
+  EndSet();
+}
+
+// SwingConstraint (swing_constraint.cc:54-108): per swing node and dim in {x,y} a position and a velocity row
+void Builder::EmitSwing(int ee) {
+  const VarSet& mo = Set(kEEMotion, ee);
+  const std::vector<int> nodes = mo.NonConstantNodes();
+  const double t_swing_avg = 0.3;                // swing_constraint.h:68
+  BeginGroup();
+  BeginSet("swing-" + mo.name, static_cast<int>(nodes.size()) * 4);
+  int row = 0;
+  for (int node : nodes) {
+    ItemRec it = NewItem(kItemSwingNode);
+    it.ee = ee;
+    it.row[0] = set_row0_ + row;
+    it.s[0] = mo.node_slot0 + node;
+    hp_.items.push_back(it);
+    for (int dim = 0; dim < 2; ++dim) {
+      auto put = [&](int r, int n, int deriv, double v) {
+        int idx = mo.OptIndex(n, deriv, dim);
+        if (idx < 0) throw std::runtime_error("swing constraint touches a node value that is not optimised");
+        Term tm; tm.g = kGOne; tm.b = AddB(v);
+        Add(r, mo.col0 + idx, tm, true);
+      };
+      put(row, node, 0, 1.0);
+      put(row, node + 1, 0, -0.5);
+      put(row, node - 1, 0, -0.5);
+      row++;
+      put(row, node, 1, 1.0);
+      put(row, node + 1, 0, -1.0 / t_swing_avg);
+      put(row, node - 1, 0, +1.0 / t_swing_avg);
+      row++;
+    }
+  }
+  EndSet();
+}
+
+void Builder::Run() {
+  if (hp_.optimize_durations) throw std::runtime_error("unsupported: optimised phase durations (PhaseSpline path)");
+  hp_.n_rows = 0;
+  for (int i = 0; i < s_.n_constraints; ++i) {
+    switch (s_.constraints[i]) {
+      case TOWR_B200_C_TERRAIN:
+        for (int e = 0; e < s_.n_ee; ++e) EmitTerrain(e);
+        break;
+      case TOWR_B200_C_DYNAMIC: EmitDynamic(); break;
+      case TOWR_B200_C_BASE_ACC: EmitSplineAcc(); break;
+      case TOWR_B200_C_ENDEFFECTOR_ROM: EmitRom(); break;
+      case TOWR_B200_C_FORCE:
+        if (!(s_.dt_constraint_force > 0.0)) throw std::runtime_error("unsupported: node-based ForceConstraint");
+        for (int e = 0; e < s_.n_ee; ++e) EmitForceDisc(e);
+        break;
+      case TOWR_B200_C_SWING:
+        for (int e = 0; e < s_.n_ee; ++e) EmitSwing(e);
+        break;
+      case TOWR_B200_C_BASE_HEIGHT: EmitBaseHeight(); break;
+      case TOWR_B200_C_TOTAL_TIME:
+      case TOWR_B200_C_TERRAIN_HARD:
+      case TOWR_B200_C_TORQUE:
+      case TOWR_B200_C_BASE_ROM:
+        throw std::runtime_error("unsupported: constraint " + std::to_string(s_.constraints[i]) + " not built yet");
+      default: throw std::runtime_error("constraint not defined!");   // nlp_formulation.cc:396
+    }
+  }
+  CloseSegment();
+  hp_.nnz = static_cast<int>(hp_.entries.size());
+}
+
+void ResetTables(HostProgram& hp) {
+  hp.con_sets.clear(); hp.pat_rows.clear(); hp.pat_cols.clear(); hp.row_bounds.clear();
+  hp.samples.clear(); hp.items.clear(); hp.entries.clear(); hp.B.clear(); hp.segments.clear();
+  hp.g_capacity = 0; hp.n_rows = 0; hp.nnz = 0;
+}
+
+}  // namespace
+
+std::string StructureSignature(const towr_b200_spec& s) {
+  // every field the tables above depend on, printed exactly
+  std::ostringstream o;
+  o.precision(17);
+  o << "E" << s.n_ee;
+  for (int e = 0; e < s.n_ee; ++e) {
+    o << "|f" << e << ":" << s.in_contact_at_start[e] << ":";
+    for (int i = 0; i < s.n_phases[e]; ++i) o << s.phase_durations[e][i] << ",";
+  }
+  o << "|c";
+  for (int i = 0; i < s.n_constraints; ++i) o << s.constraints[i] << ",";
+  o << "|dt" << s.dt_constraint_dynamic << "," << s.dt_constraint_range_of_motion << "," << s.dt_constraint_base_motion
+    << "," << s.dt_constraint_force << "," << s.dt_constraint_torque << "|bp" << s.duration_base_polynomial
+    << "|pp" << s.ee_polynomials_per_swing_phase << "," << s.force_polynomials_per_stance_phase << ","
+    << s.torque_polynomials_per_stance_phase;
+  return o.str();
+}
+
+void BuildProgram(const towr_b200_spec& s, HostProgram& hp) {
+  BuildLayout(s, hp);
+  hp.signature = StructureSignature(s);
+  // pass 1: one segment per group, to learn each group's G footprint
+  ResetTables(hp);
+  Builder sizing(s, hp, nullptr);
+  sizing.Run();
+  int cap = 3072;
+  if (const char* env = std::getenv("TOWR_B200_GCAP")) cap = std::max(64, std::atoi(env));
+  std::vector<char> plan(sizing.group_g_size.size(), 0);
+  int used = kGReserved;
+  for (size_t g = 0; g < plan.size(); ++g) {
+    if (g == 0 || used + sizing.group_g_size[g] > cap) {
+      plan[g] = 1;
+      used = kGReserved;
+    }
+    used += sizing.group_g_size[g];
+  }
+  // pass 2: the real tables
+  ResetTables(hp);
+  Builder real(s, hp, &plan);
+  real.Run();
+}
+
+}  // namespace tb

@@ -1,0 +1,35 @@
+// structure.h — internal host API of the structure-class builder.
+#pragma once
+#include <vector>
+
+#include "../../include/towr_b200.h"
+#include "program.h"
+
+namespace tb {
+
+// layout.cc
+double TotalTime(const towr_b200_spec& s);
+std::vector<double> BasePolyDurations(const towr_b200_spec& s);
+bool OptimizesDurations(const towr_b200_spec& s);
+void ValidateSpec(const towr_b200_spec& s);
+void BuildLayout(const towr_b200_spec& s, HostProgram& hp);
+
+// structure.cc
+// sample times of a TimeDiscretizationConstraint (time_discretization_constraint.cc:41-49)
+std::vector<double> SampleTimes(double T, double dt);
+// Hermite basis d{pos,vel,acc}(t)/d{start p, start v, end p, end v}: out[dx*4 + k] (polynomial.cc:106-234)
+void HermiteBasis(double T, double t, double out[12]);
+// segment lookup with the 1e-10 junction rule (spline.cc:48-78)
+int SegmentId(double t_global, const std::vector<double>& durations);
+double LocalTime(double t_global, int id, const std::vector<double>& durations);
+void BuildProgram(const towr_b200_spec& s, HostProgram& hp);
+std::string StructureSignature(const towr_b200_spec& s);
+
+// formulation.cc
+void ProblemX0(const HostProgram& hp, const towr_b200_spec& s, double* x);
+void ProblemVarBounds(const HostProgram& hp, const towr_b200_spec& s, double* lo, double* up);
+void ProblemConBounds(const HostProgram& hp, const towr_b200_spec& s, double* lo, double* up);
+void FillProblemConst(const towr_b200_spec& s, ProblemConst& pc);
+double TerrainHeight(int terrain_id, double x, double y);
+
+}  // namespace tb
