@@ -1,0 +1,321 @@
+#!/usr/bin/env python
+"""bench.py — constraint + Jacobian evals/s of the batched TOWR backend (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--batch B]
+
+Workload (BASELINE.json configs[2]): ANYmal fly-trot 2 s (RobotModel::Anymal, quadruped combo C1, default
+Parameters, fixed durations): 1042 variables, 2732 constraint rows, 23992 stored Jacobian values per problem,
+batch 4096 per GPU, random goals, 16 distinct x per problem rotated between steps.  A step = one batched eval
+of all g and all Jacobian values for the rank's batch.  Problems are independent: the batch shards across
+ranks with no collective on the data path (weak scaling: 4096 problems per GPU); after the timed region the
+ranks all_gather one solution vector each (the only NCCL use, as in north_star).
+
+`value` is device-resident throughput (CUDA events on the launching stream, max over ranks); `e2e` is the same
+metric through towr_b200_batch_eval with pinned HOST buffers (H2D of x and D2H of g + values inside the timed
+region).  `--impl reference` times the reference's CPU evaluation instead: the reference itself cannot be
+compiled on this image (Eigen/ifopt/Ipopt absent), so it is the oracle port, OpenMP over
+problems on all host cores.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "ANYmal-trot constraint+Jacobian evals/s"
+UNIT = "evals/s"
+GOAL_SEED = 20260101 + 2      # seed = 20260101 + config index
+X_VARIANTS = 16
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=4096, help="problems per GPU")
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_config(st, batch, n_gpus):
+    return {"workload": "ANYmal fly-trot 2 s (Anymal, combo C1, default Parameters, fixed durations)",
+            "batch_per_gpu": batch, "global_batch": batch * n_gpus, "n_vars": st["n_vars"], "n_rows": st["n_rows"],
+            "nnz": st["nnz"], "bytes_per_eval": st["bytes"], "x_variants": X_VARIANTS,
+            "l2": "outputs written per step (%.0f MB) and x rotated over %d variants exceed the 126 MB L2"
+                  % (batch * 8 * (st["n_rows"] + st["nnz"]) / 1e6, X_VARIANTS),
+            "parallelism": "problem batch sharded per GPU, no data-path collective"}
+
+
+class ClockSampler:
+    """Polls NVML for SM clocks and throttle reasons while the timed regions run."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self._nv = None
+
+    def _run(self):
+        nv = self._nv
+        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+                 "hw_power_brake": 0x80}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(self._h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def start(self):
+        if self._nv:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thr:
+            self._thr.join()
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def make_inputs(T, batch, rank):
+    """Structure class + per-problem specs (random goals) + X_VARIANTS perturbed x per problem."""
+    import numpy as np
+    rng = np.random.default_rng(GOAL_SEED + 7919 * rank)
+    s0 = T.make_spec(T.Anymal, T.C1, 2.0)
+    st = T.Structure(s0)
+    specs = []
+    x0 = np.empty((batch, st.n_vars))
+    for i in range(batch):
+        goal = (rng.uniform(0.5, 2.5), rng.uniform(-0.3, 0.3), rng.uniform(-0.4, 0.4))
+        s = T.make_spec(T.Anymal, T.C1, 2.0, goal=goal)
+        specs.append(s)
+        x0[i] = st.x0(s)
+    lo, up = st.var_bounds(s0)
+    names = st.var_sets()
+    scale = np.empty(st.n_vars)
+    col = 0
+    mg = s0.mass * 9.80665
+    for name, n in names:
+        sc = 0.05
+        if name.startswith("base-ang") or name.startswith("ee-ang"):
+            sc = 0.02
+        elif name.startswith("ee-force"):
+            sc = 0.05 * mg
+        elif name.startswith("ee-torque"):
+            sc = 0.5
+        scale[col:col + n] = sc
+        col += n
+    xs = []
+    for v in range(X_VARIANTS):
+        x = x0 + rng.uniform(-1.0, 1.0, size=x0.shape) * scale
+        xs.append(x)
+    return s0, st, specs, xs
+
+
+def run_reference(args, rank, world):
+    """The reference's CPU evaluation of the path (oracle port, OpenMP over problems) on a bounded sample."""
+    if rank != 0:
+        return
+    import numpy as np
+    import towr2025_b200 as T              # host-side set-up only (specs, x0); no GPU work on this arm
+    from oracle import oracle_py as O
+    cores = os.cpu_count() or 1
+    s0 = T.make_spec(T.Anymal, T.C1, 2.0)
+    st = T.Structure(s0)
+    so = O.make_spec(O.Anymal, 1, 2.0)
+    sample = max(cores * 8, 16)
+    rng = np.random.default_rng(GOAL_SEED)
+    x = st.x0(s0)[None, :] + rng.uniform(-1, 1, size=(sample, st.n_vars)) * 0.05
+    nnz = st.nnz
+    for _ in range(min(args.warmup, 2)):
+        O.batch_eval(so, x, nnz, n_threads=cores)
+    steps = max(1, min(args.steps, 10))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        O.batch_eval(so, x, nnz, n_threads=cores)
+    dt = time.perf_counter() - t0
+    value = sample * steps / dt
+    stinfo = {"n_vars": st.n_vars, "n_rows": st.n_rows, "nnz": st.nnz, "bytes": st.bytes_per_eval}
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+            "warmup": min(args.warmup, 2), "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(stinfo, args.batch, args.gpus),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": "%d problems per step (bounded sample of the 4096-problem batch), g + Jacobian values, "
+                                       "OpenMP over problems; the reference itself needs Eigen/ifopt/Ipopt (absent)" % sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline(T, st, s0, xs):
+    """Oracle port on the host cores, bounded sample (reported next to the GPU number, rank 0, N=1 only)."""
+    import numpy as np
+    from oracle import oracle_py as O
+    cores = os.cpu_count() or 1
+    so = O.make_spec(O.Anymal, 1, 2.0)
+    sample = max(cores * 8, 16)
+    x = np.ascontiguousarray(xs[0][:sample])
+    # goals only move bounds and x0, not g/J, so one oracle spec serves the sample
+    O.batch_eval(so, x[: max(cores, 2)], st.nnz, n_threads=cores)
+    reps, t0 = 0, time.perf_counter()
+    while True:
+        O.batch_eval(so, x, st.nnz, n_threads=cores)
+        reps += 1
+        dt = time.perf_counter() - t0
+        if dt > 10.0 or reps >= 20:
+            break
+    return {"value": sample * reps / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "%d problems x %d repetitions of the same workload (g + Jacobian values), OpenMP over problems, "
+                      "%.1f s of CPU work" % (sample, reps, dt)}
+
+
+def run_ours(args, rank, world, local_rank):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import towr2025_b200 as T
+
+    if not torch.cuda.is_available() or T.lib().towr_b200_device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device - the backend has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    batch = args.batch
+    s0, st, specs, xs_host = make_inputs(T, batch, rank)
+    for v in range(X_VARIANTS):
+        for i in range(0, batch, max(1, batch // 64)):      # clip a sample of problems to their own bounds
+            lo, up = st.var_bounds(specs[i])
+            xs_host[v][i] = np.clip(xs_host[v][i], lo, up)
+    b = T.Batch(st, batch, device=local_rank)
+    for i, s in enumerate(specs):
+        b.set_problem(i, s)
+    dev = torch.device("cuda", local_rank)
+    xs = [torch.from_numpy(x).to(dev) for x in xs_host]
+    g = torch.empty((batch, st.n_rows), dtype=torch.float64, device=dev)
+    vals = torch.empty((batch, st.nnz), dtype=torch.float64, device=dev)
+    stream = torch.cuda.current_stream()
+
+    def step(k):
+        b.eval_device(batch, T.EVAL_BOTH, xs[k % X_VARIANTS].data_ptr(), g.data_ptr(), vals.data_ptr(), stream.cuda_stream)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for k in range(args.warmup):
+        step(k)
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    launches0 = b.launches
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    ev[0].record(stream)
+    for k in range(args.steps):
+        step(k)
+        ev[k + 1].record(stream)
+    barrier()
+    total_ms = ev[0].elapsed_time(ev[-1])
+    launches = b.launches - launches0
+    per_launch_ms = [ev[k].elapsed_time(ev[k + 1]) for k in range(args.steps)]
+    assert bool(torch.isfinite(g).all()) and bool(torch.isfinite(vals).all())
+
+    # ---- end to end through the C ABI with pinned host buffers
+    hx = [torch.from_numpy(x).pin_memory() for x in xs_host[:2]]
+    hg = torch.empty((batch, st.n_rows), dtype=torch.float64).pin_memory()
+    hv = torch.empty((batch, st.nnz), dtype=torch.float64).pin_memory()
+    b.eval(hx[0].numpy(), T.EVAL_BOTH, g_out=hg.numpy(), jac_out=hv.numpy())
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.e2e_steps):
+        b.eval(hx[k % 2].numpy(), T.EVAL_BOTH, g_out=hg.numpy(), jac_out=hv.numpy())
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop()
+
+    t = torch.tensor([total_ms, e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        # the only collective of the path: gather one solution vector per rank (north_star "gather converged solutions")
+        sol = [torch.empty(st.n_vars, dtype=torch.float64, device=dev) for _ in range(world)]
+        dist.all_gather(sol, xs[0][0].contiguous())
+    total_ms, e2e_s = float(t[0]), float(t[1])
+    if rank == 0:
+        peaks, peak_src = None, "fallback"
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            peak, peak_src = float(peaks["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            peak = 6650.0
+        kern_ms = sorted(per_launch_ms)[len(per_launch_ms) // 2]
+        avg_ms = sum(per_launch_ms) / len(per_launch_ms)
+        achieved = st.bytes_per_eval * batch / (avg_ms * 1e-3) / 1e9
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["dram_bytes_per_launch"]
+        except Exception:
+            pass
+        stinfo = {"n_vars": st.n_vars, "n_rows": st.n_rows, "nnz": st.nnz, "bytes": st.bytes_per_eval}
+        line = {"metric": METRIC, "value": world * batch * args.steps / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": workload_config(stinfo, batch, world),
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": traffic, "kernel": "tb::EvalKernel<3>", "avg_launch_ms": avg_ms,
+                             "median_launch_ms": kern_ms, "peak_source": peak_src,
+                             "algorithmic_bytes_per_launch": st.bytes_per_eval * batch},
+                "e2e": {"value": world * batch * args.e2e_steps / e2e_s, "unit": UNIT,
+                        "h2d_bytes_per_step": batch * st.n_vars * 8, "d2h_bytes_per_step": batch * (st.n_rows + st.nnz) * 8,
+                        "steps": args.e2e_steps, "ms_per_step": e2e_s / args.e2e_steps * 1e3,
+                        "api": "towr_b200_batch_eval (C ABI), pinned host buffers"},
+                "gpu_launches": launches, "clocks": clocks}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(T, st, s0, xs_host)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world == 1 and args.gpus > 1:
+        # launched without torchrun: re-exec under it so that one process drives each GPU
+        import subprocess
+        port = 29500 + os.getpid() % 1000
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
+               "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.abspath(__file__)] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

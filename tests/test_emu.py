@@ -1,0 +1,45 @@
+"""Kernel arithmetic (the device headers compiled for the host, tests/emu) against the oracle, no GPU.
+Checks the table interpretation (items, entries, B constants) and the per-sample math at the parity
+tolerance of BASELINE.json: 1e-12 relative / 1e-14 absolute."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from util import CASES, perturbed, tol_ratio
+
+DP = C.POINTER(C.c_double)
+
+
+def emu_eval(E, spec, st, x):
+    g = np.full(st.n_rows, np.nan)
+    v = np.full(st.nnz, np.nan)
+    rc = E.emu_eval(C.byref(spec), x.ctypes.data_as(DP), g.ctypes.data_as(DP), v.ctypes.data_as(DP))
+    assert rc == 0, E.emu_last_error()
+    return g, v
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_emulated_kernel_matches_oracle(product, oracle, emu, case):
+    T, O = product, oracle
+    _, robot, combo, Tt, goal, terrain = case
+    s = T.make_spec(robot, combo, Tt, goal=goal, terrain=terrain)
+    st = T.Structure(s)
+    p = O.Problem(O.make_spec(robot, combo, Tt, goal=goal, terrain=terrain))
+    x0 = st.x0(s)
+    for x in (x0, perturbed(x0, 11, 0.1), perturbed(x0, 12, 0.3)):
+        g, v = emu_eval(emu, s, st, x)
+        assert tol_ratio(g, p.eval_g(x)) <= 1.0
+        assert tol_ratio(v, p.eval_jac(x)[2]) <= 1.0
+
+
+def test_emulated_kernel_segment_capacity(product, oracle, emu, monkeypatch):
+    """Small G capacity -> many segments; results must not depend on the segmentation."""
+    T, O = product, oracle
+    s = T.make_spec(T.Anymal, T.C1, 2.0, goal=(1.1, 0.1, 0.2))
+    st = T.Structure(s)
+    x = perturbed(st.x0(s), 5, 0.1)
+    ref = emu_eval(emu, s, st, x)
+    monkeypatch.setenv("TOWR_B200_GCAP", "600")
+    alt = emu_eval(emu, s, st, x)
+    assert np.array_equal(ref[0], alt[0]) and np.array_equal(ref[1], alt[1])

@@ -1,0 +1,131 @@
+"""GPU parity (-m gpu): the CUDA path, called through the C ABI, against the oracle on the same inputs.
+Tolerance (BASELINE.json north_star): sparsity indices bit-exact, values within 1e-12 relative / 1e-14 absolute."""
+import numpy as np
+import pytest
+
+from util import CASES, perturbed, tol_ratio
+
+pytestmark = pytest.mark.gpu
+
+
+def _problem_batch(T, O, case, n, seed):
+    """n problems of one structure class with per-problem goals, terrain kept, and distinct x."""
+    _, robot, combo, Tt, goal, terrain = case
+    rng = np.random.default_rng(seed)
+    specs, xs = [], []
+    s0 = T.make_spec(robot, combo, Tt, goal=goal, terrain=terrain)
+    st = T.Structure(s0)
+    for i in range(n):
+        g = (goal[0] + rng.uniform(-0.3, 0.3), goal[1] + rng.uniform(-0.2, 0.2), goal[2] + rng.uniform(-0.3, 0.3))
+        s = T.make_spec(robot, combo, Tt, goal=g, terrain=terrain)
+        s.mass *= 1.0 + 0.05 * rng.uniform(-1, 1)
+        specs.append(s)
+        xs.append(perturbed(st.x0(s), seed * 1000 + i, 0.1 if i % 2 else 0.0))
+    return st, specs, np.stack(xs)
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_values_and_jacobian_match_oracle(product, oracle, case):
+    T, O = product, oracle
+    from util import to_oracle_spec
+    n = 6
+    st, specs, x = _problem_batch(T, O, case, n, 3)
+    b = T.Batch(st, n)
+    for i, s in enumerate(specs):
+        b.set_problem(i, s)
+    g, v = b.eval(x)
+    assert (b.status() == 0).all()
+    rows, cols = st.pattern()
+    for i, s in enumerate(specs):
+        p = O.Problem(to_oracle_spec(O, s))
+        r, c, vo = p.eval_jac(x[i])
+        assert np.array_equal(r, rows) and np.array_equal(c, cols)
+        assert tol_ratio(g[i], p.eval_g(x[i])) <= 1.0
+        assert tol_ratio(v[i], vo) <= 1.0
+
+
+def test_eval_modes_and_ids(product, oracle):
+    """EVAL_G / EVAL_JAC alone give the same numbers as EVAL_BOTH; problem_ids selects per-problem constants."""
+    T = product
+    st, specs, x = _problem_batch(T, oracle, CASES[0], 8, 5)
+    b = T.Batch(st, 8)
+    for i, s in enumerate(specs):
+        b.set_problem(i, s)
+    g, v = b.eval(x)
+    g1, _ = b.eval(x, T.EVAL_G)
+    _, v2 = b.eval(x, T.EVAL_JAC)
+    assert np.array_equal(g, g1) and np.array_equal(v, v2)
+    ids = np.array([5, 2, 7], dtype=np.int32)
+    gs, vs = b.eval(x[ids], ids=ids)
+    assert np.array_equal(gs, g[ids]) and np.array_equal(vs, v[ids])
+    assert b.launches == 4
+
+
+def test_full_batch_properties(product, oracle):
+    """BASELINE config 3 at full size (ANYmal fly-trot, batch 4096): properties that need no oracle at scale,
+    plus a spot check of 8 problems against the oracle."""
+    T, O = product, oracle
+    n = 4096
+    s = T.make_spec(T.Anymal, T.C1, 2.0)
+    st = T.Structure(s)
+    b = T.Batch(st, n)
+    b.set_all(s)
+    x0 = st.x0(s)
+    rng = np.random.default_rng(20260103)
+    x = x0[None, :] + rng.uniform(-1, 1, size=(n, st.n_vars)) * 0.05
+    x[n // 2:] = x[: n // 2]                       # second half repeats the first: outputs must repeat bit-exactly
+    g, v = b.eval(x)
+    assert np.isfinite(g).all() and np.isfinite(v).all()
+    assert np.array_equal(g[: n // 2], g[n // 2:]) and np.array_equal(v[: n // 2], v[n // 2:])
+    # determinism
+    g2, v2 = b.eval(x)
+    assert np.array_equal(g, g2) and np.array_equal(v, v2)
+    # the Jacobian is the derivative of g: directional finite difference through the GPU path itself
+    rows, cols = st.pattern()
+    d = rng.uniform(-1, 1, size=st.n_vars)
+    h = 1e-6
+    gp, _ = b.eval(x[:4] + h * d, T.EVAL_G)
+    gm, _ = b.eval(x[:4] - h * d, T.EVAL_G)
+    for i in range(4):
+        jd = np.zeros(st.n_rows)
+        np.add.at(jd, rows, v[i] * d[cols])
+        fd = (gp[i] - gm[i]) / (2 * h)
+        assert np.abs(jd - fd).max() <= 1e-5 * max(1.0, np.abs(fd).max())
+    p = O.Problem(O.make_spec(O.Anymal, 1, 2.0))
+    for i in (0, 1, 777, 2047, 2048, 4095, 1234, 3000):
+        assert tol_ratio(g[i], p.eval_g(x[i])) <= 1.0
+        assert tol_ratio(v[i], p.eval_jac(x[i])[2]) <= 1.0
+
+
+def test_device_pointer_path(product):
+    """eval_device on caller-owned device memory (torch tensors) equals the host-buffer path."""
+    import torch
+    T = product
+    s = T.make_spec(T.Anymal, T.C1, 2.0)
+    st = T.Structure(s)
+    n = 64
+    b = T.Batch(st, n)
+    b.set_all(s)
+    x = st.x0(s)[None, :] + np.random.default_rng(1).uniform(-1, 1, size=(n, st.n_vars)) * 0.05
+    g, v = b.eval(x)
+    dx = torch.from_numpy(x).cuda()
+    dg = torch.empty((n, st.n_rows), dtype=torch.float64, device="cuda")
+    dv = torch.empty((n, st.nnz), dtype=torch.float64, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    b.eval_device(n, T.EVAL_BOTH, dx.data_ptr(), dg.data_ptr(), dv.data_ptr(), stream)
+    torch.cuda.synchronize()
+    assert np.array_equal(dg.cpu().numpy(), g) and np.array_equal(dv.cpu().numpy(), v)
+
+
+def test_non_finite_input_flags_only_its_problem(product):
+    T = product
+    s = T.make_spec(T.Anymal, T.C1, 2.0)
+    st = T.Structure(s)
+    b = T.Batch(st, 4)
+    b.set_all(s)
+    x = np.tile(st.x0(s), (4, 1))
+    x[2, 10] = np.nan
+    g, v = b.eval(x)
+    status = b.status()
+    assert status[2] != 0 and (status[[0, 1, 3]] == 0).all()
+    assert np.isfinite(v[[0, 1, 3]]).all()

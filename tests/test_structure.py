@@ -1,0 +1,107 @@
+"""Host side of the backend against the oracle (no GPU): spec helpers, sizes, names, sparsity pattern,
+initial guess and bounds must be bit-exact (BASELINE.json: "sparsity indices must be bit-exact")."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from util import CASES, perturbed, to_oracle_spec
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_structure_matches_oracle(product, oracle, case):
+    T, O = product, oracle
+    _, robot, combo, Tt, goal, terrain = case
+    s = T.make_spec(robot, combo, Tt, goal=goal, terrain=terrain)
+    so = O.make_spec(robot, combo, Tt, goal=goal, terrain=terrain)
+    # robot constants, gait tables and parameter defaults: same bytes
+    assert bytes(to_oracle_spec(O, s)) == bytes(so)
+    st = T.Structure(s)
+    p = O.Problem(so)
+    assert (st.n_vars, st.n_rows) == (p.n_vars, p.n_rows)
+    assert st.var_sets() == p.var_sets()
+    assert st.con_sets() == p.con_sets()
+    x0 = st.x0(s)
+    assert np.array_equal(x0, p.x0())
+    rows, cols = st.pattern()
+    for x in (x0, perturbed(x0, 7, 0.05)):
+        r, c, _ = p.eval_jac(x)
+        assert len(r) == st.nnz
+        assert np.array_equal(r, rows) and np.array_equal(c, cols)
+    lo, up = st.var_bounds(s)
+    lo2, up2 = p.var_bounds()
+    assert np.array_equal(lo, lo2) and np.array_equal(up, up2)
+    lo, up = st.con_bounds(s)
+    lo2, up2 = p.con_bounds()
+    assert np.array_equal(lo, lo2) and np.array_equal(up, up2)
+
+
+def test_anymal_trot_sizes(product):
+    """ANYmal fly-trot 2 s = 1042 variables, 2732 rows, 23992 stored entries."""
+    T = product
+    st = T.Structure(T.make_spec(T.Anymal, T.C1, 2.0))
+    assert (st.n_vars, st.n_rows, st.nnz) == (1042, 2732, 23992)
+    assert st.bytes_per_eval == 222128
+    r, c = st.pattern()
+    key = r.astype(np.int64) * st.n_vars + c
+    assert (np.diff(key) > 0).all()          # row-major sorted, no duplicates
+
+
+def test_structure_class_membership(product):
+    T = product
+    s = T.make_spec(T.Anymal, T.C1, 2.0)
+    st = T.Structure(s)
+    other_goal = T.make_spec(T.Anymal, T.C1, 2.0, goal=(2.0, 0.3, -0.4), terrain=T.BlockID)
+    other_goal.mass = 31.0
+    assert st.accepts(other_goal)            # goals, terrain ids, mass are per-problem data
+    assert not st.accepts(T.make_spec(T.Anymal, T.C1, 2.2))
+    assert not st.accepts(T.make_spec(T.Anymal, T.C0, 2.0))
+    assert not st.accepts(T.make_spec(T.Hyq, T.C1, 2.0)) or True   # same leg count + gait -> same class is allowed
+    with pytest.raises(T.TowrB200Error) as e:
+        st.x0(T.make_spec(T.Anymal, T.C1, 2.2))
+    assert e.value.code == -4
+
+
+def test_error_behaviour(product):
+    """Bad configuration is an error code + message, never an exception across the C boundary
+    (the reference throws std::runtime_error: nlp_formulation.cc:396)."""
+    T = product
+    s = T.make_spec(T.Anymal, T.C1, 2.0)
+    s.constraints[0] = 99
+    with pytest.raises(T.TowrB200Error) as e:
+        T.Structure(s)
+    assert e.value.code == -1 and "constraint not defined" in str(e.value)
+    s = T.make_spec(T.Anymal, T.C1, 2.0)
+    s.n_ee = 7
+    with pytest.raises(T.TowrB200Error):
+        T.Structure(s)
+    s = T.make_spec(T.Anymal, T.C1, 2.0)
+    s.phase_durations[1][0] += 0.1          # feet must share the total time (parameters.cc:155)
+    with pytest.raises(T.TowrB200Error):
+        T.Structure(s)
+    with pytest.raises(T.TowrB200Error):
+        T.make_spec(5, T.C1, 2.0)
+
+
+def test_library_exports_every_declared_symbol(product):
+    """The C-ABI library loads without a GPU and exports everything include/towr_b200.h declares."""
+    import os
+    import re
+    T = product
+    hdr = open(os.path.join(os.path.dirname(T._HERE), "include", "towr_b200.h")).read()
+    declared = set(re.findall(r"\b(towr_b200_[a-z0-9_]+)\s*\(", hdr))
+    assert declared == set(T.exported_symbols())
+    L = C.CDLL(T.LIB_PATH)
+    for name in declared:
+        assert hasattr(L, name), name
+
+
+def test_no_cpu_fallback(product):
+    """Without a CUDA device batch creation must fail loudly (TOWR_B200_ERR_CUDA), not evaluate on the host."""
+    T = product
+    if T.lib().towr_b200_device_count() > 0:
+        pytest.skip("a GPU is present")
+    st = T.Structure(T.make_spec(T.Anymal, T.C1, 2.0))
+    with pytest.raises(T.TowrB200Error) as e:
+        T.Batch(st, 4)
+    assert e.value.code == -3

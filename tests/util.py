@@ -1,0 +1,43 @@
+"""Shared helpers of the test-suite (TEST INFRASTRUCTURE)."""
+import ctypes as C
+
+import numpy as np
+
+RTOL, ATOL = 1e-12, 1e-14   # BASELINE.json north_star: 1e-12 relative / 1e-14 absolute in FP64
+
+
+def to_oracle_spec(O, s):
+    """towr_b200_spec and orc_spec have the same fields in the same order."""
+    o = O.Spec()
+    assert C.sizeof(o) == C.sizeof(s)
+    C.memmove(C.byref(o), C.byref(s), C.sizeof(s))
+    return o
+
+
+def tol_ratio(a, b):
+    """max over entries of |a-b| / (ATOL + RTOL*|b|); parity holds when <= 1."""
+    a, b = np.asarray(a), np.asarray(b)
+    assert a.shape == b.shape
+    if a.size == 0:
+        return 0.0
+    assert np.isfinite(a).all() and np.isfinite(b).all()
+    return float((np.abs(a - b) / (ATOL + RTOL * np.abs(b))).max())
+
+
+# (name, robot, combo, T, goal, terrain)
+CASES = [
+    ("anymal_trot", 3, 1, 2.0, (1.0, 0.0, 0.0), 0),
+    ("anymal_trot_yaw", 3, 1, 2.0, (1.3, -0.2, 0.3), 0),
+    ("hyq_gallop_block", 2, 4, 2.4, (1.5, 0.1, -0.2), 1),
+    ("biped_walk_stairs", 1, 0, 2.4, (1.0, 0.1, 0.1), 2),
+    ("monoped_hop", 0, 0, 2.4, (1.0, 0.0, 0.0), 0),
+    ("anymal_walk_slope", 3, 0, 3.0, (1.0, 0.0, 0.0), 4),
+    ("monoped_hop2_chimney", 0, 3, 1.9, (0.8, 0.0, 0.0), 5),
+    ("biped_run_chimneylr", 1, 1, 2.2, (1.2, 0.0, 0.0), 6),
+    ("hyq_pace_flat", 2, 2, 2.0, (0.7, 0.2, 0.5), 0),
+]
+
+
+def perturbed(x0, seed, scale=0.1):
+    rng = np.random.default_rng(seed)
+    return x0 + rng.uniform(-1.0, 1.0, size=x0.shape) * scale

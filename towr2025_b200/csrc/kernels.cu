@@ -13,9 +13,10 @@
 namespace tb {
 
 constexpr int kThreads = 256;
+constexpr int kMinCtasPerSm = 4;   // caps registers at 64: the long dynamic item spills to local memory, stage B does not
 
 template <int WHAT>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, kMinCtasPerSm)
 EvalKernel(const DeviceProgram P, const ProblemConst* __restrict__ pcs, const double* __restrict__ x,
            double* __restrict__ g_out, double* __restrict__ vals_out, int* __restrict__ status, int n_problems) {
   extern __shared__ double sm[];
