@@ -140,13 +140,16 @@ int towr_b200_batch_set_all_problems(towr_b200_batch* b, const towr_b200_spec* s
 int towr_b200_batch_eval(towr_b200_batch* b, const int* problem_ids, int n, int what, const double* x,
                          double* g_out, double* jac_values_out);
 /* Device-buffer evaluation of problems 0..n-1: pointers are device memory on the batch's GPU,
- * same shapes; `stream` is a cudaStream_t (NULL = the batch's own stream).  Asynchronous. */
+ * same shapes; `stream` is a cudaStream_t (NULL = CUDA's default stream).  Asynchronous: the launch is ordered
+ * on `stream` only. */
 int towr_b200_batch_eval_device(towr_b200_batch* b, int n, int what, const double* d_x, double* d_g,
                                 double* d_jac_values, void* stream);
 /* per-problem status of the last eval: bit 0 = non-finite value in g, bit 1 = non-finite Jacobian value */
 int towr_b200_batch_status(towr_b200_batch* b, int n, int* status_out);
 /* kernel launches issued by this batch so far (for bench.py's gpu_launches) */
 long long towr_b200_batch_launch_count(const towr_b200_batch* b);
+/* the batch's own non-blocking cudaStream_t (the one towr_b200_batch_eval works on) */
+void* towr_b200_batch_stream(const towr_b200_batch* b);
 
 #ifdef __cplusplus
 }

@@ -30,39 +30,36 @@ extern "C" int emu_eval(const towr_b200_spec* s, const double* x, double* g, dou
   try {
     HostProgram hp;
     BuildProgram(*s, hp);
-    DeviceProgram P{};
-    P.n_vars = hp.n_vars; P.n_rows = hp.n_rows; P.nnz = hp.nnz; P.n_ee = hp.n_ee;
-    P.n_node_values = hp.n_node_values; P.n_polys = (int)hp.polys.size(); P.n_segments = (int)hp.segments.size();
-    P.g_capacity = hp.g_capacity;
-    P.node_src = hp.node_src.data(); P.polys = hp.polys.data(); P.samples = hp.samples.data();
-    P.items = hp.items.data(); P.entries = hp.entries.data(); P.B = hp.B.data(); P.segments = hp.segments.data();
+    const BlobLayout& L = hp.blob;
     ProblemConst pc;
     FillProblemConst(*s, pc);
-    std::vector<double> nodes(P.n_node_values), coef(6 * P.n_polys), G(P.g_capacity);
-    for (int i = 0; i < P.n_node_values; ++i) nodes[i] = P.node_src[i] >= 0 ? x[P.node_src[i]] : 0.0;
-    for (int i = 0; i < 3 * P.n_polys; ++i) {
-      int poly = i / 3, d = i % 3;
-      const PolyRec& pr = P.polys[poly];
-      int n0 = pr.node0;
-      double p0 = nodes[n0 * 6 + d], v0 = nodes[n0 * 6 + 3 + d], p1 = nodes[n0 * 6 + 6 + d], v1 = nodes[n0 * 6 + 9 + d];
-      coef[poly * 6 + d] = -(3.0 * (p0 - p1) + pr.T * (2.0 * v0 + v1)) / pr.T2;
-      coef[poly * 6 + 3 + d] = (2.0 * (p0 - p1) + pr.T * (v0 + v1)) / pr.T3;
-    }
     ItemCtx cx;
-    cx.P = &P; cx.nodes = nodes.data(); cx.coef = coef.data(); cx.G = G.data(); cx.g = g; cx.pc = &pc;
-    for (int sgi = 0; sgi < P.n_segments; ++sgi) {
-      const SegmentRec sg = P.segments[sgi];
+    cx.T = MakeTables(hp.blob_data.data(), L);
+    std::vector<double> nodes(L.n_node_values), coef(6 * L.n_polys), G(hp.g_capacity);
+    for (int i = 0; i < L.n_node_values; ++i) nodes[i] = cx.T.node_src[i] != 0xFFFF ? x[cx.T.node_src[i]] : 0.0;
+    for (int i = 0; i < 3 * L.n_polys; ++i) {
+      int poly = i / 3, d = i % 3;
+      uint32_t pr = cx.T.polys[poly];
+      int n0 = pr & 0xFFFF;
+      const double* du = cx.T.durs + 3 * (pr >> 16);
+      double p0 = nodes[n0 * 6 + d], v0 = nodes[n0 * 6 + 3 + d], p1 = nodes[n0 * 6 + 6 + d], v1 = nodes[n0 * 6 + 9 + d];
+      coef[poly * 6 + d] = -(3.0 * (p0 - p1) + du[0] * (2.0 * v0 + v1)) / du[1];
+      coef[poly * 6 + 3 + d] = (2.0 * (p0 - p1) + du[0] * (v0 + v1)) / du[2];
+    }
+    cx.nodes = nodes.data(); cx.coef = coef.data(); cx.G = G.data(); cx.g = g; cx.pc = &pc;
+    for (const SegmentRec& sg : hp.segments) {
       std::fill(G.begin(), G.end(), std::nan(""));
       G[kGOne] = 1.0; G[kGMass] = pc.mass;
-      for (int i = 0; i < sg.n_items; ++i) RunItem(cx, P.items[sg.item0 + i]);
-      for (int e = 0; e < sg.n_entries; ++e) {
-        const EntryRec w = P.entries[sg.entry0 + e];
-        int gi = w.w0 & 0xFFFF, gs = (w.w0 >> 16) & 0xFFF, nt = ((w.w0 >> 28) & 3) + 1;
-        int bi = w.w1 & 0x3FFFFFFF, bs = w.w1 >> 31;
-        double v = G[gi] * P.B[bi];
-        for (int t = 1; t < nt; ++t) v += G[gi + t * gs] * P.B[bi + t * bs];
-        vals[sg.entry0 + e] = v;
-      }
+      for (int i = 0; i < sg.n_items; ++i) RunItem(cx, cx.T.items[sg.item0 + i]);
+      // walk the permuted descriptors exactly like the kernel's stage B
+      const int chunks = (sg.n_entries + kEntryChunk - 1) / kEntryChunk;
+      for (int k = 0; k < chunks; ++k)
+        for (int t = 0; t < kEntryThreads; ++t)
+          for (int j = 0; j < 4; ++j) {
+            uint32_t w = hp.entries_perm[4 * (static_cast<size_t>(sg.desc0) + k * kEntryThreads + t) + j];
+            if (w == kNoEntry) continue;
+            vals[sg.entry0 + k * kEntryChunk + j * kEntryThreads + t] = G[w & 0xFFFF] * cx.T.B[w >> 16];
+          }
     }
     return 0;
   } catch (const std::exception& e) {

@@ -12,7 +12,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
-LIB_PATH = os.path.join(_HERE, "libtowr_b200.so")
+LIB_PATH = os.environ.get("TOWR_B200_LIB") or os.path.join(_HERE, "libtowr_b200.so")   # override: experiments only
 CSRC = os.path.join(_HERE, "csrc")
 
 MAX_EE, MAX_PHASES, MAX_CONSTRAINTS = 4, 32, 16
@@ -90,7 +90,8 @@ towr_b200_structure_n_con_sets towr_b200_structure_var_set_name towr_b200_struct
 towr_b200_structure_con_set_name towr_b200_structure_con_set_rows towr_b200_structure_pattern towr_b200_structure_accepts
 towr_b200_problem_x0 towr_b200_problem_var_bounds towr_b200_problem_con_bounds towr_b200_batch_create
 towr_b200_batch_destroy towr_b200_batch_size towr_b200_batch_set_problem towr_b200_batch_set_all_problems
-towr_b200_batch_eval towr_b200_batch_eval_device towr_b200_batch_status towr_b200_batch_launch_count""".split()
+towr_b200_batch_eval towr_b200_batch_eval_device towr_b200_batch_status towr_b200_batch_launch_count
+towr_b200_batch_stream""".split()
 
 
 def lib():
@@ -134,6 +135,8 @@ def lib():
     L.towr_b200_batch_status.argtypes = [vp, C.c_int, ip]
     L.towr_b200_batch_launch_count.argtypes = [vp]
     L.towr_b200_batch_launch_count.restype = C.c_longlong
+    L.towr_b200_batch_stream.argtypes = [vp]
+    L.towr_b200_batch_stream.restype = C.c_void_p
     _lib = L
     return L
 
@@ -267,7 +270,8 @@ class Batch:
         return g, v
 
     def eval_device(self, n, what, d_x, d_g, d_vals, stream=None):
-        """Device-pointer evaluation (ints from tensor.data_ptr()); asynchronous on `stream` (a cudaStream_t int)."""
+        """Device-pointer evaluation (ints from tensor.data_ptr()); asynchronous on `stream`
+        (a cudaStream_t as int; None/0 = CUDA's default stream)."""
         _check(self._L.towr_b200_batch_eval_device(self._h, n, what, C.c_void_p(d_x), C.c_void_p(d_g or 0),
                                                     C.c_void_p(d_vals or 0), C.c_void_p(stream or 0)))
 

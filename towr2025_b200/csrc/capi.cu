@@ -1,6 +1,7 @@
 // capi.cu — the extern "C" boundary declared in include/towr_b200.h.
 #include <cuda_runtime.h>
 
+#include <cstdlib>
 #include <cstring>
 #include <exception>
 #include <memory>
@@ -79,7 +80,7 @@ struct towr_b200_batch {
   // staging for the host-buffer path
   double *x_dev = nullptr, *g_dev = nullptr, *v_dev = nullptr;
   tb::ProblemConst* pc_gather_dev = nullptr;
-  int max_ctas = 0;
+  int max_ctas = 0, lanes = 1;
   long long launches = 0;
 
   void SyncConsts() {
@@ -186,17 +187,12 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     const tb::HostProgram& hp = st->hp;
     tb::DeviceProgram& dp = b->dp;
     dp.n_vars = hp.n_vars; dp.n_rows = hp.n_rows; dp.nnz = hp.nnz; dp.n_ee = hp.n_ee;
-    dp.n_node_values = hp.n_node_values;
-    dp.n_polys = static_cast<int>(hp.polys.size());
     dp.n_segments = static_cast<int>(hp.segments.size());
     dp.g_capacity = hp.g_capacity;
+    dp.blob = hp.blob;
     auto keep = [&](auto* p) { b->owned.push_back(const_cast<void*>(static_cast<const void*>(p))); return p; };
-    dp.node_src = keep(Upload(hp.node_src));
-    dp.polys = keep(Upload(hp.polys));
-    dp.samples = keep(Upload(hp.samples));
-    dp.items = keep(Upload(hp.items));
-    dp.entries = keep(Upload(hp.entries));
-    dp.B = keep(Upload(hp.B));
+    dp.blob_data = keep(Upload(hp.blob_data));
+    dp.entries = reinterpret_cast<const uint4*>(keep(Upload(hp.entries_perm)));
     dp.segments = keep(Upload(hp.segments));
     b->pc_host.assign(n_problems, tb::ProblemConst{});
     Check(cudaMalloc(&b->pc_dev, sizeof(tb::ProblemConst) * n_problems), "cudaMalloc(consts)");
@@ -206,11 +202,21 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     Check(cudaMemset(b->status_dev, 0, sizeof(int) * n_problems), "cudaMemset(status)");
     cudaDeviceProp prop;
     Check(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
-    if (tb::EvalSharedBytes(dp) > static_cast<size_t>(prop.sharedMemPerBlockOptin))
+    // lanes per CTA: as many problems side by side as shared memory allows (the class tables are held once per CTA)
+    int forced = 0;
+    if (const char* env = std::getenv("TOWR_B200_LANES")) forced = std::atoi(env);
+    b->lanes = 0;
+    for (int lanes : {4, 2, 1}) {
+      if (forced && lanes != forced) continue;
+      if (tb::EvalSharedBytes(dp, lanes) > static_cast<size_t>(prop.sharedMemPerBlockOptin)) continue;
+      int occ = tb::EvalOccupancy(dp, lanes);
+      if (occ < 1) continue;
+      b->lanes = lanes;
+      b->max_ctas = prop.multiProcessorCount * occ;
+      break;
+    }
+    if (b->lanes == 0)
       throw std::runtime_error("unsupported: structure class needs more shared memory per CTA than the device has");
-    int occ = tb::EvalOccupancy(dp);
-    if (occ < 1) throw CudaError("evaluation kernel cannot be resident on this device");
-    b->max_ctas = prop.multiProcessorCount * occ * 8;
     *out = b.release();
   });
 }
@@ -244,12 +250,12 @@ int towr_b200_batch_eval_device(towr_b200_batch* b, int n, int what, const doubl
     if (!d_x || ((what & TOWR_B200_EVAL_G) && !d_g) || ((what & TOWR_B200_EVAL_JAC) && !d_jac_values))
       throw std::runtime_error("null device buffer");
     Check(cudaSetDevice(b->device), "cudaSetDevice");
-    cudaStream_t s = stream ? static_cast<cudaStream_t>(stream) : b->stream;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);   // NULL = CUDA's default stream, as everywhere in the runtime API
     if (b->pc_dirty) {
       b->SyncConsts();
       Check(cudaStreamSynchronize(b->stream), "sync consts");
     }
-    Check(tb::LaunchEval(b->dp, b->pc_dev, what, d_x, d_g, d_jac_values, b->status_dev, n, b->max_ctas, s), "launch");
+    Check(tb::LaunchEval(b->dp, b->pc_dev, what, d_x, d_g, d_jac_values, b->status_dev, n, b->lanes, b->max_ctas, s), "launch");
     b->launches += 1;
   });
 }
@@ -289,7 +295,7 @@ int towr_b200_batch_eval(towr_b200_batch* b, const int* ids, int n, int what, co
       b->SyncConsts();
     }
     Check(cudaMemcpyAsync(b->x_dev, x, sizeof(double) * dp.n_vars * n, cudaMemcpyHostToDevice, b->stream), "H2D x");
-    Check(tb::LaunchEval(dp, pcs, what, b->x_dev, b->g_dev, b->v_dev, b->status_dev, n, b->max_ctas, b->stream), "launch");
+    Check(tb::LaunchEval(dp, pcs, what, b->x_dev, b->g_dev, b->v_dev, b->status_dev, n, b->lanes, b->max_ctas, b->stream), "launch");
     b->launches += 1;
     if (what & TOWR_B200_EVAL_G)
       Check(cudaMemcpyAsync(g_out, b->g_dev, sizeof(double) * dp.n_rows * n, cudaMemcpyDeviceToHost, b->stream), "D2H g");
@@ -309,5 +315,6 @@ int towr_b200_batch_status(towr_b200_batch* b, int n, int* status_out) {
 }
 
 long long towr_b200_batch_launch_count(const towr_b200_batch* b) { return b ? b->launches : 0; }
+void* towr_b200_batch_stream(const towr_b200_batch* b) { return b ? static_cast<void*>(b->stream) : nullptr; }
 
 }  // extern "C"

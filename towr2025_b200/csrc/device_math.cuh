@@ -15,14 +15,38 @@ struct Pt3 { double p[3], v[3], a[3]; };
 
 enum { kNeedPos = 1, kNeedVel = 2, kNeedAcc = 4 };
 
+// class tables in shared memory (BlobLayout, program.h)
+struct Tables {
+  const double* B;
+  const double* times;      // 3 per entry
+  const double* durs;       // 3 per entry
+  const ItemC* items;
+  const uint32_t* samples;
+  const uint32_t* polys;
+  const uint16_t* node_src;
+};
+
+__device__ __forceinline__ Tables MakeTables(const unsigned char* blob, const BlobLayout& L) {
+  Tables t;
+  t.B = reinterpret_cast<const double*>(blob + L.off_B);
+  t.times = reinterpret_cast<const double*>(blob + L.off_times);
+  t.durs = reinterpret_cast<const double*>(blob + L.off_durs);
+  t.items = reinterpret_cast<const ItemC*>(blob + L.off_items);
+  t.samples = reinterpret_cast<const uint32_t*>(blob + L.off_samples);
+  t.polys = reinterpret_cast<const uint32_t*>(blob + L.off_polys);
+  t.node_src = reinterpret_cast<const uint16_t*>(blob + L.off_node_src);
+  return t;
+}
+
 // nodes[slot*6 + deriv*3 + dim], coef[poly*6 + {0:c,3:d} + dim]
 template <int NEED>
-__device__ __forceinline__ void EvalSpline(const DeviceProgram& P, const double* __restrict__ nodes,
+__device__ __forceinline__ void EvalSpline(const Tables& tb_, const double* __restrict__ nodes,
                                            const double* __restrict__ coef, int sample, Pt3& o) {
-  const SampleRec* sr = P.samples + sample;
-  const int poly = __ldg(&sr->poly);
-  const double t = __ldg(&sr->t), t2 = __ldg(&sr->t2), t3 = __ldg(&sr->t3);
-  const int n0 = __ldg(&P.polys[poly].node0);
+  const uint32_t sr = tb_.samples[sample];
+  const int poly = sr & 0xFFFF;
+  const double* tt = tb_.times + 3 * (sr >> 16);
+  const double t = tt[0], t2 = tt[1], t3 = tt[2];
+  const int n0 = tb_.polys[poly] & 0xFFFF;
 #pragma unroll
   for (int d = 0; d < 3; ++d) {
     const double a = nodes[n0 * 6 + d], b = nodes[n0 * 6 + 3 + d];

@@ -6,10 +6,11 @@
 #include "program.h"
 
 namespace tb {
-size_t EvalSharedBytes(const DeviceProgram& P);
+// dynamic shared memory of the evaluation kernel when `lanes` problems share one CTA
+size_t EvalSharedBytes(const DeviceProgram& P, int lanes);
 // evaluates problems 0..n_problems-1; x, g, vals, status are device pointers on the current device
 cudaError_t LaunchEval(const DeviceProgram& P, const ProblemConst* pcs, int what, const double* x, double* g,
-                       double* vals, int* status, int n_problems, int max_ctas, cudaStream_t stream);
-// resident CTAs per SM of the evaluation kernel for this program
-int EvalOccupancy(const DeviceProgram& P);
+                       double* vals, int* status, int n_problems, int lanes, int max_ctas, cudaStream_t stream);
+// resident CTAs per SM of the evaluation kernel for this program and lane count (0: does not fit)
+int EvalOccupancy(const DeviceProgram& P, int lanes);
 }  // namespace tb

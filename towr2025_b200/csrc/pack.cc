@@ -1,0 +1,135 @@
+// pack.cc — compacts the builder's tables into the device form: one shared-memory blob of class tables and the
+// thread-major permuted entry descriptors (program.h).
+#include <cstring>
+#include <map>
+#include <stdexcept>
+
+#include "structure.h"
+
+namespace tb {
+
+namespace {
+int Align16(int v) { return (v + 15) & ~15; }
+}
+
+void PackProgram(HostProgram& hp) {
+  // distinct local times and durations
+  std::vector<double> times, durs;
+  std::map<uint64_t, int> time_ix, dur_ix;
+  auto intern = [](std::map<uint64_t, int>& ix, std::vector<double>& tab, double a, double b, double c) {
+    uint64_t key;
+    std::memcpy(&key, &a, 8);
+    auto it = ix.find(key);
+    if (it != ix.end()) return it->second;
+    int i = static_cast<int>(tab.size() / 3);
+    tab.push_back(a); tab.push_back(b); tab.push_back(c);
+    ix[key] = i;
+    return i;
+  };
+  std::vector<uint32_t> polys;
+  for (const PolyRec& p : hp.polys) {
+    int d = intern(dur_ix, durs, p.T, p.T2, p.T3);
+    if (p.node0 > 0xFFFF || d > 0xFFFF) throw std::runtime_error("unsupported: spline too large for the compact tables");
+    polys.push_back(static_cast<uint32_t>(p.node0) | (static_cast<uint32_t>(d) << 16));
+  }
+  std::vector<uint32_t> samples;
+  auto add_sample = [&](int wide) {
+    const SampleRec& r = hp.samples.at(wide);
+    int t = intern(time_ix, times, r.t, r.t2, r.t3);
+    if (r.poly > 0xFFFF || t > 0xFFFF) throw std::runtime_error("unsupported: too many polynomials or sample times");
+    samples.push_back(static_cast<uint32_t>(r.poly) | (static_cast<uint32_t>(t) << 16));
+  };
+  std::vector<ItemC> items;
+  std::map<int, int> dyn_s0;   // wide index of a dynamic sample's first SampleRec -> compact s0 (shared by the 4 sub-items)
+  for (const ItemRec& it : hp.items) {
+    ItemC c;
+    std::memset(&c, 0, sizeof(c));
+    c.type = static_cast<uint8_t>(it.type);
+    c.sub = static_cast<uint8_t>(it.sub);
+    c.ee = static_cast<uint8_t>(it.ee);
+    c.n_ee = static_cast<uint8_t>(it.n_ee);
+    if (it.gslot > 0xFFFF || it.b0 > 0xFFFF) throw std::runtime_error("item slot out of range");
+    c.gslot = static_cast<uint16_t>(it.gslot);
+    c.b0 = static_cast<uint16_t>(it.b0);
+    c.row = static_cast<uint32_t>(it.row[0]);
+    const int E = it.n_ee;
+    size_t s0 = samples.size();
+    switch (it.type) {
+      case kItemDynamic: {
+        auto f = dyn_s0.find(it.s[kSBaseLin]);
+        if (f != dyn_s0.end()) { s0 = f->second; break; }
+        dyn_s0[it.s[kSBaseLin]] = static_cast<int>(s0);
+        add_sample(it.s[kSBaseLin]);
+        add_sample(it.s[kSBaseAng]);
+        for (int e = 0; e < E; ++e) { add_sample(it.s[kSMotion + e]); add_sample(it.s[kSForce + e]); add_sample(it.s[kSTorque + e]); }
+        break;
+      }
+      case kItemRom: {
+        add_sample(it.s[kSBaseLin]);
+        add_sample(it.s[kSBaseAng]);
+        for (int e = 0; e < E; ++e) add_sample(it.s[kSMotion + e]);
+        int stride = E > 1 ? it.row[1] - it.row[0] : 0;
+        for (int e = 1; e < E; ++e)
+          if (it.row[e] - it.row[e - 1] != stride) throw std::runtime_error("RoM sets are not equally spaced");
+        if (stride < 0 || stride > 0xFFFF) throw std::runtime_error("unsupported: RoM set larger than 65535 rows");
+        c.aux = static_cast<uint16_t>(stride);
+        break;
+      }
+      case kItemForce:
+        add_sample(it.s[kSMotion + it.ee]);
+        add_sample(it.s[kSForce + it.ee]);
+        break;
+      default:
+        s0 = static_cast<size_t>(it.s[0]);   // node slot or polynomial index
+        break;
+    }
+    if (s0 > 0xFFFF) throw std::runtime_error("unsupported: too many samples for the compact tables");
+    c.s0 = static_cast<uint16_t>(s0);
+    items.push_back(c);
+  }
+  if (hp.n_vars >= 0xFFFF) throw std::runtime_error("unsupported: more than 65534 variables");
+
+  BlobLayout& L = hp.blob;
+  int off = 0;
+  auto place = [&](int& o, int bytes) { o = off; off = Align16(off + bytes); };
+  L.n_B = static_cast<int>(hp.B.size());
+  L.n_times = static_cast<int>(times.size() / 3);
+  L.n_durs = static_cast<int>(durs.size() / 3);
+  L.n_items = static_cast<int>(items.size());
+  L.n_samples = static_cast<int>(samples.size());
+  L.n_polys = static_cast<int>(polys.size());
+  L.n_node_values = hp.n_node_values;
+  place(L.off_B, 8 * L.n_B);
+  place(L.off_times, 24 * L.n_times);
+  place(L.off_durs, 24 * L.n_durs);
+  place(L.off_items, 16 * L.n_items);
+  place(L.off_samples, 4 * L.n_samples);
+  place(L.off_polys, 4 * L.n_polys);
+  place(L.off_node_src, 2 * L.n_node_values);
+  L.bytes = off;
+  hp.blob_data.assign(off, 0);
+  unsigned char* d = hp.blob_data.data();
+  std::memcpy(d + L.off_B, hp.B.data(), 8 * hp.B.size());
+  std::memcpy(d + L.off_times, times.data(), 8 * times.size());
+  std::memcpy(d + L.off_durs, durs.data(), 8 * durs.size());
+  std::memcpy(d + L.off_items, items.data(), 16 * items.size());
+  std::memcpy(d + L.off_samples, samples.data(), 4 * samples.size());
+  std::memcpy(d + L.off_polys, polys.data(), 4 * polys.size());
+  uint16_t* ns = reinterpret_cast<uint16_t*>(d + L.off_node_src);
+  for (int i = 0; i < hp.n_node_values; ++i) ns[i] = hp.node_src[i] < 0 ? 0xFFFF : static_cast<uint16_t>(hp.node_src[i]);
+
+  // thread-major permuted descriptors per segment
+  hp.entries_perm.clear();
+  for (SegmentRec& sg : hp.segments) {
+    sg.desc0 = static_cast<int>(hp.entries_perm.size() / 4);
+    const int chunks = (sg.n_entries + kEntryChunk - 1) / kEntryChunk;
+    for (int k = 0; k < chunks; ++k)
+      for (int t = 0; t < kEntryThreads; ++t)
+        for (int j = 0; j < 4; ++j) {
+          int e = k * kEntryChunk + j * kEntryThreads + t;
+          hp.entries_perm.push_back(e < sg.n_entries ? hp.entries[sg.entry0 + e] : kNoEntry);
+        }
+  }
+}
+
+}  // namespace tb

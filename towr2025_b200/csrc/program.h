@@ -10,14 +10,18 @@
 //   per segment:
 //     stage A  one thread per *item* (a time sample or a node of one constraint family):
 //              writes its constraint rows g and its partial-derivative slots -> smem G[]
-//     stage B  one thread per stored Jacobian entry: val = sum_t G[g+t*gs] * B[b+t*bs],
-//              coalesced store into the problem's value array
+//     stage B  one thread per stored Jacobian entry: val = G[g] * B[b], coalesced store into the problem's
+//              value array (entries that are sums of products are finished by their item in stage A)
 //
 // B[] holds class constants (Hermite basis values at the fixed sample times, signs, 1/t_swing ...),
 // G[] holds per-problem quantities (forces, lever arms, rotation matrices, terrain slopes ...).
 #pragma once
 #include <cstdint>
+#include <cstddef>
 #include <string>
+#ifndef __CUDACC__
+struct alignas(16) uint4 { unsigned int x, y, z, w; };
+#endif
 #include <vector>
 
 namespace tb {
@@ -53,39 +57,65 @@ enum { kSBaseLin = 0, kSBaseAng = 1, kSMotion = 2, kSForce = 2 + kMaxEE, kSTorqu
 struct ItemRec {
   int type;
   int gslot;            // first G slot of this item (segment-relative)
-  int ee;               // foot (force / terrain / swing) ; splineacc: unused
-  int n_ee;
+  short ee;             // foot (force / terrain / swing) ; splineacc: unused
+  short sub;            // dynamic: 0 = wrench part, 1..3 = euler column (sub-1) of the base-ang block
+  short n_ee;
+  short pad;
+  int b0;               // dynamic: first of the 16 Hermite basis constants of this sample in B (see structure.cc)
   int row[kMaxEE];      // first constraint row written (absolute in g); RoM: one per foot
   int s[kSCount];       // SampleRec indices; node-based items: node slot / polynomial index in s[0]
 };
 
-struct EntryRec {       // one stored Jacobian entry, in storage (row-major) order
-  uint32_t w0;          // g (16 bits) | gs (12 bits) << 16 | (nt-1) (2 bits) << 28
-  uint32_t w1;          // b (30 bits) | bs (1 bit) << 31
-};
+// one stored Jacobian entry, in storage (row-major) order: G slot (low 16 bits) | B index (high 16 bits)
+using EntryRec = uint32_t;
 
+// Entry descriptors of a segment are stored thread-major in chunks of kEntryChunk: uint4 number desc0 + k*kEntryThreads + t
+// holds the descriptors of entries k*kEntryChunk + j*kEntryThreads + t, j = 0..3 (0xFFFFFFFF = past the end), so
+// that one 16-byte load feeds four coalesced 8-byte stores.
+constexpr int kEntryThreads = 256;
+constexpr int kEntryChunk = 4 * kEntryThreads;
+constexpr uint32_t kNoEntry = 0xFFFFFFFFu;
 struct SegmentRec {
   int item0, n_items;   // items of this segment
   int entry0, n_entries;// entries fed by this segment (contiguous in storage order)
   int g_size;           // G slots used
-  int pad;
+  int desc0;            // first uint4 of the segment's permuted descriptors
 };
 
 // slots 0.. of every segment's G buffer
 enum { kGOne = 0, kGMass = 1, kGReserved = 2 };
 
+// ---- compact class tables: one byte blob per structure class, copied into shared memory once per CTA so that
+// stage A never touches global memory (with ~200 KB of shared memory in use per SM the L1 is almost gone and every
+// table lookup would be an L2 round trip)
+struct ItemC {          // 16 bytes
+  uint8_t type, sub, ee, n_ee;
+  uint16_t gslot, b0;
+  uint32_t row;         // first constraint row; RoM: row of foot e = row + e * aux
+  uint16_t s0;          // first compact sample of the item; node items: node slot; splineacc: polynomial index
+  uint16_t aux;
+};
+// compact sample = polynomial index | time index << 16 ; compact polynomial = node slot | duration index << 16
+// sample order of an item: dynamic [lin, ang, (motion, force, torque) per foot], RoM [lin, ang, motion per foot],
+// force [motion, force]
+struct BlobLayout {     // byte offsets into the blob (all 16-byte aligned), element counts
+  int bytes;
+  int off_B, n_B;                 // double
+  int off_times, n_times;         // double[3] per entry: t, pow(t,2), pow(t,3)
+  int off_durs, n_durs;           // double[3] per entry: T, pow(T,2), pow(T,3)
+  int off_items, n_items;         // ItemC
+  int off_samples, n_samples;     // uint32
+  int off_polys, n_polys;         // uint32
+  int off_node_src, n_node_values;// uint16, 0xFFFF = pinned to zero
+};
+
 struct DeviceProgram {  // pointers into device memory (one copy per GPU)
   int n_vars, n_rows, nnz, n_ee;
-  int n_node_values;    // 6 per node
-  int n_polys;
   int n_segments;
   int g_capacity;       // max g_size over segments
-  const int* node_src;  // [n_node_values] column of x, or -1 for a value pinned to 0
-  const PolyRec* polys;
-  const SampleRec* samples;
-  const ItemRec* items;
-  const EntryRec* entries;
-  const double* B;
+  BlobLayout blob;
+  const unsigned char* blob_data;
+  const uint4* entries; // permuted descriptors, see SegmentRec::desc0
   const SegmentRec* segments;
 };
 
@@ -144,6 +174,10 @@ struct HostProgram {
   std::vector<EntryRec> entries;
   std::vector<double> B;
   std::vector<SegmentRec> segments;
+  // packed for the device (pack.cc)
+  BlobLayout blob{};
+  std::vector<unsigned char> blob_data;
+  std::vector<uint32_t> entries_perm;   // 4 per uint4
   int g_capacity = 0;
   int n_node_values = 0;
   std::string signature;   // canonical text of every structural field (structure_accepts compares it)

@@ -63,8 +63,8 @@ double LocalTime(double t_global, int id, const std::vector<double>& durations) 
 
 namespace {
 
-struct Term { int g = 0, gs = 0, nt = 1, b = 0, bs = 0; };
-struct ColBasis { int idx, dim; double v[3]; };   // v[dx]: d{pos,vel,acc}/d(variable idx)
+struct Term { int g = 0, b = 0; };                // value = G[g] * B[b]
+struct ColBasis { int idx, dim; double v[3]; int sd; };   // v[dx]: d{pos,vel,acc}/d(variable idx); sd = side*2+deriv of the last hit
 struct SplineAt { int sample; int poly; double t_local; };
 
 class Builder {
@@ -87,14 +87,14 @@ class Builder {
     b1_[bits] = i;
     return i;
   }
-  int AddB3(double a, double b, double c) {
-    std::array<uint64_t, 3> key;
-    std::memcpy(&key[0], &a, 8); std::memcpy(&key[1], &b, 8); std::memcpy(&key[2], &c, 8);
-    auto it = b3_.find(key);
-    if (it != b3_.end()) return it->second;
+  // a run of consecutive constants (items read them by position); identical runs are shared
+  int AddBRun(const std::vector<double>& v) {
+    std::string key(reinterpret_cast<const char*>(v.data()), v.size() * sizeof(double));
+    auto it = brun_.find(key);
+    if (it != brun_.end()) return it->second;
     int i = static_cast<int>(hp_.B.size());
-    hp_.B.push_back(a); hp_.B.push_back(b); hp_.B.push_back(c);
-    b3_[key] = i;
+    hp_.B.insert(hp_.B.end(), v.begin(), v.end());
+    brun_[key] = i;
     return i;
   }
   SplineAt At(const VarSet& set, double t_global) {
@@ -118,11 +118,12 @@ class Builder {
     HermiteBasis(set.poly_T[poly], t_local, hb);
     std::vector<ColBasis> cols;
     for (int idx = 0; idx < set.n_vars; ++idx) {
-      ColBasis cb{idx, -1, {0.0, 0.0, 0.0}};
+      ColBasis cb{idx, -1, {0.0, 0.0, 0.0}, 0};
       for (const NodeRef& r : set.refs[idx])
         for (int side = 0; side < 2; ++side)
           if (poly + side == r.node) {
             cb.dim = r.dim;
+            cb.sd = side * 2 + r.deriv;
             for (int dx = 0; dx < 3; ++dx) cb.v[dx] += hb[dx * 4 + side * 2 + r.deriv];
           }
       if (cb.dim >= 0) cols.push_back(cb);
@@ -185,11 +186,8 @@ class Builder {
       std::stable_sort(row.begin(), row.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
       for (auto& e : row) {
         const Term& t = e.second;
-        if (t.g < 0 || t.g > 65535 || t.gs < 0 || t.gs > 4095 || t.nt < 1 || t.nt > 4 || t.b < 0 || t.b >= (1 << 30))
-          throw std::runtime_error("entry descriptor out of range");
-        EntryRec er;
-        er.w0 = static_cast<uint32_t>(t.g) | (static_cast<uint32_t>(t.gs) << 16) | (static_cast<uint32_t>(t.nt - 1) << 28);
-        er.w1 = static_cast<uint32_t>(t.b) | (static_cast<uint32_t>(t.bs) << 31);
+        if (t.g < 0 || t.g > 65535 || t.b < 0 || t.b > 65535) throw std::runtime_error("entry descriptor out of range");
+        EntryRec er = static_cast<uint32_t>(t.g) | (static_cast<uint32_t>(t.b) << 16);
         hp_.entries.push_back(er);
         hp_.pat_rows.push_back(set_row0_ + static_cast<int>(r));
         hp_.pat_cols.push_back(e.first);
@@ -201,7 +199,7 @@ class Builder {
     ItemRec it;
     std::memset(&it, 0, sizeof(it));
     it.type = type;
-    it.n_ee = s_.n_ee;
+    it.n_ee = static_cast<short>(s_.n_ee);
     return it;
   }
   const VarSet& Set(int kind, int ee = -1) const {
@@ -223,7 +221,7 @@ class Builder {
   HostProgram& hp_;
   const std::vector<char>* plan_;
   std::map<uint64_t, int> b1_;
-  std::map<std::array<uint64_t, 3>, int> b3_;
+  std::map<std::string, int> brun_;
   std::vector<std::vector<std::pair<int, Term>>> rows_;
   int set_row0_ = 0;
 };
@@ -240,7 +238,7 @@ void Builder::EmitHeightRows(const VarSet& set, int item_type, int ee) {
   const int one = AddB(1.0);
   for (int node = 1; node < set.n_nodes; ++node) {
     ItemRec it = NewItem(item_type);
-    it.ee = ee;
+    it.ee = static_cast<short>(ee);
     it.row[0] = set_row0_ + node - 1;
     it.s[0] = set.node_slot0 + node;
     it.gslot = AllocG(2);
@@ -272,12 +270,19 @@ void Builder::EmitBaseHeight() {
   EndSet();
 }
 
-// DynamicConstraint, 6 rows per sample (dynamic_constraint.cc:57-126 with single_rigid_body_dynamics.cc:104-204)
+// DynamicConstraint, 6 rows per sample (dynamic_constraint.cc:57-126 with single_rigid_body_dynamics.cc:104-204).
+// Four items per sample: sub 0 evaluates the wrench part (g rows, forces, lever arms, the base-lin angular block),
+// sub 1..3 one euler column each of the base-ang block.  G layout per sample:
+//   Jang[3][12]  d(angular rows)/d(base-ang variable (sd, c)) at slot r*12 + sd*3 + c   (finished values)
+//   Jlin[3][12]  d(angular rows)/d(base-lin variable (sd, d)) at slot r*12 + sd*3 + d   (finished; d == r unused)
+//   f_e[3], (c - p_e)[3] per foot
+// B run of the sample (ItemRec::b0): base-lin pos basis [4], then base-ang pos/vel/acc basis [4] each, by sd.
 void Builder::EmitDynamic() {
   const int E = s_.n_ee;
   const VarSet& lin = Set(kBaseLin);
   const VarSet& ang = Set(kBaseAng);
   const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_dynamic);
+  const int one = AddB(1.0);
   BeginGroup();
   BeginSet("dynamic", static_cast<int>(ts.size()) * 6);
   for (size_t k = 0; k < ts.size(); ++k) {
@@ -285,29 +290,33 @@ void Builder::EmitDynamic() {
     const int r0 = static_cast<int>(k) * 6;
     ItemRec it = NewItem(kItemDynamic);
     it.row[0] = set_row0_ + r0;
-    const int g0 = AllocG(27 + 6 * E);
+    const int g0 = AllocG(72 + 6 * E);
     it.gslot = g0;
-    const int gAp = g0, gF = g0 + 27, gR = g0 + 27 + 3 * E;
+    const int gJang = g0, gJlin = g0 + 36, gF = g0 + 72, gR = g0 + 72 + 3 * E;
 
     SplineAt al = At(lin, t), aa = At(ang, t);
     it.s[kSBaseLin] = al.sample;
     it.s[kSBaseAng] = aa.sample;
-    // base-lin: angular rows -sum_e Cross(f_e) J_pos, linear rows m J_acc
+    double hbl[12], hba[12];
+    HermiteBasis(lin.poly_T[al.poly], al.t_local, hbl);
+    HermiteBasis(ang.poly_T[aa.poly], aa.t_local, hba);
+    std::vector<double> run(hbl, hbl + 4);
+    run.insert(run.end(), hba, hba + 12);
+    it.b0 = AddBRun(run);
+    // base-lin: angular rows -sum_e Cross(f_e) J_pos (finished by the item), linear rows m J_acc
     for (const ColBasis& c : Columns(lin, al.poly, al.t_local)) {
       for (int r = 0; r < 3; ++r) {
         if (r == c.dim) continue;
-        int kk; double sg;
-        CrossEntry(r, c.dim, &kk, &sg);
-        Term tm; tm.g = gF + kk; tm.gs = 3; tm.nt = E; tm.b = AddB(-(sg * c.v[0]));
+        Term tm; tm.g = gJlin + r * 12 + c.sd * 3 + c.dim; tm.b = one;
         Add(r0 + r, lin.col0 + c.idx, tm);
       }
       Term tm; tm.g = kGMass; tm.b = AddB(c.v[2]);
       Add(r0 + 3 + c.dim, lin.col0 + c.idx, tm);
     }
-    // base-ang: full 3 x 12 block, value = A_pos*Bp + A_vel*Bv + A_acc*Ba
+    // base-ang: full 3 x 12 block, A_pos*Bp + A_vel*Bv + A_acc*Ba finished by the items
     for (const ColBasis& c : Columns(ang, aa.poly, aa.t_local))
       for (int r = 0; r < 3; ++r) {
-        Term tm; tm.g = gAp + r * 3 + c.dim; tm.gs = 9; tm.nt = 3; tm.b = AddB3(c.v[0], c.v[1], c.v[2]); tm.bs = 1;
+        Term tm; tm.g = gJang + r * 12 + c.sd * 3 + c.dim; tm.b = one;
         Add(r0 + r, ang.col0 + c.idx, tm);
       }
     for (int e = 0; e < E; ++e) {
@@ -345,7 +354,10 @@ void Builder::EmitDynamic() {
         Add(r0 + c.dim, to.col0 + c.idx, tm);
       }
     }
-    hp_.items.push_back(it);
+    for (int sub = 0; sub < 4; ++sub) {
+      it.sub = static_cast<short>(sub);
+      hp_.items.push_back(it);
+    }
   }
   EndSet();
 }
@@ -441,7 +453,7 @@ void Builder::EmitForceDisc(int ee) {
   BeginSet("force-disc-" + fo.name, static_cast<int>(ts.size()) * 5);
   for (size_t k = 0; k < ts.size(); ++k) {
     ItemRec it = NewItem(kItemForce);
-    it.ee = ee;
+    it.ee = static_cast<short>(ee);
     it.row[0] = set_row0_ + static_cast<int>(k) * 5;
     it.gslot = AllocG(15);
     SplineAt am = At(mo, ts[k]), af = At(fo, ts[k]);
@@ -471,7 +483,7 @@ void Builder::EmitSwing(int ee) {
   int row = 0;
   for (int node : nodes) {
     ItemRec it = NewItem(kItemSwingNode);
-    it.ee = ee;
+    it.ee = static_cast<short>(ee);
     it.row[0] = set_row0_ + row;
     it.s[0] = mo.node_slot0 + node;
     hp_.items.push_back(it);
@@ -559,7 +571,7 @@ void BuildProgram(const towr_b200_spec& s, HostProgram& hp) {
   ResetTables(hp);
   Builder sizing(s, hp, nullptr);
   sizing.Run();
-  int cap = 3072;
+  int cap = 3500;   // G slots per segment: ANYmal trot packs into 3 balanced segments of <= 238 items
   if (const char* env = std::getenv("TOWR_B200_GCAP")) cap = std::max(64, std::atoi(env));
   std::vector<char> plan(sizing.group_g_size.size(), 0);
   int used = kGReserved;
@@ -574,6 +586,7 @@ void BuildProgram(const towr_b200_spec& s, HostProgram& hp) {
   ResetTables(hp);
   Builder real(s, hp, &plan);
   real.Run();
+  PackProgram(hp);
 }
 
 }  // namespace tb

@@ -25,6 +25,9 @@ double LocalTime(double t_global, int id, const std::vector<double>& durations);
 void BuildProgram(const towr_b200_spec& s, HostProgram& hp);
 std::string StructureSignature(const towr_b200_spec& s);
 
+// pack.cc
+void PackProgram(HostProgram& hp);
+
 // formulation.cc
 void ProblemX0(const HostProgram& hp, const towr_b200_spec& s, double* x);
 void ProblemVarBounds(const HostProgram& hp, const towr_b200_spec& s, double* lo, double* up);

@@ -94,7 +94,9 @@ TB_HD TerrainSample EvalTerrain(int id, double x, double y) {
 // v.normalized() = v / sqrt(v.v) with the squared norm summed left to right
 TB_HD void Normalize3(const double v[3], double out[3]) {
   double z = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
-  if (z > 0.0) {
+  if (z == 1.0) {            // unit already (flat ground): sqrt(1) = 1 and v/1 = v exactly, skip sqrt + 3 divisions
+    out[0] = v[0]; out[1] = v[1]; out[2] = v[2];
+  } else if (z > 0.0) {
     double n = sqrt(z);
     out[0] = v[0] / n; out[1] = v[1] / n; out[2] = v[2] / n;
   } else {
