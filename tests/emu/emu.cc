@@ -58,7 +58,7 @@ extern "C" int emu_eval(const towr_b200_spec* s, const double* x, double* g, dou
           for (int j = 0; j < 4; ++j) {
             uint32_t w = hp.entries_perm[4 * (static_cast<size_t>(sg.desc0) + k * kEntryThreads + t) + j];
             if (w == kNoEntry) continue;
-            vals[sg.entry0 + k * kEntryChunk + j * kEntryThreads + t] = G[w & 0xFFFF] * cx.T.B[w >> 16];
+            vals[sg.entry0 + k * kEntryChunk + j * kEntryThreads + t] = G[(w & 0xFFFF) / 8] * cx.T.B[(w >> 16) / 8];
           }
     }
     return 0;

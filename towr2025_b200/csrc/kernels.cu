@@ -97,15 +97,28 @@ EvalKernel(const __grid_constant__ DeviceProgram P, const ProblemConst* __restri
         double* __restrict__ out = vp + sg.entry0 + tid;
         const int n = sg.n_entries;
         const int chunks = (n + kEntryChunk - 1) / kEntryChunk;
+        const char* Gb = reinterpret_cast<const char*>(G);
+        const char* Bb = reinterpret_cast<const char*>(Bs);
+        auto val = [&](uint32_t d) {     // descriptors hold byte offsets: G in the low half, B in the high half
+          return *reinterpret_cast<const double*>(Gb + (d & 0xFFFFu)) * *reinterpret_cast<const double*>(Bb + (d >> 16));
+        };
         uint4 w = __ldg(ent);
-        for (int k = 0; k < chunks; ++k) {
+        for (int k = 0; k + 1 < chunks; ++k) {          // full chunks: no bounds checks
           const uint4 cur = w;
-          if (k + 1 < chunks) w = __ldg(ent + (k + 1) * kEntryThreads);   // prefetch the next chunk's descriptors
+          w = __ldg(ent + (k + 1) * kEntryThreads);     // prefetch the next chunk's descriptors
           double* o = out + k * kEntryChunk;
-          if (cur.x != kNoEntry) o[0] = G[cur.x & 0xFFFF] * Bs[cur.x >> 16];
-          if (cur.y != kNoEntry) o[kEntryThreads] = G[cur.y & 0xFFFF] * Bs[cur.y >> 16];
-          if (cur.z != kNoEntry) o[2 * kEntryThreads] = G[cur.z & 0xFFFF] * Bs[cur.z >> 16];
-          if (cur.w != kNoEntry) o[3 * kEntryThreads] = G[cur.w & 0xFFFF] * Bs[cur.w >> 16];
+          const double v0 = val(cur.x), v1 = val(cur.y), v2 = val(cur.z), v3 = val(cur.w);
+          o[0] = v0;
+          o[kEntryThreads] = v1;
+          o[2 * kEntryThreads] = v2;
+          o[3 * kEntryThreads] = v3;
+        }
+        if (chunks > 0) {                               // last chunk: may be partial
+          double* o = out + (chunks - 1) * kEntryChunk;
+          if (w.x != kNoEntry) o[0] = val(w.x);
+          if (w.y != kNoEntry) o[kEntryThreads] = val(w.y);
+          if (w.z != kNoEntry) o[2 * kEntryThreads] = val(w.z);
+          if (w.w != kNoEntry) o[3 * kEntryThreads] = val(w.w);
         }
         // a non-finite Jacobian value needs a non-finite G slot (B is finite): check the slots, not the entries
         for (int i = tid; i < sg.g_size; i += kThreads) bad |= NonFinite(G[i]);

@@ -41,6 +41,7 @@ void PackProgram(HostProgram& hp) {
   };
   std::vector<ItemC> items;
   std::map<int, int> dyn_s0;   // wide index of a dynamic sample's first SampleRec -> compact s0 (shared by the 4 sub-items)
+  std::vector<std::pair<int, int>> kind;   // (type, sub) per compact item
   for (const ItemRec& it : hp.items) {
     ItemC c;
     std::memset(&c, 0, sizeof(c));
@@ -86,6 +87,34 @@ void PackProgram(HostProgram& hp) {
     if (s0 > 0xFFFF) throw std::runtime_error("unsupported: too many samples for the compact tables");
     c.s0 = static_cast<uint16_t>(s0);
     items.push_back(c);
+    kind.emplace_back(it.type, it.sub);
+  }
+  // per segment: items of one (type, sub) kind are made contiguous and every kind starts on a warp boundary, so
+  // that no warp of stage A diverges between item kinds (null items fill the gaps)
+  {
+    std::vector<ItemC> padded;
+    ItemC none;
+    std::memset(&none, 0, sizeof(none));
+    none.type = kItemNone;
+    for (SegmentRec& sg : hp.segments) {
+      std::vector<std::pair<int, int>> kinds;
+      for (int i = 0; i < sg.n_items; ++i) {
+        auto k = kind[sg.item0 + i];
+        bool seen = false;
+        for (auto& q : kinds) seen |= (q == k);
+        if (!seen) kinds.push_back(k);
+      }
+      const int new0 = static_cast<int>(padded.size());
+      for (auto& k : kinds) {
+        while (padded.size() % 32) padded.push_back(none);
+        for (int i = 0; i < sg.n_items; ++i)
+          if (kind[sg.item0 + i] == k) padded.push_back(items[sg.item0 + i]);
+      }
+      while (padded.size() % 32) padded.push_back(none);
+      sg.item0 = new0;
+      sg.n_items = static_cast<int>(padded.size()) - new0;
+    }
+    items.swap(padded);
   }
   if (hp.n_vars >= 0xFFFF) throw std::runtime_error("unsupported: more than 65534 variables");
 
@@ -127,7 +156,14 @@ void PackProgram(HostProgram& hp) {
       for (int t = 0; t < kEntryThreads; ++t)
         for (int j = 0; j < 4; ++j) {
           int e = k * kEntryChunk + j * kEntryThreads + t;
-          hp.entries_perm.push_back(e < sg.n_entries ? hp.entries[sg.entry0 + e] : kNoEntry);
+          if (e < sg.n_entries) {
+            uint32_t w = hp.entries[sg.entry0 + e];
+            uint32_t g8 = (w & 0xFFFF) * 8, b8 = (w >> 16) * 8;
+            if (g8 > 0xFFFF || b8 > 0xFFFF) throw std::runtime_error("unsupported: G or B table beyond 8191 entries");
+            hp.entries_perm.push_back(g8 | (b8 << 16));
+          } else {
+            hp.entries_perm.push_back(kNoEntry);
+          }
         }
   }
 }

@@ -48,6 +48,7 @@ enum ItemType : int {
   kItemSwingNode,       // swing_constraint.cc:54-108              4 rows per swing node
   kItemSplineAcc,       // spline_acc_constraint.cc:48-80          3 rows per junction
   kItemTotalDuration,   // total_duration_constraint.cc:48-72
+  kItemNone = 255,      // padding: keeps every warp of stage A on one item kind
 };
 
 constexpr int kMaxEE = 4;
@@ -66,7 +67,8 @@ struct ItemRec {
   int s[kSCount];       // SampleRec indices; node-based items: node slot / polynomial index in s[0]
 };
 
-// one stored Jacobian entry, in storage (row-major) order: G slot (low 16 bits) | B index (high 16 bits)
+// one stored Jacobian entry, in storage (row-major) order: G slot (low 16 bits) | B index (high 16 bits);
+// the device copy (pack.cc) holds BYTE offsets (slot*8, index*8) so that stage B needs no shifts
 using EntryRec = uint32_t;
 
 // Entry descriptors of a segment are stored thread-major in chunks of kEntryChunk: uint4 number desc0 + k*kEntryThreads + t

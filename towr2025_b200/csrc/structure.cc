@@ -157,7 +157,7 @@ class Builder {
     int g = sg.g_size;
     sg.g_size += n;
     group_g_size.back() += n;
-    if (sg.g_size > 65535) throw std::runtime_error("segment needs more than 65535 G slots");
+    if (sg.g_size > 8191) throw std::runtime_error("unsupported: a constraint set needs more than 8191 G slots in one segment");
     return g;
   }
 
