@@ -43,3 +43,24 @@ def test_emulated_kernel_segment_capacity(product, oracle, emu, monkeypatch):
     monkeypatch.setenv("TOWR_B200_GCAP", "600")
     alt = emu_eval(emu, s, st, x)
     assert np.array_equal(ref[0], alt[0]) and np.array_equal(ref[1], alt[1])
+
+
+def test_emulated_kernel_reproduces_committed_fixtures(product, emu):
+    """tests/golden/*.npz (oracle outputs frozen by tests/golden/make_golden.py)."""
+    import glob
+    import os
+    from util import CASES
+    T = product
+    by_name = {c[0]: c for c in CASES}
+    files = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+    assert files
+    for f in files:
+        z = np.load(f)
+        _, robot, combo, Tt, goal, terrain = by_name[os.path.basename(f)[:-4]]
+        s = T.make_spec(robot, combo, Tt, goal=goal, terrain=terrain)
+        st = T.Structure(s)
+        g, v = emu_eval(emu, s, st, np.ascontiguousarray(z["x"]))
+        rows, cols = st.pattern()
+        assert st.nnz == int(z["nnz"])
+        assert np.array_equal(rows[z["jac_idx"]], z["jac_rows"]) and np.array_equal(cols[z["jac_idx"]], z["jac_cols"])
+        assert tol_ratio(g, z["g"]) <= 1.0 and tol_ratio(v[z["jac_idx"]], z["jac_vals"]) <= 1.0

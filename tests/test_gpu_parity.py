@@ -129,3 +129,25 @@ def test_non_finite_input_flags_only_its_problem(product):
     status = b.status()
     assert status[2] != 0 and (status[[0, 1, 3]] == 0).all()
     assert np.isfinite(v[[0, 1, 3]]).all()
+
+
+def test_gpu_reproduces_committed_fixtures(product):
+    """tests/golden/*.npz through the C ABI: the GPU box has neither /root/reference nor needs the oracle here."""
+    import glob
+    import os
+    T = product
+    by_name = {c[0]: c for c in CASES}
+    files = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+    assert files
+    for f in files:
+        z = np.load(f)
+        _, robot, combo, Tt, goal, terrain = by_name[os.path.basename(f)[:-4]]
+        s = T.make_spec(robot, combo, Tt, goal=goal, terrain=terrain)
+        st = T.Structure(s)
+        b = T.Batch(st, 3)
+        b.set_all(s)
+        g, v = b.eval(np.tile(z["x"], (3, 1)))
+        rows, cols = st.pattern()
+        assert np.array_equal(rows[z["jac_idx"]], z["jac_rows"]) and np.array_equal(cols[z["jac_idx"]], z["jac_cols"])
+        for i in range(3):
+            assert tol_ratio(g[i], z["g"]) <= 1.0 and tol_ratio(v[i][z["jac_idx"]], z["jac_vals"]) <= 1.0
