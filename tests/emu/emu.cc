@@ -33,7 +33,7 @@ extern "C" int emu_eval(const towr_b200_spec* s, const double* x, double* g, dou
     const BlobLayout& L = hp.blob;
     ProblemConst pc;
     FillProblemConst(*s, pc);
-    ItemCtx cx;
+    ItemCtx<1> cx;
     cx.T = MakeTables(hp.blob_data.data(), L);
     std::vector<double> nodes(L.n_node_values), coef(6 * L.n_polys), G(hp.g_capacity);
     for (int i = 0; i < L.n_node_values; ++i) nodes[i] = cx.T.node_src[i] != 0xFFFF ? x[cx.T.node_src[i]] : 0.0;
@@ -50,7 +50,7 @@ extern "C" int emu_eval(const towr_b200_spec* s, const double* x, double* g, dou
     for (const SegmentRec& sg : hp.segments) {
       std::fill(G.begin(), G.end(), std::nan(""));
       G[kGOne] = 1.0; G[kGMass] = pc.mass;
-      for (int i = 0; i < sg.n_items; ++i) RunItem(cx, cx.T.items[sg.item0 + i]);
+      for (int i = 0; i < sg.n_items; ++i) RunItem<1>(cx, cx.T.items[sg.item0 + i]);   // level-0 items come first
       // walk the permuted descriptors exactly like the kernel's stage B
       const int chunks = (sg.n_entries + kEntryChunk - 1) / kEntryChunk;
       for (int k = 0; k < chunks; ++k)

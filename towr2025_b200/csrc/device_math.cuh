@@ -38,8 +38,10 @@ __device__ __forceinline__ Tables MakeTables(const unsigned char* blob, const Bl
   return t;
 }
 
-// nodes[slot*6 + deriv*3 + dim], coef[poly*6 + {0:c,3:d} + dim]
-template <int NEED>
+// Per-problem arrays are interleaved over the P problems a CTA evaluates in lock step: element i of this thread's
+// problem is base[i * P] (the base pointers are already offset by the problem's lane).
+// nodes: element slot*6 + deriv*3 + dim ; coef: element poly*6 + {0:c,3:d} + dim
+template <int NEED, int P>
 __device__ __forceinline__ void EvalSpline(const Tables& tb_, const double* __restrict__ nodes,
                                            const double* __restrict__ coef, int sample, Pt3& o) {
   const uint32_t sr = tb_.samples[sample];
@@ -49,8 +51,8 @@ __device__ __forceinline__ void EvalSpline(const Tables& tb_, const double* __re
   const int n0 = tb_.polys[poly] & 0xFFFF;
 #pragma unroll
   for (int d = 0; d < 3; ++d) {
-    const double a = nodes[n0 * 6 + d], b = nodes[n0 * 6 + 3 + d];
-    const double c = coef[poly * 6 + d], dd = coef[poly * 6 + 3 + d];
+    const double a = nodes[(n0 * 6 + d) * P], b = nodes[(n0 * 6 + 3 + d) * P];
+    const double c = coef[(poly * 6 + d) * P], dd = coef[(poly * 6 + 3 + d) * P];
     if (NEED & kNeedPos) o.p[d] = ((a + t * b) + t2 * c) + t3 * dd;
     if (NEED & kNeedVel) o.v[d] = (b + (2 * t) * c) + (3 * t2) * dd;
     if (NEED & kNeedAcc) o.a[d] = 2.0 * c + (6 * t) * dd;

@@ -14,7 +14,7 @@ namespace tb {
 
 constexpr int kThreads = kEntryThreads;
 #ifndef TB_MIN_CTAS
-#define TB_MIN_CTAS 4
+#define TB_MIN_CTAS 1
 #endif
 constexpr int kMinCtasPerSm = TB_MIN_CTAS;   // caps registers at 64: the long dynamic item spills to local memory, stage B does not
 
@@ -22,110 +22,128 @@ __device__ __forceinline__ bool NonFinite(double v) {
   return (__double2hiint(v) & 0x7ff00000) == 0x7ff00000;
 }
 
-// bar.sync on a named barrier: the 256 threads of one lane (lanes are whole warps, so this is warp-uniform)
-__device__ __forceinline__ void LaneSync(int lane) {
-  asm volatile("bar.sync %0, %1;" ::"r"(lane + 1), "n"(kThreads) : "memory");
-}
-
-// LANES problems are evaluated side by side by one CTA (256 threads each) so that the class tables are held once
-// per SM; each lane has its own nodes/coef/G arrays and its own named barrier.
-template <int WHAT, int LANES>
-__global__ void __launch_bounds__(kThreads * LANES, LANES == 1 ? kMinCtasPerSm : 1)
-EvalKernel(const __grid_constant__ DeviceProgram P, const ProblemConst* __restrict__ pcs, const double* __restrict__ x,
+// P problems are evaluated in lock step by one CTA of 256*P threads: the class tables are held once per SM, every
+// stage spreads (item, problem) pairs over all threads, and in stage B one descriptor load and one B load feed the
+// P problems.  All per-problem shared arrays are interleaved (element i of problem p at [i*P + p]).
+template <int WHAT, int P>
+__global__ void __launch_bounds__(kThreads * P, 1)
+EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restrict__ pcs, const double* __restrict__ x,
            double* __restrict__ g_out, double* __restrict__ vals_out, int* __restrict__ status, int n_problems) {
+  constexpr int NT = kThreads * P;
   extern __shared__ uint4 sm4[];
   unsigned char* blob = reinterpret_cast<unsigned char*>(sm4);
-  const int lane = LANES == 1 ? 0 : threadIdx.x / kThreads;
-  const int tid = LANES == 1 ? threadIdx.x : threadIdx.x % kThreads;
-  const int lane_doubles = P.blob.n_node_values + 6 * P.blob.n_polys + P.g_capacity;
-  double* nodes = reinterpret_cast<double*>(blob + P.blob.bytes) + lane * lane_doubles;
-  double* coef = nodes + P.blob.n_node_values;
-  double* G = coef + 6 * P.blob.n_polys;
-  __shared__ ProblemConst pc_all[LANES];
-  ProblemConst& pc_s = pc_all[lane];
+  const int nnv = Pg.blob.n_node_values, npoly = Pg.blob.n_polys;
+  double* nodes = reinterpret_cast<double*>(blob + Pg.blob.bytes);
+  double* coef = nodes + nnv * P;
+  double* G = coef + 6 * npoly * P;
+  __shared__ ProblemConst pc_all[P];
+  __shared__ int bad_all[P];
+  const int tid = threadIdx.x;
 
-  // class tables: one 16-byte-vector copy per CTA, reused for every problem this CTA evaluates
+  // class tables: one 16-byte-vector copy per CTA, reused for every problem group this CTA evaluates
   {
-    const uint4* src = reinterpret_cast<const uint4*>(P.blob_data);
-    for (int i = threadIdx.x; i < P.blob.bytes / 16; i += kThreads * LANES) sm4[i] = __ldg(src + i);
+    const uint4* src = reinterpret_cast<const uint4*>(Pg.blob_data);
+    for (int i = tid; i < Pg.blob.bytes / 16; i += NT) sm4[i] = __ldg(src + i);
   }
   __syncthreads();
-  ItemCtx cx;
-  cx.T = MakeTables(blob, P.blob);
-  cx.nodes = nodes; cx.coef = coef; cx.G = G; cx.pc = &pc_s;
+  ItemCtx<P> cx;
+  cx.T = MakeTables(blob, Pg.blob);
   const double* Bs = cx.T.B;
+  const int pl = tid % P;                               // problem lane of this thread in stages N, C, A
 
-  for (int prob = blockIdx.x * LANES + lane; prob < n_problems; prob += gridDim.x * LANES) {
-    const double* xp = x + static_cast<size_t>(prob) * P.n_vars;
-    cx.g = (WHAT & TOWR_B200_EVAL_G) ? g_out + static_cast<size_t>(prob) * P.n_rows : nullptr;
-    double* vp = (WHAT & TOWR_B200_EVAL_JAC) ? vals_out + static_cast<size_t>(prob) * P.nnz : nullptr;
+  for (int base = blockIdx.x * P; base < n_problems; base += gridDim.x * P) {
+    // the last group may hold fewer than P problems: the spare lanes recompute the last problem (same values to
+    // the same addresses) so that no stage needs a bounds test
+    const int prob = min(base + pl, n_problems - 1);
+    const double* xp = x + static_cast<size_t>(prob) * Pg.n_vars;
+    cx.nodes = nodes + pl;
+    cx.coef = coef + pl;
+    cx.G = G + pl;
+    cx.pc = &pc_all[pl];
+    cx.g = (WHAT & TOWR_B200_EVAL_G) ? g_out + static_cast<size_t>(prob) * Pg.n_rows : nullptr;
     int bad = 0;
 
     // ---- stage N: node values from x (values that are not optimised are pinned to 0)
-    if (tid == 0) pc_s = pcs[prob];
-    for (int i = tid; i < P.blob.n_node_values; i += kThreads) {
-      const unsigned src = cx.T.node_src[i];
+    if (tid < P) { pc_all[tid] = pcs[min(base + tid, n_problems - 1)]; bad_all[tid] = 0; }
+    for (int i = tid; i < nnv * P; i += NT) {
+      const unsigned src = cx.T.node_src[i / P];
       const double v = src != 0xFFFFu ? __ldg(xp + src) : 0.0;
       bad |= NonFinite(v);
       nodes[i] = v;
     }
-    LaneSync(lane);
+    __syncthreads();
 
     // ---- stage C: c = -(3(p0-p1) + T(2 v0 + v1))/T^2, d = (2(p0-p1) + T(v0+v1))/T^3   (polynomial.cc:97-104)
-    for (int i = tid; i < 3 * P.blob.n_polys; i += kThreads) {
-      const int poly = i / 3, d = i - 3 * poly;
+    for (int i = tid; i < 3 * npoly * P; i += NT) {
+      const int pd = i / P;                             // (poly, dim) pair; i % P == pl
+      const int poly = pd / 3, d = pd - 3 * poly;
       const uint32_t pr = cx.T.polys[poly];
       const int n0 = pr & 0xFFFF;
       const double* du = cx.T.durs + 3 * (pr >> 16);
       const double T = du[0], T2 = du[1], T3 = du[2];
-      const double p0 = nodes[n0 * 6 + d], v0 = nodes[n0 * 6 + 3 + d];
-      const double p1 = nodes[n0 * 6 + 6 + d], v1 = nodes[n0 * 6 + 9 + d];
-      coef[poly * 6 + d] = -(3.0 * (p0 - p1) + T * (2.0 * v0 + v1)) / T2;
-      coef[poly * 6 + 3 + d] = (2.0 * (p0 - p1) + T * (v0 + v1)) / T3;
+      const double* nd = nodes + pl;
+      const double p0 = nd[(n0 * 6 + d) * P], v0 = nd[(n0 * 6 + 3 + d) * P];
+      const double p1 = nd[(n0 * 6 + 6 + d) * P], v1 = nd[(n0 * 6 + 9 + d) * P];
+      coef[(poly * 6 + d) * P + pl] = -(3.0 * (p0 - p1) + T * (2.0 * v0 + v1)) / T2;
+      coef[(poly * 6 + 3 + d) * P + pl] = (2.0 * (p0 - p1) + T * (v0 + v1)) / T3;
     }
-    LaneSync(lane);
+    __syncthreads();
 
-    for (int s = 0; s < P.n_segments; ++s) {
-      const SegmentRec sg = P.segments[s];
-      // ---- stage A
-      if (tid == 0) { G[kGOne] = 1.0; G[kGMass] = pc_s.mass; }
-      for (int i = tid; i < sg.n_items; i += kThreads) RunItem(cx, cx.T.items[sg.item0 + i]);
-      LaneSync(lane);
-      // ---- stage B: value = G[g] * B[b]; one 16-byte descriptor load feeds four coalesced 8-byte stores
+    for (int s = 0; s < Pg.n_segments; ++s) {
+      const SegmentRec sg = Pg.segments[s];
+      // ---- stage A, level 0 then level 1: thread -> (item, problem lane)
+      if (tid < P) { G[kGOne * P + tid] = 1.0; G[kGMass * P + tid] = pc_all[tid].mass; }
+      for (int i = tid; i < sg.n_items0 * P; i += NT) RunItem<P>(cx, cx.T.items[sg.item0 + i / P]);
+      __syncthreads();
+      if (sg.n_items > sg.n_items0) {
+        for (int i = tid; i < (sg.n_items - sg.n_items0) * P; i += NT)
+          RunItem<P>(cx, cx.T.items[sg.item0 + sg.n_items0 + i / P]);
+        __syncthreads();
+      }
+      // ---- stage B: value_p = G_p[g] * B[b] for the P problems; one 16-byte descriptor load feeds 4*P coalesced stores
       if (WHAT & TOWR_B200_EVAL_JAC) {
-        const uint4* __restrict__ ent = P.entries + sg.desc0 + tid;
-        double* __restrict__ out = vp + sg.entry0 + tid;
-        const int n = sg.n_entries;
-        const int chunks = (n + kEntryChunk - 1) / kEntryChunk;
+        const int tt = tid % kThreads, q = tid / kThreads;            // q: which chunks this 256-thread group takes
+        const uint4* __restrict__ ent = Pg.entries + sg.desc0 + tt;
+        const int chunks = (sg.n_entries + kEntryChunk - 1) / kEntryChunk;
         const char* Gb = reinterpret_cast<const char*>(G);
         const char* Bb = reinterpret_cast<const char*>(Bs);
-        auto val = [&](uint32_t d) {     // descriptors hold byte offsets: G in the low half, B in the high half
-          return *reinterpret_cast<const double*>(Gb + (d & 0xFFFFu)) * *reinterpret_cast<const double*>(Bb + (d >> 16));
+        double* out0 = vals_out + static_cast<size_t>(base) * Pg.nnz + sg.entry0 + tt;
+        const int np = min(P, n_problems - base);
+        auto emit = [&](uint32_t d, double* o) {          // descriptor: G byte offset (low), B byte offset (high)
+          const double bv = *reinterpret_cast<const double*>(Bb + (d >> 16));
+          const double* gp = reinterpret_cast<const double*>(Gb + (d & 0xFFFFu) * P);
+#pragma unroll
+          for (int p = 0; p < P; ++p)
+            if (p < np) o[static_cast<size_t>(p) * Pg.nnz] = gp[p] * bv;
         };
-        uint4 w = __ldg(ent);
-        for (int k = 0; k + 1 < chunks; ++k) {          // full chunks: no bounds checks
-          const uint4 cur = w;
-          w = __ldg(ent + (k + 1) * kEntryThreads);     // prefetch the next chunk's descriptors
-          double* o = out + k * kEntryChunk;
-          const double v0 = val(cur.x), v1 = val(cur.y), v2 = val(cur.z), v3 = val(cur.w);
-          o[0] = v0;
-          o[kEntryThreads] = v1;
-          o[2 * kEntryThreads] = v2;
-          o[3 * kEntryThreads] = v3;
-        }
-        if (chunks > 0) {                               // last chunk: may be partial
-          double* o = out + (chunks - 1) * kEntryChunk;
-          if (w.x != kNoEntry) o[0] = val(w.x);
-          if (w.y != kNoEntry) o[kEntryThreads] = val(w.y);
-          if (w.z != kNoEntry) o[2 * kEntryThreads] = val(w.z);
-          if (w.w != kNoEntry) o[3 * kEntryThreads] = val(w.w);
+        if (q < chunks) {
+          uint4 w = __ldg(ent + q * kEntryThreads);
+          for (int k = q; k < chunks; k += P) {
+            const uint4 cur = w;
+            if (k + P < chunks) w = __ldg(ent + (k + P) * kEntryThreads);   // prefetch this thread's next chunk
+            double* o = out0 + k * kEntryChunk;
+            if (k + 1 < chunks) {                         // full chunk: no bounds checks
+              emit(cur.x, o);
+              emit(cur.y, o + kEntryThreads);
+              emit(cur.z, o + 2 * kEntryThreads);
+              emit(cur.w, o + 3 * kEntryThreads);
+            } else {
+              if (cur.x != kNoEntry) emit(cur.x, o);
+              if (cur.y != kNoEntry) emit(cur.y, o + kEntryThreads);
+              if (cur.z != kNoEntry) emit(cur.z, o + 2 * kEntryThreads);
+              if (cur.w != kNoEntry) emit(cur.w, o + 3 * kEntryThreads);
+            }
+          }
         }
         // a non-finite Jacobian value needs a non-finite G slot (B is finite): check the slots, not the entries
-        for (int i = tid; i < sg.g_size; i += kThreads) bad |= NonFinite(G[i]);
+        for (int i = tid; i < sg.g_size * P; i += NT)
+          if (NonFinite(G[i])) atomicOr(&bad_all[i % P], 1);
       }
-      LaneSync(lane);
+      __syncthreads();
     }
-    if (bad) atomicOr(status + prob, 2);
+    if (bad) atomicOr(&bad_all[pl], 1);
+    __syncthreads();
+    if (tid < P && bad_all[tid] && base + tid < n_problems) atomicOr(status + base + tid, 2);
   }
 }
 

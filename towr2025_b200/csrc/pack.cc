@@ -1,5 +1,6 @@
 // pack.cc — compacts the builder's tables into the device form: one shared-memory blob of class tables and the
 // thread-major permuted entry descriptors (program.h).
+#include <array>
 #include <cstring>
 #include <map>
 #include <stdexcept>
@@ -40,8 +41,7 @@ void PackProgram(HostProgram& hp) {
     samples.push_back(static_cast<uint32_t>(r.poly) | (static_cast<uint32_t>(t) << 16));
   };
   std::vector<ItemC> items;
-  std::map<int, int> dyn_s0;   // wide index of a dynamic sample's first SampleRec -> compact s0 (shared by the 4 sub-items)
-  std::vector<std::pair<int, int>> kind;   // (type, sub) per compact item
+  std::vector<std::array<int, 3>> kind;   // (level, type, sub) per compact item
   for (const ItemRec& it : hp.items) {
     ItemC c;
     std::memset(&c, 0, sizeof(c));
@@ -49,33 +49,25 @@ void PackProgram(HostProgram& hp) {
     c.sub = static_cast<uint8_t>(it.sub);
     c.ee = static_cast<uint8_t>(it.ee);
     c.n_ee = static_cast<uint8_t>(it.n_ee);
-    if (it.gslot > 0xFFFF || it.b0 > 0xFFFF) throw std::runtime_error("item slot out of range");
+    if (it.gslot > 0xFFFF || it.b0 > 0xFFFF || it.aux > 0xFFFF) throw std::runtime_error("item slot out of range");
     c.gslot = static_cast<uint16_t>(it.gslot);
     c.b0 = static_cast<uint16_t>(it.b0);
+    c.aux = static_cast<uint16_t>(it.aux);
     c.row = static_cast<uint32_t>(it.row[0]);
     const int E = it.n_ee;
     size_t s0 = samples.size();
     switch (it.type) {
-      case kItemDynamic: {
-        auto f = dyn_s0.find(it.s[kSBaseLin]);
-        if (f != dyn_s0.end()) { s0 = f->second; break; }
-        dyn_s0[it.s[kSBaseLin]] = static_cast<int>(s0);
+      case kItemDynPre: add_sample(it.s[kSBaseAng]); break;
+      case kItemDynWrench:
         add_sample(it.s[kSBaseLin]);
-        add_sample(it.s[kSBaseAng]);
         for (int e = 0; e < E; ++e) { add_sample(it.s[kSMotion + e]); add_sample(it.s[kSForce + e]); add_sample(it.s[kSTorque + e]); }
         break;
-      }
-      case kItemRom: {
+      case kItemDynCol: s0 = 0; break;
+      case kItemRomPre:
         add_sample(it.s[kSBaseLin]);
         add_sample(it.s[kSBaseAng]);
-        for (int e = 0; e < E; ++e) add_sample(it.s[kSMotion + e]);
-        int stride = E > 1 ? it.row[1] - it.row[0] : 0;
-        for (int e = 1; e < E; ++e)
-          if (it.row[e] - it.row[e - 1] != stride) throw std::runtime_error("RoM sets are not equally spaced");
-        if (stride < 0 || stride > 0xFFFF) throw std::runtime_error("unsupported: RoM set larger than 65535 rows");
-        c.aux = static_cast<uint16_t>(stride);
         break;
-      }
+      case kItemRomFoot: add_sample(it.s[kSMotion + it.ee]); break;
       case kItemForce:
         add_sample(it.s[kSMotion + it.ee]);
         add_sample(it.s[kSForce + it.ee]);
@@ -87,30 +79,34 @@ void PackProgram(HostProgram& hp) {
     if (s0 > 0xFFFF) throw std::runtime_error("unsupported: too many samples for the compact tables");
     c.s0 = static_cast<uint16_t>(s0);
     items.push_back(c);
-    kind.emplace_back(it.type, it.sub);
+    kind.push_back({ItemLevel(it.type), it.type, it.sub});
   }
-  // per segment: items of one (type, sub) kind are made contiguous and every kind starts on a warp boundary, so
-  // that no warp of stage A diverges between item kinds (null items fill the gaps)
+  // per segment: level-0 items first, then level-1; items of one (type, sub) kind are contiguous and every kind
+  // starts on a warp boundary so that no warp of stage A diverges between kinds (null items fill the gaps)
   {
     std::vector<ItemC> padded;
     ItemC none;
     std::memset(&none, 0, sizeof(none));
     none.type = kItemNone;
     for (SegmentRec& sg : hp.segments) {
-      std::vector<std::pair<int, int>> kinds;
-      for (int i = 0; i < sg.n_items; ++i) {
-        auto k = kind[sg.item0 + i];
-        bool seen = false;
-        for (auto& q : kinds) seen |= (q == k);
-        if (!seen) kinds.push_back(k);
-      }
       const int new0 = static_cast<int>(padded.size());
-      for (auto& k : kinds) {
+      for (int level = 0; level < 2; ++level) {
+        std::vector<std::array<int, 3>> kinds;
+        for (int i = 0; i < sg.n_items; ++i) {
+          auto k = kind[sg.item0 + i];
+          if (k[0] != level) continue;
+          bool seen = false;
+          for (auto& q : kinds) seen |= (q == k);
+          if (!seen) kinds.push_back(k);
+        }
+        for (auto& k : kinds) {
+          while (padded.size() % 32) padded.push_back(none);
+          for (int i = 0; i < sg.n_items; ++i)
+            if (kind[sg.item0 + i] == k) padded.push_back(items[sg.item0 + i]);
+        }
         while (padded.size() % 32) padded.push_back(none);
-        for (int i = 0; i < sg.n_items; ++i)
-          if (kind[sg.item0 + i] == k) padded.push_back(items[sg.item0 + i]);
+        if (level == 0) sg.n_items0 = static_cast<int>(padded.size()) - new0;
       }
-      while (padded.size() % 32) padded.push_back(none);
       sg.item0 = new0;
       sg.n_items = static_cast<int>(padded.size()) - new0;
     }

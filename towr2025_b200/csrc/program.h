@@ -40,16 +40,29 @@ struct SampleRec {      // "spline S evaluated at global time t" for fixed durat
 };
 
 enum ItemType : int {
-  kItemDynamic = 0,     // dynamic_constraint.cc:63-148            6 rows per sample
-  kItemRom,             // range_of_motion_constraint.cc:72-131    3 rows per (sample, foot); one item serves all feet
+  // level 0: independent of other items
+  kItemDynPre = 0,      // per dynamic sample: euler point, trig, R, R I_b, I_w, M, Mdot, omega, omegadot ... -> scratch slots
+  kItemRomPre,          // per RoM sample: base position, R and dR/d(euler) -> scratch slots
   kItemForce,           // force_constraint_discretized.cc:97-221  5 rows per (sample, foot)
   kItemTerrainNode,     // terrain_constraint.cc:61-111            1 row per ee-motion node
   kItemBaseHeightNode,  // base_height_constraint.cc:58-110        1 row per base-lin node
   kItemSwingNode,       // swing_constraint.cc:54-108              4 rows per swing node
   kItemSplineAcc,       // spline_acc_constraint.cc:48-80          3 rows per junction
   kItemTotalDuration,   // total_duration_constraint.cc:48-72
+  // level 1: read the scratch slots of a level-0 item (ItemC::aux)
+  kItemDynWrench,       // dynamic_constraint.cc:63-148: 6 g rows, f_e, c - p_e, finished base-lin angular block
+  kItemDynCol,          // one euler column (sub) of the finished base-ang block of a dynamic sample
+  kItemRomFoot,         // range_of_motion_constraint.cc:72-131: 3 g rows + d(R^T r)/d(euler) of one (sample, foot)
   kItemNone = 255,      // padding: keeps every warp of stage A on one item kind
 };
+inline int ItemLevel(int type) { return type >= kItemDynWrench && type != kItemNone ? 1 : 0; }
+
+// scratch layouts written by the level-0 items (slot offsets)
+enum { kDpV = 0, kDpA = 3, kDpTrig = 6, kDpR = 12, kDpRI = 21, kDpIw = 30, kDpM = 39, kDpMd = 44, kDpW = 49, kDpWd = 52,
+       kDpIww = 55, kDpV11 = 58, kDpV21 = 61, kDynPreSize = 64 };
+enum { kRpLin = 0, kRpR = 3, kRpDR = 12, kRomPreSize = 39 };
+// G layout of a dynamic sample: finished base-ang block, finished base-lin angular block, f_e, c - p_e
+enum { kDynJang = 0, kDynJlin = 36, kDynF = 72 };
 
 constexpr int kMaxEE = 4;
 // indices into ItemRec::s
@@ -62,6 +75,7 @@ struct ItemRec {
   short sub;            // dynamic: 0 = wrench part, 1..3 = euler column (sub-1) of the base-ang block
   short n_ee;
   short pad;
+  int aux;              // level-1 items: first scratch slot of their level-0 parent
   int b0;               // dynamic: first of the 16 Hermite basis constants of this sample in B (see structure.cc)
   int row[kMaxEE];      // first constraint row written (absolute in g); RoM: one per foot
   int s[kSCount];       // SampleRec indices; node-based items: node slot / polynomial index in s[0]
@@ -78,7 +92,8 @@ constexpr int kEntryThreads = 256;
 constexpr int kEntryChunk = 4 * kEntryThreads;
 constexpr uint32_t kNoEntry = 0xFFFFFFFFu;
 struct SegmentRec {
-  int item0, n_items;   // items of this segment
+  int item0, n_items;   // items of this segment: n_items0 level-0 items first, then the level-1 items
+  int n_items0, pad;
   int entry0, n_entries;// entries fed by this segment (contiguous in storage order)
   int g_size;           // G slots used
   int desc0;            // first uint4 of the segment's permuted descriptors
@@ -93,13 +108,13 @@ enum { kGOne = 0, kGMass = 1, kGReserved = 2 };
 struct ItemC {          // 16 bytes
   uint8_t type, sub, ee, n_ee;
   uint16_t gslot, b0;
-  uint32_t row;         // first constraint row; RoM: row of foot e = row + e * aux
+  uint32_t row;         // first constraint row
   uint16_t s0;          // first compact sample of the item; node items: node slot; splineacc: polynomial index
-  uint16_t aux;
+  uint16_t aux;         // level-1 items: first scratch slot of the level-0 parent
 };
 // compact sample = polynomial index | time index << 16 ; compact polynomial = node slot | duration index << 16
-// sample order of an item: dynamic [lin, ang, (motion, force, torque) per foot], RoM [lin, ang, motion per foot],
-// force [motion, force]
+// sample order of an item: DynPre [ang], DynWrench [lin, (motion, force, torque) per foot], RomPre [lin, ang],
+// RomFoot [motion], Force [motion, force]
 struct BlobLayout {     // byte offsets into the blob (all 16-byte aligned), element counts
   int bytes;
   int off_B, n_B;                 // double

@@ -132,10 +132,14 @@ class Builder {
   }
 
   // ---- segments / groups
-  void BeginGroup() {
+  // A group is the unit of segment packing.  When a group starts a new segment in the middle of a constraint set
+  // (time-discretised sets are split by sample ranges), the rows finished so far are flushed first so that every
+  // segment owns a contiguous range of entries.  next_row_local = first row of the set the new group writes.
+  void BeginGroup(int next_row_local = 0) {
     int gi = static_cast<int>(group_g_size.size());
     bool new_seg = hp_.segments.empty() || (plan_ ? (*plan_)[gi] != 0 : true);
     if (new_seg) {
+      FlushRows(next_row_local);
       CloseSegment();
       SegmentRec sg{};
       sg.item0 = static_cast<int>(hp_.items.size());
@@ -167,6 +171,7 @@ class Builder {
     hp_.con_sets.push_back(ConSet{name, hp_.n_rows, n_rows});
     hp_.n_rows += n_rows;
     rows_.assign(n_rows, {});
+    rows_flushed_ = 0;
     hp_.row_bounds.resize(hp_.n_rows, RowBound{kBoundZero, 0, 0});
   }
   void Bound(int row_local, int kind, int ee = 0, int dim = 0) { hp_.row_bounds.at(set_row0_ + row_local) = RowBound{kind, ee, dim}; }
@@ -180,8 +185,8 @@ class Builder {
       }
     r.emplace_back(col, t);
   }
-  void EndSet() {
-    for (size_t r = 0; r < rows_.size(); ++r) {
+  void FlushRows(int upto) {            // rows [rows_flushed_, upto) of the open set are complete
+    for (int r = rows_flushed_; r < upto && r < static_cast<int>(rows_.size()); ++r) {
       auto& row = rows_[r];
       std::stable_sort(row.begin(), row.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
       for (auto& e : row) {
@@ -189,11 +194,17 @@ class Builder {
         if (t.g < 0 || t.g > 65535 || t.b < 0 || t.b > 65535) throw std::runtime_error("entry descriptor out of range");
         EntryRec er = static_cast<uint32_t>(t.g) | (static_cast<uint32_t>(t.b) << 16);
         hp_.entries.push_back(er);
-        hp_.pat_rows.push_back(set_row0_ + static_cast<int>(r));
+        hp_.pat_rows.push_back(set_row0_ + r);
         hp_.pat_cols.push_back(e.first);
       }
+      row.clear();
     }
+    if (upto > rows_flushed_) rows_flushed_ = std::min(upto, static_cast<int>(rows_.size()));
+  }
+  void EndSet() {
+    FlushRows(static_cast<int>(rows_.size()));
     rows_.clear();
+    rows_flushed_ = 0;
   }
   ItemRec NewItem(int type) const {
     ItemRec it;
@@ -224,6 +235,7 @@ class Builder {
   std::map<std::string, int> brun_;
   std::vector<std::vector<std::pair<int, Term>>> rows_;
   int set_row0_ = 0;
+  int rows_flushed_ = 0;
 };
 
 // Cross(v)(r,d) = sign * v[k] for r != d (single_rigid_body_dynamics.cc:47-57)
@@ -271,11 +283,9 @@ void Builder::EmitBaseHeight() {
 }
 
 // DynamicConstraint, 6 rows per sample (dynamic_constraint.cc:57-126 with single_rigid_body_dynamics.cc:104-204).
-// Four items per sample: sub 0 evaluates the wrench part (g rows, forces, lever arms, the base-lin angular block),
-// sub 1..3 one euler column each of the base-ang block.  G layout per sample:
-//   Jang[3][12]  d(angular rows)/d(base-ang variable (sd, c)) at slot r*12 + sd*3 + c   (finished values)
-//   Jlin[3][12]  d(angular rows)/d(base-lin variable (sd, d)) at slot r*12 + sd*3 + d   (finished; d == r unused)
-//   f_e[3], (c - p_e)[3] per foot
+// Per sample: one level-0 item (DynPre: everything that depends on the euler spline only) and four level-1 items
+// (DynWrench: g rows, forces, lever arms, base-lin angular block; DynCol x3: one euler column of the base-ang block).
+// G layout per sample: Jang[3][12] at r*12 + sd*3 + c | Jlin[3][12] at r*12 + sd*3 + d | f_e[3] | (c - p_e)[3] | scratch.
 // B run of the sample (ItemRec::b0): base-lin pos basis [4], then base-ang pos/vel/acc basis [4] each, by sd.
 void Builder::EmitDynamic() {
   const int E = s_.n_ee;
@@ -283,16 +293,21 @@ void Builder::EmitDynamic() {
   const VarSet& ang = Set(kBaseAng);
   const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_dynamic);
   const int one = AddB(1.0);
-  BeginGroup();
-  BeginSet("dynamic", static_cast<int>(ts.size()) * 6);
+  const int per_sample = 72 + 6 * E + kDynPreSize;
+  const int chunk = std::max(1, 1024 / per_sample);      // samples per group
   for (size_t k = 0; k < ts.size(); ++k) {
     const double t = ts[k];
     const int r0 = static_cast<int>(k) * 6;
-    ItemRec it = NewItem(kItemDynamic);
+    if (k % chunk == 0) {
+      if (k == 0) { BeginGroup(); BeginSet("dynamic", static_cast<int>(ts.size()) * 6); }
+      else BeginGroup(r0);
+    }
+    ItemRec it = NewItem(kItemDynWrench);
     it.row[0] = set_row0_ + r0;
-    const int g0 = AllocG(72 + 6 * E);
+    const int g0 = AllocG(per_sample);
     it.gslot = g0;
-    const int gJang = g0, gJlin = g0 + 36, gF = g0 + 72, gR = g0 + 72 + 3 * E;
+    it.aux = g0 + 72 + 6 * E;
+    const int gJang = g0 + kDynJang, gJlin = g0 + kDynJlin, gF = g0 + kDynF, gR = g0 + kDynF + 3 * E;
 
     SplineAt al = At(lin, t), aa = At(ang, t);
     it.s[kSBaseLin] = al.sample;
@@ -354,9 +369,16 @@ void Builder::EmitDynamic() {
         Add(r0 + c.dim, to.col0 + c.idx, tm);
       }
     }
-    for (int sub = 0; sub < 4; ++sub) {
-      it.sub = static_cast<short>(sub);
-      hp_.items.push_back(it);
+    ItemRec pre = it;
+    pre.type = kItemDynPre;
+    pre.gslot = it.aux;
+    hp_.items.push_back(pre);
+    hp_.items.push_back(it);
+    for (int c = 0; c < 3; ++c) {
+      ItemRec col = it;
+      col.type = kItemDynCol;
+      col.sub = static_cast<short>(c);
+      hp_.items.push_back(col);
     }
   }
   EndSet();
@@ -392,7 +414,8 @@ void Builder::EmitSplineAcc() {
 }
 
 // RangeOfMotionConstraint, one set per foot, 3 rows per sample (range_of_motion_constraint.cc:66-131).
-// One item per sample serves all feet: G = R^T (9) then d(R^T r_e)/d(euler) (9) per foot.
+// Per sample one level-0 item (RomPre: base position, R, dR/d(euler) -> 39 scratch slots) shared by the feet, and
+// per (sample, foot) one level-1 item (RomFoot: 3 g rows, d(R^T r_e)/d(euler) -> 9 slots).
 void Builder::EmitRom() {
   const int E = s_.n_ee;
   const VarSet& lin = Set(kBaseLin);
@@ -400,13 +423,12 @@ void Builder::EmitRom() {
   const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_range_of_motion);
   const int K = static_cast<int>(ts.size());
   BeginGroup();
-  const int item0 = static_cast<int>(hp_.items.size());
-  struct PerSample { int g0; SplineAt al, aa; };
+  struct PerSample { int pre; SplineAt al, aa; };
   std::vector<PerSample> ps(K);
   for (int k = 0; k < K; ++k) {
-    ItemRec it = NewItem(kItemRom);
-    ps[k].g0 = AllocG(9 + 9 * E);
-    it.gslot = ps[k].g0;
+    ItemRec it = NewItem(kItemRomPre);
+    ps[k].pre = AllocG(kRomPreSize);
+    it.gslot = ps[k].pre;
     ps[k].al = At(lin, ts[k]);
     ps[k].aa = At(ang, ts[k]);
     it.s[kSBaseLin] = ps[k].al.sample;
@@ -417,15 +439,19 @@ void Builder::EmitRom() {
     const VarSet& mo = Set(kEEMotion, e);
     BeginSet("rangeofmotion-" + std::to_string(e), 3 * K);
     for (int k = 0; k < K; ++k) {
-      ItemRec& it = hp_.items[item0 + k];
-      it.row[e] = set_row0_ + 3 * k;
+      ItemRec it = NewItem(kItemRomFoot);
+      it.ee = static_cast<short>(e);
+      it.row[0] = set_row0_ + 3 * k;
+      it.aux = ps[k].pre;
+      it.gslot = AllocG(9);
       SplineAt am = At(mo, ts[k]);
       it.s[kSMotion + e] = am.sample;
+      hp_.items.push_back(it);
       for (int r = 0; r < 3; ++r) Bound(3 * k + r, kBoundRom, e, r);
-      const int gRT = ps[k].g0, gD = ps[k].g0 + 9 + 9 * e;
+      const int gR = ps[k].pre + kRpR, gD = it.gslot;      // R^T(r,d) = R[d][r] lives at gR + d*3 + r
       for (const ColBasis& c : Columns(lin, ps[k].al.poly, ps[k].al.t_local))
         for (int r = 0; r < 3; ++r) {            // (-1 * R^T) J_c
-          Term tm; tm.g = gRT + r * 3 + c.dim; tm.b = AddB(-c.v[0]);
+          Term tm; tm.g = gR + c.dim * 3 + r; tm.b = AddB(-c.v[0]);
           Add(3 * k + r, lin.col0 + c.idx, tm);
         }
       for (const ColBasis& c : Columns(ang, ps[k].aa.poly, ps[k].aa.t_local))
@@ -436,7 +462,7 @@ void Builder::EmitRom() {
         }
       for (const ColBasis& c : Columns(mo, am.poly, am.t_local))
         for (int r = 0; r < 3; ++r) {            // R^T J_p
-          Term tm; tm.g = gRT + r * 3 + c.dim; tm.b = AddB(c.v[0]);
+          Term tm; tm.g = gR + c.dim * 3 + r; tm.b = AddB(c.v[0]);
           Add(3 * k + r, mo.col0 + c.idx, tm);
         }
     }
@@ -449,9 +475,12 @@ void Builder::EmitForceDisc(int ee) {
   const VarSet& mo = Set(kEEMotion, ee);
   const VarSet& fo = Set(kEEForce, ee);
   const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_force);
-  BeginGroup();
-  BeginSet("force-disc-" + fo.name, static_cast<int>(ts.size()) * 5);
+  const int chunk = 64;                             // samples per group (15 G slots each)
   for (size_t k = 0; k < ts.size(); ++k) {
+    if (k % chunk == 0) {
+      if (k == 0) { BeginGroup(); BeginSet("force-disc-" + fo.name, static_cast<int>(ts.size()) * 5); }
+      else BeginGroup(static_cast<int>(k) * 5);
+    }
     ItemRec it = NewItem(kItemForce);
     it.ee = static_cast<short>(ee);
     it.row[0] = set_row0_ + static_cast<int>(k) * 5;
