@@ -33,7 +33,7 @@ extern "C" int emu_eval(const towr_b200_spec* s, const double* x, double* g, dou
     const BlobLayout& L = hp.blob;
     ProblemConst pc;
     FillProblemConst(*s, pc);
-    ItemCtx<1> cx;
+    ItemCtx<Lockstep<1>> cx;
     cx.T = MakeTables(hp.blob_data.data(), L);
     std::vector<double> nodes(L.n_node_values), coef(6 * L.n_polys), G(hp.g_capacity);
     for (int i = 0; i < L.n_node_values; ++i) nodes[i] = cx.T.node_src[i] != 0xFFFF ? x[cx.T.node_src[i]] : 0.0;
@@ -43,23 +43,20 @@ extern "C" int emu_eval(const towr_b200_spec* s, const double* x, double* g, dou
       int n0 = pr & 0xFFFF;
       const double* du = cx.T.durs + 3 * (pr >> 16);
       double p0 = nodes[n0 * 6 + d], v0 = nodes[n0 * 6 + 3 + d], p1 = nodes[n0 * 6 + 6 + d], v1 = nodes[n0 * 6 + 9 + d];
-      coef[poly * 6 + d] = -(3.0 * (p0 - p1) + du[0] * (2.0 * v0 + v1)) / du[1];
-      coef[poly * 6 + 3 + d] = (2.0 * (p0 - p1) + du[0] * (v0 + v1)) / du[2];
+      const double* rd = cx.T.rdurs + 2 * (pr >> 16);
+      coef[poly * 6 + d] = ExactDiv(-(3.0 * (p0 - p1) + du[0] * (2.0 * v0 + v1)), du[1], rd[0]);
+      coef[poly * 6 + 3 + d] = ExactDiv(2.0 * (p0 - p1) + du[0] * (v0 + v1), du[2], rd[1]);
     }
     cx.nodes = nodes.data(); cx.coef = coef.data(); cx.G = G.data(); cx.g = g; cx.pc = &pc;
     for (const SegmentRec& sg : hp.segments) {
       std::fill(G.begin(), G.end(), std::nan(""));
       G[kGOne] = 1.0; G[kGMass] = pc.mass;
-      for (int i = 0; i < sg.n_items; ++i) RunItem<1>(cx, cx.T.items[sg.item0 + i]);   // level-0 items come first
-      // walk the permuted descriptors exactly like the kernel's stage B
-      const int chunks = (sg.n_entries + kEntryChunk - 1) / kEntryChunk;
-      for (int k = 0; k < chunks; ++k)
-        for (int t = 0; t < kEntryThreads; ++t)
-          for (int j = 0; j < 4; ++j) {
-            uint32_t w = hp.entries_perm[4 * (static_cast<size_t>(sg.desc0) + k * kEntryThreads + t) + j];
-            if (w == kNoEntry) continue;
-            vals[sg.entry0 + k * kEntryChunk + j * kEntryThreads + t] = G[(w & 0xFFFF) / 8] * cx.T.B[(w >> 16) / 8];
-          }
+      for (int i = 0; i < sg.n_items; ++i) RunItem<Lockstep<1>>(cx, cx.T.items[sg.item0 + i]);   // level-0 items come first
+      // the device descriptors, as the kernel's stage B reads them
+      for (int e = 0; e < sg.n_entries; ++e) {
+        const uint32_t w = hp.entries_dev[sg.entry0 + e];
+        vals[sg.entry0 + e] = G[(w & 0xFFFF) / 8] * cx.T.B[(w >> 16) / 8];
+      }
     }
     return 0;
   } catch (const std::exception& e) {

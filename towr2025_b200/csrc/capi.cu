@@ -1,6 +1,7 @@
 // capi.cu — the extern "C" boundary declared in include/towr_b200.h.
 #include <cuda_runtime.h>
 
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <exception>
@@ -192,7 +193,7 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     dp.blob = hp.blob;
     auto keep = [&](auto* p) { b->owned.push_back(const_cast<void*>(static_cast<const void*>(p))); return p; };
     dp.blob_data = keep(Upload(hp.blob_data));
-    dp.entries = reinterpret_cast<const uint4*>(keep(Upload(hp.entries_perm)));
+    dp.entries = keep(Upload(hp.entries_dev));
     dp.segments = keep(Upload(hp.segments));
     b->pc_host.assign(n_problems, tb::ProblemConst{});
     Check(cudaMalloc(&b->pc_dev, sizeof(tb::ProblemConst) * n_problems), "cudaMalloc(consts)");
@@ -217,6 +218,9 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     }
     if (b->lanes == 0)
       throw std::runtime_error("unsupported: structure class needs more shared memory per CTA than the device has");
+    if (std::getenv("TOWR_B200_DEBUG"))
+      std::fprintf(stderr, "batch: %d problems per CTA, %zu B shared (blob %d B, G capacity %d), %d CTAs\n", b->lanes,
+                   tb::EvalSharedBytes(dp, b->lanes), dp.blob.bytes, dp.g_capacity, b->max_ctas);
     *out = b.release();
   });
 }

@@ -20,6 +20,8 @@ struct Tables {
   const double* B;
   const double* times;      // 3 per entry
   const double* durs;       // 3 per entry
+  const double* rdurs;      // 2 per entry
+  const SegmentRec* segments;
   const ItemC* items;
   const uint32_t* samples;
   const uint32_t* polys;
@@ -31,11 +33,22 @@ __device__ __forceinline__ Tables MakeTables(const unsigned char* blob, const Bl
   t.B = reinterpret_cast<const double*>(blob + L.off_B);
   t.times = reinterpret_cast<const double*>(blob + L.off_times);
   t.durs = reinterpret_cast<const double*>(blob + L.off_durs);
+  t.rdurs = reinterpret_cast<const double*>(blob + L.off_rdurs);
+  t.segments = reinterpret_cast<const SegmentRec*>(blob + L.off_segments);
   t.items = reinterpret_cast<const ItemC*>(blob + L.off_items);
   t.samples = reinterpret_cast<const uint32_t*>(blob + L.off_samples);
   t.polys = reinterpret_cast<const uint32_t*>(blob + L.off_polys);
   t.node_src = reinterpret_cast<const uint16_t*>(blob + L.off_node_src);
   return t;
+}
+
+// a / b, correctly rounded, from the correctly rounded reciprocal y = RN(1/b) of a class constant b (Markstein:
+// q = RN(a y), r = a - b q exactly by FMA, RN(q + r y) = RN(a / b)): the result is bit-identical to the reference's
+// true division without the ~45-instruction software divide.  (fma is explicit: -fmad=false does not touch it.)
+__device__ __forceinline__ double ExactDiv(double a, double b, double y) {
+  const double q = a * y;
+  const double r = fma(-b, q, a);
+  return fma(r, y, q);
 }
 
 // Per-problem arrays are interleaved over the P problems a CTA evaluates in lock step: element i of this thread's

@@ -6,28 +6,35 @@
 
 namespace tb {
 
+// Memory layout of the per-problem arrays an item touches: element i of this thread's problem is at
+//   G[i * GS] (G buffer and scratch), nodes[i * NS] / coef[i * NS] (spline tables), g[i * RS] (constraint rows).
+// Lockstep<P>: the fused kernel's shared-memory arrays, interleaved over the P problems of a CTA (and the host
+// emulation, P = 1).  The tiled pipeline (tiled.cu) uses Tiled<W>.
 template <int P>
+struct Lockstep { static constexpr int GS = P, NS = P, RS = 1; };
+
+template <class L>
 struct ItemCtx {
   Tables T;
   const double* nodes;   // interleaved, offset by the problem lane (see EvalSpline)
   const double* coef;
-  double* G;             // segment-relative G buffer (shared memory), element i at G[i * P]
+  double* G;             // segment-relative G buffer (shared memory), element i at G[i * L::GS]
   double* g;             // this problem's constraint values (global), or nullptr
   const ProblemConst* pc;
 };
 
-#define TB_G(i) G[(i) * P]
+#define TB_G(i) G[(i) * L::GS]
 
 // ------------------------------------------------------------------------------------------------ dynamic, level 0
 // Everything of a dynamic sample that depends on the euler spline only (euler_converter.cc:133-221):
 // thetadot, thetaddot, trig, R, R I_b, I_w = R I_b R^T ((R I_b) first, inner index ascending), M, Mdot,
 // omega = M thetadot, omegadot = Mdot thetadot + M thetaddot, I_w omega, I_b R^T omegadot, I_b R^T omega.
-template <int P>
-__device__ __forceinline__ void ItemDynPre(const ItemCtx<P>& cx, const ItemC& it) {
+template <class L>
+__device__ __forceinline__ void ItemDynPre(const ItemCtx<L>& cx, const ItemC& it) {
   Pt3 ang;
-  EvalSpline<kNeedPos | kNeedVel | kNeedAcc, P>(cx.T, cx.nodes, cx.coef, it.s0, ang);
+  EvalSpline<kNeedPos | kNeedVel | kNeedAcc, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, ang);
   const Trig tr = MakeTrig(ang.p);
-  double* G = cx.G + it.gslot * P;
+  double* G = cx.G + it.gslot * L::GS;
   double R[9];
   RotationMatrix(tr, R);
   const double yd = ang.v[1], zd = ang.v[2];
@@ -68,85 +75,110 @@ __device__ __forceinline__ void ItemDynPre(const ItemCtx<P>& cx, const ItemC& it
   for (int d = 0; d < 3; ++d) { TB_G(kDpIww + d) = Iww[d]; TB_G(kDpV11 + d) = v11[d]; TB_G(kDpV21 + d) = v21[d]; }
 }
 
+// ------------------------------------------------------------------------------------------------ dynamic, per foot
+// f_e and (c - p_e) slots (ee-motion / ee-force blocks) and the foot's torque term Cross(f_e)(c - p_e) + tau_e
+// (dynamic_constraint.cc:63-68, single_rigid_body_dynamics.cc:80-86).
+template <class L>
+__device__ __forceinline__ void ItemDynFoot(const ItemCtx<L>& cx, const ItemC& it) {
+  const int E = it.n_ee, e = it.ee;
+  Pt3 lin, f, p, tq;
+  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, lin);
+  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 1, p);
+  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 2, f);
+  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 3, tq);
+  double* G = cx.G + it.gslot * L::GS;
+  double r[3] = {lin.p[0] - p.p[0], lin.p[1] - p.p[1], lin.p[2] - p.p[2]};
+  double cr[3];
+  Cross3(f.p, r, cr);
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    TB_G(kDynF + 3 * e + d) = f.p[d];
+    TB_G(kDynF + 3 * E + 3 * e + d) = r[d];
+    TB_G(kDynF + 6 * E + 3 * e + d) = cr[d] + tq.p[d];
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ dynamic, level 1
-// g rows (dynamic_constraint.cc:63-68,128-148 + single_rigid_body_dynamics.cc:76-102, same operation order), f_e and
-// (c - p_e) slots, and the finished base-lin angular block -sum_e Cross(f_e) J_pos.
-template <int P>
-__device__ __forceinline__ void ItemDynWrench(const ItemCtx<P>& cx, const ItemC& it) {
+// g rows (dynamic_constraint.cc:63-68,128-148 + single_rigid_body_dynamics.cc:76-102, same operation order; the feet
+// are summed in the reference's order from the DynFoot slots).
+template <class L>
+__device__ __forceinline__ void ItemDynWrench(const ItemCtx<L>& cx, const ItemC& it) {
+  if (!cx.g) return;
   const int E = it.n_ee;
   Pt3 lin;
-  EvalSpline<kNeedPos | kNeedAcc, P>(cx.T, cx.nodes, cx.coef, it.s0, lin);
-  double* G = cx.G + it.gslot * P;
-  const double* S = cx.G + it.aux * P;            // scratch of the level-0 parent
+  EvalSpline<kNeedAcc, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, lin);
+  const double* G = cx.G + it.gslot * L::GS;
+  const double* S = cx.G + it.aux * L::GS;            // scratch of the level-0 parent
   double f_sum[3] = {0.0, 0.0, 0.0}, tau_sum[3] = {0.0, 0.0, 0.0};
   for (int e = 0; e < E; ++e) {
-    Pt3 f, p, tq;
-    EvalSpline<kNeedPos, P>(cx.T, cx.nodes, cx.coef, it.s0 + 1 + 3 * e, p);
-    EvalSpline<kNeedPos, P>(cx.T, cx.nodes, cx.coef, it.s0 + 2 + 3 * e, f);
-    EvalSpline<kNeedPos, P>(cx.T, cx.nodes, cx.coef, it.s0 + 3 + 3 * e, tq);
-    double r[3] = {lin.p[0] - p.p[0], lin.p[1] - p.p[1], lin.p[2] - p.p[2]};
-    double cr[3];
-    Cross3(f.p, r, cr);
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
-      tau_sum[d] = tau_sum[d] + (cr[d] + tq.p[d]);
-      f_sum[d] = f_sum[d] + f.p[d];
-      TB_G(kDynF + 3 * e + d) = f.p[d];
-      TB_G(kDynF + 3 * E + 3 * e + d) = r[d];
+      tau_sum[d] = tau_sum[d] + TB_G(kDynF + 6 * E + 3 * e + d);
+      f_sum[d] = f_sum[d] + TB_G(kDynF + 3 * e + d);
     }
   }
-  if (cx.g) {
-    double w[3], wd[3], Iww[3], Iw[9], Iw_wd[3];
+  double w[3], wd[3], Iww[3], Iw[9], Iw_wd[3];
 #pragma unroll
-    for (int d = 0; d < 3; ++d) { w[d] = S[(kDpW + d) * P]; wd[d] = S[(kDpWd + d) * P]; Iww[d] = S[(kDpIww + d) * P]; }
+  for (int d = 0; d < 3; ++d) { w[d] = S[(kDpW + d) * L::GS]; wd[d] = S[(kDpWd + d) * L::GS]; Iww[d] = S[(kDpIww + d) * L::GS]; }
 #pragma unroll
-    for (int i = 0; i < 9; ++i) Iw[i] = S[(kDpIw + i) * P];
-    MatVec3(Iw, wd, Iw_wd);
-    double gy[3];   // Cross(w) * (I_w w): off-diagonal entries in column order
-    gy[0] = ((-w[2]) * Iww[1]) + w[1] * Iww[2];
-    gy[1] = (w[2] * Iww[0]) + (-w[0]) * Iww[2];
-    gy[2] = ((-w[1]) * Iww[0]) + w[0] * Iww[1];
-    const double m = cx.pc->mass;
-    const double grav = 9.80665;
-    double* gr = cx.g + it.row;
+  for (int i = 0; i < 9; ++i) Iw[i] = S[(kDpIw + i) * L::GS];
+  MatVec3(Iw, wd, Iw_wd);
+  double gy[3];   // Cross(w) * (I_w w): off-diagonal entries in column order
+  gy[0] = ((-w[2]) * Iww[1]) + w[1] * Iww[2];
+  gy[1] = (w[2] * Iww[0]) + (-w[0]) * Iww[2];
+  gy[2] = ((-w[1]) * Iww[0]) + w[0] * Iww[1];
+  const double m = cx.pc->mass;
+  const double grav = 9.80665;
+  double* gr = cx.g + it.row * L::RS;
 #pragma unroll
-    for (int d = 0; d < 3; ++d) gr[d] = (Iw_wd[d] + gy[d]) - tau_sum[d];
-    gr[3] = (m * lin.a[0] - f_sum[0]) - 0.0;
-    gr[4] = (m * lin.a[1] - f_sum[1]) - 0.0;
-    gr[5] = (m * lin.a[2] - f_sum[2]) - (-m * grav);
-  }
-  // base-lin angular block: entry(r, (sd,d)) = -(sum_e Cross(f_e)(r,d) * Bpos[sd]), feet summed in order
+  for (int d = 0; d < 3; ++d) gr[(d) * L::RS] = (Iw_wd[d] + gy[d]) - tau_sum[d];
+  gr[(3) * L::RS] = (m * lin.a[0] - f_sum[0]) - 0.0;
+  gr[(4) * L::RS] = (m * lin.a[1] - f_sum[1]) - 0.0;
+  gr[(5) * L::RS] = (m * lin.a[2] - f_sum[2]) - (-m * grav);
+}
+
+// row r (= sub) of the base-lin angular block: entry(r, (sd,d)) = -(sum_e Cross(f_e)(r,d) * Bpos[sd]), feet summed
+// in order
+template <class L>
+__device__ __forceinline__ void ItemDynJlin(const ItemCtx<L>& cx, const ItemC& it) {
+  const int E = it.n_ee, r = it.sub;
+  double* G = cx.G + it.gslot * L::GS;
   const double* Bl = cx.T.B + it.b0;
+  const double b4[4] = {Bl[0], Bl[1], Bl[2], Bl[3]};
 #pragma unroll
-  for (int r = 0; r < 3; ++r)
+  for (int d = 0; d < 3; ++d) {
+    if (d == r) {              // no entry uses these slots; keep them finite for the status check
 #pragma unroll
-    for (int d = 0; d < 3; ++d) {
-      if (d == r) {            // no entry uses these slots; keep them finite for the status check
-#pragma unroll
-        for (int sd = 0; sd < 4; ++sd) TB_G(kDynJlin + r * 12 + sd * 3 + d) = 0.0;
-        continue;
-      }
-      const int k = 3 - r - d;
-      const double sg = ((d - r + 3) % 3 == 2) ? 1.0 : -1.0;
-#pragma unroll
-      for (int sd = 0; sd < 4; ++sd) {
-        const double b = Bl[sd];
-        double acc = (sg * TB_G(kDynF + k)) * b;
-        for (int e = 1; e < E; ++e) acc = acc + (sg * TB_G(kDynF + 3 * e + k)) * b;
-        TB_G(kDynJlin + r * 12 + sd * 3 + d) = -acc;
-      }
+      for (int sd = 0; sd < 4; ++sd) TB_G(kDynJlin + r * 12 + sd * 3 + d) = 0.0;
+      continue;
     }
+    const int k = 3 - r - d;
+    const double sg = ((d - r + 3) % 3 == 2) ? 1.0 : -1.0;
+    double acc[4];
+    {
+      const double sf = sg * TB_G(kDynF + k);
+#pragma unroll
+      for (int sd = 0; sd < 4; ++sd) acc[sd] = sf * b4[sd];
+    }
+    for (int e = 1; e < E; ++e) {
+      const double sf = sg * TB_G(kDynF + 3 * e + k);
+#pragma unroll
+      for (int sd = 0; sd < 4; ++sd) acc[sd] = acc[sd] + sf * b4[sd];
+    }
+#pragma unroll
+    for (int sd = 0; sd < 4; ++sd) TB_G(kDynJlin + r * 12 + sd * 3 + d) = -acc[sd];
+  }
 }
 
 // One euler column c of d(angular rows)/d(base-ang variables):
 //   value(r, (sd,c)) = A_pos[r][c]*Bp[sd] + A_vel[r][c]*Bv[sd] + A_acc[r][c]*Ba[sd]
 // with A_* the partial derivatives of I_w wd + w x (I_w w) w.r.t. the euler spline's pos, vel, acc
 // (single_rigid_body_dynamics.cc:124-166 through euler_converter.cc:85-131,223-304, regrouped).
-template <int P>
-__device__ __forceinline__ void ItemDynCol(const ItemCtx<P>& cx, const ItemC& it) {
+template <class L>
+__device__ __forceinline__ void ItemDynCol(const ItemCtx<L>& cx, const ItemC& it) {
   const int c = it.sub;
-  const double* S = cx.G + it.aux * P;
-#define TB_S(i) S[(i) * P]
+  const double* S = cx.G + it.aux * L::GS;
+#define TB_S(i) S[(i) * L::GS]
   Trig tr;
   tr.sx = TB_S(kDpTrig); tr.cx = TB_S(kDpTrig + 1); tr.sy = TB_S(kDpTrig + 2);
   tr.cy = TB_S(kDpTrig + 3); tr.sz = TB_S(kDpTrig + 4); tr.cz = TB_S(kDpTrig + 5);
@@ -220,7 +252,7 @@ __device__ __forceinline__ void ItemDynCol(const ItemCtx<P>& cx, const ItemC& it
   Cross3(w, IwM, b1);
   Cross3(Iww, Mc, b2);
   const double* Ba = cx.T.B + it.b0 + 4;               // pos[4], vel[4], acc[4] basis by sd
-  double* G = cx.G + it.gslot * P;
+  double* G = cx.G + it.gslot * L::GS;
 #pragma unroll
   for (int r = 0; r < 3; ++r) {
     const double Ap = (t1[r] + t2[r] + t3[r]) + (c1[r] - c2[r]);
@@ -234,13 +266,13 @@ __device__ __forceinline__ void ItemDynCol(const ItemCtx<P>& cx, const ItemC& it
 
 // ------------------------------------------------------------------------------------------ range of motion
 // level 0: base position, R and dR/d(euler) of a RoM sample
-template <int P>
-__device__ __forceinline__ void ItemRomPre(const ItemCtx<P>& cx, const ItemC& it) {
+template <class L>
+__device__ __forceinline__ void ItemRomPre(const ItemCtx<L>& cx, const ItemC& it) {
   Pt3 lin, ang;
-  EvalSpline<kNeedPos, P>(cx.T, cx.nodes, cx.coef, it.s0, lin);
-  EvalSpline<kNeedPos, P>(cx.T, cx.nodes, cx.coef, it.s0 + 1, ang);
+  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, lin);
+  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 1, ang);
   const Trig tr = MakeTrig(ang.p);
-  double* G = cx.G + it.gslot * P;
+  double* G = cx.G + it.gslot * L::GS;
   double R[9];
   RotationMatrix(tr, R);
 #pragma unroll
@@ -256,40 +288,40 @@ __device__ __forceinline__ void ItemRomPre(const ItemCtx<P>& cx, const ItemC& it
 }
 
 // level 1: g = R^T (p_e - c) (range_of_motion_constraint.cc:72-83) and D[r][c] = (dR_c^T (p_e - c))[r]
-template <int P>
-__device__ __forceinline__ void ItemRomFoot(const ItemCtx<P>& cx, const ItemC& it) {
+template <class L>
+__device__ __forceinline__ void ItemRomFoot(const ItemCtx<L>& cx, const ItemC& it) {
   Pt3 p;
-  EvalSpline<kNeedPos, P>(cx.T, cx.nodes, cx.coef, it.s0, p);
-  const double* S = cx.G + it.aux * P;
-  double* G = cx.G + it.gslot * P;
-  const double rw[3] = {p.p[0] - S[(kRpLin + 0) * P], p.p[1] - S[(kRpLin + 1) * P], p.p[2] - S[(kRpLin + 2) * P]};
+  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, p);
+  const double* S = cx.G + it.aux * L::GS;
+  double* G = cx.G + it.gslot * L::GS;
+  const double rw[3] = {p.p[0] - S[(kRpLin + 0) * L::GS], p.p[1] - S[(kRpLin + 1) * L::GS], p.p[2] - S[(kRpLin + 2) * L::GS]};
   if (cx.g) {
-    double* gr = cx.g + it.row;
+    double* gr = cx.g + it.row * L::RS;
 #pragma unroll
     for (int r = 0; r < 3; ++r)
-      gr[r] = (S[(kRpR + r) * P] * rw[0] + S[(kRpR + 3 + r) * P] * rw[1]) + S[(kRpR + 6 + r) * P] * rw[2];
+      gr[(r) * L::RS] = (S[(kRpR + r) * L::GS] * rw[0] + S[(kRpR + 3 + r) * L::GS] * rw[1]) + S[(kRpR + 6 + r) * L::GS] * rw[2];
   }
 #pragma unroll
   for (int c = 0; c < 3; ++c)
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
-      const double* D = S + (kRpDR + 9 * c) * P;
-      TB_G(3 * r + c) = (D[r * P] * rw[0] + D[(3 + r) * P] * rw[1]) + D[(6 + r) * P] * rw[2];
+      const double* D = S + (kRpDR + 9 * c) * L::GS;
+      TB_G(3 * r + c) = (D[r * L::GS] * rw[0] + D[(3 + r) * L::GS] * rw[1]) + D[(6 + r) * L::GS] * rw[2];
     }
 }
 
 // ------------------------------------------------------------------------------------------- force (discretised)
 // g: force_constraint_discretized.cc:97-117.  G slots: b_i[3], i = 0..4: n, t1 -/+ mu n, t2 -/+ mu n.
-template <int P>
-__device__ __forceinline__ void ItemForce(const ItemCtx<P>& cx, const ItemC& it) {
+template <class L>
+__device__ __forceinline__ void ItemForce(const ItemCtx<L>& cx, const ItemC& it) {
   Pt3 p, f;
-  EvalSpline<kNeedPos, P>(cx.T, cx.nodes, cx.coef, it.s0, p);
-  EvalSpline<kNeedPos, P>(cx.T, cx.nodes, cx.coef, it.s0 + 1, f);
+  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, p);
+  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 1, f);
   const TerrainSample ts = EvalTerrain(cx.pc->terrain_id, p.p[0], p.p[1]);
   double n[3], t1[3], t2[3];
   TerrainBasis(ts, n, t1, t2);
   const double mu = kFrictionCoeff;
-  double* G = cx.G + it.gslot * P;
+  double* G = cx.G + it.gslot * L::GS;
   double b[15];
 #pragma unroll
   for (int d = 0; d < 3; ++d) {
@@ -302,71 +334,73 @@ __device__ __forceinline__ void ItemForce(const ItemCtx<P>& cx, const ItemC& it)
 #pragma unroll
   for (int i = 0; i < 15; ++i) TB_G(i) = b[i];
   if (cx.g) {
-    double* gr = cx.g + it.row;
+    double* gr = cx.g + it.row * L::RS;
 #pragma unroll
-    for (int i = 0; i < 5; ++i) gr[i] = (f.p[0] * b[3 * i] + f.p[1] * b[3 * i + 1]) + f.p[2] * b[3 * i + 2];
+    for (int i = 0; i < 5; ++i) gr[(i) * L::RS] = (f.p[0] * b[3 * i] + f.p[1] * b[3 * i + 1]) + f.p[2] * b[3 * i + 2];
   }
 }
 
 // ------------------------------------------------------------------------------------------------ node-based
 // TerrainConstraint (terrain_constraint.cc:61-111) and BaseHeightConstraint (base_height_constraint.cc:58-110)
-template <int P>
-__device__ __forceinline__ void ItemHeightNode(const ItemCtx<P>& cx, const ItemC& it, double offset) {
-  const double* n = cx.nodes + it.s0 * 6 * P;
-  const double px = n[0], py = n[P], pz = n[2 * P];
+template <class L>
+__device__ __forceinline__ void ItemHeightNode(const ItemCtx<L>& cx, const ItemC& it, double offset) {
+  const double* n = cx.nodes + it.s0 * 6 * L::NS;
+  const double px = n[0], py = n[L::NS], pz = n[2 * L::NS];
   const TerrainSample ts = EvalTerrain(cx.pc->terrain_id, px, py);
-  double* G = cx.G + it.gslot * P;
+  double* G = cx.G + it.gslot * L::GS;
   TB_G(0) = -ts.hx;
   TB_G(1) = -ts.hy;
-  if (cx.g) cx.g[it.row] = (it.type == kItemBaseHeightNode) ? (pz - ts.h) - offset : pz - ts.h;
+  if (cx.g) cx.g[it.row * L::RS] = (it.type == kItemBaseHeightNode) ? (pz - ts.h) - offset : pz - ts.h;
 }
 
 // SwingConstraint (swing_constraint.cc:54-78)
-template <int P>
-__device__ __forceinline__ void ItemSwingNode(const ItemCtx<P>& cx, const ItemC& it) {
+template <class L>
+__device__ __forceinline__ void ItemSwingNode(const ItemCtx<L>& cx, const ItemC& it) {
   if (!cx.g) return;
-  const double* cur = cx.nodes + it.s0 * 6 * P;
-  const double* prev = cur - 6 * P;
-  const double* next = cur + 6 * P;
-  double* gr = cx.g + it.row;
+  const double* cur = cx.nodes + it.s0 * 6 * L::NS;
+  const double* prev = cur - 6 * L::NS;
+  const double* next = cur + 6 * L::NS;
+  double* gr = cx.g + it.row * L::RS;
 #pragma unroll
   for (int d = 0; d < 2; ++d) {
-    const double distance = next[d * P] - prev[d * P];
-    const double center = prev[d * P] + 0.5 * distance;
+    const double distance = next[d * L::NS] - prev[d * L::NS];
+    const double center = prev[d * L::NS] + 0.5 * distance;
     const double des_vel = distance / 0.3;
-    gr[2 * d] = cur[d * P] - center;
-    gr[2 * d + 1] = cur[(3 + d) * P] - des_vel;
+    gr[(2 * d) * L::RS] = cur[d * L::NS] - center;
+    gr[(2 * d + 1) * L::RS] = cur[(3 + d) * L::NS] - des_vel;
   }
 }
 
 // SplineAccConstraint (spline_acc_constraint.cc:48-64): acc at the end of poly j minus acc at the start of poly j+1
-template <int P>
-__device__ __forceinline__ void ItemSplineAcc(const ItemCtx<P>& cx, const ItemC& it) {
+template <class L>
+__device__ __forceinline__ void ItemSplineAcc(const ItemCtx<L>& cx, const ItemC& it) {
   if (!cx.g) return;
   const int j = it.s0;
   const double T = cx.T.durs[3 * (cx.T.polys[j] >> 16)];
-  double* gr = cx.g + it.row;
+  double* gr = cx.g + it.row * L::RS;
 #pragma unroll
   for (int d = 0; d < 3; ++d) {
-    const double prev = 2.0 * cx.coef[(j * 6 + d) * P] + (6 * T) * cx.coef[(j * 6 + 3 + d) * P];
-    const double next = 2.0 * cx.coef[((j + 1) * 6 + d) * P] + (6 * 0.0) * cx.coef[((j + 1) * 6 + 3 + d) * P];
-    gr[d] = prev - next;
+    const double prev = 2.0 * cx.coef[(j * 6 + d) * L::NS] + (6 * T) * cx.coef[(j * 6 + 3 + d) * L::NS];
+    const double next = 2.0 * cx.coef[((j + 1) * 6 + d) * L::NS] + (6 * 0.0) * cx.coef[((j + 1) * 6 + 3 + d) * L::NS];
+    gr[(d) * L::RS] = prev - next;
   }
 }
 
-template <int P>
-__device__ __forceinline__ void RunItem(const ItemCtx<P>& cx, const ItemC& it) {
+template <class L>
+__device__ __forceinline__ void RunItem(const ItemCtx<L>& cx, const ItemC& it) {
   switch (it.type) {
-    case kItemDynPre: ItemDynPre<P>(cx, it); break;
-    case kItemDynWrench: ItemDynWrench<P>(cx, it); break;
-    case kItemDynCol: ItemDynCol<P>(cx, it); break;
-    case kItemRomPre: ItemRomPre<P>(cx, it); break;
-    case kItemRomFoot: ItemRomFoot<P>(cx, it); break;
-    case kItemForce: ItemForce<P>(cx, it); break;
-    case kItemTerrainNode: ItemHeightNode<P>(cx, it, 0.0); break;
-    case kItemBaseHeightNode: ItemHeightNode<P>(cx, it, 0.4); break;   // nlp_formulation.cc:597
-    case kItemSwingNode: ItemSwingNode<P>(cx, it); break;
-    case kItemSplineAcc: ItemSplineAcc<P>(cx, it); break;
+    case kItemDynPre: ItemDynPre<L>(cx, it); break;
+    case kItemDynFoot: ItemDynFoot<L>(cx, it); break;
+    case kItemDynWrench: ItemDynWrench<L>(cx, it); break;
+    case kItemDynJlin: ItemDynJlin<L>(cx, it); break;
+    case kItemDynCol: ItemDynCol<L>(cx, it); break;
+    case kItemRomPre: ItemRomPre<L>(cx, it); break;
+    case kItemRomFoot: ItemRomFoot<L>(cx, it); break;
+    case kItemForce: ItemForce<L>(cx, it); break;
+    case kItemTerrainNode: ItemHeightNode<L>(cx, it, 0.0); break;
+    case kItemBaseHeightNode: ItemHeightNode<L>(cx, it, 0.4); break;   // nlp_formulation.cc:597
+    case kItemSwingNode: ItemSwingNode<L>(cx, it); break;
+    case kItemSplineAcc: ItemSplineAcc<L>(cx, it); break;
     default: break;
   }
 }

@@ -12,14 +12,96 @@
 
 namespace tb {
 
-constexpr int kThreads = kEntryThreads;
+#ifndef TB_THREADS
+#define TB_THREADS kEntryThreads
+#endif
+constexpr int kThreads = TB_THREADS;   // threads per problem lane
 #ifndef TB_MIN_CTAS
 #define TB_MIN_CTAS 1
 #endif
 constexpr int kMinCtasPerSm = TB_MIN_CTAS;   // caps registers at 64: the long dynamic item spills to local memory, stage B does not
 
+// Phase clocks of CTA 0 (timing build only: make timing; tools/phase_timing.py)
+#ifdef TB_TIMING
+__device__ unsigned long long tb_phase_clk[64];
+#define TB_MARK(k)                                                             \
+  if (blockIdx.x == 0 && threadIdx.x == 0) {                                   \
+    const long long now_ = clock64();                                          \
+    tb_phase_clk[(k)] += static_cast<unsigned long long>(now_ - mark_);        \
+    mark_ = now_;                                                              \
+  }
+#define TB_MARK_INIT long long mark_ = clock64();
+#else
+#define TB_MARK(k)
+#define TB_MARK_INIT
+#endif
+
 __device__ __forceinline__ bool NonFinite(double v) {
   return (__double2hiint(v) & 0x7ff00000) == 0x7ff00000;
+}
+
+// Stage B of one segment.  Thread t takes entries t, t + NT, ...: a warp's descriptor load and its P stores per
+// entry are coalesced.  Descriptors are fetched kDescBatch at a time, one batch ahead of their use (the first batch
+// before the barrier that ends stage A), so the L2 latency of the descriptor stream is off the critical path.
+constexpr int kDescBatch = 4;
+
+template <int NT>
+__device__ __forceinline__ void LoadDescriptors(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[kDescBatch]) {
+#pragma unroll
+  for (int u = 0; u < kDescBatch; ++u) d[u] = left > u * NT ? __ldg(ent + u * NT) : kNoEntry;
+}
+
+// FULL: all P problem lanes of the group exist (no per-store predicate).
+template <int P, bool FULL>
+__device__ __forceinline__ void StageB(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[kDescBatch],
+                                       const double* G, const double* Bs, double* __restrict__ o, int nnz, int np) {
+  constexpr int NT = kThreads * P;
+  constexpr int U = kDescBatch;
+  const char* Gb = reinterpret_cast<const char*>(G);
+  const char* Bb = reinterpret_cast<const char*>(Bs);
+  auto emit = [&](uint32_t w, double* op) {              // descriptor: G byte offset (low 16), B byte offset (high 16)
+    const double bv = *reinterpret_cast<const double*>(Bb + (w >> 16));
+    const char* ga = Gb + (w & 0xFFFFu) * P;
+    double gv[P];
+    if constexpr (P == 1) {
+      gv[0] = *reinterpret_cast<const double*>(ga);
+    } else {
+#pragma unroll
+      for (int p = 0; p < P; p += 2) {
+        const double2 t = *reinterpret_cast<const double2*>(ga + 8 * p);
+        gv[p] = t.x;
+        gv[p + 1] = t.y;
+      }
+    }
+#pragma unroll
+    for (int p = 0; p < P; ++p)
+      if (FULL || p < np) op[static_cast<size_t>(p) * nnz] = gv[p] * bv;
+  };
+  while (left > 0) {
+    const int left_next = left - U * NT;
+    uint32_t dn[U];
+    if (left_next > 0) LoadDescriptors<NT>(ent + U * NT, left_next, dn);
+    if (left > (U - 1) * NT) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) emit(d[u], o + u * NT);
+    } else {
+#pragma unroll
+      for (int u = 0; u < U - 1; ++u)
+        if (left > u * NT) emit(d[u], o + u * NT);
+    }
+    if (left_next <= 0) break;
+#pragma unroll
+    for (int u = 0; u < U; ++u) d[u] = dn[u];
+    left = left_next;
+    ent += U * NT;
+    o += U * NT;
+  }
+}
+
+// 8-byte asynchronous global -> shared copy; src_bytes = 0 writes zeros (cp.async zero-fill)
+__device__ __forceinline__ void CpAsync8(void* smem_dst, const void* gsrc, int src_bytes) {
+  const unsigned d = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(d), "l"(gsrc), "r"(src_bytes) : "memory");
 }
 
 // P problems are evaluated in lock step by one CTA of 256*P threads: the class tables are held once per SM, every
@@ -46,32 +128,41 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
     for (int i = tid; i < Pg.blob.bytes / 16; i += NT) sm4[i] = __ldg(src + i);
   }
   __syncthreads();
-  ItemCtx<P> cx;
+  TB_MARK_INIT
+  ItemCtx<Lockstep<P>> cx;
   cx.T = MakeTables(blob, Pg.blob);
   const double* Bs = cx.T.B;
   const int pl = tid % P;                               // problem lane of this thread in stages N, C, A
+
+  // stage N: node values from x (values that are not optimised are pinned to 0), fetched asynchronously: for the first
+  // group here, for every later group while the previous group's last stage B runs (nodes[] is free by then)
+  auto fetch_group = [&](int base_n) {
+    const double* xn = x + static_cast<size_t>(min(base_n + pl, n_problems - 1)) * Pg.n_vars;
+    for (int i = tid; i < nnv * P; i += NT) {
+      const unsigned src = cx.T.node_src[i / P];
+      CpAsync8(nodes + i, xn + (src != 0xFFFFu ? src : 0u), src != 0xFFFFu ? 8 : 0);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    if (tid < P) pc_all[tid] = pcs[min(base_n + tid, n_problems - 1)];
+  };
+  if (blockIdx.x * P < n_problems) fetch_group(blockIdx.x * P);
 
   for (int base = blockIdx.x * P; base < n_problems; base += gridDim.x * P) {
     // the last group may hold fewer than P problems: the spare lanes recompute the last problem (same values to
     // the same addresses) so that no stage needs a bounds test
     const int prob = min(base + pl, n_problems - 1);
-    const double* xp = x + static_cast<size_t>(prob) * Pg.n_vars;
     cx.nodes = nodes + pl;
     cx.coef = coef + pl;
     cx.G = G + pl;
     cx.pc = &pc_all[pl];
     cx.g = (WHAT & TOWR_B200_EVAL_G) ? g_out + static_cast<size_t>(prob) * Pg.n_rows : nullptr;
-    int bad = 0;
-
-    // ---- stage N: node values from x (values that are not optimised are pinned to 0)
-    if (tid < P) { pc_all[tid] = pcs[min(base + tid, n_problems - 1)]; bad_all[tid] = 0; }
-    for (int i = tid; i < nnv * P; i += NT) {
-      const unsigned src = cx.T.node_src[i / P];
-      const double v = src != 0xFFFFu ? __ldg(xp + src) : 0.0;
-      bad |= NonFinite(v);
-      nodes[i] = v;
-    }
+    double nf[2] = {0.0, 0.0};
+    double nfx = 0.0;                                     // non-finite x of problem lane pl
+    if (tid < P) bad_all[tid] = 0;
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    TB_MARK(0)
     __syncthreads();
+    TB_MARK(1)
 
     // ---- stage C: c = -(3(p0-p1) + T(2 v0 + v1))/T^2, d = (2(p0-p1) + T(v0+v1))/T^3   (polynomial.cc:97-104)
     for (int i = tid; i < 3 * npoly * P; i += NT) {
@@ -80,68 +171,67 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
       const uint32_t pr = cx.T.polys[poly];
       const int n0 = pr & 0xFFFF;
       const double* du = cx.T.durs + 3 * (pr >> 16);
+      const double* rd = cx.T.rdurs + 2 * (pr >> 16);
       const double T = du[0], T2 = du[1], T3 = du[2];
       const double* nd = nodes + pl;
       const double p0 = nd[(n0 * 6 + d) * P], v0 = nd[(n0 * 6 + 3 + d) * P];
       const double p1 = nd[(n0 * 6 + 6 + d) * P], v1 = nd[(n0 * 6 + 9 + d) * P];
-      coef[(poly * 6 + d) * P + pl] = -(3.0 * (p0 - p1) + T * (2.0 * v0 + v1)) / T2;
-      coef[(poly * 6 + 3 + d) * P + pl] = (2.0 * (p0 - p1) + T * (v0 + v1)) / T3;
+      nfx = fma(p0, 0.0, fma(v0, 0.0, fma(p1, 0.0, fma(v1, 0.0, nfx))));   // NaN iff a node value is not finite
+      coef[(poly * 6 + d) * P + pl] = ExactDiv(-(3.0 * (p0 - p1) + T * (2.0 * v0 + v1)), T2, rd[0]);
+      coef[(poly * 6 + 3 + d) * P + pl] = ExactDiv(2.0 * (p0 - p1) + T * (v0 + v1), T3, rd[1]);
     }
+    TB_MARK(2)
     __syncthreads();
+    TB_MARK(3)
 
     for (int s = 0; s < Pg.n_segments; ++s) {
-      const SegmentRec sg = Pg.segments[s];
+      const SegmentRec sg = cx.T.segments[s];
       // ---- stage A, level 0 then level 1: thread -> (item, problem lane)
       if (tid < P) { G[kGOne * P + tid] = 1.0; G[kGMass * P + tid] = pc_all[tid].mass; }
-      for (int i = tid; i < sg.n_items0 * P; i += NT) RunItem<P>(cx, cx.T.items[sg.item0 + i / P]);
-      __syncthreads();
+      for (int i = tid; i < sg.n_items0 * P; i += NT) RunItem<Lockstep<P>>(cx, cx.T.items[sg.item0 + i / P]);
+      TB_MARK(8 + 6 * s)
       if (sg.n_items > sg.n_items0) {
-        for (int i = tid; i < (sg.n_items - sg.n_items0) * P; i += NT)
-          RunItem<P>(cx, cx.T.items[sg.item0 + sg.n_items0 + i / P]);
         __syncthreads();
+        TB_MARK(9 + 6 * s)
+        for (int i = tid; i < (sg.n_items - sg.n_items0) * P; i += NT)
+          RunItem<Lockstep<P>>(cx, cx.T.items[sg.item0 + sg.n_items0 + i / P]);
+        TB_MARK(10 + 6 * s)
       }
-      // ---- stage B: value_p = G_p[g] * B[b] for the P problems; one 16-byte descriptor load feeds 4*P coalesced stores
+      // first descriptor batch of stage B: issued before the barrier, consumed after it
+      const uint32_t* ent = Pg.entries + sg.entry0 + tid;
+      uint32_t d0[kDescBatch];
+      if (WHAT & TOWR_B200_EVAL_JAC) LoadDescriptors<NT>(ent, sg.n_entries - tid, d0);
+      __syncthreads();
+      TB_MARK(11 + 6 * s)
+      // all items of this group are done with nodes[] / pc_all after the last segment's stage A: fetch the next group
+      if (s == Pg.n_segments - 1 && base + gridDim.x * P < n_problems) fetch_group(base + gridDim.x * P);
+      // ---- stage B: value_p = G_p[g] * B[b] for the P problems: one descriptor and one B load feed P coalesced stores
       if (WHAT & TOWR_B200_EVAL_JAC) {
-        const int tt = tid % kThreads, q = tid / kThreads;            // q: which chunks this 256-thread group takes
-        const uint4* __restrict__ ent = Pg.entries + sg.desc0 + tt;
-        const int chunks = (sg.n_entries + kEntryChunk - 1) / kEntryChunk;
-        const char* Gb = reinterpret_cast<const char*>(G);
-        const char* Bb = reinterpret_cast<const char*>(Bs);
-        double* out0 = vals_out + static_cast<size_t>(base) * Pg.nnz + sg.entry0 + tt;
-        const int np = min(P, n_problems - base);
-        auto emit = [&](uint32_t d, double* o) {          // descriptor: G byte offset (low), B byte offset (high)
-          const double bv = *reinterpret_cast<const double*>(Bb + (d >> 16));
-          const double* gp = reinterpret_cast<const double*>(Gb + (d & 0xFFFFu) * P);
-#pragma unroll
-          for (int p = 0; p < P; ++p)
-            if (p < np) o[static_cast<size_t>(p) * Pg.nnz] = gp[p] * bv;
-        };
-        if (q < chunks) {
-          uint4 w = __ldg(ent + q * kEntryThreads);
-          for (int k = q; k < chunks; k += P) {
-            const uint4 cur = w;
-            if (k + P < chunks) w = __ldg(ent + (k + P) * kEntryThreads);   // prefetch this thread's next chunk
-            double* o = out0 + k * kEntryChunk;
-            if (k + 1 < chunks) {                         // full chunk: no bounds checks
-              emit(cur.x, o);
-              emit(cur.y, o + kEntryThreads);
-              emit(cur.z, o + 2 * kEntryThreads);
-              emit(cur.w, o + 3 * kEntryThreads);
-            } else {
-              if (cur.x != kNoEntry) emit(cur.x, o);
-              if (cur.y != kNoEntry) emit(cur.y, o + kEntryThreads);
-              if (cur.z != kNoEntry) emit(cur.z, o + 2 * kEntryThreads);
-              if (cur.w != kNoEntry) emit(cur.w, o + 3 * kEntryThreads);
-            }
+        double* o0 = vals_out + static_cast<size_t>(base) * Pg.nnz + sg.entry0 + tid;
+        if (n_problems - base >= P)
+          StageB<P, true>(ent, sg.n_entries - tid, d0, G, Bs, o0, Pg.nnz, P);
+        else
+          StageB<P, false>(ent, sg.n_entries - tid, d0, G, Bs, o0, Pg.nnz, n_problems - base);
+        // a non-finite Jacobian value needs a non-finite G slot (B is finite): v * 0 is NaN exactly for those
+        if constexpr (P == 1) {
+          for (int i = tid; i < sg.g_size; i += NT) nf[0] = __fma_rn(G[i], 0.0, nf[0]);
+        } else {
+          const double2* G2 = reinterpret_cast<const double2*>(G);
+          for (int i = tid; i < sg.g_size * (P / 2); i += NT) {
+            const double2 t = G2[i];
+            nf[0] = __fma_rn(t.x, 0.0, nf[0]);
+            nf[1] = __fma_rn(t.y, 0.0, nf[1]);
           }
         }
-        // a non-finite Jacobian value needs a non-finite G slot (B is finite): check the slots, not the entries
-        for (int i = tid; i < sg.g_size * P; i += NT)
-          if (NonFinite(G[i])) atomicOr(&bad_all[i % P], 1);
       }
+      TB_MARK(12 + 6 * s)
       __syncthreads();
+      TB_MARK(13 + 6 * s)
     }
-    if (bad) atomicOr(&bad_all[pl], 1);
+    if (nfx != nfx) atomicOr(&bad_all[pl], 1);
+    // thread tid checked the G slots of problems (2 tid) % P and (2 tid) % P + 1
+    if (nf[0] != nf[0]) atomicOr(&bad_all[P == 1 ? 0 : (2 * tid) % P], 1);
+    if (P > 1 && nf[1] != nf[1]) atomicOr(&bad_all[(2 * tid) % P + 1], 1);
     __syncthreads();
     if (tid < P && bad_all[tid] && base + tid < n_problems) atomicOr(status + base + tid, 2);
   }
@@ -201,3 +291,14 @@ int EvalOccupancy(const DeviceProgram& P, int lanes) {
 }
 
 }  // namespace tb
+
+#ifdef TB_TIMING
+extern "C" int towr_b200_debug_phase_clocks(unsigned long long* out, int n) {
+  unsigned long long h[64];
+  if (cudaMemcpyFromSymbol(h, tb::tb_phase_clk, sizeof(h)) != cudaSuccess) return -1;
+  for (int i = 0; i < n && i < 64; ++i) out[i] = h[i];
+  unsigned long long z[64] = {};
+  cudaMemcpyToSymbol(tb::tb_phase_clk, z, sizeof(z));
+  return 0;
+}
+#endif

@@ -1,5 +1,5 @@
 // pack.cc — compacts the builder's tables into the device form: one shared-memory blob of class tables and the
-// thread-major permuted entry descriptors (program.h).
+// byte-offset entry descriptors (program.h).
 #include <array>
 #include <cstring>
 #include <map>
@@ -54,15 +54,18 @@ void PackProgram(HostProgram& hp) {
     c.b0 = static_cast<uint16_t>(it.b0);
     c.aux = static_cast<uint16_t>(it.aux);
     c.row = static_cast<uint32_t>(it.row[0]);
-    const int E = it.n_ee;
     size_t s0 = samples.size();
     switch (it.type) {
       case kItemDynPre: add_sample(it.s[kSBaseAng]); break;
-      case kItemDynWrench:
+      case kItemDynFoot:
         add_sample(it.s[kSBaseLin]);
-        for (int e = 0; e < E; ++e) { add_sample(it.s[kSMotion + e]); add_sample(it.s[kSForce + e]); add_sample(it.s[kSTorque + e]); }
+        add_sample(it.s[kSMotion + it.ee]);
+        add_sample(it.s[kSForce + it.ee]);
+        add_sample(it.s[kSTorque + it.ee]);
         break;
-      case kItemDynCol: s0 = 0; break;
+      case kItemDynWrench: add_sample(it.s[kSBaseLin]); break;
+      case kItemDynCol:
+      case kItemDynJlin: s0 = 0; break;
       case kItemRomPre:
         add_sample(it.s[kSBaseLin]);
         add_sample(it.s[kSBaseAng]);
@@ -127,6 +130,9 @@ void PackProgram(HostProgram& hp) {
   place(L.off_B, 8 * L.n_B);
   place(L.off_times, 24 * L.n_times);
   place(L.off_durs, 24 * L.n_durs);
+  place(L.off_rdurs, 16 * L.n_durs);
+  L.n_segments = static_cast<int>(hp.segments.size());
+  place(L.off_segments, static_cast<int>(sizeof(SegmentRec)) * L.n_segments);
   place(L.off_items, 16 * L.n_items);
   place(L.off_samples, 4 * L.n_samples);
   place(L.off_polys, 4 * L.n_polys);
@@ -137,30 +143,24 @@ void PackProgram(HostProgram& hp) {
   std::memcpy(d + L.off_B, hp.B.data(), 8 * hp.B.size());
   std::memcpy(d + L.off_times, times.data(), 8 * times.size());
   std::memcpy(d + L.off_durs, durs.data(), 8 * durs.size());
+  {
+    double* rd = reinterpret_cast<double*>(d + L.off_rdurs);
+    for (int i = 0; i < L.n_durs; ++i) { rd[2 * i] = 1.0 / durs[3 * i + 1]; rd[2 * i + 1] = 1.0 / durs[3 * i + 2]; }
+  }
+  std::memcpy(d + L.off_segments, hp.segments.data(), sizeof(SegmentRec) * hp.segments.size());
   std::memcpy(d + L.off_items, items.data(), 16 * items.size());
   std::memcpy(d + L.off_samples, samples.data(), 4 * samples.size());
   std::memcpy(d + L.off_polys, polys.data(), 4 * polys.size());
   uint16_t* ns = reinterpret_cast<uint16_t*>(d + L.off_node_src);
   for (int i = 0; i < hp.n_node_values; ++i) ns[i] = hp.node_src[i] < 0 ? 0xFFFF : static_cast<uint16_t>(hp.node_src[i]);
 
-  // thread-major permuted descriptors per segment
-  hp.entries_perm.clear();
-  for (SegmentRec& sg : hp.segments) {
-    sg.desc0 = static_cast<int>(hp.entries_perm.size() / 4);
-    const int chunks = (sg.n_entries + kEntryChunk - 1) / kEntryChunk;
-    for (int k = 0; k < chunks; ++k)
-      for (int t = 0; t < kEntryThreads; ++t)
-        for (int j = 0; j < 4; ++j) {
-          int e = k * kEntryChunk + j * kEntryThreads + t;
-          if (e < sg.n_entries) {
-            uint32_t w = hp.entries[sg.entry0 + e];
-            uint32_t g8 = (w & 0xFFFF) * 8, b8 = (w >> 16) * 8;
-            if (g8 > 0xFFFF || b8 > 0xFFFF) throw std::runtime_error("unsupported: G or B table beyond 8191 entries");
-            hp.entries_perm.push_back(g8 | (b8 << 16));
-          } else {
-            hp.entries_perm.push_back(kNoEntry);
-          }
-        }
+  // device descriptors: byte offsets, so that stage B needs no index scaling
+  hp.entries_dev.clear();
+  hp.entries_dev.reserve(hp.entries.size());
+  for (uint32_t w : hp.entries) {
+    uint32_t g8 = (w & 0xFFFF) * 8, b8 = (w >> 16) * 8;
+    if (g8 > 0xFFFF || b8 > 0xFFFF) throw std::runtime_error("unsupported: G or B table beyond 8191 entries");
+    hp.entries_dev.push_back(g8 | (b8 << 16));
   }
 }
 

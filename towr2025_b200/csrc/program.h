@@ -49,8 +49,10 @@ enum ItemType : int {
   kItemSwingNode,       // swing_constraint.cc:54-108              4 rows per swing node
   kItemSplineAcc,       // spline_acc_constraint.cc:48-80          3 rows per junction
   kItemTotalDuration,   // total_duration_constraint.cc:48-72
+  kItemDynFoot,         // per (dynamic sample, foot): f_e, c - p_e slots and the foot's torque term f_e x (c - p_e) + tau_e
   // level 1: read the scratch slots of a level-0 item (ItemC::aux)
-  kItemDynWrench,       // dynamic_constraint.cc:63-148: 6 g rows, f_e, c - p_e, finished base-lin angular block
+  kItemDynWrench,       // dynamic_constraint.cc:63-148: the 6 g rows of a dynamic sample (feet summed in order)
+  kItemDynJlin,         // row (sub) of the finished base-lin angular block -sum_e Cross(f_e) J_pos of a dynamic sample
   kItemDynCol,          // one euler column (sub) of the finished base-ang block of a dynamic sample
   kItemRomFoot,         // range_of_motion_constraint.cc:72-131: 3 g rows + d(R^T r)/d(euler) of one (sample, foot)
   kItemNone = 255,      // padding: keeps every warp of stage A on one item kind
@@ -61,7 +63,8 @@ inline int ItemLevel(int type) { return type >= kItemDynWrench && type != kItemN
 enum { kDpV = 0, kDpA = 3, kDpTrig = 6, kDpR = 12, kDpRI = 21, kDpIw = 30, kDpM = 39, kDpMd = 44, kDpW = 49, kDpWd = 52,
        kDpIww = 55, kDpV11 = 58, kDpV21 = 61, kDynPreSize = 64 };
 enum { kRpLin = 0, kRpR = 3, kRpDR = 12, kRomPreSize = 39 };
-// G layout of a dynamic sample: finished base-ang block, finished base-lin angular block, f_e, c - p_e
+// G layout of a dynamic sample: finished base-ang block, finished base-lin angular block, f_e[3E], (c - p_e)[3E],
+// then scratch: per-foot torque terms [3E], DynPre block
 enum { kDynJang = 0, kDynJlin = 36, kDynF = 72 };
 
 constexpr int kMaxEE = 4;
@@ -85,18 +88,16 @@ struct ItemRec {
 // the device copy (pack.cc) holds BYTE offsets (slot*8, index*8) so that stage B needs no shifts
 using EntryRec = uint32_t;
 
-// Entry descriptors of a segment are stored thread-major in chunks of kEntryChunk: uint4 number desc0 + k*kEntryThreads + t
-// holds the descriptors of entries k*kEntryChunk + j*kEntryThreads + t, j = 0..3 (0xFFFFFFFF = past the end), so
-// that one 16-byte load feeds four coalesced 8-byte stores.
-constexpr int kEntryThreads = 256;
-constexpr int kEntryChunk = 4 * kEntryThreads;
+// The device copy of the descriptors (HostProgram::entries_dev) is in storage order too: thread t of stage B takes
+// entries t, t + blockDim, ... of its segment, so a warp's descriptor load and its P stores are all coalesced.
+constexpr int kEntryThreads = 256;   // threads per problem lane
 constexpr uint32_t kNoEntry = 0xFFFFFFFFu;
 struct SegmentRec {
   int item0, n_items;   // items of this segment: n_items0 level-0 items first, then the level-1 items
   int n_items0, pad;
   int entry0, n_entries;// entries fed by this segment (contiguous in storage order)
   int g_size;           // G slots used
-  int desc0;            // first uint4 of the segment's permuted descriptors
+  int pad2;
 };
 
 // slots 0.. of every segment's G buffer
@@ -113,13 +114,15 @@ struct ItemC {          // 16 bytes
   uint16_t aux;         // level-1 items: first scratch slot of the level-0 parent
 };
 // compact sample = polynomial index | time index << 16 ; compact polynomial = node slot | duration index << 16
-// sample order of an item: DynPre [ang], DynWrench [lin, (motion, force, torque) per foot], RomPre [lin, ang],
+// sample order of an item: DynPre [ang], DynFoot [lin, motion, force, torque], DynWrench [lin], RomPre [lin, ang],
 // RomFoot [motion], Force [motion, force]
 struct BlobLayout {     // byte offsets into the blob (all 16-byte aligned), element counts
   int bytes;
   int off_B, n_B;                 // double
   int off_times, n_times;         // double[3] per entry: t, pow(t,2), pow(t,3)
   int off_durs, n_durs;           // double[3] per entry: T, pow(T,2), pow(T,3)
+  int off_rdurs;                  // double[2] per entry: 1/pow(T,2), 1/pow(T,3) correctly rounded (ExactDiv)
+  int off_segments, n_segments;   // SegmentRec
   int off_items, n_items;         // ItemC
   int off_samples, n_samples;     // uint32
   int off_polys, n_polys;         // uint32
@@ -132,7 +135,7 @@ struct DeviceProgram {  // pointers into device memory (one copy per GPU)
   int g_capacity;       // max g_size over segments
   BlobLayout blob;
   const unsigned char* blob_data;
-  const uint4* entries; // permuted descriptors, see SegmentRec::desc0
+  const uint32_t* entries;   // G byte offset | B byte offset << 16, storage order
   const SegmentRec* segments;
 };
 
@@ -194,7 +197,7 @@ struct HostProgram {
   // packed for the device (pack.cc)
   BlobLayout blob{};
   std::vector<unsigned char> blob_data;
-  std::vector<uint32_t> entries_perm;   // 4 per uint4
+  std::vector<uint32_t> entries_dev;    // byte-offset form of entries
   int g_capacity = 0;
   int n_node_values = 0;
   std::string signature;   // canonical text of every structural field (structure_accepts compares it)

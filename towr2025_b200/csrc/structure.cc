@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <array>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -283,9 +284,11 @@ void Builder::EmitBaseHeight() {
 }
 
 // DynamicConstraint, 6 rows per sample (dynamic_constraint.cc:57-126 with single_rigid_body_dynamics.cc:104-204).
-// Per sample: one level-0 item (DynPre: everything that depends on the euler spline only) and four level-1 items
-// (DynWrench: g rows, forces, lever arms, base-lin angular block; DynCol x3: one euler column of the base-ang block).
-// G layout per sample: Jang[3][12] at r*12 + sd*3 + c | Jlin[3][12] at r*12 + sd*3 + d | f_e[3] | (c - p_e)[3] | scratch.
+// Per sample: level-0 items DynPre (everything that depends on the euler spline only) and DynFoot x E (forces, lever
+// arms, the foot's torque term); level-1 items DynWrench (the g rows), DynJlin x3 (one row of the base-lin angular
+// block) and DynCol x3 (one euler column of the base-ang block).
+// G layout per sample: Jang[3][12] at r*12 + sd*3 + c | Jlin[3][12] at r*12 + sd*3 + d | f_e[3] | (c - p_e)[3] |
+// scratch: foot torque terms [3] per foot, DynPre block.
 // B run of the sample (ItemRec::b0): base-lin pos basis [4], then base-ang pos/vel/acc basis [4] each, by sd.
 void Builder::EmitDynamic() {
   const int E = s_.n_ee;
@@ -293,7 +296,7 @@ void Builder::EmitDynamic() {
   const VarSet& ang = Set(kBaseAng);
   const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_dynamic);
   const int one = AddB(1.0);
-  const int per_sample = 72 + 6 * E + kDynPreSize;
+  const int per_sample = 72 + 9 * E + kDynPreSize;
   const int chunk = std::max(1, 1024 / per_sample);      // samples per group
   for (size_t k = 0; k < ts.size(); ++k) {
     const double t = ts[k];
@@ -306,7 +309,7 @@ void Builder::EmitDynamic() {
     it.row[0] = set_row0_ + r0;
     const int g0 = AllocG(per_sample);
     it.gslot = g0;
-    it.aux = g0 + 72 + 6 * E;
+    it.aux = g0 + 72 + 9 * E;
     const int gJang = g0 + kDynJang, gJlin = g0 + kDynJlin, gF = g0 + kDynF, gR = g0 + kDynF + 3 * E;
 
     SplineAt al = At(lin, t), aa = At(ang, t);
@@ -373,11 +376,19 @@ void Builder::EmitDynamic() {
     pre.type = kItemDynPre;
     pre.gslot = it.aux;
     hp_.items.push_back(pre);
+    for (int e = 0; e < E; ++e) {
+      ItemRec foot = it;
+      foot.type = kItemDynFoot;
+      foot.ee = static_cast<short>(e);
+      hp_.items.push_back(foot);
+    }
     hp_.items.push_back(it);
     for (int c = 0; c < 3; ++c) {
       ItemRec col = it;
       col.type = kItemDynCol;
       col.sub = static_cast<short>(c);
+      hp_.items.push_back(col);
+      col.type = kItemDynJlin;
       hp_.items.push_back(col);
     }
   }
@@ -600,21 +611,44 @@ void BuildProgram(const towr_b200_spec& s, HostProgram& hp) {
   ResetTables(hp);
   Builder sizing(s, hp, nullptr);
   sizing.Run();
-  int cap = 3500;   // G slots per segment: ANYmal trot packs into 3 balanced segments of <= 238 items
-  if (const char* env = std::getenv("TOWR_B200_GCAP")) cap = std::max(64, std::atoi(env));
-  std::vector<char> plan(sizing.group_g_size.size(), 0);
-  int used = kGReserved;
-  for (size_t g = 0; g < plan.size(); ++g) {
-    if (g == 0 || used + sizing.group_g_size[g] > cap) {
-      plan[g] = 1;
-      used = kGReserved;
+  // G slots per segment.  Every segment costs the kernel a fixed stage-A latency, so use as few segments as the
+  // 16-bit byte offsets of the entry descriptors allow (8191 slots) and balance them.  TOWR_B200_GCAP overrides.
+  const int cap_max = 8000;
+  int total = 0, largest = 0;
+  for (int g : sizing.group_g_size) { total += g; largest = std::max(largest, g); }
+  auto plan_with = [&](int cap, std::vector<char>& plan) {
+    int used = kGReserved, n = 0;
+    for (size_t g = 0; g < plan.size(); ++g) {
+      plan[g] = 0;
+      if (g == 0 || used + sizing.group_g_size[g] > cap) {
+        plan[g] = 1;
+        used = kGReserved;
+        ++n;
+      }
+      used += sizing.group_g_size[g];
     }
-    used += sizing.group_g_size[g];
+    return n;
+  };
+  std::vector<char> plan(sizing.group_g_size.size(), 0);
+  if (const char* env = std::getenv("TOWR_B200_GCAP")) {
+    plan_with(std::max(64, std::atoi(env)), plan);
+  } else {
+    const int n_min = plan_with(cap_max, plan);            // fewest segments possible
+    int cap = std::max(largest + kGReserved, total / std::max(1, n_min));
+    while (cap < cap_max && plan_with(cap, plan) > n_min) cap += 16;   // smallest cap that still gives n_min: balanced
+    if (cap >= cap_max) plan_with(cap_max, plan);
   }
   // pass 2: the real tables
   ResetTables(hp);
   Builder real(s, hp, &plan);
   real.Run();
+  if (std::getenv("TOWR_B200_DEBUG")) {
+    std::fprintf(stderr, "groups:");
+    for (int g : sizing.group_g_size) std::fprintf(stderr, " %d", g);
+    std::fprintf(stderr, "\n");
+    for (const SegmentRec& sg : hp.segments)
+      std::fprintf(stderr, "segment items %d (level0 %d) entries %d g %d\n", sg.n_items, sg.n_items0, sg.n_entries, sg.g_size);
+  }
   PackProgram(hp);
 }
 
