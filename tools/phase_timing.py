@@ -35,6 +35,17 @@ def main():
         L.towr_b200_debug_phase_clocks(out, 64)
     v = list(out)
     tot = sum(v)
+    if os.environ.get("TOWR_B200_KERNEL", "") == "ws" or v[16] or v[17]:
+        pn = ["wait x", "stage C", "wait empty", "L0 items", "L0->L1 barrier", "L1 items", "hand-off + group end"]
+        pt = sum(v[:7]) or 1
+        print("producer thread 0: %d clocks" % pt)
+        for k, nm in enumerate(pn):
+            print("  %-22s %9d %5.1f%%" % (nm, v[k], 100.0 * v[k] / pt))
+        ct = sum(v[16:19]) or 1
+        print("consumer thread 0: %d clocks" % ct)
+        for k, nm in enumerate(["descriptor issue", "wait full", "stage B + G check"]):
+            print("  %-22s %9d %5.1f%%" % (nm, v[16 + k], 100.0 * v[16 + k] / ct))
+        return
     names = {0: "N work", 1: "N wait", 2: "C work", 3: "C wait"}
     print("total clocks of CTA 0 (thread 0 view): %d" % tot)
     for k in range(4):

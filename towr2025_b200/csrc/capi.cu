@@ -82,6 +82,7 @@ struct towr_b200_batch {
   double *x_dev = nullptr, *g_dev = nullptr, *v_dev = nullptr;
   tb::ProblemConst* pc_gather_dev = nullptr;
   int max_ctas = 0, lanes = 1;
+  bool ws = false;         // warp-specialised kernel (kernels.cu)
   long long launches = 0;
 
   void SyncConsts() {
@@ -207,7 +208,18 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     int forced = 0;
     if (const char* env = std::getenv("TOWR_B200_LANES")) forced = std::atoi(env);
     b->lanes = 0;
+    // kernel variant: the warp-specialised one when its double-buffered G fits (TOWR_B200_KERNEL=lockstep|ws forces)
+    const char* kenv = std::getenv("TOWR_B200_KERNEL");
+    const bool want_ws = !kenv || std::strcmp(kenv, "ws") == 0;
+    if (want_ws && (!forced || forced == 2) && tb::EvalFitsWS(dp, 2, prop.sharedMemPerBlockOptin)) {
+      b->ws = true;
+      b->lanes = 2;
+      b->max_ctas = prop.multiProcessorCount;
+    } else if (kenv && std::strcmp(kenv, "ws") == 0) {
+      throw std::runtime_error("unsupported: the warp-specialised kernel does not fit this structure class");
+    }
     for (int lanes : {4, 2, 1}) {
+      if (b->ws) break;
       if (forced && lanes != forced) continue;
       if (tb::EvalSharedBytes(dp, lanes) > static_cast<size_t>(prop.sharedMemPerBlockOptin)) continue;
       int occ = tb::EvalOccupancy(dp, lanes);
@@ -219,8 +231,10 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     if (b->lanes == 0)
       throw std::runtime_error("unsupported: structure class needs more shared memory per CTA than the device has");
     if (std::getenv("TOWR_B200_DEBUG"))
-      std::fprintf(stderr, "batch: %d problems per CTA, %zu B shared (blob %d B, G capacity %d), %d CTAs\n", b->lanes,
-                   tb::EvalSharedBytes(dp, b->lanes), dp.blob.bytes, dp.g_capacity, b->max_ctas);
+      std::fprintf(stderr, "batch: %s kernel, %d problems per CTA, %zu B shared (blob %d B, G capacity %d), %d CTAs\n",
+                   b->ws ? "warp-specialised" : "lock-step", b->lanes,
+                   b->ws ? tb::EvalSharedBytesWS(dp, b->lanes) : tb::EvalSharedBytes(dp, b->lanes), dp.blob.bytes,
+                   dp.g_capacity, b->max_ctas);
     *out = b.release();
   });
 }
@@ -259,7 +273,8 @@ int towr_b200_batch_eval_device(towr_b200_batch* b, int n, int what, const doubl
       b->SyncConsts();
       Check(cudaStreamSynchronize(b->stream), "sync consts");
     }
-    Check(tb::LaunchEval(b->dp, b->pc_dev, what, d_x, d_g, d_jac_values, b->status_dev, n, b->lanes, b->max_ctas, s), "launch");
+    Check((b->ws ? tb::LaunchEvalWS : tb::LaunchEval)(b->dp, b->pc_dev, what, d_x, d_g, d_jac_values, b->status_dev, n,
+                                                       b->lanes, b->max_ctas, s), "launch");
     b->launches += 1;
   });
 }
@@ -299,7 +314,8 @@ int towr_b200_batch_eval(towr_b200_batch* b, const int* ids, int n, int what, co
       b->SyncConsts();
     }
     Check(cudaMemcpyAsync(b->x_dev, x, sizeof(double) * dp.n_vars * n, cudaMemcpyHostToDevice, b->stream), "H2D x");
-    Check(tb::LaunchEval(dp, pcs, what, b->x_dev, b->g_dev, b->v_dev, b->status_dev, n, b->lanes, b->max_ctas, b->stream), "launch");
+    Check((b->ws ? tb::LaunchEvalWS : tb::LaunchEval)(dp, pcs, what, b->x_dev, b->g_dev, b->v_dev, b->status_dev, n, b->lanes,
+                                                       b->max_ctas, b->stream), "launch");
     b->launches += 1;
     if (what & TOWR_B200_EVAL_G)
       Check(cudaMemcpyAsync(g_out, b->g_dev, sizeof(double) * dp.n_rows * n, cudaMemcpyDeviceToHost, b->stream), "D2H g");

@@ -13,4 +13,9 @@ cudaError_t LaunchEval(const DeviceProgram& P, const ProblemConst* pcs, int what
                        double* vals, int* status, int n_problems, int lanes, int max_ctas, cudaStream_t stream);
 // resident CTAs per SM of the evaluation kernel for this program and lane count (0: does not fit)
 int EvalOccupancy(const DeviceProgram& P, int lanes);
+// warp-specialised kernel (producer warps: stages N, C, A; consumer warps: stage B; double-buffered G)
+size_t EvalSharedBytesWS(const DeviceProgram& P, int lanes);
+bool EvalFitsWS(const DeviceProgram& P, int lanes, size_t smem_optin);
+cudaError_t LaunchEvalWS(const DeviceProgram& P, const ProblemConst* pcs, int what, const double* x, double* g,
+                         double* vals, int* status, int n_problems, int lanes, int max_ctas, cudaStream_t stream);
 }  // namespace tb

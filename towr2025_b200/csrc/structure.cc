@@ -296,7 +296,8 @@ void Builder::EmitDynamic() {
   const VarSet& ang = Set(kBaseAng);
   const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_dynamic);
   const int one = AddB(1.0);
-  const int per_sample = 72 + 9 * E + kDynPreSize;
+  // odd, so that the same slot of neighbouring samples (threads of one warp) falls into different shared-memory banks
+  const int per_sample = (72 + 9 * E + kDynPreSize) | 1;
   const int chunk = std::max(1, 1024 / per_sample);      // samples per group
   for (size_t k = 0; k < ts.size(); ++k) {
     const double t = ts[k];
