@@ -15,10 +15,12 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 from oracle import oracle_py as O   # noqa: E402
-from util import CASES, perturbed   # noqa: E402
+from util import CASES, mk, perturbed   # noqa: E402
 
-for name, robot, combo, T, goal, terrain in CASES[:5]:
-    p = O.Problem(O.make_spec(robot, combo, T, goal=goal, terrain=terrain))
+GOLDEN = list(CASES[:5]) + [c for c in CASES if c[0] in ("monoped_hop_torque", "biped_walk_torque_baserom_block")]
+for case in GOLDEN:
+    name = case[0]
+    p = O.Problem(mk(O, case))
     x0 = p.x0()
     x = perturbed(x0, 2026, 0.1)
     r, c, v = p.eval_jac(x)

@@ -6,7 +6,7 @@ import ctypes as C
 import numpy as np
 import pytest
 
-from util import CASES, perturbed, tol_ratio
+from util import CASES, mk, perturbed, tol_ratio
 
 DP = C.POINTER(C.c_double)
 
@@ -22,10 +22,9 @@ def emu_eval(E, spec, st, x):
 @pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
 def test_emulated_kernel_matches_oracle(product, oracle, emu, case):
     T, O = product, oracle
-    _, robot, combo, Tt, goal, terrain = case
-    s = T.make_spec(robot, combo, Tt, goal=goal, terrain=terrain)
+    s = mk(T, case)
     st = T.Structure(s)
-    p = O.Problem(O.make_spec(robot, combo, Tt, goal=goal, terrain=terrain))
+    p = O.Problem(mk(O, case))
     x0 = st.x0(s)
     for x in (x0, perturbed(x0, 11, 0.1), perturbed(x0, 12, 0.3)):
         g, v = emu_eval(emu, s, st, x)
@@ -56,8 +55,7 @@ def test_emulated_kernel_reproduces_committed_fixtures(product, emu):
     assert files
     for f in files:
         z = np.load(f)
-        _, robot, combo, Tt, goal, terrain = by_name[os.path.basename(f)[:-4]]
-        s = T.make_spec(robot, combo, Tt, goal=goal, terrain=terrain)
+        s = mk(T, by_name[os.path.basename(f)[:-4]])
         st = T.Structure(s)
         g, v = emu_eval(emu, s, st, np.ascontiguousarray(z["x"]))
         rows, cols = st.pattern()

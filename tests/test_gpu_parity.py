@@ -3,21 +3,21 @@ Tolerance (BASELINE.json north_star): sparsity indices bit-exact, values within 
 import numpy as np
 import pytest
 
-from util import CASES, perturbed, tol_ratio
+from util import CASES, mk, perturbed, tol_ratio
 
 pytestmark = pytest.mark.gpu
 
 
 def _problem_batch(T, O, case, n, seed):
     """n problems of one structure class with per-problem goals, terrain kept, and distinct x."""
-    _, robot, combo, Tt, goal, terrain = case
+    goal = case[4]
     rng = np.random.default_rng(seed)
     specs, xs = [], []
-    s0 = T.make_spec(robot, combo, Tt, goal=goal, terrain=terrain)
+    s0 = mk(T, case)
     st = T.Structure(s0)
     for i in range(n):
         g = (goal[0] + rng.uniform(-0.3, 0.3), goal[1] + rng.uniform(-0.2, 0.2), goal[2] + rng.uniform(-0.3, 0.3))
-        s = T.make_spec(robot, combo, Tt, goal=g, terrain=terrain)
+        s = mk(T, case, goal=g)
         s.mass *= 1.0 + 0.05 * rng.uniform(-1, 1)
         specs.append(s)
         xs.append(perturbed(st.x0(s), seed * 1000 + i, 0.1 if i % 2 else 0.0))
@@ -141,8 +141,7 @@ def test_gpu_reproduces_committed_fixtures(product):
     assert files
     for f in files:
         z = np.load(f)
-        _, robot, combo, Tt, goal, terrain = by_name[os.path.basename(f)[:-4]]
-        s = T.make_spec(robot, combo, Tt, goal=goal, terrain=terrain)
+        s = mk(T, by_name[os.path.basename(f)[:-4]])
         st = T.Structure(s)
         b = T.Batch(st, 3)
         b.set_all(s)

@@ -8,7 +8,7 @@ import os
 import numpy as np
 import pytest
 
-from util import CASES, perturbed, tol_ratio
+from util import CASES, mk, perturbed, tol_ratio
 
 DP = C.POINTER(C.c_double)
 
@@ -114,8 +114,7 @@ def test_static_stance_known_answer(oracle):
 @pytest.mark.parametrize("case", CASES[:6], ids=[c[0] for c in CASES[:6]])
 def test_oracle_jacobian_matches_finite_differences(oracle, case):
     O = oracle
-    _, robot, combo, T, goal, terrain = case
-    p = O.Problem(O.make_spec(robot, combo, T, goal=goal, terrain=terrain))
+    p = O.Problem(mk(O, case))
     x = perturbed(p.x0(), 4, 0.05)
     r, c, v = p.eval_jac(x)
     rng = np.random.default_rng(9)
@@ -127,7 +126,7 @@ def test_oracle_jacobian_matches_finite_differences(oracle, case):
         np.add.at(jd, r, v * d[c])
         # piecewise terrains (Block/Stairs) are non-smooth at their edges: allow a handful of rows to disagree
         bad = np.abs(jd - fd) > 1e-5 * max(1.0, np.abs(fd).max())
-        assert bad.sum() <= (3 if terrain in (1, 2) else 0)
+        assert bad.sum() <= (3 if case[5] in (1, 2) else 0)
 
 
 def test_oracle_reproduces_committed_fixtures(oracle):
@@ -137,8 +136,7 @@ def test_oracle_reproduces_committed_fixtures(oracle):
     by_name = {c[0]: c for c in CASES}
     for f in files:
         z = np.load(f)
-        _, robot, combo, T, goal, terrain = by_name[os.path.basename(f)[:-4]]
-        p = O.Problem(O.make_spec(robot, combo, T, goal=goal, terrain=terrain))
+        p = O.Problem(mk(O, by_name[os.path.basename(f)[:-4]]))
         r, c, v = p.eval_jac(z["x"])
         assert len(v) == int(z["nnz"])
         assert np.array_equal(r[z["jac_idx"]], z["jac_rows"]) and np.array_equal(c[z["jac_idx"]], z["jac_cols"])

@@ -5,15 +5,14 @@ import ctypes as C
 import numpy as np
 import pytest
 
-from util import CASES, perturbed, to_oracle_spec
+from util import CASES, mk, perturbed, to_oracle_spec
 
 
 @pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
 def test_structure_matches_oracle(product, oracle, case):
     T, O = product, oracle
-    _, robot, combo, Tt, goal, terrain = case
-    s = T.make_spec(robot, combo, Tt, goal=goal, terrain=terrain)
-    so = O.make_spec(robot, combo, Tt, goal=goal, terrain=terrain)
+    s = mk(T, case)
+    so = mk(O, case)
     # robot constants, gait tables and parameter defaults: same bytes
     assert bytes(to_oracle_spec(O, s)) == bytes(so)
     st = T.Structure(s)

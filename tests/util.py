@@ -24,7 +24,8 @@ def tol_ratio(a, b):
     return float((np.abs(a - b) / (ATOL + RTOL * np.abs(b))).max())
 
 
-# (name, robot, combo, T, goal, terrain)
+# (name, robot, combo, T, goal, terrain[, extra constraints (Parameters::ConstraintName ids)[, optimise durations]])
+TORQUE, BASE_ROM = 6, 8
 CASES = [
     ("anymal_trot", 3, 1, 2.0, (1.0, 0.0, 0.0), 0),
     ("anymal_trot_yaw", 3, 1, 2.0, (1.3, -0.2, 0.3), 0),
@@ -35,7 +36,18 @@ CASES = [
     ("monoped_hop2_chimney", 0, 3, 1.9, (0.8, 0.0, 0.0), 5),
     ("biped_run_chimneylr", 1, 1, 2.2, (1.2, 0.0, 0.0), 6),
     ("hyq_pace_flat", 2, 2, 2.0, (0.7, 0.2, 0.5), 0),
+    ("monoped_hop_torque", 0, 0, 2.4, (1.0, 0.0, 0.0), 0, (TORQUE,)),          # hopper_example.cc:145 enables Torque
+    ("biped_walk_torque_baserom_block", 1, 0, 2.4, (1.1, 0.0, 0.1), 1, (TORQUE, BASE_ROM)),
+    ("anymal_trot_baserom", 3, 1, 2.0, (1.0, 0.1, 0.0), 0, (BASE_ROM,)),
 ]
+
+
+def mk(M, case, goal=None):
+    """The case's NlpFormulation spec built by module M (the product package or the oracle binding)."""
+    extra = case[6] if len(case) > 6 else ()
+    opt = case[7] if len(case) > 7 else False
+    return M.make_spec(case[1], case[2], case[3], goal=goal if goal is not None else case[4], terrain=case[5],
+                       optimize_durations=opt, extra_constraints=extra)
 
 
 def perturbed(x0, seed, scale=0.1):

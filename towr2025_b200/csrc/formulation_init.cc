@@ -194,6 +194,9 @@ void ProblemConBounds(const HostProgram& hp, const towr_b200_spec& s, double* L,
       case kBoundGE0: lo = 0.0; up = +kNoBound; break;
       case kBoundBaseHeight: lo = 0.0; up = 1e20; break;
       case kBoundTotalDuration: lo = 0.1; up = hp.total_time - 0.2; break;
+      case kBoundNone: lo = -kNoBound; up = +kNoBound; break;
+      case kBoundTorqueX: lo = s.torque_tx_min; up = s.torque_tx_max; break;     // torque_constraint_discretized.cc:131-139
+      case kBoundTorqueY: lo = s.torque_ty_min; up = s.torque_ty_max; break;
     }
     L[r] = lo;
     U[r] = up;

@@ -340,6 +340,53 @@ __device__ __forceinline__ void ItemForce(const ItemCtx<L>& cx, const ItemC& it)
   }
 }
 
+// ------------------------------------------------------------------------------------------ torque (discretised)
+// g: torque_constraint_discretized.cc:105-129.  G slots: t1[3], t2[3], n[3], -n[3], (-k mu) n[3]; B[b0] = k_friction.
+template <class L>
+__device__ __forceinline__ void ItemTorque(const ItemCtx<L>& cx, const ItemC& it) {
+  Pt3 p, f, tau;
+  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, p);
+  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 1, f);
+  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 2, tau);
+  const TerrainSample ts = EvalTerrain(cx.pc->terrain_id, p.p[0], p.p[1]);
+  double n[3], t1[3], t2[3];
+  TerrainBasis(ts, n, t1, t2);
+  const double mu = kFrictionCoeff, kf = cx.T.B[it.b0];
+  double* G = cx.G + it.gslot * L::GS;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    TB_G(d) = t1[d];
+    TB_G(3 + d) = t2[d];
+    TB_G(6 + d) = n[d];
+    TB_G(9 + d) = -n[d];
+    TB_G(12 + d) = (-kf * mu) * n[d];
+  }
+  if (cx.g) {
+    auto dot = [](const double* a, const double* b) { return (a[0] * b[0] + a[1] * b[1]) + a[2] * b[2]; };
+    const double tau_t1 = dot(tau.p, t1), tau_t2 = dot(tau.p, t2), tau_n = dot(tau.p, n), f_n = dot(f.p, n);
+    const double tz_lim = kf * mu * f_n;
+    double* gr = cx.g + it.row * L::RS;
+    gr[0 * L::RS] = tau_t1;
+    gr[1 * L::RS] = tau_t2;
+    gr[2 * L::RS] = tau_n - tz_lim;
+    gr[3 * L::RS] = -tau_n - tz_lim;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ base motion
+// BaseMotionConstraint (base_motion_constraint.cc:60-66): rows AX..AZ = base euler angles, LX..LZ = base position;
+// the Jacobian is constant (Hermite basis values)
+template <class L>
+__device__ __forceinline__ void ItemBaseRom(const ItemCtx<L>& cx, const ItemC& it) {
+  if (!cx.g) return;
+  Pt3 lin, ang;
+  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, lin);
+  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 1, ang);
+  double* gr = cx.g + it.row * L::RS;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) { gr[d * L::RS] = ang.p[d]; gr[(3 + d) * L::RS] = lin.p[d]; }
+}
+
 // ------------------------------------------------------------------------------------------------ node-based
 // TerrainConstraint (terrain_constraint.cc:61-111) and BaseHeightConstraint (base_height_constraint.cc:58-110)
 template <class L>
@@ -397,6 +444,8 @@ __device__ __forceinline__ void RunItem(const ItemCtx<L>& cx, const ItemC& it) {
     case kItemRomPre: ItemRomPre<L>(cx, it); break;
     case kItemRomFoot: ItemRomFoot<L>(cx, it); break;
     case kItemForce: ItemForce<L>(cx, it); break;
+    case kItemTorque: ItemTorque<L>(cx, it); break;
+    case kItemBaseRom: ItemBaseRom<L>(cx, it); break;
     case kItemTerrainNode: ItemHeightNode<L>(cx, it, 0.0); break;
     case kItemBaseHeightNode: ItemHeightNode<L>(cx, it, 0.4); break;   // nlp_formulation.cc:597
     case kItemSwingNode: ItemSwingNode<L>(cx, it); break;

@@ -67,8 +67,14 @@ void PackProgram(HostProgram& hp) {
       case kItemDynCol:
       case kItemDynJlin: s0 = 0; break;
       case kItemRomPre:
+      case kItemBaseRom:
         add_sample(it.s[kSBaseLin]);
         add_sample(it.s[kSBaseAng]);
+        break;
+      case kItemTorque:
+        add_sample(it.s[kSMotion + it.ee]);
+        add_sample(it.s[kSForce + it.ee]);
+        add_sample(it.s[kSTorque + it.ee]);
         break;
       case kItemRomFoot: add_sample(it.s[kSMotion + it.ee]); break;
       case kItemForce:

@@ -49,6 +49,8 @@ enum ItemType : int {
   kItemSwingNode,       // swing_constraint.cc:54-108              4 rows per swing node
   kItemSplineAcc,       // spline_acc_constraint.cc:48-80          3 rows per junction
   kItemTotalDuration,   // total_duration_constraint.cc:48-72
+  kItemBaseRom,         // base_motion_constraint.cc:60-85         6 rows per sample (base euler angles, base position)
+  kItemTorque,          // torque_constraint_discretized.cc:105-235  4 rows per (sample, foot)
   kItemDynFoot,         // per (dynamic sample, foot): f_e, c - p_e slots and the foot's torque term f_e x (c - p_e) + tau_e
   // level 1: read the scratch slots of a level-0 item (ItemC::aux)
   kItemDynWrench,       // dynamic_constraint.cc:63-148: the 6 g rows of a dynamic sample (feet summed in order)
@@ -115,7 +117,7 @@ struct ItemC {          // 16 bytes
 };
 // compact sample = polynomial index | time index << 16 ; compact polynomial = node slot | duration index << 16
 // sample order of an item: DynPre [ang], DynFoot [lin, motion, force, torque], DynWrench [lin], RomPre [lin, ang],
-// RomFoot [motion], Force [motion, force]
+// RomFoot [motion], Force [motion, force], Torque [motion, force, torque], BaseRom [lin, ang]
 struct BlobLayout {     // byte offsets into the blob (all 16-byte aligned), element counts
   int bytes;
   int off_B, n_B;                 // double
@@ -176,7 +178,7 @@ struct ConSet { std::string name; int row0, n_rows; };
 
 // what ConstraintSet::GetBounds returns for one row (values depend on per-problem model data)
 enum RowBoundKind { kBoundZero = 0, kBoundTerrainSwing, kBoundRom, kBoundForceNormal, kBoundLE0, kBoundGE0,
-                    kBoundBaseHeight, kBoundTotalDuration };
+                    kBoundBaseHeight, kBoundTotalDuration, kBoundNone, kBoundTorqueX, kBoundTorqueY };
 struct RowBound { int kind, ee, dim; };
 
 struct HostProgram {

@@ -225,6 +225,8 @@ class Builder {
   void EmitSplineAcc();
   void EmitRom();
   void EmitForceDisc(int ee);
+  void EmitTorqueDisc(int ee);
+  void EmitBaseRom();
   void EmitSwing(int ee);
   void EmitBaseHeight();
   void EmitHeightRows(const VarSet& set, int item_type, int ee);
@@ -514,6 +516,78 @@ void Builder::EmitForceDisc(int ee) {
   EndSet();
 }
 
+// TorqueConstraintDiscretized (torque_constraint_discretized.cc:103-235): 4 rows per sample; G slots t1, t2, n, -n,
+// (-k mu) n.  The ee-motion block exists only where the terrain has curvature (same rule as the force constraint).
+void Builder::EmitTorqueDisc(int ee) {
+  const VarSet& mo = Set(kEEMotion, ee);
+  const VarSet& fo = Set(kEEForce, ee);
+  const VarSet& to = Set(kEETorque, ee);
+  const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_torque);
+  const int chunk = 64;
+  const int bk_friction = AddB(s_.torque_k_friction);
+  for (size_t k = 0; k < ts.size(); ++k) {
+    const int r0 = static_cast<int>(k) * 4;
+    if (k % chunk == 0) {
+      if (k == 0) { BeginGroup(); BeginSet("torque-disc-" + to.name, static_cast<int>(ts.size()) * 4); }
+      else BeginGroup(r0);
+    }
+    ItemRec it = NewItem(kItemTorque);
+    it.ee = static_cast<short>(ee);
+    it.row[0] = set_row0_ + r0;
+    it.gslot = AllocG(15);
+    it.b0 = bk_friction;
+    SplineAt am = At(mo, ts[k]), af = At(fo, ts[k]), at = At(to, ts[k]);
+    it.s[kSMotion + ee] = am.sample;
+    it.s[kSForce + ee] = af.sample;
+    it.s[kSTorque + ee] = at.sample;
+    hp_.items.push_back(it);
+    Bound(r0 + 0, kBoundTorqueX, ee);
+    Bound(r0 + 1, kBoundTorqueY, ee);
+    Bound(r0 + 2, kBoundLE0, ee);
+    Bound(r0 + 3, kBoundLE0, ee);
+    for (const ColBasis& c : Columns(to, at.poly, at.t_local))
+      for (int i = 0; i < 4; ++i) {              // t1, t2, n, -n . J_tau
+        Term tm; tm.g = it.gslot + 3 * i + c.dim; tm.b = AddB(c.v[0]);
+        Add(r0 + i, to.col0 + c.idx, tm);
+      }
+    for (const ColBasis& c : Columns(fo, af.poly, af.t_local))
+      for (int i = 2; i < 4; ++i) {              // (-k mu) n . J_f on the two yaw-friction rows
+        Term tm; tm.g = it.gslot + 12 + c.dim; tm.b = AddB(c.v[0]);
+        Add(r0 + i, fo.col0 + c.idx, tm);
+      }
+  }
+  EndSet();
+}
+
+// BaseMotionConstraint (base_motion_constraint.cc:38-85): rows AX..AZ <- base-ang position, LX..LZ <- base-lin position;
+// bounds are NoBound unless Parameters sets them (nlp_formulation.cc, not in the default set-up)
+void Builder::EmitBaseRom() {
+  const VarSet& lin = Set(kBaseLin);
+  const VarSet& ang = Set(kBaseAng);
+  const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_base_motion);
+  BeginGroup();
+  BeginSet("baseMotion", static_cast<int>(ts.size()) * 6);
+  for (size_t k = 0; k < ts.size(); ++k) {
+    const int r0 = static_cast<int>(k) * 6;
+    ItemRec it = NewItem(kItemBaseRom);
+    it.row[0] = set_row0_ + r0;
+    SplineAt al = At(lin, ts[k]), aa = At(ang, ts[k]);
+    it.s[kSBaseLin] = al.sample;
+    it.s[kSBaseAng] = aa.sample;
+    hp_.items.push_back(it);
+    for (int d = 0; d < 6; ++d) Bound(r0 + d, kBoundNone);
+    for (const ColBasis& c : Columns(ang, aa.poly, aa.t_local)) {
+      Term tm; tm.g = kGOne; tm.b = AddB(c.v[0]);
+      Add(r0 + c.dim, ang.col0 + c.idx, tm);
+    }
+    for (const ColBasis& c : Columns(lin, al.poly, al.t_local)) {
+      Term tm; tm.g = kGOne; tm.b = AddB(c.v[0]);
+      Add(r0 + 3 + c.dim, lin.col0 + c.idx, tm);
+    }
+  }
+  EndSet();
+}
+
 // SwingConstraint (swing_constraint.cc:54-108): per swing node and dim in {x,y} a position and a velocity row
 void Builder::EmitSwing(int ee) {
   const VarSet& mo = Set(kEEMotion, ee);
@@ -567,10 +641,13 @@ void Builder::Run() {
         for (int e = 0; e < s_.n_ee; ++e) EmitSwing(e);
         break;
       case TOWR_B200_C_BASE_HEIGHT: EmitBaseHeight(); break;
+      case TOWR_B200_C_TORQUE:
+        if (!(s_.dt_constraint_torque > 0.0)) throw std::runtime_error("unsupported: node-based TorqueConstraint");
+        for (int e = 0; e < s_.n_ee; ++e) EmitTorqueDisc(e);
+        break;
+      case TOWR_B200_C_BASE_ROM: EmitBaseRom(); break;
       case TOWR_B200_C_TOTAL_TIME:
       case TOWR_B200_C_TERRAIN_HARD:
-      case TOWR_B200_C_TORQUE:
-      case TOWR_B200_C_BASE_ROM:
         throw std::runtime_error("unsupported: constraint " + std::to_string(s_.constraints[i]) + " not built yet");
       default: throw std::runtime_error("constraint not defined!");   // nlp_formulation.cc:396
     }
@@ -602,6 +679,8 @@ std::string StructureSignature(const towr_b200_spec& s) {
     << "," << s.dt_constraint_force << "," << s.dt_constraint_torque << "|bp" << s.duration_base_polynomial
     << "|pp" << s.ee_polynomials_per_swing_phase << "," << s.force_polynomials_per_stance_phase << ","
     << s.torque_polynomials_per_stance_phase;
+  for (int i = 0; i < s.n_constraints; ++i)
+    if (s.constraints[i] == TOWR_B200_C_TORQUE) o << "|kf" << s.torque_k_friction;   // baked into the class tables
   return o.str();
 }
 
