@@ -25,39 +25,77 @@ static std::string g_err;
 
 extern "C" const char* emu_last_error() { return g_err.c_str(); }
 
-// x: n_vars; g: n_rows; vals: nnz
+// x: n_vars; g: n_rows; vals: nnz.  Mirrors the kernel's stages for one problem (P = 1).
+template <bool RT>
+static void EmuEval(const HostProgram& hp, const towr_b200_spec* s, const double* x, double* g, double* vals) {
+  const BlobLayout& L = hp.blob;
+  ProblemConst pc;
+  FillProblemConst(*s, pc);
+  ItemCtx<Lockstep<1, RT>> cx;
+  cx.T = MakeTables(hp.blob_data.data(), L);
+  cx.n_ee = hp.n_ee;
+  std::vector<double> nodes(L.n_node_values), coef(6 * L.n_polys), G(hp.g_capacity), rtd(5 * L.n_polys), pdur(L.n_pdur + 1);
+  for (int i = 0; i < L.n_node_values; ++i) nodes[i] = cx.T.node_src[i] != 0xFFFF ? x[cx.T.node_src[i]] : 0.0;
+  if (RT) {   // stage D
+    for (int f = 0; f < L.n_rt_feet; ++f) {
+      const RtFoot ft = cx.T.rt_feet[f];
+      double sum = 0.0;
+      for (int i = 0; i < ft.n_phases - 1; ++i) { pdur[ft.phase0 + i] = x[ft.col0 + i]; sum += x[ft.col0 + i]; }
+      pdur[ft.phase0 + ft.n_phases - 1] = hp.total_time - sum;
+    }
+    for (int poly = 0; poly < L.n_polys; ++poly) {
+      const uint32_t pm = cx.T.poly_meta[poly];
+      double* o = rtd.data() + poly * 5;
+      if (pm == kPolyFixed) {
+        const int di = cx.T.polys[poly] >> 16;
+        o[0] = cx.T.durs[3 * di]; o[1] = cx.T.durs[3 * di + 1]; o[2] = cx.T.durs[3 * di + 2];
+        o[3] = cx.T.rdurs[2 * di]; o[4] = cx.T.rdurs[2 * di + 1];
+      } else {
+        const RtFoot ft = cx.T.rt_feet[pm >> 24];
+        const double Td = pdur[ft.phase0 + (pm & 0xFF)] / static_cast<double>((pm >> 8) & 0xFF);
+        const double T2 = Td * Td, T3 = Cube(Td);
+        o[0] = Td; o[1] = T2; o[2] = T3; o[3] = 1.0 / T2; o[4] = 1.0 / T3;
+      }
+    }
+  }
+  for (int i = 0; i < 3 * L.n_polys; ++i) {
+    int poly = i / 3, d = i % 3;
+    uint32_t pr = cx.T.polys[poly];
+    int n0 = pr & 0xFFFF;
+    double T, T2, T3, r2, r3;
+    if (RT) {
+      const double* o = rtd.data() + poly * 5;
+      T = o[0]; T2 = o[1]; T3 = o[2]; r2 = o[3]; r3 = o[4];
+    } else {
+      const double* du = cx.T.durs + 3 * (pr >> 16);
+      const double* rd = cx.T.rdurs + 2 * (pr >> 16);
+      T = du[0]; T2 = du[1]; T3 = du[2]; r2 = rd[0]; r3 = rd[1];
+    }
+    double p0 = nodes[n0 * 6 + d], v0 = nodes[n0 * 6 + 3 + d], p1 = nodes[n0 * 6 + 6 + d], v1 = nodes[n0 * 6 + 9 + d];
+    coef[poly * 6 + d] = ExactDiv(-(3.0 * (p0 - p1) + T * (2.0 * v0 + v1)), T2, r2);
+    coef[poly * 6 + 3 + d] = ExactDiv(2.0 * (p0 - p1) + T * (v0 + v1), T3, r3);
+  }
+  cx.nodes = nodes.data(); cx.coef = coef.data(); cx.G = G.data(); cx.g = g; cx.pc = &pc;
+  cx.rtd = rtd.data(); cx.pdur = pdur.data();
+  for (const SegmentRec& sg : hp.segments) {
+    std::fill(G.begin(), G.end(), std::nan(""));
+    G[kGOne] = 1.0; G[kGMass] = pc.mass; G[kGMinusOne] = -1.0;
+    for (int i = 0; i < sg.n_items; ++i) RunItem<Lockstep<1, RT>>(cx, cx.T.items[sg.item0 + i]);   // level-0 items come first
+    // the device descriptors, as the kernel's stage B reads them
+    for (int e = 0; e < sg.n_entries; ++e) {
+      const uint32_t w = hp.entries_dev[sg.entry0 + e];
+      const double second = (w & 0x10000u) ? G[((w >> 16) & 0xFFF8u) / 8] : cx.T.B[(w >> 16) / 8];
+      vals[sg.entry0 + e] = G[(w & 0xFFFF) / 8] * second;
+    }
+  }
+}
+
 extern "C" int emu_eval(const towr_b200_spec* s, const double* x, double* g, double* vals) {
   try {
     HostProgram hp;
     BuildProgram(*s, hp);
-    const BlobLayout& L = hp.blob;
-    ProblemConst pc;
-    FillProblemConst(*s, pc);
-    ItemCtx<Lockstep<1>> cx;
-    cx.T = MakeTables(hp.blob_data.data(), L);
-    std::vector<double> nodes(L.n_node_values), coef(6 * L.n_polys), G(hp.g_capacity);
-    for (int i = 0; i < L.n_node_values; ++i) nodes[i] = cx.T.node_src[i] != 0xFFFF ? x[cx.T.node_src[i]] : 0.0;
-    for (int i = 0; i < 3 * L.n_polys; ++i) {
-      int poly = i / 3, d = i % 3;
-      uint32_t pr = cx.T.polys[poly];
-      int n0 = pr & 0xFFFF;
-      const double* du = cx.T.durs + 3 * (pr >> 16);
-      double p0 = nodes[n0 * 6 + d], v0 = nodes[n0 * 6 + 3 + d], p1 = nodes[n0 * 6 + 6 + d], v1 = nodes[n0 * 6 + 9 + d];
-      const double* rd = cx.T.rdurs + 2 * (pr >> 16);
-      coef[poly * 6 + d] = ExactDiv(-(3.0 * (p0 - p1) + du[0] * (2.0 * v0 + v1)), du[1], rd[0]);
-      coef[poly * 6 + 3 + d] = ExactDiv(2.0 * (p0 - p1) + du[0] * (v0 + v1), du[2], rd[1]);
-    }
-    cx.nodes = nodes.data(); cx.coef = coef.data(); cx.G = G.data(); cx.g = g; cx.pc = &pc;
-    for (const SegmentRec& sg : hp.segments) {
-      std::fill(G.begin(), G.end(), std::nan(""));
-      G[kGOne] = 1.0; G[kGMass] = pc.mass;
-      for (int i = 0; i < sg.n_items; ++i) RunItem<Lockstep<1>>(cx, cx.T.items[sg.item0 + i]);   // level-0 items come first
-      // the device descriptors, as the kernel's stage B reads them
-      for (int e = 0; e < sg.n_entries; ++e) {
-        const uint32_t w = hp.entries_dev[sg.entry0 + e];
-        vals[sg.entry0 + e] = G[(w & 0xFFFF) / 8] * cx.T.B[(w >> 16) / 8];
-      }
-    }
+    if (hp.optimize_durations) EmuEval<true>(hp, s, x, g, vals);
+    else EmuEval<false>(hp, s, x, g, vals);
     return 0;
   } catch (const std::exception& e) {
     g_err = e.what();

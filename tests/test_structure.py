@@ -23,7 +23,7 @@ def test_structure_matches_oracle(product, oracle, case):
     x0 = st.x0(s)
     assert np.array_equal(x0, p.x0())
     rows, cols = st.pattern()
-    for x in (x0, perturbed(x0, 7, 0.05)):
+    for x in (x0, perturbed(x0, 7, 0.02)):
         r, c, _ = p.eval_jac(x)
         assert len(r) == st.nnz
         assert np.array_equal(r, rows) and np.array_equal(c, cols)

@@ -5,7 +5,7 @@ import towr2025_b200 as T
 from oracle import oracle_py as O
 from util import CASES, perturbed, to_oracle_spec
 import test_gpu_parity as tg
-case = CASES[3]
+case = [c for c in CASES if c[0] == (sys.argv[1] if len(sys.argv) > 1 else 'biped_walk_stairs')][0]
 st, specs, x = tg._problem_batch(T, O, case, 6, 3)
 b = T.Batch(st, 6)
 for i, s in enumerate(specs): b.set_problem(i, s)
@@ -20,6 +20,7 @@ for i, s in enumerate(specs):
     print("problem", i, "bad g", len(bg), "bad J", len(bv), "terrain", s.terrain_id)
     for k in bg[:6]: print("   g row", k, g[i][k], go[k])
     for k in bv[:6]: print("   J", k, "row", rows[k], "col", cols[k], v[i][k], vo[k])
-off=0
-for n,r in cs:
-    print(n, off, off+r); off+=r
+if len(sys.argv) > 2:
+    off=0
+    for n,r in cs:
+        print(n, off, off+r); off+=r

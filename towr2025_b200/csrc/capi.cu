@@ -190,6 +190,7 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     tb::DeviceProgram& dp = b->dp;
     dp.n_vars = hp.n_vars; dp.n_rows = hp.n_rows; dp.nnz = hp.nnz; dp.n_ee = hp.n_ee;
     dp.n_segments = static_cast<int>(hp.segments.size());
+    dp.total_time = hp.total_time;
     dp.g_capacity = hp.g_capacity;
     dp.blob = hp.blob;
     auto keep = [&](auto* p) { b->owned.push_back(const_cast<void*>(static_cast<const void*>(p))); return p; };

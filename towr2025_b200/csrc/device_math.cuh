@@ -26,6 +26,9 @@ struct Tables {
   const uint32_t* samples;
   const uint32_t* polys;
   const uint16_t* node_src;
+  const RtSpline* rt_splines;   // optimised durations only
+  const RtFoot* rt_feet;
+  const uint32_t* poly_meta;
 };
 
 __device__ __forceinline__ Tables MakeTables(const unsigned char* blob, const BlobLayout& L) {
@@ -39,6 +42,9 @@ __device__ __forceinline__ Tables MakeTables(const unsigned char* blob, const Bl
   t.samples = reinterpret_cast<const uint32_t*>(blob + L.off_samples);
   t.polys = reinterpret_cast<const uint32_t*>(blob + L.off_polys);
   t.node_src = reinterpret_cast<const uint16_t*>(blob + L.off_node_src);
+  t.rt_splines = reinterpret_cast<const RtSpline*>(blob + L.off_rt_splines);
+  t.rt_feet = reinterpret_cast<const RtFoot*>(blob + L.off_rt_feet);
+  t.poly_meta = reinterpret_cast<const uint32_t*>(blob + L.off_poly_meta);
   return t;
 }
 
@@ -70,6 +76,114 @@ __device__ __forceinline__ void EvalSpline(const Tables& tb_, const double* __re
     if (NEED & kNeedVel) o.v[d] = (b + (2 * t) * c) + (3 * t2) * dd;
     if (NEED & kNeedAcc) o.a[d] = 2.0 * c + (6 * t) * dd;
   }
+}
+
+// t^3 rounded (almost always) correctly, like the reference's std::pow(t, 3): t*t with its rounding error carried by FMA
+__device__ __forceinline__ double Cube(double t) {
+  const double p = t * t;
+  const double e = fma(t, t, -p);
+  return fma(p, t, e * t);
+}
+
+// t^4 likewise (std::pow(T, 4) in polynomial.cc:240)
+__device__ __forceinline__ double Pow4(double t) {
+  const double p = t * t;
+  const double e = fma(t, t, -p);
+  const double hi = p * p;
+  return hi + (fma(p, p, -hi) + 2.0 * p * e);
+}
+
+// ---- PhaseSpline with optimised durations: the polynomial a global time falls into and its local time depend on
+// the problem's current durations.  rtd: per-problem polynomial durations, 5 per polynomial (T, T^2, T^3, 1/T^2,
+// 1/T^3), element i at rtd[i * NS].
+struct RtPoint {
+  int poly;            // global polynomial index
+  double t, T;         // local time, polynomial duration
+};
+
+// Spline::GetSegmentID / GetLocalTime (spline.cc:48-78): first i with sum_{j<=i} d_j >= t - 1e-10; the local time
+// subtracts the earlier durations one by one.  Then polynomial.cc:47-61 with the reference's association.
+template <int NEED, int NS>
+__device__ __forceinline__ RtPoint EvalSplineRt(const Tables& tb_, const double* __restrict__ nodes,
+                                                const double* __restrict__ coef, const double* __restrict__ rtd,
+                                                int sample, Pt3& o) {
+  const uint32_t sr = tb_.samples[sample];
+  const RtSpline sp = tb_.rt_splines[sr & 0xFFFF];
+  const double tg = tb_.times[3 * (sr >> 16)];
+  int id = sp.n_polys - 1;
+  double acc = 0.0;
+  for (int i = 0; i < sp.n_polys; ++i) {
+    acc += rtd[(sp.poly0 + i) * 5 * NS];
+    if (acc >= tg - 1e-10) { id = i; break; }
+  }
+  double t = tg;
+  for (int i = 0; i < id; ++i) t -= rtd[(sp.poly0 + i) * 5 * NS];
+  RtPoint r;
+  r.poly = sp.poly0 + id;
+  r.t = t;
+  r.T = rtd[r.poly * 5 * NS];
+  const double t2 = t * t, t3 = Cube(t);
+  const int n0 = tb_.polys[r.poly] & 0xFFFF;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    const double a = nodes[(n0 * 6 + d) * NS], b = nodes[(n0 * 6 + 3 + d) * NS];
+    const double c = coef[(r.poly * 6 + d) * NS], dd = coef[(r.poly * 6 + 3 + d) * NS];
+    if (NEED & kNeedPos) o.p[d] = ((a + t * b) + t2 * c) + t3 * dd;
+    if (NEED & kNeedVel) o.v[d] = (b + (2 * t) * c) + (3 * t2) * dd;
+    if (NEED & kNeedAcc) o.a[d] = 2.0 * c + (6 * t) * dd;
+  }
+  return r;
+}
+
+// W[c] = d pos(t) / d (variable c of the spline's set), all columns (NodeSpline::FillJacobianWrtNodes,
+// node_spline.cc:84-112, on the pre-filled structure of phase_spline.cc:45-51): zero except the variables mapped to
+// the active polynomial's two nodes; closed forms polynomial.cc:106-160 (kPos).  W: element c at W[c * GS].
+template <int GS>
+__device__ __forceinline__ void WriteHermiteWeights(const Tables& tb_, const RtSpline& sp, const RtPoint& r, double* W) {
+  for (int c = 0; c < sp.n_cols; ++c) W[c * GS] = 0.0;
+  const double t = r.t, T = r.T;
+  const double t2 = t * t, t3 = Cube(t), T2 = T * T, T3 = Cube(T);
+  double b[4];
+  b[0] = (2 * t3) / T3 - (3 * t2) / T2 + 1;     // start node, position
+  b[1] = t - (2 * t2) / T + t3 / T2;             // start node, velocity
+  b[2] = (3 * t2) / T2 - (2 * t3) / T3;          // end node, position
+  b[3] = t3 / T2 - t2 / T;                       // end node, velocity
+  const int n0 = tb_.polys[r.poly] & 0xFFFF;
+#pragma unroll
+  for (int side = 0; side < 2; ++side)
+#pragma unroll
+    for (int deriv = 0; deriv < 2; ++deriv)
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        const unsigned src = tb_.node_src[(n0 + side) * 6 + deriv * 3 + d];
+        if (src != 0xFFFFu) {
+          double* w = W + (static_cast<int>(src) - sp.col0) * GS;
+          *w = *w + b[side * 2 + deriv];
+        }
+      }
+}
+
+// PhaseSpline::GetDerivativeOfPosWrtPhaseDuration (phase_spline.cc:77-93) with
+// CubicHermitePolynomial::GetDerivativeOfPosWrtDuration (polynomial.cc:236-257); returns the current phase
+template <int NS>
+__device__ __forceinline__ int PosWrtPhaseDuration(const Tables& tb_, const double* __restrict__ nodes, const RtPoint& r,
+                                                   const double vel[3], double dxdT[3]) {
+  const uint32_t pm = tb_.poly_meta[r.poly];
+  const int phase = pm & 0xFF, nin = (pm >> 8) & 0xFF, prev = (pm >> 16) & 0xFF;
+  const double t = r.t, T = r.T;
+  const double t2 = t * t, t3 = Cube(t), T2 = T * T, T3 = Cube(T), T4 = Pow4(T);
+  const int n0 = tb_.polys[r.poly] & 0xFFFF;
+  const double inner = 1.0 / nin;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    const double x0 = nodes[(n0 * 6 + d) * NS], v0 = nodes[(n0 * 6 + 3 + d) * NS];
+    const double x1 = nodes[(n0 * 6 + 6 + d) * NS], v1 = nodes[(n0 * 6 + 9 + d) * NS];
+    const double dx = (((t3 * (v0 + v1)) / T3 - (t2 * (2.0 * v0 + v1)) / T2) -
+                       ((3 * t3) * (((2.0 * x0 - 2.0 * x1) + T * v0) + T * v1)) / T4) +
+                      ((2 * t2) * (((3.0 * x0 - 3.0 * x1) + (2 * T) * v0) + T * v1)) / T3;
+    dxdT[d] = inner * (dx - prev * vel[d]);
+  }
+  return phase;
 }
 
 struct Trig { double sx, cx, sy, cy, sz, cz; };

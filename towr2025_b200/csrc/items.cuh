@@ -10,8 +10,10 @@ namespace tb {
 //   G[i * GS] (G buffer and scratch), nodes[i * NS] / coef[i * NS] (spline tables), g[i * RS] (constraint rows).
 // Lockstep<P>: the fused kernel's shared-memory arrays, interleaved over the P problems of a CTA (and the host
 // emulation, P = 1).  The tiled pipeline (tiled.cu) uses Tiled<W>.
-template <int P>
-struct Lockstep { static constexpr int GS = P, NS = P, RS = 1; };
+// RT: the structure class optimises the phase durations (PhaseSpline path): ee-motion / ee-force / ee-torque samples are
+// resolved per problem, their Jacobian weights and the ee-schedule columns are written by the items.
+template <int P, bool RT_ = false>
+struct Lockstep { static constexpr int GS = P, NS = P, RS = 1; static constexpr bool RT = RT_; };
 
 template <class L>
 struct ItemCtx {
@@ -21,7 +23,25 @@ struct ItemCtx {
   double* G;             // segment-relative G buffer (shared memory), element i at G[i * L::GS]
   double* g;             // this problem's constraint values (global), or nullptr
   const ProblemConst* pc;
+  const double* rtd;     // RT: per-problem polynomial durations (device_math.cuh), interleaved like nodes
+  const double* pdur;    // RT: per-problem phase durations, element RtFoot::phase0 + phase
+  int n_ee;
 };
+
+// column j of PhaseDurations::GetJacobianOfPos (phase_durations.cc:126-154): d pos / d (phase duration j)
+__device__ __forceinline__ void DurationColumn(int j, int cur, int n_phases, const double dxdT[3], const double xd[3], double c[3]) {
+  const bool in_last = cur == n_phases - 1;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    double v = 0.0;
+    if (!in_last && j == cur) v = dxdT[d];
+    if (j < cur) {
+      v = -1.0 * xd[d];
+      if (in_last) v = v - dxdT[d];
+    }
+    c[d] = v;
+  }
+}
 
 #define TB_G(i) G[(i) * L::GS]
 
@@ -83,9 +103,16 @@ __device__ __forceinline__ void ItemDynFoot(const ItemCtx<L>& cx, const ItemC& i
   const int E = it.n_ee, e = it.ee;
   Pt3 lin, f, p, tq;
   EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, lin);
-  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 1, p);
-  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 2, f);
-  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 3, tq);
+  RtPoint rp, rf, rt;
+  if constexpr (L::RT) {
+    rp = EvalSplineRt<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0 + 1, p);
+    rf = EvalSplineRt<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0 + 2, f);
+    rt = EvalSplineRt<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0 + 3, tq);
+  } else {
+    EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 1, p);
+    EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 2, f);
+    EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 3, tq);
+  }
   double* G = cx.G + it.gslot * L::GS;
   double r[3] = {lin.p[0] - p.p[0], lin.p[1] - p.p[1], lin.p[2] - p.p[2]};
   double cr[3];
@@ -95,6 +122,42 @@ __device__ __forceinline__ void ItemDynFoot(const ItemCtx<L>& cx, const ItemC& i
     TB_G(kDynF + 3 * e + d) = f.p[d];
     TB_G(kDynF + 3 * E + 3 * e + d) = r[d];
     TB_G(kDynF + 6 * E + 3 * e + d) = cr[d] + tq.p[d];
+  }
+  if constexpr (L::RT) {
+    // negated copies (the Cross() entries with a minus sign), the Hermite weights of the three splines and the finished
+    // ee-schedule block 6 x (P-1): GetJacobianWrtForce(J_f,dT) + GetJacobianWrtEEPos(J_p,dT)
+    // (dynamic_constraint.cc:99-104, single_rigid_body_dynamics.cc:168-204)
+    const int neg = DynNegOffset(E);
+#pragma unroll
+    for (int d = 0; d < 3; ++d) { TB_G(neg + 3 * e + d) = -f.p[d]; TB_G(neg + 3 * E + 3 * e + d) = -r[d]; }
+    const RtSpline sm = cx.T.rt_splines[e], sf = cx.T.rt_splines[E + e], st = cx.T.rt_splines[2 * E + e];
+    double* X = cx.G + it.aux * L::GS;                 // this foot's block: W_p | W_f | W_tau | schedule[6][P-1]
+    WriteHermiteWeights<L::GS>(cx.T, sm, rp, X);
+    WriteHermiteWeights<L::GS>(cx.T, sf, rf, X + sm.n_cols * L::GS);
+    WriteHermiteWeights<L::GS>(cx.T, st, rt, X + (sm.n_cols + sf.n_cols) * L::GS);
+    double* S = X + (sm.n_cols + sf.n_cols + st.n_cols) * L::GS;
+    const RtFoot ft = cx.T.rt_feet[e];
+    double dpT[3], dfT[3];
+    const int cur_p = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, rp, p.v, dpT);
+    const int cur_f = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, rf, f.v, dfT);
+    const int nc = ft.n_phases - 1;
+    for (int j = 0; j < nc; ++j) {
+      double cf[3], cp[3];
+      DurationColumn(j, cur_f, ft.n_phases, dfT, f.v, cf);
+      DurationColumn(j, cur_p, ft.n_phases, dpT, p.v, cp);
+      // -((-Cross(r)) J_f,dT) rows, then + -(Cross(f) (-J_p,dT)) rows; stored off-diagonal entries in column order
+      const double af0 = -((r[2]) * cf[1] + (-r[1]) * cf[2]);
+      const double af1 = -((-r[2]) * cf[0] + (r[0]) * cf[2]);
+      const double af2 = -((r[1]) * cf[0] + (-r[0]) * cf[1]);
+      const double ap0 = -((-f.p[2]) * (-cp[1]) + (f.p[1]) * (-cp[2]));
+      const double ap1 = -((f.p[2]) * (-cp[0]) + (-f.p[0]) * (-cp[2]));
+      const double ap2 = -((-f.p[1]) * (-cp[0]) + (f.p[0]) * (-cp[1]));
+      S[(0 * nc + j) * L::GS] = af0 + ap0;
+      S[(1 * nc + j) * L::GS] = af1 + ap1;
+      S[(2 * nc + j) * L::GS] = af2 + ap2;
+#pragma unroll
+      for (int d = 0; d < 3; ++d) S[((3 + d) * nc + j) * L::GS] = -cf[d];
+    }
   }
 }
 
@@ -291,9 +354,29 @@ __device__ __forceinline__ void ItemRomPre(const ItemCtx<L>& cx, const ItemC& it
 template <class L>
 __device__ __forceinline__ void ItemRomFoot(const ItemCtx<L>& cx, const ItemC& it) {
   Pt3 p;
-  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, p);
+  RtPoint rp;
+  if constexpr (L::RT) rp = EvalSplineRt<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0, p);
+  else EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, p);
   const double* S = cx.G + it.aux * L::GS;
   double* G = cx.G + it.gslot * L::GS;
+  if constexpr (L::RT) {
+    // Hermite weights of the ee-motion spline and the finished ee-schedule block R^T J_p,dT
+    // (range_of_motion_constraint.cc:126-130): G + 9 = W_p[n_cols] | schedule[3][P-1]
+    const RtSpline sm = cx.T.rt_splines[it.ee];
+    WriteHermiteWeights<L::GS>(cx.T, sm, rp, G + 9 * L::GS);
+    double* Sc = G + (9 + sm.n_cols) * L::GS;
+    const RtFoot ft = cx.T.rt_feet[it.ee];
+    double dpT[3];
+    const int cur = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, rp, p.v, dpT);
+    const int nc = ft.n_phases - 1;
+    for (int j = 0; j < nc; ++j) {
+      double c[3];
+      DurationColumn(j, cur, ft.n_phases, dpT, p.v, c);
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+        Sc[(r * nc + j) * L::GS] = (S[(kRpR + r) * L::GS] * c[0] + S[(kRpR + 3 + r) * L::GS] * c[1]) + S[(kRpR + 6 + r) * L::GS] * c[2];
+    }
+  }
   const double rw[3] = {p.p[0] - S[(kRpLin + 0) * L::GS], p.p[1] - S[(kRpLin + 1) * L::GS], p.p[2] - S[(kRpLin + 2) * L::GS]};
   if (cx.g) {
     double* gr = cx.g + it.row * L::RS;
@@ -315,8 +398,14 @@ __device__ __forceinline__ void ItemRomFoot(const ItemCtx<L>& cx, const ItemC& i
 template <class L>
 __device__ __forceinline__ void ItemForce(const ItemCtx<L>& cx, const ItemC& it) {
   Pt3 p, f;
-  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, p);
-  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 1, f);
+  RtPoint rf;
+  if constexpr (L::RT) {
+    EvalSplineRt<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0, p);
+    rf = EvalSplineRt<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0 + 1, f);
+  } else {
+    EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, p);
+    EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 1, f);
+  }
   const TerrainSample ts = EvalTerrain(cx.pc->terrain_id, p.p[0], p.p[1]);
   double n[3], t1[3], t2[3];
   TerrainBasis(ts, n, t1, t2);
@@ -338,6 +427,24 @@ __device__ __forceinline__ void ItemForce(const ItemCtx<L>& cx, const ItemC& it)
 #pragma unroll
     for (int i = 0; i < 5; ++i) gr[(i) * L::RS] = (f.p[0] * b[3 * i] + f.p[1] * b[3 * i + 1]) + f.p[2] * b[3 * i + 2];
   }
+  if constexpr (L::RT) {
+    // G + 15 = W_f[n_cols] | schedule[5][P-1] = b_i . J_f,dT (force_constraint_discretized.cc:190-220; the terrain-basis
+    // part is dropped where the terrain has no curvature, :58)
+    const int E = cx.n_ee;
+    const RtSpline sf = cx.T.rt_splines[E + it.ee];
+    WriteHermiteWeights<L::GS>(cx.T, sf, rf, G + 15 * L::GS);
+    double* Sc = G + (15 + sf.n_cols) * L::GS;
+    const RtFoot ft = cx.T.rt_feet[it.ee];
+    double dfT[3];
+    const int cur = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, rf, f.v, dfT);
+    const int nc = ft.n_phases - 1;
+    for (int j = 0; j < nc; ++j) {
+      double c[3];
+      DurationColumn(j, cur, ft.n_phases, dfT, f.v, c);
+#pragma unroll
+      for (int i = 0; i < 5; ++i) Sc[(i * nc + j) * L::GS] = (b[3 * i] * c[0] + b[3 * i + 1] * c[1]) + b[3 * i + 2] * c[2];
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------ torque (discretised)
@@ -345,9 +452,16 @@ __device__ __forceinline__ void ItemForce(const ItemCtx<L>& cx, const ItemC& it)
 template <class L>
 __device__ __forceinline__ void ItemTorque(const ItemCtx<L>& cx, const ItemC& it) {
   Pt3 p, f, tau;
-  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, p);
-  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 1, f);
-  EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 2, tau);
+  RtPoint rf, rt;
+  if constexpr (L::RT) {
+    EvalSplineRt<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0, p);
+    rf = EvalSplineRt<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0 + 1, f);
+    rt = EvalSplineRt<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0 + 2, tau);
+  } else {
+    EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, p);
+    EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 1, f);
+    EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 2, tau);
+  }
   const TerrainSample ts = EvalTerrain(cx.pc->terrain_id, p.p[0], p.p[1]);
   double n[3], t1[3], t2[3];
   TerrainBasis(ts, n, t1, t2);
@@ -370,6 +484,31 @@ __device__ __forceinline__ void ItemTorque(const ItemCtx<L>& cx, const ItemC& it
     gr[1 * L::RS] = tau_t2;
     gr[2 * L::RS] = tau_n - tz_lim;
     gr[3 * L::RS] = -tau_n - tz_lim;
+  }
+  if constexpr (L::RT) {
+    // G + 15 = W_tau | W_f | schedule[4][P-1] (torque_constraint_discretized.cc:222-234)
+    const int E = cx.n_ee;
+    const RtSpline sf = cx.T.rt_splines[E + it.ee], st = cx.T.rt_splines[2 * E + it.ee];
+    WriteHermiteWeights<L::GS>(cx.T, st, rt, G + 15 * L::GS);
+    WriteHermiteWeights<L::GS>(cx.T, sf, rf, G + (15 + st.n_cols) * L::GS);
+    double* Sc = G + (15 + st.n_cols + sf.n_cols) * L::GS;
+    const RtFoot ft = cx.T.rt_feet[it.ee];
+    double dtT[3], dfT[3];
+    const int cur_t = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, rt, tau.v, dtT);
+    const int cur_f = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, rf, f.v, dfT);
+    const int nc = ft.n_phases - 1;
+    for (int j = 0; j < nc; ++j) {
+      double ct[3], cf[3];
+      DurationColumn(j, cur_t, ft.n_phases, dtT, tau.v, ct);
+      DurationColumn(j, cur_f, ft.n_phases, dfT, f.v, cf);
+      const double bf[3] = {(-kf * mu) * n[0], (-kf * mu) * n[1], (-kf * mu) * n[2]};
+      Sc[(0 * nc + j) * L::GS] = (t1[0] * ct[0] + t1[1] * ct[1]) + t1[2] * ct[2];
+      Sc[(1 * nc + j) * L::GS] = (t2[0] * ct[0] + t2[1] * ct[1]) + t2[2] * ct[2];
+      const double a2 = (n[0] * ct[0] + n[1] * ct[1]) + n[2] * ct[2];
+      const double a3 = ((-n[0]) * ct[0] + (-n[1]) * ct[1]) + (-n[2]) * ct[2];
+      Sc[(2 * nc + j) * L::GS] = ((a2 + bf[0] * cf[0]) + bf[1] * cf[1]) + bf[2] * cf[2];
+      Sc[(3 * nc + j) * L::GS] = ((a3 + bf[0] * cf[0]) + bf[1] * cf[1]) + bf[2] * cf[2];
+    }
   }
 }
 
@@ -433,6 +572,18 @@ __device__ __forceinline__ void ItemSplineAcc(const ItemCtx<L>& cx, const ItemC&
   }
 }
 
+// TotalDurationConstraint (total_duration_constraint.cc:48-54): sum of the P-1 optimised durations of one foot
+template <class L>
+__device__ __forceinline__ void ItemTotalDuration(const ItemCtx<L>& cx, const ItemC& it) {
+  if (!cx.g) return;
+  if constexpr (L::RT) {
+    const RtFoot ft = cx.T.rt_feet[it.ee];
+    double s = 0.0;
+    for (int i = 0; i < ft.n_phases - 1; ++i) s += cx.pdur[(ft.phase0 + i) * L::NS];
+    cx.g[it.row * L::RS] = s;
+  }
+}
+
 template <class L>
 __device__ __forceinline__ void RunItem(const ItemCtx<L>& cx, const ItemC& it) {
   switch (it.type) {
@@ -450,6 +601,7 @@ __device__ __forceinline__ void RunItem(const ItemCtx<L>& cx, const ItemC& it) {
     case kItemBaseHeightNode: ItemHeightNode<L>(cx, it, 0.4); break;   // nlp_formulation.cc:597
     case kItemSwingNode: ItemSwingNode<L>(cx, it); break;
     case kItemSplineAcc: ItemSplineAcc<L>(cx, it); break;
+    case kItemTotalDuration: ItemTotalDuration<L>(cx, it); break;
     default: break;
   }
 }

@@ -55,7 +55,7 @@ __device__ __forceinline__ void LoadDescriptors(const uint32_t* __restrict__ ent
 
 // FULL: all P problem lanes of the group exist (no per-store predicate).
 // nf[p] accumulates value * 0 per problem lane: NaN exactly when a stored value is not finite (status bit 2).
-template <int P, bool FULL, int NT>
+template <int P, bool FULL, int NT, bool GG = false>
 __device__ __forceinline__ void StageB(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[kDescBatch],
                                        const double* G, const double* Bs, double* __restrict__ o, int nnz, int np,
                                        double (&nf)[P]) {
@@ -63,7 +63,17 @@ __device__ __forceinline__ void StageB(const uint32_t* __restrict__ ent, int lef
   const char* Gb = reinterpret_cast<const char*>(G);
   const char* Bb = reinterpret_cast<const char*>(Bs);
   auto emit = [&](uint32_t w, double* op) {              // descriptor: G byte offset (low 16), B byte offset (high 16)
-    const double bv = *reinterpret_cast<const double*>(Bb + (w >> 16));
+    double bv = 0.0;
+    double bw[P];                                         // GG entries: the second factor is a per-problem G slot
+    bool gg = false;
+    if constexpr (GG) gg = (w & 0x10000u) != 0;
+    if (!gg) {
+      bv = *reinterpret_cast<const double*>(Bb + (w >> 16));
+    } else {
+      const double* wa = reinterpret_cast<const double*>(Gb + ((w >> 16) & 0xFFF8u) * P);
+#pragma unroll
+      for (int p = 0; p < P; ++p) bw[p] = wa[p];
+    }
     const char* ga = Gb + (w & 0xFFFFu) * P;
     double gv[P];
     if constexpr (P == 1) {
@@ -78,7 +88,7 @@ __device__ __forceinline__ void StageB(const uint32_t* __restrict__ ent, int lef
     }
 #pragma unroll
     for (int p = 0; p < P; ++p) {
-      const double v = gv[p] * bv;
+      const double v = gv[p] * ((GG && gg) ? bw[p] : bv);
       nf[p] = fma(v, 0.0, nf[p]);
       if (FULL || p < np) op[static_cast<size_t>(p) * nnz] = v;
     }
@@ -113,7 +123,8 @@ __device__ __forceinline__ void CpAsync8(void* smem_dst, const void* gsrc, int s
 // P problems are evaluated in lock step by one CTA of 256*P threads: the class tables are held once per SM, every
 // stage spreads (item, problem) pairs over all threads, and in stage B one descriptor load and one B load feed the
 // P problems.  All per-problem shared arrays are interleaved (element i of problem p at [i*P + p]).
-template <int WHAT, int P>
+// RT: structure classes with optimised phase durations (stage D below; items.cuh Lockstep<P, true>).
+template <int WHAT, int P, bool RT>
 __global__ void __launch_bounds__(kThreads * P, 1)
 EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restrict__ pcs, const double* __restrict__ x,
            double* __restrict__ g_out, double* __restrict__ vals_out, int* __restrict__ status, int n_problems) {
@@ -123,7 +134,9 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
   const int nnv = Pg.blob.n_node_values, npoly = Pg.blob.n_polys;
   double* nodes = reinterpret_cast<double*>(blob + Pg.blob.bytes);
   double* coef = nodes + nnv * P;
-  double* G = coef + 6 * npoly * P;
+  double* rtd = coef + 6 * npoly * P;                   // RT: 5 per polynomial, then the phase durations
+  double* pdur = rtd + (RT ? 5 * npoly * P : 0);
+  double* G = pdur + (RT ? Pg.blob.n_pdur * P : 0);
   __shared__ ProblemConst pc_all[P];
   __shared__ int bad_all[P];
   const int tid = threadIdx.x;
@@ -135,7 +148,8 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
   }
   __syncthreads();
   TB_MARK_INIT
-  ItemCtx<Lockstep<P>> cx;
+  ItemCtx<Lockstep<P, RT>> cx;
+  cx.n_ee = Pg.n_ee;
   cx.T = MakeTables(blob, Pg.blob);
   const double* Bs = cx.T.B;
   const int pl = tid % P;                               // problem lane of this thread in stages N, C, A
@@ -160,6 +174,8 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
     cx.nodes = nodes + pl;
     cx.coef = coef + pl;
     cx.G = G + pl;
+    cx.rtd = rtd + pl;
+    cx.pdur = pdur + pl;
     cx.pc = &pc_all[pl];
     cx.g = (WHAT & TOWR_B200_EVAL_G) ? g_out + static_cast<size_t>(prob) * Pg.n_rows : nullptr;
     double nf[P];
@@ -172,21 +188,62 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
     __syncthreads();
     TB_MARK(1)
 
+    // ---- stage D (optimised durations): phase durations from x (phase_durations.cc:78-100: the last one is
+    // T - sum of the others), then every polynomial's duration T, T^2, T^3, 1/T^2, 1/T^3
+    // (ConvertPhaseToPolyDurations, nodes_variables_phase_based.cc:75-86; base splines keep their class constants)
+    if constexpr (RT) {
+      const double* xg = x + static_cast<size_t>(prob) * Pg.n_vars;
+      if (tid < Pg.blob.n_rt_feet * P) {
+        const RtFoot ft = cx.T.rt_feet[tid / P];
+        double sum = 0.0;
+        for (int i = 0; i < ft.n_phases - 1; ++i) {
+          const double d = __ldg(xg + ft.col0 + i);
+          nfx = fma(d, 0.0, nfx);
+          pdur[(ft.phase0 + i) * P + pl] = d;
+          sum += d;
+        }
+        pdur[(ft.phase0 + ft.n_phases - 1) * P + pl] = Pg.total_time - sum;
+      }
+      __syncthreads();
+      for (int i = tid; i < npoly * P; i += NT) {
+        const int poly = i / P;
+        const uint32_t pm = cx.T.poly_meta[poly];
+        double* o = rtd + poly * 5 * P + pl;
+        if (pm == kPolyFixed) {
+          const int di = cx.T.polys[poly] >> 16;
+          o[0] = cx.T.durs[3 * di]; o[P] = cx.T.durs[3 * di + 1]; o[2 * P] = cx.T.durs[3 * di + 2];
+          o[3 * P] = cx.T.rdurs[2 * di]; o[4 * P] = cx.T.rdurs[2 * di + 1];
+        } else {
+          const RtFoot ft = cx.T.rt_feet[pm >> 24];
+          const double Td = pdur[(ft.phase0 + (pm & 0xFF)) * P + pl] / static_cast<double>((pm >> 8) & 0xFF);
+          const double T2 = Td * Td, T3 = Cube(Td);
+          o[0] = Td; o[P] = T2; o[2 * P] = T3; o[3 * P] = 1.0 / T2; o[4 * P] = 1.0 / T3;
+        }
+      }
+      __syncthreads();
+    }
+
     // ---- stage C: c = -(3(p0-p1) + T(2 v0 + v1))/T^2, d = (2(p0-p1) + T(v0+v1))/T^3   (polynomial.cc:97-104)
     for (int i = tid; i < 3 * npoly * P; i += NT) {
       const int pd = i / P;                             // (poly, dim) pair; i % P == pl
       const int poly = pd / 3, d = pd - 3 * poly;
       const uint32_t pr = cx.T.polys[poly];
       const int n0 = pr & 0xFFFF;
-      const double* du = cx.T.durs + 3 * (pr >> 16);
-      const double* rd = cx.T.rdurs + 2 * (pr >> 16);
-      const double T = du[0], T2 = du[1], T3 = du[2];
+      double T, T2, T3, r2, r3;
+      if constexpr (RT) {
+        const double* o = rtd + poly * 5 * P + pl;
+        T = o[0]; T2 = o[P]; T3 = o[2 * P]; r2 = o[3 * P]; r3 = o[4 * P];
+      } else {
+        const double* du = cx.T.durs + 3 * (pr >> 16);
+        const double* rd = cx.T.rdurs + 2 * (pr >> 16);
+        T = du[0]; T2 = du[1]; T3 = du[2]; r2 = rd[0]; r3 = rd[1];
+      }
       const double* nd = nodes + pl;
       const double p0 = nd[(n0 * 6 + d) * P], v0 = nd[(n0 * 6 + 3 + d) * P];
       const double p1 = nd[(n0 * 6 + 6 + d) * P], v1 = nd[(n0 * 6 + 9 + d) * P];
       nfx = fma(p0, 0.0, fma(v0, 0.0, fma(p1, 0.0, fma(v1, 0.0, nfx))));   // NaN iff a node value is not finite
-      coef[(poly * 6 + d) * P + pl] = ExactDiv(-(3.0 * (p0 - p1) + T * (2.0 * v0 + v1)), T2, rd[0]);
-      coef[(poly * 6 + 3 + d) * P + pl] = ExactDiv(2.0 * (p0 - p1) + T * (v0 + v1), T3, rd[1]);
+      coef[(poly * 6 + d) * P + pl] = ExactDiv(-(3.0 * (p0 - p1) + T * (2.0 * v0 + v1)), T2, r2);
+      coef[(poly * 6 + 3 + d) * P + pl] = ExactDiv(2.0 * (p0 - p1) + T * (v0 + v1), T3, r3);
     }
     TB_MARK(2)
     __syncthreads();
@@ -195,14 +252,14 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
     for (int s = 0; s < Pg.n_segments; ++s) {
       const SegmentRec sg = cx.T.segments[s];
       // ---- stage A, level 0 then level 1: thread -> (item, problem lane)
-      if (tid < P) { G[kGOne * P + tid] = 1.0; G[kGMass * P + tid] = pc_all[tid].mass; }
-      for (int i = tid; i < sg.n_items0 * P; i += NT) RunItem<Lockstep<P>>(cx, cx.T.items[sg.item0 + i / P]);
+      if (tid < P) { G[kGOne * P + tid] = 1.0; G[kGMass * P + tid] = pc_all[tid].mass; G[kGMinusOne * P + tid] = -1.0; }
+      for (int i = tid; i < sg.n_items0 * P; i += NT) RunItem<Lockstep<P, RT>>(cx, cx.T.items[sg.item0 + i / P]);
       TB_MARK(8 + 6 * s)
       if (sg.n_items > sg.n_items0) {
         __syncthreads();
         TB_MARK(9 + 6 * s)
         for (int i = tid; i < (sg.n_items - sg.n_items0) * P; i += NT)
-          RunItem<Lockstep<P>>(cx, cx.T.items[sg.item0 + sg.n_items0 + i / P]);
+          RunItem<Lockstep<P, RT>>(cx, cx.T.items[sg.item0 + sg.n_items0 + i / P]);
         TB_MARK(10 + 6 * s)
       }
       // first descriptor batch of stage B: issued before the barrier, consumed after it
@@ -217,9 +274,9 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
       if (WHAT & TOWR_B200_EVAL_JAC) {
         double* o0 = vals_out + static_cast<size_t>(base) * Pg.nnz + sg.entry0 + tid;
         if (n_problems - base >= P)
-          StageB<P, true, NT>(ent, sg.n_entries - tid, d0, G, Bs, o0, Pg.nnz, P, nf);
+          StageB<P, true, NT, RT>(ent, sg.n_entries - tid, d0, G, Bs, o0, Pg.nnz, P, nf);
         else
-          StageB<P, false, NT>(ent, sg.n_entries - tid, d0, G, Bs, o0, Pg.nnz, n_problems - base, nf);
+          StageB<P, false, NT, RT>(ent, sg.n_entries - tid, d0, G, Bs, o0, Pg.nnz, n_problems - base, nf);
       }
       TB_MARK(12 + 6 * s)
       __syncthreads();
@@ -275,6 +332,9 @@ EvalKernelWS(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __res
     // ------------------------------------------------------------------------------------------ producers
     ItemCtx<Lockstep<P>> cx;
     cx.T = T;
+    cx.n_ee = Pg.n_ee;
+    cx.rtd = nullptr;
+    cx.pdur = nullptr;
     const int pl = tid % P;
     auto fetch_group = [&](int base_n) {
       const double* xn = x + static_cast<size_t>(min(base_n + pl, n_problems - 1)) * Pg.n_vars;
@@ -321,7 +381,7 @@ EvalKernelWS(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __res
         if (k >= 2) BarSync(kBarEmpty + buf, NALL);       // the consumers are done with this buffer
         TB_MARK(2)
         cx.G = G + pl;
-        if (tid < P) { G[kGOne * P + tid] = 1.0; G[kGMass * P + tid] = pc_all[tid].mass; }
+        if (tid < P) { G[kGOne * P + tid] = 1.0; G[kGMass * P + tid] = pc_all[tid].mass; G[kGMinusOne * P + tid] = -1.0; }
         for (int i = tid; i < sg.n_items0 * P; i += NA) RunItem<Lockstep<P>>(cx, T.items[sg.item0 + i / P]);
         TB_MARK(3)
         if (sg.n_items > sg.n_items0) {
@@ -413,25 +473,27 @@ cudaError_t LaunchEvalWS(const DeviceProgram& P, const ProblemConst* pcs, int wh
 }
 
 bool EvalFitsWS(const DeviceProgram& P, int lanes, size_t smem_optin) {
-  if (lanes != 2) return false;
+  if (lanes != 2 || P.blob.rt) return false;   // optimised durations run on the lock-step kernel
   const size_t smem = EvalSharedBytesWS(P, lanes) + 1024;   // static shared memory of the kernel
   return smem <= smem_optin;
 }
 
 size_t EvalSharedBytes(const DeviceProgram& P, int lanes) {
+  const size_t rt = P.blob.rt ? 5 * static_cast<size_t>(P.blob.n_polys) + P.blob.n_pdur : 0;
   return static_cast<size_t>(P.blob.bytes) + sizeof(double) * lanes *
-         (static_cast<size_t>(P.blob.n_node_values) + 6 * static_cast<size_t>(P.blob.n_polys) + P.g_capacity);
+         (static_cast<size_t>(P.blob.n_node_values) + 6 * static_cast<size_t>(P.blob.n_polys) + rt + P.g_capacity);
 }
 
 template <int WHAT, int LANES>
 static cudaError_t LaunchT(const DeviceProgram& P, const ProblemConst* pcs, const double* x, double* g, double* vals,
                            int* status, int n_problems, int max_ctas, cudaStream_t stream) {
   const size_t smem = EvalSharedBytes(P, LANES);
-  cudaError_t err = cudaFuncSetAttribute(EvalKernel<WHAT, LANES>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+  auto kern = P.blob.rt ? EvalKernel<WHAT, LANES, true> : EvalKernel<WHAT, LANES, false>;
+  cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
   if (err != cudaSuccess) return err;
   int grid = (n_problems + LANES - 1) / LANES;
   if (grid > max_ctas) grid = max_ctas;
-  EvalKernel<WHAT, LANES><<<grid, kThreads * LANES, smem, stream>>>(P, pcs, x, g, vals, status, n_problems);
+  kern<<<grid, kThreads * LANES, smem, stream>>>(P, pcs, x, g, vals, status, n_problems);
   return cudaGetLastError();
 }
 
@@ -462,9 +524,12 @@ int EvalOccupancy(const DeviceProgram& P, int lanes) {
   const size_t smem = EvalSharedBytes(P, lanes);
   cudaError_t e = cudaErrorInvalidValue;
 #define TB_OCC(L)                                                                                                   \
-  if (cudaFuncSetAttribute(EvalKernel<3, L>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != \
-      cudaSuccess) { cudaGetLastError(); return 0; }                                                                \
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, EvalKernel<3, L>, kThreads * L, smem);
+  {                                                                                                                 \
+    auto kern = P.blob.rt ? EvalKernel<3, L, true> : EvalKernel<3, L, false>;                                       \
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) !=          \
+        cudaSuccess) { cudaGetLastError(); return 0; }                                                              \
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, kThreads * L, smem);                                \
+  }
   if (lanes == 1) { TB_OCC(1) } else if (lanes == 2) { TB_OCC(2) } else if (lanes == 4) { TB_OCC(4) }
 #undef TB_OCC
   if (e != cudaSuccess) { cudaGetLastError(); return 0; }

@@ -234,6 +234,28 @@ void BuildLayout(const towr_b200_spec& s, HostProgram& hp) {
   }
   hp.n_vars = col;
   hp.n_node_values = node_slot * 6;
+
+  // runtime tables of the PhaseSpline path
+  hp.rt_splines.clear();
+  hp.rt_feet.clear();
+  hp.poly_meta.assign(hp.polys.size(), kPolyFixed);
+  if (hp.optimize_durations) {
+    const int kinds[3] = {kEEMotion, kEEForce, kEETorque};
+    hp.rt_splines.resize(3 * static_cast<size_t>(E));
+    for (int k = 0; k < 3; ++k)
+      for (int e = 0; e < E; ++e) {
+        const VarSet& v = *hp.Find(kinds[k], e);
+        hp.rt_splines[k * E + e] = RtSpline{v.poly0, v.n_polys(), v.col0, v.n_vars};
+        for (int pl = 0; pl < v.n_polys(); ++pl)
+          hp.poly_meta[v.poly0 + pl] = static_cast<uint32_t>(v.poly_phase[pl]) | (static_cast<uint32_t>(v.polys_in_phase[pl]) << 8) |
+                                       (static_cast<uint32_t>(v.poly_in_phase[pl]) << 16) | (static_cast<uint32_t>(e) << 24);
+      }
+    int phase0 = 0;
+    for (int e = 0; e < E; ++e) {
+      hp.rt_feet.push_back(RtFoot{phase0, s.n_phases[e], hp.Find(kEESchedule, e)->col0, 0});
+      phase0 += s.n_phases[e];
+    }
+  }
 }
 
 }  // namespace tb

@@ -37,8 +37,10 @@ void PackProgram(HostProgram& hp) {
   auto add_sample = [&](int wide) {
     const SampleRec& r = hp.samples.at(wide);
     int t = intern(time_ix, times, r.t, r.t2, r.t3);
-    if (r.poly > 0xFFFF || t > 0xFFFF) throw std::runtime_error("unsupported: too many polynomials or sample times");
-    samples.push_back(static_cast<uint32_t>(r.poly) | (static_cast<uint32_t>(t) << 16));
+    // runtime samples of a PhaseSpline (optimised durations): poly = -(1 + RtSpline index), t = global time
+    const int lo = r.poly < 0 ? -r.poly - 1 : r.poly;
+    if (lo > 0xFFFF || t > 0xFFFF) throw std::runtime_error("unsupported: too many polynomials or sample times");
+    samples.push_back(static_cast<uint32_t>(lo) | (static_cast<uint32_t>(t) << 16));
   };
   std::vector<ItemC> items;
   std::vector<std::array<int, 3>> kind;   // (level, type, sub) per compact item
@@ -143,6 +145,14 @@ void PackProgram(HostProgram& hp) {
   place(L.off_samples, 4 * L.n_samples);
   place(L.off_polys, 4 * L.n_polys);
   place(L.off_node_src, 2 * L.n_node_values);
+  L.rt = hp.optimize_durations ? 1 : 0;
+  L.n_rt_splines = static_cast<int>(hp.rt_splines.size());
+  L.n_rt_feet = static_cast<int>(hp.rt_feet.size());
+  L.n_pdur = 0;
+  for (const RtFoot& f : hp.rt_feet) L.n_pdur += f.n_phases;
+  place(L.off_rt_splines, static_cast<int>(sizeof(RtSpline)) * L.n_rt_splines);
+  place(L.off_rt_feet, static_cast<int>(sizeof(RtFoot)) * L.n_rt_feet);
+  place(L.off_poly_meta, 4 * L.n_polys);
   L.bytes = off;
   hp.blob_data.assign(off, 0);
   unsigned char* d = hp.blob_data.data();
@@ -157,6 +167,9 @@ void PackProgram(HostProgram& hp) {
   std::memcpy(d + L.off_items, items.data(), 16 * items.size());
   std::memcpy(d + L.off_samples, samples.data(), 4 * samples.size());
   std::memcpy(d + L.off_polys, polys.data(), 4 * polys.size());
+  if (!hp.rt_splines.empty()) std::memcpy(d + L.off_rt_splines, hp.rt_splines.data(), sizeof(RtSpline) * hp.rt_splines.size());
+  if (!hp.rt_feet.empty()) std::memcpy(d + L.off_rt_feet, hp.rt_feet.data(), sizeof(RtFoot) * hp.rt_feet.size());
+  std::memcpy(d + L.off_poly_meta, hp.poly_meta.data(), 4 * hp.poly_meta.size());
   uint16_t* ns = reinterpret_cast<uint16_t*>(d + L.off_node_src);
   for (int i = 0; i < hp.n_node_values; ++i) ns[i] = hp.node_src[i] < 0 ? 0xFFFF : static_cast<uint16_t>(hp.node_src[i]);
 
@@ -164,9 +177,9 @@ void PackProgram(HostProgram& hp) {
   hp.entries_dev.clear();
   hp.entries_dev.reserve(hp.entries.size());
   for (uint32_t w : hp.entries) {
-    uint32_t g8 = (w & 0xFFFF) * 8, b8 = (w >> 16) * 8;
+    uint32_t g8 = (w & 0xFFFF) * 8, b8 = ((w >> 16) & 0x7FFF) * 8;
     if (g8 > 0xFFFF || b8 > 0xFFFF) throw std::runtime_error("unsupported: G or B table beyond 8191 entries");
-    hp.entries_dev.push_back(g8 | (b8 << 16));
+    hp.entries_dev.push_back(g8 | ((b8 | ((w & kEntryGG) ? 1u : 0u)) << 16));
   }
 }
 

@@ -65,9 +65,17 @@ inline int ItemLevel(int type) { return type >= kItemDynWrench && type != kItemN
 enum { kDpV = 0, kDpA = 3, kDpTrig = 6, kDpR = 12, kDpRI = 21, kDpIw = 30, kDpM = 39, kDpMd = 44, kDpW = 49, kDpWd = 52,
        kDpIww = 55, kDpV11 = 58, kDpV21 = 61, kDynPreSize = 64 };
 enum { kRpLin = 0, kRpR = 3, kRpDR = 12, kRomPreSize = 39 };
+#ifdef __CUDACC__
+#define TB_PHD __host__ __device__
+#else
+#define TB_PHD
+#endif
 // G layout of a dynamic sample: finished base-ang block, finished base-lin angular block, f_e[3E], (c - p_e)[3E],
 // then scratch: per-foot torque terms [3E], DynPre block
 enum { kDynJang = 0, kDynJlin = 36, kDynF = 72 };
+// optimised durations: -f_e[3E], -(c - p_e)[3E] follow the fixed-duration block, then one block per foot (ItemC::aux of
+// the foot's DynFoot item): W_p | W_f | W_tau | finished ee-schedule block [6][P-1]
+TB_PHD inline int DynNegOffset(int E) { return (72 + 9 * E + kDynPreSize) | 1; }
 
 constexpr int kMaxEE = 4;
 // indices into ItemRec::s
@@ -86,9 +94,11 @@ struct ItemRec {
   int s[kSCount];       // SampleRec indices; node-based items: node slot / polynomial index in s[0]
 };
 
-// one stored Jacobian entry, in storage (row-major) order: G slot (low 16 bits) | B index (high 16 bits);
-// the device copy (pack.cc) holds BYTE offsets (slot*8, index*8) so that stage B needs no shifts
+// one stored Jacobian entry, in storage (row-major) order: G slot (low 16 bits) | B index (bits 16..30);
+// bit 31 (kEntryGG): the second factor is a G slot as well (runtime Hermite weights of a PhaseSpline column, classes
+// with optimised durations).  The device copy (pack.cc) holds BYTE offsets (slot*8, index*8), the flag in bit 16.
 using EntryRec = uint32_t;
+constexpr uint32_t kEntryGG = 0x80000000u;
 
 // The device copy of the descriptors (HostProgram::entries_dev) is in storage order too: thread t of stage B takes
 // entries t, t + blockDim, ... of its segment, so a warp's descriptor load and its P stores are all coalesced.
@@ -103,7 +113,7 @@ struct SegmentRec {
 };
 
 // slots 0.. of every segment's G buffer
-enum { kGOne = 0, kGMass = 1, kGReserved = 2 };
+enum { kGOne = 0, kGMass = 1, kGMinusOne = 2, kGReserved = 3 };
 
 // ---- compact class tables: one byte blob per structure class, copied into shared memory once per CTA so that
 // stage A never touches global memory (with ~200 KB of shared memory in use per SM the L1 is almost gone and every
@@ -118,6 +128,21 @@ struct ItemC {          // 16 bytes
 // compact sample = polynomial index | time index << 16 ; compact polynomial = node slot | duration index << 16
 // sample order of an item: DynPre [ang], DynFoot [lin, motion, force, torque], DynWrench [lin], RomPre [lin, ang],
 // RomFoot [motion], Force [motion, force], Torque [motion, force, torque], BaseRom [lin, ang]
+// ---- classes with optimised phase durations (PhaseSpline path, phase_spline.cc / phase_durations.cc): which
+// polynomial a sample time falls into, its local time and the Hermite weights are per-problem quantities
+struct RtSpline {       // one PhaseSpline: index kind*E + foot, kind 0 = ee-motion, 1 = ee-force, 2 = ee-torque
+  int poly0, n_polys;   // global polynomial range
+  int col0, n_cols;     // its variable set's columns
+};
+struct RtFoot {         // one PhaseDurations set
+  int phase0, n_phases; // offset into the per-problem phase-duration array; P
+  int col0;             // first ee-schedule column (P - 1 of them)
+  int pad;
+};
+// per global polynomial: phase | polys_in_phase << 8 | prev_polys_in_phase << 16 | foot << 24 ; kPolyFixed for the
+// base splines (class-constant duration)
+constexpr uint32_t kPolyFixed = 0xFFFFFFFFu;
+
 struct BlobLayout {     // byte offsets into the blob (all 16-byte aligned), element counts
   int bytes;
   int off_B, n_B;                 // double
@@ -129,12 +154,18 @@ struct BlobLayout {     // byte offsets into the blob (all 16-byte aligned), ele
   int off_samples, n_samples;     // uint32
   int off_polys, n_polys;         // uint32
   int off_node_src, n_node_values;// uint16, 0xFFFF = pinned to zero
+  int off_rt_splines, n_rt_splines;   // RtSpline (3 * n_ee, optimised durations only)
+  int off_rt_feet, n_rt_feet;         // RtFoot
+  int off_poly_meta;                  // uint32 per polynomial
+  int n_pdur;                         // phase durations per problem (sum of n_phases)
+  int rt;                             // 1: optimised durations
 };
 
 struct DeviceProgram {  // pointers into device memory (one copy per GPU)
   int n_vars, n_rows, nnz, n_ee;
   int n_segments;
   int g_capacity;       // max g_size over segments
+  double total_time;
   BlobLayout blob;
   const unsigned char* blob_data;
   const uint32_t* entries;   // G byte offset | B byte offset << 16, storage order
@@ -196,6 +227,9 @@ struct HostProgram {
   std::vector<EntryRec> entries;
   std::vector<double> B;
   std::vector<SegmentRec> segments;
+  std::vector<RtSpline> rt_splines;
+  std::vector<RtFoot> rt_feet;
+  std::vector<uint32_t> poly_meta;
   // packed for the device (pack.cc)
   BlobLayout blob{};
   std::vector<unsigned char> blob_data;

@@ -64,7 +64,7 @@ double LocalTime(double t_global, int id, const std::vector<double>& durations) 
 
 namespace {
 
-struct Term { int g = 0, b = 0; };                // value = G[g] * B[b]
+struct Term { int g = 0, b = 0; bool gg = false; };   // value = G[g] * B[b], or G[g] * G[b] when gg (runtime weights)
 struct ColBasis { int idx, dim; double v[3]; int sd; };   // v[dx]: d{pos,vel,acc}/d(variable idx); sd = side*2+deriv of the last hit
 struct SplineAt { int sample; int poly; double t_local; };
 
@@ -111,6 +111,35 @@ class Builder {
     a.sample = static_cast<int>(hp_.samples.size());
     hp_.samples.push_back(r);
     return a;
+  }
+  // optimised durations: a PhaseSpline sample is resolved per problem on the device; kind_idx 0 motion, 1 force, 2 torque
+  bool rt() const { return hp_.optimize_durations; }
+  int AtRt(int kind_idx, int ee, double t_global) {
+    SampleRec r;
+    r.poly = -(1 + kind_idx * s_.n_ee + ee);
+    r.pad = 0;
+    r.t = t_global;
+    r.t2 = 0.0;
+    r.t3 = 0.0;
+    hp_.samples.push_back(r);
+    return static_cast<int>(hp_.samples.size()) - 1;
+  }
+  // PhaseSpline's pre-filled structure (phase_spline.cc:45-51): every variable of the set, with its dimension
+  static std::vector<std::pair<int, int>> AllCols(const VarSet& set) {
+    std::vector<std::pair<int, int>> c;
+    for (int idx = 0; idx < set.n_vars; ++idx) c.emplace_back(idx, set.refs[idx].front().dim);
+    return c;
+  }
+  Term GG(int g, int w) const { Term t; t.g = g; t.b = w; t.gg = true; return t; }
+  // the finished ee-schedule block of one item: rows x (P-1) values at slot0 + r * (P-1) + j
+  void AddScheduleBlock(int row0_local, int n_rows, int ee, int slot0) {
+    const VarSet& sc = Set(kEESchedule, ee);
+    const int one = AddB(1.0);
+    for (int r = 0; r < n_rows; ++r)
+      for (int j = 0; j < sc.n_vars; ++j) {
+        Term tm; tm.g = slot0 + r * sc.n_vars + j; tm.b = one;
+        Add(row0_local + r, sc.col0 + j, tm);
+      }
   }
   // stored columns of NodeSpline::GetJacobianWrtNodes(poly, t_local, *) with their values for all three dx
   // (node_spline.cc:84-112): ascending idx, start side before end side, contributions added from 0.0
@@ -192,8 +221,8 @@ class Builder {
       std::stable_sort(row.begin(), row.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
       for (auto& e : row) {
         const Term& t = e.second;
-        if (t.g < 0 || t.g > 65535 || t.b < 0 || t.b > 65535) throw std::runtime_error("entry descriptor out of range");
-        EntryRec er = static_cast<uint32_t>(t.g) | (static_cast<uint32_t>(t.b) << 16);
+        if (t.g < 0 || t.g > 65535 || t.b < 0 || t.b > 32767) throw std::runtime_error("entry descriptor out of range");
+        EntryRec er = static_cast<uint32_t>(t.g) | (static_cast<uint32_t>(t.b) << 16) | (t.gg ? kEntryGG : 0u);
         hp_.entries.push_back(er);
         hp_.pat_rows.push_back(set_row0_ + r);
         hp_.pat_cols.push_back(e.first);
@@ -227,6 +256,8 @@ class Builder {
   void EmitForceDisc(int ee);
   void EmitTorqueDisc(int ee);
   void EmitBaseRom();
+  void EmitRomRt();
+  void EmitTotalDuration(int ee);
   void EmitSwing(int ee);
   void EmitBaseHeight();
   void EmitHeightRows(const VarSet& set, int item_type, int ee);
@@ -299,7 +330,17 @@ void Builder::EmitDynamic() {
   const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_dynamic);
   const int one = AddB(1.0);
   // odd, so that the same slot of neighbouring samples (threads of one warp) falls into different shared-memory banks
-  const int per_sample = (72 + 9 * E + kDynPreSize) | 1;
+  int per_sample = (72 + 9 * E + kDynPreSize) | 1;
+  std::vector<int> foot_block(E, 0);                     // optimised durations: offset of each foot's block in the sample
+  if (rt()) {
+    per_sample = DynNegOffset(E) + 6 * E;
+    for (int e = 0; e < E; ++e) {
+      foot_block[e] = per_sample;
+      per_sample += Set(kEEMotion, e).n_vars + Set(kEEForce, e).n_vars + Set(kEETorque, e).n_vars +
+                    6 * Set(kEESchedule, e).n_vars;
+    }
+    per_sample |= 1;
+  }
   const int chunk = std::max(1, 1024 / per_sample);      // samples per group
   for (size_t k = 0; k < ts.size(); ++k) {
     const double t = ts[k];
@@ -344,6 +385,33 @@ void Builder::EmitDynamic() {
       const VarSet& mo = Set(kEEMotion, e);
       const VarSet& fo = Set(kEEForce, e);
       const VarSet& to = Set(kEETorque, e);
+      if (rt()) {
+        // every column of the three PhaseSplines (pre-filled structure), weights written by the foot's DynFoot item
+        it.s[kSMotion + e] = AtRt(0, e, t);
+        it.s[kSForce + e] = AtRt(1, e, t);
+        it.s[kSTorque + e] = AtRt(2, e, t);
+        const int gNegF = g0 + DynNegOffset(E), gNegR = gNegF + 3 * E;
+        const int wP = g0 + foot_block[e], wF = wP + mo.n_vars, wT = wF + fo.n_vars, sched = wT + to.n_vars;
+        for (auto& c : AllCols(mo))
+          for (int r = 0; r < 3; ++r) {
+            if (r == c.second) continue;
+            int kk; double sg;
+            CrossEntry(r, c.second, &kk, &sg);
+            Add(r0 + r, mo.col0 + c.first, GG((sg > 0 ? gF : gNegF) + 3 * e + kk, wP + c.first));
+          }
+        for (auto& c : AllCols(fo)) {
+          for (int r = 0; r < 3; ++r) {
+            if (r == c.second) continue;
+            int kk; double sg;
+            CrossEntry(r, c.second, &kk, &sg);
+            Add(r0 + r, fo.col0 + c.first, GG((sg > 0 ? gR : gNegR) + 3 * e + kk, wF + c.first));
+          }
+          Add(r0 + 3 + c.second, fo.col0 + c.first, GG(kGMinusOne, wF + c.first));
+        }
+        for (auto& c : AllCols(to)) Add(r0 + c.second, to.col0 + c.first, GG(kGMinusOne, wT + c.first));
+        AddScheduleBlock(r0, 6, e, sched);
+        continue;
+      }
       SplineAt am = At(mo, t), af = At(fo, t), at = At(to, t);
       it.s[kSMotion + e] = am.sample;
       it.s[kSForce + e] = af.sample;
@@ -383,6 +451,7 @@ void Builder::EmitDynamic() {
       ItemRec foot = it;
       foot.type = kItemDynFoot;
       foot.ee = static_cast<short>(e);
+      if (rt()) foot.aux = g0 + foot_block[e];
       hp_.items.push_back(foot);
     }
     hp_.items.push_back(it);
@@ -489,7 +558,9 @@ void Builder::EmitForceDisc(int ee) {
   const VarSet& mo = Set(kEEMotion, ee);
   const VarSet& fo = Set(kEEForce, ee);
   const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_force);
-  const int chunk = 64;                             // samples per group (15 G slots each)
+  // G slots per sample: 15, plus with optimised durations W_f[n_cols] and the finished ee-schedule block [5][P-1]
+  const int per_item = (15 + (rt() ? fo.n_vars + 5 * Set(kEESchedule, ee).n_vars : 0)) | 1;
+  const int chunk = std::max(1, 960 / per_item);    // samples per group
   for (size_t k = 0; k < ts.size(); ++k) {
     if (k % chunk == 0) {
       if (k == 0) { BeginGroup(); BeginSet("force-disc-" + fo.name, static_cast<int>(ts.size()) * 5); }
@@ -498,13 +569,23 @@ void Builder::EmitForceDisc(int ee) {
     ItemRec it = NewItem(kItemForce);
     it.ee = static_cast<short>(ee);
     it.row[0] = set_row0_ + static_cast<int>(k) * 5;
-    it.gslot = AllocG(15);
+    it.gslot = AllocG(per_item);
+    const int bk[5] = {kBoundForceNormal, kBoundLE0, kBoundGE0, kBoundLE0, kBoundGE0};
+    for (int i = 0; i < 5; ++i) Bound(static_cast<int>(k) * 5 + i, bk[i], ee);
+    if (rt()) {
+      it.s[kSMotion + ee] = AtRt(0, ee, ts[k]);
+      it.s[kSForce + ee] = AtRt(1, ee, ts[k]);
+      hp_.items.push_back(it);
+      for (auto& c : AllCols(fo))
+        for (int i = 0; i < 5; ++i)
+          Add(static_cast<int>(k) * 5 + i, fo.col0 + c.first, GG(it.gslot + 3 * i + c.second, it.gslot + 15 + c.first));
+      AddScheduleBlock(static_cast<int>(k) * 5, 5, ee, it.gslot + 15 + fo.n_vars);
+      continue;
+    }
     SplineAt am = At(mo, ts[k]), af = At(fo, ts[k]);
     it.s[kSMotion + ee] = am.sample;
     it.s[kSForce + ee] = af.sample;
     hp_.items.push_back(it);
-    const int bk[5] = {kBoundForceNormal, kBoundLE0, kBoundGE0, kBoundLE0, kBoundGE0};
-    for (int i = 0; i < 5; ++i) Bound(static_cast<int>(k) * 5 + i, bk[i], ee);
     for (const ColBasis& c : Columns(fo, af.poly, af.t_local))
       for (int i = 0; i < 5; ++i) {              // b_i . J_f
         Term tm; tm.g = it.gslot + 3 * i + c.dim; tm.b = AddB(c.v[0]);
@@ -516,6 +597,77 @@ void Builder::EmitForceDisc(int ee) {
   EndSet();
 }
 
+// RangeOfMotionConstraint with optimised durations: the ee-motion block stores every column of the set (weights written
+// by the RomFoot item) and the ee-schedule block is finished by the item.  The sets are split into sample groups, so
+// every foot's set carries its own RomPre items.
+void Builder::EmitRomRt() {
+  const int E = s_.n_ee;
+  const VarSet& lin = Set(kBaseLin);
+  const VarSet& ang = Set(kBaseAng);
+  const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_range_of_motion);
+  const int K = static_cast<int>(ts.size());
+  for (int e = 0; e < E; ++e) {
+    const VarSet& mo = Set(kEEMotion, e);
+    const int nsched = Set(kEESchedule, e).n_vars;
+    const int foot_size = (9 + mo.n_vars + 3 * nsched) | 1;
+    const int chunk = std::max(1, 960 / (kRomPreSize + foot_size));
+    for (int k = 0; k < K; ++k) {
+      if (k % chunk == 0) {
+        if (k == 0) { BeginGroup(); BeginSet("rangeofmotion-" + std::to_string(e), 3 * K); }
+        else BeginGroup(3 * k);
+      }
+      ItemRec pre = NewItem(kItemRomPre);
+      pre.gslot = AllocG(kRomPreSize);
+      SplineAt al = At(lin, ts[k]), aa = At(ang, ts[k]);
+      pre.s[kSBaseLin] = al.sample;
+      pre.s[kSBaseAng] = aa.sample;
+      hp_.items.push_back(pre);
+      ItemRec it = NewItem(kItemRomFoot);
+      it.ee = static_cast<short>(e);
+      it.row[0] = set_row0_ + 3 * k;
+      it.aux = pre.gslot;
+      it.gslot = AllocG(foot_size);
+      it.s[kSMotion + e] = AtRt(0, e, ts[k]);
+      hp_.items.push_back(it);
+      for (int r = 0; r < 3; ++r) Bound(3 * k + r, kBoundRom, e, r);
+      const int gR = pre.gslot + kRpR, gD = it.gslot;
+      for (const ColBasis& c : Columns(lin, al.poly, al.t_local))
+        for (int r = 0; r < 3; ++r) {
+          Term tm; tm.g = gR + c.dim * 3 + r; tm.b = AddB(-c.v[0]);
+          Add(3 * k + r, lin.col0 + c.idx, tm);
+        }
+      for (const ColBasis& c : Columns(ang, aa.poly, aa.t_local))
+        for (int r = 0; r < 3; ++r) {
+          if (r == 0 && c.dim == 0) continue;
+          Term tm; tm.g = gD + 3 * r + c.dim; tm.b = AddB(c.v[0]);
+          Add(3 * k + r, ang.col0 + c.idx, tm);
+        }
+      for (auto& c : AllCols(mo))
+        for (int r = 0; r < 3; ++r) Add(3 * k + r, mo.col0 + c.first, GG(gR + c.second * 3 + r, it.gslot + 9 + c.first));
+      AddScheduleBlock(3 * k, 3, e, it.gslot + 9 + mo.n_vars);
+    }
+    EndSet();
+  }
+}
+
+// TotalDurationConstraint (total_duration_constraint.cc:36-72): one row per foot, 1.0 in every ee-schedule column
+void Builder::EmitTotalDuration(int ee) {
+  const VarSet& sc = Set(kEESchedule, ee);
+  BeginGroup();
+  BeginSet("totalduration-" + std::to_string(ee), 1);
+  ItemRec it = NewItem(kItemTotalDuration);
+  it.ee = static_cast<short>(ee);
+  it.row[0] = set_row0_;
+  hp_.items.push_back(it);
+  Bound(0, kBoundTotalDuration, ee);
+  const int one = AddB(1.0);
+  for (int j = 0; j < sc.n_vars; ++j) {
+    Term tm; tm.g = kGOne; tm.b = one;
+    Add(0, sc.col0 + j, tm);
+  }
+  EndSet();
+}
+
 // TorqueConstraintDiscretized (torque_constraint_discretized.cc:103-235): 4 rows per sample; G slots t1, t2, n, -n,
 // (-k mu) n.  The ee-motion block exists only where the terrain has curvature (same rule as the force constraint).
 void Builder::EmitTorqueDisc(int ee) {
@@ -523,7 +675,8 @@ void Builder::EmitTorqueDisc(int ee) {
   const VarSet& fo = Set(kEEForce, ee);
   const VarSet& to = Set(kEETorque, ee);
   const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_torque);
-  const int chunk = 64;
+  const int per_item = (15 + (rt() ? to.n_vars + fo.n_vars + 4 * Set(kEESchedule, ee).n_vars : 0)) | 1;
+  const int chunk = std::max(1, 960 / per_item);
   const int bk_friction = AddB(s_.torque_k_friction);
   for (size_t k = 0; k < ts.size(); ++k) {
     const int r0 = static_cast<int>(k) * 4;
@@ -534,17 +687,30 @@ void Builder::EmitTorqueDisc(int ee) {
     ItemRec it = NewItem(kItemTorque);
     it.ee = static_cast<short>(ee);
     it.row[0] = set_row0_ + r0;
-    it.gslot = AllocG(15);
+    it.gslot = AllocG(per_item);
     it.b0 = bk_friction;
+    Bound(r0 + 0, kBoundTorqueX, ee);
+    Bound(r0 + 1, kBoundTorqueY, ee);
+    Bound(r0 + 2, kBoundLE0, ee);
+    Bound(r0 + 3, kBoundLE0, ee);
+    if (rt()) {
+      it.s[kSMotion + ee] = AtRt(0, ee, ts[k]);
+      it.s[kSForce + ee] = AtRt(1, ee, ts[k]);
+      it.s[kSTorque + ee] = AtRt(2, ee, ts[k]);
+      hp_.items.push_back(it);
+      const int wT = it.gslot + 15, wF = wT + to.n_vars;
+      for (auto& c : AllCols(to))
+        for (int i = 0; i < 4; ++i) Add(r0 + i, to.col0 + c.first, GG(it.gslot + 3 * i + c.second, wT + c.first));
+      for (auto& c : AllCols(fo))
+        for (int i = 2; i < 4; ++i) Add(r0 + i, fo.col0 + c.first, GG(it.gslot + 12 + c.second, wF + c.first));
+      AddScheduleBlock(r0, 4, ee, wF + fo.n_vars);
+      continue;
+    }
     SplineAt am = At(mo, ts[k]), af = At(fo, ts[k]), at = At(to, ts[k]);
     it.s[kSMotion + ee] = am.sample;
     it.s[kSForce + ee] = af.sample;
     it.s[kSTorque + ee] = at.sample;
     hp_.items.push_back(it);
-    Bound(r0 + 0, kBoundTorqueX, ee);
-    Bound(r0 + 1, kBoundTorqueY, ee);
-    Bound(r0 + 2, kBoundLE0, ee);
-    Bound(r0 + 3, kBoundLE0, ee);
     for (const ColBasis& c : Columns(to, at.poly, at.t_local))
       for (int i = 0; i < 4; ++i) {              // t1, t2, n, -n . J_tau
         Term tm; tm.g = it.gslot + 3 * i + c.dim; tm.b = AddB(c.v[0]);
@@ -623,7 +789,6 @@ void Builder::EmitSwing(int ee) {
 }
 
 void Builder::Run() {
-  if (hp_.optimize_durations) throw std::runtime_error("unsupported: optimised phase durations (PhaseSpline path)");
   hp_.n_rows = 0;
   for (int i = 0; i < s_.n_constraints; ++i) {
     switch (s_.constraints[i]) {
@@ -632,7 +797,7 @@ void Builder::Run() {
         break;
       case TOWR_B200_C_DYNAMIC: EmitDynamic(); break;
       case TOWR_B200_C_BASE_ACC: EmitSplineAcc(); break;
-      case TOWR_B200_C_ENDEFFECTOR_ROM: EmitRom(); break;
+      case TOWR_B200_C_ENDEFFECTOR_ROM: if (rt()) EmitRomRt(); else EmitRom(); break;
       case TOWR_B200_C_FORCE:
         if (!(s_.dt_constraint_force > 0.0)) throw std::runtime_error("unsupported: node-based ForceConstraint");
         for (int e = 0; e < s_.n_ee; ++e) EmitForceDisc(e);
@@ -647,6 +812,9 @@ void Builder::Run() {
         break;
       case TOWR_B200_C_BASE_ROM: EmitBaseRom(); break;
       case TOWR_B200_C_TOTAL_TIME:
+        if (!rt()) throw std::runtime_error("TotalTime constraint without ee-schedule variables");
+        for (int e = 0; e < s_.n_ee; ++e) EmitTotalDuration(e);
+        break;
       case TOWR_B200_C_TERRAIN_HARD:
         throw std::runtime_error("unsupported: constraint " + std::to_string(s_.constraints[i]) + " not built yet");
       default: throw std::runtime_error("constraint not defined!");   // nlp_formulation.cc:396
