@@ -27,6 +27,24 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 METRIC = "ANYmal-trot constraint+Jacobian evals/s"
+# name -> (robot, gait combo, total time, optimise durations, terrain, description).  The default is the configuration
+# BASELINE.json's metric is quoted on (configs[2]); the others are the remaining BASELINE configs, measured on request.
+WORKLOADS = {
+    "anymal_trot": (3, 1, 2.0, False, 0, "ANYmal fly-trot 2 s (Anymal, combo C1, default Parameters, fixed durations)"),
+    "anymal_trot_durations": (3, 1, 2.0, True, 0, "ANYmal fly-trot 2 s with optimised phase durations"),
+    "hyq_gallop_durations": (2, 4, 2.4, True, 1, "HyQ gallop 2.4 s over Block with optimised step durations"),
+    "biped_walk_durations": (1, 0, 2.4, True, 0, "biped walk 2.4 s with gait/phase-duration optimisation"),
+    "monoped_hop": (0, 0, 2.4, False, 0, "monoped hop 2.4 s on flat ground"),
+}
+WL = WORKLOADS["anymal_trot"]
+
+
+def wl_spec(M, goal=(1.0, 0.0, 0.0)):
+    return M.make_spec(WL[0], WL[1], WL[2], goal=goal, terrain=WL[4], optimize_durations=WL[3])
+
+
+def metric_name(name):
+    return METRIC if name == "anymal_trot" else name + " constraint+Jacobian evals/s"
 UNIT = "evals/s"
 GOAL_SEED = 20260101 + 2      # seed = 20260101 + config index
 X_VARIANTS = 16
@@ -41,11 +59,15 @@ def parse():
     ap.add_argument("--batch", type=int, default=4096, help="problems per GPU")
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    return ap.parse_args()
+    ap.add_argument("--workload", default="anymal_trot", choices=sorted(WORKLOADS))
+    a = ap.parse_args()
+    global WL
+    WL = WORKLOADS[a.workload]
+    return a
 
 
 def workload_config(st, batch, n_gpus):
-    return {"workload": "ANYmal fly-trot 2 s (Anymal, combo C1, default Parameters, fixed durations)",
+    return {"workload": WL[5],
             "batch_per_gpu": batch, "global_batch": batch * n_gpus, "n_vars": st["n_vars"], "n_rows": st["n_rows"],
             "nnz": st["nnz"], "bytes_per_eval": st["bytes"], "x_variants": X_VARIANTS,
             "l2": "outputs written per step (%.0f MB) and x rotated over %d variants exceed the 126 MB L2"
@@ -102,13 +124,13 @@ def make_inputs(T, batch, rank):
     """Structure class + per-problem specs (random goals) + X_VARIANTS perturbed x per problem."""
     import numpy as np
     rng = np.random.default_rng(GOAL_SEED + 7919 * rank)
-    s0 = T.make_spec(T.Anymal, T.C1, 2.0)
+    s0 = wl_spec(T)
     st = T.Structure(s0)
     specs = []
     x0 = np.empty((batch, st.n_vars))
     for i in range(batch):
         goal = (rng.uniform(0.5, 2.5), rng.uniform(-0.3, 0.3), rng.uniform(-0.4, 0.4))
-        s = T.make_spec(T.Anymal, T.C1, 2.0, goal=goal)
+        s = wl_spec(T, goal)
         specs.append(s)
         x0[i] = st.x0(s)
     lo, up = st.var_bounds(s0)
@@ -124,6 +146,8 @@ def make_inputs(T, batch, rank):
             sc = 0.05 * mg
         elif name.startswith("ee-torque"):
             sc = 0.5
+        elif name.startswith("ee-schedule"):
+            sc = 0.02
         scale[col:col + n] = sc
         col += n
     xs = []
@@ -141,9 +165,9 @@ def run_reference(args, rank, world):
     import towr2025_b200 as T              # host-side set-up only (specs, x0); no GPU work on this arm
     from oracle import oracle_py as O
     cores = os.cpu_count() or 1
-    s0 = T.make_spec(T.Anymal, T.C1, 2.0)
+    s0 = wl_spec(T)
     st = T.Structure(s0)
-    so = O.make_spec(O.Anymal, 1, 2.0)
+    so = wl_spec(O)
     sample = max(cores * 8, 16)
     rng = np.random.default_rng(GOAL_SEED)
     x = st.x0(s0)[None, :] + rng.uniform(-1, 1, size=(sample, st.n_vars)) * 0.05
@@ -157,7 +181,7 @@ def run_reference(args, rank, world):
     dt = time.perf_counter() - t0
     value = sample * steps / dt
     stinfo = {"n_vars": st.n_vars, "n_rows": st.n_rows, "nnz": st.nnz, "bytes": st.bytes_per_eval}
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+    line = {"impl": "reference", "metric": metric_name(args.workload), "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
             "warmup": min(args.warmup, 2), "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(stinfo, args.batch, args.gpus),
@@ -174,7 +198,7 @@ def cpu_baseline(T, st, s0, xs):
     import numpy as np
     from oracle import oracle_py as O
     cores = os.cpu_count() or 1
-    so = O.make_spec(O.Anymal, 1, 2.0)
+    so = wl_spec(O)
     sample = max(cores * 8, 16)
     x = np.ascontiguousarray(xs[0][:sample])
     # goals only move bounds and x0, not g/J, so one oracle spec serves the sample
@@ -276,11 +300,13 @@ def run_ours(args, rank, world, local_rank):
         achieved = st.bytes_per_eval * batch / (avg_ms * 1e-3) / 1e9
         traffic = None
         try:
+            if args.workload != "anymal_trot":
+                raise KeyError("the ncu capture under profiles/ is of the default workload")
             traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["dram_bytes_per_launch"]
         except Exception:
             pass
         stinfo = {"n_vars": st.n_vars, "n_rows": st.n_rows, "nnz": st.nnz, "bytes": st.bytes_per_eval}
-        line = {"metric": METRIC, "value": world * batch * args.steps / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+        line = {"metric": metric_name(args.workload), "value": world * batch * args.steps / (total_ms * 1e-3), "unit": UNIT, "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": workload_config(stinfo, batch, world),

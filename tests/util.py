@@ -44,6 +44,11 @@ CASES = [
     ("anymal_trot_durations", 3, 1, 2.0, (1.0, 0.0, 0.1), 0, (), True),
     ("hyq_gallop_block_durations_torque", 2, 4, 2.4, (1.4, 0.0, 0.0), 1, (TORQUE,), True),
     ("monoped_hop_stairs_durations", 0, 0, 2.4, (0.9, 0.0, 0.0), 2, (), True),
+    # node-based ForceConstraint (Parameters::dt_constraint_force_ <= 0, force_constraint.cc) and other sampling steps
+    ("anymal_trot_force_nodes_slope", 3, 1, 2.0, (1.0, 0.0, 0.0), 4, (), False, {"dt_constraint_force": -1.0}),
+    ("biped_walk_force_nodes_durations", 1, 0, 2.4, (1.0, 0.0, 0.0), 0, (), True, {"dt_constraint_force": -1.0}),
+    ("hyq_trot_fine_dt", 2, 1, 2.0, (0.8, 0.1, 0.0), 0, (), False,
+     {"dt_constraint_dynamic": 0.05, "dt_constraint_range_of_motion": 0.04, "dt_constraint_force": 0.01}),
 ]
 
 
@@ -73,8 +78,11 @@ def mk(M, case, goal=None):
     """The case's NlpFormulation spec built by module M (the product package or the oracle binding)."""
     extra = case[6] if len(case) > 6 else ()
     opt = case[7] if len(case) > 7 else False
-    return M.make_spec(case[1], case[2], case[3], goal=goal if goal is not None else case[4], terrain=case[5],
-                       optimize_durations=opt, extra_constraints=extra)
+    s = M.make_spec(case[1], case[2], case[3], goal=goal if goal is not None else case[4], terrain=case[5],
+                    optimize_durations=opt, extra_constraints=extra)
+    for k, v in (case[8] if len(case) > 8 else {}).items():     # Parameters overrides (same field names in both specs)
+        setattr(s, k, v)
+    return s
 
 
 def perturbed(x0, seed, scale=0.1):

@@ -447,6 +447,55 @@ __device__ __forceinline__ void ItemForce(const ItemCtx<L>& cx, const ItemC& it)
   }
 }
 
+// ------------------------------------------------------------------------------------------- force (node-based)
+// ForceConstraint (force_constraint.cc:62-171): basis at the stance foothold (ee-motion node at the start of the force
+// node's phase, slot ItemC::aux), force = the force node's position value (slot ItemC::s0).
+// G slots: b_i[3] (ee-force block), then f . d b_i / d(x|y) at 15 + 2 i + dim (ee-motion block, always stored).
+template <class L>
+__device__ __forceinline__ void ItemForceNode(const ItemCtx<L>& cx, const ItemC& it) {
+  const double* fn = cx.nodes + it.s0 * 6 * L::NS;
+  const double* pn = cx.nodes + it.aux * 6 * L::NS;
+  const double f[3] = {fn[0], fn[L::NS], fn[2 * L::NS]};
+  const TerrainSample ts = EvalTerrain(cx.pc->terrain_id, pn[0], pn[L::NS]);
+  double n[3], t1[3], t2[3];
+  TerrainBasis(ts, n, t1, t2);
+  const double mu = kFrictionCoeff;
+  double* G = cx.G + it.gslot * L::GS;
+  double b[15];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    b[d] = n[d];
+    b[3 + d] = t1[d] - mu * n[d];
+    b[6 + d] = t1[d] + mu * n[d];
+    b[9 + d] = t2[d] - mu * n[d];
+    b[12 + d] = t2[d] + mu * n[d];
+  }
+#pragma unroll
+  for (int i = 0; i < 15; ++i) TB_G(i) = b[i];
+#pragma unroll
+  for (int dim = 0; dim < 2; ++dim) {
+    double dn[3], dt1[3], dt2[3], v[15];
+    TerrainBasisDeriv(ts, 0, dim, dn);
+    TerrainBasisDeriv(ts, 1, dim, dt1);
+    TerrainBasisDeriv(ts, 2, dim, dt2);
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      v[d] = dn[d];
+      v[3 + d] = dt1[d] - mu * dn[d];
+      v[6 + d] = dt1[d] + mu * dn[d];
+      v[9 + d] = dt2[d] - mu * dn[d];
+      v[12 + d] = dt2[d] + mu * dn[d];
+    }
+#pragma unroll
+    for (int i = 0; i < 5; ++i) TB_G(15 + 2 * i + dim) = (f[0] * v[3 * i] + f[1] * v[3 * i + 1]) + f[2] * v[3 * i + 2];
+  }
+  if (cx.g) {
+    double* gr = cx.g + it.row * L::RS;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) gr[(i) * L::RS] = (f[0] * b[3 * i] + f[1] * b[3 * i + 1]) + f[2] * b[3 * i + 2];
+  }
+}
+
 // ------------------------------------------------------------------------------------------ torque (discretised)
 // g: torque_constraint_discretized.cc:105-129.  G slots: t1[3], t2[3], n[3], -n[3], (-k mu) n[3]; B[b0] = k_friction.
 template <class L>
@@ -596,6 +645,7 @@ __device__ __forceinline__ void RunItem(const ItemCtx<L>& cx, const ItemC& it) {
     case kItemRomFoot: ItemRomFoot<L>(cx, it); break;
     case kItemForce: ItemForce<L>(cx, it); break;
     case kItemTorque: ItemTorque<L>(cx, it); break;
+    case kItemForceNode: ItemForceNode<L>(cx, it); break;
     case kItemBaseRom: ItemBaseRom<L>(cx, it); break;
     case kItemTerrainNode: ItemHeightNode<L>(cx, it, 0.0); break;
     case kItemBaseHeightNode: ItemHeightNode<L>(cx, it, 0.4); break;   // nlp_formulation.cc:597

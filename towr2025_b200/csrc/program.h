@@ -49,6 +49,7 @@ enum ItemType : int {
   kItemSwingNode,       // swing_constraint.cc:54-108              4 rows per swing node
   kItemSplineAcc,       // spline_acc_constraint.cc:48-80          3 rows per junction
   kItemTotalDuration,   // total_duration_constraint.cc:48-72
+  kItemForceNode,       // force_constraint.cc:62-171                5 rows per stance force node (node-based variant)
   kItemBaseRom,         // base_motion_constraint.cc:60-85         6 rows per sample (base euler angles, base position)
   kItemTorque,          // torque_constraint_discretized.cc:105-235  4 rows per (sample, foot)
   kItemDynFoot,         // per (dynamic sample, foot): f_e, c - p_e slots and the foot's torque term f_e x (c - p_e) + tau_e

@@ -254,6 +254,7 @@ class Builder {
   void EmitSplineAcc();
   void EmitRom();
   void EmitForceDisc(int ee);
+  void EmitForceNodes(int ee);
   void EmitTorqueDisc(int ee);
   void EmitBaseRom();
   void EmitRomRt();
@@ -668,6 +669,43 @@ void Builder::EmitTotalDuration(int ee) {
   EndSet();
 }
 
+// ForceConstraint, node-based (force_constraint.cc:37-171; used when dt_constraint_force <= 0): 5 rows per non-constant
+// force node; the ee-force block holds b_i, the ee-motion block (x, y of the stance foothold) f . d b_i - always stored.
+void Builder::EmitForceNodes(int ee) {
+  const VarSet& mo = Set(kEEMotion, ee);
+  const VarSet& fo = Set(kEEForce, ee);
+  const std::vector<int> nodes = fo.NonConstantNodes();
+  const int one = AddB(1.0);
+  BeginGroup();
+  BeginSet("force-" + fo.name, static_cast<int>(nodes.size()) * 5);
+  int row = 0;
+  for (int node : nodes) {
+    const int phase = fo.PhaseOfNode(node);
+    const int ee_node = mo.PolyAtStartOfPhase(phase);      // GetNodeIDAtStartOfPhase: start node of that polynomial
+    ItemRec it = NewItem(kItemForceNode);
+    it.ee = static_cast<short>(ee);
+    it.row[0] = set_row0_ + row;
+    it.s[0] = fo.node_slot0 + node;
+    it.aux = mo.node_slot0 + ee_node;
+    it.gslot = AllocG(25);
+    hp_.items.push_back(it);
+    const int bk[5] = {kBoundForceNormal, kBoundLE0, kBoundGE0, kBoundLE0, kBoundGE0};
+    for (int i = 0; i < 5; ++i) Bound(row + i, bk[i], ee);
+    for (int dim = 0; dim < 3; ++dim) {
+      const int idx = fo.OptIndex(node, 0, dim);
+      if (idx < 0) throw std::runtime_error("force constraint touches a node value that is not optimised");
+      for (int i = 0; i < 5; ++i) { Term tm; tm.g = it.gslot + 3 * i + dim; tm.b = one; Add(row + i, fo.col0 + idx, tm, true); }
+    }
+    for (int dim = 0; dim < 2; ++dim) {
+      const int idx = mo.OptIndex(ee_node, 0, dim);
+      if (idx < 0) throw std::runtime_error("force constraint touches a foothold that is not optimised");
+      for (int i = 0; i < 5; ++i) { Term tm; tm.g = it.gslot + 15 + 2 * i + dim; tm.b = one; Add(row + i, mo.col0 + idx, tm, true); }
+    }
+    row += 5;
+  }
+  EndSet();
+}
+
 // TorqueConstraintDiscretized (torque_constraint_discretized.cc:103-235): 4 rows per sample; G slots t1, t2, n, -n,
 // (-k mu) n.  The ee-motion block exists only where the terrain has curvature (same rule as the force constraint).
 void Builder::EmitTorqueDisc(int ee) {
@@ -799,8 +837,10 @@ void Builder::Run() {
       case TOWR_B200_C_BASE_ACC: EmitSplineAcc(); break;
       case TOWR_B200_C_ENDEFFECTOR_ROM: if (rt()) EmitRomRt(); else EmitRom(); break;
       case TOWR_B200_C_FORCE:
-        if (!(s_.dt_constraint_force > 0.0)) throw std::runtime_error("unsupported: node-based ForceConstraint");
-        for (int e = 0; e < s_.n_ee; ++e) EmitForceDisc(e);
+        for (int e = 0; e < s_.n_ee; ++e) {
+          if (s_.dt_constraint_force > 0.0) EmitForceDisc(e);
+          else EmitForceNodes(e);
+        }
         break;
       case TOWR_B200_C_SWING:
         for (int e = 0; e < s_.n_ee; ++e) EmitSwing(e);
