@@ -1,0 +1,84 @@
+"""include/towr_b200_ifopt.hpp: the C++ mirror of the ifopt component surface over the C ABI."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(ROOT, "tests", "cpp", "_build", "ifopt_surface")
+
+
+def build(name="ifopt_surface"):
+    import towr2025_b200 as T
+    T.build()
+    exe = os.path.join(os.path.dirname(EXE), name)
+    os.makedirs(os.path.dirname(EXE), exist_ok=True)
+    src = os.path.join(ROOT, "tests", "cpp", name + ".cc")
+    lib_dir = os.path.join(ROOT, "towr2025_b200")
+    hdrs = [os.path.join(ROOT, "include", h) for h in ("towr_b200_ifopt.hpp", "towr_b200_coalescer.hpp", "towr_b200.h")]
+    newest = max([os.path.getmtime(src), os.path.getmtime(os.path.join(lib_dir, "libtowr_b200.so"))] +
+                 [os.path.getmtime(h) for h in hdrs])
+    if not os.path.exists(exe) or os.path.getmtime(exe) < newest:
+        subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-pthread", "-I", os.path.join(ROOT, "include"), src,
+                               "-o", exe, "-L", lib_dir, "-ltowr_b200", "-Wl,-rpath," + lib_dir])
+    return exe
+
+
+def run(*args):
+    out = subprocess.run([build(), *args], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    return {l.split()[0]: l.split()[1:] for l in out.stdout.splitlines() if l.strip()}
+
+
+@pytest.mark.parametrize("mode", ["fixed", "durations"])
+def test_surface_host_side(product, oracle, mode):
+    T, O = product, oracle
+    r = run("host", mode)
+    opt = mode == "durations"
+    p = O.Problem(O.make_spec(O.Anymal, 1, 2.0, goal=(0.7, 0.0, 0.0), optimize_durations=opt))
+    st = T.Structure(T.make_spec(T.Anymal, T.C1, 2.0, optimize_durations=opt))
+    assert [int(v) for v in r["sizes"]] == [st.n_vars, st.n_rows, st.nnz]
+    assert float(r["x0sum"][0]) == pytest.approx(float(np.sum(p.x0())), rel=1e-13)
+    assert "ok" in r
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["fixed", "durations"])
+def test_surface_batched_eval(product, oracle, mode):
+    T, O = product, oracle
+    r = run("gpu", mode)
+    opt = mode == "durations"
+    p = O.Problem(O.make_spec(O.Anymal, 1, 2.0, goal=(1.5, 0.0, 0.0), optimize_durations=opt))
+    x = p.x0()
+    x = x + 0.01 * np.sin(0.37 * np.arange(len(x)))
+    g = p.eval_g(x)
+    rows, cols, v = p.eval_jac(x)
+    assert float(r["gsum"][0]) == pytest.approx(float(g.sum()), rel=1e-9, abs=1e-9)
+    assert float(r["gsum"][2]) == pytest.approx(float(v.sum()), rel=1e-9, abs=1e-7)
+    dyn = dict(p.con_sets())["dynamic"]
+    assert int(r["dynamic"][1]) == dyn
+    off = 0
+    for name, n in p.con_sets():
+        if name == "dynamic":
+            break
+        off += n
+    m = (rows >= off) & (rows < off + dyn)
+    assert int(r["dynamic"][3]) == int(m.sum())
+    assert float(r["dynamic"][5]) == pytest.approx(float(v[m].sum()), rel=1e-9, abs=1e-7)
+    assert float(r["dynamic"][7]) == pytest.approx(float(g[off]), rel=1e-9, abs=1e-12)
+
+
+def test_callback_coalescer_policy():
+    """Solver threads with diverging iteration / line-search counts: every request answered, no deadlock when
+    solvers finish early, and far fewer launches than requests (stub evaluator, no device needed)."""
+    out = subprocess.run([build("coalescer"), "host"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "ok" in out.stdout
+
+
+@pytest.mark.gpu
+def test_callback_coalescer_on_gpu():
+    out = subprocess.run([build("coalescer"), "gpu"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "ok" in out.stdout
