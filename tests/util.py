@@ -49,6 +49,9 @@ CASES = [
     ("biped_walk_force_nodes_durations", 1, 0, 2.4, (1.0, 0.0, 0.0), 0, (), True, {"dt_constraint_force": -1.0}),
     ("hyq_trot_fine_dt", 2, 1, 2.0, (0.8, 0.1, 0.0), 0, (), False,
      {"dt_constraint_dynamic": 0.05, "dt_constraint_range_of_motion": 0.04, "dt_constraint_force": 0.01}),
+    # large class tables: the range-of-motion sets are split into sample groups, the batch lowers the G capacity
+    ("anymal_trot_very_fine_dt", 3, 1, 2.0, (1.0, 0.0, 0.0), 0, (), False,
+     {"dt_constraint_dynamic": 0.025, "dt_constraint_range_of_motion": 0.02, "dt_constraint_force": 0.005}),
 ]
 
 

@@ -22,6 +22,7 @@ void SpecNominalStates(towr_b200_spec* s, double gx, double gy, double gyaw);
 
 struct towr_b200_structure {
   tb::HostProgram hp;
+  towr_b200_spec spec;     // the class's defining spec (a batch may rebuild the program with a smaller G capacity)
 };
 
 namespace {
@@ -83,6 +84,7 @@ struct towr_b200_batch {
   tb::ProblemConst* pc_gather_dev = nullptr;
   int max_ctas = 0, lanes = 1;
   bool ws = false;         // warp-specialised kernel (kernels.cu)
+  std::unique_ptr<tb::HostProgram> hp_local;   // program rebuilt with a smaller G capacity (large class tables)
   long long launches = 0;
 
   void SyncConsts() {
@@ -129,6 +131,7 @@ int towr_b200_structure_create(const towr_b200_spec* s, towr_b200_structure** ou
     if (!s || !out) throw std::runtime_error("null argument");
     auto st = std::make_unique<towr_b200_structure>();
     tb::BuildProgram(*s, st->hp);
+    st->spec = *s;
     *out = st.release();
   });
 }
@@ -186,7 +189,27 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     b->n = n_problems;
     b->device = device;
     Check(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking), "cudaStreamCreate");
-    const tb::HostProgram& hp = st->hp;
+    cudaDeviceProp prop;
+    Check(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
+    // The class tables, one problem's spline arrays and one G buffer must fit the SM's shared memory.  Classes with many
+    // samples have large tables: rebuild the program with the G capacity that is left (more, smaller segments).
+    const tb::HostProgram* hpp = &st->hp;
+    auto shared_need = [](const tb::HostProgram& h, int g_cap) {
+      tb::DeviceProgram t{};
+      t.blob = h.blob;
+      t.g_capacity = g_cap;
+      return tb::EvalSharedBytes(t, 1) + 1024;
+    };
+    if (shared_need(*hpp, hpp->g_capacity) > prop.sharedMemPerBlockOptin) {
+      const long long left = static_cast<long long>(prop.sharedMemPerBlockOptin) - static_cast<long long>(shared_need(*hpp, 0)) - 2048;
+      if (left < 8 * 256) throw std::runtime_error("unsupported: the class tables alone exceed the SM's shared memory");
+      b->hp_local = std::make_unique<tb::HostProgram>();
+      tb::BuildProgram(st->spec, *b->hp_local, static_cast<int>(left / 8));
+      hpp = b->hp_local.get();
+      if (shared_need(*hpp, hpp->g_capacity) > prop.sharedMemPerBlockOptin)
+        throw std::runtime_error("unsupported: structure class needs more shared memory per CTA than the device has");
+    }
+    const tb::HostProgram& hp = *hpp;
     tb::DeviceProgram& dp = b->dp;
     dp.n_vars = hp.n_vars; dp.n_rows = hp.n_rows; dp.nnz = hp.nnz; dp.n_ee = hp.n_ee;
     dp.n_segments = static_cast<int>(hp.segments.size());
@@ -203,8 +226,6 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     Check(cudaMalloc(&b->status_dev, sizeof(int) * n_problems), "cudaMalloc(status)");
     keep(b->status_dev);
     Check(cudaMemset(b->status_dev, 0, sizeof(int) * n_problems), "cudaMemset(status)");
-    cudaDeviceProp prop;
-    Check(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
     // lanes per CTA: as many problems side by side as shared memory allows (the class tables are held once per CTA)
     int forced = 0;
     if (const char* env = std::getenv("TOWR_B200_LANES")) forced = std::atoi(env);

@@ -257,7 +257,7 @@ class Builder {
   void EmitForceNodes(int ee);
   void EmitTorqueDisc(int ee);
   void EmitBaseRom();
-  void EmitRomRt();
+  void EmitRomSplit();
   void EmitTotalDuration(int ee);
   void EmitSwing(int ee);
   void EmitBaseHeight();
@@ -598,10 +598,10 @@ void Builder::EmitForceDisc(int ee) {
   EndSet();
 }
 
-// RangeOfMotionConstraint with optimised durations: the ee-motion block stores every column of the set (weights written
-// by the RomFoot item) and the ee-schedule block is finished by the item.  The sets are split into sample groups, so
-// every foot's set carries its own RomPre items.
-void Builder::EmitRomRt() {
+// RangeOfMotionConstraint split into sample groups (every foot's set carries its own RomPre items), used when one
+// group for all samples would not fit a segment, and with optimised durations: there the ee-motion block stores every
+// column of the set (weights written by the RomFoot item) and the ee-schedule block is finished by the item.
+void Builder::EmitRomSplit() {
   const int E = s_.n_ee;
   const VarSet& lin = Set(kBaseLin);
   const VarSet& ang = Set(kBaseAng);
@@ -609,8 +609,8 @@ void Builder::EmitRomRt() {
   const int K = static_cast<int>(ts.size());
   for (int e = 0; e < E; ++e) {
     const VarSet& mo = Set(kEEMotion, e);
-    const int nsched = Set(kEESchedule, e).n_vars;
-    const int foot_size = (9 + mo.n_vars + 3 * nsched) | 1;
+    const int nsched = rt() ? Set(kEESchedule, e).n_vars : 0;
+    const int foot_size = (9 + (rt() ? mo.n_vars + 3 * nsched : 0)) | 1;
     const int chunk = std::max(1, 960 / (kRomPreSize + foot_size));
     for (int k = 0; k < K; ++k) {
       if (k % chunk == 0) {
@@ -628,7 +628,9 @@ void Builder::EmitRomRt() {
       it.row[0] = set_row0_ + 3 * k;
       it.aux = pre.gslot;
       it.gslot = AllocG(foot_size);
-      it.s[kSMotion + e] = AtRt(0, e, ts[k]);
+      SplineAt am{0, 0, 0.0};
+      if (rt()) it.s[kSMotion + e] = AtRt(0, e, ts[k]);
+      else { am = At(mo, ts[k]); it.s[kSMotion + e] = am.sample; }
       hp_.items.push_back(it);
       for (int r = 0; r < 3; ++r) Bound(3 * k + r, kBoundRom, e, r);
       const int gR = pre.gslot + kRpR, gD = it.gslot;
@@ -643,9 +645,17 @@ void Builder::EmitRomRt() {
           Term tm; tm.g = gD + 3 * r + c.dim; tm.b = AddB(c.v[0]);
           Add(3 * k + r, ang.col0 + c.idx, tm);
         }
-      for (auto& c : AllCols(mo))
-        for (int r = 0; r < 3; ++r) Add(3 * k + r, mo.col0 + c.first, GG(gR + c.second * 3 + r, it.gslot + 9 + c.first));
-      AddScheduleBlock(3 * k, 3, e, it.gslot + 9 + mo.n_vars);
+      if (rt()) {
+        for (auto& c : AllCols(mo))
+          for (int r = 0; r < 3; ++r) Add(3 * k + r, mo.col0 + c.first, GG(gR + c.second * 3 + r, it.gslot + 9 + c.first));
+        AddScheduleBlock(3 * k, 3, e, it.gslot + 9 + mo.n_vars);
+      } else {
+        for (const ColBasis& c : Columns(mo, am.poly, am.t_local))
+          for (int r = 0; r < 3; ++r) {            // R^T J_p
+            Term tm; tm.g = gR + c.dim * 3 + r; tm.b = AddB(c.v[0]);
+            Add(3 * k + r, mo.col0 + c.idx, tm);
+          }
+      }
     }
     EndSet();
   }
@@ -835,7 +845,12 @@ void Builder::Run() {
         break;
       case TOWR_B200_C_DYNAMIC: EmitDynamic(); break;
       case TOWR_B200_C_BASE_ACC: EmitSplineAcc(); break;
-      case TOWR_B200_C_ENDEFFECTOR_ROM: if (rt()) EmitRomRt(); else EmitRom(); break;
+      case TOWR_B200_C_ENDEFFECTOR_ROM: {
+        const int K = static_cast<int>(SampleTimes(hp_.total_time, s_.dt_constraint_range_of_motion).size());
+        if (rt() || K * (kRomPreSize + 9 * s_.n_ee) > 6000) EmitRomSplit();
+        else EmitRom();
+        break;
+      }
       case TOWR_B200_C_FORCE:
         for (int e = 0; e < s_.n_ee; ++e) {
           if (s_.dt_constraint_force > 0.0) EmitForceDisc(e);
@@ -892,7 +907,7 @@ std::string StructureSignature(const towr_b200_spec& s) {
   return o.str();
 }
 
-void BuildProgram(const towr_b200_spec& s, HostProgram& hp) {
+void BuildProgram(const towr_b200_spec& s, HostProgram& hp, int g_cap) {
   BuildLayout(s, hp);
   hp.signature = StructureSignature(s);
   // pass 1: one segment per group, to learn each group's G footprint
@@ -918,7 +933,9 @@ void BuildProgram(const towr_b200_spec& s, HostProgram& hp) {
     return n;
   };
   std::vector<char> plan(sizing.group_g_size.size(), 0);
-  if (const char* env = std::getenv("TOWR_B200_GCAP")) {
+  if (g_cap > 0) {
+    plan_with(std::max(largest + kGReserved, g_cap), plan);
+  } else if (const char* env = std::getenv("TOWR_B200_GCAP")) {
     plan_with(std::max(64, std::atoi(env)), plan);
   } else {
     const int n_min = plan_with(cap_max, plan);            // fewest segments possible
@@ -938,6 +955,9 @@ void BuildProgram(const towr_b200_spec& s, HostProgram& hp) {
       std::fprintf(stderr, "segment items %d (level0 %d) entries %d g %d\n", sg.n_items, sg.n_items0, sg.n_entries, sg.g_size);
   }
   PackProgram(hp);
+  if (std::getenv("TOWR_B200_DEBUG"))
+    std::fprintf(stderr, "blob %d B (B %d, times %d, items %d, samples %d, polys %d), G capacity %d, %zu segments\n", hp.blob.bytes,
+                 hp.blob.n_B, hp.blob.n_times, hp.blob.n_items, hp.blob.n_samples, hp.blob.n_polys, hp.g_capacity, hp.segments.size());
 }
 
 }  // namespace tb

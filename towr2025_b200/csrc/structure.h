@@ -22,7 +22,8 @@ void HermiteBasis(double T, double t, double out[12]);
 // segment lookup with the 1e-10 junction rule (spline.cc:48-78)
 int SegmentId(double t_global, const std::vector<double>& durations);
 double LocalTime(double t_global, int id, const std::vector<double>& durations);
-void BuildProgram(const towr_b200_spec& s, HostProgram& hp);
+// g_cap > 0 overrides the G slots per segment (the batch lowers it when a class's tables leave less shared memory)
+void BuildProgram(const towr_b200_spec& s, HostProgram& hp, int g_cap = 0);
 std::string StructureSignature(const towr_b200_spec& s);
 
 // pack.cc
