@@ -32,10 +32,12 @@ def main():
     for it in range(3):
         b.eval_device(batch, T.EVAL_BOTH, dx.data_ptr(), dg.data_ptr(), dv.data_ptr())
         torch.cuda.synchronize()
-        L.towr_b200_debug_phase_clocks(out, 64)
+        reader = "towr_b200_debug_phase_clocks" + ("_bulk" if os.environ.get("TOWR_B200_KERNEL", "bulk") == "bulk" else "")
+        getattr(L, reader)(out, 64)
     v = list(out)
     tot = sum(v)
-    if os.environ.get("TOWR_B200_KERNEL", "") == "ws" or v[16] or v[17]:
+    print("raw:", v)
+    if os.environ.get("TOWR_B200_KERNEL", "") == "ws":
         pn = ["wait x", "stage C", "wait empty", "L0 items", "L0->L1 barrier", "L1 items", "hand-off + group end"]
         pt = sum(v[:7]) or 1
         print("producer thread 0: %d clocks" % pt)

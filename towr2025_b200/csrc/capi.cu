@@ -1,6 +1,7 @@
 // capi.cu — the extern "C" boundary declared in include/towr_b200.h.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -82,8 +83,9 @@ struct towr_b200_batch {
   // staging for the host-buffer path
   double *x_dev = nullptr, *g_dev = nullptr, *v_dev = nullptr;
   tb::ProblemConst* pc_gather_dev = nullptr;
-  int max_ctas = 0, lanes = 1;
-  bool ws = false;         // warp-specialised kernel (kernels.cu)
+  int max_ctas = 0, lanes = 0;
+  bool ws = false;         // warp-specialised kernel (kernels_ws.cu)
+  bool bulk = false;       // bulk-store kernel (kernels_tma.cu)
   std::unique_ptr<tb::HostProgram> hp_local;   // program rebuilt with a smaller G capacity (large class tables)
   long long launches = 0;
 
@@ -209,12 +211,51 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
       if (shared_need(*hpp, hpp->g_capacity) > prop.sharedMemPerBlockOptin)
         throw std::runtime_error("unsupported: structure class needs more shared memory per CTA than the device has");
     }
+    int forced = 0;
+    if (const char* env = std::getenv("TOWR_B200_LANES")) forced = std::atoi(env);
+    // kernel variant: TOWR_B200_KERNEL = bulk | lockstep | ws forces one.  The bulk-store kernel needs the G buffer and
+    // the staging buffer of the largest segment side by side: lower the G capacity until both fit.
+    const char* kenv = std::getenv("TOWR_B200_KERNEL");
+    const bool want_bulk = kenv && std::strcmp(kenv, "bulk") == 0;   // opt-in: measured slower than lock-step
+    if (want_bulk) {
+      auto fits = [&](const tb::HostProgram& h, int lanes) {
+        tb::DeviceProgram t{};
+        t.blob = h.blob;
+        t.g_capacity = h.g_capacity;
+        t.joint_capacity = tb::JointCapacity(h.segments.data(), static_cast<int>(h.segments.size()));
+        return tb::EvalFitsBulk(t, lanes, prop.sharedMemPerBlockOptin);
+      };
+      for (int lanes : {2, 1}) {
+        // one lane per CTA only on request: two lock-step lanes beat it
+        if (b->bulk || (forced ? lanes != forced : lanes != 2)) continue;
+        if (fits(*hpp, lanes)) { b->bulk = true; b->lanes = lanes; break; }
+        // elements per problem lane that the class tables and spline arrays leave for G + staging
+        tb::DeviceProgram t0{};
+        t0.blob = hpp->blob;
+        const long long fixed = static_cast<long long>(tb::EvalSharedBytesBulk(t0, lanes)) + 1024 + 6144;   // + table growth
+        long long joint = (static_cast<long long>(prop.sharedMemPerBlockOptin) - fixed) / (8 * lanes);
+        if (const char* env = std::getenv("TOWR_B200_JOINT")) joint = std::atoi(env);
+        for (int attempt = 0; attempt < 6 && joint > 1024; ++attempt, joint = joint * 15 / 16) {
+          auto h = std::make_unique<tb::HostProgram>();
+          tb::BuildProgram(st->spec, *h, 0, static_cast<int>(joint));
+          if (fits(*h, lanes)) {
+            b->hp_local = std::move(h);
+            hpp = b->hp_local.get();
+            b->bulk = true;
+            b->lanes = lanes;
+            break;
+          }
+        }
+      }
+      if (!b->bulk && kenv) throw std::runtime_error("unsupported: the bulk-store kernel does not fit this structure class");
+    }
     const tb::HostProgram& hp = *hpp;
     tb::DeviceProgram& dp = b->dp;
     dp.n_vars = hp.n_vars; dp.n_rows = hp.n_rows; dp.nnz = hp.nnz; dp.n_ee = hp.n_ee;
     dp.n_segments = static_cast<int>(hp.segments.size());
     dp.total_time = hp.total_time;
     dp.g_capacity = hp.g_capacity;
+    dp.joint_capacity = tb::JointCapacity(hp.segments.data(), dp.n_segments);
     dp.blob = hp.blob;
     auto keep = [&](auto* p) { b->owned.push_back(const_cast<void*>(static_cast<const void*>(p))); return p; };
     dp.blob_data = keep(Upload(hp.blob_data));
@@ -227,12 +268,9 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     keep(b->status_dev);
     Check(cudaMemset(b->status_dev, 0, sizeof(int) * n_problems), "cudaMemset(status)");
     // lanes per CTA: as many problems side by side as shared memory allows (the class tables are held once per CTA)
-    int forced = 0;
-    if (const char* env = std::getenv("TOWR_B200_LANES")) forced = std::atoi(env);
-    b->lanes = 0;
-    // kernel variant: the warp-specialised one when its double-buffered G fits (TOWR_B200_KERNEL=lockstep|ws forces)
-    const char* kenv = std::getenv("TOWR_B200_KERNEL");
-    const bool want_ws = !kenv || std::strcmp(kenv, "ws") == 0;
+    if (b->bulk) b->max_ctas = prop.multiProcessorCount;
+    // the warp-specialised kernel when its double-buffered G fits
+    const bool want_ws = !b->bulk && (!kenv || std::strcmp(kenv, "ws") == 0);
     if (want_ws && (!forced || forced == 2) && tb::EvalFitsWS(dp, 2, prop.sharedMemPerBlockOptin)) {
       b->ws = true;
       b->lanes = 2;
@@ -241,7 +279,7 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
       throw std::runtime_error("unsupported: the warp-specialised kernel does not fit this structure class");
     }
     for (int lanes : {4, 2, 1}) {
-      if (b->ws) break;
+      if (b->ws || b->bulk) break;
       if (forced && lanes != forced) continue;
       if (tb::EvalSharedBytes(dp, lanes) > static_cast<size_t>(prop.sharedMemPerBlockOptin)) continue;
       int occ = tb::EvalOccupancy(dp, lanes);
@@ -254,9 +292,12 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
       throw std::runtime_error("unsupported: structure class needs more shared memory per CTA than the device has");
     if (std::getenv("TOWR_B200_DEBUG"))
       std::fprintf(stderr, "batch: %s kernel, %d problems per CTA, %zu B shared (blob %d B, G capacity %d), %d CTAs\n",
-                   b->ws ? "warp-specialised" : "lock-step", b->lanes,
-                   b->ws ? tb::EvalSharedBytesWS(dp, b->lanes) : tb::EvalSharedBytes(dp, b->lanes), dp.blob.bytes,
-                   dp.g_capacity, b->max_ctas);
+                   b->bulk ? "bulk-store" : b->ws ? "warp-specialised" : "lock-step", b->lanes,
+                   b->bulk ? tb::EvalSharedBytesBulk(dp, b->lanes)
+                           : b->ws ? tb::EvalSharedBytesWS(dp, b->lanes) : tb::EvalSharedBytes(dp, b->lanes),
+                   dp.blob.bytes, dp.g_capacity, b->max_ctas);
+    if (std::getenv("TOWR_B200_DEBUG"))
+      std::fprintf(stderr, "batch: %d segments, joint capacity %d\n", dp.n_segments, dp.joint_capacity);
     *out = b.release();
   });
 }
@@ -295,7 +336,7 @@ int towr_b200_batch_eval_device(towr_b200_batch* b, int n, int what, const doubl
       b->SyncConsts();
       Check(cudaStreamSynchronize(b->stream), "sync consts");
     }
-    Check((b->ws ? tb::LaunchEvalWS : tb::LaunchEval)(b->dp, b->pc_dev, what, d_x, d_g, d_jac_values, b->status_dev, n,
+    Check((b->bulk ? tb::LaunchEvalBulk : b->ws ? tb::LaunchEvalWS : tb::LaunchEval)(b->dp, b->pc_dev, what, d_x, d_g, d_jac_values, b->status_dev, n,
                                                        b->lanes, b->max_ctas, s), "launch");
     b->launches += 1;
   });
@@ -336,7 +377,7 @@ int towr_b200_batch_eval(towr_b200_batch* b, const int* ids, int n, int what, co
       b->SyncConsts();
     }
     Check(cudaMemcpyAsync(b->x_dev, x, sizeof(double) * dp.n_vars * n, cudaMemcpyHostToDevice, b->stream), "H2D x");
-    Check((b->ws ? tb::LaunchEvalWS : tb::LaunchEval)(dp, pcs, what, b->x_dev, b->g_dev, b->v_dev, b->status_dev, n, b->lanes,
+    Check((b->bulk ? tb::LaunchEvalBulk : b->ws ? tb::LaunchEvalWS : tb::LaunchEval)(dp, pcs, what, b->x_dev, b->g_dev, b->v_dev, b->status_dev, n, b->lanes,
                                                        b->max_ctas, b->stream), "launch");
     b->launches += 1;
     if (what & TOWR_B200_EVAL_G)

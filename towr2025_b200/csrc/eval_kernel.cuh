@@ -1,0 +1,358 @@
+// eval_kernel.cuh — the lock-step evaluation kernel (sm_100a).
+//
+// One CTA evaluates P problems at a time (grid-stride over the batch).  Shared memory holds the class tables, the
+// problems' spline node values, the Hermite coefficients of every polynomial and the G buffer of the current segment;
+// x is read once (coalesced gather through node_src), g and the Jacobian values are written once, the
+// values with fully coalesced 8-byte stores in storage order.  HBM traffic per eval = 8*(n_vars+n_rows+nnz)
+// bytes plus L2-resident class tables (entries, B, items), which are shared by all problems of the batch.
+#pragma once
+#include "kernel_common.cuh"
+
+namespace tb {
+
+// FULL: all P problem lanes of the group exist (no per-store predicate).
+// nf[p] accumulates value * 0 per problem lane: NaN exactly when a stored value is not finite (status bit 2).
+template <int P, bool FULL, int NT, bool GG = false>
+__device__ __forceinline__ void StageB(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[kDescBatch],
+                                       const double* G, const double* Bs, double* __restrict__ o, int nnz, int np,
+                                       double (&nf)[P]) {
+  constexpr int U = kDescBatch;
+  const char* Gb = reinterpret_cast<const char*>(G);
+  const char* Bb = reinterpret_cast<const char*>(Bs);
+  auto emit = [&](uint32_t w, double* op) {              // descriptor: G byte offset (low 16), B byte offset (high 16)
+    double bv = 0.0;
+    double bw[P];                                         // GG entries: the second factor is a per-problem G slot
+    bool gg = false;
+    if constexpr (GG) gg = (w & 0x10000u) != 0;
+    if (!gg) {
+      bv = *reinterpret_cast<const double*>(Bb + (w >> 16));
+    } else {
+      const double* wa = reinterpret_cast<const double*>(Gb + ((w >> 16) & 0xFFF8u) * P);
+#pragma unroll
+      for (int p = 0; p < P; ++p) bw[p] = wa[p];
+    }
+    const char* ga = Gb + (w & 0xFFFFu) * P;
+    double gv[P];
+    if constexpr (P == 1) {
+      gv[0] = *reinterpret_cast<const double*>(ga);
+    } else {
+#pragma unroll
+      for (int p = 0; p < P; p += 2) {
+        const double2 t = *reinterpret_cast<const double2*>(ga + 8 * p);
+        gv[p] = t.x;
+        gv[p + 1] = t.y;
+      }
+    }
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      const double v = gv[p] * ((GG && gg) ? bw[p] : bv);
+      nf[p] = fma(v, 0.0, nf[p]);
+      if (FULL || p < np) op[static_cast<size_t>(p) * nnz] = v;
+    }
+  };
+  while (left > 0) {
+    const int left_next = left - U * NT;
+    uint32_t dn[U];
+    if (left_next > 0) LoadDescriptors<NT>(ent + U * NT, left_next, dn);
+    if (left > (U - 1) * NT) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) emit(d[u], o + u * NT);
+    } else {
+#pragma unroll
+      for (int u = 0; u < U - 1; ++u)
+        if (left > u * NT) emit(d[u], o + u * NT);
+    }
+    if (left_next <= 0) break;
+#pragma unroll
+    for (int u = 0; u < U; ++u) d[u] = dn[u];
+    left = left_next;
+    ent += U * NT;
+    o += U * NT;
+  }
+}
+
+// ---- bulk-store variant (BULK): stage B writes the products into a shared-memory staging buffer in storage order and
+// one thread per problem lane hands the whole segment to the TMA engine (cp.async.bulk shared -> global).  The stores
+// then drain asynchronously while the CTA runs stage A of the next segment: they no longer occupy the LSU pipe that
+// stage A needs for its shared-memory traffic.
+__device__ __forceinline__ void FenceProxyAsync() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void BulkStore(void* gdst, const void* ssrc, unsigned bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),
+               "r"(static_cast<unsigned>(__cvta_generic_to_shared(ssrc))), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void BulkCommit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void BulkWaitRead() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void BulkWaitAll() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+// Stage B into the staging buffer: so[p] = lane p's staging element of entry tid (conflict-free 8-byte stores).
+template <int P, int NT, bool GG>
+__device__ __forceinline__ void StageBShared(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[kDescBatch],
+                                             const double* G, const double* Bs, double* const (&so)[P], double (&nf)[P]) {
+  constexpr int U = kDescBatch;
+  const char* Gb = reinterpret_cast<const char*>(G);
+  const char* Bb = reinterpret_cast<const char*>(Bs);
+  auto emit = [&](uint32_t w, int off) {
+    double bv = 0.0;
+    double bw[P];
+    bool gg = false;
+    if constexpr (GG) gg = (w & 0x10000u) != 0;
+    if (!gg) {
+      bv = *reinterpret_cast<const double*>(Bb + (w >> 16));
+    } else {
+      const double* wa = reinterpret_cast<const double*>(Gb + ((w >> 16) & 0xFFF8u) * P);
+#pragma unroll
+      for (int p = 0; p < P; ++p) bw[p] = wa[p];
+    }
+    const char* ga = Gb + (w & 0xFFFFu) * P;
+    double gv[P];
+    if constexpr (P == 1) {
+      gv[0] = *reinterpret_cast<const double*>(ga);
+    } else {
+#pragma unroll
+      for (int p = 0; p < P; p += 2) {
+        const double2 t = *reinterpret_cast<const double2*>(ga + 8 * p);
+        gv[p] = t.x;
+        gv[p + 1] = t.y;
+      }
+    }
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      const double v = gv[p] * ((GG && gg) ? bw[p] : bv);
+      nf[p] = fma(v, 0.0, nf[p]);
+      so[p][off] = v;
+    }
+  };
+  int off = 0;
+  while (left > 0) {
+    const int left_next = left - U * NT;
+    uint32_t dn[U];
+    if (left_next > 0) LoadDescriptors<NT>(ent + U * NT, left_next, dn);
+    if (left > (U - 1) * NT) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) emit(d[u], off + u * NT);
+    } else {
+#pragma unroll
+      for (int u = 0; u < U - 1; ++u)
+        if (left > u * NT) emit(d[u], off + u * NT);
+    }
+    if (left_next <= 0) break;
+#pragma unroll
+    for (int u = 0; u < U; ++u) d[u] = dn[u];
+    left = left_next;
+    ent += U * NT;
+    off += U * NT;
+  }
+}
+
+// P problems are evaluated in lock step by one CTA of 256*P threads: the class tables are held once per SM, every
+// stage spreads (item, problem) pairs over all threads, and in stage B one descriptor load and one B load feed the
+// P problems.  All per-problem shared arrays are interleaved (element i of problem p at [i*P + p]).
+// RT: structure classes with optimised phase durations (stage D below; items.cuh Lockstep<P, true>).
+template <int WHAT, int P, bool RT, bool BULK = false>
+__global__ void __launch_bounds__(kThreads * P, (P == 1 && !BULK) ? 2 : 1)   // one lane: two CTAs per SM (128 registers each)
+EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restrict__ pcs, const double* __restrict__ x,
+           double* __restrict__ g_out, double* __restrict__ vals_out, int* __restrict__ status, int n_problems) {
+  constexpr int NT = kThreads * P;
+  extern __shared__ uint4 sm4[];
+  unsigned char* blob = reinterpret_cast<unsigned char*>(sm4);
+  const int nnv = Pg.blob.n_node_values, npoly = Pg.blob.n_polys;
+  double* nodes = reinterpret_cast<double*>(blob + Pg.blob.bytes);
+  double* coef = nodes + nnv * P;
+  double* rtd = coef + 6 * npoly * P;                   // RT: 5 per polynomial, then the phase durations
+  double* pdur = rtd + (RT ? 5 * npoly * P : 0);
+  double* G = pdur + (RT ? Pg.blob.n_pdur * P : 0);
+  // BULK: G shares a joint region with the staging buffer, which is aligned to the region's (16-byte aligned) end
+  double* const joint_end = reinterpret_cast<double*>(reinterpret_cast<uintptr_t>(G + Pg.joint_capacity * P) & ~static_cast<uintptr_t>(15));
+  __shared__ ProblemConst pc_all[P];
+  __shared__ int bad_all[P];
+  const int tid = threadIdx.x;
+
+  // class tables: one 16-byte-vector copy per CTA, reused for every problem group this CTA evaluates
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(Pg.blob_data);
+    for (int i = tid; i < Pg.blob.bytes / 16; i += NT) sm4[i] = __ldg(src + i);
+  }
+  __syncthreads();
+  TB_MARK_INIT
+  ItemCtx<Lockstep<P, RT>> cx;
+  cx.n_ee = Pg.n_ee;
+  cx.T = MakeTables(blob, Pg.blob);
+  const double* Bs = cx.T.B;
+  const int pl = tid % P;                               // problem lane of this thread in stages N, C, A
+
+  // stage N: node values from x (values that are not optimised are pinned to 0), fetched asynchronously: for the first
+  // group here, for every later group while the previous group's last stage B runs (nodes[] is free by then)
+  auto fetch_group = [&](int base_n) {
+    const double* xn = x + static_cast<size_t>(min(base_n + pl, n_problems - 1)) * Pg.n_vars;
+    for (int i = tid; i < nnv * P; i += NT) {
+      const unsigned src = cx.T.node_src[i / P];
+      CpAsync8(nodes + i, xn + (src != 0xFFFFu ? src : 0u), src != 0xFFFFu ? 8 : 0);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    if (tid < P) pc_all[tid] = pcs[min(base_n + tid, n_problems - 1)];
+  };
+  if (blockIdx.x * P < n_problems) fetch_group(blockIdx.x * P);
+
+  for (int base = blockIdx.x * P; base < n_problems; base += gridDim.x * P) {
+    // the last group may hold fewer than P problems: the spare lanes recompute the last problem (same values to
+    // the same addresses) so that no stage needs a bounds test
+    const int prob = min(base + pl, n_problems - 1);
+    cx.nodes = nodes + pl;
+    cx.coef = coef + pl;
+    cx.G = G + pl;
+    cx.rtd = rtd + pl;
+    cx.pdur = pdur + pl;
+    cx.pc = &pc_all[pl];
+    cx.g = (WHAT & TOWR_B200_EVAL_G) ? g_out + static_cast<size_t>(prob) * Pg.n_rows : nullptr;
+    double nf[P];
+#pragma unroll
+    for (int p = 0; p < P; ++p) nf[p] = 0.0;
+    double nfx = 0.0;                                     // non-finite x of problem lane pl
+    if (tid < P) bad_all[tid] = 0;
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    TB_MARK(0)
+    __syncthreads();
+    TB_MARK(1)
+
+    // ---- stage D (optimised durations): phase durations from x (phase_durations.cc:78-100: the last one is
+    // T - sum of the others), then every polynomial's duration T, T^2, T^3, 1/T^2, 1/T^3
+    // (ConvertPhaseToPolyDurations, nodes_variables_phase_based.cc:75-86; base splines keep their class constants)
+    if constexpr (RT) {
+      const double* xg = x + static_cast<size_t>(prob) * Pg.n_vars;
+      if (tid < Pg.blob.n_rt_feet * P) {
+        const RtFoot ft = cx.T.rt_feet[tid / P];
+        double sum = 0.0;
+        for (int i = 0; i < ft.n_phases - 1; ++i) {
+          const double d = __ldg(xg + ft.col0 + i);
+          nfx = fma(d, 0.0, nfx);
+          pdur[(ft.phase0 + i) * P + pl] = d;
+          sum += d;
+        }
+        pdur[(ft.phase0 + ft.n_phases - 1) * P + pl] = Pg.total_time - sum;
+      }
+      __syncthreads();
+      for (int i = tid; i < npoly * P; i += NT) {
+        const int poly = i / P;
+        const uint32_t pm = cx.T.poly_meta[poly];
+        double* o = rtd + poly * 5 * P + pl;
+        if (pm == kPolyFixed) {
+          const int di = cx.T.polys[poly] >> 16;
+          o[0] = cx.T.durs[3 * di]; o[P] = cx.T.durs[3 * di + 1]; o[2 * P] = cx.T.durs[3 * di + 2];
+          o[3 * P] = cx.T.rdurs[2 * di]; o[4 * P] = cx.T.rdurs[2 * di + 1];
+        } else {
+          const RtFoot ft = cx.T.rt_feet[pm >> 24];
+          const double Td = pdur[(ft.phase0 + (pm & 0xFF)) * P + pl] / static_cast<double>((pm >> 8) & 0xFF);
+          const double T2 = Td * Td, T3 = Cube(Td);
+          o[0] = Td; o[P] = T2; o[2 * P] = T3; o[3 * P] = 1.0 / T2; o[4 * P] = 1.0 / T3;
+        }
+      }
+      __syncthreads();
+    }
+
+    // ---- stage C: c = -(3(p0-p1) + T(2 v0 + v1))/T^2, d = (2(p0-p1) + T(v0+v1))/T^3   (polynomial.cc:97-104)
+    for (int i = tid; i < 3 * npoly * P; i += NT) {
+      const int pd = i / P;                             // (poly, dim) pair; i % P == pl
+      const int poly = pd / 3, d = pd - 3 * poly;
+      const uint32_t pr = cx.T.polys[poly];
+      const int n0 = pr & 0xFFFF;
+      double T, T2, T3, r2, r3;
+      if constexpr (RT) {
+        const double* o = rtd + poly * 5 * P + pl;
+        T = o[0]; T2 = o[P]; T3 = o[2 * P]; r2 = o[3 * P]; r3 = o[4 * P];
+      } else {
+        const double* du = cx.T.durs + 3 * (pr >> 16);
+        const double* rd = cx.T.rdurs + 2 * (pr >> 16);
+        T = du[0]; T2 = du[1]; T3 = du[2]; r2 = rd[0]; r3 = rd[1];
+      }
+      const double* nd = nodes + pl;
+      const double p0 = nd[(n0 * 6 + d) * P], v0 = nd[(n0 * 6 + 3 + d) * P];
+      const double p1 = nd[(n0 * 6 + 6 + d) * P], v1 = nd[(n0 * 6 + 9 + d) * P];
+      nfx = fma(p0, 0.0, fma(v0, 0.0, fma(p1, 0.0, fma(v1, 0.0, nfx))));   // NaN iff a node value is not finite
+      coef[(poly * 6 + d) * P + pl] = ExactDiv(-(3.0 * (p0 - p1) + T * (2.0 * v0 + v1)), T2, r2);
+      coef[(poly * 6 + 3 + d) * P + pl] = ExactDiv(2.0 * (p0 - p1) + T * (v0 + v1), T3, r3);
+    }
+    TB_MARK(2)
+    __syncthreads();
+    TB_MARK(3)
+
+    for (int s = 0; s < Pg.n_segments; ++s) {
+      const SegmentRec sg = cx.T.segments[s];
+      // ---- stage A, level 0 then level 1: thread -> (item, problem lane)
+      if (tid < P) { G[kGOne * P + tid] = 1.0; G[kGMass * P + tid] = pc_all[tid].mass; G[kGMinusOne * P + tid] = -1.0; }
+      for (int i = tid; i < sg.n_items0 * P; i += NT) RunItem<Lockstep<P, RT>>(cx, cx.T.items[sg.item0 + i / P]);
+      TB_MARK(8 + 6 * s)
+      if (sg.n_items > sg.n_items0) {
+        __syncthreads();
+        TB_MARK(9 + 6 * s)
+        for (int i = tid; i < (sg.n_items - sg.n_items0) * P; i += NT)
+          RunItem<Lockstep<P, RT>>(cx, cx.T.items[sg.item0 + sg.n_items0 + i / P]);
+        TB_MARK(10 + 6 * s)
+      }
+      // first descriptor batch of stage B: issued before the barrier, consumed after it
+      const uint32_t* ent = Pg.entries + sg.entry0 + tid;
+      uint32_t d0[kDescBatch];
+      if (WHAT & TOWR_B200_EVAL_JAC) LoadDescriptors<NT>(ent, sg.n_entries - tid, d0);
+      // BULK: the TMA engine must have read the previous segment's values out of the staging buffer
+      if (BULK && (WHAT & TOWR_B200_EVAL_JAC) && tid < P) BulkWaitRead();
+      __syncthreads();
+      TB_MARK(11 + 6 * s)
+      // all items of this group are done with nodes[] / pc_all after the last segment's stage A: fetch the next group
+      if (s == Pg.n_segments - 1 && base + gridDim.x * P < n_problems) fetch_group(base + gridDim.x * P);
+      // ---- stage B: value_p = G_p[g] * B[b] for the P problems: one descriptor and one B load feed P coalesced stores
+      if constexpr (BULK) {
+        if (WHAT & TOWR_B200_EVAL_JAC) {
+          // first destination element of each lane and its 8-byte parity (spare lanes of a short group repeat the last problem)
+          const int sst = StagingStride(sg.n_entries);
+          double* const stg = joint_end - P * sst;
+          double* so[P];
+#pragma unroll
+          for (int p = 0; p < P; ++p) {
+            const size_t e0 = static_cast<size_t>(min(base + p, n_problems - 1)) * Pg.nnz + sg.entry0;
+            const int q = static_cast<int>(((reinterpret_cast<uintptr_t>(vals_out) >> 3) + e0) & 1);
+            so[p] = stg + p * sst + q + tid;
+          }
+          StageBShared<P, NT, RT>(ent, sg.n_entries - tid, d0, G, Bs, so, nf);
+          FenceProxyAsync();
+        }
+        TB_MARK(12 + 6 * s)
+        __syncthreads();
+        TB_MARK(13 + 6 * s)
+        if ((WHAT & TOWR_B200_EVAL_JAC) && tid < P && base + tid < n_problems) {
+          const size_t e0 = static_cast<size_t>(base + tid) * Pg.nnz + sg.entry0;
+          double* dst = vals_out + e0;
+          const int q = static_cast<int>(((reinterpret_cast<uintptr_t>(vals_out) >> 3) + e0) & 1);
+          const int sst = StagingStride(sg.n_entries);
+          const double* src = joint_end - P * sst + tid * sst + q;   // entry i of the segment at src[i]
+          const int ne = sg.n_entries;
+          if (q) dst[0] = src[0];                             // odd first element: plain store
+          const int body = (ne - q) & ~1;
+          if (body > 0) BulkStore(dst + q, src + q, static_cast<unsigned>(body) * 8u);
+          if ((ne - q) & 1) dst[ne - 1] = src[ne - 1];        // odd last element
+          BulkCommit();
+        }
+      } else {
+        if (WHAT & TOWR_B200_EVAL_JAC) {
+          double* o0 = vals_out + static_cast<size_t>(base) * Pg.nnz + sg.entry0 + tid;
+          if (n_problems - base >= P)
+            StageB<P, true, NT, RT>(ent, sg.n_entries - tid, d0, G, Bs, o0, Pg.nnz, P, nf);
+          else
+            StageB<P, false, NT, RT>(ent, sg.n_entries - tid, d0, G, Bs, o0, Pg.nnz, n_problems - base, nf);
+        }
+        TB_MARK(12 + 6 * s)
+        __syncthreads();
+        TB_MARK(13 + 6 * s)
+      }
+    }
+    if (nfx != nfx) atomicOr(&bad_all[pl], 1);
+#pragma unroll
+    for (int p = 0; p < P; ++p)
+      if (nf[p] != nf[p]) atomicOr(&bad_all[p], 1);
+    __syncthreads();
+    if (tid < P && bad_all[tid] && base + tid < n_problems) atomicOr(status + base + tid, 2);
+  }
+  // the staging buffer must outlive the bulk copies that read it
+  if (BULK && (WHAT & TOWR_B200_EVAL_JAC) && tid < P) BulkWaitAll();
+}
+
+}  // namespace tb

@@ -113,6 +113,20 @@ struct SegmentRec {
   int pad2;
 };
 
+// Bulk-store kernel: G sits at the front of a joint region, the staging buffer of segment s at its end.  The TMA engine
+// still reads segment s's staged values while stage A of segment s + 1 (cyclically) fills G, so the region must hold
+// max(g_s, g_{s+1}) + staging_s elements per problem lane.
+TB_PHD inline int StagingStride(int n_entries) { return (n_entries + 3) & ~1; }   // + parity slack, even
+inline int JointCapacity(const SegmentRec* sg, int n) {
+  int cap = 0;
+  for (int s = 0; s < n; ++s) {
+    const int g = sg[s].g_size > sg[(s + 1) % n].g_size ? sg[s].g_size : sg[(s + 1) % n].g_size;
+    const int need = g + StagingStride(sg[s].n_entries) + 2;
+    if (need > cap) cap = need;
+  }
+  return cap;
+}
+
 // slots 0.. of every segment's G buffer
 enum { kGOne = 0, kGMass = 1, kGMinusOne = 2, kGReserved = 3 };
 
@@ -166,6 +180,7 @@ struct DeviceProgram {  // pointers into device memory (one copy per GPU)
   int n_vars, n_rows, nnz, n_ee;
   int n_segments;
   int g_capacity;       // max g_size over segments
+  int joint_capacity;   // bulk-store kernel: elements per problem lane of the region G and the staging buffer share (JointCapacity)
   double total_time;
   BlobLayout blob;
   const unsigned char* blob_data;

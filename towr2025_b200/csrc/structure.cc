@@ -266,6 +266,9 @@ class Builder {
   const towr_b200_spec& s_;
   HostProgram& hp_;
   const std::vector<char>* plan_;
+ public:
+  int rom_feet_per_group = 0;   // 0: all feet of a sample share one RomPre item (one group); else groups of this many feet
+ private:
   std::map<uint64_t, int> b1_;
   std::map<std::string, int> brun_;
   std::vector<std::vector<std::pair<int, Term>>> rows_;
@@ -506,20 +509,23 @@ void Builder::EmitRom() {
   const VarSet& ang = Set(kBaseAng);
   const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_range_of_motion);
   const int K = static_cast<int>(ts.size());
-  BeginGroup();
   struct PerSample { int pre; SplineAt al, aa; };
   std::vector<PerSample> ps(K);
-  for (int k = 0; k < K; ++k) {
-    ItemRec it = NewItem(kItemRomPre);
-    ps[k].pre = AllocG(kRomPreSize);
-    it.gslot = ps[k].pre;
-    ps[k].al = At(lin, ts[k]);
-    ps[k].aa = At(ang, ts[k]);
-    it.s[kSBaseLin] = ps[k].al.sample;
-    it.s[kSBaseAng] = ps[k].aa.sample;
-    hp_.items.push_back(it);
-  }
+  const int fpg = rom_feet_per_group > 0 ? rom_feet_per_group : E;
   for (int e = 0; e < E; ++e) {
+    if (e % fpg == 0) {                                    // a new group with its own RomPre items
+      BeginGroup();
+      for (int k = 0; k < K; ++k) {
+        ItemRec it = NewItem(kItemRomPre);
+        ps[k].pre = AllocG(kRomPreSize);
+        it.gslot = ps[k].pre;
+        ps[k].al = At(lin, ts[k]);
+        ps[k].aa = At(ang, ts[k]);
+        it.s[kSBaseLin] = ps[k].al.sample;
+        it.s[kSBaseAng] = ps[k].aa.sample;
+        hp_.items.push_back(it);
+      }
+    }
     const VarSet& mo = Set(kEEMotion, e);
     BeginSet("rangeofmotion-" + std::to_string(e), 3 * K);
     for (int k = 0; k < K; ++k) {
@@ -907,13 +913,28 @@ std::string StructureSignature(const towr_b200_spec& s) {
   return o.str();
 }
 
-void BuildProgram(const towr_b200_spec& s, HostProgram& hp, int g_cap) {
+void BuildProgram(const towr_b200_spec& s, HostProgram& hp, int g_cap, int joint_cap) {
   BuildLayout(s, hp);
   hp.signature = StructureSignature(s);
   // pass 1: one segment per group, to learn each group's G footprint
   ResetTables(hp);
+  // bulk-store kernel: the range-of-motion sets of all feet in one group may exceed the joint budget: group fewer feet
+  int rom_fpg = 0;
+  if (joint_cap > 0 && !hp.optimize_durations) {
+    const double T = hp.total_time, dt = s.dt_constraint_range_of_motion;
+    const long long K = static_cast<long long>(T / dt) + 2;
+    for (int f = s.n_ee; f >= 1; f = f > 2 ? f / 2 : f - 1) {
+      rom_fpg = f;
+      if (K * (kRomPreSize + 9 * f) + f * K * 90 <= joint_cap * 9LL / 10) break;
+    }
+    if (rom_fpg == s.n_ee) rom_fpg = 0;
+  }
   Builder sizing(s, hp, nullptr);
+  sizing.rom_feet_per_group = rom_fpg;
   sizing.Run();
+  std::vector<int> group_entries;                          // one segment per group in this pass
+  for (const SegmentRec& sg : hp.segments) group_entries.push_back(sg.n_entries);
+  group_entries.resize(sizing.group_g_size.size(), 0);
   // G slots per segment.  Every segment costs the kernel a fixed stage-A latency, so use as few segments as the
   // 16-bit byte offsets of the entry descriptors allow (8191 slots) and balance them.  TOWR_B200_GCAP overrides.
   const int cap_max = 8000;
@@ -932,8 +953,32 @@ void BuildProgram(const towr_b200_spec& s, HostProgram& hp, int g_cap) {
     }
     return n;
   };
+  // bulk-store kernel: a segment's G slots and its staged values share one budget (joint_cap elements per problem)
+  auto plan_joint = [&](int cap, std::vector<char>& plan) {
+    int used = kGReserved + 2, used_g = kGReserved, n = 0;
+    for (size_t g = 0; g < plan.size(); ++g) {
+      const int need = sizing.group_g_size[g] + group_entries[g];
+      plan[g] = 0;
+      if (g == 0 || used + need > cap || used_g + sizing.group_g_size[g] > cap_max) {
+        plan[g] = 1;
+        used = kGReserved + 2;
+        used_g = kGReserved;
+        ++n;
+      }
+      used += need;
+      used_g += sizing.group_g_size[g];
+    }
+    return n;
+  };
   std::vector<char> plan(sizing.group_g_size.size(), 0);
-  if (g_cap > 0) {
+  if (joint_cap > 0) {
+    const int n_min = plan_joint(joint_cap, plan);
+    int lo = 0;
+    for (size_t g = 0; g < plan.size(); ++g) lo = std::max(lo, sizing.group_g_size[g] + group_entries[g] + kGReserved + 2);
+    int cap = std::max(lo, (total + hp.nnz) / std::max(1, n_min));
+    while (cap < joint_cap && plan_joint(cap, plan) > n_min) cap += 32;   // balanced: smallest budget with n_min segments
+    if (cap >= joint_cap) plan_joint(joint_cap, plan);
+  } else if (g_cap > 0) {
     plan_with(std::max(largest + kGReserved, g_cap), plan);
   } else if (const char* env = std::getenv("TOWR_B200_GCAP")) {
     plan_with(std::max(64, std::atoi(env)), plan);
@@ -946,10 +991,11 @@ void BuildProgram(const towr_b200_spec& s, HostProgram& hp, int g_cap) {
   // pass 2: the real tables
   ResetTables(hp);
   Builder real(s, hp, &plan);
+  real.rom_feet_per_group = rom_fpg;
   real.Run();
   if (std::getenv("TOWR_B200_DEBUG")) {
     std::fprintf(stderr, "groups:");
-    for (int g : sizing.group_g_size) std::fprintf(stderr, " %d", g);
+    for (size_t g = 0; g < sizing.group_g_size.size(); ++g) std::fprintf(stderr, " %d/%d", sizing.group_g_size[g], group_entries[g]);
     std::fprintf(stderr, "\n");
     for (const SegmentRec& sg : hp.segments)
       std::fprintf(stderr, "segment items %d (level0 %d) entries %d g %d\n", sg.n_items, sg.n_items0, sg.n_entries, sg.g_size);
