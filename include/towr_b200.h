@@ -151,6 +151,23 @@ long long towr_b200_batch_launch_count(const towr_b200_batch* b);
 /* the batch's own non-blocking cudaStream_t (the one towr_b200_batch_eval works on) */
 void* towr_b200_batch_stream(const towr_b200_batch* b);
 
+/* ---- trajectory sampling: the step on the far side of the solver -------------------------------------------------
+ * Replaces towr::SaveTrajectoryToCSV's sampling loop (towr/src/utils/save_data.cpp:54-119), i.e. SplineHolder's
+ * NodeSpline::GetPoint (towr/src/variables/spline.cc:80-93, towr/include/towr/variables/spline_holder.h:48-84) and
+ * PhaseDurations::IsContactPhase (towr/src/variables/phase_durations.cc:113-118), for a whole batch of solution
+ * vectors x.  One row per sample time t = 0, dt, 2 dt, ... <= T + 1e-9 (repeated addition, save_data.cpp:55,118):
+ *   time | base pos, vel, acc | base euler, rates, accelerations | per foot: pos, vel, acc, euler, rates, accelerations,
+ *   contact force, contact torque, is_contact                       (19 + 25 n_ee columns, save_data.cpp:27-46) */
+int towr_b200_trajectory_width(const towr_b200_structure* st);
+int towr_b200_trajectory_samples(const towr_b200_structure* st, double dt);          /* rows per problem, < 0 on error */
+/* host buffers: x is n x n_vars, rows_out is n x samples x width, both row-major */
+int towr_b200_batch_sample_trajectory(towr_b200_batch* b, int n, double dt, const double* x, double* rows_out);
+/* device buffers already on the batch's device; stream NULL = the default stream */
+int towr_b200_batch_sample_trajectory_device(towr_b200_batch* b, int n, double dt, const double* d_x, double* d_rows,
+                                             void* stream);
+/* one problem's rows in the reference's CSV format (header line, std::fixed, 6 decimals; save_data.cpp:24-46,68-116) */
+int towr_b200_trajectory_write_csv(const towr_b200_structure* st, const double* rows, int n_rows, const char* filename);
+
 #ifdef __cplusplus
 }
 #endif

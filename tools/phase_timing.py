@@ -18,7 +18,7 @@ import towr2025_b200 as T  # noqa: E402
 
 def main():
     batch = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
-    s0 = T.make_spec(T.Anymal, T.C1, 2.0)
+    s0 = T.make_spec(T.Anymal, T.C1, 2.0, optimize_durations=len(sys.argv) > 2 and sys.argv[2] == "durations")
     st = T.Structure(s0)
     b = T.Batch(st, batch, 0)
     b.set_all(s0)

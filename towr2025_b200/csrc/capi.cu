@@ -3,6 +3,9 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <fstream>
+#include <iomanip>
+#include <map>
 #include <cstdlib>
 #include <cstring>
 #include <exception>
@@ -13,6 +16,7 @@
 
 #include "kernels.h"
 #include "structure.h"
+#include "trajectory.h"
 
 namespace tb {
 void SpecDefaults(towr_b200_spec* s);
@@ -88,6 +92,11 @@ struct towr_b200_batch {
   bool bulk = false;       // bulk-store kernel (kernels_tma.cu)
   std::unique_ptr<tb::HostProgram> hp_local;   // program rebuilt with a smaller G capacity (large class tables)
   long long launches = 0;
+  // trajectory sampler tables per sampling period (trajectory.h)
+  struct Traj { tb::TrajTables host; tb::TrajDevice dev; };
+  std::map<double, std::unique_ptr<Traj>> traj;
+  double* traj_out_dev = nullptr;
+  size_t traj_out_cap = 0;
 
   void SyncConsts() {
     if (!pc_dirty) return;
@@ -394,6 +403,130 @@ int towr_b200_batch_status(towr_b200_batch* b, int n, int* status_out) {
     Check(cudaSetDevice(b->device), "cudaSetDevice");
     Check(cudaMemcpy(status_out, b->status_dev, sizeof(int) * n, cudaMemcpyDeviceToHost), "D2H status");
     Check(cudaMemset(b->status_dev, 0, sizeof(int) * n), "reset status");
+  });
+}
+
+// ---- trajectory sampling -------------------------------------------------------------------------------------------
+int towr_b200_trajectory_width(const towr_b200_structure* st) { return st ? tb::TrajectoryWidth(st->hp.n_ee) : -1; }
+
+int towr_b200_trajectory_samples(const towr_b200_structure* st, double dt) {
+  int n = -1;
+  const int rc = Guard([&] {
+    if (!st) throw std::runtime_error("null structure");
+    n = static_cast<int>(tb::TrajectoryTimes(st->hp, dt).size());
+  });
+  return rc == TOWR_B200_OK ? n : -1;
+}
+
+namespace {
+template <class T>
+const T* UploadVec(towr_b200_batch* b, const std::vector<T>& v) {
+  if (v.empty()) return nullptr;
+  T* d = nullptr;
+  Check(cudaMalloc(&d, sizeof(T) * v.size()), "cudaMalloc(trajectory tables)");
+  b->owned.push_back(d);
+  Check(cudaMemcpy(d, v.data(), sizeof(T) * v.size(), cudaMemcpyHostToDevice), "H2D trajectory tables");
+  return d;
+}
+
+const towr_b200_batch::Traj& TrajFor(towr_b200_batch* b, double dt) {
+  auto it = b->traj.find(dt);
+  if (it != b->traj.end()) return *it->second;
+  auto t = std::make_unique<towr_b200_batch::Traj>();
+  tb::BuildTrajTables(b->st->hp, b->st->spec, dt, t->host);
+  const tb::TrajTables& h = t->host;
+  tb::TrajDevice& d = t->dev;
+  d.n_vars = h.n_vars; d.n_ee = h.n_ee; d.width = h.width; d.n_samples = h.n_samples;
+  d.n_splines = static_cast<int>(h.splines.size());
+  d.n_nodes = h.n_nodes; d.n_polys = h.n_polys; d.n_phases = h.n_phases; d.rt = h.rt ? 1 : 0;
+  d.total_time = h.total_time;
+  d.times = UploadVec(b, h.times);
+  d.splines = UploadVec(b, h.splines);
+  d.feet = UploadVec(b, h.feet);
+  d.node_src = UploadVec(b, h.node_src);
+  d.poly_T = UploadVec(b, h.poly_T);
+  d.poly_meta = UploadVec(b, h.poly_meta);
+  d.samp_poly = UploadVec(b, h.samp_poly);
+  d.samp_t = UploadVec(b, h.samp_t);
+  d.contact = UploadVec(b, h.contact);
+  cudaDeviceProp prop;
+  Check(cudaGetDeviceProperties(&prop, b->device), "cudaGetDeviceProperties");
+  if (tb::TrajSharedBytes(d) > prop.sharedMemPerBlockOptin)
+    throw std::runtime_error("unsupported: the problem's spline tables exceed the SM's shared memory");
+  return *(b->traj[dt] = std::move(t));
+}
+}  // namespace
+
+int towr_b200_batch_sample_trajectory_device(towr_b200_batch* b, int n, double dt, const double* d_x, double* d_rows,
+                                             void* stream) {
+  return Guard([&] {
+    if (!b || n < 0 || n > b->n) throw std::runtime_error("bad problem count");
+    if (!d_x || !d_rows) throw std::runtime_error("null device buffer");
+    Check(cudaSetDevice(b->device), "cudaSetDevice");
+    const towr_b200_batch::Traj& t = TrajFor(b, dt);
+    int sms = 0;
+    Check(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device), "device attribute");
+    Check(tb::LaunchSampleTrajectory(t.dev, d_x, d_rows, n, 2 * sms, static_cast<cudaStream_t>(stream)), "launch");
+    b->launches += 1;
+  });
+}
+
+int towr_b200_batch_sample_trajectory(towr_b200_batch* b, int n, double dt, const double* x, double* rows_out) {
+  return Guard([&] {
+    if (!b || n < 0 || n > b->n) throw std::runtime_error("bad problem count");
+    if (!x || !rows_out) throw std::runtime_error("null host buffer");
+    if (n == 0) return;
+    Check(cudaSetDevice(b->device), "cudaSetDevice");
+    const towr_b200_batch::Traj& t = TrajFor(b, dt);
+    const size_t per = static_cast<size_t>(t.dev.n_samples) * t.dev.width;
+    if (!b->x_dev) {
+      Check(cudaMalloc(&b->x_dev, sizeof(double) * b->dp.n_vars * b->n), "cudaMalloc(staging)");
+      b->owned.push_back(b->x_dev);
+    }
+    if (b->traj_out_cap < per * n) {
+      double* p = nullptr;
+      Check(cudaMalloc(&p, sizeof(double) * per * b->n), "cudaMalloc(trajectory rows)");
+      b->owned.push_back(p);
+      b->traj_out_dev = p;
+      b->traj_out_cap = per * b->n;
+    }
+    Check(cudaMemcpyAsync(b->x_dev, x, sizeof(double) * b->dp.n_vars * n, cudaMemcpyHostToDevice, b->stream), "H2D x");
+    int sms = 0;
+    Check(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device), "device attribute");
+    Check(tb::LaunchSampleTrajectory(t.dev, b->x_dev, b->traj_out_dev, n, 2 * sms, b->stream), "launch");
+    b->launches += 1;
+    Check(cudaMemcpyAsync(rows_out, b->traj_out_dev, sizeof(double) * per * n, cudaMemcpyDeviceToHost, b->stream), "D2H rows");
+    Check(cudaStreamSynchronize(b->stream), "sample_trajectory");
+  });
+}
+
+int towr_b200_trajectory_write_csv(const towr_b200_structure* st, const double* rows, int n_rows, const char* filename) {
+  return Guard([&] {
+    if (!st || !rows || n_rows < 0 || !filename) throw std::runtime_error("bad argument");
+    const int E = st->hp.n_ee, W = tb::TrajectoryWidth(E);
+    std::ofstream f(filename);
+    if (!f.is_open()) throw std::runtime_error(std::string("cannot create ") + filename);
+    f << std::fixed << std::setprecision(6);
+    f << "time,base_pos_x,base_pos_y,base_pos_z,base_vel_x,base_vel_y,base_vel_z,base_acc_x,base_acc_y,base_acc_z,"
+      << "base_euler_roll,base_euler_pitch,base_euler_yaw,base_omega_x,base_omega_y,base_omega_z,"
+      << "base_omegadot_x,base_omegadot_y,base_omegadot_z";
+    static const char* kCols[8] = {"ee_pos", "ee_vel", "ee_acc", "ee_euler", "ee_omega", "ee_omegadot", "contact_force", "contact_torque"};
+    static const char* kAxes[2][3] = {{"x", "y", "z"}, {"roll", "pitch", "yaw"}};
+    for (int i = 0; i < E; ++i) {
+      for (int c = 0; c < 8; ++c)
+        for (int d = 0; d < 3; ++d) f << "," << kCols[c] << "_" << kAxes[c == 3 ? 1 : 0][d] << "_" << i;
+      f << ",is_contact_phase_" << i;
+    }
+    f << std::endl;
+    for (int k = 0; k < n_rows; ++k) {
+      const double* r = rows + static_cast<size_t>(k) * W;
+      for (int c = 0; c < W; ++c) {
+        if (c) f << ",";
+        if (c >= 19 && (c - 19) % 25 == 24) f << (r[c] != 0.0 ? 1 : 0);   // is_contact is written as an integer
+        else f << r[c];
+      }
+      f << std::endl;
+    }
   });
 }
 

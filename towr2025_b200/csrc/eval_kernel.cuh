@@ -13,7 +13,7 @@ namespace tb {
 // FULL: all P problem lanes of the group exist (no per-store predicate).
 // nf[p] accumulates value * 0 per problem lane: NaN exactly when a stored value is not finite (status bit 2).
 template <int P, bool FULL, int NT, bool GG = false>
-__device__ __forceinline__ void StageB(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[kDescBatch],
+__device__ __forceinline__ void StageB(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[DescAhead<GG>::value][kDescBatch],
                                        const double* G, const double* Bs, double* __restrict__ o, int nnz, int np,
                                        double (&nf)[P]) {
   constexpr int U = kDescBatch;
@@ -50,24 +50,25 @@ __device__ __forceinline__ void StageB(const uint32_t* __restrict__ ent, int lef
       if (FULL || p < np) op[static_cast<size_t>(p) * nnz] = v;
     }
   };
-  while (left > 0) {
-    const int left_next = left - U * NT;
-    uint32_t dn[U];
-    if (left_next > 0) LoadDescriptors<NT>(ent + U * NT, left_next, dn);
-    if (left > (U - 1) * NT) {
+  constexpr int A = DescAhead<GG>::value;
+  while (true) {
 #pragma unroll
-      for (int u = 0; u < U; ++u) emit(d[u], o + u * NT);
-    } else {
+    for (int a = 0; a < A; ++a) {                         // batch in d[a]; refilled with the batch A further on
+      if (left <= 0) return;
+      if (left > (U - 1) * NT) {
 #pragma unroll
-      for (int u = 0; u < U - 1; ++u)
-        if (left > u * NT) emit(d[u], o + u * NT);
+        for (int u = 0; u < U; ++u) emit(d[a][u], o + u * NT);
+      } else {
+#pragma unroll
+        for (int u = 0; u < U - 1; ++u)
+          if (left > u * NT) emit(d[a][u], o + u * NT);
+      }
+      const int left_a = left - A * U * NT;
+      if (left_a > 0) LoadDescriptors<NT>(ent + A * U * NT, left_a, d[a]);
+      left -= U * NT;
+      ent += U * NT;
+      o += U * NT;
     }
-    if (left_next <= 0) break;
-#pragma unroll
-    for (int u = 0; u < U; ++u) d[u] = dn[u];
-    left = left_next;
-    ent += U * NT;
-    o += U * NT;
   }
 }
 
@@ -87,7 +88,7 @@ __device__ __forceinline__ void BulkWaitAll() { asm volatile("cp.async.bulk.wait
 
 // Stage B into the staging buffer: so[p] = lane p's staging element of entry tid (conflict-free 8-byte stores).
 template <int P, int NT, bool GG>
-__device__ __forceinline__ void StageBShared(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[kDescBatch],
+__device__ __forceinline__ void StageBShared(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[DescAhead<GG>::value][kDescBatch],
                                              const double* G, const double* Bs, double* const (&so)[P], double (&nf)[P]) {
   constexpr int U = kDescBatch;
   const char* Gb = reinterpret_cast<const char*>(G);
@@ -123,25 +124,26 @@ __device__ __forceinline__ void StageBShared(const uint32_t* __restrict__ ent, i
       so[p][off] = v;
     }
   };
+  constexpr int A = DescAhead<GG>::value;
   int off = 0;
-  while (left > 0) {
-    const int left_next = left - U * NT;
-    uint32_t dn[U];
-    if (left_next > 0) LoadDescriptors<NT>(ent + U * NT, left_next, dn);
-    if (left > (U - 1) * NT) {
+  while (true) {
 #pragma unroll
-      for (int u = 0; u < U; ++u) emit(d[u], off + u * NT);
-    } else {
+    for (int a = 0; a < A; ++a) {
+      if (left <= 0) return;
+      if (left > (U - 1) * NT) {
 #pragma unroll
-      for (int u = 0; u < U - 1; ++u)
-        if (left > u * NT) emit(d[u], off + u * NT);
+        for (int u = 0; u < U; ++u) emit(d[a][u], off + u * NT);
+      } else {
+#pragma unroll
+        for (int u = 0; u < U - 1; ++u)
+          if (left > u * NT) emit(d[a][u], off + u * NT);
+      }
+      const int left_a = left - A * U * NT;
+      if (left_a > 0) LoadDescriptors<NT>(ent + A * U * NT, left_a, d[a]);
+      left -= U * NT;
+      ent += U * NT;
+      off += U * NT;
     }
-    if (left_next <= 0) break;
-#pragma unroll
-    for (int u = 0; u < U; ++u) d[u] = dn[u];
-    left = left_next;
-    ent += U * NT;
-    off += U * NT;
   }
 }
 
@@ -150,7 +152,7 @@ __device__ __forceinline__ void StageBShared(const uint32_t* __restrict__ ent, i
 // P problems.  All per-problem shared arrays are interleaved (element i of problem p at [i*P + p]).
 // RT: structure classes with optimised phase durations (stage D below; items.cuh Lockstep<P, true>).
 template <int WHAT, int P, bool RT, bool BULK = false>
-__global__ void __launch_bounds__(kThreads * P, (P == 1 && !BULK) ? 2 : 1)   // one lane: two CTAs per SM (128 registers each)
+__global__ void __launch_bounds__(kThreads * P, (P == 1 && !BULK && !RT) ? 2 : 1)   // one lane: two CTAs per SM (128 registers each)
 EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restrict__ pcs, const double* __restrict__ x,
            double* __restrict__ g_out, double* __restrict__ vals_out, int* __restrict__ status, int n_problems) {
   constexpr int NT = kThreads * P;
@@ -291,8 +293,8 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
       }
       // first descriptor batch of stage B: issued before the barrier, consumed after it
       const uint32_t* ent = Pg.entries + sg.entry0 + tid;
-      uint32_t d0[kDescBatch];
-      if (WHAT & TOWR_B200_EVAL_JAC) LoadDescriptors<NT>(ent, sg.n_entries - tid, d0);
+      uint32_t d0[DescAhead<RT>::value][kDescBatch];
+      if (WHAT & TOWR_B200_EVAL_JAC) LoadDescriptorRing<NT>(ent, sg.n_entries - tid, d0);
       // BULK: the TMA engine must have read the previous segment's values out of the staging buffer
       if (BULK && (WHAT & TOWR_B200_EVAL_JAC) && tid < P) BulkWaitRead();
       __syncthreads();

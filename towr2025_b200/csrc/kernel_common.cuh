@@ -45,14 +45,24 @@ __device__ __forceinline__ bool NonFinite(double v) {
 }
 
 // Stage B of one segment.  Thread t takes entries t, t + NT, ...: a warp's descriptor load and its P stores per
-// entry are coalesced.  Descriptors are fetched kDescBatch at a time, one batch ahead of their use (the first batch
-// before the barrier that ends stage A), so the L2 latency of the descriptor stream is off the critical path.
+// entry are coalesced.  Descriptors are fetched kDescBatch at a time into a register ring of A = DescAhead<RT> batches: a batch
+// is loaded A batches before its use (the first ones before the barrier that ends stage A), so the L2 latency
+// of the descriptor stream - several hundred clocks while the value stores keep the memory pipe busy - stays off the
+// critical path.
+// Classes with optimised durations run one problem per CTA (8 warps): fewer warps to hide the latency, deeper ring.
+template <bool RT> struct DescAhead { static constexpr int value = RT ? 8 : 4; };
 constexpr int kDescBatch = 4;
 
 template <int NT>
 __device__ __forceinline__ void LoadDescriptors(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[kDescBatch]) {
 #pragma unroll
   for (int u = 0; u < kDescBatch; ++u) d[u] = left > u * NT ? __ldg(ent + u * NT) : kNoEntry;
+}
+// the first A batches of a segment (thread's first entry at ent, `left` entries from there on)
+template <int NT, int A>
+__device__ __forceinline__ void LoadDescriptorRing(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[A][kDescBatch]) {
+#pragma unroll
+  for (int a = 0; a < A; ++a) LoadDescriptors<NT>(ent + a * kDescBatch * NT, left - a * kDescBatch * NT, d[a]);
 }
 
 // 8-byte asynchronous global -> shared copy; src_bytes = 0 writes zeros (cp.async zero-fill)

@@ -125,8 +125,8 @@ EvalKernelWS(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __res
         const int buf = k & 1;
         const double* G = Gbuf + buf * gstride;
         const uint32_t* ent = Pg.entries + sg.entry0 + ct;
-        uint32_t d0[kDescBatch];
-        if (WHAT & TOWR_B200_EVAL_JAC) LoadDescriptors<NB>(ent, sg.n_entries - ct, d0);
+        uint32_t d0[DescAhead<false>::value][kDescBatch];
+        if (WHAT & TOWR_B200_EVAL_JAC) LoadDescriptorRing<NB>(ent, sg.n_entries - ct, d0);
         TB_MARK_T(16, NA)
         BarSync(kBarFull + buf, NALL);
         TB_MARK_T(17, NA)
