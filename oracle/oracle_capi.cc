@@ -2,6 +2,7 @@
 #include "oracle_capi.h"
 
 #include <cstring>
+#include <numeric>
 #include <exception>
 #include <stdexcept>
 #include <string>
@@ -303,6 +304,39 @@ void orc_sample_times(double T, double dt, double* out, int* n) {
   } probe(T, dt);
   *n = static_cast<int>(probe.SampleTimes().size());
   if (out) for (int i = 0; i < *n; ++i) out[i] = probe.SampleTimes()[i];
+}
+
+int orc_trajectory_width(const orc_problem* p) { return 19 + 25 * static_cast<int>(p->splines.ee_motion_.size()); }
+
+// utils/save_data.cpp:54-119, column order :68-112
+int orc_sample_trajectory(orc_problem* p, const double* x, double dt, double* rows) {
+  p->nlp.SetVariables(x);
+  const SplineHolder& sol = p->splines;
+  Vec durs = sol.base_linear_->GetPolyDurations();     // Spline::GetTotalTime (spline.cc:118-123)
+  const double T_total = std::accumulate(durs.begin(), durs.end(), 0.0);
+  const int E = static_cast<int>(sol.ee_motion_.size()), W = 19 + 25 * E;
+  int n = 0;
+  double t = 0.0;
+  while (t <= T_total + 1e-9) {
+    if (rows) {
+      double* r = rows + static_cast<size_t>(n) * W;
+      auto put9 = [&](double* o, const State3& st) { for (int d = 0; d < 3; ++d) { o[d] = st.p(d); o[3 + d] = st.v(d); o[6 + d] = st.a(d); } };
+      r[0] = t;
+      put9(r + 1, sol.base_linear_->GetPoint(t));
+      put9(r + 10, sol.base_angular_->GetPoint(t));
+      for (int i = 0; i < E; ++i) {
+        double* o = r + 19 + 25 * i;
+        put9(o, sol.ee_motion_.at(i)->GetPoint(t));
+        put9(o + 9, sol.ee_ang_.at(i)->GetPoint(t));
+        const State3 f = sol.ee_force_.at(i)->GetPoint(t), tq = sol.ee_torque_.at(i)->GetPoint(t);
+        for (int d = 0; d < 3; ++d) { o[18 + d] = f.p(d); o[21 + d] = tq.p(d); }
+        o[24] = sol.phase_durations_.at(i)->IsContactPhase(t) ? 1.0 : 0.0;
+      }
+    }
+    t += dt;
+    ++n;
+  }
+  return n;
 }
 
 }  // extern "C"

@@ -90,6 +90,11 @@ void orc_terrain(int terrain_id, double x, double y, double* height, double* dh 
                  double* dbasis /*3x2x3: [basis][dim][xyz]*/);
 void orc_sample_times(double T, double dt, double* out, int* n);    /* time_discretization_constraint.cc:41-49 */
 
+/* utils/save_data.cpp:9-132 (SaveTrajectoryToCSV): the sampling loop and the values of one CSV row per sample
+ * (19 + 25 n_ee doubles: time, base, per foot ...; is_contact as 0/1).  rows may be NULL; returns the row count. */
+int orc_trajectory_width(const orc_problem* p);
+int orc_sample_trajectory(orc_problem* p, const double* x, double dt, double* rows);
+
 #ifdef __cplusplus
 }
 #endif

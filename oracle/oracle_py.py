@@ -101,6 +101,8 @@ def lib():
     L.orc_hermite_dpos_dT.argtypes = [dp, dp, dp, dp, C.c_double, C.c_double, dp]
     L.orc_terrain.argtypes = [C.c_int, C.c_double, C.c_double, dp, dp, dp, dp]
     L.orc_sample_times.argtypes = [C.c_double, C.c_double, dp, ip]
+    L.orc_trajectory_width.argtypes = [C.c_void_p]
+    L.orc_sample_trajectory.argtypes = [C.c_void_p, dp, C.c_double, dp]
     _lib = L
     return L
 
@@ -172,6 +174,15 @@ class Problem:
         lo, up = np.empty(self.n_rows), np.empty(self.n_rows)
         self._L.orc_con_bounds(self._p, _dp(lo), _dp(up))
         return lo, up
+
+    def sample_trajectory(self, x, dt):
+        """Rows of SaveTrajectoryToCSV (utils/save_data.cpp) for the solution vector x: (n_samples, 19 + 25 n_ee)."""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        w = self._L.orc_trajectory_width(self._p)
+        n = self._L.orc_sample_trajectory(self._p, _dp(x), float(dt), None)
+        rows = np.empty((n, w))
+        self._L.orc_sample_trajectory(self._p, _dp(x), float(dt), _dp(rows))
+        return rows
 
     def eval_g(self, x):
         x = np.ascontiguousarray(x, dtype=np.float64)

@@ -91,7 +91,8 @@ towr_b200_structure_con_set_name towr_b200_structure_con_set_rows towr_b200_stru
 towr_b200_problem_x0 towr_b200_problem_var_bounds towr_b200_problem_con_bounds towr_b200_batch_create
 towr_b200_batch_destroy towr_b200_batch_size towr_b200_batch_set_problem towr_b200_batch_set_all_problems
 towr_b200_batch_eval towr_b200_batch_eval_device towr_b200_batch_status towr_b200_batch_launch_count
-towr_b200_batch_stream""".split()
+towr_b200_batch_stream towr_b200_trajectory_width towr_b200_trajectory_samples towr_b200_batch_sample_trajectory
+towr_b200_batch_sample_trajectory_device towr_b200_trajectory_write_csv""".split()
 
 
 def lib():
@@ -133,6 +134,11 @@ def lib():
     L.towr_b200_batch_eval.argtypes = [vp, ip, C.c_int, C.c_int, dp, dp, dp]
     L.towr_b200_batch_eval_device.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp]
     L.towr_b200_batch_status.argtypes = [vp, C.c_int, ip]
+    L.towr_b200_trajectory_width.argtypes = [vp]
+    L.towr_b200_trajectory_samples.argtypes = [vp, C.c_double]
+    L.towr_b200_batch_sample_trajectory.argtypes = [vp, C.c_int, C.c_double, dp, dp]
+    L.towr_b200_batch_sample_trajectory_device.argtypes = [vp, C.c_int, C.c_double, vp, vp, vp]
+    L.towr_b200_trajectory_write_csv.argtypes = [vp, dp, C.c_int, C.c_char_p]
     L.towr_b200_batch_launch_count.argtypes = [vp]
     L.towr_b200_batch_launch_count.restype = C.c_longlong
     L.towr_b200_batch_stream.argtypes = [vp]
@@ -203,6 +209,22 @@ class Structure:
         return [(L.towr_b200_structure_con_set_name(h, i).decode(), L.towr_b200_structure_con_set_rows(h, i))
                 for i in range(L.towr_b200_structure_n_con_sets(h))]
 
+    def trajectory_width(self):
+        """Columns of one trajectory row (towr_b200_trajectory_width): 19 + 25 n_ee."""
+        return self._L.towr_b200_trajectory_width(self._h)
+
+    def trajectory_samples(self, dt):
+        """Rows per problem for the sampling period dt (towr_b200_trajectory_samples)."""
+        n = self._L.towr_b200_trajectory_samples(self._h, float(dt))
+        if n < 0:
+            raise TowrB200Error(-1, self._L.towr_b200_last_error().decode())
+        return n
+
+    def write_csv(self, rows, filename):
+        """One problem's trajectory rows in the reference's CSV format (towr_b200_trajectory_write_csv)."""
+        rows = np.ascontiguousarray(rows, dtype=np.float64)
+        _check(self._L.towr_b200_trajectory_write_csv(self._h, _dp(rows), rows.shape[0], filename.encode()))
+
     def pattern(self):
         r, c = np.empty(self.nnz, np.int32), np.empty(self.nnz, np.int32)
         _check(self._L.towr_b200_structure_pattern(self._h, _ip(r), _ip(c)))
@@ -268,6 +290,19 @@ class Batch:
             idp = _ip(ids)
         _check(self._L.towr_b200_batch_eval(self._h, idp, n, what, _dp(x), _dp(g), _dp(v)))
         return g, v
+
+    def sample_trajectory(self, x, dt):
+        """Host-buffer trajectory sampling (towr_b200_batch_sample_trajectory): (n, samples, width) rows."""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        n = x.shape[0]
+        rows = np.empty((n, self.structure.trajectory_samples(dt), self.structure.trajectory_width()))
+        _check(self._L.towr_b200_batch_sample_trajectory(self._h, n, float(dt), _dp(x), _dp(rows)))
+        return rows
+
+    def sample_trajectory_device(self, n, dt, d_x, d_rows, stream=None):
+        """Device-pointer trajectory sampling, asynchronous on `stream`."""
+        _check(self._L.towr_b200_batch_sample_trajectory_device(self._h, n, float(dt), C.c_void_p(d_x), C.c_void_p(d_rows),
+                                                                C.c_void_p(stream or 0)))
 
     def eval_device(self, n, what, d_x, d_g, d_vals, stream=None):
         """Device-pointer evaluation (ints from tensor.data_ptr()); asynchronous on `stream`

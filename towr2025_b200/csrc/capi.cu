@@ -418,6 +418,8 @@ int towr_b200_trajectory_samples(const towr_b200_structure* st, double dt) {
   return rc == TOWR_B200_OK ? n : -1;
 }
 
+}  // extern "C"
+
 namespace {
 template <class T>
 const T* UploadVec(towr_b200_batch* b, const std::vector<T>& v) {
@@ -456,6 +458,8 @@ const towr_b200_batch::Traj& TrajFor(towr_b200_batch* b, double dt) {
   return *(b->traj[dt] = std::move(t));
 }
 }  // namespace
+
+extern "C" {
 
 int towr_b200_batch_sample_trajectory_device(towr_b200_batch* b, int n, double dt, const double* d_x, double* d_rows,
                                              void* stream) {
