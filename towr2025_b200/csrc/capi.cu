@@ -448,6 +448,7 @@ const towr_b200_batch::Traj& TrajFor(towr_b200_batch* b, double dt) {
   d.node_src = UploadVec(b, h.node_src);
   d.poly_T = UploadVec(b, h.poly_T);
   d.poly_meta = UploadVec(b, h.poly_meta);
+  d.poly_spline = UploadVec(b, h.poly_spline);
   d.samp_poly = UploadVec(b, h.samp_poly);
   d.samp_t = UploadVec(b, h.samp_t);
   d.contact = UploadVec(b, h.contact);
@@ -470,7 +471,7 @@ int towr_b200_batch_sample_trajectory_device(towr_b200_batch* b, int n, double d
     const towr_b200_batch::Traj& t = TrajFor(b, dt);
     int sms = 0;
     Check(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device), "device attribute");
-    Check(tb::LaunchSampleTrajectory(t.dev, d_x, d_rows, n, 2 * sms, static_cast<cudaStream_t>(stream)), "launch");
+    Check(tb::LaunchSampleTrajectory(t.dev, d_x, d_rows, n, sms, static_cast<cudaStream_t>(stream)), "launch");
     b->launches += 1;
   });
 }
@@ -497,7 +498,7 @@ int towr_b200_batch_sample_trajectory(towr_b200_batch* b, int n, double dt, cons
     Check(cudaMemcpyAsync(b->x_dev, x, sizeof(double) * b->dp.n_vars * n, cudaMemcpyHostToDevice, b->stream), "H2D x");
     int sms = 0;
     Check(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device), "device attribute");
-    Check(tb::LaunchSampleTrajectory(t.dev, b->x_dev, b->traj_out_dev, n, 2 * sms, b->stream), "launch");
+    Check(tb::LaunchSampleTrajectory(t.dev, b->x_dev, b->traj_out_dev, n, sms, b->stream), "launch");
     b->launches += 1;
     Check(cudaMemcpyAsync(rows_out, b->traj_out_dev, sizeof(double) * per * n, cudaMemcpyDeviceToHost, b->stream), "D2H rows");
     Check(cudaStreamSynchronize(b->stream), "sample_trajectory");

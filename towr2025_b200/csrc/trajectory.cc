@@ -52,6 +52,7 @@ void BuildTrajTables(const HostProgram& hp, const towr_b200_spec& s, double dt, 
       o.poly_T.push_back(T);
       o.poly_T.push_back(std::pow(T, 2));
       o.poly_T.push_back(std::pow(T, 3));
+      o.poly_spline.push_back(static_cast<uint16_t>(o.splines.size()));
       o.poly_meta.push_back(r.rt ? (static_cast<uint32_t>(v.poly_phase[p]) | (static_cast<uint32_t>(v.polys_in_phase[p]) << 8))
                                  : kPolyFixed);
     }

@@ -33,6 +33,7 @@ struct TrajTables {      // host side, one per (structure class, dt)
   std::vector<uint16_t> node_src;   // 6 per node, 0xFFFF = not optimised (0)
   std::vector<double> poly_T;       // 3 per polynomial: T, pow(T,2), pow(T,3)
   std::vector<uint32_t> poly_meta;  // phase | polys_in_phase << 8 ; kPolyFixed: class-constant duration
+  std::vector<uint16_t> poly_spline;// spline of every polynomial
   std::vector<uint32_t> samp_poly;  // fixed durations: [spline][sample] polynomial (global index)
   std::vector<double> samp_t;       // fixed durations: [spline][sample] t_local, pow(t,2), pow(t,3)
   std::vector<uint8_t> contact;     // fixed durations: [foot][sample] PhaseDurations::IsContactPhase
@@ -47,6 +48,7 @@ struct TrajDevice {
   const uint16_t* node_src;
   const double* poly_T;
   const uint32_t* poly_meta;
+  const uint16_t* poly_spline;
   const uint32_t* samp_poly;
   const double* samp_t;
   const uint8_t* contact;
@@ -58,7 +60,7 @@ std::vector<double> TrajectoryTimes(const HostProgram& hp, double dt);
 void BuildTrajTables(const HostProgram& hp, const towr_b200_spec& s, double dt, TrajTables& out);
 size_t TrajSharedBytes(const TrajDevice& t);
 #ifdef __CUDACC__
-cudaError_t LaunchSampleTrajectory(const TrajDevice& t, const double* x, double* out, int n_problems, int max_ctas,
+cudaError_t LaunchSampleTrajectory(const TrajDevice& t, const double* x, double* out, int n_problems, int sms,
                                    cudaStream_t stream);
 #endif
 
