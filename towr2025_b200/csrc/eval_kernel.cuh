@@ -282,13 +282,23 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
       const SegmentRec sg = cx.T.segments[s];
       // ---- stage A, level 0 then level 1: thread -> (item, problem lane)
       if (tid < P) { G[kGOne * P + tid] = 1.0; G[kGMass * P + tid] = pc_all[tid].mass; G[kGMinusOne * P + tid] = -1.0; }
-      for (int i = tid; i < sg.n_items0 * P; i += NT) RunItem<Lockstep<P, RT>>(cx, cx.T.items[sg.item0 + i / P]);
+      // a level with more (item, lane) pairs than threads runs in rounds of NT / P items.  The kinds are ordered longest
+      // first (pack.cc) and odd rounds map the items to the threads in reverse, so the short items of a second round go to
+      // the threads whose first item was short
+      auto run_level = [&](int first, int count) {
+        constexpr int kPerRound = NT / P;
+        int r = 0;
+        for (int base_i = 0; base_i < count; base_i += kPerRound, ++r) {
+          const int idx = base_i + ((r & 1) ? kPerRound - 1 - tid / P : tid / P);
+          if (idx < count) RunItem<Lockstep<P, RT>>(cx, cx.T.items[first + idx]);
+        }
+      };
+      run_level(sg.item0, sg.n_items0);
       TB_MARK(8 + 6 * s)
       if (sg.n_items > sg.n_items0) {
         __syncthreads();
         TB_MARK(9 + 6 * s)
-        for (int i = tid; i < (sg.n_items - sg.n_items0) * P; i += NT)
-          RunItem<Lockstep<P, RT>>(cx, cx.T.items[sg.item0 + sg.n_items0 + i / P]);
+        run_level(sg.item0 + sg.n_items0, sg.n_items - sg.n_items0);
         TB_MARK(10 + 6 * s)
       }
       // first descriptor batch of stage B: issued before the barrier, consumed after it

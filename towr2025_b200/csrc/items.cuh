@@ -200,36 +200,40 @@ __device__ __forceinline__ void ItemDynWrench(const ItemCtx<L>& cx, const ItemC&
   gr[(5) * L::RS] = (m * lin.a[2] - f_sum[2]) - (-m * grav);
 }
 
-// row r (= sub) of the base-lin angular block: entry(r, (sd,d)) = -(sum_e Cross(f_e)(r,d) * Bpos[sd]), feet summed
+// rows of the base-lin angular block (sub = r: one row, sub = 3: all): entry(r, (sd,d)) = -(sum_e Cross(f_e)(r,d) * Bpos[sd]), feet summed
 // in order
 template <class L>
 __device__ __forceinline__ void ItemDynJlin(const ItemCtx<L>& cx, const ItemC& it) {
-  const int E = it.n_ee, r = it.sub;
+  const int E = it.n_ee;
   double* G = cx.G + it.gslot * L::GS;
   const double* Bl = cx.T.B + it.b0;
   const double b4[4] = {Bl[0], Bl[1], Bl[2], Bl[3]};
+  // sub = 0..2: that row only; sub = 3: all three rows (one item per sample)
+  const int r0 = it.sub < 3 ? it.sub : 0, r1 = it.sub < 3 ? it.sub + 1 : 3;
+  for (int r = r0; r < r1; ++r) {
 #pragma unroll
-  for (int d = 0; d < 3; ++d) {
-    if (d == r) {              // no entry uses these slots; keep them finite for the status check
+    for (int d = 0; d < 3; ++d) {
+      if (d == r) {              // no entry uses these slots; keep them finite for the status check
 #pragma unroll
-      for (int sd = 0; sd < 4; ++sd) TB_G(kDynJlin + r * 12 + sd * 3 + d) = 0.0;
-      continue;
+        for (int sd = 0; sd < 4; ++sd) TB_G(kDynJlin + r * 12 + sd * 3 + d) = 0.0;
+        continue;
+      }
+      const int k = 3 - r - d;
+      const double sg = ((d - r + 3) % 3 == 2) ? 1.0 : -1.0;
+      double acc[4];
+      {
+        const double sf = sg * TB_G(kDynF + k);
+#pragma unroll
+        for (int sd = 0; sd < 4; ++sd) acc[sd] = sf * b4[sd];
+      }
+      for (int e = 1; e < E; ++e) {
+        const double sf = sg * TB_G(kDynF + 3 * e + k);
+#pragma unroll
+        for (int sd = 0; sd < 4; ++sd) acc[sd] = acc[sd] + sf * b4[sd];
+      }
+#pragma unroll
+      for (int sd = 0; sd < 4; ++sd) TB_G(kDynJlin + r * 12 + sd * 3 + d) = -acc[sd];
     }
-    const int k = 3 - r - d;
-    const double sg = ((d - r + 3) % 3 == 2) ? 1.0 : -1.0;
-    double acc[4];
-    {
-      const double sf = sg * TB_G(kDynF + k);
-#pragma unroll
-      for (int sd = 0; sd < 4; ++sd) acc[sd] = sf * b4[sd];
-    }
-    for (int e = 1; e < E; ++e) {
-      const double sf = sg * TB_G(kDynF + 3 * e + k);
-#pragma unroll
-      for (int sd = 0; sd < 4; ++sd) acc[sd] = acc[sd] + sf * b4[sd];
-    }
-#pragma unroll
-    for (int sd = 0; sd < 4; ++sd) TB_G(kDynJlin + r * 12 + sd * 3 + d) = -acc[sd];
   }
 }
 

@@ -1,5 +1,6 @@
 // pack.cc — compacts the builder's tables into the device form: one shared-memory blob of class tables and the
 // byte-offset entry descriptors (program.h).
+#include <algorithm>
 #include <array>
 #include <cstring>
 #include <map>
@@ -93,7 +94,8 @@ void PackProgram(HostProgram& hp) {
     kind.push_back({ItemLevel(it.type), it.type, it.sub});
   }
   // per segment: level-0 items first, then level-1; items of one (type, sub) kind are contiguous and every kind
-  // starts on a warp boundary so that no warp of stage A diverges between kinds (null items fill the gaps)
+  // starts on a warp boundary of the two-lane kernel (16 items x 2 problem lanes) so that no warp of stage A diverges
+  // between kinds (null items fill the gaps; one-lane kernels share a warp between two kinds at most)
   {
     std::vector<ItemC> padded;
     ItemC none;
@@ -110,12 +112,16 @@ void PackProgram(HostProgram& hp) {
           for (auto& q : kinds) seen |= (q == k);
           if (!seen) kinds.push_back(k);
         }
+        // longest kinds first: where a level needs a second round of threads, that round holds the short items
+        std::stable_sort(kinds.begin(), kinds.end(), [](const std::array<int, 3>& a, const std::array<int, 3>& b) {
+          return ItemCostRank(a[1]) < ItemCostRank(b[1]);
+        });
         for (auto& k : kinds) {
-          while (padded.size() % 32) padded.push_back(none);
+          while (padded.size() % kItemPad) padded.push_back(none);
           for (int i = 0; i < sg.n_items; ++i)
             if (kind[sg.item0 + i] == k) padded.push_back(items[sg.item0 + i]);
         }
-        while (padded.size() % 32) padded.push_back(none);
+        while (padded.size() % kItemPad) padded.push_back(none);
         if (level == 0) sg.n_items0 = static_cast<int>(padded.size()) - new0;
       }
       sg.item0 = new0;

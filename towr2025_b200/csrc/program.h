@@ -60,6 +60,18 @@ enum ItemType : int {
   kItemRomFoot,         // range_of_motion_constraint.cc:72-131: 3 g rows + d(R^T r)/d(euler) of one (sample, foot)
   kItemNone = 255,      // padding: keeps every warp of stage A on one item kind
 };
+constexpr int kItemPad = 16;   // items of one kind are padded to a multiple of this (pack.cc)
+// relative cost of an item kind: lower = longer dependent chain (pack.cc orders the kinds of a level by it)
+inline int ItemCostRank(int type) {
+  switch (type) {
+    case kItemDynPre: case kItemDynCol: return 0;
+    case kItemForce: case kItemTorque: case kItemForceNode: case kItemRomFoot: return 1;
+    case kItemDynFoot: case kItemRomPre: return 2;
+    case kItemDynJlin: case kItemBaseRom: return 3;
+    case kItemDynWrench: return 4;
+    default: return 5;
+  }
+}
 inline int ItemLevel(int type) { return type >= kItemDynWrench && type != kItemNone ? 1 : 0; }
 
 // scratch layouts written by the level-0 items (slot offsets)

@@ -464,8 +464,12 @@ void Builder::EmitDynamic() {
       col.type = kItemDynCol;
       col.sub = static_cast<short>(c);
       hp_.items.push_back(col);
-      col.type = kItemDynJlin;
-      hp_.items.push_back(col);
+    }
+    {
+      ItemRec jl = it;                                    // one item finishes all three rows of the base-lin angular block
+      jl.type = kItemDynJlin;
+      jl.sub = 3;
+      hp_.items.push_back(jl);
     }
   }
   EndSet();
