@@ -222,6 +222,31 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     }
     int forced = 0;
     if (const char* env = std::getenv("TOWR_B200_LANES")) forced = std::atoi(env);
+    // Two problems per CTA share the class tables and the descriptor stream.  Where the default program only fits one
+    // lane (classes with optimised durations have large G footprints), a lower G capacity - more, smaller segments -
+    // that lets two lanes fit is faster as long as it keeps about half of the default capacity (HyQ gallop with
+    // optimised durations: 4.40 ms with 2 lanes / 17 segments against 6.69 ms with 1 lane / 14 segments).
+    if (!forced && !std::getenv("TOWR_B200_GCAP") && !b->hp_local) {
+      auto need2 = [](const tb::HostProgram& h, int g_cap) {
+        tb::DeviceProgram t{};
+        t.blob = h.blob;
+        t.g_capacity = g_cap;
+        return static_cast<long long>(tb::EvalSharedBytes(t, 2)) + 1024;
+      };
+      const long long optin = static_cast<long long>(prop.sharedMemPerBlockOptin);
+      if (need2(*hpp, hpp->g_capacity) > optin) {
+        long long cap = (optin - need2(*hpp, 0) - 6144) / 16;           // tables grow a little with the segment count
+        for (int attempt = 0; attempt < 4 && cap * 100 >= 45LL * hpp->g_capacity; ++attempt, cap = cap * 31 / 32) {
+          auto h = std::make_unique<tb::HostProgram>();
+          tb::BuildProgram(st->spec, *h, static_cast<int>(cap));
+          if (need2(*h, h->g_capacity) <= optin) {
+            b->hp_local = std::move(h);
+            hpp = b->hp_local.get();
+            break;
+          }
+        }
+      }
+    }
     // kernel variant: TOWR_B200_KERNEL = bulk | lockstep | ws forces one.  The bulk-store kernel needs the G buffer and
     // the staging buffer of the largest segment side by side: lower the G capacity until both fit.
     const char* kenv = std::getenv("TOWR_B200_KERNEL");
