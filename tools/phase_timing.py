@@ -32,7 +32,7 @@ def main():
     for it in range(3):
         b.eval_device(batch, T.EVAL_BOTH, dx.data_ptr(), dg.data_ptr(), dv.data_ptr())
         torch.cuda.synchronize()
-        reader = "towr_b200_debug_phase_clocks" + ("_bulk" if os.environ.get("TOWR_B200_KERNEL", "bulk") == "bulk" else "")
+        reader = "towr_b200_debug_phase_clocks" + {"bulk": "_bulk", "ws": "_ws"}.get(os.environ.get("TOWR_B200_KERNEL", "lockstep"), "")
         getattr(L, reader)(out, 64)
     v = list(out)
     tot = sum(v)

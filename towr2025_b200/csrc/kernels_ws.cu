@@ -1,4 +1,7 @@
 // kernels_ws.cu — warp-specialised variant of the evaluation kernel.
+#if defined(TB_TIMING)
+#define TB_TIMING_HERE
+#endif
 #include "eval_kernel.cuh"
 
 namespace tb {
@@ -191,3 +194,5 @@ bool EvalFitsWS(const DeviceProgram& P, int lanes, size_t smem_optin) {
 }
 
 }  // namespace tb
+
+TB_PHASE_CLOCK_READER(towr_b200_debug_phase_clocks_ws)
