@@ -1,0 +1,75 @@
+"""BASELINE config 0: the formulation of the reference's own example, towr/test/hopper_example.cc:98-150 (Monoped on the
+FiveStepStairs terrain of :53-86, 13 phases :105-113, +Torque :145, OptimizePhaseDurations :150), stated through the
+spec fields instead of a gait generator.  enable_stance_tracking stays false, so ee_stance_position_
+(:114-122, variable bounds only) does not enter; costs (:147-148) are outside the constraint/Jacobian path."""
+import numpy as np
+import pytest
+
+from util import parity_ok, perturbed, to_oracle_spec
+
+PHASES = [0.5, 0.3, 0.4, 0.3, 0.4, 0.3, 0.4, 0.3, 0.4, 0.3, 0.4, 0.3, 0.4]   # hopper_example.cc:105-113
+TORQUE = 6
+
+
+def hopper_spec(M):
+    s = M.make_spec(M.Monoped, 0, 2.4)          # robot model and defaults; the gait is replaced below
+    s.terrain_id = 7                            # FiveStepStairs
+    s.n_phases[0] = len(PHASES)
+    for i, d in enumerate(PHASES):
+        s.phase_durations[0][i] = d
+    s.in_contact_at_start[0] = 1                # :141
+    for i, v in enumerate([0.0, 0.0, 0.6, 0.0, 0.0, 0.0]):     # :125-126
+        s.initial_base_lin[i] = v
+        s.final_base_lin[i] = v                 # :132: z = 0.6 + GetHeight(0, 0) = 0.6
+    for i in range(6):
+        s.initial_base_ang[i] = 0.0
+        s.final_base_ang[i] = 0.0
+    for i in range(3):
+        s.initial_ee_W[0][i] = 0.0              # :129
+    s.constraints[s.n_constraints] = TORQUE     # :145
+    s.n_constraints += 1
+    if hasattr(M, "lib") and hasattr(M.lib(), "towr_b200_spec_optimize_durations"):
+        M._check(M.lib().towr_b200_spec_optimize_durations(__import__("ctypes").byref(s)))
+    return s
+
+
+def test_hopper_example_structure(product, oracle):
+    """Sizes of SURVEY.md section 8 (888 variables, 2 026 + 948 rows) and the pattern, bit-exact against the oracle."""
+    T, O = product, oracle
+    s = hopper_spec(T)
+    st = T.Structure(s)
+    p = O.Problem(to_oracle_spec(O, s))
+    assert st.n_vars == p.n_vars == 888
+    assert st.n_rows == p.n_rows == 2026 + 948
+    x0 = st.x0(s)
+    assert np.array_equal(x0, p.x0())
+    r, c, _ = p.eval_jac(x0)
+    rows, cols = st.pattern()
+    assert np.array_equal(r, rows) and np.array_equal(c, cols)
+    r2, c2, _ = p.eval_jac(perturbed(x0, 3, 0.02))
+    assert np.array_equal(r2, rows) and np.array_equal(c2, cols)
+    lo, up = st.con_bounds(s)
+    olo, oup = p.con_bounds()
+    assert np.array_equal(lo, olo) and np.array_equal(up, oup)
+    assert st.trajectory_samples(0.01) == 471 and st.trajectory_width() == 44      # T = 4.7 s
+
+
+@pytest.mark.gpu
+def test_hopper_example_gpu_parity(product, oracle):
+    T, O = product, oracle
+    s = hopper_spec(T)
+    st = T.Structure(s)
+    p = O.Problem(to_oracle_spec(O, s))
+    n = 4
+    x = np.stack([perturbed(st.x0(s), 40 + i, 0.02 if i else 0.0) for i in range(n)])
+    b = T.Batch(st, n)
+    b.set_all(s)
+    g, v = b.eval(x)
+    assert (b.status() == 0).all()
+    for i in range(n):
+        _, _, vo = p.eval_jac(x[i])
+        assert parity_ok(g[i], p.eval_g(x[i]), True)
+        assert parity_ok(v[i], vo, True)
+    rows = b.sample_trajectory(x, 0.02)
+    for i in range(n):
+        assert parity_ok(rows[i], p.sample_trajectory(x[i], 0.02), True)

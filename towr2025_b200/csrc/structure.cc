@@ -1001,10 +1001,11 @@ void BuildProgram(const towr_b200_spec& s, HostProgram& hp, int g_cap, int joint
     std::fprintf(stderr, "groups:");
     for (size_t g = 0; g < sizing.group_g_size.size(); ++g) std::fprintf(stderr, " %d/%d", sizing.group_g_size[g], group_entries[g]);
     std::fprintf(stderr, "\n");
-    for (const SegmentRec& sg : hp.segments)
-      std::fprintf(stderr, "segment items %d (level0 %d) entries %d g %d\n", sg.n_items, sg.n_items0, sg.n_entries, sg.g_size);
   }
   PackProgram(hp);
+  if (std::getenv("TOWR_B200_DEBUG"))
+    for (const SegmentRec& sg : hp.segments)
+      std::fprintf(stderr, "segment items %d (level 0: %d, padded) entries %d g %d\n", sg.n_items, sg.n_items0, sg.n_entries, sg.g_size);
   if (std::getenv("TOWR_B200_DEBUG"))
     std::fprintf(stderr, "blob %d B (B %d, times %d, items %d, samples %d, polys %d), G capacity %d, %zu segments\n", hp.blob.bytes,
                  hp.blob.n_B, hp.blob.n_times, hp.blob.n_items, hp.blob.n_samples, hp.blob.n_polys, hp.g_capacity, hp.segments.size());
