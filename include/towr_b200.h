@@ -33,6 +33,7 @@ extern "C" {
 #define TOWR_B200_MAX_EE 4
 #define TOWR_B200_MAX_PHASES 32
 #define TOWR_B200_MAX_CONSTRAINTS 16
+#define TOWR_B200_MAX_COSTS 4
 
 typedef enum towr_b200_status {
   TOWR_B200_OK = 0,
@@ -51,6 +52,8 @@ enum { TOWR_B200_MONOPED = 0, TOWR_B200_BIPED, TOWR_B200_HYQ, TOWR_B200_ANYMAL }
 /* towr::HeightMap::TerrainID, include/towr/terrain/height_map.h; 7 = FiveStepStairs of test/hopper_example.cc:53-86 */
 enum { TOWR_B200_FLAT = 0, TOWR_B200_BLOCK, TOWR_B200_STAIRS, TOWR_B200_GAP, TOWR_B200_SLOPE, TOWR_B200_CHIMNEY,
        TOWR_B200_CHIMNEY_LR, TOWR_B200_FIVE_STEP_STAIRS, TOWR_B200_TERRAIN_COUNT };
+/* towr::Parameters::CostName, include/towr/parameters.h:157-161 */
+enum { TOWR_B200_COST_FORCES = 0, TOWR_B200_COST_EE_MOTION = 1, TOWR_B200_COST_ENERGY = 2, TOWR_B200_COST_ANG_MOM = 3 };
 /* what to evaluate */
 enum { TOWR_B200_EVAL_G = 1, TOWR_B200_EVAL_JAC = 2, TOWR_B200_EVAL_BOTH = 3 };
 
@@ -82,6 +85,10 @@ typedef struct towr_b200_spec {
   /* initial_base_, final_base_ (p xyz then v xyz), initial_ee_W_ */
   double initial_base_lin[6], initial_base_ang[6], final_base_lin[6], final_base_ang[6];
   double initial_ee_W[TOWR_B200_MAX_EE][3];
+  /* params_.costs_ (parameters.h:163,192): (CostName, weight) pairs in order; empty by default (parameters.cc:90) */
+  int n_costs;
+  int cost_ids[TOWR_B200_MAX_COSTS];
+  double cost_weights[TOWR_B200_MAX_COSTS];
 } towr_b200_spec;
 
 const char* towr_b200_last_error(void);
@@ -150,6 +157,16 @@ int towr_b200_batch_status(towr_b200_batch* b, int n, int* status_out);
 long long towr_b200_batch_launch_count(const towr_b200_batch* b);
 /* the batch's own non-blocking cudaStream_t (the one towr_b200_batch_eval works on) */
 void* towr_b200_batch_stream(const towr_b200_batch* b);
+
+/* ---- the other two Ipopt callbacks: eval_f / eval_grad_f --------------------------------------------------------------
+ * Replaces ifopt::Problem::EvaluateCostFunction / EvaluateCostFunctionGradient over the cost terms of
+ * NlpFormulation::GetCosts (towr/src/nlp_formulation.cc:605-681) for the NodeCost families (towr/src/costs/node_cost.cc:
+ * 36-76): ForcesCostID and EEMotionCostID, as test/hopper_example.cc:147-148 enables them.  spec.n_costs = 0 (the
+ * reference's default, parameters.cc:90) gives f = 0 and a zero gradient.  what: bit 0 = f (n doubles), bit 1 = dense
+ * gradient (n x n_vars doubles).  EnergyCostID / AngMomCostID make towr_b200_structure_create fail as unsupported. */
+int towr_b200_batch_eval_cost(towr_b200_batch* b, int n, int what, const double* x, double* f_out, double* grad_out);
+int towr_b200_batch_eval_cost_device(towr_b200_batch* b, int n, int what, const double* d_x, double* d_f, double* d_grad,
+                                     void* stream);
 
 /* ---- trajectory sampling: the step on the far side of the solver -------------------------------------------------
  * Replaces towr::SaveTrajectoryToCSV's sampling loop (towr/src/utils/save_data.cpp:54-119), i.e. SplineHolder's

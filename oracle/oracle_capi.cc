@@ -1,6 +1,7 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY (see towr_oracle.h header).
 #include "oracle_capi.h"
 
+#include <cmath>
 #include <cstring>
 #include <numeric>
 #include <exception>
@@ -17,6 +18,7 @@ using namespace orc;
 static thread_local std::string g_err;
 
 struct orc_problem {
+  std::vector<std::pair<int, double>> costs;   // Parameters::costs_ (CostName, weight)
   NlpFormulation formulation;
   SplineHolder splines;
   Problem nlp;
@@ -76,6 +78,7 @@ static NlpFormulation MakeFormulation(const orc_spec& s) {
 
 static void Build(orc_problem* p, const orc_spec& s) {
   p->formulation = MakeFormulation(s);
+  for (int c = 0; c < s.n_costs && c < ORC_MAX_COSTS; ++c) p->costs.emplace_back(s.cost_ids[c], s.cost_weights[c]);
   for (auto& v : p->formulation.GetVariableSets(p->splines)) p->nlp.AddVariableSet(v);
   for (auto& c : p->formulation.GetConstraints(p->splines)) p->nlp.AddConstraintSet(c);
   p->x0 = p->nlp.GetVariableValues();
@@ -86,6 +89,7 @@ extern "C" {
 void orc_spec_defaults(orc_spec* s) {
   std::memset(s, 0, sizeof(*s));
   Parameters d;
+  s->n_costs = 0;   // parameters.cc:90: no cost by default
   s->n_constraints = static_cast<int>(d.constraints_.size());
   for (int i = 0; i < s->n_constraints; ++i) s->constraints[i] = d.constraints_[i];
   s->dt_constraint_dynamic = d.dt_constraint_dynamic_;
@@ -304,6 +308,77 @@ void orc_sample_times(double T, double dt, double* out, int* n) {
   } probe(T, dt);
   *n = static_cast<int>(probe.SampleTimes().size());
   if (out) for (int i = 0; i < *n; ++i) out[i] = probe.SampleTimes()[i];
+}
+
+// ---- costs: NlpFormulation::GetCosts / GetCost / MakeForcesCost / MakeEEMotionCost (nlp_formulation.cc:605-681)
+}  // extern "C"
+namespace {
+struct NodeCostDef { std::string nodes_id; Dx deriv; int dim; double weight; };   // costs/node_cost.cc:36-45
+std::vector<NodeCostDef> CostTerms(const orc_problem* p) {
+  std::vector<NodeCostDef> terms;
+  const int E = static_cast<int>(p->splines.ee_motion_.size());
+  for (const auto& pr : p->costs) {
+    const double weight = pr.second;
+    if (pr.first == 0) {            // ForcesCostID, :648-666
+      for (int ee = 0; ee < E; ee++)
+        for (int dim : {0, 1, 2}) {
+          terms.push_back({"ee-force_" + std::to_string(ee), kPos, dim, weight});
+          terms.push_back({"ee-torque_" + std::to_string(ee), kPos, dim, weight});
+          terms.push_back({"ee-force_" + std::to_string(ee), kVel, dim, 0.1 * weight});
+          terms.push_back({"ee-torque_" + std::to_string(ee), kVel, dim, 0.1 * weight});
+        }
+    } else if (pr.first == 1) {     // EEMotionCostID, :668-681
+      for (int ee = 0; ee < E; ee++) {
+        terms.push_back({"ee-motion_" + std::to_string(ee), kVel, 0, weight});
+        terms.push_back({"ee-motion_" + std::to_string(ee), kVel, 1, weight});
+        terms.push_back({"ee-motion_" + std::to_string(ee), kVel, 2, 0.5 * weight});
+      }
+    } else {
+      throw std::runtime_error("unsupported: EnergyCost / AngularMomentumCost are not restated");
+    }
+  }
+  return terms;
+}
+}  // namespace
+extern "C" {
+
+// ifopt::Problem::EvaluateCostFunction: sum of the cost terms' values.  NodeCost::GetCost (node_cost.cc:53-62); the
+// reference leaves `cost` uninitialised there (:55), restated with the intended 0.
+double orc_eval_f(orc_problem* p, const double* x) {
+  p->nlp.SetVariables(x);
+  double total = 0.0;
+  for (const NodeCostDef& t : CostTerms(p)) {
+    auto nodes = p->nlp.Vars()->GetComponent<NodesVariables>(t.nodes_id);
+    double cost = 0.0;
+    for (const Node& n : nodes->GetNodes()) {
+      double val = n.at(t.deriv)(t.dim);
+      cost += t.weight * std::pow(val, 2);
+    }
+    total += cost;
+  }
+  return total;
+}
+
+// ifopt::Problem::EvaluateCostFunctionGradient: NodeCost::FillJacobianBlock (node_cost.cc:64-76) of every term, summed
+void orc_eval_grad_f(orc_problem* p, const double* x, double* grad) {
+  p->nlp.SetVariables(x);
+  const int n = p->nlp.GetNumberOfOptimizationVariables();
+  for (int i = 0; i < n; ++i) grad[i] = 0.0;
+  for (const NodeCostDef& t : CostTerms(p)) {
+    int col0 = 0;
+    for (auto& vs : p->nlp.Vars()->GetComponents()) {
+      if (vs->GetName() == t.nodes_id) {
+        auto nodes = std::dynamic_pointer_cast<NodesVariables>(vs);
+        for (int i = 0; i < nodes->GetRows(); ++i)
+          for (const auto& nvi : nodes->GetNodeValuesInfo(i))
+            if (nvi.deriv == t.deriv && nvi.dim == t.dim) {
+              double val = nodes->GetNodes().at(nvi.id).at(t.deriv)(t.dim);
+              grad[col0 + i] += t.weight * 2.0 * val;
+            }
+      }
+      col0 += vs->GetRows();
+    }
+  }
 }
 
 int orc_trajectory_width(const orc_problem* p) { return 19 + 25 * static_cast<int>(p->splines.ee_motion_.size()); }

@@ -12,6 +12,7 @@ extern "C" {
 #define ORC_MAX_EE 4
 #define ORC_MAX_PHASES 32
 #define ORC_MAX_CONSTRAINTS 16
+#define ORC_MAX_COSTS 4
 
 /* The public members of towr::NlpFormulation (nlp_formulation.h:100-105) plus the
  * fields of towr::Parameters (parameters.h:135-336) the hot path reads. */
@@ -41,6 +42,10 @@ typedef struct orc_spec {
   /* BaseState initial/final: p(3) then v(3); initial_ee_W_ */
   double initial_base_lin[6], initial_base_ang[6], final_base_lin[6], final_base_ang[6];
   double initial_ee_W[ORC_MAX_EE][3];
+  /* Parameters::costs_ (parameters.h:163,192): (CostName, weight) pairs in order */
+  int n_costs;
+  int cost_ids[ORC_MAX_COSTS];
+  double cost_weights[ORC_MAX_COSTS];
 } orc_spec;
 
 /* Parameters::Parameters() defaults (parameters.cc:40-105), enable_stance_tracking=false. */
@@ -92,6 +97,10 @@ void orc_sample_times(double T, double dt, double* out, int* n);    /* time_disc
 
 /* utils/save_data.cpp:9-132 (SaveTrajectoryToCSV): the sampling loop and the values of one CSV row per sample
  * (19 + 25 n_ee doubles: time, base, per foot ...; is_contact as 0/1).  rows may be NULL; returns the row count. */
+/* eval_f / eval_grad_f: ifopt::Problem::EvaluateCostFunction / EvaluateCostFunctionGradient over the cost terms of
+ * NlpFormulation::GetCosts (nlp_formulation.cc:605-681; NodeCost, costs/node_cost.cc:36-76).  grad is n_vars doubles. */
+double orc_eval_f(orc_problem* p, const double* x);
+void orc_eval_grad_f(orc_problem* p, const double* x, double* grad);
 int orc_trajectory_width(const orc_problem* p);
 int orc_sample_trajectory(orc_problem* p, const double* x, double dt, double* rows);
 

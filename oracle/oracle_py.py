@@ -53,6 +53,9 @@ class Spec(C.Structure):
         ("initial_base_lin", C.c_double * 6), ("initial_base_ang", C.c_double * 6),
         ("final_base_lin", C.c_double * 6), ("final_base_ang", C.c_double * 6),
         ("initial_ee_W", (C.c_double * 3) * MAX_EE),
+        ("n_costs", C.c_int),
+        ("cost_ids", C.c_int * 4),
+        ("cost_weights", C.c_double * 4),
     ]
 
 
@@ -102,6 +105,9 @@ def lib():
     L.orc_terrain.argtypes = [C.c_int, C.c_double, C.c_double, dp, dp, dp, dp]
     L.orc_sample_times.argtypes = [C.c_double, C.c_double, dp, ip]
     L.orc_trajectory_width.argtypes = [C.c_void_p]
+    L.orc_eval_f.argtypes = [C.c_void_p, dp]
+    L.orc_eval_f.restype = C.c_double
+    L.orc_eval_grad_f.argtypes = [C.c_void_p, dp, dp]
     L.orc_sample_trajectory.argtypes = [C.c_void_p, dp, C.c_double, dp]
     _lib = L
     return L
@@ -183,6 +189,16 @@ class Problem:
         rows = np.empty((n, w))
         self._L.orc_sample_trajectory(self._p, _dp(x), float(dt), _dp(rows))
         return rows
+
+    def eval_f(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        return float(self._L.orc_eval_f(self._p, _dp(x)))
+
+    def eval_grad_f(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        grad = np.empty(self.n_vars)
+        self._L.orc_eval_grad_f(self._p, _dp(x), _dp(grad))
+        return grad
 
     def eval_g(self, x):
         x = np.ascontiguousarray(x, dtype=np.float64)

@@ -59,6 +59,9 @@ class Spec(C.Structure):
         ("initial_base_lin", C.c_double * 6), ("initial_base_ang", C.c_double * 6),
         ("final_base_lin", C.c_double * 6), ("final_base_ang", C.c_double * 6),
         ("initial_ee_W", (C.c_double * 3) * MAX_EE),
+        ("n_costs", C.c_int),
+        ("cost_ids", C.c_int * 4),
+        ("cost_weights", C.c_double * 4),
     ]
 
     def copy(self):
@@ -92,7 +95,8 @@ towr_b200_problem_x0 towr_b200_problem_var_bounds towr_b200_problem_con_bounds t
 towr_b200_batch_destroy towr_b200_batch_size towr_b200_batch_set_problem towr_b200_batch_set_all_problems
 towr_b200_batch_eval towr_b200_batch_eval_device towr_b200_batch_status towr_b200_batch_launch_count
 towr_b200_batch_stream towr_b200_trajectory_width towr_b200_trajectory_samples towr_b200_batch_sample_trajectory
-towr_b200_batch_sample_trajectory_device towr_b200_trajectory_write_csv""".split()
+towr_b200_batch_sample_trajectory_device towr_b200_trajectory_write_csv towr_b200_batch_eval_cost
+towr_b200_batch_eval_cost_device""".split()
 
 
 def lib():
@@ -134,6 +138,8 @@ def lib():
     L.towr_b200_batch_eval.argtypes = [vp, ip, C.c_int, C.c_int, dp, dp, dp]
     L.towr_b200_batch_eval_device.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp]
     L.towr_b200_batch_status.argtypes = [vp, C.c_int, ip]
+    L.towr_b200_batch_eval_cost.argtypes = [vp, C.c_int, C.c_int, dp, dp, dp]
+    L.towr_b200_batch_eval_cost_device.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp]
     L.towr_b200_trajectory_width.argtypes = [vp]
     L.towr_b200_trajectory_samples.argtypes = [vp, C.c_double]
     L.towr_b200_batch_sample_trajectory.argtypes = [vp, C.c_int, C.c_double, dp, dp]
@@ -290,6 +296,15 @@ class Batch:
             idp = _ip(ids)
         _check(self._L.towr_b200_batch_eval(self._h, idp, n, what, _dp(x), _dp(g), _dp(v)))
         return g, v
+
+    def eval_cost(self, x, what=3):
+        """Host-buffer eval_f / eval_grad_f (towr_b200_batch_eval_cost): (f[n], grad[n, n_vars])."""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        n = x.shape[0]
+        f = np.empty(n) if what & 1 else None
+        grad = np.empty((n, self.structure.n_vars)) if what & 2 else None
+        _check(self._L.towr_b200_batch_eval_cost(self._h, n, what, _dp(x), _dp(f), _dp(grad)))
+        return f, grad
 
     def sample_trajectory(self, x, dt):
         """Host-buffer trajectory sampling (towr_b200_batch_sample_trajectory): (n, samples, width) rows."""

@@ -12,11 +12,13 @@
 #include <memory>
 #include <stdexcept>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "kernels.h"
 #include "structure.h"
 #include "trajectory.h"
+#include "cost.h"
 
 namespace tb {
 void SpecDefaults(towr_b200_spec* s);
@@ -97,6 +99,10 @@ struct towr_b200_batch {
   std::map<double, std::unique_ptr<Traj>> traj;
   double* traj_out_dev = nullptr;
   size_t traj_out_cap = 0;
+  // cost tables (cost.h), built at the first eval_cost call
+  bool cost_ready = false;
+  tb::CostDevice cost_dev{};
+  double *cost_f_dev = nullptr, *cost_grad_dev = nullptr;
 
   void SyncConsts() {
     if (!pc_dirty) return;
@@ -428,6 +434,73 @@ int towr_b200_batch_status(towr_b200_batch* b, int n, int* status_out) {
     Check(cudaSetDevice(b->device), "cudaSetDevice");
     Check(cudaMemcpy(status_out, b->status_dev, sizeof(int) * n, cudaMemcpyDeviceToHost), "D2H status");
     Check(cudaMemset(b->status_dev, 0, sizeof(int) * n), "reset status");
+  });
+}
+
+// ---- eval_f / eval_grad_f --------------------------------------------------------------------------------------------
+}  // extern "C"
+namespace {
+void EnsureCost(towr_b200_batch* b) {
+  if (b->cost_ready) return;
+  tb::CostTables h;
+  tb::BuildCostTables(b->st->hp, b->st->spec, h);
+  auto up = [&](const auto& v) {
+    using T = typename std::decay<decltype(v)>::type::value_type;
+    T* d = nullptr;
+    Check(cudaMalloc(&d, sizeof(T) * std::max<size_t>(1, v.size())), "cudaMalloc(cost tables)");
+    b->owned.push_back(d);
+    if (!v.empty()) Check(cudaMemcpy(d, v.data(), sizeof(T) * v.size(), cudaMemcpyHostToDevice), "H2D cost tables");
+    return d;
+  };
+  b->cost_dev.n_vars = h.n_vars;
+  b->cost_dev.col_ptr = up(h.col_ptr);
+  b->cost_dev.weights = up(h.weights);
+  b->cost_ready = true;
+}
+}  // namespace
+extern "C" {
+
+int towr_b200_batch_eval_cost_device(towr_b200_batch* b, int n, int what, const double* d_x, double* d_f, double* d_grad,
+                                     void* stream) {
+  return Guard([&] {
+    if (!b || n < 0 || n > b->n) throw std::runtime_error("bad problem count");
+    if (what < 1 || what > 3) throw std::runtime_error("what must be 1 (f), 2 (gradient) or 3 (both)");
+    if (!d_x || ((what & 1) && !d_f) || ((what & 2) && !d_grad)) throw std::runtime_error("null device buffer");
+    Check(cudaSetDevice(b->device), "cudaSetDevice");
+    EnsureCost(b);
+    int sms = 0;
+    Check(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device), "device attribute");
+    Check(tb::LaunchCost(b->cost_dev, what, d_x, d_f, d_grad, n, 16 * sms, static_cast<cudaStream_t>(stream)), "launch");
+    b->launches += 1;
+  });
+}
+
+int towr_b200_batch_eval_cost(towr_b200_batch* b, int n, int what, const double* x, double* f_out, double* grad_out) {
+  return Guard([&] {
+    if (!b || n < 0 || n > b->n) throw std::runtime_error("bad problem count");
+    if (what < 1 || what > 3) throw std::runtime_error("what must be 1 (f), 2 (gradient) or 3 (both)");
+    if (!x || ((what & 1) && !f_out) || ((what & 2) && !grad_out)) throw std::runtime_error("null host buffer");
+    if (n == 0) return;
+    Check(cudaSetDevice(b->device), "cudaSetDevice");
+    EnsureCost(b);
+    auto ensure = [&](double*& p, size_t per) {
+      if (!p) {
+        Check(cudaMalloc(&p, sizeof(double) * per * b->n), "cudaMalloc(staging)");
+        b->owned.push_back(p);
+      }
+    };
+    ensure(b->x_dev, b->dp.n_vars);
+    ensure(b->cost_f_dev, 1);
+    if (what & 2) ensure(b->cost_grad_dev, b->dp.n_vars);
+    Check(cudaMemcpyAsync(b->x_dev, x, sizeof(double) * b->dp.n_vars * n, cudaMemcpyHostToDevice, b->stream), "H2D x");
+    int sms = 0;
+    Check(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device), "device attribute");
+    Check(tb::LaunchCost(b->cost_dev, what, b->x_dev, b->cost_f_dev, b->cost_grad_dev, n, 16 * sms, b->stream), "launch");
+    b->launches += 1;
+    if (what & 1) Check(cudaMemcpyAsync(f_out, b->cost_f_dev, sizeof(double) * n, cudaMemcpyDeviceToHost, b->stream), "D2H f");
+    if (what & 2)
+      Check(cudaMemcpyAsync(grad_out, b->cost_grad_dev, sizeof(double) * b->dp.n_vars * n, cudaMemcpyDeviceToHost, b->stream), "D2H gradient");
+    Check(cudaStreamSynchronize(b->stream), "eval_cost");
   });
 }
 

@@ -167,6 +167,13 @@ void ValidateSpec(const towr_b200_spec& s) {
       s.torque_polynomials_per_stance_phase < 1)
     throw std::runtime_error("polynomials per phase must be >= 1");
   if (s.terrain_id < 0 || s.terrain_id >= TOWR_B200_TERRAIN_COUNT) throw std::runtime_error("unknown terrain id");
+  if (s.n_costs < 0 || s.n_costs > TOWR_B200_MAX_COSTS) throw std::runtime_error("bad n_costs");
+  for (int c = 0; c < s.n_costs; ++c) {
+    if (s.cost_ids[c] == TOWR_B200_COST_ENERGY || s.cost_ids[c] == TOWR_B200_COST_ANG_MOM)
+      throw std::runtime_error("unsupported: EnergyCost / AngularMomentumCost are not built");
+    if (s.cost_ids[c] != TOWR_B200_COST_FORCES && s.cost_ids[c] != TOWR_B200_COST_EE_MOTION)
+      throw std::runtime_error("cost not defined!");   // nlp_formulation.cc:644
+  }
 }
 
 void BuildLayout(const towr_b200_spec& s, HostProgram& hp) {

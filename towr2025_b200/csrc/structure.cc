@@ -914,6 +914,7 @@ std::string StructureSignature(const towr_b200_spec& s) {
     << s.torque_polynomials_per_stance_phase;
   for (int i = 0; i < s.n_constraints; ++i)
     if (s.constraints[i] == TOWR_B200_C_TORQUE) o << "|kf" << s.torque_k_friction;   // baked into the class tables
+  for (int c = 0; c < s.n_costs; ++c) o << "|cost" << s.cost_ids[c] << ":" << s.cost_weights[c];   // class-level weight table
   return o.str();
 }
 
