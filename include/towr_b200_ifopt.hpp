@@ -51,6 +51,12 @@ class NlpFormulation {
     if (spec_.n_constraints >= TOWR_B200_MAX_CONSTRAINTS) throw std::runtime_error("too many constraints");
     spec_.constraints[spec_.n_constraints++] = name;
   }
+  // params_.costs_.push_back({name, weight})   (parameters.h:163,192; hopper_example.cc:147-148)
+  void AddCost(int name, double weight) {
+    if (spec_.n_costs >= TOWR_B200_MAX_COSTS) throw std::runtime_error("too many costs");
+    spec_.cost_ids[spec_.n_costs] = name;
+    spec_.cost_weights[spec_.n_costs++] = weight;
+  }
   towr_b200_spec& params() { return spec_; }
   const towr_b200_spec& params() const { return spec_; }
 
@@ -147,6 +153,7 @@ class BatchedProblem {
   void SetVariables(int p, const double* x) {
     std::copy(x, x + n_vars_, x_.begin() + static_cast<size_t>(p) * n_vars_);
     dirty_ = true;
+    cost_dirty_ = true;
   }
   VecBound GetBoundsOnOptimizationVariables(int p) const {
     VectorXd lo(n_vars_), up(n_vars_);
@@ -171,13 +178,48 @@ class BatchedProblem {
     Evaluate();
     return v_.data() + static_cast<size_t>(p) * nnz_;
   }
+  // eval_f / eval_grad_f (ifopt::Problem::EvaluateCostFunction / EvaluateCostFunctionGradient): one launch for the
+  // whole batch, like Evaluate()
+  double EvaluateCostFunction(int p, const double* x) {
+    SetVariables(p, x);
+    EvaluateCosts();
+    return f_[p];
+  }
+  VectorXd EvaluateCostFunctionGradient(int p, const double* x) {
+    SetVariables(p, x);
+    EvaluateCosts();
+    return VectorXd(grad_.begin() + static_cast<size_t>(p) * n_vars_, grad_.begin() + static_cast<size_t>(p + 1) * n_vars_);
+  }
+  void EvaluateCosts() {
+    if (!cost_dirty_ && !f_.empty()) return;
+    EnsureBatch();
+    f_.resize(n_);
+    grad_.resize(static_cast<size_t>(n_) * n_vars_);
+    Check(towr_b200_batch_eval_cost(batch_, n_, 3, x_.data(), f_.data(), grad_.data()));
+    cost_dirty_ = false;
+  }
+  // towr::SaveTrajectoryToCSV's sampling loop (save_data.cpp:54-119) for every problem's current variables:
+  // n x samples x width doubles, row layout in include/towr_b200.h.  SplineHolder::GetPoint(t) of problem p is the
+  // row of sample k = t / T_sample.
+  int GetTrajectoryWidth() const { return towr_b200_trajectory_width(st_); }
+  int GetTrajectorySamples(double T_sample) const { return towr_b200_trajectory_samples(st_, T_sample); }
+  std::vector<double> SampleTrajectories(double T_sample) {
+    EnsureBatch();
+    const int samples = GetTrajectorySamples(T_sample);
+    if (samples < 0) throw std::runtime_error(towr_b200_last_error());
+    std::vector<double> rows(static_cast<size_t>(n_) * samples * GetTrajectoryWidth());
+    Check(towr_b200_batch_sample_trajectory(batch_, n_, T_sample, x_.data(), rows.data()));
+    return rows;
+  }
+  bool SaveTrajectoryToCSV(int p, const std::string& filename, double T_sample) {
+    const std::vector<double> rows = SampleTrajectories(T_sample);
+    const size_t per = static_cast<size_t>(GetTrajectorySamples(T_sample)) * GetTrajectoryWidth();
+    return towr_b200_trajectory_write_csv(st_, rows.data() + p * per, GetTrajectorySamples(T_sample), filename.c_str()) == 0;
+  }
   // one launch for the whole batch (no-op when nothing changed since the last one)
   void Evaluate() {
     if (!dirty_ && !g_.empty()) return;
-    if (!batch_) {
-      Check(towr_b200_batch_create(st_, n_, device_, &batch_));
-      for (int p = 0; p < n_; ++p) Check(towr_b200_batch_set_problem(batch_, p, &specs_[p]));
-    }
+    EnsureBatch();
     g_.resize(static_cast<size_t>(n_) * n_rows_);
     v_.resize(static_cast<size_t>(n_) * nnz_);
     Check(towr_b200_batch_eval(batch_, nullptr, n_, TOWR_B200_EVAL_BOTH, x_.data(), g_.data(), v_.data()));
@@ -226,7 +268,13 @@ class BatchedProblem {
   std::vector<SetInfo> var_sets_, con_sets_;
   std::vector<int> rows_, cols_;
   std::vector<double> x_, g_, v_;
-  bool dirty_ = true;
+  bool dirty_ = true, cost_dirty_ = true;
+  std::vector<double> f_, grad_;
+  void EnsureBatch() {
+    if (batch_) return;
+    Check(towr_b200_batch_create(st_, n_, device_, &batch_));
+    for (int p = 0; p < n_; ++p) Check(towr_b200_batch_set_problem(batch_, p, &specs_[p]));
+  }
 };
 
 inline VectorXd VariableSetView::GetValues() const {
@@ -237,6 +285,7 @@ inline void VariableSetView::SetVariables(const VectorXd& x) {
   if (static_cast<int>(x.size()) != rows_) throw std::runtime_error("SetVariables: wrong size for " + name_);
   std::copy(x.begin(), x.end(), b_->x_.begin() + static_cast<size_t>(p_) * b_->n_vars_ + col0_);
   b_->dirty_ = true;
+  b_->cost_dirty_ = true;
 }
 inline VecBound VariableSetView::GetBounds() const {
   VecBound all = b_->GetBoundsOnOptimizationVariables(p_);

@@ -15,6 +15,8 @@ static NlpFormulation Make(double gx, bool durations) {
   f.SetGait(1, 2.0);
   f.SetNominalStates(gx, 0.0, 0.0);
   if (durations) f.OptimizePhaseDurations();
+  f.AddCost(TOWR_B200_COST_FORCES, 1e-9);      // hopper_example.cc:147-148
+  f.AddCost(TOWR_B200_COST_EE_MOTION, 1e-4);
   return f;
 }
 
@@ -73,6 +75,20 @@ int main(int argc, char** argv) {
         }
       }
       std::printf("dynamic rows %d entries %zu blocksum %.17g g0 %.17g\n", dyn.GetRows(), n_block, block_sum, gd[0]);
+    }
+    if (gpu) {
+      // eval_f / eval_grad_f and the trajectory rows of problem 1 at its current variables
+      VectorXd x = nlp.GetVariableValues(1);
+      const double f = nlp.EvaluateCostFunction(1, x.data());
+      VectorXd gr = nlp.EvaluateCostFunctionGradient(1, x.data());
+      double grs = 0.0;
+      for (double a : gr) grs += a;
+      std::printf("cost %.17g gradsum %.17g\n", f, grs);
+      const std::vector<double> rows = nlp.SampleTrajectories(0.05);
+      const size_t per = static_cast<size_t>(nlp.GetTrajectorySamples(0.05)) * nlp.GetTrajectoryWidth();
+      double rs = 0.0;
+      for (size_t i = 0; i < per; ++i) rs += rows[per + i];
+      std::printf("trajectory %d %d %.17g\n", nlp.GetTrajectorySamples(0.05), nlp.GetTrajectoryWidth(), rs);
     }
     std::printf("ok\n");
     return 0;

@@ -67,6 +67,17 @@ def test_surface_batched_eval(product, oracle, mode):
     assert int(r["dynamic"][3]) == int(m.sum())
     assert float(r["dynamic"][5]) == pytest.approx(float(v[m].sum()), rel=1e-9, abs=1e-7)
     assert float(r["dynamic"][7]) == pytest.approx(float(g[off]), rel=1e-9, abs=1e-12)
+    # eval_f / eval_grad_f and the trajectory rows (costs as in hopper_example.cc:147-148)
+    so = O.make_spec(O.Anymal, 1, 2.0, goal=(1.5, 0.0, 0.0), optimize_durations=opt)
+    so.n_costs = 2
+    so.cost_ids[0], so.cost_weights[0] = 0, 1e-9
+    so.cost_ids[1], so.cost_weights[1] = 1, 1e-4
+    pc = O.Problem(so)
+    assert float(r["cost"][0]) == pytest.approx(pc.eval_f(x), rel=1e-10, abs=1e-14)
+    assert float(r["cost"][2]) == pytest.approx(float(pc.eval_grad_f(x).sum()), rel=1e-9, abs=1e-12)
+    traj = pc.sample_trajectory(x, 0.05)
+    assert [int(r["trajectory"][0]), int(r["trajectory"][1])] == list(traj.shape)
+    assert float(r["trajectory"][2]) == pytest.approx(float(traj.sum()), rel=1e-9, abs=1e-7)
 
 
 def test_callback_coalescer_policy():
