@@ -14,14 +14,16 @@
 namespace tb {
 
 constexpr int kSampleThreads = 256;
-constexpr int kRowChunk = 32;          // samples staged per pass
+constexpr int kRowChunk = 24;          // samples staged per pass (three CTAs per SM stay resident)
+constexpr int kRec = 7;                // doubles per node / coefficient record in shared memory: 6 used; with a stride of 6
+                                       // doubles the records of a warp's splines fall onto 8 bank groups (9 wavefronts per LDS.64)
 
 __global__ void __launch_bounds__(kSampleThreads, 3)
 SampleKernel(const __grid_constant__ TrajDevice Tj, const double* __restrict__ x, double* __restrict__ out, int n_problems) {
   extern __shared__ double sm[];
   double* nodes = sm;                         // 6 per node
-  double* coef = nodes + 6 * Tj.n_nodes;      // 6 per polynomial: c[3], d[3]
-  double* pT = coef + 6 * Tj.n_polys;         // 3 per polynomial: T, T^2, T^3
+  double* coef = nodes + kRec * Tj.n_nodes;   // 6 per polynomial: c[3], d[3]
+  double* pT = coef + kRec * Tj.n_polys;         // 3 per polynomial: T, T^2, T^3
   double* pdur = pT + 3 * Tj.n_polys;         // optimised durations: phase durations of every foot
   double* rowbuf = pdur + Tj.n_phases;        // kRowChunk rows
   // class tables, staged once per CTA (every lookup below would otherwise be an L2 round trip)
@@ -43,7 +45,7 @@ SampleKernel(const __grid_constant__ TrajDevice Tj, const double* __restrict__ x
     // node values (NodesVariables::SetVariables, nodes_variables.cc:68-76): values that are not optimised stay 0
     for (int i = tid; i < 6 * Tj.n_nodes; i += kSampleThreads) {
       const unsigned src = nsrc[i];
-      nodes[i] = src != 0xFFFFu ? __ldg(xp + src) : 0.0;
+      nodes[(i / 6) * kRec + i % 6] = src != 0xFFFFu ? __ldg(xp + src) : 0.0;
     }
     if (Tj.rt && tid < Tj.n_ee) {             // PhaseDurations::SetVariables (phase_durations.cc:78-100)
       const TrajFootRec ft = feet[tid];
@@ -70,11 +72,11 @@ SampleKernel(const __grid_constant__ TrajDevice Tj, const double* __restrict__ x
     for (int i = tid; i < 3 * Tj.n_polys; i += kSampleThreads) {
       const int poly = i / 3, d = i - 3 * poly;
       const TrajSplineRec sp = splines[pspl[poly]];
-      const double* n0 = nodes + 6 * (sp.node0 + (poly - sp.poly0));
-      const double p0 = n0[d], v0 = n0[3 + d], p1 = n0[6 + d], v1 = n0[9 + d];
+      const double* n0 = nodes + kRec * (sp.node0 + (poly - sp.poly0));
+      const double p0 = n0[d], v0 = n0[3 + d], p1 = n0[kRec + d], v1 = n0[kRec + 3 + d];
       const double T = pT[3 * poly], T2 = pT[3 * poly + 1], T3 = pT[3 * poly + 2];
-      coef[6 * poly + d] = -(3.0 * (p0 - p1) + T * (2.0 * v0 + v1)) / T2;
-      coef[6 * poly + 3 + d] = (2.0 * (p0 - p1) + T * (v0 + v1)) / T3;
+      coef[kRec * poly + d] = -(3.0 * (p0 - p1) + T * (2.0 * v0 + v1)) / T2;
+      coef[kRec * poly + 3 + d] = (2.0 * (p0 - p1) + T * (v0 + v1)) / T3;
     }
     __syncthreads();
     // rows are staged in shared memory kRowChunk samples at a time and written with coalesced stores (a problem's rows
@@ -106,12 +108,12 @@ SampleKernel(const __grid_constant__ TrajDevice Tj, const double* __restrict__ x
           poly = sp.poly0 + id;
           t2 = t * t; t3 = Cube(t);
         }
-        const double* n0 = nodes + 6 * (sp.node0 + (poly - sp.poly0));
+        const double* n0 = nodes + kRec * (sp.node0 + (poly - sp.poly0));
         double* row = rowbuf + kl * Tj.width;
         double* o = row + sp.out_col;
 #pragma unroll
         for (int d = 0; d < 3; ++d) {          // Polynomial::GetPoint (polynomial.cc:47-61), coefficients A..D in order
-          const double a = n0[d], b = n0[3 + d], c = coef[6 * poly + d], dd = coef[6 * poly + 3 + d];
+          const double a = n0[d], b = n0[3 + d], c = coef[kRec * poly + d], dd = coef[kRec * poly + 3 + d];
           o[d] = ((a + t * b) + t2 * c) + t3 * dd;
           if (sp.n_out == 9) {
             o[3 + d] = (b + (2 * t) * c) + (3 * t2) * dd;
@@ -147,7 +149,7 @@ SampleKernel(const __grid_constant__ TrajDevice Tj, const double* __restrict__ x
 }
 
 size_t TrajSharedBytes(const TrajDevice& t) {
-  return sizeof(double) * (6 * static_cast<size_t>(t.n_nodes) + 12 * static_cast<size_t>(t.n_polys) + t.n_phases +
+  return sizeof(double) * (kRec * static_cast<size_t>(t.n_nodes) + (kRec + 6) * static_cast<size_t>(t.n_polys) + t.n_phases +
                            static_cast<size_t>(kRowChunk) * t.width) +
          sizeof(TrajSplineRec) * t.n_splines + sizeof(TrajFootRec) * t.n_ee + 6 * static_cast<size_t>(t.n_polys) +
          12 * static_cast<size_t>(t.n_nodes) + 16;
