@@ -150,3 +150,29 @@ def test_gpu_reproduces_committed_fixtures(product):
         assert np.array_equal(rows[z["jac_idx"]], z["jac_rows"]) and np.array_equal(cols[z["jac_idx"]], z["jac_cols"])
         for i in range(3):
             assert tol_ratio(g[i], z["g"]) <= 1.0 and tol_ratio(v[i][z["jac_idx"]], z["jac_vals"]) <= 1.0
+
+
+@pytest.mark.parametrize("name", ["anymal_trot", "anymal_trot_durations"])
+def test_ragged_and_empty_batches(product, name):
+    """n = 0 is a no-op; odd n (a last problem group with one lane only) and n = 1 give the rows of the full eval;
+    the same for the cost and trajectory entry points."""
+    T = product
+    case = [c for c in CASES if c[0] == name][0]
+    s = mk(T, case)
+    st = T.Structure(s)
+    nb = 7
+    x = np.stack([perturbed(st.x0(s), 900 + i, 0.02) for i in range(nb)])
+    b = T.Batch(st, nb)
+    b.set_all(s)
+    g, v = b.eval(x)
+    rows = b.sample_trajectory(x, 0.05)
+    f, gr = b.eval_cost(x)
+    for n in (0, 1, 3, 7):
+        gn, vn = b.eval(x[:n])
+        assert gn.shape == (n, st.n_rows) and vn.shape == (n, st.nnz)
+        assert np.array_equal(gn, g[:n]) and np.array_equal(vn, v[:n])
+        assert np.array_equal(b.sample_trajectory(x[:n], 0.05), rows[:n])
+        fn, grn = b.eval_cost(x[:n])
+        assert np.array_equal(fn, f[:n]) and np.array_equal(grn, gr[:n])
+    with pytest.raises(T.TowrB200Error):
+        b.eval(np.tile(x, (2, 1)))              # more problems than the batch holds
