@@ -34,7 +34,7 @@ static void EmuEval(const HostProgram& hp, const towr_b200_spec* s, const double
   ItemCtx<Lockstep<1, RT>> cx;
   cx.T = MakeTables(hp.blob_data.data(), L);
   cx.n_ee = hp.n_ee;
-  std::vector<double> nodes(L.n_node_values), coef(6 * L.n_polys), G(hp.g_capacity), rtd(5 * L.n_polys), pdur(L.n_pdur + 1);
+  std::vector<double> nodes(L.n_node_values), coef(6 * L.n_polys), G(hp.g_capacity), rtd(kRtd * L.n_polys), pdur(L.n_pdur + 1);
   for (int i = 0; i < L.n_node_values; ++i) nodes[i] = cx.T.node_src[i] != 0xFFFF ? x[cx.T.node_src[i]] : 0.0;
   if (RT) {   // stage D
     for (int f = 0; f < L.n_rt_feet; ++f) {
@@ -45,16 +45,27 @@ static void EmuEval(const HostProgram& hp, const towr_b200_spec* s, const double
     }
     for (int poly = 0; poly < L.n_polys; ++poly) {
       const uint32_t pm = cx.T.poly_meta[poly];
-      double* o = rtd.data() + poly * 5;
+      double* o = rtd.data() + poly * kRtd;
       if (pm == kPolyFixed) {
         const int di = cx.T.polys[poly] >> 16;
-        o[0] = cx.T.durs[3 * di]; o[1] = cx.T.durs[3 * di + 1]; o[2] = cx.T.durs[3 * di + 2];
-        o[3] = cx.T.rdurs[2 * di]; o[4] = cx.T.rdurs[2 * di + 1];
+        o[kRtT] = cx.T.durs[3 * di]; o[kRtT2] = cx.T.durs[3 * di + 1]; o[kRtT3] = cx.T.durs[3 * di + 2];
+        o[kRtR2] = cx.T.rdurs[2 * di]; o[kRtR3] = cx.T.rdurs[2 * di + 1];
+        o[kRtR1] = 0.0; o[kRtR4] = 0.0; o[kRtEnd] = 0.0;
       } else {
         const RtFoot ft = cx.T.rt_feet[pm >> 24];
         const double Td = pdur[ft.phase0 + (pm & 0xFF)] / static_cast<double>((pm >> 8) & 0xFF);
         const double T2 = Td * Td, T3 = Cube(Td);
-        o[0] = Td; o[1] = T2; o[2] = T3; o[3] = 1.0 / T2; o[4] = 1.0 / T3;
+        o[kRtT] = Td; o[kRtT2] = T2; o[kRtT3] = T3; o[kRtR2] = 1.0 / T2; o[kRtR3] = 1.0 / T3;
+        o[kRtR1] = 1.0 / Td; o[kRtR4] = 1.0 / Pow4(Td);
+      }
+    }
+    for (int k = 0; k < L.n_rt_splines; ++k) {
+      const RtSpline sp = cx.T.rt_splines[k];
+      double acc = 0.0;
+      for (int j = 0; j < sp.n_polys; ++j) {
+        double* o = rtd.data() + (sp.poly0 + j) * kRtd;
+        acc += o[kRtT];
+        o[kRtEnd] = acc;
       }
     }
   }
@@ -64,8 +75,8 @@ static void EmuEval(const HostProgram& hp, const towr_b200_spec* s, const double
     int n0 = pr & 0xFFFF;
     double T, T2, T3, r2, r3;
     if (RT) {
-      const double* o = rtd.data() + poly * 5;
-      T = o[0]; T2 = o[1]; T3 = o[2]; r2 = o[3]; r3 = o[4];
+      const double* o = rtd.data() + poly * kRtd;
+      T = o[kRtT]; T2 = o[kRtT2]; T3 = o[kRtT3]; r2 = o[kRtR2]; r3 = o[kRtR3];
     } else {
       const double* du = cx.T.durs + 3 * (pr >> 16);
       const double* rd = cx.T.rdurs + 2 * (pr >> 16);

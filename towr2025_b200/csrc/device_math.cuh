@@ -94,8 +94,12 @@ __device__ __forceinline__ double Pow4(double t) {
 }
 
 // ---- PhaseSpline with optimised durations: the polynomial a global time falls into and its local time depend on
-// the problem's current durations.  rtd: per-problem polynomial durations, 5 per polynomial (T, T^2, T^3, 1/T^2,
-// 1/T^3), element i at rtd[i * NS].
+// the problem's current durations.  rtd: per-problem polynomial records of kRtd doubles (T, T^2, T^3, 1/T^2, 1/T^3,
+// 1/T, 1/T^4 and the end time of the polynomial within its spline, accumulated left to right like Spline::GetSegmentID's
+// `t += d`), element i at rtd[i * NS].  The reciprocals are true divisions (correctly rounded), so ExactDiv with them is
+// bit-identical to the reference's divisions at 3 instructions instead of a ~45-instruction software divide.
+constexpr int kRtd = 8;
+enum { kRtT = 0, kRtT2, kRtT3, kRtR2, kRtR3, kRtR1, kRtR4, kRtEnd };
 struct RtPoint {
   int poly;            // global polynomial index
   double t, T;         // local time, polynomial duration
@@ -110,18 +114,20 @@ __device__ __forceinline__ RtPoint EvalSplineRt(const Tables& tb_, const double*
   const uint32_t sr = tb_.samples[sample];
   const RtSpline sp = tb_.rt_splines[sr & 0xFFFF];
   const double tg = tb_.times[3 * (sr >> 16)];
+  // the polynomial end times are prefix sums made once per problem (stage D): the search only loads and compares
+  const double* pr = rtd + sp.poly0 * kRtd * NS;
+  const double lim = tg - 1e-10;
   int id = sp.n_polys - 1;
-  double acc = 0.0;
+#pragma unroll 4
   for (int i = 0; i < sp.n_polys; ++i) {
-    acc += rtd[(sp.poly0 + i) * 5 * NS];
-    if (acc >= tg - 1e-10) { id = i; break; }
+    if (pr[(i * kRtd + kRtEnd) * NS] >= lim) { id = i; break; }
   }
   double t = tg;
-  for (int i = 0; i < id; ++i) t -= rtd[(sp.poly0 + i) * 5 * NS];
+  for (int i = 0; i < id; ++i) t -= pr[i * kRtd * NS];
   RtPoint r;
   r.poly = sp.poly0 + id;
   r.t = t;
-  r.T = rtd[r.poly * 5 * NS];
+  r.T = pr[id * kRtd * NS];
   const double t2 = t * t, t3 = Cube(t);
   const int n0 = tb_.polys[r.poly] & 0xFFFF;
 #pragma unroll
@@ -138,16 +144,19 @@ __device__ __forceinline__ RtPoint EvalSplineRt(const Tables& tb_, const double*
 // W[c] = d pos(t) / d (variable c of the spline's set), all columns (NodeSpline::FillJacobianWrtNodes,
 // node_spline.cc:84-112, on the pre-filled structure of phase_spline.cc:45-51): zero except the variables mapped to
 // the active polynomial's two nodes; closed forms polynomial.cc:106-160 (kPos).  W: element c at W[c * GS].
-template <int GS>
-__device__ __forceinline__ void WriteHermiteWeights(const Tables& tb_, const RtSpline& sp, const RtPoint& r, double* W) {
+template <int GS, int NS>
+__device__ __forceinline__ void WriteHermiteWeights(const Tables& tb_, const double* __restrict__ rtd, const RtSpline& sp,
+                                                    const RtPoint& r, double* W) {
   for (int c = 0; c < sp.n_cols; ++c) W[c * GS] = 0.0;
-  const double t = r.t, T = r.T;
-  const double t2 = t * t, t3 = Cube(t), T2 = T * T, T3 = Cube(T);
+  const double* q = rtd + r.poly * kRtd * NS;
+  const double t = r.t, T = r.T, T2 = q[kRtT2 * NS], T3 = q[kRtT3 * NS];
+  const double r1 = q[kRtR1 * NS], r2 = q[kRtR2 * NS], r3 = q[kRtR3 * NS];
+  const double t2 = t * t, t3 = Cube(t);
   double b[4];
-  b[0] = (2 * t3) / T3 - (3 * t2) / T2 + 1;     // start node, position
-  b[1] = t - (2 * t2) / T + t3 / T2;             // start node, velocity
-  b[2] = (3 * t2) / T2 - (2 * t3) / T3;          // end node, position
-  b[3] = t3 / T2 - t2 / T;                       // end node, velocity
+  b[0] = ExactDiv(2 * t3, T3, r3) - ExactDiv(3 * t2, T2, r2) + 1;     // start node, position
+  b[1] = t - ExactDiv(2 * t2, T, r1) + ExactDiv(t3, T2, r2);          // start node, velocity
+  b[2] = ExactDiv(3 * t2, T2, r2) - ExactDiv(2 * t3, T3, r3);         // end node, position
+  b[3] = ExactDiv(t3, T2, r2) - ExactDiv(t2, T, r1);                  // end node, velocity
   const int n0 = tb_.polys[r.poly] & 0xFFFF;
 #pragma unroll
   for (int side = 0; side < 2; ++side)
@@ -166,21 +175,24 @@ __device__ __forceinline__ void WriteHermiteWeights(const Tables& tb_, const RtS
 // PhaseSpline::GetDerivativeOfPosWrtPhaseDuration (phase_spline.cc:77-93) with
 // CubicHermitePolynomial::GetDerivativeOfPosWrtDuration (polynomial.cc:236-257); returns the current phase
 template <int NS>
-__device__ __forceinline__ int PosWrtPhaseDuration(const Tables& tb_, const double* __restrict__ nodes, const RtPoint& r,
-                                                   const double vel[3], double dxdT[3]) {
+__device__ __forceinline__ int PosWrtPhaseDuration(const Tables& tb_, const double* __restrict__ nodes,
+                                                   const double* __restrict__ rtd, const RtPoint& r, const double vel[3],
+                                                   double dxdT[3]) {
   const uint32_t pm = tb_.poly_meta[r.poly];
   const int phase = pm & 0xFF, nin = (pm >> 8) & 0xFF, prev = (pm >> 16) & 0xFF;
-  const double t = r.t, T = r.T;
-  const double t2 = t * t, t3 = Cube(t), T2 = T * T, T3 = Cube(T), T4 = Pow4(T);
+  const double* q = rtd + r.poly * kRtd * NS;
+  const double t = r.t, T = r.T, T2 = q[kRtT2 * NS], T3 = q[kRtT3 * NS], T4 = Pow4(T);
+  const double r2 = q[kRtR2 * NS], r3 = q[kRtR3 * NS], r4 = q[kRtR4 * NS];
+  const double t2 = t * t, t3 = Cube(t);
   const int n0 = tb_.polys[r.poly] & 0xFFFF;
   const double inner = 1.0 / nin;
 #pragma unroll
   for (int d = 0; d < 3; ++d) {
     const double x0 = nodes[(n0 * 6 + d) * NS], v0 = nodes[(n0 * 6 + 3 + d) * NS];
     const double x1 = nodes[(n0 * 6 + 6 + d) * NS], v1 = nodes[(n0 * 6 + 9 + d) * NS];
-    const double dx = (((t3 * (v0 + v1)) / T3 - (t2 * (2.0 * v0 + v1)) / T2) -
-                       ((3 * t3) * (((2.0 * x0 - 2.0 * x1) + T * v0) + T * v1)) / T4) +
-                      ((2 * t2) * (((3.0 * x0 - 3.0 * x1) + (2 * T) * v0) + T * v1)) / T3;
+    const double dx = ((ExactDiv(t3 * (v0 + v1), T3, r3) - ExactDiv(t2 * (2.0 * v0 + v1), T2, r2)) -
+                       ExactDiv((3 * t3) * (((2.0 * x0 - 2.0 * x1) + T * v0) + T * v1), T4, r4)) +
+                      ExactDiv((2 * t2) * (((3.0 * x0 - 3.0 * x1) + (2 * T) * v0) + T * v1), T3, r3);
     dxdT[d] = inner * (dx - prev * vel[d]);
   }
   return phase;

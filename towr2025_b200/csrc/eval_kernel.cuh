@@ -161,8 +161,8 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
   const int nnv = Pg.blob.n_node_values, npoly = Pg.blob.n_polys;
   double* nodes = reinterpret_cast<double*>(blob + Pg.blob.bytes);
   double* coef = nodes + nnv * P;
-  double* rtd = coef + 6 * npoly * P;                   // RT: 5 per polynomial, then the phase durations
-  double* pdur = rtd + (RT ? 5 * npoly * P : 0);
+  double* rtd = coef + 6 * npoly * P;                   // RT: kRtd per polynomial, then the phase durations
+  double* pdur = rtd + (RT ? kRtd * npoly * P : 0);
   double* G = pdur + (RT ? Pg.blob.n_pdur * P : 0);
   // BULK: G shares a joint region with the staging buffer, which is aligned to the region's (16-byte aligned) end
   double* const joint_end = reinterpret_cast<double*>(reinterpret_cast<uintptr_t>(G + Pg.joint_capacity * P) & ~static_cast<uintptr_t>(15));
@@ -237,16 +237,29 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
       for (int i = tid; i < npoly * P; i += NT) {
         const int poly = i / P;
         const uint32_t pm = cx.T.poly_meta[poly];
-        double* o = rtd + poly * 5 * P + pl;
+        double* o = rtd + poly * kRtd * P + pl;
         if (pm == kPolyFixed) {
           const int di = cx.T.polys[poly] >> 16;
-          o[0] = cx.T.durs[3 * di]; o[P] = cx.T.durs[3 * di + 1]; o[2 * P] = cx.T.durs[3 * di + 2];
-          o[3 * P] = cx.T.rdurs[2 * di]; o[4 * P] = cx.T.rdurs[2 * di + 1];
+          o[kRtT * P] = cx.T.durs[3 * di]; o[kRtT2 * P] = cx.T.durs[3 * di + 1]; o[kRtT3 * P] = cx.T.durs[3 * di + 2];
+          o[kRtR2 * P] = cx.T.rdurs[2 * di]; o[kRtR3 * P] = cx.T.rdurs[2 * di + 1];
+          o[kRtR1 * P] = 0.0; o[kRtR4 * P] = 0.0; o[kRtEnd * P] = 0.0;   // base splines are never searched at run time
         } else {
           const RtFoot ft = cx.T.rt_feet[pm >> 24];
           const double Td = pdur[(ft.phase0 + (pm & 0xFF)) * P + pl] / static_cast<double>((pm >> 8) & 0xFF);
           const double T2 = Td * Td, T3 = Cube(Td);
-          o[0] = Td; o[P] = T2; o[2 * P] = T3; o[3 * P] = 1.0 / T2; o[4 * P] = 1.0 / T3;
+          o[kRtT * P] = Td; o[kRtT2 * P] = T2; o[kRtT3 * P] = T3; o[kRtR2 * P] = 1.0 / T2; o[kRtR3 * P] = 1.0 / T3;
+          o[kRtR1 * P] = 1.0 / Td; o[kRtR4 * P] = 1.0 / Pow4(Td);
+        }
+      }
+      __syncthreads();
+      // end time of every polynomial within its PhaseSpline: t += d from 0, as Spline::GetSegmentID (spline.cc:48-66)
+      for (int i = tid; i < Pg.blob.n_rt_splines * P; i += NT) {
+        const RtSpline sp = cx.T.rt_splines[i / P];
+        double acc = 0.0;
+        for (int j = 0; j < sp.n_polys; ++j) {
+          double* o = rtd + (sp.poly0 + j) * kRtd * P + pl;
+          acc += o[kRtT * P];
+          o[kRtEnd * P] = acc;
         }
       }
       __syncthreads();
@@ -260,8 +273,8 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
       const int n0 = pr & 0xFFFF;
       double T, T2, T3, r2, r3;
       if constexpr (RT) {
-        const double* o = rtd + poly * 5 * P + pl;
-        T = o[0]; T2 = o[P]; T3 = o[2 * P]; r2 = o[3 * P]; r3 = o[4 * P];
+        const double* o = rtd + poly * kRtd * P + pl;
+        T = o[kRtT * P]; T2 = o[kRtT2 * P]; T3 = o[kRtT3 * P]; r2 = o[kRtR2 * P]; r3 = o[kRtR3 * P];
       } else {
         const double* du = cx.T.durs + 3 * (pr >> 16);
         const double* rd = cx.T.rdurs + 2 * (pr >> 16);

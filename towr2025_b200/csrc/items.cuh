@@ -132,14 +132,14 @@ __device__ __forceinline__ void ItemDynFoot(const ItemCtx<L>& cx, const ItemC& i
     for (int d = 0; d < 3; ++d) { TB_G(neg + 3 * e + d) = -f.p[d]; TB_G(neg + 3 * E + 3 * e + d) = -r[d]; }
     const RtSpline sm = cx.T.rt_splines[e], sf = cx.T.rt_splines[E + e], st = cx.T.rt_splines[2 * E + e];
     double* X = cx.G + it.aux * L::GS;                 // this foot's block: W_p | W_f | W_tau | schedule[6][P-1]
-    WriteHermiteWeights<L::GS>(cx.T, sm, rp, X);
-    WriteHermiteWeights<L::GS>(cx.T, sf, rf, X + sm.n_cols * L::GS);
-    WriteHermiteWeights<L::GS>(cx.T, st, rt, X + (sm.n_cols + sf.n_cols) * L::GS);
+    WriteHermiteWeights<L::GS, L::NS>(cx.T, cx.rtd, sm, rp, X);
+    WriteHermiteWeights<L::GS, L::NS>(cx.T, cx.rtd, sf, rf, X + sm.n_cols * L::GS);
+    WriteHermiteWeights<L::GS, L::NS>(cx.T, cx.rtd, st, rt, X + (sm.n_cols + sf.n_cols) * L::GS);
     double* S = X + (sm.n_cols + sf.n_cols + st.n_cols) * L::GS;
     const RtFoot ft = cx.T.rt_feet[e];
     double dpT[3], dfT[3];
-    const int cur_p = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, rp, p.v, dpT);
-    const int cur_f = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, rf, f.v, dfT);
+    const int cur_p = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, cx.rtd, rp, p.v, dpT);
+    const int cur_f = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, cx.rtd, rf, f.v, dfT);
     const int nc = ft.n_phases - 1;
     for (int j = 0; j < nc; ++j) {
       double cf[3], cp[3];
@@ -367,11 +367,11 @@ __device__ __forceinline__ void ItemRomFoot(const ItemCtx<L>& cx, const ItemC& i
     // Hermite weights of the ee-motion spline and the finished ee-schedule block R^T J_p,dT
     // (range_of_motion_constraint.cc:126-130): G + 9 = W_p[n_cols] | schedule[3][P-1]
     const RtSpline sm = cx.T.rt_splines[it.ee];
-    WriteHermiteWeights<L::GS>(cx.T, sm, rp, G + 9 * L::GS);
+    WriteHermiteWeights<L::GS, L::NS>(cx.T, cx.rtd, sm, rp, G + 9 * L::GS);
     double* Sc = G + (9 + sm.n_cols) * L::GS;
     const RtFoot ft = cx.T.rt_feet[it.ee];
     double dpT[3];
-    const int cur = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, rp, p.v, dpT);
+    const int cur = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, cx.rtd, rp, p.v, dpT);
     const int nc = ft.n_phases - 1;
     for (int j = 0; j < nc; ++j) {
       double c[3];
@@ -436,11 +436,11 @@ __device__ __forceinline__ void ItemForce(const ItemCtx<L>& cx, const ItemC& it)
     // part is dropped where the terrain has no curvature, :58)
     const int E = cx.n_ee;
     const RtSpline sf = cx.T.rt_splines[E + it.ee];
-    WriteHermiteWeights<L::GS>(cx.T, sf, rf, G + 15 * L::GS);
+    WriteHermiteWeights<L::GS, L::NS>(cx.T, cx.rtd, sf, rf, G + 15 * L::GS);
     double* Sc = G + (15 + sf.n_cols) * L::GS;
     const RtFoot ft = cx.T.rt_feet[it.ee];
     double dfT[3];
-    const int cur = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, rf, f.v, dfT);
+    const int cur = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, cx.rtd, rf, f.v, dfT);
     const int nc = ft.n_phases - 1;
     for (int j = 0; j < nc; ++j) {
       double c[3];
@@ -542,13 +542,13 @@ __device__ __forceinline__ void ItemTorque(const ItemCtx<L>& cx, const ItemC& it
     // G + 15 = W_tau | W_f | schedule[4][P-1] (torque_constraint_discretized.cc:222-234)
     const int E = cx.n_ee;
     const RtSpline sf = cx.T.rt_splines[E + it.ee], st = cx.T.rt_splines[2 * E + it.ee];
-    WriteHermiteWeights<L::GS>(cx.T, st, rt, G + 15 * L::GS);
-    WriteHermiteWeights<L::GS>(cx.T, sf, rf, G + (15 + st.n_cols) * L::GS);
+    WriteHermiteWeights<L::GS, L::NS>(cx.T, cx.rtd, st, rt, G + 15 * L::GS);
+    WriteHermiteWeights<L::GS, L::NS>(cx.T, cx.rtd, sf, rf, G + (15 + st.n_cols) * L::GS);
     double* Sc = G + (15 + st.n_cols + sf.n_cols) * L::GS;
     const RtFoot ft = cx.T.rt_feet[it.ee];
     double dtT[3], dfT[3];
-    const int cur_t = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, rt, tau.v, dtT);
-    const int cur_f = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, rf, f.v, dfT);
+    const int cur_t = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, cx.rtd, rt, tau.v, dtT);
+    const int cur_f = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, cx.rtd, rf, f.v, dfT);
     const int nc = ft.n_phases - 1;
     for (int j = 0; j < nc; ++j) {
       double ct[3], cf[3];

@@ -14,7 +14,7 @@ TB_DECL(1, 0) TB_DECL(1, 1) TB_DECL(2, 0) TB_DECL(2, 1) TB_DECL(4, 0) TB_DECL(4,
 #undef TB_DECL
 
 size_t EvalSharedBytes(const DeviceProgram& P, int lanes) {
-  const size_t rt = P.blob.rt ? 5 * static_cast<size_t>(P.blob.n_polys) + P.blob.n_pdur : 0;
+  const size_t rt = P.blob.rt ? 8 * static_cast<size_t>(P.blob.n_polys) + P.blob.n_pdur : 0;   // kRtd (device_math.cuh)
   return static_cast<size_t>(P.blob.bytes) + sizeof(double) * lanes *
          (static_cast<size_t>(P.blob.n_node_values) + 6 * static_cast<size_t>(P.blob.n_polys) + rt + P.g_capacity);
 }
