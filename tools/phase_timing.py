@@ -32,12 +32,12 @@ def main():
     for it in range(3):
         b.eval_device(batch, T.EVAL_BOTH, dx.data_ptr(), dg.data_ptr(), dv.data_ptr())
         torch.cuda.synchronize()
-        reader = "towr_b200_debug_phase_clocks" + {"bulk": "_bulk", "ws": "_ws"}.get(os.environ.get("TOWR_B200_KERNEL", "lockstep"), "")
+        reader = "towr_b200_debug_phase_clocks" + {"bulk": "_bulk", "ws": "_ws", "wsbulk": "_ws"}.get(os.environ.get("TOWR_B200_KERNEL", "lockstep"), "")
         getattr(L, reader)(out, 64)
     v = list(out)
     tot = sum(v)
     print("raw:", v)
-    if os.environ.get("TOWR_B200_KERNEL", "") == "ws":
+    if os.environ.get("TOWR_B200_KERNEL", "") in ("ws", "wsbulk"):
         pn = ["wait x", "stage C", "wait empty", "L0 items", "L0->L1 barrier", "L1 items", "hand-off + group end"]
         pt = sum(v[:7]) or 1
         print("producer thread 0: %d clocks" % pt)

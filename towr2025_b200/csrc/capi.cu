@@ -92,6 +92,7 @@ struct towr_b200_batch {
   int max_ctas = 0, lanes = 0;
   bool ws = false;         // warp-specialised kernel (kernels_ws.cu)
   bool bulk = false;       // bulk-store kernel (kernels_tma.cu)
+  bool wsb = false;        // warp-specialised kernel with bulk-store consumers (kernels_ws.cu)
   std::unique_ptr<tb::HostProgram> hp_local;   // program rebuilt with a smaller G capacity (large class tables)
   long long launches = 0;
   // trajectory sampler tables per sampling period (trajectory.h)
@@ -289,6 +290,35 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
       }
       if (!b->bulk && kenv) throw std::runtime_error("unsupported: the bulk-store kernel does not fit this structure class");
     }
+    // warp-specialised kernel with bulk-store consumers: double-buffered G next to the consumers' staging ring
+    const bool want_wsb = kenv && std::strcmp(kenv, "wsbulk") == 0;
+    if (want_wsb) {
+      auto fits = [&](const tb::HostProgram& h) {
+        tb::DeviceProgram t{};
+        t.blob = h.blob;
+        t.g_capacity = h.g_capacity;
+        return tb::EvalFitsWSBulk(t, 2, prop.sharedMemPerBlockOptin);
+      };
+      if (!fits(*hpp)) {
+        tb::DeviceProgram t0{};
+        t0.blob = hpp->blob;
+        long long cap = (static_cast<long long>(prop.sharedMemPerBlockOptin) - static_cast<long long>(tb::EvalSharedBytesWSBulk(t0, 2)) - 1024 - 6144) / 32;
+        if (const char* env = std::getenv("TOWR_B200_GCAP")) cap = std::atoi(env);
+        bool ok = false;
+        for (int attempt = 0; attempt < 6 && cap > 256 && !ok; ++attempt, cap = cap * 15 / 16) {
+          auto h = std::make_unique<tb::HostProgram>();
+          tb::BuildProgram(st->spec, *h, static_cast<int>(cap));
+          if (fits(*h)) {
+            b->hp_local = std::move(h);
+            hpp = b->hp_local.get();
+            ok = true;
+          }
+        }
+        if (!ok) throw std::runtime_error("unsupported: the warp-specialised bulk kernel does not fit this structure class");
+      }
+      b->wsb = true;
+      b->lanes = 2;
+    }
     const tb::HostProgram& hp = *hpp;
     tb::DeviceProgram& dp = b->dp;
     dp.n_vars = hp.n_vars; dp.n_rows = hp.n_rows; dp.nnz = hp.nnz; dp.n_ee = hp.n_ee;
@@ -308,9 +338,9 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     keep(b->status_dev);
     Check(cudaMemset(b->status_dev, 0, sizeof(int) * n_problems), "cudaMemset(status)");
     // lanes per CTA: as many problems side by side as shared memory allows (the class tables are held once per CTA)
-    if (b->bulk) b->max_ctas = prop.multiProcessorCount;
+    if (b->bulk || b->wsb) b->max_ctas = prop.multiProcessorCount;
     // the warp-specialised kernel when its double-buffered G fits
-    const bool want_ws = !b->bulk && (!kenv || std::strcmp(kenv, "ws") == 0);
+    const bool want_ws = !b->bulk && !b->wsb && (!kenv || std::strcmp(kenv, "ws") == 0);
     if (want_ws && (!forced || forced == 2) && tb::EvalFitsWS(dp, 2, prop.sharedMemPerBlockOptin)) {
       b->ws = true;
       b->lanes = 2;
@@ -319,7 +349,7 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
       throw std::runtime_error("unsupported: the warp-specialised kernel does not fit this structure class");
     }
     for (int lanes : {4, 2, 1}) {
-      if (b->ws || b->bulk) break;
+      if (b->ws || b->bulk || b->wsb) break;
       if (forced && lanes != forced) continue;
       if (tb::EvalSharedBytes(dp, lanes) > static_cast<size_t>(prop.sharedMemPerBlockOptin)) continue;
       int occ = tb::EvalOccupancy(dp, lanes);
@@ -332,8 +362,8 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
       throw std::runtime_error("unsupported: structure class needs more shared memory per CTA than the device has");
     if (std::getenv("TOWR_B200_DEBUG"))
       std::fprintf(stderr, "batch: %s kernel, %d problems per CTA, %zu B shared (blob %d B, G capacity %d), %d CTAs\n",
-                   b->bulk ? "bulk-store" : b->ws ? "warp-specialised" : "lock-step", b->lanes,
-                   b->bulk ? tb::EvalSharedBytesBulk(dp, b->lanes)
+                   b->wsb ? "warp-specialised bulk" : b->bulk ? "bulk-store" : b->ws ? "warp-specialised" : "lock-step", b->lanes,
+                   b->wsb ? tb::EvalSharedBytesWSBulk(dp, b->lanes) : b->bulk ? tb::EvalSharedBytesBulk(dp, b->lanes)
                            : b->ws ? tb::EvalSharedBytesWS(dp, b->lanes) : tb::EvalSharedBytes(dp, b->lanes),
                    dp.blob.bytes, dp.g_capacity, b->max_ctas);
     if (std::getenv("TOWR_B200_DEBUG"))
@@ -376,7 +406,7 @@ int towr_b200_batch_eval_device(towr_b200_batch* b, int n, int what, const doubl
       b->SyncConsts();
       Check(cudaStreamSynchronize(b->stream), "sync consts");
     }
-    Check((b->bulk ? tb::LaunchEvalBulk : b->ws ? tb::LaunchEvalWS : tb::LaunchEval)(b->dp, b->pc_dev, what, d_x, d_g, d_jac_values, b->status_dev, n,
+    Check((b->wsb ? tb::LaunchEvalWSBulk : b->bulk ? tb::LaunchEvalBulk : b->ws ? tb::LaunchEvalWS : tb::LaunchEval)(b->dp, b->pc_dev, what, d_x, d_g, d_jac_values, b->status_dev, n,
                                                        b->lanes, b->max_ctas, s), "launch");
     b->launches += 1;
   });
@@ -417,7 +447,7 @@ int towr_b200_batch_eval(towr_b200_batch* b, const int* ids, int n, int what, co
       b->SyncConsts();
     }
     Check(cudaMemcpyAsync(b->x_dev, x, sizeof(double) * dp.n_vars * n, cudaMemcpyHostToDevice, b->stream), "H2D x");
-    Check((b->bulk ? tb::LaunchEvalBulk : b->ws ? tb::LaunchEvalWS : tb::LaunchEval)(dp, pcs, what, b->x_dev, b->g_dev, b->v_dev, b->status_dev, n, b->lanes,
+    Check((b->wsb ? tb::LaunchEvalWSBulk : b->bulk ? tb::LaunchEvalBulk : b->ws ? tb::LaunchEvalWS : tb::LaunchEval)(dp, pcs, what, b->x_dev, b->g_dev, b->v_dev, b->status_dev, n, b->lanes,
                                                        b->max_ctas, b->stream), "launch");
     b->launches += 1;
     if (what & TOWR_B200_EVAL_G)

@@ -18,6 +18,11 @@ size_t EvalSharedBytesWS(const DeviceProgram& P, int lanes);
 bool EvalFitsWS(const DeviceProgram& P, int lanes, size_t smem_optin);
 cudaError_t LaunchEvalWS(const DeviceProgram& P, const ProblemConst* pcs, int what, const double* x, double* g,
                          double* vals, int* status, int n_problems, int lanes, int max_ctas, cudaStream_t stream);
+// warp-specialised kernel whose consumer warps stage sub-blocks in shared memory and store them with cp.async.bulk
+size_t EvalSharedBytesWSBulk(const DeviceProgram& P, int lanes);
+bool EvalFitsWSBulk(const DeviceProgram& P, int lanes, size_t smem_optin);
+cudaError_t LaunchEvalWSBulk(const DeviceProgram& P, const ProblemConst* pcs, int what, const double* x, double* g,
+                             double* vals, int* status, int n_problems, int lanes, int max_ctas, cudaStream_t stream);
 // bulk-store kernel (kernels_tma.cu): stage B goes through a shared-memory staging buffer and cp.async.bulk stores
 size_t EvalSharedBytesBulk(const DeviceProgram& P, int lanes);
 bool EvalFitsBulk(const DeviceProgram& P, int lanes, size_t smem_optin);

@@ -16,7 +16,16 @@ namespace tb {
 __device__ __forceinline__ void BarSync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ void BarArrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
-template <int WHAT, int P, int NA, int NB>
+// BULK: the consumer warps do not store to global memory themselves.  Each warp multiplies a sub-block of kSubBlock
+// consecutive entries into a private ring slot in shared memory (storage order, one row per problem lane) and one lane per
+// problem hands the row to the TMA engine (cp.async.bulk shared -> global, >= 2 KB per copy: the engine retires about one
+// copy per 64 clocks, tools/micro/bulk_store_bw.cu).  The value stores then never enter the LSU pipe, which the producers
+// need for stage A's shared-memory traffic, and the consumers are done with a G buffer as soon as its products are staged.
+constexpr int kSubBlock = 256;          // entries per sub-block: 8 per lane
+constexpr int kRingSlots = 2;           // sub-blocks in flight per consumer warp
+constexpr int kRingRow = kSubBlock + 2; // doubles per problem lane in a slot (+ parity slack, even)
+
+template <int WHAT, int P, int NA, int NB, bool BULK = false>
 __global__ void __launch_bounds__(NA + NB, 1)
 EvalKernelWS(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restrict__ pcs, const double* __restrict__ x,
              double* __restrict__ g_out, double* __restrict__ vals_out, int* __restrict__ status, int n_problems) {
@@ -29,6 +38,8 @@ EvalKernelWS(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __res
   double* coef = nodes + nnv * P;
   double* Gbuf = coef + 6 * npoly * P;                   // two buffers of g_capacity * P
   const int gstride = Pg.g_capacity * P;
+  // BULK: ring of staging slots, one set per consumer warp, 16-byte aligned
+  double* const ring_base = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(Gbuf + 2 * gstride) + 15) & ~static_cast<uintptr_t>(15));
   __shared__ ProblemConst pc_all[P];
   const int tid = threadIdx.x;
   {
@@ -119,6 +130,7 @@ EvalKernelWS(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __res
     // ------------------------------------------------------------------------------------------ consumers
     const int ct = tid - NA;
     int k = 0;
+    int slot = 0;                                          // BULK: ring slot counter of this warp
     for (int base = blockIdx.x * P; base < n_problems; base += gridDim.x * P) {
       double nf[P];
 #pragma unroll
@@ -127,6 +139,89 @@ EvalKernelWS(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __res
         const SegmentRec sg = T.segments[s];
         const int buf = k & 1;
         const double* G = Gbuf + buf * gstride;
+        if constexpr (BULK) {
+          constexpr int NBW = NB / 32, U = kSubBlock / 32;
+          const int cw = ct >> 5, lane = ct & 31;
+          double* const ring = ring_base + cw * (kRingSlots * P * kRingRow);
+          const uint32_t* ent = Pg.entries + sg.entry0;
+          const int ne = sg.n_entries;
+          const int n_sub = (ne + kSubBlock - 1) / kSubBlock;
+          uint32_t dn[U];
+          auto load_desc = [&](int j, uint32_t (&d)[U]) {
+            const int e0 = j * kSubBlock + lane;
+#pragma unroll
+            for (int u = 0; u < U; ++u) d[u] = (j < n_sub && e0 + 32 * u < ne) ? __ldg(ent + e0 + 32 * u) : kNoEntry;
+          };
+          if (WHAT & TOWR_B200_EVAL_JAC) load_desc(cw, dn);            // before the wait: off the critical path
+          TB_MARK_T(16, NA)
+          BarSync(kBarFull + buf, NALL);
+          TB_MARK_T(17, NA)
+          if (WHAT & TOWR_B200_EVAL_JAC) {
+            // 8-byte parity of each lane's first destination element (sub-blocks start at even offsets)
+            int q[P];
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+              const size_t e0 = static_cast<size_t>(min(base + p, n_problems - 1)) * Pg.nnz + sg.entry0;
+              q[p] = static_cast<int>(((reinterpret_cast<uintptr_t>(vals_out) >> 3) + e0) & 1);
+            }
+            const char* Gb = reinterpret_cast<const char*>(G);
+            const char* Bb = reinterpret_cast<const char*>(T.B);
+            for (int j = cw; j < n_sub; j += NBW, ++slot) {
+              uint32_t d[U];
+#pragma unroll
+              for (int u = 0; u < U; ++u) d[u] = dn[u];
+              load_desc(j + NBW, dn);                                   // next sub-block of this warp
+              // the slot's previous copy must have been read out
+              if (lane < P) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kRingSlots - 1) : "memory");
+              __syncwarp();
+              double* const sl = ring + (slot % kRingSlots) * (P * kRingRow);
+              auto emit = [&](uint32_t w, int u) {
+                const double bv = *reinterpret_cast<const double*>(Bb + (w >> 16));
+                const char* ga = Gb + (w & 0xFFFFu) * P;
+#pragma unroll
+                for (int p = 0; p < P; p += 2) {
+                  const double2 t = *reinterpret_cast<const double2*>(ga + 8 * p);
+                  const double v0 = t.x * bv, v1 = t.y * bv;
+                  nf[p] = fma(v0, 0.0, nf[p]);
+                  nf[p + 1] = fma(v1, 0.0, nf[p + 1]);
+                  sl[p * kRingRow + q[p] + 32 * u + lane] = v0;
+                  sl[(p + 1) * kRingRow + q[p + 1] + 32 * u + lane] = v1;
+                }
+              };
+              if (ne - j * kSubBlock >= kSubBlock) {                    // full sub-block: no per-entry test, loads batch up
+#pragma unroll
+                for (int u = 0; u < U; ++u) emit(d[u], u);
+              } else {
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+                  if (d[u] != kNoEntry) emit(d[u], u);
+              }
+#if defined(TB_WSB_FENCE_ONE)
+              __syncwarp();
+              if (lane < P) FenceProxyAsync();
+#elif !defined(TB_WSB_NOFENCE)
+              FenceProxyAsync();
+              __syncwarp();
+#else
+              __syncwarp();
+#endif
+              if (lane < P && base + lane < n_problems) {
+                const int e0 = j * kSubBlock, cnt = min(kSubBlock, ne - e0);
+                double* dst = vals_out + static_cast<size_t>(base + lane) * Pg.nnz + sg.entry0 + e0;
+                int ql = q[0];
+#pragma unroll
+                for (int p = 1; p < P; ++p)
+                  if (lane == p) ql = q[p];
+                const double* src = sl + lane * kRingRow + ql;         // entry i of the sub-block at src[i]
+                if (ql) dst[0] = src[0];
+                const int body = (cnt - ql) & ~1;
+                if (body > 0) BulkStore(dst + ql, src + ql, static_cast<unsigned>(body) * 8u);
+                if ((cnt - ql) & 1) dst[cnt - 1] = src[cnt - 1];
+              }
+              if (lane < P) BulkCommit();
+            }
+          }
+        } else {
         const uint32_t* ent = Pg.entries + sg.entry0 + ct;
         uint32_t d0[DescAhead<false>::value][kDescBatch];
         if (WHAT & TOWR_B200_EVAL_JAC) LoadDescriptorRing<NB>(ent, sg.n_entries - ct, d0);
@@ -140,6 +235,7 @@ EvalKernelWS(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __res
           else
             StageB<P, false, NB>(ent, sg.n_entries - ct, d0, G, T.B, o0, Pg.nnz, n_problems - base, nf);
         }
+        }
         TB_MARK_T(18, NA)
         if (k + 2 < k_total) BarArrive(kBarEmpty + buf, NALL);
       }
@@ -147,6 +243,8 @@ EvalKernelWS(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __res
       for (int p = 0; p < P; ++p)
         if (nf[p] != nf[p] && base + p < n_problems) atomicOr(status + base + p, 2);
     }
+    // the ring must outlive the bulk copies that read it
+    if (BULK && (WHAT & TOWR_B200_EVAL_JAC) && (ct & 31) < P) BulkWaitAll();
   }
 }
 
@@ -156,22 +254,33 @@ size_t EvalSharedBytesWS(const DeviceProgram& P, int lanes) {
 }
 
 #ifndef TB_WS_NA
-#define TB_WS_NA 256
+#define TB_WS_NA 320
 #endif
 #ifndef TB_WS_NB
-#define TB_WS_NB 256
+#define TB_WS_NB 192
+#endif
+#ifndef TB_WSB_NA
+#define TB_WSB_NA 384
+#endif
+#ifndef TB_WSB_NB
+#define TB_WSB_NB 128
 #endif
 
-template <int WHAT, int LANES>
+size_t EvalSharedBytesWSBulk(const DeviceProgram& P, int lanes) {
+  return EvalSharedBytesWS(P, lanes) + 16 + sizeof(double) * (TB_WSB_NB / 32) * kRingSlots * lanes * kRingRow;
+}
+
+template <int WHAT, int LANES, bool BULK>
 static cudaError_t LaunchWS(const DeviceProgram& P, const ProblemConst* pcs, const double* x, double* g, double* vals,
                             int* status, int n_problems, int max_ctas, cudaStream_t stream) {
-  const size_t smem = EvalSharedBytesWS(P, LANES);
-  auto kern = EvalKernelWS<WHAT, LANES, TB_WS_NA, TB_WS_NB>;
+  constexpr int NA = BULK ? TB_WSB_NA : TB_WS_NA, NB = BULK ? TB_WSB_NB : TB_WS_NB;
+  const size_t smem = BULK ? EvalSharedBytesWSBulk(P, LANES) : EvalSharedBytesWS(P, LANES);
+  auto kern = EvalKernelWS<WHAT, LANES, NA, NB, BULK>;
   cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
   if (err != cudaSuccess) return err;
   int grid = (n_problems + LANES - 1) / LANES;
   if (grid > max_ctas) grid = max_ctas;
-  kern<<<grid, TB_WS_NA + TB_WS_NB, smem, stream>>>(P, pcs, x, g, vals, status, n_problems);
+  kern<<<grid, NA + NB, smem, stream>>>(P, pcs, x, g, vals, status, n_problems);
   return cudaGetLastError();
 }
 
@@ -180,11 +289,28 @@ cudaError_t LaunchEvalWS(const DeviceProgram& P, const ProblemConst* pcs, int wh
   if (n_problems <= 0) return cudaSuccess;
   if (lanes != 2) return cudaErrorInvalidValue;
   switch (what) {
-    case TOWR_B200_EVAL_G: return LaunchWS<1, 2>(P, pcs, x, g, vals, status, n_problems, max_ctas, stream);
-    case TOWR_B200_EVAL_JAC: return LaunchWS<2, 2>(P, pcs, x, g, vals, status, n_problems, max_ctas, stream);
-    case TOWR_B200_EVAL_BOTH: return LaunchWS<3, 2>(P, pcs, x, g, vals, status, n_problems, max_ctas, stream);
+    case TOWR_B200_EVAL_G: return LaunchWS<1, 2, false>(P, pcs, x, g, vals, status, n_problems, max_ctas, stream);
+    case TOWR_B200_EVAL_JAC: return LaunchWS<2, 2, false>(P, pcs, x, g, vals, status, n_problems, max_ctas, stream);
+    case TOWR_B200_EVAL_BOTH: return LaunchWS<3, 2, false>(P, pcs, x, g, vals, status, n_problems, max_ctas, stream);
   }
   return cudaErrorInvalidValue;
+}
+
+cudaError_t LaunchEvalWSBulk(const DeviceProgram& P, const ProblemConst* pcs, int what, const double* x, double* g,
+                             double* vals, int* status, int n_problems, int lanes, int max_ctas, cudaStream_t stream) {
+  if (n_problems <= 0) return cudaSuccess;
+  if (lanes != 2) return cudaErrorInvalidValue;
+  switch (what) {
+    case TOWR_B200_EVAL_G: return LaunchWS<1, 2, true>(P, pcs, x, g, vals, status, n_problems, max_ctas, stream);
+    case TOWR_B200_EVAL_JAC: return LaunchWS<2, 2, true>(P, pcs, x, g, vals, status, n_problems, max_ctas, stream);
+    case TOWR_B200_EVAL_BOTH: return LaunchWS<3, 2, true>(P, pcs, x, g, vals, status, n_problems, max_ctas, stream);
+  }
+  return cudaErrorInvalidValue;
+}
+
+bool EvalFitsWSBulk(const DeviceProgram& P, int lanes, size_t smem_optin) {
+  if (lanes != 2 || P.blob.rt) return false;
+  return EvalSharedBytesWSBulk(P, lanes) + 1024 <= smem_optin;
 }
 
 bool EvalFitsWS(const DeviceProgram& P, int lanes, size_t smem_optin) {
