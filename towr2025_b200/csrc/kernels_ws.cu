@@ -174,6 +174,7 @@ EvalKernelWS(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __res
               // the slot's previous copy must have been read out
               if (lane < P) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kRingSlots - 1) : "memory");
               __syncwarp();
+              TB_MARK_T(19, NA)
               double* const sl = ring + (slot % kRingSlots) * (P * kRingRow);
               auto emit = [&](uint32_t w, int u) {
                 const double bv = *reinterpret_cast<const double*>(Bb + (w >> 16));
@@ -196,6 +197,7 @@ EvalKernelWS(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __res
                 for (int u = 0; u < U; ++u)
                   if (d[u] != kNoEntry) emit(d[u], u);
               }
+              TB_MARK_T(20, NA)
 #if defined(TB_WSB_FENCE_ONE)
               __syncwarp();
               if (lane < P) FenceProxyAsync();
@@ -219,6 +221,7 @@ EvalKernelWS(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __res
                 if ((cnt - ql) & 1) dst[cnt - 1] = src[cnt - 1];
               }
               if (lane < P) BulkCommit();
+              TB_MARK_T(21, NA)
             }
           }
         } else {
