@@ -290,19 +290,22 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
       }
       if (!b->bulk && kenv) throw std::runtime_error("unsupported: the bulk-store kernel does not fit this structure class");
     }
-    // warp-specialised kernel with bulk-store consumers: double-buffered G next to the consumers' staging ring
+    // warp-specialised kernels (opt-in): a double-buffered G (and, with bulk-store consumers, their staging ring) must
+    // fit: lower the G capacity until it does
     const bool want_wsb = kenv && std::strcmp(kenv, "wsbulk") == 0;
-    if (want_wsb) {
+    const bool want_ws_forced = kenv && std::strcmp(kenv, "ws") == 0;
+    if ((want_wsb || want_ws_forced) && !hpp->optimize_durations) {
+      auto bytes = [&](const tb::DeviceProgram& t) { return want_wsb ? tb::EvalSharedBytesWSBulk(t, 2) : tb::EvalSharedBytesWS(t, 2); };
       auto fits = [&](const tb::HostProgram& h) {
         tb::DeviceProgram t{};
         t.blob = h.blob;
         t.g_capacity = h.g_capacity;
-        return tb::EvalFitsWSBulk(t, 2, prop.sharedMemPerBlockOptin);
+        return bytes(t) + 1024 <= static_cast<size_t>(prop.sharedMemPerBlockOptin);
       };
       if (!fits(*hpp)) {
         tb::DeviceProgram t0{};
         t0.blob = hpp->blob;
-        long long cap = (static_cast<long long>(prop.sharedMemPerBlockOptin) - static_cast<long long>(tb::EvalSharedBytesWSBulk(t0, 2)) - 1024 - 6144) / 32;
+        long long cap = (static_cast<long long>(prop.sharedMemPerBlockOptin) - static_cast<long long>(bytes(t0)) - 1024 - 6144) / 32;
         if (const char* env = std::getenv("TOWR_B200_GCAP")) cap = std::atoi(env);
         bool ok = false;
         for (int attempt = 0; attempt < 6 && cap > 256 && !ok; ++attempt, cap = cap * 15 / 16) {
@@ -314,10 +317,14 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
             ok = true;
           }
         }
-        if (!ok) throw std::runtime_error("unsupported: the warp-specialised bulk kernel does not fit this structure class");
+        if (!ok) throw std::runtime_error("unsupported: the warp-specialised kernel does not fit this structure class");
       }
-      b->wsb = true;
-      b->lanes = 2;
+      if (want_wsb) {
+        b->wsb = true;
+        b->lanes = 2;
+      }
+    } else if (want_wsb) {
+      throw std::runtime_error("unsupported: classes with optimised durations run on the lock-step kernel");
     }
     const tb::HostProgram& hp = *hpp;
     tb::DeviceProgram& dp = b->dp;
