@@ -189,9 +189,28 @@ EvalKernelWS(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __res
                   sl[(p + 1) * kRingRow + q[p + 1] + 32 * u + lane] = v1;
                 }
               };
-              if (ne - j * kSubBlock >= kSubBlock) {                    // full sub-block: no per-entry test, loads batch up
+              if (ne - j * kSubBlock >= kSubBlock) {
+                // full sub-block: all operands first, then the products (the staging stores could alias G and B for the
+                // compiler, which would otherwise keep every load behind the previous entry's stores)
+                double bv[U];
+                double2 gv[U][P / 2];
 #pragma unroll
-                for (int u = 0; u < U; ++u) emit(d[u], u);
+                for (int u = 0; u < U; ++u) {
+                  bv[u] = *reinterpret_cast<const double*>(Bb + (d[u] >> 16));
+                  const char* ga = Gb + (d[u] & 0xFFFFu) * P;
+#pragma unroll
+                  for (int p = 0; p < P; p += 2) gv[u][p / 2] = *reinterpret_cast<const double2*>(ga + 8 * p);
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u)
+#pragma unroll
+                  for (int p = 0; p < P; p += 2) {
+                    const double v0 = gv[u][p / 2].x * bv[u], v1 = gv[u][p / 2].y * bv[u];
+                    nf[p] = fma(v0, 0.0, nf[p]);
+                    nf[p + 1] = fma(v1, 0.0, nf[p + 1]);
+                    sl[p * kRingRow + q[p] + 32 * u + lane] = v0;
+                    sl[(p + 1) * kRingRow + q[p + 1] + 32 * u + lane] = v1;
+                  }
               } else {
 #pragma unroll
                 for (int u = 0; u < U; ++u)
