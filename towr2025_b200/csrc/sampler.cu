@@ -86,7 +86,9 @@ SampleKernel(const __grid_constant__ TrajDevice Tj, const double* __restrict__ x
       const int kc = min(kRowChunk, Tj.n_samples - k0);
       const int n_items = kc * Tj.n_splines;
       for (int i = tid; i < n_items; i += kSampleThreads) {
-        const int kl = i / Tj.n_splines, s = i - kl * Tj.n_splines, k = k0 + kl;
+        // consecutive threads take consecutive samples of one spline: they mostly share the polynomial (broadcast reads
+        // of its node / coefficient record), read the sample tables coalesced and write rows with an odd stride
+        const int s = i / kc, kl = i - s * kc, k = k0 + kl;
         const TrajSplineRec sp = splines[s];
         const double tg = __ldg(Tj.times + k);
         int poly;
