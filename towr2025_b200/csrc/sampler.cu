@@ -14,7 +14,7 @@
 namespace tb {
 
 constexpr int kSampleThreads = 256;
-constexpr int kRowChunk = 24;          // samples staged per pass (three CTAs per SM stay resident)
+constexpr int kRowChunk = 32;          // samples staged per pass (one warp = one spline's samples of the chunk)
 constexpr int kRec = 7;                // doubles per node / coefficient record in shared memory: 6 used; with a stride of 6
                                        // doubles the records of a warp's splines fall onto 8 bank groups (9 wavefronts per LDS.64)
 
@@ -27,14 +27,12 @@ SampleKernel(const __grid_constant__ TrajDevice Tj, const double* __restrict__ x
   double* pdur = pT + 3 * Tj.n_polys;         // optimised durations: phase durations of every foot
   double* rowbuf = pdur + Tj.n_phases;        // kRowChunk rows
   // class tables, staged once per CTA (every lookup below would otherwise be an L2 round trip)
-  double* cT = rowbuf + kRowChunk * Tj.width;                                   // poly_T
-  TrajSplineRec* splines = reinterpret_cast<TrajSplineRec*>(cT + 3 * Tj.n_polys);
+  TrajSplineRec* splines = reinterpret_cast<TrajSplineRec*>(rowbuf + kRowChunk * Tj.width);
   TrajFootRec* feet = reinterpret_cast<TrajFootRec*>(splines + Tj.n_splines);
   uint32_t* pmeta = reinterpret_cast<uint32_t*>(feet + Tj.n_ee);
   uint16_t* pspl = reinterpret_cast<uint16_t*>(pmeta + Tj.n_polys);
   uint16_t* nsrc = pspl + Tj.n_polys;
   const int tid = threadIdx.x;
-  for (int i = tid; i < 3 * Tj.n_polys; i += kSampleThreads) cT[i] = Tj.poly_T[i];
   for (int i = tid; i < Tj.n_splines; i += kSampleThreads) splines[i] = Tj.splines[i];
   for (int i = tid; i < Tj.n_ee; i += kSampleThreads) feet[i] = Tj.feet[i];
   for (int i = tid; i < Tj.n_polys; i += kSampleThreads) { pmeta[i] = Tj.poly_meta[i]; pspl[i] = Tj.poly_spline[i]; }
@@ -61,7 +59,8 @@ SampleKernel(const __grid_constant__ TrajDevice Tj, const double* __restrict__ x
     for (int poly = tid; poly < Tj.n_polys; poly += kSampleThreads) {   // polynomial durations
       const uint32_t pm = pmeta[poly];
       if (pm == kPolyFixed) {
-        pT[3 * poly] = cT[3 * poly]; pT[3 * poly + 1] = cT[3 * poly + 1]; pT[3 * poly + 2] = cT[3 * poly + 2];
+        pT[3 * poly] = __ldg(Tj.poly_T + 3 * poly); pT[3 * poly + 1] = __ldg(Tj.poly_T + 3 * poly + 1);
+        pT[3 * poly + 2] = __ldg(Tj.poly_T + 3 * poly + 2);
       } else {                                 // ConvertPhaseToPolyDurations (nodes_variables_phase_based.cc:75-86)
         const double Td = pdur[feet[splines[pspl[poly]].foot].phase0 + (pm & 0xFF)] / static_cast<double>((pm >> 8) & 0xFF);
         pT[3 * poly] = Td; pT[3 * poly + 1] = Td * Td; pT[3 * poly + 2] = Cube(Td);
@@ -151,7 +150,7 @@ SampleKernel(const __grid_constant__ TrajDevice Tj, const double* __restrict__ x
 }
 
 size_t TrajSharedBytes(const TrajDevice& t) {
-  return sizeof(double) * (kRec * static_cast<size_t>(t.n_nodes) + (kRec + 6) * static_cast<size_t>(t.n_polys) + t.n_phases +
+  return sizeof(double) * (kRec * static_cast<size_t>(t.n_nodes) + (kRec + 3) * static_cast<size_t>(t.n_polys) + t.n_phases +
                            static_cast<size_t>(kRowChunk) * t.width) +
          sizeof(TrajSplineRec) * t.n_splines + sizeof(TrajFootRec) * t.n_ee + 6 * static_cast<size_t>(t.n_polys) +
          12 * static_cast<size_t>(t.n_nodes) + 16;
