@@ -143,7 +143,7 @@ SampleKernel(const __grid_constant__ TrajDevice Tj, const double* __restrict__ x
       __syncthreads();
       double* dst = rows + static_cast<size_t>(k0) * Tj.width;
 #pragma unroll 4
-      for (int i = tid; i < kc * Tj.width; i += kSampleThreads) dst[i] = rowbuf[i];
+      for (int i = tid; i < kc * Tj.width; i += kSampleThreads) __stcs(dst + i, rowbuf[i]);   // streaming: rows are never read back
       __syncthreads();
     }
   }
