@@ -82,6 +82,23 @@ def test_error_behaviour(product):
         T.make_spec(5, T.C1, 2.0)
 
 
+def test_gap_terrain_is_refused(product):
+    """Gap has a value-dependent curvature block (force_constraint_discretized.cc:52-67) that is not built: creating a
+    class on it, or admitting a Gap problem into a curvature-free class, must fail as UNSUPPORTED - never rc 0 with a
+    Jacobian that lacks the block."""
+    T = product
+    for opt in (False, True):
+        with pytest.raises(T.TowrB200Error) as e:
+            T.Structure(T.make_spec(T.Hyq, T.C4, 2.4, terrain=T.GapID, optimize_durations=opt))
+        assert e.value.code == -2 and "Gap" in str(e.value)
+    st = T.Structure(T.make_spec(T.Hyq, T.C4, 2.4, terrain=T.BlockID))
+    gap = T.make_spec(T.Hyq, T.C4, 2.4, terrain=T.GapID)
+    assert not st.accepts(gap)
+    with pytest.raises(T.TowrB200Error) as e:
+        st.x0(gap)
+    assert "Gap" in str(e.value)
+
+
 def test_library_exports_every_declared_symbol(product):
     """The C-ABI library loads without a GPU and exports everything include/towr_b200.h declares."""
     import os

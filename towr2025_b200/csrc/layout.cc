@@ -167,6 +167,12 @@ void ValidateSpec(const towr_b200_spec& s) {
       s.torque_polynomials_per_stance_phase < 1)
     throw std::runtime_error("polynomials per phase must be >= 1");
   if (s.terrain_id < 0 || s.terrain_id >= TOWR_B200_TERRAIN_COUNT) throw std::runtime_error("unknown terrain id");
+  // Gap is the one terrain with non-zero second derivatives (height_map_examples.cc:89-120): the reference then stores
+  // f . d(basis)/dx entries in the force / torque constraint's ee-motion block whenever a foot is over the parabola
+  // (force_constraint_discretized.cc:52-67, value-dependent pattern).  That block is not built: refuse the
+  // terrain instead of returning a Jacobian without it.
+  if (s.terrain_id == TOWR_B200_GAP)
+    throw std::runtime_error("unsupported: the Gap terrain (curvature block of the force constraint is not built)");
   if (s.n_costs < 0 || s.n_costs > TOWR_B200_MAX_COSTS) throw std::runtime_error("bad n_costs");
   for (int c = 0; c < s.n_costs; ++c) {
     if (s.cost_ids[c] == TOWR_B200_COST_ENERGY || s.cost_ids[c] == TOWR_B200_COST_ANG_MOM)
