@@ -168,6 +168,22 @@ int towr_b200_batch_eval_cost(towr_b200_batch* b, int n, int what, const double*
 int towr_b200_batch_eval_cost_device(towr_b200_batch* b, int n, int what, const double* d_x, double* d_f, double* d_grad,
                                      void* stream);
 
+/* Allocation-free eval_f / eval_grad_f.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same kernel and results as towr_b200_batch_eval_cost_device, but it needs no batch and performs no cudaMalloc /
+ * cudaFree or any other device allocation: the kernel's work tables (column pointers and weights of the class's cost
+ * terms) go into a fixed file-scope device array of the library (about 144 KB, held by every GPU that loads the library
+ * until the process exits) by two cudaMemcpyAsync on `stream`.  Limits: n_vars <= TOWR_B200_STATIC_COST_MAX_VARS and at
+ * most TOWR_B200_STATIC_COST_MAX_WEIGHTS (variable, node value) weights, else TOWR_B200_ERR_ARG with a message naming
+ * the limit.  d_x (n x n_vars), d_f (n) and d_grad (n x n_vars) are device memory on `device`, as for the _device entry
+ * point.  ALL calls share the one array, which keeps the last call's tables (each call rewrites the part it uses;
+ * nothing in it has to start at zero): calls that overlap on the GPU - different streams, or threads - race; order
+ * them on one stream. */
+#define TOWR_B200_STATIC_COST_MAX_VARS 4096
+#define TOWR_B200_STATIC_COST_MAX_WEIGHTS 16384
+int towr_b200_eval_cost_static(const towr_b200_structure* st, int device, int n, int what, const double* d_x, double* d_f,
+                               double* d_grad, void* stream);
+
 /* ---- trajectory sampling: the step on the far side of the solver -------------------------------------------------
  * Replaces towr::SaveTrajectoryToCSV's sampling loop (towr/src/utils/save_data.cpp:54-119), i.e. SplineHolder's
  * NodeSpline::GetPoint (towr/src/variables/spline.cc:80-93, towr/include/towr/variables/spline_holder.h:48-84) and

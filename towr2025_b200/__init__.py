@@ -96,7 +96,7 @@ towr_b200_batch_destroy towr_b200_batch_size towr_b200_batch_set_problem towr_b2
 towr_b200_batch_eval towr_b200_batch_eval_device towr_b200_batch_status towr_b200_batch_launch_count
 towr_b200_batch_stream towr_b200_trajectory_width towr_b200_trajectory_samples towr_b200_batch_sample_trajectory
 towr_b200_batch_sample_trajectory_device towr_b200_trajectory_write_csv towr_b200_batch_eval_cost
-towr_b200_batch_eval_cost_device""".split()
+towr_b200_batch_eval_cost_device towr_b200_eval_cost_static""".split()
 
 
 def lib():
@@ -140,6 +140,7 @@ def lib():
     L.towr_b200_batch_status.argtypes = [vp, C.c_int, ip]
     L.towr_b200_batch_eval_cost.argtypes = [vp, C.c_int, C.c_int, dp, dp, dp]
     L.towr_b200_batch_eval_cost_device.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp]
+    L.towr_b200_eval_cost_static.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp]
     L.towr_b200_trajectory_width.argtypes = [vp]
     L.towr_b200_trajectory_samples.argtypes = [vp, C.c_double]
     L.towr_b200_batch_sample_trajectory.argtypes = [vp, C.c_int, C.c_double, dp, dp]
@@ -253,6 +254,11 @@ class Structure:
         lo, up = np.empty(self.n_rows), np.empty(self.n_rows)
         _check(self._L.towr_b200_problem_con_bounds(self._h, C.byref(spec), _dp(lo), _dp(up)))
         return lo, up
+
+    def eval_cost_static(self, n, what, d_x, d_f, d_grad, device=0, stream=None):
+        """Allocation-free eval_f / eval_grad_f on device pointers (towr_b200_eval_cost_static); asynchronous on `stream`."""
+        _check(self._L.towr_b200_eval_cost_static(self._h, device, n, what, C.c_void_p(d_x), C.c_void_p(d_f or 0),
+                                                   C.c_void_p(d_grad or 0), C.c_void_p(stream or 0)))
 
     @property
     def bytes_per_eval(self):

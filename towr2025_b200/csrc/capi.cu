@@ -541,6 +541,23 @@ int towr_b200_batch_eval_cost(towr_b200_batch* b, int n, int what, const double*
   });
 }
 
+// Allocation-free variant (no counterpart in the reference; see include/towr_b200.h): no batch, no cudaMalloc / cudaFree.
+int towr_b200_eval_cost_static(const towr_b200_structure* st, int device, int n, int what, const double* d_x, double* d_f,
+                               double* d_grad, void* stream) {
+  return Guard([&] {
+    if (!st || n < 0) throw std::runtime_error("bad argument to eval_cost_static");
+    if (what < 1 || what > 3) throw std::runtime_error("what must be 1 (f), 2 (gradient) or 3 (both)");
+    if (!d_x || ((what & 1) && !d_f) || ((what & 2) && !d_grad)) throw std::runtime_error("null device buffer");
+    if (towr_b200_device_count() < 1) throw CudaError("no CUDA device visible: this backend has no CPU fallback");
+    tb::CostTables h;                                   // host tables only
+    tb::BuildCostTables(st->hp, st->spec, h);
+    const char* why = "";
+    const cudaError_t err = tb::LaunchCostStatic(h, device, what, d_x, d_f, d_grad, n, static_cast<cudaStream_t>(stream), &why);
+    if (err == cudaErrorInvalidValue && *why) throw std::runtime_error(std::string("eval_cost_static: ") + why);
+    if (err != cudaSuccess) throw CudaError(std::string("eval_cost_static") + (*why ? std::string(" (") + why + ")" : std::string()) + ": " + cudaGetErrorString(err));
+  });
+}
+
 // ---- trajectory sampling -------------------------------------------------------------------------------------------
 int towr_b200_trajectory_width(const towr_b200_structure* st) { return st ? tb::TrajectoryWidth(st->hp.n_ee) : -1; }
 

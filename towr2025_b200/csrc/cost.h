@@ -28,6 +28,10 @@ void BuildCostTables(const HostProgram& hp, const towr_b200_spec& s, CostTables&
 #ifdef __CUDACC__
 cudaError_t LaunchCost(const CostDevice& c, int what, const double* x, double* f, double* grad, int n_problems, int max_ctas,
                        cudaStream_t stream);
+// allocation-free variant: the tables go into a file-scope device array of cost_kernel.cu (no cudaMalloc / cudaFree);
+// *why names the limit or call that failed
+cudaError_t LaunchCostStatic(const CostTables& h, int device, int what, const double* x, double* f, double* grad,
+                             int n_problems, cudaStream_t stream, const char** why);
 #endif
 
 }  // namespace tb

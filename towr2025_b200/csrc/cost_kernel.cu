@@ -4,6 +4,8 @@
 // nodes is counted twice, as in the reference).  One CTA per problem; thread c owns column c of the dense gradient.
 #include <cuda_runtime.h>
 
+#include <mutex>
+
 #include "cost.h"
 
 namespace tb {
@@ -52,6 +54,64 @@ cudaError_t LaunchCost(const CostDevice& c, int what, const double* x, double* f
   const int grid = n_problems < max_ctas ? n_problems : max_ctas;
   CostKernel<<<grid, kCostThreads, 0, stream>>>(c, what, x, f, grad, n_problems);
   return cudaGetLastError();
+}
+
+// ---- allocation-free variant (towr_b200_eval_cost_static, include/towr_b200.h) --------------------------------------
+// The work tables of the cost kernel (column pointers and weights), which towr_b200_batch_eval_cost[_device] keeps in
+// cudaMalloc'ed memory, live here in a file-scope device array: every GPU that loads the library holds these
+// kCostStaticBytes until the process exits.  All calls share the array and each call rewrites the part it uses (nothing
+// in it has to start at zero), so calls that overlap on the GPU race.
+constexpr int kCostStaticMaxVars = TOWR_B200_STATIC_COST_MAX_VARS;
+constexpr int kCostStaticMaxWeights = TOWR_B200_STATIC_COST_MAX_WEIGHTS;
+constexpr size_t kCostStaticWeightsOff = ((sizeof(int) * (kCostStaticMaxVars + 1)) + 255) & ~static_cast<size_t>(255);
+constexpr size_t kCostStaticBytes = kCostStaticWeightsOff + sizeof(double) * kCostStaticMaxWeights;
+static __device__ __align__(256) unsigned char g_cost_static[kCostStaticBytes];
+
+constexpr int kMaxDevices = 64;
+static unsigned char* g_cost_static_addr[kMaxDevices];     // device address of g_cost_static per device, looked up once
+static int g_cost_static_sms[kMaxDevices];
+static std::mutex g_cost_static_mu;
+
+cudaError_t LaunchCostStatic(const CostTables& h, int device, int what, const double* x, double* f, double* grad,
+                             int n_problems, cudaStream_t stream, const char** why) {
+  *why = "";
+  if (device < 0 || device >= kMaxDevices) { *why = "device index out of range"; return cudaErrorInvalidDevice; }
+  if (h.n_vars > kCostStaticMaxVars || static_cast<int>(h.weights.size()) > kCostStaticMaxWeights) {
+    *why = "the class exceeds TOWR_B200_STATIC_COST_MAX_VARS / _MAX_WEIGHTS";
+    return cudaErrorInvalidValue;
+  }
+  cudaError_t err = cudaSetDevice(device);
+  if (err != cudaSuccess) return err;
+  unsigned char* base = nullptr;
+  int sms = 0;
+  {
+    std::lock_guard<std::mutex> lock(g_cost_static_mu);
+    if (!g_cost_static_addr[device]) {
+      // in host code `g_cost_static` is only a stand-in for the symbol: the kernel needs the device address
+      void* p = nullptr;
+      err = cudaGetSymbolAddress(&p, g_cost_static);
+      if (err != cudaSuccess) { *why = "cudaGetSymbolAddress(g_cost_static)"; return err; }
+      err = cudaDeviceGetAttribute(&g_cost_static_sms[device], cudaDevAttrMultiProcessorCount, device);
+      if (err != cudaSuccess) return err;
+      g_cost_static_addr[device] = static_cast<unsigned char*>(p);
+    }
+    base = g_cost_static_addr[device];
+    sms = g_cost_static_sms[device];
+  }
+  if (n_problems <= 0) return cudaSuccess;
+  int* col_ptr = reinterpret_cast<int*>(base);
+  double* weights = reinterpret_cast<double*>(base + kCostStaticWeightsOff);
+  err = cudaMemcpyAsync(col_ptr, h.col_ptr.data(), sizeof(int) * h.col_ptr.size(), cudaMemcpyHostToDevice, stream);
+  if (err != cudaSuccess) return err;
+  if (!h.weights.empty()) {
+    err = cudaMemcpyAsync(weights, h.weights.data(), sizeof(double) * h.weights.size(), cudaMemcpyHostToDevice, stream);
+    if (err != cudaSuccess) return err;
+  }
+  CostDevice c;
+  c.n_vars = h.n_vars;
+  c.col_ptr = col_ptr;
+  c.weights = weights;
+  return LaunchCost(c, what, x, f, grad, n_problems, 16 * sms, stream);
 }
 
 }  // namespace tb
