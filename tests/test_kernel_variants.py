@@ -1,5 +1,5 @@
-"""The opt-in kernel variants (TOWR_B200_KERNEL = bulk | ws | wsbulk) compute the same products as the
-default lock-step kernel: values and g must be bit-identical on the same inputs, including a short last problem group."""
+"""The kernel variants (TOWR_B200_KERNEL = lockstep | ring | streams | streamsring) compute the same
+products as each other: values and g must be bit-identical on the same inputs, including a short last problem group."""
 import os
 
 import numpy as np
@@ -29,7 +29,7 @@ def _eval_with(T, kernel, st, s, x):
             os.environ["TOWR_B200_KERNEL"] = old
 
 
-@pytest.mark.parametrize("kernel", ["bulk", "ws", "wsbulk"])
+@pytest.mark.parametrize("kernel", ["ring", "streams", "streamsring"])
 @pytest.mark.parametrize("name", ["anymal_trot", "hyq_gallop_block", "monoped_hop"])
 def test_variant_matches_default_kernel(product, kernel, name):
     T = product
@@ -38,7 +38,7 @@ def test_variant_matches_default_kernel(product, kernel, name):
     st = T.Structure(s)
     n = 301                                   # odd: the last group holds one problem; > 2 x 148 so CTAs loop
     x = np.stack([perturbed(st.x0(s), 500 + i, 0.05) for i in range(n)])
-    g0, v0 = _eval_with(T, None, st, s, x)
+    g0, v0 = _eval_with(T, "lockstep", st, s, x)
     try:
         g1, v1 = _eval_with(T, kernel, st, s, x)
     except T.TowrB200Error as e:
@@ -49,12 +49,13 @@ def test_variant_matches_default_kernel(product, kernel, name):
     assert np.array_equal(v0, v1)
 
 
-def test_bulk_variant_with_optimised_durations(product):
+@pytest.mark.parametrize("kernel", ["ring", "streamsring"])
+def test_ring_variants_with_optimised_durations(product, kernel):
     T = product
     case = [c for c in CASES if c[0] == "biped_walk_durations"][0]
     s = mk(T, case)
     st = T.Structure(s)
     x = np.stack([perturbed(st.x0(s), 700 + i, 0.02) for i in range(9)])
-    g0, v0 = _eval_with(T, None, st, s, x)
-    g1, v1 = _eval_with(T, "bulk", st, s, x)
+    g0, v0 = _eval_with(T, "lockstep", st, s, x)
+    g1, v1 = _eval_with(T, kernel, st, s, x)
     assert np.array_equal(g0, g1) and np.array_equal(v0, v1)

@@ -32,22 +32,10 @@ def main():
     for it in range(3):
         b.eval_device(batch, T.EVAL_BOTH, dx.data_ptr(), dg.data_ptr(), dv.data_ptr())
         torch.cuda.synchronize()
-        reader = "towr_b200_debug_phase_clocks" + {"bulk": "_bulk", "ws": "_ws", "wsbulk": "_ws"}.get(os.environ.get("TOWR_B200_KERNEL", "lockstep"), "")
-        getattr(L, reader)(out, 64)
+        L.towr_b200_debug_phase_clocks(out, 64)
     v = list(out)
     tot = sum(v)
     print("raw:", v)
-    if os.environ.get("TOWR_B200_KERNEL", "") in ("ws", "wsbulk"):
-        pn = ["wait x", "stage C", "wait empty", "L0 items", "L0->L1 barrier", "L1 items", "hand-off + group end"]
-        pt = sum(v[:7]) or 1
-        print("producer thread 0: %d clocks" % pt)
-        for k, nm in enumerate(pn):
-            print("  %-22s %9d %5.1f%%" % (nm, v[k], 100.0 * v[k] / pt))
-        ct = sum(v[16:19]) or 1
-        print("consumer thread 0: %d clocks" % ct)
-        for k, nm in enumerate(["descriptor issue", "wait full", "stage B + G check"]):
-            print("  %-22s %9d %5.1f%%" % (nm, v[16 + k], 100.0 * v[16 + k] / ct))
-        return
     names = {0: "N work", 1: "N wait", 2: "C work", 3: "C wait"}
     print("total clocks of CTA 0 (thread 0 view): %d" % tot)
     for k in range(4):

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Small invocation of every kernel through the C ABI, meant to run under compute-sanitizer:
-    compute-sanitizer --tool memcheck python tools/sanitize_smoke.py [kernel]      (kernel: lockstep | bulk | ws | wsbulk)"""
+    compute-sanitizer --tool memcheck python tools/sanitize_smoke.py [kernel]      (kernel: lockstep | ring | streams | streamsring)"""
 import os
 import sys
 
@@ -13,7 +13,7 @@ import towr2025_b200 as T  # noqa: E402
 
 
 def main():
-    fixed_only = os.environ.get("TOWR_B200_KERNEL", "lockstep") in ("ws", "wsbulk")
+    fixed_only = os.environ.get("TOWR_B200_KERNEL", "lockstep") == "streams"
     for dur in ([False] if fixed_only else [False, True]):
         for robot, combo, Tt in ((T.Anymal, T.C1, 2.0), (T.Monoped, 0, 2.4)):
             s = T.make_spec(robot, combo, Tt, optimize_durations=dur)

@@ -89,10 +89,8 @@ struct towr_b200_batch {
   // staging for the host-buffer path
   double *x_dev = nullptr, *g_dev = nullptr, *v_dev = nullptr;
   tb::ProblemConst* pc_gather_dev = nullptr;
-  int max_ctas = 0, lanes = 0;
-  bool ws = false;         // warp-specialised kernel (kernels_ws.cu)
-  bool bulk = false;       // bulk-store kernel (kernels_tma.cu)
-  bool wsb = false;        // warp-specialised kernel with bulk-store consumers (kernels_ws.cu)
+  int max_ctas = 0;
+  tb::EvalVariant var{0, 1, false, 0};   // kernel variant (kernels.h); lanes = 0 until chosen
   std::unique_ptr<tb::HostProgram> hp_local;   // program rebuilt with a smaller G capacity (large class tables)
   long long launches = 0;
   // trajectory sampler tables per sampling period (trajectory.h)
@@ -212,119 +210,54 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     // The class tables, one problem's spline arrays and one G buffer must fit the SM's shared memory.  Classes with many
     // samples have large tables: rebuild the program with the G capacity that is left (more, smaller segments).
     const tb::HostProgram* hpp = &st->hp;
-    auto shared_need = [](const tb::HostProgram& h, int g_cap) {
+    const long long optin = static_cast<long long>(prop.sharedMemPerBlockOptin);
+    auto need = [](const tb::HostProgram& h, int g_cap, const tb::EvalVariant& v) {
       tb::DeviceProgram t{};
       t.blob = h.blob;
       t.g_capacity = g_cap;
-      return tb::EvalSharedBytes(t, 1) + 1024;
+      return static_cast<long long>(tb::EvalSharedBytes(t, v.lanes, v.streams, v.ring)) + 1024;   // + the kernel's static shared memory
     };
-    if (shared_need(*hpp, hpp->g_capacity) > prop.sharedMemPerBlockOptin) {
-      const long long left = static_cast<long long>(prop.sharedMemPerBlockOptin) - static_cast<long long>(shared_need(*hpp, 0)) - 2048;
-      if (left < 8 * 256) throw std::runtime_error("unsupported: the class tables alone exceed the SM's shared memory");
-      b->hp_local = std::make_unique<tb::HostProgram>();
-      tb::BuildProgram(st->spec, *b->hp_local, static_cast<int>(left / 8));
+    // rebuilds the program with at most `cap` G slots per segment (more, smaller segments); true when `v` then fits
+    auto rebuild = [&](long long cap, const tb::EvalVariant& v) {
+      if (cap < 256) return false;
+      auto h = std::make_unique<tb::HostProgram>();
+      tb::BuildProgram(st->spec, *h, static_cast<int>(cap));
+      if (need(*h, h->g_capacity, v) > optin) return false;
+      b->hp_local = std::move(h);
       hpp = b->hp_local.get();
-      if (shared_need(*hpp, hpp->g_capacity) > prop.sharedMemPerBlockOptin)
+      return true;
+    };
+    const tb::EvalVariant one_lane{1, 1, false, 0};
+    if (need(*hpp, hpp->g_capacity, one_lane) > optin) {
+      const long long left = optin - need(*hpp, 0, one_lane) - 2048;
+      if (left < 8 * 256) throw std::runtime_error("unsupported: the class tables alone exceed the SM's shared memory");
+      if (!rebuild(left / 8, one_lane))
         throw std::runtime_error("unsupported: structure class needs more shared memory per CTA than the device has");
     }
     int forced = 0;
     if (const char* env = std::getenv("TOWR_B200_LANES")) forced = std::atoi(env);
+    // kernel variant (eval_kernel.cuh).  TOWR_B200_KERNEL = lockstep | ring | streams | streamsring selects one for
+    // experiments; the default is chosen below.
+    const char* kenv = std::getenv("TOWR_B200_KERNEL");
+    tb::EvalVariant want{2, 1, false, 0};
+    bool forced_variant = false;
+    if (kenv && *kenv && std::strcmp(kenv, "lockstep") != 0) {
+      forced_variant = true;
+      if (std::strcmp(kenv, "ring") == 0) want = tb::EvalVariant{forced ? forced : 2, 1, true, 0};
+      else if (std::strcmp(kenv, "streams") == 0) want = tb::EvalVariant{1, 2, false, 0};
+      else if (std::strcmp(kenv, "streamsring") == 0) want = tb::EvalVariant{1, 2, true, 0};
+      else throw std::runtime_error(std::string("unknown TOWR_B200_KERNEL: ") + kenv);
+    }
+    if (const char* env = std::getenv("TOWR_B200_SKEW")) want.skew = std::atoi(env);
     // Two problems per CTA share the class tables and the descriptor stream.  Where the default program only fits one
     // lane (classes with optimised durations have large G footprints), a lower G capacity - more, smaller segments -
     // that lets two lanes fit is faster as long as it keeps about half of the default capacity (HyQ gallop with
     // optimised durations: 4.40 ms with 2 lanes / 17 segments against 6.69 ms with 1 lane / 14 segments).
-    if (!forced && !std::getenv("TOWR_B200_GCAP") && !b->hp_local) {
-      auto need2 = [](const tb::HostProgram& h, int g_cap) {
-        tb::DeviceProgram t{};
-        t.blob = h.blob;
-        t.g_capacity = g_cap;
-        return static_cast<long long>(tb::EvalSharedBytes(t, 2)) + 1024;
-      };
-      const long long optin = static_cast<long long>(prop.sharedMemPerBlockOptin);
-      if (need2(*hpp, hpp->g_capacity) > optin) {
-        long long cap = (optin - need2(*hpp, 0) - 6144) / 16;           // tables grow a little with the segment count
-        for (int attempt = 0; attempt < 4 && cap * 100 >= 45LL * hpp->g_capacity; ++attempt, cap = cap * 31 / 32) {
-          auto h = std::make_unique<tb::HostProgram>();
-          tb::BuildProgram(st->spec, *h, static_cast<int>(cap));
-          if (need2(*h, h->g_capacity) <= optin) {
-            b->hp_local = std::move(h);
-            hpp = b->hp_local.get();
-            break;
-          }
-        }
-      }
-    }
-    // kernel variant: TOWR_B200_KERNEL = bulk | lockstep | ws forces one.  The bulk-store kernel needs the G buffer and
-    // the staging buffer of the largest segment side by side: lower the G capacity until both fit.
-    const char* kenv = std::getenv("TOWR_B200_KERNEL");
-    const bool want_bulk = kenv && std::strcmp(kenv, "bulk") == 0;   // opt-in: measured slower than lock-step
-    if (want_bulk) {
-      auto fits = [&](const tb::HostProgram& h, int lanes) {
-        tb::DeviceProgram t{};
-        t.blob = h.blob;
-        t.g_capacity = h.g_capacity;
-        t.joint_capacity = tb::JointCapacity(h.segments.data(), static_cast<int>(h.segments.size()));
-        return tb::EvalFitsBulk(t, lanes, prop.sharedMemPerBlockOptin);
-      };
-      for (int lanes : {2, 1}) {
-        // one lane per CTA only on request: two lock-step lanes beat it
-        if (b->bulk || (forced ? lanes != forced : lanes != 2)) continue;
-        if (fits(*hpp, lanes)) { b->bulk = true; b->lanes = lanes; break; }
-        // elements per problem lane that the class tables and spline arrays leave for G + staging
-        tb::DeviceProgram t0{};
-        t0.blob = hpp->blob;
-        const long long fixed = static_cast<long long>(tb::EvalSharedBytesBulk(t0, lanes)) + 1024 + 6144;   // + table growth
-        long long joint = (static_cast<long long>(prop.sharedMemPerBlockOptin) - fixed) / (8 * lanes);
-        if (const char* env = std::getenv("TOWR_B200_JOINT")) joint = std::atoi(env);
-        for (int attempt = 0; attempt < 6 && joint > 1024; ++attempt, joint = joint * 15 / 16) {
-          auto h = std::make_unique<tb::HostProgram>();
-          tb::BuildProgram(st->spec, *h, 0, static_cast<int>(joint));
-          if (fits(*h, lanes)) {
-            b->hp_local = std::move(h);
-            hpp = b->hp_local.get();
-            b->bulk = true;
-            b->lanes = lanes;
-            break;
-          }
-        }
-      }
-      if (!b->bulk && kenv) throw std::runtime_error("unsupported: the bulk-store kernel does not fit this structure class");
-    }
-    // warp-specialised kernels (opt-in): a double-buffered G (and, with bulk-store consumers, their staging ring) must
-    // fit: lower the G capacity until it does
-    const bool want_wsb = kenv && std::strcmp(kenv, "wsbulk") == 0;
-    const bool want_ws_forced = kenv && std::strcmp(kenv, "ws") == 0;
-    if ((want_wsb || want_ws_forced) && !hpp->optimize_durations) {
-      auto bytes = [&](const tb::DeviceProgram& t) { return want_wsb ? tb::EvalSharedBytesWSBulk(t, 2) : tb::EvalSharedBytesWS(t, 2); };
-      auto fits = [&](const tb::HostProgram& h) {
-        tb::DeviceProgram t{};
-        t.blob = h.blob;
-        t.g_capacity = h.g_capacity;
-        return bytes(t) + 1024 <= static_cast<size_t>(prop.sharedMemPerBlockOptin);
-      };
-      if (!fits(*hpp)) {
-        tb::DeviceProgram t0{};
-        t0.blob = hpp->blob;
-        long long cap = (static_cast<long long>(prop.sharedMemPerBlockOptin) - static_cast<long long>(bytes(t0)) - 1024 - 6144) / 32;
-        if (const char* env = std::getenv("TOWR_B200_GCAP")) cap = std::atoi(env);
-        bool ok = false;
-        for (int attempt = 0; attempt < 6 && cap > 256 && !ok; ++attempt, cap = cap * 15 / 16) {
-          auto h = std::make_unique<tb::HostProgram>();
-          tb::BuildProgram(st->spec, *h, static_cast<int>(cap));
-          if (fits(*h)) {
-            b->hp_local = std::move(h);
-            hpp = b->hp_local.get();
-            ok = true;
-          }
-        }
-        if (!ok) throw std::runtime_error("unsupported: the warp-specialised kernel does not fit this structure class");
-      }
-      if (want_wsb) {
-        b->wsb = true;
-        b->lanes = 2;
-      }
-    } else if (want_wsb) {
-      throw std::runtime_error("unsupported: classes with optimised durations run on the lock-step kernel");
+    if (!std::getenv("TOWR_B200_GCAP") && !b->hp_local && (forced_variant || !forced) && need(*hpp, hpp->g_capacity, want) > optin) {
+      const int default_cap = hpp->g_capacity;
+      long long cap = (optin - need(*hpp, 0, want) - 6144) / (8LL * want.lanes * want.streams);   // tables grow a little with the segment count
+      for (int attempt = 0; attempt < 4 && (forced_variant || cap * 100 >= 45LL * default_cap); ++attempt, cap = cap * 31 / 32)
+        if (rebuild(cap, want)) break;
     }
     const tb::HostProgram& hp = *hpp;
     tb::DeviceProgram& dp = b->dp;
@@ -332,7 +265,6 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     dp.n_segments = static_cast<int>(hp.segments.size());
     dp.total_time = hp.total_time;
     dp.g_capacity = hp.g_capacity;
-    dp.joint_capacity = tb::JointCapacity(hp.segments.data(), dp.n_segments);
     dp.blob = hp.blob;
     auto keep = [&](auto* p) { b->owned.push_back(const_cast<void*>(static_cast<const void*>(p))); return p; };
     dp.blob_data = keep(Upload(hp.blob_data));
@@ -344,37 +276,30 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     Check(cudaMalloc(&b->status_dev, sizeof(int) * n_problems), "cudaMalloc(status)");
     keep(b->status_dev);
     Check(cudaMemset(b->status_dev, 0, sizeof(int) * n_problems), "cudaMemset(status)");
-    // lanes per CTA: as many problems side by side as shared memory allows (the class tables are held once per CTA)
-    if (b->bulk || b->wsb) b->max_ctas = prop.multiProcessorCount;
-    // the warp-specialised kernel when its double-buffered G fits
-    const bool want_ws = !b->bulk && !b->wsb && (!kenv || std::strcmp(kenv, "ws") == 0);
-    if (want_ws && (!forced || forced == 2) && tb::EvalFitsWS(dp, 2, prop.sharedMemPerBlockOptin)) {
-      b->ws = true;
-      b->lanes = 2;
-      b->max_ctas = prop.multiProcessorCount;
-    } else if (kenv && std::strcmp(kenv, "ws") == 0) {
-      throw std::runtime_error("unsupported: the warp-specialised kernel does not fit this structure class");
-    }
-    for (int lanes : {4, 2, 1}) {
-      if (b->ws || b->bulk || b->wsb) break;
-      if (forced && lanes != forced) continue;
-      if (tb::EvalSharedBytes(dp, lanes) > static_cast<size_t>(prop.sharedMemPerBlockOptin)) continue;
-      int occ = tb::EvalOccupancy(dp, lanes);
-      if (occ < 1) continue;
-      b->lanes = lanes;
+    auto try_variant = [&](const tb::EvalVariant& v) {
+      if (b->var.lanes || !tb::EvalVariantBuilt(dp, v)) return;
+      if (need(hp, hp.g_capacity, v) > optin) return;
+      const int occ = tb::EvalOccupancy(dp, v);
+      if (occ < 1) return;
+      b->var = v;
       b->max_ctas = prop.multiProcessorCount * occ;
-      break;
+    };
+    if (forced_variant) {
+      try_variant(want);
+      if (!b->var.lanes) throw std::runtime_error(std::string("unsupported: kernel variant ") + kenv + " does not fit this structure class");
     }
-    if (b->lanes == 0)
+    // lanes per CTA: as many problems side by side as shared memory allows (the class tables are held once per CTA)
+    for (int lanes : {4, 2, 1}) {
+      if (forced && lanes != forced) continue;
+      try_variant(tb::EvalVariant{lanes, 1, false, 0});
+    }
+    if (b->var.lanes == 0)
       throw std::runtime_error("unsupported: structure class needs more shared memory per CTA than the device has");
     if (std::getenv("TOWR_B200_DEBUG"))
-      std::fprintf(stderr, "batch: %s kernel, %d problems per CTA, %zu B shared (blob %d B, G capacity %d), %d CTAs\n",
-                   b->wsb ? "warp-specialised bulk" : b->bulk ? "bulk-store" : b->ws ? "warp-specialised" : "lock-step", b->lanes,
-                   b->wsb ? tb::EvalSharedBytesWSBulk(dp, b->lanes) : b->bulk ? tb::EvalSharedBytesBulk(dp, b->lanes)
-                           : b->ws ? tb::EvalSharedBytesWS(dp, b->lanes) : tb::EvalSharedBytes(dp, b->lanes),
-                   dp.blob.bytes, dp.g_capacity, b->max_ctas);
-    if (std::getenv("TOWR_B200_DEBUG"))
-      std::fprintf(stderr, "batch: %d segments, joint capacity %d\n", dp.n_segments, dp.joint_capacity);
+      std::fprintf(stderr, "batch: %d lane(s) x %d stream(s)%s, skew %d, %zu B shared (blob %d B, G capacity %d), %d CTAs, %d segments\n",
+                   b->var.lanes, b->var.streams, b->var.ring ? ", bulk-store ring" : "", b->var.skew,
+                   tb::EvalSharedBytes(dp, b->var.lanes, b->var.streams, b->var.ring), dp.blob.bytes, dp.g_capacity, b->max_ctas,
+                   dp.n_segments);
     *out = b.release();
   });
 }
@@ -413,8 +338,7 @@ int towr_b200_batch_eval_device(towr_b200_batch* b, int n, int what, const doubl
       b->SyncConsts();
       Check(cudaStreamSynchronize(b->stream), "sync consts");
     }
-    Check((b->wsb ? tb::LaunchEvalWSBulk : b->bulk ? tb::LaunchEvalBulk : b->ws ? tb::LaunchEvalWS : tb::LaunchEval)(b->dp, b->pc_dev, what, d_x, d_g, d_jac_values, b->status_dev, n,
-                                                       b->lanes, b->max_ctas, s), "launch");
+    Check(tb::LaunchEval(b->dp, b->pc_dev, what, d_x, d_g, d_jac_values, b->status_dev, n, b->var, b->max_ctas, s), "launch");
     b->launches += 1;
   });
 }
@@ -454,8 +378,7 @@ int towr_b200_batch_eval(towr_b200_batch* b, const int* ids, int n, int what, co
       b->SyncConsts();
     }
     Check(cudaMemcpyAsync(b->x_dev, x, sizeof(double) * dp.n_vars * n, cudaMemcpyHostToDevice, b->stream), "H2D x");
-    Check((b->wsb ? tb::LaunchEvalWSBulk : b->bulk ? tb::LaunchEvalBulk : b->ws ? tb::LaunchEvalWS : tb::LaunchEval)(dp, pcs, what, b->x_dev, b->g_dev, b->v_dev, b->status_dev, n, b->lanes,
-                                                       b->max_ctas, b->stream), "launch");
+    Check(tb::LaunchEval(dp, pcs, what, b->x_dev, b->g_dev, b->v_dev, b->status_dev, n, b->var, b->max_ctas, b->stream), "launch");
     b->launches += 1;
     if (what & TOWR_B200_EVAL_G)
       Check(cudaMemcpyAsync(g_out, b->g_dev, sizeof(double) * dp.n_rows * n, cudaMemcpyDeviceToHost, b->stream), "D2H g");

@@ -1,10 +1,21 @@
-// eval_kernel.cuh — the lock-step evaluation kernel (sm_100a).
+// eval_kernel.cuh — the evaluation kernel (sm_100a).
 //
-// One CTA evaluates P problems at a time (grid-stride over the batch).  Shared memory holds the class tables, the
-// problems' spline node values, the Hermite coefficients of every polynomial and the G buffer of the current segment;
-// x is read once (coalesced gather through node_src), g and the Jacobian values are written once, the
-// values with fully coalesced 8-byte stores in storage order.  HBM traffic per eval = 8*(n_vars+n_rows+nnz)
-// bytes plus L2-resident class tables (entries, B, items), which are shared by all problems of the batch.
+// One CTA runs S independent *streams* of NT = 256 * P threads; a stream evaluates P problems at a time in lock step
+// (grid-stride over the batch).  Shared memory holds the class tables once per CTA and, per stream, the problems'
+// spline node values, the Hermite coefficients of every polynomial and the G buffer of the current segment; x is
+// read once (coalesced gather through node_src), g and the Jacobian values are written once, in storage order.
+// HBM traffic per eval = 8*(n_vars+n_rows+nnz) bytes plus L2-resident class tables (entries, B, items), which are
+// shared by all problems of the batch.
+//
+//   S = 1            the lock-step kernel of round 1: all threads run stage A, then all run stage B
+//   S = 2, P = 1     two streams in anti-phase (the second starts `skew` clocks late): one stream's stage A overlaps
+//                    the other's value stores; the streams only share the class tables and synchronise on named
+//                    barriers of their own
+//   RING             stage B writes its products into a small shared-memory ring in storage order and one thread per
+//                    stream hands each chunk to the TMA engine (cp.async.bulk shared -> global).  The value stores then
+//                    never enter the SM's LSU pipe, which serialises global stores with the shared-memory traffic of
+//                    stage A (profiles/r01_ncu_summary.md: mio_throttle / lg_throttle), and drain while the next
+//                    chunk - or the next segment's stage A - runs.
 #pragma once
 #include "kernel_common.cuh"
 
@@ -15,6 +26,36 @@ namespace tb {
 // durations, whose descriptor stream is as long as the output; neutral on ANYmal trot)
 #define TB_STORE_VALUE(ptr, v) __stcs((ptr), (v))
 
+// one product: descriptor w = G byte offset (low 16) | B byte offset (high 16; bit 16 set: second factor is a G slot)
+template <int P, bool GG>
+__device__ __forceinline__ void Products(uint32_t w, const char* Gb, const char* Bb, double (&v)[P]) {
+  double bv = 0.0;
+  double bw[P];                                         // GG entries: the second factor is a per-problem G slot
+  bool gg = false;
+  if constexpr (GG) gg = (w & 0x10000u) != 0;
+  if (!gg) {
+    bv = *reinterpret_cast<const double*>(Bb + (w >> 16));
+  } else {
+    const double* wa = reinterpret_cast<const double*>(Gb + ((w >> 16) & 0xFFF8u) * P);
+#pragma unroll
+    for (int p = 0; p < P; ++p) bw[p] = wa[p];
+  }
+  const char* ga = Gb + (w & 0xFFFFu) * P;
+  double gv[P];
+  if constexpr (P == 1) {
+    gv[0] = *reinterpret_cast<const double*>(ga);
+  } else {
+#pragma unroll
+    for (int p = 0; p < P; p += 2) {
+      const double2 t = *reinterpret_cast<const double2*>(ga + 8 * p);
+      gv[p] = t.x;
+      gv[p + 1] = t.y;
+    }
+  }
+#pragma unroll
+  for (int p = 0; p < P; ++p) v[p] = gv[p] * ((GG && gg) ? bw[p] : bv);
+}
+
 // FULL: all P problem lanes of the group exist (no per-store predicate).
 // nf[p] accumulates value * 0 per problem lane: NaN exactly when a stored value is not finite (status bit 2).
 template <int P, bool FULL, int NT, bool GG = false>
@@ -24,35 +65,13 @@ __device__ __forceinline__ void StageB(const uint32_t* __restrict__ ent, int lef
   constexpr int U = kDescBatch;
   const char* Gb = reinterpret_cast<const char*>(G);
   const char* Bb = reinterpret_cast<const char*>(Bs);
-  auto emit = [&](uint32_t w, double* op) {              // descriptor: G byte offset (low 16), B byte offset (high 16)
-    double bv = 0.0;
-    double bw[P];                                         // GG entries: the second factor is a per-problem G slot
-    bool gg = false;
-    if constexpr (GG) gg = (w & 0x10000u) != 0;
-    if (!gg) {
-      bv = *reinterpret_cast<const double*>(Bb + (w >> 16));
-    } else {
-      const double* wa = reinterpret_cast<const double*>(Gb + ((w >> 16) & 0xFFF8u) * P);
-#pragma unroll
-      for (int p = 0; p < P; ++p) bw[p] = wa[p];
-    }
-    const char* ga = Gb + (w & 0xFFFFu) * P;
-    double gv[P];
-    if constexpr (P == 1) {
-      gv[0] = *reinterpret_cast<const double*>(ga);
-    } else {
-#pragma unroll
-      for (int p = 0; p < P; p += 2) {
-        const double2 t = *reinterpret_cast<const double2*>(ga + 8 * p);
-        gv[p] = t.x;
-        gv[p + 1] = t.y;
-      }
-    }
+  auto emit = [&](uint32_t w, double* op) {
+    double v[P];
+    Products<P, GG>(w, Gb, Bb, v);
 #pragma unroll
     for (int p = 0; p < P; ++p) {
-      const double v = gv[p] * ((GG && gg) ? bw[p] : bv);
-      nf[p] = fma(v, 0.0, nf[p]);
-      if (FULL || p < np) TB_STORE_VALUE(op + static_cast<size_t>(p) * nnz, v);
+      nf[p] = fma(v[p], 0.0, nf[p]);
+      if (FULL || p < np) TB_STORE_VALUE(op + static_cast<size_t>(p) * nnz, v[p]);
     }
   };
   constexpr int A = DescAhead<GG>::value;
@@ -69,7 +88,7 @@ __device__ __forceinline__ void StageB(const uint32_t* __restrict__ ent, int lef
           if (left > u * NT) emit(d[a][u], o + u * NT);
       }
       const int left_a = left - A * U * NT;
-      if (left_a > 0) LoadDescriptors<NT>(ent + A * U * NT, left_a, d[a]);
+      if (left_a > 0) LoadDescriptors<NT, U>(ent + A * U * NT, left_a, d[a]);
       left -= U * NT;
       ent += U * NT;
       o += U * NT;
@@ -77,10 +96,7 @@ __device__ __forceinline__ void StageB(const uint32_t* __restrict__ ent, int lef
   }
 }
 
-// ---- bulk-store variant (BULK): stage B writes the products into a shared-memory staging buffer in storage order and
-// one thread per problem lane hands the whole segment to the TMA engine (cp.async.bulk shared -> global).  The stores
-// then drain asynchronously while the CTA runs stage A of the next segment: they no longer occupy the LSU pipe that
-// stage A needs for its shared-memory traffic.
+// ---- RING: cp.async.bulk (TMA engine) stores from a shared-memory ring
 __device__ __forceinline__ void FenceProxyAsync() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void BulkStore(void* gdst, const void* ssrc, unsigned bytes) {
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),
@@ -88,97 +104,113 @@ __device__ __forceinline__ void BulkStore(void* gdst, const void* ssrc, unsigned
                : "memory");
 }
 __device__ __forceinline__ void BulkCommit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void BulkWaitRead() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void BulkWaitRead() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ void BulkWaitAll() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
-// Stage B into the staging buffer: so[p] = lane p's staging element of entry tid (conflict-free 8-byte stores).
-template <int P, int NT, bool GG>
-__device__ __forceinline__ void StageBShared(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[DescAhead<GG>::value][kDescBatch],
-                                             const double* G, const double* Bs, double* const (&so)[P], double (&nf)[P]) {
-  constexpr int U = kDescBatch;
+// all NT threads of stream `sidx`
+template <int S, int NT>
+__device__ __forceinline__ void StreamSync(int sidx) {
+  if constexpr (S == 1) __syncthreads();
+  else asm volatile("bar.sync %0, %1;" ::"r"(sidx + 1), "n"(NT) : "memory");
+}
+
+// Ring geometry (program.h): a chunk holds UB = RingBatchFor(P) entries per thread (UB * NT consecutive entries of the
+// segment) for each of the P lanes; kRingDepth chunks per stream.  A lane's row has two spare elements: the row is
+// shifted by the 8-byte parity of its destination so that the body of every copy is 16-byte aligned on both sides.
+//
+// Stage B of one segment into the ring.  ctr: chunks this stream has staged so far (selects the ring slot).
+// dst[p]: global address of the segment's first entry of lane p; np lanes exist.
+// Protocol per chunk: all threads write their products into the slot and fence them for the async proxy; thread 0 (which
+// owns the stream's bulk groups) waits until the engine has READ the previous chunk - whose slot the next chunk reuses -
+// then the stream's barrier, then thread 0 issues this chunk's copies while the others start on the next chunk.
+template <int P, int NT, int S, int UB, int A, bool GG>
+__device__ __forceinline__ void StageBRing(const uint32_t* __restrict__ ent, int n_entries, int tid, int sidx,
+                                           uint32_t (&d)[A][UB], const double* G, const double* Bs, double* ring, unsigned& ctr,
+                                           double* const (&dst)[P], int np, double (&nf)[P]) {
+  constexpr int CE = UB * NT, ROW = UB * NT + 2;
   const char* Gb = reinterpret_cast<const char*>(G);
   const char* Bb = reinterpret_cast<const char*>(Bs);
-  auto emit = [&](uint32_t w, int off) {
-    double bv = 0.0;
-    double bw[P];
-    bool gg = false;
-    if constexpr (GG) gg = (w & 0x10000u) != 0;
-    if (!gg) {
-      bv = *reinterpret_cast<const double*>(Bb + (w >> 16));
-    } else {
-      const double* wa = reinterpret_cast<const double*>(Gb + ((w >> 16) & 0xFFF8u) * P);
+  int q[P];
 #pragma unroll
-      for (int p = 0; p < P; ++p) bw[p] = wa[p];
-    }
-    const char* ga = Gb + (w & 0xFFFFu) * P;
-    double gv[P];
-    if constexpr (P == 1) {
-      gv[0] = *reinterpret_cast<const double*>(ga);
-    } else {
-#pragma unroll
-      for (int p = 0; p < P; p += 2) {
-        const double2 t = *reinterpret_cast<const double2*>(ga + 8 * p);
-        gv[p] = t.x;
-        gv[p + 1] = t.y;
-      }
-    }
-#pragma unroll
-    for (int p = 0; p < P; ++p) {
-      const double v = gv[p] * ((GG && gg) ? bw[p] : bv);
-      nf[p] = fma(v, 0.0, nf[p]);
-      so[p][off] = v;
-    }
-  };
-  constexpr int A = DescAhead<GG>::value;
-  int off = 0;
-  while (true) {
+  for (int p = 0; p < P; ++p) q[p] = static_cast<int>((reinterpret_cast<uintptr_t>(dst[p]) >> 3) & 1);
+  int left = n_entries - tid;
+  const int n_chunks = (n_entries + CE - 1) / CE;
+  for (int c0 = 0; c0 < n_chunks; c0 += A) {
 #pragma unroll
     for (int a = 0; a < A; ++a) {
-      if (left <= 0) return;
-      if (left > (U - 1) * NT) {
+      const int c = c0 + a;
+      if (c >= n_chunks) break;
+      double* sb = ring + (ctr % kRingDepth) * (P * ROW);
 #pragma unroll
-        for (int u = 0; u < U; ++u) emit(d[a][u], off + u * NT);
-      } else {
+      for (int u = 0; u < UB; ++u) {
+        if (left > u * NT) {
+          double v[P];
+          Products<P, GG>(d[a][u], Gb, Bb, v);
 #pragma unroll
-        for (int u = 0; u < U - 1; ++u)
-          if (left > u * NT) emit(d[a][u], off + u * NT);
+          for (int p = 0; p < P; ++p) {
+            nf[p] = fma(v[p], 0.0, nf[p]);
+            sb[p * ROW + q[p] + u * NT + tid] = v[p];
+          }
+        }
       }
-      const int left_a = left - A * U * NT;
-      if (left_a > 0) LoadDescriptors<NT>(ent + A * U * NT, left_a, d[a]);
-      left -= U * NT;
-      ent += U * NT;
-      off += U * NT;
+      const int left_a = left - A * CE;
+      if (left_a > 0) LoadDescriptors<NT, UB>(ent + A * CE, left_a, d[a]);
+      left -= CE;
+      ent += CE;
+      FenceProxyAsync();
+      if (tid == 0) BulkWaitRead<kRingDepth - 2>();
+      StreamSync<S, NT>(sidx);
+      if (tid == 0) {
+        const int e0 = c * CE;
+        const int nc = min(CE, n_entries - e0);
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+          if (p < np) {
+            double* D0 = dst[p] + e0;
+            const double* src = sb + p * ROW + q[p];          // entry i of the chunk at src[i]
+            if (q[p]) D0[0] = src[0];                         // odd first element: plain store
+            const int body = (nc - q[p]) & ~1;
+            if (body > 0) BulkStore(D0 + q[p], src + q[p], static_cast<unsigned>(body) * 8u);
+            if ((nc - q[p]) & 1) D0[nc - 1] = src[nc - 1];    // odd last element
+          }
+        }
+        BulkCommit();
+      }
+      ++ctr;
     }
   }
 }
 
-// P problems are evaluated in lock step by one CTA of 256*P threads: the class tables are held once per SM, every
-// stage spreads (item, problem) pairs over all threads, and in stage B one descriptor load and one B load feed the
-// P problems.  All per-problem shared arrays are interleaved (element i of problem p at [i*P + p]).
 // RT: structure classes with optimised phase durations (stage D below; items.cuh Lockstep<P, true>).
-template <int WHAT, int P, bool RT, bool BULK = false>
-__global__ void __launch_bounds__(kThreads * P, (P == 1 && !BULK && !RT) ? 2 : 1)   // one lane: two CTAs per SM (128 registers each)
+template <int WHAT, int P, bool RT, int S = 1, bool RING = false>
+__global__ void __launch_bounds__(kThreads * P * S, (P == 1 && S == 1 && !RT) ? 2 : 1)   // one lane, one stream: two CTAs per SM (128 registers each)
 EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restrict__ pcs, const double* __restrict__ x,
-           double* __restrict__ g_out, double* __restrict__ vals_out, int* __restrict__ status, int n_problems) {
+           double* __restrict__ g_out, double* __restrict__ vals_out, int* __restrict__ status, int n_problems, int skew) {
   constexpr int NT = kThreads * P;
+  constexpr int UB = RING ? RingBatchFor(P) : kDescBatch;           // descriptors per batch
+  constexpr int AH = RING ? (16 / UB) * (RT ? 2 : 1) : DescAhead<RT>::value;   // batches fetched ahead
   extern __shared__ uint4 sm4[];
   unsigned char* blob = reinterpret_cast<unsigned char*>(sm4);
   const int nnv = Pg.blob.n_node_values, npoly = Pg.blob.n_polys;
-  double* nodes = reinterpret_cast<double*>(blob + Pg.blob.bytes);
+  const int sidx = S == 1 ? 0 : static_cast<int>(threadIdx.x) / NT;
+  const int tid = S == 1 ? static_cast<int>(threadIdx.x) : static_cast<int>(threadIdx.x) % NT;
+  // per-stream arrays (StreamDoubles, program.h)
+  double* nodes = reinterpret_cast<double*>(blob + Pg.blob.bytes) + static_cast<size_t>(sidx) * StreamDoubles(Pg, P, RING);
   double* coef = nodes + nnv * P;
   double* rtd = coef + 6 * npoly * P;                   // RT: kRtd per polynomial, then the phase durations
   double* pdur = rtd + (RT ? kRtd * npoly * P : 0);
   double* G = pdur + (RT ? Pg.blob.n_pdur * P : 0);
-  // BULK: G shares a joint region with the staging buffer, which is aligned to the region's (16-byte aligned) end
-  double* const joint_end = reinterpret_cast<double*>(reinterpret_cast<uintptr_t>(G + Pg.joint_capacity * P) & ~static_cast<uintptr_t>(15));
-  __shared__ ProblemConst pc_all[P];
-  __shared__ int bad_all[P];
-  const int tid = threadIdx.x;
+  double* const ring = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(G + Pg.g_capacity * P) + 15) & ~static_cast<uintptr_t>(15));
+  __shared__ ProblemConst pc_all[P * S];
+  __shared__ int bad_all[P * S];
+  ProblemConst* const pc_s = pc_all + sidx * P;
+  int* const bad_s = bad_all + sidx * P;
 
   // class tables: one 16-byte-vector copy per CTA, reused for every problem group this CTA evaluates
   {
     const uint4* src = reinterpret_cast<const uint4*>(Pg.blob_data);
-    for (int i = tid; i < Pg.blob.bytes / 16; i += NT) sm4[i] = __ldg(src + i);
+    for (int i = threadIdx.x; i < Pg.blob.bytes / 16; i += NT * S) sm4[i] = __ldg(src + i);
   }
   __syncthreads();
   TB_MARK_INIT
@@ -187,6 +219,8 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
   cx.T = MakeTables(blob, Pg.blob);
   const double* Bs = cx.T.B;
   const int pl = tid % P;                               // problem lane of this thread in stages N, C, A
+  const int first = (static_cast<int>(blockIdx.x) * S + sidx) * P, stride = static_cast<int>(gridDim.x) * S * P;
+  unsigned ring_ctr = 0;
 
   // stage N: node values from x (values that are not optimised are pinned to 0), fetched asynchronously: for the first
   // group here, for every later group while the previous group's last stage B runs (nodes[] is free by then)
@@ -197,11 +231,15 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
       CpAsync8(nodes + i, xn + (src != 0xFFFFu ? src : 0u), src != 0xFFFFu ? 8 : 0);
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
-    if (tid < P) pc_all[tid] = pcs[min(base_n + tid, n_problems - 1)];
+    if (tid < P) pc_s[tid] = pcs[min(base_n + tid, n_problems - 1)];
   };
-  if (blockIdx.x * P < n_problems) fetch_group(blockIdx.x * P);
+  if (first < n_problems) fetch_group(first);
+  if (S > 1 && sidx > 0 && skew > 0) {                    // anti-phase start of the later streams
+    const long long t0 = clock64();
+    while (clock64() - t0 < static_cast<long long>(skew) * sidx) __nanosleep(200);
+  }
 
-  for (int base = blockIdx.x * P; base < n_problems; base += gridDim.x * P) {
+  for (int base = first; base < n_problems; base += stride) {
     // the last group may hold fewer than P problems: the spare lanes recompute the last problem (same values to
     // the same addresses) so that no stage needs a bounds test
     const int prob = min(base + pl, n_problems - 1);
@@ -210,16 +248,16 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
     cx.G = G + pl;
     cx.rtd = rtd + pl;
     cx.pdur = pdur + pl;
-    cx.pc = &pc_all[pl];
+    cx.pc = &pc_s[pl];
     cx.g = (WHAT & TOWR_B200_EVAL_G) ? g_out + static_cast<size_t>(prob) * Pg.n_rows : nullptr;
     double nf[P];
 #pragma unroll
     for (int p = 0; p < P; ++p) nf[p] = 0.0;
     double nfx = 0.0;                                     // non-finite x of problem lane pl
-    if (tid < P) bad_all[tid] = 0;
+    if (tid < P) bad_s[tid] = 0;
     asm volatile("cp.async.wait_all;" ::: "memory");
     TB_MARK(0)
-    __syncthreads();
+    StreamSync<S, NT>(sidx);
     TB_MARK(1)
 
     // ---- stage D (optimised durations): phase durations from x (phase_durations.cc:78-100: the last one is
@@ -238,7 +276,7 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
         }
         pdur[(ft.phase0 + ft.n_phases - 1) * P + pl] = Pg.total_time - sum;
       }
-      __syncthreads();
+      StreamSync<S, NT>(sidx);
       for (int i = tid; i < npoly * P; i += NT) {
         const int poly = i / P;
         const uint32_t pm = cx.T.poly_meta[poly];
@@ -256,7 +294,7 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
           o[kRtR1 * P] = 1.0 / Td; o[kRtR4 * P] = 1.0 / Pow4(Td);
         }
       }
-      __syncthreads();
+      StreamSync<S, NT>(sidx);
       // end time of every polynomial within its PhaseSpline: t += d from 0, as Spline::GetSegmentID (spline.cc:48-66)
       for (int i = tid; i < Pg.blob.n_rt_splines * P; i += NT) {
         const RtSpline sp = cx.T.rt_splines[i / P];
@@ -267,7 +305,7 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
           o[kRtEnd * P] = acc;
         }
       }
-      __syncthreads();
+      StreamSync<S, NT>(sidx);
     }
 
     // ---- stage C: c = -(3(p0-p1) + T(2 v0 + v1))/T^2, d = (2(p0-p1) + T(v0+v1))/T^3   (polynomial.cc:97-104)
@@ -293,96 +331,70 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
       coef[(poly * 6 + 3 + d) * P + pl] = ExactDiv(2.0 * (p0 - p1) + T * (v0 + v1), T3, r3);
     }
     TB_MARK(2)
-    __syncthreads();
+    StreamSync<S, NT>(sidx);
     TB_MARK(3)
+
 
     for (int s = 0; s < Pg.n_segments; ++s) {
       const SegmentRec sg = cx.T.segments[s];
       // ---- stage A, level 0 then level 1: thread -> (item, problem lane)
-      if (tid < P) { G[kGOne * P + tid] = 1.0; G[kGMass * P + tid] = pc_all[tid].mass; G[kGMinusOne * P + tid] = -1.0; }
+      if (tid < P) { G[kGOne * P + tid] = 1.0; G[kGMass * P + tid] = pc_s[tid].mass; G[kGMinusOne * P + tid] = -1.0; }
       // a level with more (item, lane) pairs than threads runs in rounds of NT / P items.  The kinds are ordered longest
       // first (pack.cc) and odd rounds map the items to the threads in reverse, so the short items of a second round go to
       // the threads whose first item was short
-      auto run_level = [&](int first, int count) {
+      auto run_level = [&](int first_item, int count) {
         constexpr int kPerRound = NT / P;
         int r = 0;
         for (int base_i = 0; base_i < count; base_i += kPerRound, ++r) {
           const int idx = base_i + ((r & 1) ? kPerRound - 1 - tid / P : tid / P);
-          if (idx < count) RunItem<Lockstep<P, RT>>(cx, cx.T.items[first + idx]);
+          if (idx < count) RunItem<Lockstep<P, RT>>(cx, cx.T.items[first_item + idx]);
         }
       };
       run_level(sg.item0, sg.n_items0);
       TB_MARK(8 + 6 * s)
       if (sg.n_items > sg.n_items0) {
-        __syncthreads();
+        StreamSync<S, NT>(sidx);
         TB_MARK(9 + 6 * s)
         run_level(sg.item0 + sg.n_items0, sg.n_items - sg.n_items0);
         TB_MARK(10 + 6 * s)
       }
-      // first descriptor batch of stage B: issued before the barrier, consumed after it
+      // first descriptor batches of stage B: issued before the barrier, consumed after it
       const uint32_t* ent = Pg.entries + sg.entry0 + tid;
-      uint32_t d0[DescAhead<RT>::value][kDescBatch];
-      if (WHAT & TOWR_B200_EVAL_JAC) LoadDescriptorRing<NT>(ent, sg.n_entries - tid, d0);
-      // BULK: the TMA engine must have read the previous segment's values out of the staging buffer
-      if (BULK && (WHAT & TOWR_B200_EVAL_JAC) && tid < P) BulkWaitRead();
-      __syncthreads();
+      uint32_t d0[AH][UB];
+      if (WHAT & TOWR_B200_EVAL_JAC) LoadDescriptorRing<NT, AH, UB>(ent, sg.n_entries - tid, d0);
+      StreamSync<S, NT>(sidx);
       TB_MARK(11 + 6 * s)
-      // all items of this group are done with nodes[] / pc_all after the last segment's stage A: fetch the next group
-      if (s == Pg.n_segments - 1 && base + gridDim.x * P < n_problems) fetch_group(base + gridDim.x * P);
-      // ---- stage B: value_p = G_p[g] * B[b] for the P problems: one descriptor and one B load feed P coalesced stores
-      if constexpr (BULK) {
-        if (WHAT & TOWR_B200_EVAL_JAC) {
-          // first destination element of each lane and its 8-byte parity (spare lanes of a short group repeat the last problem)
-          const int sst = StagingStride(sg.n_entries);
-          double* const stg = joint_end - P * sst;
-          double* so[P];
+      // all items of this group are done with nodes[] / pc_s after the last segment's stage A: fetch the next group
+      if (s == Pg.n_segments - 1 && base + stride < n_problems) fetch_group(base + stride);
+      // ---- stage B: value_p = G_p[g] * B[b] for the P problems: one descriptor and one B load feed P products
+      if (WHAT & TOWR_B200_EVAL_JAC) {
+        if constexpr (RING) {
+          double* dst[P];
 #pragma unroll
-          for (int p = 0; p < P; ++p) {
-            const size_t e0 = static_cast<size_t>(min(base + p, n_problems - 1)) * Pg.nnz + sg.entry0;
-            const int q = static_cast<int>(((reinterpret_cast<uintptr_t>(vals_out) >> 3) + e0) & 1);
-            so[p] = stg + p * sst + q + tid;
-          }
-          StageBShared<P, NT, RT>(ent, sg.n_entries - tid, d0, G, Bs, so, nf);
-          FenceProxyAsync();
-        }
-        TB_MARK(12 + 6 * s)
-        __syncthreads();
-        TB_MARK(13 + 6 * s)
-        if ((WHAT & TOWR_B200_EVAL_JAC) && tid < P && base + tid < n_problems) {
-          const size_t e0 = static_cast<size_t>(base + tid) * Pg.nnz + sg.entry0;
-          double* dst = vals_out + e0;
-          const int q = static_cast<int>(((reinterpret_cast<uintptr_t>(vals_out) >> 3) + e0) & 1);
-          const int sst = StagingStride(sg.n_entries);
-          const double* src = joint_end - P * sst + tid * sst + q;   // entry i of the segment at src[i]
-          const int ne = sg.n_entries;
-          if (q) dst[0] = src[0];                             // odd first element: plain store
-          const int body = (ne - q) & ~1;
-          if (body > 0) BulkStore(dst + q, src + q, static_cast<unsigned>(body) * 8u);
-          if ((ne - q) & 1) dst[ne - 1] = src[ne - 1];        // odd last element
-          BulkCommit();
-        }
-      } else {
-        if (WHAT & TOWR_B200_EVAL_JAC) {
+          for (int p = 0; p < P; ++p) dst[p] = vals_out + static_cast<size_t>(min(base + p, n_problems - 1)) * Pg.nnz + sg.entry0;
+          StageBRing<P, NT, S, UB, AH, RT>(ent, sg.n_entries, tid, sidx, d0, G, Bs, ring, ring_ctr, dst, min(P, n_problems - base), nf);
+        } else {
           double* o0 = vals_out + static_cast<size_t>(base) * Pg.nnz + sg.entry0 + tid;
           if (n_problems - base >= P)
             StageB<P, true, NT, RT>(ent, sg.n_entries - tid, d0, G, Bs, o0, Pg.nnz, P, nf);
           else
             StageB<P, false, NT, RT>(ent, sg.n_entries - tid, d0, G, Bs, o0, Pg.nnz, n_problems - base, nf);
         }
-        TB_MARK(12 + 6 * s)
-        __syncthreads();
-        TB_MARK(13 + 6 * s)
       }
+      TB_MARK(12 + 6 * s)
+      // RING: the last chunk's barrier already ordered every G read before the next stage A
+      if (!RING || !(WHAT & TOWR_B200_EVAL_JAC) || sg.n_entries == 0) StreamSync<S, NT>(sidx);
+      TB_MARK(13 + 6 * s)
     }
-    if (nfx != nfx) atomicOr(&bad_all[pl], 1);
+    if (nfx != nfx) atomicOr(&bad_s[pl], 1);
 #pragma unroll
     for (int p = 0; p < P; ++p)
-      if (nf[p] != nf[p]) atomicOr(&bad_all[p], 1);
-    __syncthreads();
-    if (tid < P && bad_all[tid] && base + tid < n_problems) atomicOr(status + base + tid, 2);
+      if (nf[p] != nf[p]) atomicOr(&bad_s[p], 1);
+    StreamSync<S, NT>(sidx);
+    if (tid < P && bad_s[tid] && base + tid < n_problems) atomicOr(status + base + tid, 2);
   }
-  // the staging buffer must outlive the bulk copies that read it
-  if (BULK && (WHAT & TOWR_B200_EVAL_JAC) && tid < P) BulkWaitAll();
+  // the ring must outlive the bulk copies that read it
+  if (RING && (WHAT & TOWR_B200_EVAL_JAC) && tid == 0) BulkWaitAll();
 }
 
 }  // namespace tb

@@ -1,4 +1,4 @@
-// kernel_common.cuh — helpers shared by the evaluation kernels (lock-step, warp-specialised, bulk-store).
+// kernel_common.cuh — helpers shared by the evaluation kernel variants.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -53,16 +53,16 @@ __device__ __forceinline__ bool NonFinite(double v) {
 template <bool RT> struct DescAhead { static constexpr int value = RT ? 8 : 4; };
 constexpr int kDescBatch = 4;
 
-template <int NT>
-__device__ __forceinline__ void LoadDescriptors(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[kDescBatch]) {
+template <int NT, int U>
+__device__ __forceinline__ void LoadDescriptors(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[U]) {
 #pragma unroll
-  for (int u = 0; u < kDescBatch; ++u) d[u] = left > u * NT ? __ldg(ent + u * NT) : kNoEntry;
+  for (int u = 0; u < U; ++u) d[u] = left > u * NT ? __ldg(ent + u * NT) : kNoEntry;
 }
 // the first A batches of a segment (thread's first entry at ent, `left` entries from there on)
-template <int NT, int A>
-__device__ __forceinline__ void LoadDescriptorRing(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[A][kDescBatch]) {
+template <int NT, int A, int U>
+__device__ __forceinline__ void LoadDescriptorRing(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[A][U]) {
 #pragma unroll
-  for (int a = 0; a < A; ++a) LoadDescriptors<NT>(ent + a * kDescBatch * NT, left - a * kDescBatch * NT, d[a]);
+  for (int a = 0; a < A; ++a) LoadDescriptors<NT, U>(ent + a * U * NT, left - a * U * NT, d[a]);
 }
 
 // 8-byte asynchronous global -> shared copy; src_bytes = 0 writes zeros (cp.async zero-fill)

@@ -1,0 +1,55 @@
+// kernels_variant.cu — explicit instantiations of the evaluation kernel for one variant.  Compiled once per variant with
+// -DTB_LANES=<1|2|4> -DTB_RT=<0|1> -DTB_STREAMS=<1|2> -DTB_RING=<0|1> (Makefile) so that the variants build in parallel.
+#if defined(TB_TIMING) && TB_LANES == 2 && TB_RT == 0 && TB_STREAMS == 1 && TB_RING == 0
+#define TB_TIMING_HERE
+#endif
+#include "eval_kernel.cuh"
+
+namespace tb {
+
+template <int WHAT>
+static cudaError_t LaunchT(const DeviceProgram& P, const ProblemConst* pcs, const double* x, double* g, double* vals,
+                           int* status, int n_problems, int max_ctas, int skew, cudaStream_t stream) {
+  constexpr int LANES = TB_LANES, STREAMS = TB_STREAMS;
+  const size_t smem = EvalSharedBytes(P, LANES, STREAMS, TB_RING != 0);
+  auto kern = EvalKernel<WHAT, LANES, TB_RT != 0, STREAMS, TB_RING != 0>;
+  cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+  if (err != cudaSuccess) return err;
+  int grid = (n_problems + LANES * STREAMS - 1) / (LANES * STREAMS);
+  if (grid > max_ctas) grid = max_ctas;
+  kern<<<grid, kThreads * LANES * STREAMS, smem, stream>>>(P, pcs, x, g, vals, status, n_problems, skew);
+  return cudaGetLastError();
+}
+
+#define TB_CAT5(a, b, c, d, e) a##b##_##c##_##d##_##e
+#define TB_NAME(a, b, c, d, e) TB_CAT5(a, b, c, d, e)
+
+cudaError_t TB_NAME(LaunchV, TB_LANES, TB_RT, TB_STREAMS, TB_RING)(const DeviceProgram& P, const ProblemConst* pcs, int what,
+                                                                   const double* x, double* g, double* vals, int* status,
+                                                                   int n_problems, int max_ctas, int skew, cudaStream_t stream) {
+  switch (what) {
+    case TOWR_B200_EVAL_G: return LaunchT<1>(P, pcs, x, g, vals, status, n_problems, max_ctas, skew, stream);
+    case TOWR_B200_EVAL_JAC: return LaunchT<2>(P, pcs, x, g, vals, status, n_problems, max_ctas, skew, stream);
+    case TOWR_B200_EVAL_BOTH: return LaunchT<3>(P, pcs, x, g, vals, status, n_problems, max_ctas, skew, stream);
+  }
+  return cudaErrorInvalidValue;
+}
+
+int TB_NAME(OccupancyV, TB_LANES, TB_RT, TB_STREAMS, TB_RING)(const DeviceProgram& P) {
+  int n = 0;
+  const size_t smem = EvalSharedBytes(P, TB_LANES, TB_STREAMS, TB_RING != 0);
+  auto kern = EvalKernel<3, TB_LANES, TB_RT != 0, TB_STREAMS, TB_RING != 0>;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, kThreads * TB_LANES * TB_STREAMS, smem) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+}  // namespace tb
+
+TB_PHASE_CLOCK_READER(towr_b200_debug_phase_clocks)

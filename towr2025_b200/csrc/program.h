@@ -125,20 +125,6 @@ struct SegmentRec {
   int pad2;
 };
 
-// Bulk-store kernel: G sits at the front of a joint region, the staging buffer of segment s at its end.  The TMA engine
-// still reads segment s's staged values while stage A of segment s + 1 (cyclically) fills G, so the region must hold
-// max(g_s, g_{s+1}) + staging_s elements per problem lane.
-TB_PHD inline int StagingStride(int n_entries) { return (n_entries + 3) & ~1; }   // + parity slack, even
-inline int JointCapacity(const SegmentRec* sg, int n) {
-  int cap = 0;
-  for (int s = 0; s < n; ++s) {
-    const int g = sg[s].g_size > sg[(s + 1) % n].g_size ? sg[s].g_size : sg[(s + 1) % n].g_size;
-    const int need = g + StagingStride(sg[s].n_entries) + 2;
-    if (need > cap) cap = need;
-  }
-  return cap;
-}
-
 // slots 0.. of every segment's G buffer
 enum { kGOne = 0, kGMass = 1, kGMinusOne = 2, kGReserved = 3 };
 
@@ -192,13 +178,26 @@ struct DeviceProgram {  // pointers into device memory (one copy per GPU)
   int n_vars, n_rows, nnz, n_ee;
   int n_segments;
   int g_capacity;       // max g_size over segments
-  int joint_capacity;   // bulk-store kernel: elements per problem lane of the region G and the staging buffer share (JointCapacity)
   double total_time;
   BlobLayout blob;
   const unsigned char* blob_data;
   const uint32_t* entries;   // G byte offset | B byte offset << 16, storage order
   const SegmentRec* segments;
 };
+
+// ---- shared-memory geometry of the evaluation kernel (eval_kernel.cuh), used by the host-side sizing as well.
+// RING variants stage the products of stage B in a ring of kRingDepth chunks per stream; a chunk holds
+// RingBatchFor(lanes) entries per thread for each lane, each lane's row has 2 spare elements (destination parity).
+constexpr int kRingDepth = 2;
+TB_PHD constexpr int RingBatchFor(int lanes) { return lanes >= 2 ? 2 : 4; }
+TB_PHD inline int RingRow(int lanes) { return RingBatchFor(lanes) * kEntryThreads * lanes + 2; }
+// doubles one stream of `lanes` problem lanes needs next to the class tables (even: keeps 16-byte alignment)
+TB_PHD inline int StreamDoubles(const DeviceProgram& P, int lanes, bool ring) {
+  const int rt = P.blob.rt ? 8 * P.blob.n_polys + P.blob.n_pdur : 0;   // kRtd (device_math.cuh)
+  int n = lanes * (P.blob.n_node_values + 6 * P.blob.n_polys + rt + P.g_capacity);
+  if (ring) n += kRingDepth * lanes * RingRow(lanes) + 2;
+  return (n + 1) & ~1;
+}
 
 struct ProblemConst {   // per-problem constants read by the kernels
   double mass;

@@ -918,22 +918,12 @@ std::string StructureSignature(const towr_b200_spec& s) {
   return o.str();
 }
 
-void BuildProgram(const towr_b200_spec& s, HostProgram& hp, int g_cap, int joint_cap) {
+void BuildProgram(const towr_b200_spec& s, HostProgram& hp, int g_cap) {
   BuildLayout(s, hp);
   hp.signature = StructureSignature(s);
   // pass 1: one segment per group, to learn each group's G footprint
   ResetTables(hp);
-  // bulk-store kernel: the range-of-motion sets of all feet in one group may exceed the joint budget: group fewer feet
-  int rom_fpg = 0;
-  if (joint_cap > 0 && !hp.optimize_durations) {
-    const double T = hp.total_time, dt = s.dt_constraint_range_of_motion;
-    const long long K = static_cast<long long>(T / dt) + 2;
-    for (int f = s.n_ee; f >= 1; f = f > 2 ? f / 2 : f - 1) {
-      rom_fpg = f;
-      if (K * (kRomPreSize + 9 * f) + f * K * 90 <= joint_cap * 9LL / 10) break;
-    }
-    if (rom_fpg == s.n_ee) rom_fpg = 0;
-  }
+  const int rom_fpg = 0;
   Builder sizing(s, hp, nullptr);
   sizing.rom_feet_per_group = rom_fpg;
   sizing.Run();
@@ -958,32 +948,8 @@ void BuildProgram(const towr_b200_spec& s, HostProgram& hp, int g_cap, int joint
     }
     return n;
   };
-  // bulk-store kernel: a segment's G slots and its staged values share one budget (joint_cap elements per problem)
-  auto plan_joint = [&](int cap, std::vector<char>& plan) {
-    int used = kGReserved + 2, used_g = kGReserved, n = 0;
-    for (size_t g = 0; g < plan.size(); ++g) {
-      const int need = sizing.group_g_size[g] + group_entries[g];
-      plan[g] = 0;
-      if (g == 0 || used + need > cap || used_g + sizing.group_g_size[g] > cap_max) {
-        plan[g] = 1;
-        used = kGReserved + 2;
-        used_g = kGReserved;
-        ++n;
-      }
-      used += need;
-      used_g += sizing.group_g_size[g];
-    }
-    return n;
-  };
   std::vector<char> plan(sizing.group_g_size.size(), 0);
-  if (joint_cap > 0) {
-    const int n_min = plan_joint(joint_cap, plan);
-    int lo = 0;
-    for (size_t g = 0; g < plan.size(); ++g) lo = std::max(lo, sizing.group_g_size[g] + group_entries[g] + kGReserved + 2);
-    int cap = std::max(lo, (total + hp.nnz) / std::max(1, n_min));
-    while (cap < joint_cap && plan_joint(cap, plan) > n_min) cap += 32;   // balanced: smallest budget with n_min segments
-    if (cap >= joint_cap) plan_joint(joint_cap, plan);
-  } else if (g_cap > 0) {
+  if (g_cap > 0) {
     plan_with(std::max(largest + kGReserved, g_cap), plan);
   } else if (const char* env = std::getenv("TOWR_B200_GCAP")) {
     plan_with(std::max(64, std::atoi(env)), plan);

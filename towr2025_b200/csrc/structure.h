@@ -23,8 +23,7 @@ void HermiteBasis(double T, double t, double out[12]);
 int SegmentId(double t_global, const std::vector<double>& durations);
 double LocalTime(double t_global, int id, const std::vector<double>& durations);
 // g_cap > 0 overrides the G slots per segment (the batch lowers it when a class's tables leave less shared memory)
-// joint_cap > 0 (bulk-store kernel): G slots + stored entries per segment share this budget
-void BuildProgram(const towr_b200_spec& s, HostProgram& hp, int g_cap = 0, int joint_cap = 0);
+void BuildProgram(const towr_b200_spec& s, HostProgram& hp, int g_cap = 0);
 std::string StructureSignature(const towr_b200_spec& s);
 
 // pack.cc
