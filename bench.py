@@ -120,25 +120,12 @@ class ClockSampler:
                 "samples": len(s)}
 
 
-def make_inputs(T, batch, rank):
-    """Structure class + per-problem specs (random goals) + X_VARIANTS perturbed x per problem (SURVEY.md §8d)."""
+def x_scales(var_sets, mass):
+    """Per-variable perturbation scale of the evaluation points, from the variable-set names."""
     import numpy as np
-    rng = np.random.default_rng(GOAL_SEED + 7919 * rank)
-    s0 = wl_spec(T)
-    st = T.Structure(s0)
-    specs = []
-    x0 = np.empty((batch, st.n_vars))
-    for i in range(batch):
-        goal = (rng.uniform(0.5, 2.5), rng.uniform(-0.3, 0.3), rng.uniform(-0.4, 0.4))
-        s = wl_spec(T, goal)
-        specs.append(s)
-        x0[i] = st.x0(s)
-    lo, up = st.var_bounds(s0)
-    names = st.var_sets()
-    scale = np.empty(st.n_vars)
-    col = 0
-    mg = s0.mass * 9.80665
-    for name, n in names:
+    mg = mass * 9.80665
+    out = []
+    for name, n in var_sets:
         sc = 0.05
         if name.startswith("base-ang") or name.startswith("ee-ang"):
             sc = 0.02
@@ -148,71 +135,108 @@ def make_inputs(T, batch, rank):
             sc = 0.5
         elif name.startswith("ee-schedule"):
             sc = 0.02
-        scale[col:col + n] = sc
-        col += n
+        out.append(np.full(n, sc))
+    return np.concatenate(out)
+
+
+def draw_goal(rng):
+    return (rng.uniform(0.5, 2.5), rng.uniform(-0.3, 0.3), rng.uniform(-0.4, 0.4))
+
+
+def make_inputs(T, batch, rank):
+    """Structure class + per-problem specs (random goals) + X_VARIANTS perturbed x per problem (SURVEY.md §8d)."""
+    import numpy as np
+    rng = np.random.default_rng(GOAL_SEED + 7919 * rank)
+    s0 = wl_spec(T)
+    st = T.Structure(s0)
+    specs = []
+    x0 = np.empty((batch, st.n_vars))
+    for i in range(batch):
+        s = wl_spec(T, draw_goal(rng))
+        specs.append(s)
+        x0[i] = st.x0(s)
+    scale = x_scales(st.var_sets(), s0.mass)
     xs = []
     for v in range(X_VARIANTS):
-        x = x0 + rng.uniform(-1.0, 1.0, size=x0.shape) * scale
-        xs.append(x)
+        xs.append(x0 + rng.uniform(-1.0, 1.0, size=x0.shape) * scale)
     return s0, st, specs, xs
 
 
+def oracle_inputs(O, sample, variants):
+    """The same distribution of evaluation points as make_inputs, built with the oracle only (reference arm and
+    cpu_baseline): random goals, x = the goal's initial guess + U[-1,1] * scale.  Goals only move x0 and bounds, not g / J
+    (SURVEY.md H7), so one oracle object graph per thread serves every problem of the sample."""
+    import numpy as np
+    rng = np.random.default_rng(GOAL_SEED)
+    so = wl_spec(O)
+    probe = O.Problem(so)
+    x0 = np.empty((sample, probe.n_vars))
+    for i in range(sample):
+        x0[i] = O.Problem(wl_spec(O, draw_goal(rng))).x0()
+    scale = x_scales(probe.var_sets(), so.mass)
+    xs = [x0 + rng.uniform(-1.0, 1.0, size=x0.shape) * scale for _ in range(variants)]
+    return so, probe, xs
+
+
 def run_reference(args, rank, world):
-    """The reference's CPU evaluation of the path (oracle port, OpenMP over problems) on a bounded sample."""
+    """The reference's CPU evaluation of the path on a bounded sample: the oracle port (the reference itself needs Eigen /
+    ifopt / Ipopt, absent), OpenMP over problems on all host cores, one object graph per thread built before the timed
+    region.  This arm imports nothing of the product: sizes, x0 and the pattern size come from the oracle."""
     if rank != 0:
         return
-    import numpy as np
-    import towr2025_b200 as T              # host-side set-up only (specs, x0); no GPU work on this arm
     from oracle import oracle_py as O
     cores = os.cpu_count() or 1
-    s0 = wl_spec(T)
-    st = T.Structure(s0)
-    so = wl_spec(O)
-    sample = max(cores * 8, 16)
-    rng = np.random.default_rng(GOAL_SEED)
-    x = st.x0(s0)[None, :] + rng.uniform(-1, 1, size=(sample, st.n_vars)) * 0.05
-    nnz = st.nnz
-    for _ in range(min(args.warmup, 2)):
-        O.batch_eval(so, x, nnz, n_threads=cores)
-    steps = max(1, min(args.steps, 10))
+    sample = max(cores * 16, 32)
+    so, probe, xs = oracle_inputs(O, sample, 4)
+    pool = O.Pool(so, cores)
+    nnz = pool.nnz
+    import numpy as np
+    g = np.empty((sample, pool.n_rows))
+    v = np.empty((sample, nnz))
+    for k in range(args.warmup):
+        pool.eval(xs[k % len(xs)], g, v)
     t0 = time.perf_counter()
-    for _ in range(steps):
-        O.batch_eval(so, x, nnz, n_threads=cores)
+    for k in range(args.steps):
+        pool.eval(xs[k % len(xs)], g, v)
     dt = time.perf_counter() - t0
-    value = sample * steps / dt
-    stinfo = {"n_vars": st.n_vars, "n_rows": st.n_rows, "nnz": st.nnz, "bytes": st.bytes_per_eval}
-    line = {"impl": "reference", "metric": metric_name(args.workload), "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
-            "warmup": min(args.warmup, 2), "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+    value = sample * args.steps / dt
+    stinfo = {"n_vars": pool.n_vars, "n_rows": pool.n_rows, "nnz": nnz, "bytes": 8 * (pool.n_vars + pool.n_rows + nnz)}
+    line = {"impl": "reference", "metric": metric_name(args.workload), "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(stinfo, args.batch, args.gpus),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": "%d problems per step (bounded sample of the 4096-problem batch), g + Jacobian values, "
-                                       "OpenMP over problems; the reference itself needs Eigen/ifopt/Ipopt (absent)" % sample},
+                             "sample": "%d problems per step (bounded sample of the %d-problem batch, same goal and x "
+                                       "distribution), g + Jacobian values, OpenMP over problems, object graphs built before "
+                                       "the timed region; the reference itself needs Eigen/ifopt/Ipopt (absent)"
+                                       % (sample, args.batch)},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
 
-def cpu_baseline(T, st, s0, xs):
+def cpu_baseline(n_rows, nnz):
     """Oracle port on the host cores, bounded sample (reported next to the GPU number, rank 0, N=1 only)."""
     import numpy as np
     from oracle import oracle_py as O
     cores = os.cpu_count() or 1
-    so = wl_spec(O)
-    sample = max(cores * 8, 16)
-    x = np.ascontiguousarray(xs[0][:sample])
-    # goals only move bounds and x0, not g/J (SURVEY.md H7), so one oracle spec serves the sample
-    O.batch_eval(so, x[: max(cores, 2)], st.nnz, n_threads=cores)
+    sample = max(cores * 16, 32)
+    so, probe, xs = oracle_inputs(O, sample, 2)
+    pool = O.Pool(so, cores)
+    assert pool.nnz == nnz and pool.n_rows == n_rows
+    g = np.empty((sample, pool.n_rows))
+    v = np.empty((sample, nnz))
+    pool.eval(xs[0], g, v)
     reps, t0 = 0, time.perf_counter()
     while True:
-        O.batch_eval(so, x, st.nnz, n_threads=cores)
+        pool.eval(xs[reps % 2], g, v)
         reps += 1
         dt = time.perf_counter() - t0
         if dt > 10.0:
             break
     return {"value": sample * reps / dt, "unit": UNIT, "cores": cores, "kind": "port",
             "sample": "%d problems x %d repetitions of the same workload (g + Jacobian values), OpenMP over problems, "
-                      "%.1f s of CPU work" % (sample, reps, dt)}
+                      "one object graph per thread built before the timed region, %.1f s of CPU work" % (sample, reps, dt)}
 
 
 def run_ours(args, rank, world, local_rank):
@@ -320,7 +344,7 @@ def run_ours(args, rank, world, local_rank):
                         "api": "towr_b200_batch_eval (C ABI), pinned host buffers"},
                 "gpu_launches": launches, "clocks": clocks}
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(T, st, s0, xs_host)
+            line["cpu_baseline"] = cpu_baseline(st.n_rows, st.nnz)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

@@ -254,6 +254,101 @@ int orc_batch_eval(const orc_spec* s, int n, const double* x, double* g, double*
   return status;
 }
 
+// TEST SWITCH: 0 = std::pow everywhere (the reference, default); 1 = PhaseSpline polynomials use the correctly rounded
+// integer powers the device computes at run time.  Global, not thread-safe: set it before evaluating.
+void orc_set_pow_mode(int mode) { SetPowMode(mode); }
+int orc_get_pow_mode(void) { return GetPowMode(); }
+// x^n (n = 2..4) three ways: std::pow, the device's compensated product (ExactPow), and the __float128 product rounded
+// to double (correct rounding up to a 2^-113 relative error before the final rounding)
+void orc_pow_compare(double x, int n, double* std_pow, double* exact_pow, double* quad_rounded) {
+  *std_pow = std::pow(x, n);
+  *exact_pow = ExactPow(x, n);
+  __float128 q = 1;
+  for (int i = 0; i < n; ++i) q *= static_cast<__float128>(x);
+  *quad_rounded = static_cast<double>(q);
+}
+
+// Debug hook: state of one spline at global time t after SetVariables(x).  kind: 0 ee-motion, 1 ee-force, 2 ee-torque,
+// 3 base-lin, 4 base-ang.  out[0] polynomial id, out[1] local time, out[2] polynomial duration, out[3..5] pos,
+// out[6..8] vel, out[9..11] d pos / d phase durations column 0 (PhaseSpline only, else 0), out[12] number of polynomials
+void orc_debug_spline(orc_problem* p, const double* x, int kind, int ee, double t, double* out) {
+  p->nlp.SetVariables(x);
+  std::shared_ptr<NodeSpline> sp = kind == 0 ? p->splines.ee_motion_.at(ee) : kind == 1 ? p->splines.ee_force_.at(ee)
+                                   : kind == 2 ? p->splines.ee_torque_.at(ee) : kind == 3 ? p->splines.base_linear_
+                                                                                          : p->splines.base_angular_;
+  const Vec d = sp->GetPolyDurations();
+  auto lt = sp->GetLocalTime(t, d);
+  out[0] = lt.first; out[1] = lt.second; out[2] = d.at(lt.first);
+  State3 pt = sp->GetPoint(t);
+  for (int i = 0; i < 3; ++i) { out[3 + i] = pt.p(i); out[6 + i] = pt.v(i); out[9 + i] = 0.0; }
+  SpMat J = sp->GetJacobianOfPosWrtDurations(t);
+  for (int r = 0; r < 3 && r < static_cast<int>(J.r.size()); ++r)
+    for (auto& en : J.r[r]) if (en.first == 0) out[9 + r] = en.second;
+  out[12] = static_cast<double>(d.size());
+}
+
+// Persistent pool for the timed CPU baseline: one object graph per thread built ONCE (set-up, as a solver thread would
+// hold its own NlpFormulation), so that the timed region holds evaluations only.
+struct orc_pool {
+  std::vector<std::unique_ptr<orc_problem>> per_thread;
+  int nv = 0, nr = 0, nnz = 0;
+};
+
+orc_pool* orc_pool_create(const orc_spec* s, int n_threads) {
+  try {
+    auto pool = std::make_unique<orc_pool>();
+    if (n_threads < 1) n_threads = 1;
+    for (int t = 0; t < n_threads; ++t) {
+      pool->per_thread.emplace_back(new orc_problem);
+      Build(pool->per_thread.back().get(), *s);
+    }
+    orc_problem* p0 = pool->per_thread[0].get();
+    pool->nv = p0->nlp.GetNumberOfOptimizationVariables();
+    pool->nr = p0->nlp.GetNumberOfConstraints();
+    pool->nnz = orc_nnz(p0, nullptr);
+    return pool.release();
+  } catch (const std::exception& e) {
+    g_err = e.what();
+    return nullptr;
+  }
+}
+void orc_pool_destroy(orc_pool* p) { delete p; }
+int orc_pool_threads(const orc_pool* p) { return static_cast<int>(p->per_thread.size()); }
+int orc_pool_nnz(const orc_pool* p) { return p->nnz; }
+
+int orc_pool_eval(orc_pool* pool, int n, const double* x, double* g, double* vals) {
+  int status = 0;
+  const int nv = pool->nv, nr = pool->nr, nnz = pool->nnz;
+  const int nt = static_cast<int>(pool->per_thread.size());
+#pragma omp parallel num_threads(nt)
+  {
+    int me = 0;
+#ifdef _OPENMP
+    me = omp_get_thread_num();
+#endif
+    orc_problem& local = *pool->per_thread[me % nt];
+    std::vector<double> v;
+#pragma omp for schedule(dynamic)
+    for (int i = 0; i < n; ++i) {
+      const double* xi = x + static_cast<size_t>(i) * nv;
+      if (g) {
+        Vec gi = local.nlp.EvaluateConstraints(xi);
+        std::memcpy(g + static_cast<size_t>(i) * nr, gi.data(), nr * sizeof(double));
+      }
+      if (vals) {
+        local.nlp.EvalJacobian(xi, nullptr, nullptr, &v);
+        if (static_cast<int>(v.size()) != nnz) {
+#pragma omp atomic write
+          status = -1;
+        } else {
+          std::memcpy(vals + static_cast<size_t>(i) * nnz, v.data(), nnz * sizeof(double));
+        }
+      }
+    }
+  }
+  return status;
+}
+
 static Node MakeNode(const double* p, const double* v) { Node n; n.p = V3(p[0], p[1], p[2]); n.v = V3(v[0], v[1], v[2]); return n; }
 
 void orc_hermite_point(const double* p0, const double* v0, const double* p1, const double* v1, double T, double t,

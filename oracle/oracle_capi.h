@@ -85,6 +85,25 @@ int orc_eval_jac(orc_problem* p, const double* x, int* rows, int* cols, double* 
  * OpenMP over problems, one object graph per thread.  Returns 0, or -1 on a pattern-size mismatch. */
 int orc_batch_eval(const orc_spec* s, int n, const double* x, double* g, double* vals, int n_threads);
 
+/* The same with one object graph per thread built once at pool creation (what the timed CPU baseline uses: the timed
+ * region then holds evaluations only).  x: n x n_vars, g: n x n_rows, vals: n x orc_pool_nnz (each may be NULL). */
+typedef struct orc_pool orc_pool;
+orc_pool* orc_pool_create(const orc_spec* s, int n_threads);
+void orc_pool_destroy(orc_pool* p);
+int orc_pool_threads(const orc_pool* p);
+int orc_pool_nnz(const orc_pool* p);
+int orc_pool_eval(orc_pool* p, int n, const double* x, double* g, double* vals);
+
+/* TEST SWITCH (no counterpart in the reference): 0 = std::pow everywhere (default, the reference's arithmetic);
+ * 1 = the polynomials of a PhaseSpline (optimised durations) use correctly rounded x^2, x^3, x^4 - what the device
+ * computes at run time, where glibc's pow is not available.  Global; set before evaluating. */
+void orc_set_pow_mode(int mode);
+int orc_get_pow_mode(void);
+void orc_pow_compare(double x, int n, double* std_pow, double* exact_pow, double* quad_rounded);
+
+/* debug hook: see oracle_capi.cc */
+void orc_debug_spline(orc_problem* p, const double* x, int kind, int ee, double t, double* out13);
+
 /* unit hooks for known-answer tests */
 void orc_hermite_point(const double* p0, const double* v0, const double* p1, const double* v1, double T, double t,
                        double* pos, double* vel, double* acc);

@@ -99,6 +99,15 @@ def lib():
     L.orc_nnz.argtypes = [C.c_void_p, dp]
     L.orc_eval_jac.argtypes = [C.c_void_p, dp, ip, ip, dp]
     L.orc_batch_eval.argtypes = [sp, C.c_int, dp, dp, dp, C.c_int]
+    L.orc_pool_create.argtypes = [sp, C.c_int]
+    L.orc_pool_create.restype = C.c_void_p
+    L.orc_pool_destroy.argtypes = [C.c_void_p]
+    L.orc_pool_threads.argtypes = [C.c_void_p]
+    L.orc_pool_nnz.argtypes = [C.c_void_p]
+    L.orc_pool_eval.argtypes = [C.c_void_p, C.c_int, dp, dp, dp]
+    L.orc_debug_spline.argtypes = [C.c_void_p, dp, C.c_int, C.c_int, C.c_double, dp]
+    L.orc_set_pow_mode.argtypes = [C.c_int]
+    L.orc_pow_compare.argtypes = [C.c_double, C.c_int, dp, dp, dp]
     L.orc_hermite_point.argtypes = [dp, dp, dp, dp, C.c_double, C.c_double, dp, dp, dp]
     L.orc_hermite_basis.argtypes = [C.c_double, C.c_double, dp]
     L.orc_hermite_dpos_dT.argtypes = [dp, dp, dp, dp, C.c_double, C.c_double, dp]
@@ -225,3 +234,50 @@ def batch_eval(spec, x, nnz, want_g=True, want_jac=True, n_threads=0):
     if rc != 0:
         raise RuntimeError("oracle pattern size changed across the batch")
     return g, v
+
+
+class Pool:
+    """One oracle object graph per host thread, built once (orc_pool): the timed CPU baseline evaluates through it."""
+
+    def __init__(self, spec, n_threads):
+        self._L = lib()
+        self._p = self._L.orc_pool_create(C.byref(spec), int(n_threads))
+        if not self._p:
+            raise RuntimeError(self._L.orc_last_error().decode())
+        self.n_threads = self._L.orc_pool_threads(self._p)
+        self.nnz = self._L.orc_pool_nnz(self._p)
+        probe = Problem(spec)
+        self.n_vars, self.n_rows = probe.n_vars, probe.n_rows
+        self._x0 = probe.x0()
+
+    def x0(self):
+        return self._x0.copy()
+
+    def __del__(self):
+        if getattr(self, "_p", None):
+            self._L.orc_pool_destroy(self._p)
+            self._p = None
+
+    def eval(self, x, g=None, vals=None):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        n = x.shape[0]
+        assert x.shape[1] == self.n_vars
+        g = np.empty((n, self.n_rows)) if g is None else g
+        vals = np.empty((n, self.nnz)) if vals is None else vals
+        if self._L.orc_pool_eval(self._p, n, _dp(x), _dp(g), _dp(vals)) != 0:
+            raise RuntimeError("oracle pattern size changed across the batch")
+        return g, vals
+
+
+class pow_mode:
+    """with pow_mode(1): the oracle's PhaseSpline polynomials use correctly rounded integer powers (orc_set_pow_mode)."""
+
+    def __init__(self, mode):
+        self.mode = mode
+
+    def __enter__(self):
+        self.old = lib().orc_get_pow_mode()
+        lib().orc_set_pow_mode(self.mode)
+
+    def __exit__(self, *a):
+        lib().orc_set_pow_mode(self.old)

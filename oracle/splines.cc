@@ -9,21 +9,51 @@
 
 namespace orc {
 
+// ---- test switch: which power function the run-time (PhaseSpline) polynomials use
+static int g_pow_mode = 0;
+void SetPowMode(int mode) { g_pow_mode = mode; }
+int GetPowMode() { return g_pow_mode; }
+
+double ExactPow(double x, int n) {
+  switch (n) {
+    case 0: return 1.0;
+    case 1: return x;
+    case 2: return x * x;
+    case 3: {                      // x*x with its rounding error carried by FMA
+      const double p = x * x;
+      const double e = std::fma(x, x, -p);
+      return std::fma(p, x, e * x);
+    }
+    case 4: {
+      const double p = x * x;
+      const double e = std::fma(x, x, -p);
+      const double hi = p * p;
+      return hi + (std::fma(p, p, -hi) + 2.0 * p * e);
+    }
+  }
+  return std::pow(x, n);
+}
+
+double CubicHermitePolynomial::Pw(double x, int n) const {
+  return (runtime_ && g_pow_mode == 1) ? ExactPow(x, n) : std::pow(x, n);
+}
+
 // ============================================================ polynomial.cc
 // polynomial.cc:97-104
 void CubicHermitePolynomial::UpdateCoeff() {
   coeff_[0] = n0_.p;
   coeff_[1] = n0_.v;
-  coeff_[2] = -(3.0 * (n0_.p - n1_.p) + T_ * (2.0 * n0_.v + n1_.v)) / std::pow(T_, 2);
-  coeff_[3] = (2.0 * (n0_.p - n1_.p) + T_ * (n0_.v + n1_.v)) / std::pow(T_, 3);
+  coeff_[2] = -(3.0 * (n0_.p - n1_.p) + T_ * (2.0 * n0_.v + n1_.v)) / Pw(T_, 2);
+  coeff_[3] = (2.0 * (n0_.p - n1_.p) + T_ * (n0_.v + n1_.v)) / Pw(T_, 3);
 }
 
 // polynomial.cc:63-72  d(t^c-derivative)/d(coeff c)
-static double DerivWrtCoeff(double t, Dx d, int c) {
+template <class PowFn>
+static double DerivWrtCoeff(double t, Dx d, int c, PowFn pw) {
   switch (d) {
-    case kPos: return std::pow(t, c);
-    case kVel: return c >= 1 ? c * std::pow(t, c - 1) : 0.0;
-    case kAcc: return c >= 2 ? c * (c - 1) * std::pow(t, c - 2) : 0.0;
+    case kPos: return pw(t, c);
+    case kVel: return c >= 1 ? c * pw(t, c - 1) : 0.0;
+    case kAcc: return c >= 2 ? c * (c - 1) * pw(t, c - 2) : 0.0;
   }
   return 0.0;
 }
@@ -33,7 +63,7 @@ State3 CubicHermitePolynomial::GetPoint(double t_local) const {
   State3 out;
   for (Dx d : {kPos, kVel, kAcc}) {
     V3 acc;
-    for (int c = 0; c < 4; ++c) acc += DerivWrtCoeff(t_local, d, c) * coeff_[c];
+    for (int c = 0; c < 4; ++c) acc += DerivWrtCoeff(t_local, d, c, [this](double x, int n) { return Pw(x, n); }) * coeff_[c];
     (d == kPos ? out.p : d == kVel ? out.v : out.a) = acc;
   }
   return out;
@@ -41,8 +71,8 @@ State3 CubicHermitePolynomial::GetPoint(double t_local) const {
 
 // polynomial.cc:106-180
 double CubicHermitePolynomial::GetDerivativeWrtStartNode(Dx dfdt, Dx node_value, double t) const {
-  double t2 = std::pow(t, 2), t3 = std::pow(t, 3);
-  double T = T_, T2 = std::pow(T_, 2), T3 = std::pow(T_, 3);
+  double t2 = Pw(t, 2), t3 = Pw(t, 3);
+  double T = T_, T2 = Pw(T_, 2), T3 = Pw(T_, 3);
   switch (dfdt) {
     case kPos: return node_value == kPos ? (2*t3)/T3 - (3*t2)/T2 + 1 : t - (2*t2)/T + t3/T2;
     case kVel: return node_value == kPos ? (6*t2)/T3 - (6*t)/T2 : (3*t2)/T2 - (4*t)/T + 1;
@@ -53,8 +83,8 @@ double CubicHermitePolynomial::GetDerivativeWrtStartNode(Dx dfdt, Dx node_value,
 
 // polynomial.cc:122-234
 double CubicHermitePolynomial::GetDerivativeWrtEndNode(Dx dfdt, Dx node_value, double t) const {
-  double t2 = std::pow(t, 2), t3 = std::pow(t, 3);
-  double T = T_, T2 = std::pow(T_, 2), T3 = std::pow(T_, 3);
+  double t2 = Pw(t, 2), t3 = Pw(t, 3);
+  double T = T_, T2 = Pw(T_, 2), T3 = Pw(T_, 3);
   switch (dfdt) {
     case kPos: return node_value == kPos ? (3*t2)/T2 - (2*t3)/T3 : t3/T2 - t2/T;
     case kVel: return node_value == kPos ? (6*t)/T2 - (6*t2)/T3 : (3*t2)/T2 - (2*t)/T;
@@ -66,8 +96,8 @@ double CubicHermitePolynomial::GetDerivativeWrtEndNode(Dx dfdt, Dx node_value, d
 // polynomial.cc:236-257
 V3 CubicHermitePolynomial::GetDerivativeOfPosWrtDuration(double t) const {
   V3 x0 = n0_.p, x1 = n1_.p, v0 = n0_.v, v1 = n1_.v;
-  double t2 = std::pow(t, 2), t3 = std::pow(t, 3);
-  double T = T_, T2 = std::pow(T_, 2), T3 = std::pow(T_, 3), T4 = std::pow(T_, 4);
+  double t2 = Pw(t, 2), t3 = Pw(t, 3);
+  double T = T_, T2 = Pw(T_, 2), T3 = Pw(T_, 3), T4 = Pw(T_, 4);
   return (t3 * (v0 + v1)) / T3
        - (t2 * (2.0 * v0 + v1)) / T2
        - ((3 * t3) * (2.0 * x0 - 2.0 * x1 + T * v0 + T * v1)) / T4
@@ -423,6 +453,7 @@ PhaseSpline::PhaseSpline(const std::shared_ptr<NodesVariablesPhaseBased>& nodes,
     : NodeSpline(nodes.get(), nodes->ConvertPhaseToPolyDurations(durations->GetPhaseDurations())),
       phase_nodes_(nodes), phase_durations_(durations) {
   durations->AddObserver(this);        // helpers/phase_durations_observer.cc:37-44
+  for (auto& p : polys_) p.MarkRuntimeDurations();   // test switch only (SetPowMode), no effect in the default mode
   UpdatePolynomialDurations();
   // every global time can fall into every polynomial: pre-fill all columns
   for (int i = 0; i < nodes->GetPolynomialCount(); ++i) FillJacobianWrtNodes(i, 0.0, kPos, jac_wrt_nodes_structure_, true);

@@ -59,11 +59,23 @@ class CubicHermitePolynomial {
   double GetDerivativeWrtStartNode(Dx dfdt, Dx node_deriv, double t) const;
   double GetDerivativeWrtEndNode(Dx dfdt, Dx node_deriv, double t) const;
   V3 GetDerivativeOfPosWrtDuration(double t) const;
+  // TEST SWITCH (not in the reference): polynomials of a PhaseSpline are marked; with SetPowMode(1) their integer powers
+  // are the correctly rounded ones the device computes at run time instead of glibc's std::pow (see Pw in splines.cc)
+  void MarkRuntimeDurations() { runtime_ = true; }
  private:
+  double Pw(double x, int n) const;
+  bool runtime_ = false;
   double T_ = 0.0;
   Node n0_, n1_;
   V3 coeff_[4];
 };
+
+// 0 (default): std::pow everywhere, as the reference.  1: marked polynomials use correctly rounded x^2, x^3, x^4.
+void SetPowMode(int mode);
+int GetPowMode();
+// x^n for n = 0..4, correctly rounded (n = 3, 4: up to the rare double-rounding case): the device's Cube / Pow4
+// (towr2025_b200/csrc/device_math.cuh) restated
+double ExactPow(double x, int n);
 
 // ------------------------------------------------------------- variable sets
 class VariableSet {
