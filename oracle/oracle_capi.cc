@@ -286,6 +286,20 @@ void orc_debug_spline(orc_problem* p, const double* x, int kind, int ee, double 
     for (auto& en : J.r[r]) if (en.first == 0) out[9 + r] = en.second;
   out[12] = static_cast<double>(d.size());
 }
+// node values (p0, v0, p1, v1: 12 doubles) of polynomial `poly` of the same spline
+void orc_debug_poly_nodes(orc_problem* p, int kind, int ee, int poly, double* out12) {
+  std::shared_ptr<NodesVariables> nv;
+  for (auto& v : p->nlp.Vars()->GetComponents()) {
+    const std::string want = kind == 0 ? "ee-motion_" + std::to_string(ee) : kind == 1 ? "ee-force_" + std::to_string(ee)
+                             : kind == 2 ? "ee-torque_" + std::to_string(ee) : kind == 3 ? "base-lin" : "base-ang";
+    if (v->GetName() == want) nv = std::dynamic_pointer_cast<NodesVariables>(v);
+  }
+  const auto& nodes = nv->GetNodes();
+  for (int i = 0; i < 3; ++i) {
+    out12[i] = nodes.at(poly).p(i); out12[3 + i] = nodes.at(poly).v(i);
+    out12[6 + i] = nodes.at(poly + 1).p(i); out12[9 + i] = nodes.at(poly + 1).v(i);
+  }
+}
 
 // Persistent pool for the timed CPU baseline: one object graph per thread built ONCE (set-up, as a solver thread would
 // hold its own NlpFormulation), so that the timed region holds evaluations only.

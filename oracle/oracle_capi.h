@@ -103,6 +103,7 @@ void orc_pow_compare(double x, int n, double* std_pow, double* exact_pow, double
 
 /* debug hook: see oracle_capi.cc */
 void orc_debug_spline(orc_problem* p, const double* x, int kind, int ee, double t, double* out13);
+void orc_debug_poly_nodes(orc_problem* p, int kind, int ee, int poly, double* out12);
 
 /* unit hooks for known-answer tests */
 void orc_hermite_point(const double* p0, const double* v0, const double* p1, const double* v1, double T, double t,

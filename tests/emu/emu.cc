@@ -41,7 +41,7 @@ static void EmuEval(const HostProgram& hp, const towr_b200_spec* s, const double
       const RtFoot ft = cx.T.rt_feet[f];
       double sum = 0.0;
       for (int i = 0; i < ft.n_phases - 1; ++i) { pdur[ft.phase0 + i] = x[ft.col0 + i]; sum += x[ft.col0 + i]; }
-      pdur[ft.phase0 + ft.n_phases - 1] = hp.total_time - sum;
+      pdur[ft.phase0 + ft.n_phases - 1] = ft.total - sum;
     }
     for (int poly = 0; poly < L.n_polys; ++poly) {
       const uint32_t pm = cx.T.poly_meta[poly];

@@ -143,3 +143,19 @@ def test_oracle_reproduces_committed_fixtures(oracle):
         assert tol_ratio(p.eval_g(z["x"]), z["g"]) <= 1.0
         assert tol_ratio(v[z["jac_idx"]], z["jac_vals"]) <= 1.0
         assert abs(v.sum() - float(z["sum_vals"])) <= 1e-9 * float(z["sum_abs"])
+
+
+def test_exact_powers_are_correctly_rounded(oracle):
+    """oracle/splines.cc ExactPow (the device's Cube / Pow4 restated, used by orc_set_pow_mode(1)) equals the __float128
+    product rounded to double; glibc's pow is within one ulp of it and differs for a small fraction of arguments."""
+    L = oracle.lib()
+    rng = np.random.default_rng(5)
+    std, ex, qd = C.c_double(), C.c_double(), C.c_double()
+    n, diff_std = 20000, 0
+    for n_pow in (2, 3, 4):
+        for x in rng.uniform(1e-3, 3.0, size=n):
+            L.orc_pow_compare(float(x), n_pow, C.byref(std), C.byref(ex), C.byref(qd))
+            assert ex.value == qd.value, (x, n_pow)
+            assert abs(std.value - qd.value) <= np.spacing(qd.value)
+            diff_std += std.value != qd.value
+    assert diff_std < 0.01 * 3 * n

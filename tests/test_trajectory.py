@@ -89,7 +89,7 @@ def test_gpu_trajectory_matches_oracle(product, oracle, case):
             assert np.array_equal(rows[i][:, 0], ref[:, 0])                       # sample times: bit-exact
             cc = [19 + 25 * e + 24 for e in range((st.trajectory_width() - 19) // 25)]
             assert np.array_equal(rows[i][:, cc], ref[:, cc])                     # is_contact: exact
-            assert parity_ok(rows[i], ref, is_rt(case))
+            assert parity_ok(rows[i], ref)
 
 
 @pytest.mark.gpu

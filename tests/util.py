@@ -59,22 +59,42 @@ def is_rt(case):
     return len(case) > 7 and bool(case[7])
 
 
-def parity_ok(a, b, rt=False):
-    """Value parity.  Fixed durations: every entry within ATOL + RTOL*|b|.
-    Optimised durations: the device cannot call glibc's std::pow; its t^3 / T^3 / T^4 are correctly rounded while
-    glibc's are not for ~0.08 % of arguments, and entries that cancel heavily (duration derivatives) amplify that one
-    ulp (one affected spline sample touches all the rows / columns of that sample).  There: at most 0.5 % of the
-    entries may leave the band, and none by more than 1e-11 + 1e-9 relative."""
+REGROUPED_BAND = 4.0   # x the strict band, allowed only on the dynamic x base-ang block (see parity_ok)
+
+
+def regrouped_mask(st):
+    """Entries of the dynamic constraint's base-ang block (boolean mask over the structure's stored entries)."""
+    rows, cols = st.pattern()
+    r0 = c0 = 0
+    rlo = rhi = clo = chi = -1
+    for name, n in st.con_sets():
+        if name == "dynamic":
+            rlo, rhi = r0, r0 + n
+        r0 += n
+    for name, n in st.var_sets():
+        if name == "base-ang":
+            clo, chi = c0, c0 + n
+        c0 += n
+    return (rows >= rlo) & (rows < rhi) & (cols >= clo) & (cols < chi)
+
+
+def parity_ok(a, b, mask=None):
+    """Value parity (BASELINE.json north_star): every entry within ATOL + RTOL*|b| - fixed AND optimised durations.
+
+    One documented exception, `mask` = regrouped_mask(st): the kernel forms the dynamic constraint's base-ang block
+    (d(I_w wd + w x I_w w)/d euler nodes) as A_pos*B_pos + A_vel*B_vel + A_acc*B_acc from dense 3x3 partials, the reference
+    sums about ten sparse row products in Eigen's order (single_rigid_body_dynamics.cc:124-166).  Where those terms cancel
+    the two associations differ by a few 1e-16 of the LARGEST term, which can exceed 1e-12 of the (small) result: measured
+    over 20 classes x 8 x: 6 of 160128 entries of that block outside the strict band, worst 2.4 x.
+    Entries under the mask may therefore reach REGROUPED_BAND x the strict band; nothing else may leave it."""
     a, b = np.asarray(a), np.asarray(b)
     assert a.shape == b.shape and np.isfinite(a).all() and np.isfinite(b).all()
     if a.size == 0:
         return True
     ratio = np.abs(a - b) / (ATOL + RTOL * np.abs(b))
-    if not rt:
+    if mask is None:
         return bool(ratio.max() <= 1.0)
-    out = ratio > 1.0
-    loose = np.abs(a - b) <= 1e-11 + 1e-9 * np.abs(b)
-    return bool(out.mean() <= 5e-3 and loose.all())
+    return bool((ratio[~mask] <= 1.0).all() and (ratio[mask] <= REGROUPED_BAND).all())
 
 
 def mk(M, case, goal=None):

@@ -274,7 +274,7 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
           pdur[(ft.phase0 + i) * P + pl] = d;
           sum += d;
         }
-        pdur[(ft.phase0 + ft.n_phases - 1) * P + pl] = Pg.total_time - sum;
+        pdur[(ft.phase0 + ft.n_phases - 1) * P + pl] = ft.total - sum;
       }
       StreamSync<S, NT>(sidx);
       for (int i = tid; i < npoly * P; i += NT) {

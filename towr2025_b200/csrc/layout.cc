@@ -265,7 +265,9 @@ void BuildLayout(const towr_b200_spec& s, HostProgram& hp) {
       }
     int phase0 = 0;
     for (int e = 0; e < E; ++e) {
-      hp.rt_feet.push_back(RtFoot{phase0, s.n_phases[e], hp.Find(kEESchedule, e)->col0, 0});
+      double total = 0.0;                       // std::accumulate(timings.begin(), timings.end(), 0.0)
+      for (int i = 0; i < s.n_phases[e]; ++i) total += s.phase_durations[e][i];
+      hp.rt_feet.push_back(RtFoot{phase0, s.n_phases[e], hp.Find(kEESchedule, e)->col0, 0, total});
       phase0 += s.n_phases[e];
     }
   }

@@ -151,6 +151,8 @@ struct RtFoot {         // one PhaseDurations set
   int phase0, n_phases; // offset into the per-problem phase-duration array; P
   int col0;             // first ee-schedule column (P - 1 of them)
   int pad;
+  double total;         // t_total_ of THIS foot: its own initial durations summed in order (phase_durations.cc:40-50);
+                        // feet may differ from each other in the last bit (2.4 vs 2.3999999999999995)
 };
 // per global polynomial: phase | polys_in_phase << 8 | prev_polys_in_phase << 16 | foot << 24 ; kPolyFixed for the
 // base splines (class-constant duration)

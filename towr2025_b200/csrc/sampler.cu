@@ -53,7 +53,7 @@ SampleKernel(const __grid_constant__ TrajDevice Tj, const double* __restrict__ x
         pdur[ft.phase0 + i] = d;
         sum += d;
       }
-      pdur[ft.phase0 + ft.n_phases - 1] = Tj.total_time - sum;
+      pdur[ft.phase0 + ft.n_phases - 1] = ft.total - sum;
     }
     __syncthreads();
     for (int poly = tid; poly < Tj.n_polys; poly += kSampleThreads) {   // polynomial durations

@@ -88,6 +88,7 @@ void BuildTrajTables(const HostProgram& hp, const towr_b200_spec& s, double dt, 
     f.n_phases = s.n_phases[e];
     f.col0 = o.rt ? hp.Find(kEESchedule, e)->col0 : 0;
     f.contact_at_start = s.in_contact_at_start[e] != 0;
+    for (int i = 0; i < s.n_phases[e]; ++i) f.total += s.phase_durations[e][i];   // phase_durations.cc:40-50
     o.feet.push_back(f);
     o.n_phases += s.n_phases[e];
     // fixed durations: PhaseDurations::IsContactPhase (phase_durations.cc:113-118) on the class's phase durations

@@ -21,7 +21,7 @@ struct TrajSplineRec {   // one spline of the SplineHolder, CSV column order
   int rt;                // 1: polynomial durations follow the ee-schedule variables (PhaseSpline)
   int pad;
 };
-struct TrajFootRec { int phase0, n_phases, col0, contact_at_start; };
+struct TrajFootRec { int phase0, n_phases, col0, contact_at_start; double total; };   // total: this foot's own t_total_
 
 struct TrajTables {      // host side, one per (structure class, dt)
   int n_vars = 0, n_ee = 0, width = 0, n_samples = 0, n_nodes = 0, n_polys = 0, n_phases = 0;
