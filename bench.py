@@ -32,15 +32,20 @@ METRIC = "ANYmal-trot constraint+Jacobian evals/s"
 WORKLOADS = {
     "anymal_trot": (3, 1, 2.0, False, 0, "ANYmal fly-trot 2 s (Anymal, combo C1, default Parameters, fixed durations)"),
     "anymal_trot_durations": (3, 1, 2.0, True, 0, "ANYmal fly-trot 2 s with optimised phase durations"),
-    "hyq_gallop_durations": (2, 4, 2.4, True, 1, "HyQ gallop 2.4 s over Block with optimised step durations"),
+    "hyq_gallop_durations": (2, 4, 2.4, True, 3, "HyQ gallop 2.4 s, terrains cycling Block / Gap / Stairs inside the batch, optimised "
+                                                 "step durations (class declares Gap's curvature block)"),
     "biped_walk_durations": (1, 0, 2.4, True, 0, "biped walk 2.4 s with gait/phase-duration optimisation"),
     "monoped_hop": (0, 0, 2.4, False, 0, "monoped hop 2.4 s on flat ground"),
 }
 WL = WORKLOADS["anymal_trot"]
 
 
-def wl_spec(M, goal=(1.0, 0.0, 0.0)):
-    return M.make_spec(WL[0], WL[1], WL[2], goal=goal, terrain=WL[4], optimize_durations=WL[3])
+def wl_spec(M, goal=(1.0, 0.0, 0.0), index=None):
+    """The workload's spec; BASELINE config 4 (terrain id 3 = Gap class) cycles Block / Gap / Stairs over the problem index."""
+    terrain = WL[4]
+    if terrain == 3 and index is not None:
+        terrain = (1, 3, 2)[index % 3]
+    return M.make_spec(WL[0], WL[1], WL[2], goal=goal, terrain=terrain, optimize_durations=WL[3])
 
 
 def metric_name(name):
@@ -152,7 +157,7 @@ def make_inputs(T, batch, rank):
     specs = []
     x0 = np.empty((batch, st.n_vars))
     for i in range(batch):
-        s = wl_spec(T, draw_goal(rng))
+        s = wl_spec(T, draw_goal(rng), index=i)
         specs.append(s)
         x0[i] = st.x0(s)
     scale = x_scales(st.var_sets(), s0.mass)

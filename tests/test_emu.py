@@ -6,7 +6,7 @@ import ctypes as C
 import numpy as np
 import pytest
 
-from util import CASES, is_rt, mk, parity_ok, perturbed, regrouped_mask, tol_ratio
+from util import CASES, GAP_CASES, is_rt, mk, parity_ok, perturbed, regrouped_mask, superset_parity, tol_ratio
 
 DP = C.POINTER(C.c_double)
 
@@ -31,6 +31,22 @@ def test_emulated_kernel_matches_oracle(product, oracle, emu, case):
         g, v = emu_eval(emu, s, st, x)
         assert parity_ok(g, p.eval_g(x))
         assert parity_ok(v, p.eval_jac(x)[2], regrouped_mask(st))
+
+
+@pytest.mark.parametrize("case", GAP_CASES, ids=[c[0] for c in GAP_CASES])
+def test_emulated_kernel_on_gap_superset_pattern(product, oracle, emu, case):
+    """Gap: the declared pattern is a superset of what the oracle stores at any x; equal values there, exact zeros elsewhere."""
+    T, O = product, oracle
+    s = mk(T, case)
+    st = T.Structure(s)
+    p = O.Problem(mk(O, case))
+    x0 = st.x0(s)
+    n_extra = []
+    for x in (x0, perturbed(x0, 3, 0.02), perturbed(x0, 4, 0.05)):
+        g, v = emu_eval(emu, s, st, x)
+        assert parity_ok(g, p.eval_g(x))
+        n_extra.append(superset_parity(st, p.eval_jac(x), v, regrouped_mask(st)))
+    assert len(set(n_extra)) > 1          # the oracle's pattern really depends on x here
 
 
 def test_emulated_kernel_segment_capacity(product, oracle, emu, monkeypatch):

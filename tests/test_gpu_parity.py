@@ -3,7 +3,7 @@ Tolerance (BASELINE.json north_star): sparsity indices bit-exact, values within 
 import numpy as np
 import pytest
 
-from util import CASES, is_rt, mk, parity_ok, perturbed, regrouped_mask, tol_ratio
+from util import CASES, GAP_CASES, is_rt, mk, parity_ok, perturbed, regrouped_mask, superset_parity, tol_ratio
 
 pytestmark = pytest.mark.gpu
 
@@ -42,6 +42,59 @@ def test_values_and_jacobian_match_oracle(product, oracle, case):
         assert np.array_equal(r, rows) and np.array_equal(c, cols)
         assert parity_ok(g[i], p.eval_g(x[i]))
         assert parity_ok(v[i], vo, regrouped_mask(st))
+
+
+@pytest.mark.parametrize("case", GAP_CASES, ids=[c[0] for c in GAP_CASES])
+def test_gap_superset_pattern_matches_oracle(product, oracle, case):
+    """Gap (curvature): the class's pattern is a superset of what the oracle stores at any x; values equal on the oracle's
+    entries, exact zeros on the others (force_constraint_discretized.cc:52-67, torque_constraint_discretized.cc:176-197)."""
+    T, O = product, oracle
+    from util import to_oracle_spec
+    n = 6
+    st, specs, x = _problem_batch(T, O, case, n, 7)
+    b = T.Batch(st, n)
+    for i, s in enumerate(specs):
+        b.set_problem(i, s)
+    g, v = b.eval(x)
+    assert (b.status() == 0).all()
+    extras = set()
+    for i, s in enumerate(specs):
+        p = O.Problem(to_oracle_spec(O, s))
+        assert parity_ok(g[i], p.eval_g(x[i]))
+        extras.add(superset_parity(st, p.eval_jac(x[i]), v[i], regrouped_mask(st)))
+    assert len(extras) > 1
+
+
+@pytest.mark.parametrize("optimise", [False, True], ids=["fixed", "durations"])
+def test_mixed_terrain_batch_block_gap_stairs(product, oracle, optimise):
+    """BASELINE config 4 as written: HyQ gallop, terrain ids cycling Block / Gap / Stairs inside ONE batch.  The class is
+    created on Gap (declares the curvature block); Block and Stairs problems write exact zeros there."""
+    T, O = product, oracle
+    from util import to_oracle_spec
+    terrains = (T.BlockID, T.GapID, T.StairsID)
+    rng = np.random.default_rng(11)
+    st = T.Structure(T.make_spec(T.Hyq, T.C4, 2.4, terrain=T.GapID, optimize_durations=optimise))
+    n = 9
+    specs, xs = [], []
+    for i in range(n):
+        s = T.make_spec(T.Hyq, T.C4, 2.4, goal=(rng.uniform(1.0, 2.0), rng.uniform(-0.2, 0.2), rng.uniform(-0.3, 0.3)),
+                        terrain=terrains[i % 3], optimize_durations=optimise)
+        specs.append(s)
+        xs.append(perturbed(st.x0(s), 300 + i, (0.02 if optimise else 0.08) if i >= 3 else 0.0))
+    x = np.stack(xs)
+    b = T.Batch(st, n)
+    for i, s in enumerate(specs):
+        b.set_problem(i, s)
+    g, v = b.eval(x)
+    assert (b.status() == 0).all()
+    mask = regrouped_mask(st)
+    n_extra = []
+    for i, s in enumerate(specs):
+        p = O.Problem(to_oracle_spec(O, s))
+        assert parity_ok(g[i], p.eval_g(x[i]))
+        n_extra.append(superset_parity(st, p.eval_jac(x[i]), v[i], mask))
+    # Block / Stairs: the whole declared curvature block is extra (never stored by the reference); Gap: part of it
+    assert n_extra[0] == n_extra[2] and n_extra[1] < n_extra[0]
 
 
 def test_eval_modes_and_ids(product, oracle):

@@ -82,21 +82,22 @@ def test_error_behaviour(product):
         T.make_spec(5, T.C1, 2.0)
 
 
-def test_gap_terrain_is_refused(product):
-    """Gap has a value-dependent curvature block (force_constraint_discretized.cc:52-67) that is not built: creating a
-    class on it, or admitting a Gap problem into a curvature-free class, must fail as UNSUPPORTED - never rc 0 with a
-    Jacobian that lacks the block."""
+def test_gap_needs_a_class_that_declares_the_curvature_block(product):
+    """Gap has a value-dependent curvature block (force_constraint_discretized.cc:52-67).  A class created on Gap declares
+    it (superset pattern: more stored entries) and admits problems on any terrain; a class created on a curvature-free
+    terrain must refuse a Gap problem - never rc 0 with a Jacobian that lacks the block."""
     T = product
     for opt in (False, True):
+        flat = T.Structure(T.make_spec(T.Hyq, T.C4, 2.4, terrain=T.BlockID, optimize_durations=opt))
+        curv = T.Structure(T.make_spec(T.Hyq, T.C4, 2.4, terrain=T.GapID, optimize_durations=opt))
+        assert curv.nnz > flat.nnz and curv.n_rows == flat.n_rows and curv.n_vars == flat.n_vars
+        gap = T.make_spec(T.Hyq, T.C4, 2.4, terrain=T.GapID, optimize_durations=opt)
+        assert not flat.accepts(gap)
         with pytest.raises(T.TowrB200Error) as e:
-            T.Structure(T.make_spec(T.Hyq, T.C4, 2.4, terrain=T.GapID, optimize_durations=opt))
-        assert e.value.code == -2 and "Gap" in str(e.value)
-    st = T.Structure(T.make_spec(T.Hyq, T.C4, 2.4, terrain=T.BlockID))
-    gap = T.make_spec(T.Hyq, T.C4, 2.4, terrain=T.GapID)
-    assert not st.accepts(gap)
-    with pytest.raises(T.TowrB200Error) as e:
-        st.x0(gap)
-    assert "Gap" in str(e.value)
+            flat.x0(gap)
+        assert e.value.code == -4 and "Gap" in str(e.value)
+        for terrain in (T.BlockID, T.StairsID, T.GapID, T.FlatID):
+            assert curv.accepts(T.make_spec(T.Hyq, T.C4, 2.4, terrain=terrain, optimize_durations=opt))
 
 
 def test_library_exports_every_declared_symbol(product):

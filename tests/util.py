@@ -55,6 +55,33 @@ CASES = [
 ]
 
 
+# Terrain with curvature (Gap, id 3): the class declares the force / torque constraint's ee-motion block for every sample
+# (superset); the reference / oracle store such an entry only where its scale is non-zero (value-dependent pattern).
+GAP = 3
+GAP_CASES = [
+    ("hyq_gallop_gap", 2, 4, 2.4, (1.5, 0.1, -0.2), GAP),
+    ("hyq_gallop_gap_durations", 2, 4, 2.4, (1.5, 0.1, -0.2), GAP, (), True),                 # BASELINE config 4
+    ("biped_walk_gap_torque", 1, 0, 2.4, (1.4, 0.0, 0.1), GAP, (TORQUE,)),
+    ("monoped_hop_gap_torque_durations", 0, 0, 2.4, (1.3, 0.0, 0.0), GAP, (TORQUE,), True),
+]
+
+
+def superset_parity(st, oracle_rcv, v, mask=None):
+    """The oracle's stored entries (rows, cols, values at this x) must all be in the class's pattern with equal values
+    (parity_ok); the entries the oracle did not store at this x must be exact zeros.  Returns the number of extras."""
+    r, c, vo = oracle_rcv
+    rows, cols = st.pattern()
+    keys = rows.astype(np.int64) * st.n_vars + cols
+    ko = r.astype(np.int64) * st.n_vars + c
+    pos = np.searchsorted(keys, ko)
+    assert (pos < keys.size).all() and np.array_equal(keys[pos], ko), "oracle stores an entry outside the declared pattern"
+    extra = np.ones(st.nnz, bool)
+    extra[pos] = False
+    assert not np.any(v[extra] != 0.0), "an entry the reference does not store is not an exact zero"
+    assert parity_ok(v[pos], vo, None if mask is None else mask[pos])
+    return int(extra.sum())
+
+
 def is_rt(case):
     return len(case) > 7 and bool(case[7])
 

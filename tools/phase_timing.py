@@ -9,7 +9,9 @@ import os
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-os.environ["TOWR_B200_LIB"] = os.path.join(ROOT, "towr2025_b200", "libtowr_b200_timing.so")
+# TIMING_CODE = <lanes><rt><streams><ring> of the instrumented variant (make -C towr2025_b200/csrc timing TIMING_CODE=...)
+CODE = os.environ.get("TIMING_CODE", "2010")
+os.environ["TOWR_B200_LIB"] = os.path.join(ROOT, "towr2025_b200", "libtowr_b200_timing_%s.so" % CODE)
 sys.path.insert(0, ROOT)
 import numpy as np  # noqa: E402
 import torch  # noqa: E402

@@ -17,6 +17,7 @@
 
 #include "kernels.h"
 #include "structure.h"
+#include "terrain.h"
 #include "trajectory.h"
 #include "cost.h"
 
@@ -172,7 +173,11 @@ int towr_b200_structure_accepts(const towr_b200_structure* st, const towr_b200_s
   return Guard([&] {
     if (!st || !s) throw std::runtime_error("null argument");
     tb::ValidateSpec(*s);
-    if (tb::StructureSignature(*s) != st->hp.signature) throw StructureError("spec belongs to a different structure class");
+    if (tb::TerrainCurvatureDims(s->terrain_id) & ~st->hp.curvature_dims)
+      throw StructureError("the problem's terrain has curvature (Gap) and this structure class does not declare the curvature block: "
+                           "create the class from a spec on that terrain");
+    if (tb::StructureSignature(*s, st->hp.curvature_dims) != st->hp.signature)
+      throw StructureError("spec belongs to a different structure class");
   });
 }
 
@@ -243,7 +248,7 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     bool forced_variant = false;
     if (kenv && *kenv && std::strcmp(kenv, "lockstep") != 0) {
       forced_variant = true;
-      if (std::strcmp(kenv, "ring") == 0) want = tb::EvalVariant{forced ? forced : 2, 1, true, 0};
+      if (std::strcmp(kenv, "ring") == 0) want = tb::EvalVariant{1, 1, true, 0};
       else if (std::strcmp(kenv, "streams") == 0) want = tb::EvalVariant{1, 2, false, 0};
       else if (std::strcmp(kenv, "streamsring") == 0) want = tb::EvalVariant{1, 2, true, 0};
       else throw std::runtime_error(std::string("unknown TOWR_B200_KERNEL: ") + kenv);
@@ -291,7 +296,7 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     // lanes per CTA: as many problems side by side as shared memory allows (the class tables are held once per CTA)
     for (int lanes : {4, 2, 1}) {
       if (forced && lanes != forced) continue;
-      try_variant(tb::EvalVariant{lanes, 1, false, 0});
+      try_variant(tb::EvalVariant{lanes, 1, false, want.skew});
     }
     if (b->var.lanes == 0)
       throw std::runtime_error("unsupported: structure class needs more shared memory per CTA than the device has");

@@ -11,8 +11,8 @@
 //   S = 2, P = 1     two streams in anti-phase (the second starts `skew` clocks late): one stream's stage A overlaps
 //                    the other's value stores; the streams only share the class tables and synchronise on named
 //                    barriers of their own
-//   RING             stage B writes its products into a small shared-memory ring in storage order and one thread per
-//                    stream hands each chunk to the TMA engine (cp.async.bulk shared -> global).  The value stores then
+//   RING             stage B writes its products into small per-warp shared-memory rings in storage order and lane 0 of
+//                    each warp hands every 2 KB block to the TMA engine (cp.async.bulk shared -> global).  The value stores then
 //                    never enter the SM's LSU pipe, which serialises global stores with the shared-memory traffic of
 //                    stage A (profiles/r01_ncu_summary.md: mio_throttle / lg_throttle), and drain while the next
 //                    chunk - or the next segment's stage A - runs.
@@ -115,60 +115,63 @@ __device__ __forceinline__ void StreamSync(int sidx) {
   else asm volatile("bar.sync %0, %1;" ::"r"(sidx + 1), "n"(NT) : "memory");
 }
 
-// Ring geometry (program.h): a chunk holds UB = RingBatchFor(P) entries per thread (UB * NT consecutive entries of the
-// segment) for each of the P lanes; kRingDepth chunks per stream.  A lane's row has two spare elements: the row is
-// shifted by the 8-byte parity of its destination so that the body of every copy is 16-byte aligned on both sides.
+// Ring geometry (program.h): every WARP of a stream owns kRingDepth slots of kRingBlock = 32 * kRingUB consecutive entries
+// per problem lane.  A lane's row has two spare elements: the row is shifted by the 8-byte parity of its destination so
+// that the body of every copy is 16-byte aligned on both sides.
 //
-// Stage B of one segment into the ring.  ctr: chunks this stream has staged so far (selects the ring slot).
-// dst[p]: global address of the segment's first entry of lane p; np lanes exist.
-// Protocol per chunk: all threads write their products into the slot and fence them for the async proxy; thread 0 (which
-// owns the stream's bulk groups) waits until the engine has READ the previous chunk - whose slot the next chunk reuses -
-// then the stream's barrier, then thread 0 issues this chunk's copies while the others start on the next chunk.
-template <int P, int NT, int S, int UB, int A, bool GG>
-__device__ __forceinline__ void StageBRing(const uint32_t* __restrict__ ent, int n_entries, int tid, int sidx,
-                                           uint32_t (&d)[A][UB], const double* G, const double* Bs, double* ring, unsigned& ctr,
-                                           double* const (&dst)[P], int np, double (&nf)[P]) {
-  constexpr int CE = UB * NT, ROW = UB * NT + 2;
+// Stage B of one segment through the ring.  Warp w takes blocks w, w + NW, ... of the segment (a block = kRingBlock
+// consecutive entries; lane l takes entries l, l + 32, ... of it, so descriptor loads stay coalesced).  Per block: lane 0
+// waits until the engine has READ the copy that used this slot kRingDepth blocks ago, the warp writes its products into
+// the slot and fences them for the async proxy, __syncwarp, lane 0 issues one cp.async.bulk per problem lane (2 KB).  No
+// CTA-wide barrier: the warps of a stream run independently and up to NW * kRingDepth copies are in flight.
+// ctr: blocks this warp has staged so far (selects the slot).  dst[p]: global address of the segment's first entry of
+// problem lane p; np lanes exist.  d: descriptors of this warp's first AH blocks (loaded before the barrier).
+template <int P, int NT, int AH, bool GG>
+__device__ __forceinline__ void StageBRing(const uint32_t* __restrict__ ent_seg, int n_entries, int tid,
+                                           uint32_t (&d)[AH][kRingUB], const double* G, const double* Bs, double* ring_warp,
+                                           unsigned& ctr, double* const (&dst)[P], int np, double (&nf)[P]) {
+  constexpr int UB = kRingUB, BE = kRingBlock, ROW = kRingBlock + 2, NW = NT / 32;
   const char* Gb = reinterpret_cast<const char*>(G);
   const char* Bb = reinterpret_cast<const char*>(Bs);
+  const int warp = tid >> 5, lane = tid & 31;
   int q[P];
 #pragma unroll
   for (int p = 0; p < P; ++p) q[p] = static_cast<int>((reinterpret_cast<uintptr_t>(dst[p]) >> 3) & 1);
-  int left = n_entries - tid;
-  const int n_chunks = (n_entries + CE - 1) / CE;
-  for (int c0 = 0; c0 < n_chunks; c0 += A) {
+  const int n_blocks = (n_entries + BE - 1) / BE;
+  for (int blk0 = warp; blk0 < n_blocks; blk0 += NW * AH) {
 #pragma unroll
-    for (int a = 0; a < A; ++a) {
-      const int c = c0 + a;
-      if (c >= n_chunks) break;
-      double* sb = ring + (ctr % kRingDepth) * (P * ROW);
+    for (int a = 0; a < AH; ++a) {
+      const int blk = blk0 + a * NW;
+      if (blk >= n_blocks) break;
+      const int e0 = blk * BE;
+      double* sb = ring_warp + (ctr % kRingDepth) * (P * ROW);
+      if (lane == 0) BulkWaitRead<kRingDepth - 1>();
+      __syncwarp();
 #pragma unroll
       for (int u = 0; u < UB; ++u) {
-        if (left > u * NT) {
+        if (e0 + lane + 32 * u < n_entries) {
           double v[P];
           Products<P, GG>(d[a][u], Gb, Bb, v);
 #pragma unroll
           for (int p = 0; p < P; ++p) {
             nf[p] = fma(v[p], 0.0, nf[p]);
-            sb[p * ROW + q[p] + u * NT + tid] = v[p];
+            sb[p * ROW + q[p] + lane + 32 * u] = v[p];
           }
         }
       }
-      const int left_a = left - A * CE;
-      if (left_a > 0) LoadDescriptors<NT, UB>(ent + A * CE, left_a, d[a]);
-      left -= CE;
-      ent += CE;
+      // this warp's block AH further on
+      const int e_next = (blk + AH * NW) * BE;
+#pragma unroll
+      for (int u = 0; u < UB; ++u) d[a][u] = e_next + lane + 32 * u < n_entries ? __ldg(ent_seg + e_next + lane + 32 * u) : kNoEntry;
       FenceProxyAsync();
-      if (tid == 0) BulkWaitRead<kRingDepth - 2>();
-      StreamSync<S, NT>(sidx);
-      if (tid == 0) {
-        const int e0 = c * CE;
-        const int nc = min(CE, n_entries - e0);
+      __syncwarp();
+      if (lane == 0) {
+        const int nc = min(BE, n_entries - e0);
 #pragma unroll
         for (int p = 0; p < P; ++p) {
           if (p < np) {
             double* D0 = dst[p] + e0;
-            const double* src = sb + p * ROW + q[p];          // entry i of the chunk at src[i]
+            const double* src = sb + p * ROW + q[p];          // entry i of the block at src[i]
             if (q[p]) D0[0] = src[0];                         // odd first element: plain store
             const int body = (nc - q[p]) & ~1;
             if (body > 0) BulkStore(D0 + q[p], src + q[p], static_cast<unsigned>(body) * 8u);
@@ -188,8 +191,8 @@ __global__ void __launch_bounds__(kThreads * P * S, (P == 1 && S == 1 && !RT) ? 
 EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restrict__ pcs, const double* __restrict__ x,
            double* __restrict__ g_out, double* __restrict__ vals_out, int* __restrict__ status, int n_problems, int skew) {
   constexpr int NT = kThreads * P;
-  constexpr int UB = RING ? RingBatchFor(P) : kDescBatch;           // descriptors per batch
-  constexpr int AH = RING ? (16 / UB) * (RT ? 2 : 1) : DescAhead<RT>::value;   // batches fetched ahead
+  constexpr int UB = RING ? kRingUB : kDescBatch;                   // descriptors per batch
+  constexpr int AH = RING ? 2 : DescAhead<RT>::value;               // batches fetched ahead
   extern __shared__ uint4 sm4[];
   unsigned char* blob = reinterpret_cast<unsigned char*>(sm4);
   const int nnv = Pg.blob.n_node_values, npoly = Pg.blob.n_polys;
@@ -201,7 +204,9 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
   double* rtd = coef + 6 * npoly * P;                   // RT: kRtd per polynomial, then the phase durations
   double* pdur = rtd + (RT ? kRtd * npoly * P : 0);
   double* G = pdur + (RT ? Pg.blob.n_pdur * P : 0);
-  double* const ring = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(G + Pg.g_capacity * P) + 15) & ~static_cast<uintptr_t>(15));
+  // RING: this warp's slots (16-byte aligned: the stream's arrays hold an even number of doubles, a slot as well)
+  double* const ring = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(G + Pg.g_capacity * P) + 15) & ~static_cast<uintptr_t>(15)) +
+                       (tid >> 5) * (kRingDepth * P * (kRingBlock + 2));
   __shared__ ProblemConst pc_all[P * S];
   __shared__ int bad_all[P * S];
   ProblemConst* const pc_s = pc_all + sidx * P;
@@ -234,9 +239,14 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
     if (tid < P) pc_s[tid] = pcs[min(base_n + tid, n_problems - 1)];
   };
   if (first < n_problems) fetch_group(first);
-  if (S > 1 && sidx > 0 && skew > 0) {                    // anti-phase start of the later streams
-    const long long t0 = clock64();
-    while (clock64() - t0 < static_cast<long long>(skew) * sidx) __nanosleep(200);
+  // skew > 0: later streams (S > 1) or odd CTAs (S = 1) start `skew` clocks late, so that not every SM of the chip is in
+  // its HBM-idle stage A - or its HBM-bound stage B - at the same time
+  {
+    const int late = S > 1 ? sidx : static_cast<int>(blockIdx.x & 1);
+    if (late > 0 && skew > 0) {
+      const long long t0 = clock64();
+      while (clock64() - t0 < static_cast<long long>(skew) * late) __nanosleep(200);
+    }
   }
 
   for (int base = first; base < n_problems; base += stride) {
@@ -361,7 +371,19 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
       // first descriptor batches of stage B: issued before the barrier, consumed after it
       const uint32_t* ent = Pg.entries + sg.entry0 + tid;
       uint32_t d0[AH][UB];
-      if (WHAT & TOWR_B200_EVAL_JAC) LoadDescriptorRing<NT, AH, UB>(ent, sg.n_entries - tid, d0);
+      if (WHAT & TOWR_B200_EVAL_JAC) {
+        if constexpr (RING) {                           // this warp's first AH blocks (StageBRing's entry order)
+#pragma unroll
+          for (int a = 0; a < AH; ++a)
+#pragma unroll
+            for (int u = 0; u < UB; ++u) {
+              const int e = ((tid >> 5) + a * (NT / 32)) * kRingBlock + (tid & 31) + 32 * u;
+              d0[a][u] = e < sg.n_entries ? __ldg(Pg.entries + sg.entry0 + e) : kNoEntry;
+            }
+        } else {
+          LoadDescriptorRing<NT, AH, UB>(ent, sg.n_entries - tid, d0);
+        }
+      }
       StreamSync<S, NT>(sidx);
       TB_MARK(11 + 6 * s)
       // all items of this group are done with nodes[] / pc_s after the last segment's stage A: fetch the next group
@@ -372,7 +394,7 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
           double* dst[P];
 #pragma unroll
           for (int p = 0; p < P; ++p) dst[p] = vals_out + static_cast<size_t>(min(base + p, n_problems - 1)) * Pg.nnz + sg.entry0;
-          StageBRing<P, NT, S, UB, AH, RT>(ent, sg.n_entries, tid, sidx, d0, G, Bs, ring, ring_ctr, dst, min(P, n_problems - base), nf);
+          StageBRing<P, NT, AH, RT>(Pg.entries + sg.entry0, sg.n_entries, tid, d0, G, Bs, ring, ring_ctr, dst, min(P, n_problems - base), nf);
         } else {
           double* o0 = vals_out + static_cast<size_t>(base) * Pg.nnz + sg.entry0 + tid;
           if (n_problems - base >= P)
@@ -382,8 +404,7 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
         }
       }
       TB_MARK(12 + 6 * s)
-      // RING: the last chunk's barrier already ordered every G read before the next stage A
-      if (!RING || !(WHAT & TOWR_B200_EVAL_JAC) || sg.n_entries == 0) StreamSync<S, NT>(sidx);
+      StreamSync<S, NT>(sidx);                          // every G read of this segment before the next stage A
       TB_MARK(13 + 6 * s)
     }
     if (nfx != nfx) atomicOr(&bad_s[pl], 1);
@@ -394,7 +415,7 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
     if (tid < P && bad_s[tid] && base + tid < n_problems) atomicOr(status + base + tid, 2);
   }
   // the ring must outlive the bulk copies that read it
-  if (RING && (WHAT & TOWR_B200_EVAL_JAC) && tid == 0) BulkWaitAll();
+  if (RING && (WHAT & TOWR_B200_EVAL_JAC) && (tid & 31) == 0) BulkWaitAll();
 }
 
 }  // namespace tb

@@ -8,7 +8,7 @@ namespace tb {
 
 // (lanes, rt, streams, ring) tuples the Makefile builds (LANE_OBJS there)
 #define TB_VARIANTS(X) X(1, 0, 1, 0) X(1, 1, 1, 0) X(2, 0, 1, 0) X(2, 1, 1, 0) X(4, 0, 1, 0) X(4, 1, 1, 0) \
-                       X(2, 0, 1, 1) X(2, 1, 1, 1) X(1, 0, 2, 0) X(1, 0, 2, 1) X(1, 1, 2, 1)
+                       X(1, 0, 1, 1) X(1, 0, 2, 0) X(1, 0, 2, 1) X(1, 1, 2, 1)
 
 #define TB_DECL(L, R, S, G)                                                                                             \
   cudaError_t LaunchV##L##_##R##_##S##_##G(const DeviceProgram&, const ProblemConst*, int, const double*, double*, double*, \

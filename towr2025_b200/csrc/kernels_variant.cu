@@ -1,6 +1,10 @@
 // kernels_variant.cu — explicit instantiations of the evaluation kernel for one variant.  Compiled once per variant with
 // -DTB_LANES=<1|2|4> -DTB_RT=<0|1> -DTB_STREAMS=<1|2> -DTB_RING=<0|1> (Makefile) so that the variants build in parallel.
-#if defined(TB_TIMING) && TB_LANES == 2 && TB_RT == 0 && TB_STREAMS == 1 && TB_RING == 0
+// timing build (make timing [TIMING_CODE=<lanes><rt><streams><ring>]): the one variant that owns the phase counters
+#ifndef TB_TIMING_CODE
+#define TB_TIMING_CODE 2010
+#endif
+#if defined(TB_TIMING) && (TB_LANES * 1000 + TB_RT * 100 + TB_STREAMS * 10 + TB_RING) == TB_TIMING_CODE
 #define TB_TIMING_HERE
 #endif
 #include "eval_kernel.cuh"
@@ -52,4 +56,6 @@ int TB_NAME(OccupancyV, TB_LANES, TB_RT, TB_STREAMS, TB_RING)(const DeviceProgra
 
 }  // namespace tb
 
+#ifdef TB_TIMING_HERE
 TB_PHASE_CLOCK_READER(towr_b200_debug_phase_clocks)
+#endif

@@ -6,6 +6,7 @@
 //   Parameters::GetBasePolyDurations               towr/src/parameters.cc:114-130
 //   column order of the NLP                        towr/src/nlp_formulation.cc:81-101
 #include "structure.h"
+#include "terrain.h"
 
 #include <cmath>
 #include <numeric>
@@ -167,12 +168,6 @@ void ValidateSpec(const towr_b200_spec& s) {
       s.torque_polynomials_per_stance_phase < 1)
     throw std::runtime_error("polynomials per phase must be >= 1");
   if (s.terrain_id < 0 || s.terrain_id >= TOWR_B200_TERRAIN_COUNT) throw std::runtime_error("unknown terrain id");
-  // Gap is the one terrain with non-zero second derivatives (height_map_examples.cc:89-120): the reference then stores
-  // f . d(basis)/dx entries in the force / torque constraint's ee-motion block whenever a foot is over the parabola
-  // (force_constraint_discretized.cc:52-67, value-dependent pattern).  That block is not built: refuse the
-  // terrain instead of returning a Jacobian without it.
-  if (s.terrain_id == TOWR_B200_GAP)
-    throw std::runtime_error("unsupported: the Gap terrain (curvature block of the force constraint is not built)");
   if (s.n_costs < 0 || s.n_costs > TOWR_B200_MAX_COSTS) throw std::runtime_error("bad n_costs");
   for (int c = 0; c < s.n_costs; ++c) {
     if (s.cost_ids[c] == TOWR_B200_COST_ENERGY || s.cost_ids[c] == TOWR_B200_COST_ANG_MOM)
@@ -187,6 +182,7 @@ void BuildLayout(const towr_b200_spec& s, HostProgram& hp) {
   hp.n_ee = s.n_ee;
   hp.total_time = TotalTime(s);
   hp.optimize_durations = OptimizesDurations(s);
+  hp.curvature_dims = TerrainCurvatureDims(s.terrain_id);
   const int E = s.n_ee;
   const std::vector<double> base_T = BasePolyDurations(s);
   const int n_base_nodes = static_cast<int>(base_T.size()) + 1;

@@ -2,6 +2,8 @@
 // byte-offset entry descriptors (program.h).
 #include <algorithm>
 #include <array>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <stdexcept>
@@ -116,16 +118,53 @@ void PackProgram(HostProgram& hp) {
         std::stable_sort(kinds.begin(), kinds.end(), [](const std::array<int, 3>& a, const std::array<int, 3>& b) {
           return ItemCostRank(a[1]) < ItemCostRank(b[1]);
         });
-        for (auto& k : kinds) {
-          while (padded.size() % kItemPad) padded.push_back(none);
+        // A level runs in rounds of kItemsPerRound (item, lane) slots.  If the padding between kinds is all that pushes
+        // the level into one more round, the cheapest kinds (the last ones) are packed back to back instead: one warp
+        // that runs two short kinds in turn costs far less than a round of its own (ANYmal trot: 272 -> 256 slots).
+        std::vector<int> count(kinds.size(), 0);
+        for (size_t q = 0; q < kinds.size(); ++q)
+          for (int i = 0; i < sg.n_items; ++i) count[q] += kind[sg.item0 + i] == kinds[q];
+        auto pad_to = [](int n) { return (n + kItemPad - 1) / kItemPad * kItemPad; };
+        int total_padded = 0, total_raw = 0;
+        for (int c : count) { total_padded += pad_to(c); total_raw += c; }
+        size_t first_unpadded = kinds.size();                   // kinds [first_unpadded, end) share warps
+        const int rounds_padded = (total_padded + kItemsPerRound - 1) / kItemsPerRound;
+        if (pad_to(total_raw) <= (rounds_padded - 1) * kItemsPerRound || rounds_padded > (pad_to(total_raw) + kItemsPerRound - 1) / kItemsPerRound) {
+          int t = total_padded;
+          while (first_unpadded > 1 && (t + kItemsPerRound - 1) / kItemsPerRound >= rounds_padded) {
+            --first_unpadded;
+            int merged = 0;
+            t = 0;
+            for (size_t q = 0; q < kinds.size(); ++q) {
+              if (q < first_unpadded) t += pad_to(count[q]);
+              else merged += count[q];
+            }
+            t += pad_to(merged);
+          }
+        }
+        for (size_t q = 0; q < kinds.size(); ++q) {
+          if (q <= first_unpadded) while (padded.size() % kItemPad) padded.push_back(none);
           for (int i = 0; i < sg.n_items; ++i)
-            if (kind[sg.item0 + i] == k) padded.push_back(items[sg.item0 + i]);
+            if (kind[sg.item0 + i] == kinds[q]) padded.push_back(items[sg.item0 + i]);
         }
         while (padded.size() % kItemPad) padded.push_back(none);
         if (level == 0) sg.n_items0 = static_cast<int>(padded.size()) - new0;
       }
       sg.item0 = new0;
       sg.n_items = static_cast<int>(padded.size()) - new0;
+      if (std::getenv("TOWR_B200_DEBUG")) {
+        std::fprintf(stderr, "segment %d kinds (type.sub x count):", static_cast<int>(&sg - hp.segments.data()));
+        int run = 0, last_t = -1, last_s = -1, pos = new0;
+        auto flush = [&]() { if (run) std::fprintf(stderr, " %d.%d x%d", last_t, last_s, run); };
+        for (; pos < static_cast<int>(padded.size()); ++pos) {
+          if (pos == new0 + sg.n_items0) { flush(); run = 0; std::fprintf(stderr, " |"); }
+          const ItemC& c = padded[pos];
+          if (c.type != last_t || c.sub != last_s) { flush(); run = 0; last_t = c.type; last_s = c.sub; }
+          ++run;
+        }
+        flush();
+        std::fprintf(stderr, "\n");
+      }
     }
     items.swap(padded);
   }

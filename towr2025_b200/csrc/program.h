@@ -61,6 +61,7 @@ enum ItemType : int {
   kItemNone = 255,      // padding: keeps every warp of stage A on one item kind
 };
 constexpr int kItemPad = 16;   // items of one kind are padded to a multiple of this (pack.cc)
+constexpr int kItemsPerRound = 256;   // items one stage-A round of the kernel takes (kEntryThreads: NT / P)
 // relative cost of an item kind: lower = longer dependent chain (pack.cc orders the kinds of a level by it)
 inline int ItemCostRank(int type) {
   switch (type) {
@@ -89,6 +90,12 @@ enum { kDynJang = 0, kDynJlin = 36, kDynF = 72 };
 // optimised durations: -f_e[3E], -(c - p_e)[3E] follow the fixed-duration block, then one block per foot (ItemC::aux of
 // the foot's DynFoot item): W_p | W_f | W_tau | finished ee-schedule block [6][P-1]
 TB_PHD inline int DynNegOffset(int E) { return (72 + 9 * E + kDynPreSize) | 1; }
+// classes that declare the curvature block (TerrainCurvatureDims): slot offset, within a Force / Torque item, of the
+// scales S[dim][rows] (f . d b_i / d(dim)); with optimised durations the ee-motion weights W_p follow them.
+// n_w: Hermite-weight slots already there (W_f, or W_tau + W_f), n_sched: ee-schedule columns (0 with fixed durations)
+TB_PHD inline int CurvDimCount(int dims) { return (dims & 1) + ((dims >> 1) & 1); }
+TB_PHD inline int ForceCurvOffset(int n_w, int n_sched) { return 15 + n_w + 5 * n_sched; }
+TB_PHD inline int TorqueCurvOffset(int n_w, int n_sched) { return 15 + n_w + 4 * n_sched; }
 
 constexpr int kMaxEE = 4;
 // indices into ItemRec::s
@@ -188,16 +195,16 @@ struct DeviceProgram {  // pointers into device memory (one copy per GPU)
 };
 
 // ---- shared-memory geometry of the evaluation kernel (eval_kernel.cuh), used by the host-side sizing as well.
-// RING variants stage the products of stage B in a ring of kRingDepth chunks per stream; a chunk holds
-// RingBatchFor(lanes) entries per thread for each lane, each lane's row has 2 spare elements (destination parity).
+// RING variants stage the products of stage B in per-warp rings: kRingDepth slots of kRingBlock = 32 * kRingUB entries
+// per warp and problem lane; each lane's row has 2 spare elements (destination parity).
 constexpr int kRingDepth = 2;
-TB_PHD constexpr int RingBatchFor(int lanes) { return lanes >= 2 ? 2 : 4; }
-TB_PHD inline int RingRow(int lanes) { return RingBatchFor(lanes) * kEntryThreads * lanes + 2; }
+constexpr int kRingUB = 8;
+constexpr int kRingBlock = 32 * kRingUB;
 // doubles one stream of `lanes` problem lanes needs next to the class tables (even: keeps 16-byte alignment)
 TB_PHD inline int StreamDoubles(const DeviceProgram& P, int lanes, bool ring) {
   const int rt = P.blob.rt ? 8 * P.blob.n_polys + P.blob.n_pdur : 0;   // kRtd (device_math.cuh)
   int n = lanes * (P.blob.n_node_values + 6 * P.blob.n_polys + rt + P.g_capacity);
-  if (ring) n += kRingDepth * lanes * RingRow(lanes) + 2;
+  if (ring) n += (kEntryThreads * lanes / 32) * kRingDepth * lanes * (kRingBlock + 2) + 2;
   return (n + 1) & ~1;
 }
 
@@ -244,6 +251,7 @@ struct RowBound { int kind, ee, dim; };
 struct HostProgram {
   int n_vars = 0, n_rows = 0, nnz = 0, n_ee = 0;
   bool optimize_durations = false;
+  int curvature_dims = 0;            // TerrainCurvatureDims of the class: the force / torque ee-motion block is declared for these
   double total_time = 0.0;
   std::vector<VarSet> var_sets;      // NLP column order (base-lin, base-ang, ee-motion.., ee-ang.., ee-force.., ee-torque.., [ee-schedule..])
   std::vector<ConSet> con_sets;

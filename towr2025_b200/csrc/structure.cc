@@ -569,8 +569,12 @@ void Builder::EmitForceDisc(int ee) {
   const VarSet& mo = Set(kEEMotion, ee);
   const VarSet& fo = Set(kEEForce, ee);
   const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_force);
-  // G slots per sample: 15, plus with optimised durations W_f[n_cols] and the finished ee-schedule block [5][P-1]
-  const int per_item = (15 + (rt() ? fo.n_vars + 5 * Set(kEESchedule, ee).n_vars : 0)) | 1;
+  // G slots per sample: 15, plus with optimised durations W_f[n_cols] and the finished ee-schedule block [5][P-1];
+  // classes that declare the curvature block (hp_.curvature_dims): S[dim][5] = f . d b_i / d(dim) after those, and with
+  // optimised durations the ee-motion spline's weights W_p[n_cols] (ForceCurvOffset, program.h)
+  const int nd = CurvDimCount(hp_.curvature_dims);
+  const int off_S = ForceCurvOffset(rt() ? fo.n_vars : 0, rt() ? Set(kEESchedule, ee).n_vars : 0);
+  const int per_item = (off_S + 5 * nd + ((rt() && nd) ? mo.n_vars : 0)) | 1;
   const int chunk = std::max(1, 960 / per_item);    // samples per group
   for (size_t k = 0; k < ts.size(); ++k) {
     if (k % chunk == 0) {
@@ -581,12 +585,22 @@ void Builder::EmitForceDisc(int ee) {
     it.ee = static_cast<short>(ee);
     it.row[0] = set_row0_ + static_cast<int>(k) * 5;
     it.gslot = AllocG(per_item);
+    it.sub = static_cast<short>(hp_.curvature_dims);
     const int bk[5] = {kBoundForceNormal, kBoundLE0, kBoundGE0, kBoundLE0, kBoundGE0};
     for (int i = 0; i < 5; ++i) Bound(static_cast<int>(k) * 5 + i, bk[i], ee);
+    // ee-motion block f . d b_i / d(dim) * J_p(row dim): the reference stores it only where the scale is non-zero
+    // (force_constraint_discretized.cc:52-67,163-183); a class with curvature declares it for every sample (superset),
+    // entries the reference would skip are exact zeros
+    auto dim_slot = [&](int dim) { return dim == 0 ? 0 : (hp_.curvature_dims & 1 ? 1 : 0); };
     if (rt()) {
       it.s[kSMotion + ee] = AtRt(0, ee, ts[k]);
       it.s[kSForce + ee] = AtRt(1, ee, ts[k]);
       hp_.items.push_back(it);
+      for (auto& c : AllCols(mo))
+        if (c.second < 2 && (hp_.curvature_dims >> c.second) & 1)
+          for (int i = 0; i < 5; ++i)
+            Add(static_cast<int>(k) * 5 + i, mo.col0 + c.first,
+                GG(it.gslot + off_S + 5 * dim_slot(c.second) + i, it.gslot + off_S + 5 * nd + c.first));
       for (auto& c : AllCols(fo))
         for (int i = 0; i < 5; ++i)
           Add(static_cast<int>(k) * 5 + i, fo.col0 + c.first, GG(it.gslot + 3 * i + c.second, it.gslot + 15 + c.first));
@@ -602,8 +616,12 @@ void Builder::EmitForceDisc(int ee) {
         Term tm; tm.g = it.gslot + 3 * i + c.dim; tm.b = AddB(c.v[0]);
         Add(static_cast<int>(k) * 5 + i, fo.col0 + c.idx, tm);
       }
-    // the ee-motion block is stored only where the terrain's second derivatives are non-zero
-    // (force_constraint_discretized.cc:58): never for the terrains a curvature-free class admits.
+    for (const ColBasis& c : Columns(mo, am.poly, am.t_local))
+      if (c.dim < 2 && (hp_.curvature_dims >> c.dim) & 1)
+        for (int i = 0; i < 5; ++i) {
+          Term tm; tm.g = it.gslot + off_S + 5 * dim_slot(c.dim) + i; tm.b = AddB(c.v[0]);
+          Add(static_cast<int>(k) * 5 + i, mo.col0 + c.idx, tm);
+        }
   }
   EndSet();
 }
@@ -733,9 +751,13 @@ void Builder::EmitTorqueDisc(int ee) {
   const VarSet& fo = Set(kEEForce, ee);
   const VarSet& to = Set(kEETorque, ee);
   const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_torque);
-  const int per_item = (15 + (rt() ? to.n_vars + fo.n_vars + 4 * Set(kEESchedule, ee).n_vars : 0)) | 1;
+  // curvature classes: S[dim][4] and (optimised durations) W_p[n_cols] after the existing slots, as in EmitForceDisc
+  const int nd = CurvDimCount(hp_.curvature_dims);
+  const int off_S = TorqueCurvOffset(rt() ? to.n_vars + fo.n_vars : 0, rt() ? Set(kEESchedule, ee).n_vars : 0);
+  const int per_item = (off_S + 4 * nd + ((rt() && nd) ? mo.n_vars : 0)) | 1;
   const int chunk = std::max(1, 960 / per_item);
   const int bk_friction = AddB(s_.torque_k_friction);
+  auto dim_slot = [&](int dim) { return dim == 0 ? 0 : (hp_.curvature_dims & 1 ? 1 : 0); };
   for (size_t k = 0; k < ts.size(); ++k) {
     const int r0 = static_cast<int>(k) * 4;
     if (k % chunk == 0) {
@@ -747,6 +769,7 @@ void Builder::EmitTorqueDisc(int ee) {
     it.row[0] = set_row0_ + r0;
     it.gslot = AllocG(per_item);
     it.b0 = bk_friction;
+    it.sub = static_cast<short>(hp_.curvature_dims);
     Bound(r0 + 0, kBoundTorqueX, ee);
     Bound(r0 + 1, kBoundTorqueY, ee);
     Bound(r0 + 2, kBoundLE0, ee);
@@ -762,6 +785,10 @@ void Builder::EmitTorqueDisc(int ee) {
       for (auto& c : AllCols(fo))
         for (int i = 2; i < 4; ++i) Add(r0 + i, fo.col0 + c.first, GG(it.gslot + 12 + c.second, wF + c.first));
       AddScheduleBlock(r0, 4, ee, wF + fo.n_vars);
+      for (auto& c : AllCols(mo))       // torque_constraint_discretized.cc:176-197
+        if (c.second < 2 && (hp_.curvature_dims >> c.second) & 1)
+          for (int i = 0; i < 4; ++i)
+            Add(r0 + i, mo.col0 + c.first, GG(it.gslot + off_S + 4 * dim_slot(c.second) + i, it.gslot + off_S + 4 * nd + c.first));
       continue;
     }
     SplineAt am = At(mo, ts[k]), af = At(fo, ts[k]), at = At(to, ts[k]);
@@ -779,6 +806,12 @@ void Builder::EmitTorqueDisc(int ee) {
         Term tm; tm.g = it.gslot + 12 + c.dim; tm.b = AddB(c.v[0]);
         Add(r0 + i, fo.col0 + c.idx, tm);
       }
+    for (const ColBasis& c : Columns(mo, am.poly, am.t_local))
+      if (c.dim < 2 && (hp_.curvature_dims >> c.dim) & 1)
+        for (int i = 0; i < 4; ++i) {
+          Term tm; tm.g = it.gslot + off_S + 4 * dim_slot(c.dim) + i; tm.b = AddB(c.v[0]);
+          Add(r0 + i, mo.col0 + c.idx, tm);
+        }
   }
   EndSet();
 }
@@ -897,11 +930,11 @@ void ResetTables(HostProgram& hp) {
 
 }  // namespace
 
-std::string StructureSignature(const towr_b200_spec& s) {
+std::string StructureSignature(const towr_b200_spec& s, int curvature_dims) {
   // every field the tables above depend on, printed exactly
   std::ostringstream o;
   o.precision(17);
-  o << "E" << s.n_ee;
+  o << "E" << s.n_ee << "|curv" << curvature_dims;
   for (int e = 0; e < s.n_ee; ++e) {
     o << "|f" << e << ":" << s.in_contact_at_start[e] << ":";
     for (int i = 0; i < s.n_phases[e]; ++i) o << s.phase_durations[e][i] << ",";
@@ -920,7 +953,7 @@ std::string StructureSignature(const towr_b200_spec& s) {
 
 void BuildProgram(const towr_b200_spec& s, HostProgram& hp, int g_cap) {
   BuildLayout(s, hp);
-  hp.signature = StructureSignature(s);
+  hp.signature = StructureSignature(s, hp.curvature_dims);
   // pass 1: one segment per group, to learn each group's G footprint
   ResetTables(hp);
   const int rom_fpg = 0;

@@ -24,7 +24,9 @@ int SegmentId(double t_global, const std::vector<double>& durations);
 double LocalTime(double t_global, int id, const std::vector<double>& durations);
 // g_cap > 0 overrides the G slots per segment (the batch lowers it when a class's tables leave less shared memory)
 void BuildProgram(const towr_b200_spec& s, HostProgram& hp, int g_cap = 0);
-std::string StructureSignature(const towr_b200_spec& s);
+// curvature_dims: the class's TerrainCurvatureDims (a problem on a curvature-free terrain may join a class that declares
+// the curvature block; it then writes explicit zeros there)
+std::string StructureSignature(const towr_b200_spec& s, int curvature_dims);
 
 // pack.cc
 void PackProgram(HostProgram& hp);

@@ -90,6 +90,11 @@ TB_HD TerrainSample EvalTerrain(int id, double x, double y) {
   return s;
 }
 
+// Dimensions (bit 0: x, bit 1: y) in which the terrain's SECOND derivatives can be non-zero.  Only then does the reference
+// store the force / torque constraint's ee-motion block (force_constraint_discretized.cc:52-67 skips scale == 0.0): a
+// structure class built for such a terrain declares that block (superset pattern, structure.cc).
+TB_HD int TerrainCurvatureDims(int id) { return id == 3 ? 1 : 0; }   // Gap: h_xx != 0 over the parabola
+
 // normalised normal / tangents at (x,y): n = (-hx,-hy,1)/|.|, t1 = (1,0,hx)/|.|, t2 = (0,1,hy)/|.|
 // v.normalized() = v / sqrt(v.v) with the squared norm summed left to right
 TB_HD void Normalize3(const double v[3], double out[3]) {
