@@ -55,7 +55,10 @@ enum { TOWR_B200_FLAT = 0, TOWR_B200_BLOCK, TOWR_B200_STAIRS, TOWR_B200_GAP, TOW
 /* towr::Parameters::CostName, include/towr/parameters.h:157-161 */
 enum { TOWR_B200_COST_FORCES = 0, TOWR_B200_COST_EE_MOTION = 1, TOWR_B200_COST_ENERGY = 2, TOWR_B200_COST_ANG_MOM = 3 };
 /* what to evaluate */
-enum { TOWR_B200_EVAL_G = 1, TOWR_B200_EVAL_JAC = 2, TOWR_B200_EVAL_BOTH = 3 };
+enum { TOWR_B200_EVAL_G = 1, TOWR_B200_EVAL_JAC = 2, TOWR_B200_EVAL_BOTH = 3,
+       /* host-buffer interface only: like EVAL_JAC, but jac_values_out receives n x n_dynamic values - the stored entries
+        * that depend on x, in the order of towr_b200_batch_dynamic_index - instead of n x nnz (towr_b200_batch_dynamic_index below) */
+       TOWR_B200_EVAL_JAC_DYNAMIC = 4 };
 
 /* One NlpFormulation: the six public members of towr::NlpFormulation plus the Parameters fields
  * the path reads.  Same meaning as the reference fields of the same name. */
@@ -142,8 +145,10 @@ int towr_b200_batch_set_problem(towr_b200_batch* b, int i, const towr_b200_spec*
 int towr_b200_batch_set_all_problems(towr_b200_batch* b, const towr_b200_spec* s);
 
 /* Host-buffer evaluation (what an Ipopt callback sees).  problem_ids may be NULL (= 0..n-1).
- * x: n x n_vars row-major.  g_out: n x n_rows, jac_values_out: n x nnz; each may be NULL when
- * `what` does not ask for it.  Copies H2D, launches, copies D2H, synchronises. */
+ * x: n x n_vars row-major.  g_out: n x n_rows, jac_values_out: n x nnz (n x n_dynamic with
+ * TOWR_B200_EVAL_JAC_DYNAMIC); each may be NULL when `what` does not ask for it.  Copies H2D, launches, copies D2H,
+ * synchronises; large batches go through in chunks on two streams so that one chunk's D2H overlaps the next chunk's
+ * H2D and kernel. */
 int towr_b200_batch_eval(towr_b200_batch* b, const int* problem_ids, int n, int what, const double* x,
                          double* g_out, double* jac_values_out);
 /* Device-buffer evaluation of problems 0..n-1: pointers are device memory on the batch's GPU,
@@ -151,6 +156,24 @@ int towr_b200_batch_eval(towr_b200_batch* b, const int* problem_ids, int n, int 
  * on `stream` only. */
 int towr_b200_batch_eval_device(towr_b200_batch* b, int n, int what, const double* d_x, double* d_g,
                                 double* d_jac_values, void* stream);
+/* Entries of the Jacobian that depend on x.  The other stored values are constants of a problem: Hermite basis values,
+ * +-1, the mass times a basis value (what the reference recomputes in every FillJacobianBlock, e.g.
+ * src/constraints/spline_acc_constraint.cc:66-80, swing_constraint.cc:86-108, the linear rows of
+ * single_rigid_body_dynamics.cc:104-122) and, when EVERY problem of the batch is on a terrain without slope (Flat,
+ * Stairs, FiveStepStairs), the terrain-basis entries of the force / torque / terrain constraints as well
+ * (force_constraint_discretized.cc:146-152: b_i . J_f with constant b_i).  ANYmal trot on flat ground: 49 % of the
+ * entries.  A caller on the host interface fetches them once per problem (towr_b200_batch_constant_values) and asks
+ * every eval for the dynamic ones only (TOWR_B200_EVAL_JAC_DYNAMIC): that is what crosses PCIe;
+ * towr_b200_batch_scatter_dynamic merges them into full n x nnz arrays.  The index depends on the terrains of the
+ * batch's problems: query it after the last towr_b200_batch_set_problem. */
+int towr_b200_batch_n_dynamic(const towr_b200_batch* b);
+/* ascending storage positions (indices into the nnz stored entries) of the dynamic entries; n_dynamic ints */
+int towr_b200_batch_dynamic_index(const towr_b200_batch* b, int* index);
+/* values[nnz]: the constant entries of problem i, 0.0 at the dynamic positions (host, set-up only) */
+int towr_b200_batch_constant_values(const towr_b200_batch* b, int i, double* values);
+/* values[p * nnz + index[k]] = dynamic[p * n_dynamic + k] for p < n, on n_threads host threads (<= 0: all cores); the
+ * constant positions of `values` are left as they are */
+int towr_b200_batch_scatter_dynamic(const towr_b200_batch* b, int n, const double* dynamic, double* values, int n_threads);
 /* per-problem status of the last eval: bit 0 = non-finite value in g, bit 1 = non-finite Jacobian value */
 int towr_b200_batch_status(towr_b200_batch* b, int n, int* status_out);
 /* kernel launches issued by this batch so far (for bench.py's gpu_launches) */

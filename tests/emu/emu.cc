@@ -26,12 +26,12 @@ static std::string g_err;
 extern "C" const char* emu_last_error() { return g_err.c_str(); }
 
 // x: n_vars; g: n_rows; vals: nnz.  Mirrors the kernel's stages for one problem (P = 1).
-template <bool RT>
+template <bool RT, bool CURV>
 static void EmuEval(const HostProgram& hp, const towr_b200_spec* s, const double* x, double* g, double* vals) {
   const BlobLayout& L = hp.blob;
   ProblemConst pc;
   FillProblemConst(*s, pc);
-  ItemCtx<Lockstep<1, RT>> cx;
+  ItemCtx<Lockstep<1, RT, CURV>> cx;
   cx.T = MakeTables(hp.blob_data.data(), L);
   cx.n_ee = hp.n_ee;
   std::vector<double> nodes(L.n_node_values), coef(6 * L.n_polys), G(hp.g_capacity), rtd(kRtd * L.n_polys), pdur(L.n_pdur + 1);
@@ -91,7 +91,7 @@ static void EmuEval(const HostProgram& hp, const towr_b200_spec* s, const double
   for (const SegmentRec& sg : hp.segments) {
     std::fill(G.begin(), G.end(), std::nan(""));
     G[kGOne] = 1.0; G[kGMass] = pc.mass; G[kGMinusOne] = -1.0;
-    for (int i = 0; i < sg.n_items; ++i) RunItem<Lockstep<1, RT>>(cx, cx.T.items[sg.item0 + i]);   // level-0 items come first
+    for (int i = 0; i < sg.n_items; ++i) RunItem<Lockstep<1, RT, CURV>>(cx, cx.T.items[sg.item0 + i]);   // level-0 items come first
     // the device descriptors, as the kernel's stage B reads them
     for (int e = 0; e < sg.n_entries; ++e) {
       const uint32_t w = hp.entries_dev[sg.entry0 + e];
@@ -105,8 +105,9 @@ extern "C" int emu_eval(const towr_b200_spec* s, const double* x, double* g, dou
   try {
     HostProgram hp;
     BuildProgram(*s, hp);
-    if (hp.optimize_durations) EmuEval<true>(hp, s, x, g, vals);
-    else EmuEval<false>(hp, s, x, g, vals);
+    const bool curv = hp.curvature_dims != 0;
+    if (hp.optimize_durations) { if (curv) EmuEval<true, true>(hp, s, x, g, vals); else EmuEval<true, false>(hp, s, x, g, vals); }
+    else { if (curv) EmuEval<false, true>(hp, s, x, g, vals); else EmuEval<false, false>(hp, s, x, g, vals); }
     return 0;
   } catch (const std::exception& e) {
     g_err = e.what();

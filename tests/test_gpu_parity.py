@@ -3,7 +3,7 @@ Tolerance (BASELINE.json north_star): sparsity indices bit-exact, values within 
 import numpy as np
 import pytest
 
-from util import CASES, GAP_CASES, is_rt, mk, parity_ok, perturbed, regrouped_mask, superset_parity, tol_ratio
+from util import CASES, GAP_CASES, check_against_oracle, is_rt, mk, perturbed, tol_ratio
 
 pytestmark = pytest.mark.gpu
 
@@ -35,13 +35,8 @@ def test_values_and_jacobian_match_oracle(product, oracle, case):
         b.set_problem(i, s)
     g, v = b.eval(x)
     assert (b.status() == 0).all()
-    rows, cols = st.pattern()
     for i, s in enumerate(specs):
-        p = O.Problem(to_oracle_spec(O, s))
-        r, c, vo = p.eval_jac(x[i])
-        assert np.array_equal(r, rows) and np.array_equal(c, cols)
-        assert parity_ok(g[i], p.eval_g(x[i]))
-        assert parity_ok(v[i], vo, regrouped_mask(st))
+        check_against_oracle(O, to_oracle_spec(O, s), st, x[i], g[i], v[i], is_rt(case))
 
 
 @pytest.mark.parametrize("case", GAP_CASES, ids=[c[0] for c in GAP_CASES])
@@ -59,9 +54,7 @@ def test_gap_superset_pattern_matches_oracle(product, oracle, case):
     assert (b.status() == 0).all()
     extras = set()
     for i, s in enumerate(specs):
-        p = O.Problem(to_oracle_spec(O, s))
-        assert parity_ok(g[i], p.eval_g(x[i]))
-        extras.add(superset_parity(st, p.eval_jac(x[i]), v[i], regrouped_mask(st)))
+        extras.add(check_against_oracle(O, to_oracle_spec(O, s), st, x[i], g[i], v[i], is_rt(case), superset=True))
     assert len(extras) > 1
 
 
@@ -87,12 +80,9 @@ def test_mixed_terrain_batch_block_gap_stairs(product, oracle, optimise):
         b.set_problem(i, s)
     g, v = b.eval(x)
     assert (b.status() == 0).all()
-    mask = regrouped_mask(st)
     n_extra = []
     for i, s in enumerate(specs):
-        p = O.Problem(to_oracle_spec(O, s))
-        assert parity_ok(g[i], p.eval_g(x[i]))
-        n_extra.append(superset_parity(st, p.eval_jac(x[i]), v[i], mask))
+        n_extra.append(check_against_oracle(O, to_oracle_spec(O, s), st, x[i], g[i], v[i], optimise, superset=True))
     # Block / Stairs: the whole declared curvature block is extra (never stored by the reference); Gap: part of it
     assert n_extra[0] == n_extra[2] and n_extra[1] < n_extra[0]
 
@@ -112,6 +102,41 @@ def test_eval_modes_and_ids(product, oracle):
     gs, vs = b.eval(x[ids], ids=ids)
     assert np.array_equal(gs, g[ids]) and np.array_equal(vs, v[ids])
     assert b.launches == 4
+
+
+@pytest.mark.parametrize("name", ["anymal_trot", "anymal_trot_durations", "monoped_hop_torque", "anymal_walk_slope",
+                                  "anymal_trot_force_nodes_slope", "biped_walk_stairs"])
+def test_dynamic_only_mode_equals_full_mode(product, name):
+    """TOWR_B200_EVAL_JAC_DYNAMIC: constants once (towr_b200_problem_constant_values) + the dynamic entries of every eval,
+    scattered on the host, are bit-identical to the full n x nnz result; chunked evals equal unchunked ones."""
+    import os
+    T = product
+    case = [c for c in CASES if c[0] == name][0]
+    n = 37
+    st, specs, x = _problem_batch(T, None, case, n, 9)
+    b = T.Batch(st, n)
+    for i, s in enumerate(specs):
+        b.set_problem(i, s)
+    g, v = b.eval(x)
+    idx = b.dynamic_index()
+    assert 0 < b.n_dynamic < st.nnz and (np.diff(idx) > 0).all()
+    if name == "anymal_trot":                     # flat ground: the force constraint's basis entries are constants too
+        assert b.n_dynamic < 0.55 * st.nnz
+    g2, dyn = b.eval(x, T.EVAL_G | T.EVAL_JAC_DYNAMIC)
+    assert np.array_equal(g2, g) and dyn.shape == (n, b.n_dynamic)
+    full = np.stack([b.constant_values(i) for i in range(n)])
+    const_mask = np.ones(st.nnz, bool)
+    const_mask[idx] = False
+    assert np.array_equal(full[:, const_mask], v[:, const_mask])      # the constants are what the kernel stores
+    b.scatter_dynamic(dyn, full, n_threads=3)
+    assert np.array_equal(full, v)
+    os.environ["TOWR_B200_CHUNK"] = "8"                                 # 5 chunks, alternating streams, ragged last one
+    try:
+        g3, v3 = b.eval(x)
+        _, dyn3 = b.eval(x, T.EVAL_JAC_DYNAMIC)
+    finally:
+        del os.environ["TOWR_B200_CHUNK"]
+    assert np.array_equal(g3, g) and np.array_equal(v3, v) and np.array_equal(dyn3, dyn)
 
 
 def test_full_batch_properties(product, oracle):

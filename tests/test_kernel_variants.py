@@ -1,5 +1,6 @@
-"""The kernel variants (TOWR_B200_KERNEL = lockstep | ring | streams | streamsring) compute the same
-products as each other: values and g must be bit-identical on the same inputs, including a short last problem group."""
+"""The experimental kernel variants (TOWR_B200_KERNEL = ring | streams | streamsring; built only by
+`make -C towr2025_b200/csrc EXPERIMENTS=1` into libtowr_b200_experiments.so, because they measured slower than the default
+lock-step kernel) compute the same products as the default kernel: values and g must be bit-identical on the same inputs, including a short last problem group."""
 import os
 
 import numpy as np
@@ -49,7 +50,7 @@ def test_variant_matches_default_kernel(product, kernel, name):
     assert np.array_equal(v0, v1)
 
 
-@pytest.mark.parametrize("kernel", ["ring", "streamsring"])
+@pytest.mark.parametrize("kernel", ["streamsring"])
 def test_ring_variants_with_optimised_durations(product, kernel):
     T = product
     case = [c for c in CASES if c[0] == "biped_walk_durations"][0]
@@ -57,5 +58,10 @@ def test_ring_variants_with_optimised_durations(product, kernel):
     st = T.Structure(s)
     x = np.stack([perturbed(st.x0(s), 700 + i, 0.02) for i in range(9)])
     g0, v0 = _eval_with(T, "lockstep", st, s, x)
-    g1, v1 = _eval_with(T, kernel, st, s, x)
+    try:
+        g1, v1 = _eval_with(T, kernel, st, s, x)
+    except T.TowrB200Error as e:
+        if e.code == -2:
+            pytest.skip("variant not built or does not fit this class: " + str(e))
+        raise
     assert np.array_equal(g0, g1) and np.array_equal(v0, v1)

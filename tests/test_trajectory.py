@@ -5,7 +5,7 @@ import os
 import numpy as np
 import pytest
 
-from util import CASES, is_rt, mk, parity_ok, perturbed, to_oracle_spec
+from util import CASES, is_rt, mk, parity_ok, perturbed, pow_ok, to_oracle_spec
 
 TRAJ_CASES = [c for c in CASES if c[0] in ("anymal_trot", "hyq_gallop_block", "biped_walk_stairs", "monoped_hop_torque",
                                            "biped_walk_durations", "anymal_trot_durations", "monoped_hop_stairs_durations")]
@@ -84,12 +84,18 @@ def test_gpu_trajectory_matches_oracle(product, oracle, case):
     for dt in (0.01, 0.037):
         rows = b.sample_trajectory(x, dt)
         for i, s in enumerate(specs):
-            ref = O.Problem(to_oracle_spec(O, s)).sample_trajectory(x[i], dt)
+            po = O.Problem(to_oracle_spec(O, s))
+            ref = po.sample_trajectory(x[i], dt)
             assert rows[i].shape == ref.shape
             assert np.array_equal(rows[i][:, 0], ref[:, 0])                       # sample times: bit-exact
             cc = [19 + 25 * e + 24 for e in range((st.trajectory_width() - 19) // 25)]
             assert np.array_equal(rows[i][:, cc], ref[:, cc])                     # is_contact: exact
-            assert parity_ok(rows[i], ref)
+            if is_rt(case):          # strict against the exact-power oracle, pow_ok against std::pow (tests/util.py)
+                with O.pow_mode(1):
+                    assert parity_ok(rows[i], po.sample_trajectory(x[i], dt))
+                assert pow_ok(rows[i], ref)
+            else:
+                assert parity_ok(rows[i], ref)
 
 
 @pytest.mark.gpu

@@ -66,7 +66,7 @@ GAP_CASES = [
 ]
 
 
-def superset_parity(st, oracle_rcv, v, mask=None):
+def superset_parity(st, oracle_rcv, v, mask=None, cmp=None):
     """The oracle's stored entries (rows, cols, values at this x) must all be in the class's pattern with equal values
     (parity_ok); the entries the oracle did not store at this x must be exact zeros.  Returns the number of extras."""
     r, c, vo = oracle_rcv
@@ -78,7 +78,7 @@ def superset_parity(st, oracle_rcv, v, mask=None):
     extra = np.ones(st.nnz, bool)
     extra[pos] = False
     assert not np.any(v[extra] != 0.0), "an entry the reference does not store is not an exact zero"
-    assert parity_ok(v[pos], vo, None if mask is None else mask[pos])
+    assert (cmp or parity_ok)(v[pos], vo, None if mask is None else mask[pos])
     return int(extra.sum())
 
 
@@ -122,6 +122,49 @@ def parity_ok(a, b, mask=None):
     if mask is None:
         return bool(ratio.max() <= 1.0)
     return bool((ratio[~mask] <= 1.0).all() and (ratio[mask] <= REGROUPED_BAND).all())
+
+
+POW_BAND, POW_FRACTION = 10.0, 5e-3
+
+
+def pow_ok(a, b, mask=None):
+    """Optimised durations against the oracle in its DEFAULT mode (std::pow, the reference's arithmetic): the device's
+    t^3, T^3, T^4 are correctly rounded, glibc's pow is not for ~0.1 % of arguments, and where a spline value cancels
+    (a contact force of 0.0016 N made of terms of order 100) that one ulp shows as a few 1e-14 absolute (one affected
+    spline sample touches all rows / columns of that sample: 5 of 2736 g rows in one measured case).  Allowed: at
+    most POW_FRACTION of the entries outside the strict band, none beyond POW_BAND x it.  Everything else about the path
+    is held to the strict band by the comparison with the oracle's exact-power mode (check_against_oracle)."""
+    a, b = np.asarray(a), np.asarray(b)
+    assert a.shape == b.shape and np.isfinite(a).all() and np.isfinite(b).all()
+    if a.size == 0:
+        return True
+    ratio = np.abs(a - b) / (ATOL + RTOL * np.abs(b))
+    lim = np.where(mask, max(REGROUPED_BAND, POW_BAND), POW_BAND) if mask is not None else POW_BAND
+    out = ratio > (np.where(mask, REGROUPED_BAND, 1.0) if mask is not None else 1.0)
+    return bool((ratio <= lim).all() and out.mean() <= POW_FRACTION)
+
+
+def check_against_oracle(O, ospec, st, x, g, v, rt, superset=False):
+    """g and the Jacobian values of one problem against the oracle.  Fixed durations: strict band (parity_ok).  Optimised
+    durations: strict band against the oracle with correctly rounded powers (O.pow_mode(1)) AND pow_ok against the
+    oracle's default std::pow mode.  superset: Gap classes (superset_parity).  Returns the number of extra entries."""
+    mask = regrouped_mask(st)
+    p = O.Problem(ospec)
+    rows, cols = st.pattern()
+    extras = 0
+    for mode in ((1, 0) if rt else (0,)):
+        with O.pow_mode(mode):
+            go = p.eval_g(x)
+            r, c, vo = p.eval_jac(x)
+        strict = (mode == 1) or not rt
+        cmp = parity_ok if strict else pow_ok
+        assert cmp(g, go), "g, oracle pow mode %d" % mode
+        if superset:
+            extras = superset_parity(st, (r, c, vo), v, mask, cmp)
+        else:
+            assert np.array_equal(r, rows) and np.array_equal(c, cols)
+            assert cmp(v, vo, mask), "Jacobian values, oracle pow mode %d" % mode
+    return extras
 
 
 def mk(M, case, goal=None):

@@ -21,7 +21,7 @@ MAX_EE, MAX_PHASES, MAX_CONSTRAINTS = 4, 32, 16
 Dynamic, EndeffectorRom, TotalTime, Terrain, TerrainHard, Force, Torque, Swing, BaseRom, BaseAcc, BaseHeight = range(11)
 Monoped, Biped, Hyq, Anymal = range(4)
 FlatID, BlockID, StairsID, GapID, SlopeID, ChimneyID, ChimneyLRID, FiveStepStairsID = range(8)
-EVAL_G, EVAL_JAC, EVAL_BOTH = 1, 2, 3
+EVAL_G, EVAL_JAC, EVAL_BOTH, EVAL_JAC_DYNAMIC = 1, 2, 3, 4
 C0, C1, C2, C3, C4 = range(5)
 
 
@@ -96,7 +96,8 @@ towr_b200_batch_destroy towr_b200_batch_size towr_b200_batch_set_problem towr_b2
 towr_b200_batch_eval towr_b200_batch_eval_device towr_b200_batch_status towr_b200_batch_launch_count
 towr_b200_batch_stream towr_b200_trajectory_width towr_b200_trajectory_samples towr_b200_batch_sample_trajectory
 towr_b200_batch_sample_trajectory_device towr_b200_trajectory_write_csv towr_b200_batch_eval_cost
-towr_b200_batch_eval_cost_device towr_b200_eval_cost_static""".split()
+towr_b200_batch_eval_cost_device towr_b200_eval_cost_static towr_b200_batch_n_dynamic
+towr_b200_batch_dynamic_index towr_b200_batch_constant_values towr_b200_batch_scatter_dynamic""".split()
 
 
 def lib():
@@ -125,6 +126,10 @@ def lib():
     for f in ("var_set_rows", "con_set_rows"):
         getattr(L, "towr_b200_structure_" + f).argtypes = [vp, C.c_int]
     L.towr_b200_structure_pattern.argtypes = [vp, ip, ip]
+    L.towr_b200_batch_n_dynamic.argtypes = [vp]
+    L.towr_b200_batch_dynamic_index.argtypes = [vp, ip]
+    L.towr_b200_batch_constant_values.argtypes = [vp, C.c_int, dp]
+    L.towr_b200_batch_scatter_dynamic.argtypes = [vp, C.c_int, dp, dp, C.c_int]
     L.towr_b200_structure_accepts.argtypes = [vp, sp]
     L.towr_b200_problem_x0.argtypes = [vp, sp, dp]
     L.towr_b200_problem_var_bounds.argtypes = [vp, sp, dp, dp]
@@ -295,7 +300,11 @@ class Batch:
         st = self.structure
         assert x.shape[1] == st.n_vars
         g = (g_out if g_out is not None else np.empty((n, st.n_rows))) if what & EVAL_G else None
-        v = (jac_out if jac_out is not None else np.empty((n, st.nnz))) if what & EVAL_JAC else None
+        v = None
+        if what & EVAL_JAC:
+            v = jac_out if jac_out is not None else np.empty((n, st.nnz))
+        elif what & EVAL_JAC_DYNAMIC:           # the x-dependent entries only, n x n_dynamic
+            v = jac_out if jac_out is not None else np.empty((n, self.n_dynamic))
         idp = None
         if ids is not None:
             ids = np.ascontiguousarray(ids, dtype=np.int32)
@@ -330,6 +339,28 @@ class Batch:
         (a cudaStream_t as int; None/0 = CUDA's default stream)."""
         _check(self._L.towr_b200_batch_eval_device(self._h, n, what, C.c_void_p(d_x), C.c_void_p(d_g or 0),
                                                     C.c_void_p(d_vals or 0), C.c_void_p(stream or 0)))
+
+    @property
+    def n_dynamic(self):
+        """Stored Jacobian entries that depend on x for this batch (towr_b200_batch_n_dynamic)."""
+        return self._L.towr_b200_batch_n_dynamic(self._h)
+
+    def dynamic_index(self):
+        idx = np.empty(self.n_dynamic, np.int32)
+        _check(self._L.towr_b200_batch_dynamic_index(self._h, _ip(idx)))
+        return idx
+
+    def constant_values(self, i):
+        """nnz values: the x-independent entries of problem i, 0.0 at the dynamic positions."""
+        v = np.empty(self.structure.nnz)
+        _check(self._L.towr_b200_batch_constant_values(self._h, i, _dp(v)))
+        return v
+
+    def scatter_dynamic(self, dynamic, values, n_threads=0):
+        """values[p, dynamic_index] = dynamic[p] for every problem row (towr_b200_scatter_dynamic), in place."""
+        assert dynamic.flags.c_contiguous and values.flags.c_contiguous and dynamic.shape[0] == values.shape[0]
+        assert dynamic.shape[1] == self.n_dynamic and values.shape[1] == self.structure.nnz
+        _check(self._L.towr_b200_batch_scatter_dynamic(self._h, dynamic.shape[0], _dp(dynamic), _dp(values), n_threads))
 
     def status(self, n=None):
         n = self.n if n is None else n

@@ -12,6 +12,7 @@
 #include <memory>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <type_traits>
 #include <vector>
 
@@ -80,7 +81,8 @@ T* Upload(const std::vector<T>& v) {
 struct towr_b200_batch {
   const towr_b200_structure* st = nullptr;
   int n = 0, device = 0;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr, stream2 = nullptr;   // host-buffer evals alternate their chunks between the two
+  cudaEvent_t consts_ready = nullptr;
   tb::DeviceProgram dp{};
   std::vector<void*> owned;            // device allocations
   std::vector<tb::ProblemConst> pc_host;
@@ -88,7 +90,9 @@ struct towr_b200_batch {
   bool pc_dirty = true;
   int* status_dev = nullptr;
   // staging for the host-buffer path
-  double *x_dev = nullptr, *g_dev = nullptr, *v_dev = nullptr;
+  double *x_dev = nullptr, *g_dev = nullptr, *v_dev = nullptr, *dyn_dev = nullptr;
+  int* dyn_idx_dev = nullptr;
+  int n_dynamic = 0;
   tb::ProblemConst* pc_gather_dev = nullptr;
   int max_ctas = 0;
   tb::EvalVariant var{0, 1, false, 0};   // kernel variant (kernels.h); lanes = 0 until chosen
@@ -112,6 +116,8 @@ struct towr_b200_batch {
   ~towr_b200_batch() {
     cudaSetDevice(device);
     for (void* p : owned) cudaFree(p);
+    if (consts_ready) cudaEventDestroy(consts_ready);
+    if (stream2) cudaStreamDestroy(stream2);
     if (stream) cudaStreamDestroy(stream);
   }
 };
@@ -210,6 +216,8 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     b->n = n_problems;
     b->device = device;
     Check(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+    Check(cudaStreamCreateWithFlags(&b->stream2, cudaStreamNonBlocking), "cudaStreamCreate");
+    Check(cudaEventCreateWithFlags(&b->consts_ready, cudaEventDisableTiming), "cudaEventCreate");
     cudaDeviceProp prop;
     Check(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
     // The class tables, one problem's spline arrays and one G buffer must fit the SM's shared memory.  Classes with many
@@ -270,6 +278,7 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     dp.n_segments = static_cast<int>(hp.segments.size());
     dp.total_time = hp.total_time;
     dp.g_capacity = hp.g_capacity;
+    dp.curvature_dims = hp.curvature_dims;
     dp.blob = hp.blob;
     auto keep = [&](auto* p) { b->owned.push_back(const_cast<void*>(static_cast<const void*>(p))); return p; };
     dp.blob_data = keep(Upload(hp.blob_data));
@@ -330,6 +339,67 @@ int towr_b200_batch_set_all_problems(towr_b200_batch* b, const towr_b200_spec* s
   });
 }
 
+}  // extern "C"
+namespace {
+// every problem of the batch on a terrain without slope: the terrain basis is a constant too
+bool FlatBasis(const towr_b200_batch* b) {
+  for (const tb::ProblemConst& pc : b->pc_host)
+    if (tb::TerrainHasSlope(pc.terrain_id)) return false;
+  return true;
+}
+const std::vector<int>& DynIndex(const towr_b200_batch* b) {
+  const tb::HostProgram& hp = b->st->hp;
+  return FlatBasis(b) ? hp.dyn_index_flat : hp.dyn_index;
+}
+}  // namespace
+extern "C" {
+
+int towr_b200_batch_n_dynamic(const towr_b200_batch* b) { return b ? static_cast<int>(DynIndex(b).size()) : -1; }
+int towr_b200_batch_dynamic_index(const towr_b200_batch* b, int* index) {
+  return Guard([&] {
+    if (!b || !index) throw std::runtime_error("null argument");
+    const std::vector<int>& idx = DynIndex(b);
+    std::memcpy(index, idx.data(), sizeof(int) * idx.size());
+  });
+}
+int towr_b200_batch_constant_values(const towr_b200_batch* b, int i, double* values) {
+  return Guard([&] {
+    if (!b || i < 0 || i >= b->n || !values) throw std::runtime_error("bad argument to batch_constant_values");
+    tb::ProblemConstantValues(b->st->hp, b->pc_host[i].mass, b->st->spec.torque_k_friction, FlatBasis(b), values);
+  });
+}
+int towr_b200_batch_scatter_dynamic(const towr_b200_batch* b, int n, const double* dynamic, double* values, int n_threads) {
+  return Guard([&] {
+    if (!b || n < 0 || n > b->n || !dynamic || !values) throw std::runtime_error("bad argument to scatter_dynamic");
+    const std::vector<int>& idx = DynIndex(b);
+    const size_t nd = idx.size(), nnz = static_cast<size_t>(b->st->hp.nnz);
+    // runs of consecutive dynamic entries: one memcpy each
+    struct Run { int dst, src, len; };
+    std::vector<Run> runs;
+    for (size_t k = 0; k < nd;) {
+      size_t e = k + 1;
+      while (e < nd && idx[e] == idx[e - 1] + 1) ++e;
+      runs.push_back(Run{idx[k], static_cast<int>(k), static_cast<int>(e - k)});
+      k = e;
+    }
+    auto work = [&](int p0, int p1) {
+      for (int p = p0; p < p1; ++p) {
+        const double* src = dynamic + static_cast<size_t>(p) * nd;
+        double* dst = values + static_cast<size_t>(p) * nnz;
+        for (const Run& r : runs) std::memcpy(dst + r.dst, src + r.src, sizeof(double) * static_cast<size_t>(r.len));
+      }
+    };
+    int nt = n_threads > 0 ? n_threads : static_cast<int>(std::thread::hardware_concurrency());
+    if (nt < 1) nt = 1;
+    if (nt > n) nt = n > 0 ? n : 1;
+    if (nt == 1) { work(0, n); return; }
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nt; ++t)
+      pool.emplace_back(work, static_cast<int>(static_cast<long long>(n) * t / nt), static_cast<int>(static_cast<long long>(n) * (t + 1) / nt));
+    for (auto& th : pool) th.join();
+  });
+}
+
 int towr_b200_batch_eval_device(towr_b200_batch* b, int n, int what, const double* d_x, double* d_g,
                                 double* d_jac_values, void* stream) {
   return Guard([&] {
@@ -352,12 +422,15 @@ int towr_b200_batch_eval(towr_b200_batch* b, const int* ids, int n, int what, co
                          double* jac_out) {
   return Guard([&] {
     if (!b || n < 0 || n > b->n) throw std::runtime_error("bad problem count");
-    if (what < 1 || what > 3) throw std::runtime_error("what must be EVAL_G, EVAL_JAC or EVAL_BOTH");
-    if (!x || ((what & TOWR_B200_EVAL_G) && !g_out) || ((what & TOWR_B200_EVAL_JAC) && !jac_out))
-      throw std::runtime_error("null host buffer");
+    const bool want_g = (what & TOWR_B200_EVAL_G) != 0, want_jac = (what & TOWR_B200_EVAL_JAC) != 0;
+    const bool want_dyn = (what & TOWR_B200_EVAL_JAC_DYNAMIC) != 0;
+    if (what < 1 || what > 5 || (want_jac && want_dyn))
+      throw std::runtime_error("what must be EVAL_G, EVAL_JAC, EVAL_BOTH or EVAL_JAC_DYNAMIC [| EVAL_G]");
+    if (!x || (want_g && !g_out) || ((want_jac || want_dyn) && !jac_out)) throw std::runtime_error("null host buffer");
     if (n == 0) return;
     Check(cudaSetDevice(b->device), "cudaSetDevice");
     const tb::DeviceProgram& dp = b->dp;
+    const int kernel_what = (want_g ? TOWR_B200_EVAL_G : 0) | ((want_jac || want_dyn) ? TOWR_B200_EVAL_JAC : 0);
     auto ensure = [&](auto*& p, size_t per) {
       if (!p) {
         Check(cudaMalloc(&p, sizeof(*p) * per * b->n), "cudaMalloc(staging)");
@@ -365,8 +438,21 @@ int towr_b200_batch_eval(towr_b200_batch* b, const int* ids, int n, int what, co
       }
     };
     ensure(b->x_dev, dp.n_vars);
-    if (what & TOWR_B200_EVAL_G) ensure(b->g_dev, dp.n_rows);
-    if (what & TOWR_B200_EVAL_JAC) ensure(b->v_dev, dp.nnz);
+    if (want_g) ensure(b->g_dev, dp.n_rows);
+    if (want_jac || want_dyn) ensure(b->v_dev, dp.nnz);
+    const std::vector<int>& dyn_index = DynIndex(b);
+    const size_t nd = dyn_index.size();
+    if (want_dyn && nd > 0) {
+      ensure(b->dyn_dev, b->st->hp.dyn_index.size());          // sized for the general index (>= the flat one)
+      if (!b->dyn_idx_dev) {
+        Check(cudaMalloc(&b->dyn_idx_dev, sizeof(int) * b->st->hp.dyn_index.size()), "cudaMalloc(dynamic index)");
+        b->owned.push_back(b->dyn_idx_dev);
+      }
+      if (b->n_dynamic != static_cast<int>(nd)) {               // first use, or the batch's terrains changed
+        Check(cudaMemcpy(b->dyn_idx_dev, dyn_index.data(), sizeof(int) * nd, cudaMemcpyHostToDevice), "H2D dynamic index");
+        b->n_dynamic = static_cast<int>(nd);
+      }
+    }
     const tb::ProblemConst* pcs = b->pc_dev;
     if (ids) {
       // gather the constants of the requested problems (the callers' x rows are already in request order)
@@ -382,14 +468,34 @@ int towr_b200_batch_eval(towr_b200_batch* b, const int* ids, int n, int what, co
     } else {
       b->SyncConsts();
     }
-    Check(cudaMemcpyAsync(b->x_dev, x, sizeof(double) * dp.n_vars * n, cudaMemcpyHostToDevice, b->stream), "H2D x");
-    Check(tb::LaunchEval(dp, pcs, what, b->x_dev, b->g_dev, b->v_dev, b->status_dev, n, b->var, b->max_ctas, b->stream), "launch");
-    b->launches += 1;
-    if (what & TOWR_B200_EVAL_G)
-      Check(cudaMemcpyAsync(g_out, b->g_dev, sizeof(double) * dp.n_rows * n, cudaMemcpyDeviceToHost, b->stream), "D2H g");
-    if (what & TOWR_B200_EVAL_JAC)
-      Check(cudaMemcpyAsync(jac_out, b->v_dev, sizeof(double) * dp.nnz * n, cudaMemcpyDeviceToHost, b->stream), "D2H values");
+    Check(cudaEventRecord(b->consts_ready, b->stream), "record consts");
+    Check(cudaStreamWaitEvent(b->stream2, b->consts_ready, 0), "wait consts");
+    // chunks alternate between two streams: D2H of chunk k (the long pole: PCIe) overlaps H2D + kernel of chunk k + 1
+    int chunk = n;
+    if (n > 1536) chunk = 1024;
+    if (const char* env = std::getenv("TOWR_B200_CHUNK")) chunk = std::max(1, std::atoi(env));
+    int k = 0;
+    for (int c0 = 0; c0 < n; c0 += chunk, ++k) {
+      const int m = std::min(chunk, n - c0);
+      cudaStream_t st = (k & 1) ? b->stream2 : b->stream;
+      const size_t o = static_cast<size_t>(c0);
+      Check(cudaMemcpyAsync(b->x_dev + o * dp.n_vars, x + o * dp.n_vars, sizeof(double) * dp.n_vars * m, cudaMemcpyHostToDevice, st), "H2D x");
+      Check(tb::LaunchEval(dp, pcs + c0, kernel_what, b->x_dev + o * dp.n_vars, want_g ? b->g_dev + o * dp.n_rows : nullptr,
+                           (want_jac || want_dyn) ? b->v_dev + o * dp.nnz : nullptr, b->status_dev + c0, m, b->var, b->max_ctas, st), "launch");
+      b->launches += 1;
+      if (want_dyn && nd > 0) {
+        Check(tb::LaunchCompact(b->v_dev + o * dp.nnz, b->dyn_idx_dev, b->dyn_dev + o * nd, dp.nnz, static_cast<int>(nd), m, st), "launch compact");
+        b->launches += 1;
+      }
+      if (want_g)
+        Check(cudaMemcpyAsync(g_out + o * dp.n_rows, b->g_dev + o * dp.n_rows, sizeof(double) * dp.n_rows * m, cudaMemcpyDeviceToHost, st), "D2H g");
+      if (want_jac)
+        Check(cudaMemcpyAsync(jac_out + o * dp.nnz, b->v_dev + o * dp.nnz, sizeof(double) * dp.nnz * m, cudaMemcpyDeviceToHost, st), "D2H values");
+      if (want_dyn && nd > 0)
+        Check(cudaMemcpyAsync(jac_out + o * nd, b->dyn_dev + o * nd, sizeof(double) * nd * m, cudaMemcpyDeviceToHost, st), "D2H dynamic values");
+    }
     Check(cudaStreamSynchronize(b->stream), "eval");
+    Check(cudaStreamSynchronize(b->stream2), "eval");
   });
 }
 

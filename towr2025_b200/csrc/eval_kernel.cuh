@@ -186,7 +186,7 @@ __device__ __forceinline__ void StageBRing(const uint32_t* __restrict__ ent_seg,
 }
 
 // RT: structure classes with optimised phase durations (stage D below; items.cuh Lockstep<P, true>).
-template <int WHAT, int P, bool RT, int S = 1, bool RING = false>
+template <int WHAT, int P, bool RT, int S = 1, bool RING = false, bool CURV = false>
 __global__ void __launch_bounds__(kThreads * P * S, (P == 1 && S == 1 && !RT) ? 2 : 1)   // one lane, one stream: two CTAs per SM (128 registers each)
 EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restrict__ pcs, const double* __restrict__ x,
            double* __restrict__ g_out, double* __restrict__ vals_out, int* __restrict__ status, int n_problems, int skew) {
@@ -219,7 +219,7 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
   }
   __syncthreads();
   TB_MARK_INIT
-  ItemCtx<Lockstep<P, RT>> cx;
+  ItemCtx<Lockstep<P, RT, CURV>> cx;
   cx.n_ee = Pg.n_ee;
   cx.T = MakeTables(blob, Pg.blob);
   const double* Bs = cx.T.B;
@@ -357,7 +357,7 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
         int r = 0;
         for (int base_i = 0; base_i < count; base_i += kPerRound, ++r) {
           const int idx = base_i + ((r & 1) ? kPerRound - 1 - tid / P : tid / P);
-          if (idx < count) RunItem<Lockstep<P, RT>>(cx, cx.T.items[first_item + idx]);
+          if (idx < count) RunItem<Lockstep<P, RT, CURV>>(cx, cx.T.items[first_item + idx]);
         }
       };
       run_level(sg.item0, sg.n_items0);

@@ -212,6 +212,44 @@ void FillProblemConst(const towr_b200_spec& s, ProblemConst& pc) {
   pc.pad = 0;
 }
 
+void ProblemConstantValues(const HostProgram& hp, double mass, double torque_k_friction, bool flat_basis, double* vals) {
+  // the terrain-basis components as ItemForce / ItemTorque / ItemHeightNode compute them where h_x = h_y = 0
+  double code_value[kCodeCount];
+  {
+    TerrainSample ts = EvalTerrain(0, 0.0, 0.0);
+    double n[3], t1[3], t2[3];
+    TerrainBasis(ts, n, t1, t2);
+    const double mu = kFrictionCoeff, kf = torque_k_friction;
+    for (int d = 0; d < 3; ++d) {
+      code_value[kCodeForce + d] = n[d];
+      code_value[kCodeForce + 3 + d] = t1[d] - mu * n[d];
+      code_value[kCodeForce + 6 + d] = t1[d] + mu * n[d];
+      code_value[kCodeForce + 9 + d] = t2[d] - mu * n[d];
+      code_value[kCodeForce + 12 + d] = t2[d] + mu * n[d];
+      code_value[kCodeTorque + d] = t1[d];
+      code_value[kCodeTorque + 3 + d] = t2[d];
+      code_value[kCodeTorque + 6 + d] = n[d];
+      code_value[kCodeTorque + 9 + d] = -n[d];
+      code_value[kCodeTorque + 12 + d] = (-kf * mu) * n[d];
+    }
+    code_value[kCodeHeight] = -ts.hx;
+    code_value[kCodeHeight + 1] = -ts.hy;
+  }
+  for (size_t e = 0; e < hp.entries.size(); ++e) {
+    const uint32_t w = hp.entries[e];
+    const int g = static_cast<int>(w & 0xFFFF);
+    const double bv = hp.B[(w >> 16) & 0x7FFF];
+    if (!(w & kEntryGG) && g < kGReserved) {
+      const double gv = g == kGOne ? 1.0 : g == kGMinusOne ? -1.0 : mass;       // what stage A puts into these slots
+      vals[e] = gv * bv;                                                          // the same product stage B forms
+    } else if (flat_basis && hp.entry_code[e] >= 0) {
+      vals[e] = code_value[hp.entry_code[e]] * bv;
+    } else {
+      vals[e] = 0.0;
+    }
+  }
+}
+
 double TerrainHeight(int terrain_id, double x, double y) { return EvalTerrain(terrain_id, x, y).h; }
 
 }  // namespace tb

@@ -12,8 +12,10 @@ namespace tb {
 // emulation, P = 1).  The tiled pipeline (tiled.cu) uses Tiled<W>.
 // RT: the structure class optimises the phase durations (PhaseSpline path): ee-motion / ee-force / ee-torque samples are
 // resolved per problem, their Jacobian weights and the ee-schedule columns are written by the items.
-template <int P, bool RT_ = false>
-struct Lockstep { static constexpr int GS = P, NS = P, RS = 1; static constexpr bool RT = RT_; };
+// CURV: the class declares the curvature block of the force / torque constraints (Gap; ItemCurvature below).  A template
+// flag, not a run-time branch: with the code merely present the other classes' kernels lose registers (measured: +19 %).
+template <int P, bool RT_ = false, bool CURV_ = false>
+struct Lockstep { static constexpr int GS = P, NS = P, RS = 1; static constexpr bool RT = RT_, CURV = CURV_; };
 
 template <class L>
 struct ItemCtx {
@@ -397,8 +399,9 @@ __device__ __forceinline__ void ItemRomFoot(const ItemCtx<L>& cx, const ItemC& i
     }
 }
 
-// ------------------------------------------------------------------------------------------- force (discretised)
-// g: force_constraint_discretized.cc:97-117.  G slots: b_i[3], i = 0..4: n, t1 -/+ mu n, t2 -/+ mu n.
+// ---------------------------------------------------------------------------- curvature block (Gap), out of line
+// Classes that declare the curvature block (ItemC::sub = TerrainCurvatureDims of the class, structure.cc); compiled
+// only into the CURV instantiations of the kernel (Lockstep<P, RT, true>).
 // f . d(b_i)/d(dim) for the five force rows (force_constraint_discretized.cc:166-176): b_i = n, t1 -/+ mu n, t2 -/+ mu n
 __device__ __forceinline__ void ForceBasisScales(const TerrainSample& ts, int dim, const double f[3], double s[5]) {
   const double mu = kFrictionCoeff;
@@ -418,12 +421,81 @@ __device__ __forceinline__ void ForceBasisScales(const TerrainSample& ts, int di
   for (int i = 0; i < 5; ++i) s[i] = (f[0] * v[3 * i] + f[1] * v[3 * i + 1]) + f[2] * v[3 * i + 2];
 }
 
+// ROWS = 5: force constraint (scales f . d b_i); ROWS = 4: torque constraint (tau . dt1, tau . dt2, +-tau . dn - k mu f . dn,
+// torque_constraint_discretized.cc:176-197).  Writes S[slot][ROWS] behind the item's other slots; with optimised
+// durations also the ee-motion weights W_p and "+ scale * J_p,dT(row dim)" onto the finished ee-schedule block.
+template <class L, int ROWS>
+__device__ __forceinline__ void ItemCurvature(const ItemCtx<L>& cx, const ItemC& it) {
+  const int dims = it.sub, nd = CurvDimCount(dims), E = cx.n_ee;
+  Pt3 p, f, tau;
+  RtPoint rp;
+  if constexpr (L::RT) {
+    rp = EvalSplineRt<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0, p);
+    EvalSplineRt<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0 + 1, f);
+    if (ROWS == 4) EvalSplineRt<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0 + 2, tau);
+  } else {
+    EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, p);
+    EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 1, f);
+    if (ROWS == 4) EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 2, tau);
+  }
+  const TerrainSample ts = EvalTerrain(cx.pc->terrain_id, p.p[0], p.p[1]);
+  double* G = cx.G + it.gslot * L::GS;
+  int n_w = 0, n_sched = 0;
+  if constexpr (L::RT) {
+    n_w = cx.T.rt_splines[E + it.ee].n_cols + (ROWS == 4 ? cx.T.rt_splines[2 * E + it.ee].n_cols : 0);
+    n_sched = cx.T.rt_feet[it.ee].n_phases - 1;
+  }
+  double* S = G + (ROWS == 5 ? ForceCurvOffset(n_w, n_sched) : TorqueCurvOffset(n_w, n_sched)) * L::GS;
+  double sc[2][5];
+  int slot = 0;
+  for (int dim = 0; dim < 2; ++dim) {
+    if (!((dims >> dim) & 1)) continue;
+    if (ROWS == 5) {
+      ForceBasisScales(ts, dim, f.p, sc[slot]);
+    } else {
+      double dn[3], dt1[3], dt2[3];
+      TerrainBasisDeriv(ts, 0, dim, dn);
+      TerrainBasisDeriv(ts, 1, dim, dt1);
+      TerrainBasisDeriv(ts, 2, dim, dt2);
+      const double kf = cx.T.B[it.b0], mu = kFrictionCoeff;
+      const double s_tx = (tau.p[0] * dt1[0] + tau.p[1] * dt1[1]) + tau.p[2] * dt1[2];
+      const double s_ty = (tau.p[0] * dt2[0] + tau.p[1] * dt2[1]) + tau.p[2] * dt2[2];
+      const double s_tau_n = (tau.p[0] * dn[0] + tau.p[1] * dn[1]) + tau.p[2] * dn[2];
+      const double s_f_n = (f.p[0] * dn[0] + f.p[1] * dn[1]) + f.p[2] * dn[2];
+      const double s_lim = (kf * mu) * s_f_n;
+      sc[slot][0] = s_tx; sc[slot][1] = s_ty; sc[slot][2] = s_tau_n - s_lim; sc[slot][3] = -s_tau_n - s_lim;
+    }
+    for (int i = 0; i < ROWS; ++i) S[(ROWS * slot + i) * L::GS] = sc[slot][i];
+    ++slot;
+  }
+  if constexpr (L::RT) {
+    WriteHermiteWeights<L::GS, L::NS>(cx.T, cx.rtd, cx.T.rt_splines[it.ee], rp, S + ROWS * nd * L::GS);
+    double* Sc = G + (15 + n_w) * L::GS;                  // the item's finished ee-schedule block [ROWS][P-1]
+    const RtFoot ft = cx.T.rt_feet[it.ee];
+    double dpT[3];
+    const int cur_p = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, cx.rtd, rp, p.v, dpT);
+    const int nc = ft.n_phases - 1;
+    for (int j = 0; j < nc; ++j) {
+      double cp[3];
+      DurationColumn(j, cur_p, ft.n_phases, dpT, p.v, cp);
+      slot = 0;
+      for (int dim = 0; dim < 2; ++dim) {
+        if (!((dims >> dim) & 1)) continue;
+        for (int i = 0; i < ROWS; ++i) Sc[(i * nc + j) * L::GS] = Sc[(i * nc + j) * L::GS] + sc[slot][i] * cp[dim];
+        ++slot;
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------- force (discretised)
+// g: force_constraint_discretized.cc:97-117.  G slots: b_i[3], i = 0..4: n, t1 -/+ mu n, t2 -/+ mu n.
 template <class L>
 __device__ __forceinline__ void ItemForce(const ItemCtx<L>& cx, const ItemC& it) {
   Pt3 p, f;
-  RtPoint rp, rf;
+  RtPoint rf;
   if constexpr (L::RT) {
-    rp = EvalSplineRt<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0, p);
+    EvalSplineRt<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0, p);
     rf = EvalSplineRt<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0 + 1, f);
   } else {
     EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, p);
@@ -450,61 +522,25 @@ __device__ __forceinline__ void ItemForce(const ItemCtx<L>& cx, const ItemC& it)
 #pragma unroll
     for (int i = 0; i < 5; ++i) gr[(i) * L::RS] = (f.p[0] * b[3 * i] + f.p[1] * b[3 * i + 1]) + f.p[2] * b[3 * i + 2];
   }
-  // classes that declare the curvature block (it.sub = TerrainCurvatureDims of the class): S[slot][5] = f . d b_i / d(dim)
-  // for the ee-motion block; exact zeros on a terrain without curvature, where the reference stores nothing
-  const int dims = it.sub, nd = CurvDimCount(dims);
-  double sc[2][5];
-  int n_w = 0, n_sched = 0;
   if constexpr (L::RT) {
-    n_w = cx.T.rt_splines[cx.n_ee + it.ee].n_cols;
-    n_sched = cx.T.rt_feet[it.ee].n_phases - 1;
-  }
-  double* S = G + ForceCurvOffset(n_w, n_sched) * L::GS;
-  if (dims) {
-    int slot = 0;
-    for (int dim = 0; dim < 2; ++dim) {
-      if (!((dims >> dim) & 1)) continue;
-      ForceBasisScales(ts, dim, f.p, sc[slot]);
-#pragma unroll
-      for (int i = 0; i < 5; ++i) S[(5 * slot + i) * L::GS] = sc[slot][i];
-      ++slot;
-    }
-  }
-  if constexpr (L::RT) {
-    // G + 15 = W_f[n_cols] | schedule[5][P-1] = b_i . J_f,dT  (+ S_i J_p,dT(row dim) in curvature classes)
-    // (force_constraint_discretized.cc:190-220)
+    // G + 15 = W_f[n_cols] | schedule[5][P-1] = b_i . J_f,dT (force_constraint_discretized.cc:190-220; the terrain-basis
+    // part is dropped where the terrain has no curvature, :58)
     const int E = cx.n_ee;
     const RtSpline sf = cx.T.rt_splines[E + it.ee];
     WriteHermiteWeights<L::GS, L::NS>(cx.T, cx.rtd, sf, rf, G + 15 * L::GS);
     double* Sc = G + (15 + sf.n_cols) * L::GS;
     const RtFoot ft = cx.T.rt_feet[it.ee];
-    double dfT[3], dpT[3];
+    double dfT[3];
     const int cur = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, cx.rtd, rf, f.v, dfT);
-    int cur_p = 0;
-    if (dims) {
-      cur_p = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, cx.rtd, rp, p.v, dpT);
-      WriteHermiteWeights<L::GS, L::NS>(cx.T, cx.rtd, cx.T.rt_splines[it.ee], rp, S + 5 * nd * L::GS);
-    }
     const int nc = ft.n_phases - 1;
     for (int j = 0; j < nc; ++j) {
-      double c[3], cp[3];
+      double c[3];
       DurationColumn(j, cur, ft.n_phases, dfT, f.v, c);
-      if (dims) DurationColumn(j, cur_p, ft.n_phases, dpT, p.v, cp);
 #pragma unroll
-      for (int i = 0; i < 5; ++i) {
-        double v = (b[3 * i] * c[0] + b[3 * i + 1] * c[1]) + b[3 * i + 2] * c[2];
-        if (dims) {
-          int slot = 0;
-          for (int dim = 0; dim < 2; ++dim) {
-            if (!((dims >> dim) & 1)) continue;
-            v = v + sc[slot][i] * cp[dim];
-            ++slot;
-          }
-        }
-        Sc[(i * nc + j) * L::GS] = v;
-      }
+      for (int i = 0; i < 5; ++i) Sc[(i * nc + j) * L::GS] = (b[3 * i] * c[0] + b[3 * i + 1] * c[1]) + b[3 * i + 2] * c[2];
     }
   }
+  if constexpr (L::CURV) ItemCurvature<L, 5>(cx, it);
 }
 
 // ------------------------------------------------------------------------------------------- force (node-based)
@@ -561,9 +597,9 @@ __device__ __forceinline__ void ItemForceNode(const ItemCtx<L>& cx, const ItemC&
 template <class L>
 __device__ __forceinline__ void ItemTorque(const ItemCtx<L>& cx, const ItemC& it) {
   Pt3 p, f, tau;
-  RtPoint rp, rf, rt;
+  RtPoint rf, rt;
   if constexpr (L::RT) {
-    rp = EvalSplineRt<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0, p);
+    EvalSplineRt<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0, p);
     rf = EvalSplineRt<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0 + 1, f);
     rt = EvalSplineRt<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0 + 2, tau);
   } else {
@@ -594,35 +630,6 @@ __device__ __forceinline__ void ItemTorque(const ItemCtx<L>& cx, const ItemC& it
     gr[2 * L::RS] = tau_n - tz_lim;
     gr[3 * L::RS] = -tau_n - tz_lim;
   }
-  // classes that declare the curvature block: S[slot][4] = the four rows' d/d(dim) scales
-  // (torque_constraint_discretized.cc:176-197): tau.dt1, tau.dt2, (tau.dn - k mu f.dn), (-tau.dn - k mu f.dn)
-  const int dims = it.sub, nd = CurvDimCount(dims);
-  double sc[2][4];
-  int n_w = 0, n_sched = 0;
-  if constexpr (L::RT) {
-    n_w = cx.T.rt_splines[cx.n_ee + it.ee].n_cols + cx.T.rt_splines[2 * cx.n_ee + it.ee].n_cols;
-    n_sched = cx.T.rt_feet[it.ee].n_phases - 1;
-  }
-  double* S = G + TorqueCurvOffset(n_w, n_sched) * L::GS;
-  if (dims) {
-    int slot = 0;
-    for (int dim = 0; dim < 2; ++dim) {
-      if (!((dims >> dim) & 1)) continue;
-      double dn[3], dt1[3], dt2[3];
-      TerrainBasisDeriv(ts, 0, dim, dn);
-      TerrainBasisDeriv(ts, 1, dim, dt1);
-      TerrainBasisDeriv(ts, 2, dim, dt2);
-      const double s_tx = (tau.p[0] * dt1[0] + tau.p[1] * dt1[1]) + tau.p[2] * dt1[2];
-      const double s_ty = (tau.p[0] * dt2[0] + tau.p[1] * dt2[1]) + tau.p[2] * dt2[2];
-      const double s_tau_n = (tau.p[0] * dn[0] + tau.p[1] * dn[1]) + tau.p[2] * dn[2];
-      const double s_f_n = (f.p[0] * dn[0] + f.p[1] * dn[1]) + f.p[2] * dn[2];
-      const double s_lim = (kf * mu) * s_f_n;
-      sc[slot][0] = s_tx; sc[slot][1] = s_ty; sc[slot][2] = s_tau_n - s_lim; sc[slot][3] = -s_tau_n - s_lim;
-#pragma unroll
-      for (int i = 0; i < 4; ++i) S[(4 * slot + i) * L::GS] = sc[slot][i];
-      ++slot;
-    }
-  }
   if constexpr (L::RT) {
     // G + 15 = W_tau | W_f | schedule[4][P-1] (torque_constraint_discretized.cc:222-234)
     const int E = cx.n_ee;
@@ -634,39 +641,21 @@ __device__ __forceinline__ void ItemTorque(const ItemCtx<L>& cx, const ItemC& it
     double dtT[3], dfT[3];
     const int cur_t = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, cx.rtd, rt, tau.v, dtT);
     const int cur_f = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, cx.rtd, rf, f.v, dfT);
-    double dpT[3];
-    int cur_p = 0;
-    if (dims) {
-      cur_p = PosWrtPhaseDuration<L::NS>(cx.T, cx.nodes, cx.rtd, rp, p.v, dpT);
-      WriteHermiteWeights<L::GS, L::NS>(cx.T, cx.rtd, cx.T.rt_splines[it.ee], rp, S + 4 * nd * L::GS);
-    }
     const int nc = ft.n_phases - 1;
     for (int j = 0; j < nc; ++j) {
-      double ct[3], cf[3], cp[3];
+      double ct[3], cf[3];
       DurationColumn(j, cur_t, ft.n_phases, dtT, tau.v, ct);
       DurationColumn(j, cur_f, ft.n_phases, dfT, f.v, cf);
-      if (dims) DurationColumn(j, cur_p, ft.n_phases, dpT, p.v, cp);
       const double bf[3] = {(-kf * mu) * n[0], (-kf * mu) * n[1], (-kf * mu) * n[2]};
-      double v4[4];
-      v4[0] = (t1[0] * ct[0] + t1[1] * ct[1]) + t1[2] * ct[2];
-      v4[1] = (t2[0] * ct[0] + t2[1] * ct[1]) + t2[2] * ct[2];
+      Sc[(0 * nc + j) * L::GS] = (t1[0] * ct[0] + t1[1] * ct[1]) + t1[2] * ct[2];
+      Sc[(1 * nc + j) * L::GS] = (t2[0] * ct[0] + t2[1] * ct[1]) + t2[2] * ct[2];
       const double a2 = (n[0] * ct[0] + n[1] * ct[1]) + n[2] * ct[2];
       const double a3 = ((-n[0]) * ct[0] + (-n[1]) * ct[1]) + (-n[2]) * ct[2];
-      v4[2] = ((a2 + bf[0] * cf[0]) + bf[1] * cf[1]) + bf[2] * cf[2];
-      v4[3] = ((a3 + bf[0] * cf[0]) + bf[1] * cf[1]) + bf[2] * cf[2];
-      if (dims) {                                      // + scale_i * J_p,dT(row dim), :222-234
-        int slot = 0;
-        for (int dim = 0; dim < 2; ++dim) {
-          if (!((dims >> dim) & 1)) continue;
-#pragma unroll
-          for (int i = 0; i < 4; ++i) v4[i] = v4[i] + sc[slot][i] * cp[dim];
-          ++slot;
-        }
-      }
-#pragma unroll
-      for (int i = 0; i < 4; ++i) Sc[(i * nc + j) * L::GS] = v4[i];
+      Sc[(2 * nc + j) * L::GS] = ((a2 + bf[0] * cf[0]) + bf[1] * cf[1]) + bf[2] * cf[2];
+      Sc[(3 * nc + j) * L::GS] = ((a3 + bf[0] * cf[0]) + bf[1] * cf[1]) + bf[2] * cf[2];
     }
   }
+  if constexpr (L::CURV) ItemCurvature<L, 4>(cx, it);
 }
 
 // ------------------------------------------------------------------------------------------------ base motion

@@ -1,10 +1,13 @@
 // kernels_variant.cu — explicit instantiations of the evaluation kernel for one variant.  Compiled once per variant with
-// -DTB_LANES=<1|2|4> -DTB_RT=<0|1> -DTB_STREAMS=<1|2> -DTB_RING=<0|1> (Makefile) so that the variants build in parallel.
+// -DTB_LANES=<1|2|4> -DTB_RT=<0|1> -DTB_STREAMS=<1|2> -DTB_RING=<0|1> -DTB_CURV=<0|1> (Makefile) so that the variants build in parallel.
 // timing build (make timing [TIMING_CODE=<lanes><rt><streams><ring>]): the one variant that owns the phase counters
 #ifndef TB_TIMING_CODE
 #define TB_TIMING_CODE 2010
 #endif
-#if defined(TB_TIMING) && (TB_LANES * 1000 + TB_RT * 100 + TB_STREAMS * 10 + TB_RING) == TB_TIMING_CODE
+#ifndef TB_CURV
+#define TB_CURV 0
+#endif
+#if defined(TB_TIMING) && TB_CURV == 0 && (TB_LANES * 1000 + TB_RT * 100 + TB_STREAMS * 10 + TB_RING) == TB_TIMING_CODE
 #define TB_TIMING_HERE
 #endif
 #include "eval_kernel.cuh"
@@ -16,7 +19,7 @@ static cudaError_t LaunchT(const DeviceProgram& P, const ProblemConst* pcs, cons
                            int* status, int n_problems, int max_ctas, int skew, cudaStream_t stream) {
   constexpr int LANES = TB_LANES, STREAMS = TB_STREAMS;
   const size_t smem = EvalSharedBytes(P, LANES, STREAMS, TB_RING != 0);
-  auto kern = EvalKernel<WHAT, LANES, TB_RT != 0, STREAMS, TB_RING != 0>;
+  auto kern = EvalKernel<WHAT, LANES, TB_RT != 0, STREAMS, TB_RING != 0, TB_CURV != 0>;
   cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
   if (err != cudaSuccess) return err;
   int grid = (n_problems + LANES * STREAMS - 1) / (LANES * STREAMS);
@@ -25,8 +28,9 @@ static cudaError_t LaunchT(const DeviceProgram& P, const ProblemConst* pcs, cons
   return cudaGetLastError();
 }
 
-#define TB_CAT5(a, b, c, d, e) a##b##_##c##_##d##_##e
-#define TB_NAME(a, b, c, d, e) TB_CAT5(a, b, c, d, e)
+#define TB_CAT6(a, b, c, d, e, f) a##b##_##c##_##d##_##e##_##f
+#define TB_NAME6(a, b, c, d, e, f) TB_CAT6(a, b, c, d, e, f)
+#define TB_NAME(a, b, c, d, e) TB_NAME6(a, b, c, d, e, TB_CURV)
 
 cudaError_t TB_NAME(LaunchV, TB_LANES, TB_RT, TB_STREAMS, TB_RING)(const DeviceProgram& P, const ProblemConst* pcs, int what,
                                                                    const double* x, double* g, double* vals, int* status,
@@ -42,7 +46,7 @@ cudaError_t TB_NAME(LaunchV, TB_LANES, TB_RT, TB_STREAMS, TB_RING)(const DeviceP
 int TB_NAME(OccupancyV, TB_LANES, TB_RT, TB_STREAMS, TB_RING)(const DeviceProgram& P) {
   int n = 0;
   const size_t smem = EvalSharedBytes(P, TB_LANES, TB_STREAMS, TB_RING != 0);
-  auto kern = EvalKernel<3, TB_LANES, TB_RT != 0, TB_STREAMS, TB_RING != 0>;
+  auto kern = EvalKernel<3, TB_LANES, TB_RT != 0, TB_STREAMS, TB_RING != 0, TB_CURV != 0>;
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess) {
     cudaGetLastError();
     return 0;

@@ -263,7 +263,7 @@ void BuildLayout(const towr_b200_spec& s, HostProgram& hp) {
     for (int e = 0; e < E; ++e) {
       double total = 0.0;                       // std::accumulate(timings.begin(), timings.end(), 0.0)
       for (int i = 0; i < s.n_phases[e]; ++i) total += s.phase_durations[e][i];
-      hp.rt_feet.push_back(RtFoot{phase0, s.n_phases[e], hp.Find(kEESchedule, e)->col0, 0, total});
+      hp.rt_feet.push_back(RtFoot{static_cast<short>(phase0), static_cast<short>(s.n_phases[e]), hp.Find(kEESchedule, e)->col0, total});
       phase0 += s.n_phases[e];
     }
   }

@@ -118,34 +118,10 @@ void PackProgram(HostProgram& hp) {
         std::stable_sort(kinds.begin(), kinds.end(), [](const std::array<int, 3>& a, const std::array<int, 3>& b) {
           return ItemCostRank(a[1]) < ItemCostRank(b[1]);
         });
-        // A level runs in rounds of kItemsPerRound (item, lane) slots.  If the padding between kinds is all that pushes
-        // the level into one more round, the cheapest kinds (the last ones) are packed back to back instead: one warp
-        // that runs two short kinds in turn costs far less than a round of its own (ANYmal trot: 272 -> 256 slots).
-        std::vector<int> count(kinds.size(), 0);
-        for (size_t q = 0; q < kinds.size(); ++q)
-          for (int i = 0; i < sg.n_items; ++i) count[q] += kind[sg.item0 + i] == kinds[q];
-        auto pad_to = [](int n) { return (n + kItemPad - 1) / kItemPad * kItemPad; };
-        int total_padded = 0, total_raw = 0;
-        for (int c : count) { total_padded += pad_to(c); total_raw += c; }
-        size_t first_unpadded = kinds.size();                   // kinds [first_unpadded, end) share warps
-        const int rounds_padded = (total_padded + kItemsPerRound - 1) / kItemsPerRound;
-        if (pad_to(total_raw) <= (rounds_padded - 1) * kItemsPerRound || rounds_padded > (pad_to(total_raw) + kItemsPerRound - 1) / kItemsPerRound) {
-          int t = total_padded;
-          while (first_unpadded > 1 && (t + kItemsPerRound - 1) / kItemsPerRound >= rounds_padded) {
-            --first_unpadded;
-            int merged = 0;
-            t = 0;
-            for (size_t q = 0; q < kinds.size(); ++q) {
-              if (q < first_unpadded) t += pad_to(count[q]);
-              else merged += count[q];
-            }
-            t += pad_to(merged);
-          }
-        }
-        for (size_t q = 0; q < kinds.size(); ++q) {
-          if (q <= first_unpadded) while (padded.size() % kItemPad) padded.push_back(none);
+        for (auto& k : kinds) {
+          while (padded.size() % kItemPad) padded.push_back(none);
           for (int i = 0; i < sg.n_items; ++i)
-            if (kind[sg.item0 + i] == kinds[q]) padded.push_back(items[sg.item0 + i]);
+            if (kind[sg.item0 + i] == k) padded.push_back(items[sg.item0 + i]);
         }
         while (padded.size() % kItemPad) padded.push_back(none);
         if (level == 0) sg.n_items0 = static_cast<int>(padded.size()) - new0;
@@ -218,6 +194,15 @@ void PackProgram(HostProgram& hp) {
   uint16_t* ns = reinterpret_cast<uint16_t*>(d + L.off_node_src);
   for (int i = 0; i < hp.n_node_values; ++i) ns[i] = hp.node_src[i] < 0 ? 0xFFFF : static_cast<uint16_t>(hp.node_src[i]);
 
+  hp.dyn_index.clear();
+  hp.dyn_index_flat.clear();
+  for (size_t e = 0; e < hp.entries.size(); ++e) {
+    const uint32_t w = hp.entries[e];
+    if ((w & kEntryGG) || static_cast<int>(w & 0xFFFF) >= kGReserved) {
+      hp.dyn_index.push_back(static_cast<int>(e));
+      if (hp.entry_code[e] < 0) hp.dyn_index_flat.push_back(static_cast<int>(e));
+    }
+  }
   // device descriptors: byte offsets, so that stage B needs no index scaling
   hp.entries_dev.clear();
   hp.entries_dev.reserve(hp.entries.size());

@@ -61,7 +61,6 @@ enum ItemType : int {
   kItemNone = 255,      // padding: keeps every warp of stage A on one item kind
 };
 constexpr int kItemPad = 16;   // items of one kind are padded to a multiple of this (pack.cc)
-constexpr int kItemsPerRound = 256;   // items one stage-A round of the kernel takes (kEntryThreads: NT / P)
 // relative cost of an item kind: lower = longer dependent chain (pack.cc orders the kinds of a level by it)
 inline int ItemCostRank(int type) {
   switch (type) {
@@ -132,6 +131,12 @@ struct SegmentRec {
   int pad2;
 };
 
+// BasisCode of an entry whose G factor is a terrain-basis component (constant on a terrain without slope):
+//   kCodeForce + 3 i + d   : b_i[d], i = 0..4: n, t1 - mu n, t1 + mu n, t2 - mu n, t2 + mu n   (ItemForce, ItemForceNode)
+//   kCodeTorque + 3 i + d  : i = 0..4: t1, t2, n, -n, (-k mu) n                               (ItemTorque)
+//   kCodeHeight + d        : -h_x, -h_y                                                       (ItemHeightNode)
+enum { kCodeForce = 0, kCodeTorque = 15, kCodeHeight = 30, kCodeCount = 32 };
+
 // slots 0.. of every segment's G buffer
 enum { kGOne = 0, kGMass = 1, kGMinusOne = 2, kGReserved = 3 };
 
@@ -154,10 +159,9 @@ struct RtSpline {       // one PhaseSpline: index kind*E + foot, kind 0 = ee-mot
   int poly0, n_polys;   // global polynomial range
   int col0, n_cols;     // its variable set's columns
 };
-struct RtFoot {         // one PhaseDurations set
-  int phase0, n_phases; // offset into the per-problem phase-duration array; P
+struct RtFoot {         // one PhaseDurations set (16 bytes: one shared-memory load)
+  short phase0, n_phases; // offset into the per-problem phase-duration array; P
   int col0;             // first ee-schedule column (P - 1 of them)
-  int pad;
   double total;         // t_total_ of THIS foot: its own initial durations summed in order (phase_durations.cc:40-50);
                         // feet may differ from each other in the last bit (2.4 vs 2.3999999999999995)
 };
@@ -187,6 +191,7 @@ struct DeviceProgram {  // pointers into device memory (one copy per GPU)
   int n_vars, n_rows, nnz, n_ee;
   int n_segments;
   int g_capacity;       // max g_size over segments
+  int curvature_dims;   // != 0: the class declares the curvature block (CURV kernel instantiations)
   double total_time;
   BlobLayout blob;
   const unsigned char* blob_data;
@@ -271,6 +276,13 @@ struct HostProgram {
   BlobLayout blob{};
   std::vector<unsigned char> blob_data;
   std::vector<uint32_t> entries_dev;    // byte-offset form of entries
+  // storage positions of the entries whose value depends on x (ascending).  The others are G[kGOne | kGMinusOne | kGMass]
+  // * B: constant for a problem (ProblemConstantValues); the host interface can leave them off the bus
+  std::vector<int> dyn_index;
+  // the same when every problem of a batch is on a terrain without slope (TerrainHasSlope, terrain.h): the terrain basis
+  // is then constant as well, and so are the entries tagged with a BasisCode (entry_code, one per stored entry, -1: none)
+  std::vector<int> dyn_index_flat;
+  std::vector<signed char> entry_code;
   int g_capacity = 0;
   int n_node_values = 0;
   std::string signature;   // canonical text of every structural field (structure_accepts compares it)

@@ -64,7 +64,9 @@ double LocalTime(double t_global, int id, const std::vector<double>& durations) 
 
 namespace {
 
-struct Term { int g = 0, b = 0; bool gg = false; };   // value = G[g] * B[b], or G[g] * G[b] when gg (runtime weights)
+// value = G[g] * B[b], or G[g] * G[b] when gg (runtime weights).  code >= 0: G[g] is a component of the terrain basis
+// (BasisCode, program.h), a constant of the problem on a terrain without slope
+struct Term { int g = 0, b = 0; bool gg = false; int code = -1; };
 struct ColBasis { int idx, dim; double v[3]; int sd; };   // v[dx]: d{pos,vel,acc}/d(variable idx); sd = side*2+deriv of the last hit
 struct SplineAt { int sample; int poly; double t_local; };
 
@@ -224,6 +226,7 @@ class Builder {
         if (t.g < 0 || t.g > 65535 || t.b < 0 || t.b > 32767) throw std::runtime_error("entry descriptor out of range");
         EntryRec er = static_cast<uint32_t>(t.g) | (static_cast<uint32_t>(t.b) << 16) | (t.gg ? kEntryGG : 0u);
         hp_.entries.push_back(er);
+        hp_.entry_code.push_back(static_cast<signed char>(t.gg ? -1 : t.code));
         hp_.pat_rows.push_back(set_row0_ + r);
         hp_.pat_cols.push_back(e.first);
       }
@@ -298,7 +301,7 @@ void Builder::EmitHeightRows(const VarSet& set, int item_type, int ee) {
     Term tz; tz.g = kGOne; tz.b = one;
     Add(node - 1, set.col0 + set.OptIndex(node, 0, 2), tz, true);
     for (int dim = 0; dim < 2; ++dim) {
-      Term t; t.g = it.gslot + dim; t.b = one;
+      Term t; t.g = it.gslot + dim; t.b = one; t.code = kCodeHeight + dim;
       Add(node - 1, set.col0 + set.OptIndex(node, 0, dim), t, true);
     }
   }
@@ -613,7 +616,7 @@ void Builder::EmitForceDisc(int ee) {
     hp_.items.push_back(it);
     for (const ColBasis& c : Columns(fo, af.poly, af.t_local))
       for (int i = 0; i < 5; ++i) {              // b_i . J_f
-        Term tm; tm.g = it.gslot + 3 * i + c.dim; tm.b = AddB(c.v[0]);
+        Term tm; tm.g = it.gslot + 3 * i + c.dim; tm.b = AddB(c.v[0]); tm.code = kCodeForce + 3 * i + c.dim;
         Add(static_cast<int>(k) * 5 + i, fo.col0 + c.idx, tm);
       }
     for (const ColBasis& c : Columns(mo, am.poly, am.t_local))
@@ -732,7 +735,7 @@ void Builder::EmitForceNodes(int ee) {
     for (int dim = 0; dim < 3; ++dim) {
       const int idx = fo.OptIndex(node, 0, dim);
       if (idx < 0) throw std::runtime_error("force constraint touches a node value that is not optimised");
-      for (int i = 0; i < 5; ++i) { Term tm; tm.g = it.gslot + 3 * i + dim; tm.b = one; Add(row + i, fo.col0 + idx, tm, true); }
+      for (int i = 0; i < 5; ++i) { Term tm; tm.g = it.gslot + 3 * i + dim; tm.b = one; tm.code = kCodeForce + 3 * i + dim; Add(row + i, fo.col0 + idx, tm, true); }
     }
     for (int dim = 0; dim < 2; ++dim) {
       const int idx = mo.OptIndex(ee_node, 0, dim);
@@ -798,12 +801,12 @@ void Builder::EmitTorqueDisc(int ee) {
     hp_.items.push_back(it);
     for (const ColBasis& c : Columns(to, at.poly, at.t_local))
       for (int i = 0; i < 4; ++i) {              // t1, t2, n, -n . J_tau
-        Term tm; tm.g = it.gslot + 3 * i + c.dim; tm.b = AddB(c.v[0]);
+        Term tm; tm.g = it.gslot + 3 * i + c.dim; tm.b = AddB(c.v[0]); tm.code = kCodeTorque + 3 * i + c.dim;
         Add(r0 + i, to.col0 + c.idx, tm);
       }
     for (const ColBasis& c : Columns(fo, af.poly, af.t_local))
       for (int i = 2; i < 4; ++i) {              // (-k mu) n . J_f on the two yaw-friction rows
-        Term tm; tm.g = it.gslot + 12 + c.dim; tm.b = AddB(c.v[0]);
+        Term tm; tm.g = it.gslot + 12 + c.dim; tm.b = AddB(c.v[0]); tm.code = kCodeTorque + 12 + c.dim;
         Add(r0 + i, fo.col0 + c.idx, tm);
       }
     for (const ColBasis& c : Columns(mo, am.poly, am.t_local))
@@ -924,7 +927,7 @@ void Builder::Run() {
 
 void ResetTables(HostProgram& hp) {
   hp.con_sets.clear(); hp.pat_rows.clear(); hp.pat_cols.clear(); hp.row_bounds.clear();
-  hp.samples.clear(); hp.items.clear(); hp.entries.clear(); hp.B.clear(); hp.segments.clear();
+  hp.samples.clear(); hp.items.clear(); hp.entries.clear(); hp.entry_code.clear(); hp.B.clear(); hp.segments.clear();
   hp.g_capacity = 0; hp.n_rows = 0; hp.nnz = 0;
 }
 

@@ -36,6 +36,9 @@ void ProblemX0(const HostProgram& hp, const towr_b200_spec& s, double* x);
 void ProblemVarBounds(const HostProgram& hp, const towr_b200_spec& s, double* lo, double* up);
 void ProblemConBounds(const HostProgram& hp, const towr_b200_spec& s, double* lo, double* up);
 void FillProblemConst(const towr_b200_spec& s, ProblemConst& pc);
+// vals[nnz]: the x-independent stored values of a problem (+-B, mass * B; flat_basis: also terrain-basis component * B on
+// a terrain without slope), 0.0 at the positions of hp.dyn_index (flat_basis: hp.dyn_index_flat)
+void ProblemConstantValues(const HostProgram& hp, double mass, double torque_k_friction, bool flat_basis, double* vals);
 double TerrainHeight(int terrain_id, double x, double y);
 
 }  // namespace tb

@@ -95,6 +95,9 @@ TB_HD TerrainSample EvalTerrain(int id, double x, double y) {
 // structure class built for such a terrain declares that block (superset pattern, structure.cc).
 TB_HD int TerrainCurvatureDims(int id) { return id == 3 ? 1 : 0; }   // Gap: h_xx != 0 over the parabola
 
+// false: h_x = h_y = 0 everywhere (piecewise constant height): normal and tangents are the same constants at every (x, y)
+TB_HD bool TerrainHasSlope(int id) { return !(id == 0 || id == 2 || id == 7); }   // Flat, Stairs, FiveStepStairs
+
 // normalised normal / tangents at (x,y): n = (-hx,-hy,1)/|.|, t1 = (1,0,hx)/|.|, t2 = (0,1,hy)/|.|
 // v.normalized() = v / sqrt(v.v) with the squared norm summed left to right
 TB_HD void Normalize3(const double v[3], double out[3]) {
