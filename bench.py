@@ -297,14 +297,13 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- end to end through the C ABI with pinned HOST buffers: x goes up, g and the Jacobian values come back as full
     # n x nnz arrays.  The x-independent entries of every problem are fetched once at set-up
-    # (towr_b200_batch_constant_values); each timed step moves x (H2D), g and the x-dependent entries (D2H,
-    # TOWR_B200_EVAL_JAC_DYNAMIC) and merges the latter into the full arrays on the host cores
-    # (towr_b200_batch_scatter_dynamic) - all inside the timed region.  The plain full transfer is timed next to it.
+    # (towr_b200_batch_constant_values) into the pinned n x nnz array; each timed step moves x (H2D), g and the
+    # x-dependent entries (D2H, TOWR_B200_EVAL_JAC_DYNAMIC: strided copies straight to their places in that array).  The
+    # plain full transfer is timed next to it.
     hx = [torch.from_numpy(x).pin_memory() for x in xs_host[:2]]
     hg = torch.empty((batch, st.n_rows), dtype=torch.float64).pin_memory()
     hv = torch.empty((batch, st.nnz), dtype=torch.float64).pin_memory()
-    nd = b.n_dynamic
-    hdyn = torch.empty((batch, nd), dtype=torch.float64).pin_memory()
+    nd, nd_moved = b.n_dynamic, b.dynamic_transfer_entries
     b.eval(hx[0].numpy(), T.EVAL_BOTH, g_out=hg.numpy(), jac_out=hv.numpy())
     barrier()
     t0 = time.perf_counter()
@@ -316,16 +315,15 @@ def run_ours(args, rank, world, local_rank):
     hvn = hv.numpy()
     for i in range(batch):                                        # set-up: constants of every problem, once
         hvn[i] = b.constant_values(i)
-    b.eval(hx[0].numpy(), T.EVAL_G | T.EVAL_JAC_DYNAMIC, g_out=hg.numpy(), jac_out=hdyn.numpy())
+    b.eval(hx[0].numpy(), T.EVAL_G | T.EVAL_JAC_DYNAMIC, g_out=hg.numpy(), jac_out=hvn)
     barrier()
     t0 = time.perf_counter()
     for k in range(args.e2e_steps):
-        b.eval(hx[k % 2].numpy(), T.EVAL_G | T.EVAL_JAC_DYNAMIC, g_out=hg.numpy(), jac_out=hdyn.numpy())
-        b.scatter_dynamic(hdyn.numpy(), hvn)
+        b.eval(hx[k % 2].numpy(), T.EVAL_G | T.EVAL_JAC_DYNAMIC, g_out=hg.numpy(), jac_out=hvn)
     barrier()
     e2e_s = time.perf_counter() - t0
     # both loops end on the same x: the merged arrays must be bit-identical to the full transfer
-    assert np.array_equal(hvn[:: max(1, batch // 16)], v_check), "dynamic-only transfer + scatter differs from the full transfer"
+    assert np.array_equal(hvn[:: max(1, batch // 16)], v_check), "dynamic-only transfer differs from the full transfer"
     clocks = sampler.stop()
 
     t = torch.tensor([total_ms, e2e_s, e2e_full_s], dtype=torch.float64, device=dev)
@@ -364,11 +362,11 @@ def run_ours(args, rank, world, local_rank):
                              "median_launch_ms": kern_ms, "peak_source": peak_src,
                              "algorithmic_bytes_per_launch": st.bytes_per_eval * batch},
                 "e2e": {"value": world * batch * args.e2e_steps / e2e_s, "unit": UNIT,
-                        "h2d_bytes_per_step": batch * st.n_vars * 8, "d2h_bytes_per_step": batch * (st.n_rows + nd) * 8,
+                        "h2d_bytes_per_step": batch * st.n_vars * 8, "d2h_bytes_per_step": batch * (st.n_rows + nd_moved) * 8,
                         "steps": args.e2e_steps, "ms_per_step": e2e_s / args.e2e_steps * 1e3,
-                        "api": "towr_b200_batch_eval(EVAL_G | EVAL_JAC_DYNAMIC) + towr_b200_batch_scatter_dynamic (C ABI), pinned "
-                               "host buffers; result = full n x nnz value arrays on the host (constants fetched once at set-up)",
-                        "dynamic_entries": nd, "stored_entries": st.nnz,
+                        "api": "towr_b200_batch_eval(EVAL_G | EVAL_JAC_DYNAMIC) (C ABI), pinned host buffers; result = full n x nnz "
+                               "value arrays on the host (their constant entries filled once at set-up)",
+                        "dynamic_entries": nd, "entries_copied": nd_moved, "stored_entries": st.nnz,
                         "full_transfer": {"value": world * batch * args.e2e_steps / e2e_full_s, "ms_per_step": e2e_full_s / args.e2e_steps * 1e3,
                                           "d2h_bytes_per_step": batch * (st.n_rows + st.nnz) * 8,
                                           "api": "towr_b200_batch_eval(EVAL_BOTH): every stored value crosses PCIe"}},

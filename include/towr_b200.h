@@ -34,6 +34,7 @@ extern "C" {
 #define TOWR_B200_MAX_PHASES 32
 #define TOWR_B200_MAX_CONSTRAINTS 16
 #define TOWR_B200_MAX_COSTS 4
+#define TOWR_B200_MAX_STANCES 17   /* stance phases of one foot: (MAX_PHASES + 1) / 2 */
 
 typedef enum towr_b200_status {
   TOWR_B200_OK = 0,
@@ -56,8 +57,9 @@ enum { TOWR_B200_FLAT = 0, TOWR_B200_BLOCK, TOWR_B200_STAIRS, TOWR_B200_GAP, TOW
 enum { TOWR_B200_COST_FORCES = 0, TOWR_B200_COST_EE_MOTION = 1, TOWR_B200_COST_ENERGY = 2, TOWR_B200_COST_ANG_MOM = 3 };
 /* what to evaluate */
 enum { TOWR_B200_EVAL_G = 1, TOWR_B200_EVAL_JAC = 2, TOWR_B200_EVAL_BOTH = 3,
-       /* host-buffer interface only: like EVAL_JAC, but jac_values_out receives n x n_dynamic values - the stored entries
-        * that depend on x, in the order of towr_b200_batch_dynamic_index - instead of n x nnz (towr_b200_batch_dynamic_index below) */
+       /* host-buffer interface only: like EVAL_JAC (jac_values_out is n x nnz), but only the stored entries that depend
+        * on x are brought back; the other positions of jac_values_out keep what the caller put there - the constants:
+        * a few of them, between two dynamic runs, are rewritten with that same constant (towr_b200_batch_dynamic_index) */
        TOWR_B200_EVAL_JAC_DYNAMIC = 4 };
 
 /* One NlpFormulation: the six public members of towr::NlpFormulation plus the Parameters fields
@@ -92,6 +94,14 @@ typedef struct towr_b200_spec {
   int n_costs;
   int cost_ids[TOWR_B200_MAX_COSTS];
   double cost_weights[TOWR_B200_MAX_COSTS];
+  /* params_.enable_stance_tracking / ee_stance_position_ (parameters.h:179,225; nlp_formulation.cc:218-231): the fork's
+   * default foothold bounds - x, y of the k-th stance phase of foot e fixed to ee_stance_position[e][k] instead of the
+   * start / final foothold bounds.  Bounds only: g and the Jacobian do not depend on it.  towr_b200_spec_defaults leaves
+   * it OFF (upstream behaviour); the reference's default is ON and then needs the positions (hopper_example.cc:114-122),
+   * or it throws std::out_of_range - here TOWR_B200_ERR_ARG. */
+  int enable_stance_tracking;
+  int n_stance_positions[TOWR_B200_MAX_EE];
+  double ee_stance_position[TOWR_B200_MAX_EE][TOWR_B200_MAX_STANCES][2];
 } towr_b200_spec;
 
 const char* towr_b200_last_error(void);
@@ -145,8 +155,8 @@ int towr_b200_batch_set_problem(towr_b200_batch* b, int i, const towr_b200_spec*
 int towr_b200_batch_set_all_problems(towr_b200_batch* b, const towr_b200_spec* s);
 
 /* Host-buffer evaluation (what an Ipopt callback sees).  problem_ids may be NULL (= 0..n-1).
- * x: n x n_vars row-major.  g_out: n x n_rows, jac_values_out: n x nnz (n x n_dynamic with
- * TOWR_B200_EVAL_JAC_DYNAMIC); each may be NULL when `what` does not ask for it.  Copies H2D, launches, copies D2H,
+ * x: n x n_vars row-major.  g_out: n x n_rows, jac_values_out: n x nnz (with TOWR_B200_EVAL_JAC_DYNAMIC only its
+ * x-dependent positions are written); each may be NULL when `what` does not ask for it.  Copies H2D, launches, copies D2H,
  * synchronises; large batches go through in chunks on two streams so that one chunk's D2H overlaps the next chunk's
  * H2D and kernel. */
 int towr_b200_batch_eval(towr_b200_batch* b, const int* problem_ids, int n, int what, const double* x,
@@ -162,19 +172,25 @@ int towr_b200_batch_eval_device(towr_b200_batch* b, int n, int what, const doubl
  * single_rigid_body_dynamics.cc:104-122) and, when EVERY problem of the batch is on a terrain without slope (Flat,
  * Stairs, FiveStepStairs), the terrain-basis entries of the force / torque / terrain constraints as well
  * (force_constraint_discretized.cc:146-152: b_i . J_f with constant b_i).  ANYmal trot on flat ground: 49 % of the
- * entries.  A caller on the host interface fetches them once per problem (towr_b200_batch_constant_values) and asks
- * every eval for the dynamic ones only (TOWR_B200_EVAL_JAC_DYNAMIC): that is what crosses PCIe;
- * towr_b200_batch_scatter_dynamic merges them into full n x nnz arrays.  The index depends on the terrains of the
- * batch's problems: query it after the last towr_b200_batch_set_problem. */
+ * entries.  A caller on the host interface fills its n x nnz value arrays with them once
+ * (towr_b200_batch_constant_values) and then evaluates with TOWR_B200_EVAL_JAC_DYNAMIC: every eval rewrites only the
+ * dynamic entries, in place - one strided device-to-host copy per run of consecutive dynamic entries (61 runs for ANYmal
+ * trot) - so the constants never cross PCIe again.  The index depends on the terrains of the batch's problems: fill the
+ * constants after the last towr_b200_batch_set_problem. */
 int towr_b200_batch_n_dynamic(const towr_b200_batch* b);
+/* entries per problem an EVAL_JAC_DYNAMIC eval actually copies device -> host: n_dynamic plus the constants between
+ * dynamic runs that are closer than 64 entries (they travel along so that the strided copies have long rows) */
+int towr_b200_batch_dynamic_transfer_entries(const towr_b200_batch* b);
 /* ascending storage positions (indices into the nnz stored entries) of the dynamic entries; n_dynamic ints */
 int towr_b200_batch_dynamic_index(const towr_b200_batch* b, int* index);
 /* values[nnz]: the constant entries of problem i, 0.0 at the dynamic positions (host, set-up only) */
 int towr_b200_batch_constant_values(const towr_b200_batch* b, int i, double* values);
-/* values[p * nnz + index[k]] = dynamic[p * n_dynamic + k] for p < n, on n_threads host threads (<= 0: all cores); the
- * constant positions of `values` are left as they are */
-int towr_b200_batch_scatter_dynamic(const towr_b200_batch* b, int n, const double* dynamic, double* values, int n_threads);
-/* per-problem status of the last eval: bit 0 = non-finite value in g, bit 1 = non-finite Jacobian value */
+/* Per-problem status flags, accumulated over every eval since the last call of this function (which reads and clears
+ * them): bit 1 (value 2) = a non-finite number in the problem's x, spline nodes or durations, or in one of its stored
+ * Jacobian values.  g is not scanned separately: with EVAL_G alone a finite x that produces a non-finite g (a phase
+ * duration of 0 gives 1/T^2 = inf) is only flagged through the Jacobian pass (EVAL_JAC / EVAL_BOTH); bit 0 is reserved.
+ * Indexed by launch slot: with problem_ids, flag i belongs to the i-th requested problem.  The read-out is ordered after
+ * all evals issued through this batch, including towr_b200_batch_eval_device launches on caller streams. */
 int towr_b200_batch_status(towr_b200_batch* b, int n, int* status_out);
 /* kernel launches issued by this batch so far (for bench.py's gpu_launches) */
 long long towr_b200_batch_launch_count(const towr_b200_batch* b);

@@ -60,7 +60,14 @@ static NlpFormulation MakeFormulation(const orc_spec& s) {
   p.torque_ty_min_ = s.torque_ty_min; p.torque_ty_max_ = s.torque_ty_max;
   p.torque_k_friction_ = s.torque_k_friction;
   p.bound_phase_duration_ = {s.bound_phase_duration[0], s.bound_phase_duration[1]};
-  p.enable_stance_tracking = false;
+  p.enable_stance_tracking = s.enable_stance_tracking != 0;   // orc_spec_defaults: off
+  p.ee_stance_position_.clear();
+  for (int e = 0; e < E; ++e) {
+    std::vector<std::vector<double>> pos;
+    for (int k = 0; k < s.n_stance_positions[e] && k < ORC_MAX_STANCES; ++k)
+      pos.push_back({s.ee_stance_position[e][k][0], s.ee_stance_position[e][k][1]});
+    p.ee_stance_position_.push_back(pos);
+  }
   auto dims = [](const int* flags) { std::vector<int> d; for (int i = 0; i < 3; ++i) if (flags[i]) d.push_back(i); return d; };
   p.bounds_final_lin_pos_ = dims(s.bounds_final_lin_pos);
   p.bounds_final_lin_vel_ = dims(s.bounds_final_lin_vel);

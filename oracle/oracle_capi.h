@@ -13,6 +13,7 @@ extern "C" {
 #define ORC_MAX_PHASES 32
 #define ORC_MAX_CONSTRAINTS 16
 #define ORC_MAX_COSTS 4
+#define ORC_MAX_STANCES 17
 
 /* The public members of towr::NlpFormulation (nlp_formulation.h:100-105) plus the
  * fields of towr::Parameters (parameters.h:135-336) the hot path reads. */
@@ -46,6 +47,10 @@ typedef struct orc_spec {
   int n_costs;
   int cost_ids[ORC_MAX_COSTS];
   double cost_weights[ORC_MAX_COSTS];
+  /* Parameters::enable_stance_tracking, ee_stance_position_ (parameters.h:179,225) */
+  int enable_stance_tracking;
+  int n_stance_positions[ORC_MAX_EE];
+  double ee_stance_position[ORC_MAX_EE][ORC_MAX_STANCES][2];
 } orc_spec;
 
 /* Parameters::Parameters() defaults (parameters.cc:40-105), enable_stance_tracking=false. */

@@ -56,6 +56,9 @@ class Spec(C.Structure):
         ("n_costs", C.c_int),
         ("cost_ids", C.c_int * 4),
         ("cost_weights", C.c_double * 4),
+        ("enable_stance_tracking", C.c_int),
+        ("n_stance_positions", C.c_int * MAX_EE),
+        ("ee_stance_position", ((C.c_double * 2) * 17) * MAX_EE),
     ]
 
 

@@ -107,8 +107,8 @@ def test_eval_modes_and_ids(product, oracle):
 @pytest.mark.parametrize("name", ["anymal_trot", "anymal_trot_durations", "monoped_hop_torque", "anymal_walk_slope",
                                   "anymal_trot_force_nodes_slope", "biped_walk_stairs"])
 def test_dynamic_only_mode_equals_full_mode(product, name):
-    """TOWR_B200_EVAL_JAC_DYNAMIC: constants once (towr_b200_problem_constant_values) + the dynamic entries of every eval,
-    scattered on the host, are bit-identical to the full n x nnz result; chunked evals equal unchunked ones."""
+    """TOWR_B200_EVAL_JAC_DYNAMIC: constants once (towr_b200_batch_constant_values) + the dynamic entries of every eval,
+    written in place, are bit-identical to the full n x nnz result; chunked evals equal unchunked ones."""
     import os
     T = product
     case = [c for c in CASES if c[0] == name][0]
@@ -122,21 +122,27 @@ def test_dynamic_only_mode_equals_full_mode(product, name):
     assert 0 < b.n_dynamic < st.nnz and (np.diff(idx) > 0).all()
     if name == "anymal_trot":                     # flat ground: the force constraint's basis entries are constants too
         assert b.n_dynamic < 0.55 * st.nnz
-    g2, dyn = b.eval(x, T.EVAL_G | T.EVAL_JAC_DYNAMIC)
-    assert np.array_equal(g2, g) and dyn.shape == (n, b.n_dynamic)
-    full = np.stack([b.constant_values(i) for i in range(n)])
     const_mask = np.ones(st.nnz, bool)
     const_mask[idx] = False
+    full = np.stack([b.constant_values(i) for i in range(n)])
     assert np.array_equal(full[:, const_mask], v[:, const_mask])      # the constants are what the kernel stores
-    b.scatter_dynamic(dyn, full, n_threads=3)
-    assert np.array_equal(full, v)
+    assert not full[:, ~const_mask].any()
+    g2, _ = b.eval(x, T.EVAL_G | T.EVAL_JAC_DYNAMIC, jac_out=full)      # rewrites the dynamic positions in place
+    assert np.array_equal(g2, g) and np.array_equal(full, v)
+    poison = np.full((n, st.nnz), np.nan)                               # constants: untouched, or rewritten with themselves
+    b.eval(x, T.EVAL_JAC_DYNAMIC, jac_out=poison)
+    assert np.array_equal(poison[:, ~const_mask], v[:, ~const_mask])
+    touched = ~np.isnan(poison)
+    assert np.array_equal(poison[touched], v[touched])
+    assert int(touched[0].sum()) == b.dynamic_transfer_entries
     os.environ["TOWR_B200_CHUNK"] = "8"                                 # 5 chunks, alternating streams, ragged last one
     try:
         g3, v3 = b.eval(x)
-        _, dyn3 = b.eval(x, T.EVAL_JAC_DYNAMIC)
+        full3 = np.stack([b.constant_values(i) for i in range(n)])
+        b.eval(x, T.EVAL_JAC_DYNAMIC, jac_out=full3)
     finally:
         del os.environ["TOWR_B200_CHUNK"]
-    assert np.array_equal(g3, g) and np.array_equal(v3, v) and np.array_equal(dyn3, dyn)
+    assert np.array_equal(g3, g) and np.array_equal(v3, v) and np.array_equal(full3, v)
 
 
 def test_full_batch_properties(product, oracle):

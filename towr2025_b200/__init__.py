@@ -62,6 +62,9 @@ class Spec(C.Structure):
         ("n_costs", C.c_int),
         ("cost_ids", C.c_int * 4),
         ("cost_weights", C.c_double * 4),
+        ("enable_stance_tracking", C.c_int),
+        ("n_stance_positions", C.c_int * MAX_EE),
+        ("ee_stance_position", ((C.c_double * 2) * 17) * MAX_EE),
     ]
 
     def copy(self):
@@ -97,7 +100,7 @@ towr_b200_batch_eval towr_b200_batch_eval_device towr_b200_batch_status towr_b20
 towr_b200_batch_stream towr_b200_trajectory_width towr_b200_trajectory_samples towr_b200_batch_sample_trajectory
 towr_b200_batch_sample_trajectory_device towr_b200_trajectory_write_csv towr_b200_batch_eval_cost
 towr_b200_batch_eval_cost_device towr_b200_eval_cost_static towr_b200_batch_n_dynamic
-towr_b200_batch_dynamic_index towr_b200_batch_constant_values towr_b200_batch_scatter_dynamic""".split()
+towr_b200_batch_dynamic_index towr_b200_batch_constant_values towr_b200_batch_dynamic_transfer_entries""".split()
 
 
 def lib():
@@ -127,9 +130,9 @@ def lib():
         getattr(L, "towr_b200_structure_" + f).argtypes = [vp, C.c_int]
     L.towr_b200_structure_pattern.argtypes = [vp, ip, ip]
     L.towr_b200_batch_n_dynamic.argtypes = [vp]
+    L.towr_b200_batch_dynamic_transfer_entries.argtypes = [vp]
     L.towr_b200_batch_dynamic_index.argtypes = [vp, ip]
     L.towr_b200_batch_constant_values.argtypes = [vp, C.c_int, dp]
-    L.towr_b200_batch_scatter_dynamic.argtypes = [vp, C.c_int, dp, dp, C.c_int]
     L.towr_b200_structure_accepts.argtypes = [vp, sp]
     L.towr_b200_problem_x0.argtypes = [vp, sp, dp]
     L.towr_b200_problem_var_bounds.argtypes = [vp, sp, dp, dp]
@@ -303,8 +306,10 @@ class Batch:
         v = None
         if what & EVAL_JAC:
             v = jac_out if jac_out is not None else np.empty((n, st.nnz))
-        elif what & EVAL_JAC_DYNAMIC:           # the x-dependent entries only, n x n_dynamic
-            v = jac_out if jac_out is not None else np.empty((n, self.n_dynamic))
+        elif what & EVAL_JAC_DYNAMIC:           # only the x-dependent positions of the n x nnz array are written
+            if jac_out is None:                 # convenience: start from the constants of problems 0..n-1
+                jac_out = np.stack([self.constant_values(i if ids is None else int(ids[i])) for i in range(n)])
+            v = jac_out
         idp = None
         if ids is not None:
             ids = np.ascontiguousarray(ids, dtype=np.int32)
@@ -345,6 +350,11 @@ class Batch:
         """Stored Jacobian entries that depend on x for this batch (towr_b200_batch_n_dynamic)."""
         return self._L.towr_b200_batch_n_dynamic(self._h)
 
+    @property
+    def dynamic_transfer_entries(self):
+        """Entries per problem an EVAL_JAC_DYNAMIC eval copies back (towr_b200_batch_dynamic_transfer_entries)."""
+        return self._L.towr_b200_batch_dynamic_transfer_entries(self._h)
+
     def dynamic_index(self):
         idx = np.empty(self.n_dynamic, np.int32)
         _check(self._L.towr_b200_batch_dynamic_index(self._h, _ip(idx)))
@@ -355,12 +365,6 @@ class Batch:
         v = np.empty(self.structure.nnz)
         _check(self._L.towr_b200_batch_constant_values(self._h, i, _dp(v)))
         return v
-
-    def scatter_dynamic(self, dynamic, values, n_threads=0):
-        """values[p, dynamic_index] = dynamic[p] for every problem row (towr_b200_scatter_dynamic), in place."""
-        assert dynamic.flags.c_contiguous and values.flags.c_contiguous and dynamic.shape[0] == values.shape[0]
-        assert dynamic.shape[1] == self.n_dynamic and values.shape[1] == self.structure.nnz
-        _check(self._L.towr_b200_batch_scatter_dynamic(self._h, dynamic.shape[0], _dp(dynamic), _dp(values), n_threads))
 
     def status(self, n=None):
         n = self.n if n is None else n

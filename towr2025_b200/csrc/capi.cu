@@ -12,7 +12,6 @@
 #include <memory>
 #include <stdexcept>
 #include <string>
-#include <thread>
 #include <type_traits>
 #include <vector>
 
@@ -83,6 +82,10 @@ struct towr_b200_batch {
   int n = 0, device = 0;
   cudaStream_t stream = nullptr, stream2 = nullptr;   // host-buffer evals alternate their chunks between the two
   cudaEvent_t consts_ready = nullptr;
+  // eval_device launches on caller streams read pc_dev / write status_dev: the last one's completion, so that a later
+  // H2D of the constants or a status read-out is ordered after it
+  cudaEvent_t device_eval_done = nullptr;
+  bool device_eval_pending = false;
   tb::DeviceProgram dp{};
   std::vector<void*> owned;            // device allocations
   std::vector<tb::ProblemConst> pc_host;
@@ -90,16 +93,20 @@ struct towr_b200_batch {
   bool pc_dirty = true;
   int* status_dev = nullptr;
   // staging for the host-buffer path
-  double *x_dev = nullptr, *g_dev = nullptr, *v_dev = nullptr, *dyn_dev = nullptr;
-  int* dyn_idx_dev = nullptr;
-  int n_dynamic = 0;
+  double *x_dev = nullptr, *g_dev = nullptr, *v_dev = nullptr;
   tb::ProblemConst* pc_gather_dev = nullptr;
   int max_ctas = 0;
   tb::EvalVariant var{0, 1, false, 0};   // kernel variant (kernels.h); lanes = 0 until chosen
   std::unique_ptr<tb::HostProgram> hp_local;   // program rebuilt with a smaller G capacity (large class tables)
   long long launches = 0;
   // trajectory sampler tables per sampling period (trajectory.h)
-  struct Traj { tb::TrajTables host; tb::TrajDevice dev; };
+  struct Traj {                        // owns its device tables (freed when the entry is evicted or the batch dies)
+    tb::TrajTables host;
+    tb::TrajDevice dev;
+    std::vector<void*> owned;
+    ~Traj() { for (void* p : owned) cudaFree(p); }
+  };
+  static constexpr size_t kMaxTrajTables = 8;   // sampling periods cached per batch
   std::map<double, std::unique_ptr<Traj>> traj;
   double* traj_out_dev = nullptr;
   size_t traj_out_cap = 0;
@@ -110,13 +117,17 @@ struct towr_b200_batch {
 
   void SyncConsts() {
     if (!pc_dirty) return;
+    if (device_eval_pending) Check(cudaStreamWaitEvent(stream, device_eval_done, 0), "order consts after eval_device");
     Check(cudaMemcpyAsync(pc_dev, pc_host.data(), sizeof(tb::ProblemConst) * n, cudaMemcpyHostToDevice, stream), "H2D consts");
     pc_dirty = false;
   }
   ~towr_b200_batch() {
     cudaSetDevice(device);
     for (void* p : owned) cudaFree(p);
+    if (traj_out_dev) cudaFree(traj_out_dev);
+    traj.clear();
     if (consts_ready) cudaEventDestroy(consts_ready);
+    if (device_eval_done) cudaEventDestroy(device_eval_done);
     if (stream2) cudaStreamDestroy(stream2);
     if (stream) cudaStreamDestroy(stream);
   }
@@ -218,6 +229,7 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     Check(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking), "cudaStreamCreate");
     Check(cudaStreamCreateWithFlags(&b->stream2, cudaStreamNonBlocking), "cudaStreamCreate");
     Check(cudaEventCreateWithFlags(&b->consts_ready, cudaEventDisableTiming), "cudaEventCreate");
+    Check(cudaEventCreateWithFlags(&b->device_eval_done, cudaEventDisableTiming), "cudaEventCreate");
     cudaDeviceProp prop;
     Check(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
     // The class tables, one problem's spline arrays and one G buffer must fit the SM's shared memory.  Classes with many
@@ -351,10 +363,33 @@ const std::vector<int>& DynIndex(const towr_b200_batch* b) {
   const tb::HostProgram& hp = b->st->hp;
   return FlatBasis(b) ? hp.dyn_index_flat : hp.dyn_index;
 }
+// Rows of the EVAL_JAC_DYNAMIC transfer: runs of x-dependent entries.  Runs separated by fewer than kMergeGap constant
+// entries travel as one row: short rows make poor DMA (measured: 61 rows of 0.3-1 KB per problem reach 38 GB/s, the
+// merged rows the link's rate); the constants in between are rewritten with the value the kernel stores for them, which
+// is the constant itself.
+struct DynRun { int pos, len; };
+std::vector<DynRun> DynRuns(const towr_b200_batch* b) {
+  constexpr int kMergeGap = 64;
+  std::vector<DynRun> runs;
+  const std::vector<int>& idx = DynIndex(b);
+  for (size_t k = 0; k < idx.size();) {
+    size_t e = k + 1;
+    while (e < idx.size() && idx[e] - idx[e - 1] <= kMergeGap) ++e;
+    runs.push_back(DynRun{idx[k], idx[e - 1] - idx[k] + 1});
+    k = e;
+  }
+  return runs;
+}
 }  // namespace
 extern "C" {
 
 int towr_b200_batch_n_dynamic(const towr_b200_batch* b) { return b ? static_cast<int>(DynIndex(b).size()) : -1; }
+int towr_b200_batch_dynamic_transfer_entries(const towr_b200_batch* b) {
+  if (!b) return -1;
+  int n = 0;
+  for (const DynRun& r : DynRuns(b)) n += r.len;
+  return n;
+}
 int towr_b200_batch_dynamic_index(const towr_b200_batch* b, int* index) {
   return Guard([&] {
     if (!b || !index) throw std::runtime_error("null argument");
@@ -368,38 +403,6 @@ int towr_b200_batch_constant_values(const towr_b200_batch* b, int i, double* val
     tb::ProblemConstantValues(b->st->hp, b->pc_host[i].mass, b->st->spec.torque_k_friction, FlatBasis(b), values);
   });
 }
-int towr_b200_batch_scatter_dynamic(const towr_b200_batch* b, int n, const double* dynamic, double* values, int n_threads) {
-  return Guard([&] {
-    if (!b || n < 0 || n > b->n || !dynamic || !values) throw std::runtime_error("bad argument to scatter_dynamic");
-    const std::vector<int>& idx = DynIndex(b);
-    const size_t nd = idx.size(), nnz = static_cast<size_t>(b->st->hp.nnz);
-    // runs of consecutive dynamic entries: one memcpy each
-    struct Run { int dst, src, len; };
-    std::vector<Run> runs;
-    for (size_t k = 0; k < nd;) {
-      size_t e = k + 1;
-      while (e < nd && idx[e] == idx[e - 1] + 1) ++e;
-      runs.push_back(Run{idx[k], static_cast<int>(k), static_cast<int>(e - k)});
-      k = e;
-    }
-    auto work = [&](int p0, int p1) {
-      for (int p = p0; p < p1; ++p) {
-        const double* src = dynamic + static_cast<size_t>(p) * nd;
-        double* dst = values + static_cast<size_t>(p) * nnz;
-        for (const Run& r : runs) std::memcpy(dst + r.dst, src + r.src, sizeof(double) * static_cast<size_t>(r.len));
-      }
-    };
-    int nt = n_threads > 0 ? n_threads : static_cast<int>(std::thread::hardware_concurrency());
-    if (nt < 1) nt = 1;
-    if (nt > n) nt = n > 0 ? n : 1;
-    if (nt == 1) { work(0, n); return; }
-    std::vector<std::thread> pool;
-    for (int t = 0; t < nt; ++t)
-      pool.emplace_back(work, static_cast<int>(static_cast<long long>(n) * t / nt), static_cast<int>(static_cast<long long>(n) * (t + 1) / nt));
-    for (auto& th : pool) th.join();
-  });
-}
-
 int towr_b200_batch_eval_device(towr_b200_batch* b, int n, int what, const double* d_x, double* d_g,
                                 double* d_jac_values, void* stream) {
   return Guard([&] {
@@ -414,6 +417,8 @@ int towr_b200_batch_eval_device(towr_b200_batch* b, int n, int what, const doubl
       Check(cudaStreamSynchronize(b->stream), "sync consts");
     }
     Check(tb::LaunchEval(b->dp, b->pc_dev, what, d_x, d_g, d_jac_values, b->status_dev, n, b->var, b->max_ctas, s), "launch");
+    Check(cudaEventRecord(b->device_eval_done, s), "record eval_device");
+    b->device_eval_pending = true;
     b->launches += 1;
   });
 }
@@ -440,19 +445,10 @@ int towr_b200_batch_eval(towr_b200_batch* b, const int* ids, int n, int what, co
     ensure(b->x_dev, dp.n_vars);
     if (want_g) ensure(b->g_dev, dp.n_rows);
     if (want_jac || want_dyn) ensure(b->v_dev, dp.nnz);
-    const std::vector<int>& dyn_index = DynIndex(b);
-    const size_t nd = dyn_index.size();
-    if (want_dyn && nd > 0) {
-      ensure(b->dyn_dev, b->st->hp.dyn_index.size());          // sized for the general index (>= the flat one)
-      if (!b->dyn_idx_dev) {
-        Check(cudaMalloc(&b->dyn_idx_dev, sizeof(int) * b->st->hp.dyn_index.size()), "cudaMalloc(dynamic index)");
-        b->owned.push_back(b->dyn_idx_dev);
-      }
-      if (b->n_dynamic != static_cast<int>(nd)) {               // first use, or the batch's terrains changed
-        Check(cudaMemcpy(b->dyn_idx_dev, dyn_index.data(), sizeof(int) * nd, cudaMemcpyHostToDevice), "H2D dynamic index");
-        b->n_dynamic = static_cast<int>(nd);
-      }
-    }
+    // EVAL_JAC_DYNAMIC: runs of consecutive x-dependent entries; each goes back with one strided copy for all problems of
+    // a chunk, straight to its place in the caller's n x nnz array (whose constant entries the caller filled once)
+    std::vector<DynRun> runs;
+    if (want_dyn) runs = DynRuns(b);
     const tb::ProblemConst* pcs = b->pc_dev;
     if (ids) {
       // gather the constants of the requested problems (the callers' x rows are already in request order)
@@ -483,16 +479,13 @@ int towr_b200_batch_eval(towr_b200_batch* b, const int* ids, int n, int what, co
       Check(tb::LaunchEval(dp, pcs + c0, kernel_what, b->x_dev + o * dp.n_vars, want_g ? b->g_dev + o * dp.n_rows : nullptr,
                            (want_jac || want_dyn) ? b->v_dev + o * dp.nnz : nullptr, b->status_dev + c0, m, b->var, b->max_ctas, st), "launch");
       b->launches += 1;
-      if (want_dyn && nd > 0) {
-        Check(tb::LaunchCompact(b->v_dev + o * dp.nnz, b->dyn_idx_dev, b->dyn_dev + o * nd, dp.nnz, static_cast<int>(nd), m, st), "launch compact");
-        b->launches += 1;
-      }
       if (want_g)
         Check(cudaMemcpyAsync(g_out + o * dp.n_rows, b->g_dev + o * dp.n_rows, sizeof(double) * dp.n_rows * m, cudaMemcpyDeviceToHost, st), "D2H g");
       if (want_jac)
         Check(cudaMemcpyAsync(jac_out + o * dp.nnz, b->v_dev + o * dp.nnz, sizeof(double) * dp.nnz * m, cudaMemcpyDeviceToHost, st), "D2H values");
-      if (want_dyn && nd > 0)
-        Check(cudaMemcpyAsync(jac_out + o * nd, b->dyn_dev + o * nd, sizeof(double) * nd * m, cudaMemcpyDeviceToHost, st), "D2H dynamic values");
+      for (const DynRun& r : runs)
+        Check(cudaMemcpy2DAsync(jac_out + o * dp.nnz + r.pos, sizeof(double) * dp.nnz, b->v_dev + o * dp.nnz + r.pos, sizeof(double) * dp.nnz,
+                                sizeof(double) * r.len, m, cudaMemcpyDeviceToHost, st), "D2H dynamic values");
     }
     Check(cudaStreamSynchronize(b->stream), "eval");
     Check(cudaStreamSynchronize(b->stream2), "eval");
@@ -503,8 +496,13 @@ int towr_b200_batch_status(towr_b200_batch* b, int n, int* status_out) {
   return Guard([&] {
     if (!b || n < 0 || n > b->n || !status_out) throw std::runtime_error("bad argument");
     Check(cudaSetDevice(b->device), "cudaSetDevice");
-    Check(cudaMemcpy(status_out, b->status_dev, sizeof(int) * n, cudaMemcpyDeviceToHost), "D2H status");
-    Check(cudaMemset(b->status_dev, 0, sizeof(int) * n), "reset status");
+    // ordered after every eval that may still be writing the flags: host-buffer evals have synchronised already, the
+    // last eval_device launch (on a caller stream) is waited for through its event
+    if (b->device_eval_pending) Check(cudaStreamWaitEvent(b->stream, b->device_eval_done, 0), "order status after eval_device");
+    Check(cudaMemcpyAsync(status_out, b->status_dev, sizeof(int) * n, cudaMemcpyDeviceToHost, b->stream), "D2H status");
+    Check(cudaMemsetAsync(b->status_dev, 0, sizeof(int) * n, b->stream), "reset status");
+    Check(cudaStreamSynchronize(b->stream), "status");
+    b->device_eval_pending = false;
   });
 }
 
@@ -608,11 +606,11 @@ int towr_b200_trajectory_samples(const towr_b200_structure* st, double dt) {
 
 namespace {
 template <class T>
-const T* UploadVec(towr_b200_batch* b, const std::vector<T>& v) {
+const T* UploadVec(std::vector<void*>& owned, const std::vector<T>& v) {
   if (v.empty()) return nullptr;
   T* d = nullptr;
   Check(cudaMalloc(&d, sizeof(T) * v.size()), "cudaMalloc(trajectory tables)");
-  b->owned.push_back(d);
+  owned.push_back(d);
   Check(cudaMemcpy(d, v.data(), sizeof(T) * v.size(), cudaMemcpyHostToDevice), "H2D trajectory tables");
   return d;
 }
@@ -628,20 +626,26 @@ const towr_b200_batch::Traj& TrajFor(towr_b200_batch* b, double dt) {
   d.n_splines = static_cast<int>(h.splines.size());
   d.n_nodes = h.n_nodes; d.n_polys = h.n_polys; d.n_phases = h.n_phases; d.rt = h.rt ? 1 : 0;
   d.total_time = h.total_time;
-  d.times = UploadVec(b, h.times);
-  d.splines = UploadVec(b, h.splines);
-  d.feet = UploadVec(b, h.feet);
-  d.node_src = UploadVec(b, h.node_src);
-  d.poly_T = UploadVec(b, h.poly_T);
-  d.poly_meta = UploadVec(b, h.poly_meta);
-  d.poly_spline = UploadVec(b, h.poly_spline);
-  d.samp_poly = UploadVec(b, h.samp_poly);
-  d.samp_t = UploadVec(b, h.samp_t);
-  d.contact = UploadVec(b, h.contact);
+  d.times = UploadVec(t->owned, h.times);
+  d.splines = UploadVec(t->owned, h.splines);
+  d.feet = UploadVec(t->owned, h.feet);
+  d.node_src = UploadVec(t->owned, h.node_src);
+  d.poly_T = UploadVec(t->owned, h.poly_T);
+  d.poly_meta = UploadVec(t->owned, h.poly_meta);
+  d.poly_spline = UploadVec(t->owned, h.poly_spline);
+  d.samp_poly = UploadVec(t->owned, h.samp_poly);
+  d.samp_t = UploadVec(t->owned, h.samp_t);
+  d.contact = UploadVec(t->owned, h.contact);
   cudaDeviceProp prop;
   Check(cudaGetDeviceProperties(&prop, b->device), "cudaGetDeviceProperties");
   if (tb::TrajSharedBytes(d) > prop.sharedMemPerBlockOptin)
     throw std::runtime_error("unsupported: the problem's spline tables exceed the SM's shared memory");
+  if (b->traj.size() >= towr_b200_batch::kMaxTrajTables) {
+    // evict one cached sampling period (its kernels have completed: the sampler entry points synchronise or run on a
+    // caller stream the caller is responsible for; be safe and drain the device first)
+    Check(cudaDeviceSynchronize(), "sync before evicting trajectory tables");
+    b->traj.erase(b->traj.begin());
+  }
   return *(b->traj[dt] = std::move(t));
 }
 }  // namespace
@@ -675,9 +679,13 @@ int towr_b200_batch_sample_trajectory(towr_b200_batch* b, int n, double dt, cons
       b->owned.push_back(b->x_dev);
     }
     if (b->traj_out_cap < per * n) {
+      if (b->traj_out_dev) {                               // superseded: the previous call synchronised, nothing reads it
+        Check(cudaFree(b->traj_out_dev), "cudaFree(trajectory rows)");
+        b->traj_out_dev = nullptr;
+        b->traj_out_cap = 0;
+      }
       double* p = nullptr;
       Check(cudaMalloc(&p, sizeof(double) * per * b->n), "cudaMalloc(trajectory rows)");
-      b->owned.push_back(p);
       b->traj_out_dev = p;
       b->traj_out_cap = per * b->n;
     }

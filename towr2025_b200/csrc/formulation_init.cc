@@ -146,9 +146,24 @@ void ProblemVarBounds(const HostProgram& hp, const towr_b200_spec& s, double* L,
         fix(v, last, 0, s.bounds_final_ang_pos, s.final_base_ang);
         fix(v, last, 1, s.bounds_final_ang_vel, s.final_base_ang + 3);
         break;
-      case kEEMotion:      // enable_stance_tracking = false branch (nlp_formulation.cc:232-236)
-        fix(v, 0, 0, nullptr, s.initial_ee_W[v.ee]);
-        fix(v, last, 0, nullptr, d.ee_final[v.ee].v);
+      case kEEMotion:
+        if (s.enable_stance_tracking) {                    // nlp_formulation.cc:218-231
+          int stance_id = 0;
+          for (int phase = 0; phase < s.n_phases[v.ee]; ++phase) {
+            const int node = v.PolyAtStartOfPhase(phase);  // GetNodeIDAtStartOfPhase: start node of that polynomial
+            if (!v.IsConstantNode(node)) continue;
+            if (stance_id >= s.n_stance_positions[v.ee] || stance_id >= TOWR_B200_MAX_STANCES)
+              throw std::out_of_range("ee_stance_position_ has fewer entries than the foot has stance phases (enable_stance_tracking)");
+            const double pos[3] = {s.ee_stance_position[v.ee][stance_id][0], s.ee_stance_position[v.ee][stance_id][1], 0.0};
+            const int xy[3] = {1, 1, 0};
+            fix(v, node, 0, xy, pos);
+            ++stance_id;
+            ++phase;                                       // the reference skips the phase after a bounded one (:229)
+          }
+        } else {                                           // :232-236
+          fix(v, 0, 0, nullptr, s.initial_ee_W[v.ee]);
+          fix(v, last, 0, nullptr, d.ee_final[v.ee].v);
+        }
         break;
       case kEEAng:
         fix(v, 0, 0, nullptr, s.initial_base_ang);

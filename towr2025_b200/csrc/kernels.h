@@ -20,8 +20,6 @@ size_t EvalSharedBytes(const DeviceProgram& P, int lanes, int streams = 1, bool 
 // evaluates problems 0..n_problems-1; x, g, vals, status are device pointers on the current device
 cudaError_t LaunchEval(const DeviceProgram& P, const ProblemConst* pcs, int what, const double* x, double* g,
                        double* vals, int* status, int n_problems, const EvalVariant& v, int max_ctas, cudaStream_t stream);
-// dyn[p][k] = vals[p][idx[k]] for p < n (compact.cu)
-cudaError_t LaunchCompact(const double* vals, const int* idx, double* dyn, int nnz, int nd, int n, cudaStream_t stream);
 // resident CTAs per SM of the evaluation kernel for this program and variant (0: does not fit)
 int EvalOccupancy(const DeviceProgram& P, const EvalVariant& v);
 }  // namespace tb

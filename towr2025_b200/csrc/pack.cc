@@ -203,6 +203,17 @@ void PackProgram(HostProgram& hp) {
       if (hp.entry_code[e] < 0) hp.dyn_index_flat.push_back(static_cast<int>(e));
     }
   }
+  if (std::getenv("TOWR_B200_DEBUG")) {
+    auto runs = [](const std::vector<int>& v) { int r = v.empty() ? 0 : 1; for (size_t i = 1; i < v.size(); ++i) r += v[i] != v[i - 1] + 1; return r; };
+    std::fprintf(stderr, "dynamic entries: %zu of %zu in %d runs; on zero-slope terrains %zu in %d runs\n", hp.dyn_index.size(),
+                 hp.entries.size(), runs(hp.dyn_index), hp.dyn_index_flat.size(), runs(hp.dyn_index_flat));
+    if (std::atoi(std::getenv("TOWR_B200_DEBUG")) > 1) {
+      const std::vector<int>& v = hp.dyn_index_flat;
+      std::fprintf(stderr, "flat runs (pos:len):");
+      for (size_t k = 0; k < v.size();) { size_t e = k + 1; while (e < v.size() && v[e] == v[e - 1] + 1) ++e; std::fprintf(stderr, " %d:%zu", v[k], e - k); k = e; }
+      std::fprintf(stderr, "\n");
+    }
+  }
   // device descriptors: byte offsets, so that stage B needs no index scaling
   hp.entries_dev.clear();
   hp.entries_dev.reserve(hp.entries.size());
