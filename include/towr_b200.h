@@ -26,6 +26,8 @@
 #ifndef TOWR_B200_H_
 #define TOWR_B200_H_
 
+#include <stddef.h>
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -194,6 +196,12 @@ int towr_b200_batch_constant_values(const towr_b200_batch* b, int i, double* val
 int towr_b200_batch_status(towr_b200_batch* b, int n, int* status_out);
 /* kernel launches issued by this batch so far (for bench.py's gpu_launches) */
 long long towr_b200_batch_launch_count(const towr_b200_batch* b);
+/* page-locked (pinned) host memory, visible to every device: host buffers handed to towr_b200_batch_eval copy at the full
+ * PCIe rate and asynchronously only from such memory (the callback coalescer stages its requests in it) */
+int towr_b200_host_alloc(size_t bytes, void** out);
+void towr_b200_host_free(void* p);
+/* human-readable description of the kernel instantiation and launch geometry this batch uses (for logs / bench.py) */
+int towr_b200_batch_kernel_info(const towr_b200_batch* b, char* buf, int n);
 /* the batch's own non-blocking cudaStream_t (the one towr_b200_batch_eval works on) */
 void* towr_b200_batch_stream(const towr_b200_batch* b);
 

@@ -20,8 +20,12 @@ def build(name="ifopt_surface"):
     newest = max([os.path.getmtime(src), os.path.getmtime(os.path.join(lib_dir, "libtowr_b200.so"))] +
                  [os.path.getmtime(h) for h in hdrs])
     if not os.path.exists(exe) or os.path.getmtime(exe) < newest:
+        from oracle import oracle_py as O      # TEST INFRASTRUCTURE: the coalescer test checks values against the oracle
+        O.lib()
+        orc_dir = os.path.join(ROOT, "oracle", "_build")
         subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-pthread", "-I", os.path.join(ROOT, "include"), src,
-                               "-o", exe, "-L", lib_dir, "-ltowr_b200", "-Wl,-rpath," + lib_dir])
+                               "-o", exe, "-L", lib_dir, "-ltowr_b200", "-Wl,-rpath," + lib_dir,
+                               "-L", orc_dir, "-loracle", "-Wl,-rpath," + orc_dir, "-fopenmp"])
     return exe
 
 
@@ -93,3 +97,20 @@ def test_callback_coalescer_on_gpu():
     out = subprocess.run([build("coalescer"), "gpu"], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout + out.stderr
     assert "ok" in out.stdout
+
+
+def test_callback_coalescer_survives_failures():
+    """An evaluator that throws and a staging allocation that fails reach the waiting solver threads as exceptions; nobody
+    stays blocked (the timeout is the deadlock detector)."""
+    out = subprocess.run([build("coalescer"), "throw"], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "ok" in out.stdout
+
+
+@pytest.mark.gpu
+def test_callback_coalescer_values_match_oracle_on_gpu():
+    """GPU leg: every g row and every stored Jacobian value each solver thread receives is compared with the oracle."""
+    out = subprocess.run([build("coalescer"), "gpu"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    line = [l for l in out.stdout.splitlines() if l.startswith("oracle_checks")][0].split()
+    assert int(line[1]) > 100 and float(line[3]) <= 1.0 and float(line[5]) <= 4.0

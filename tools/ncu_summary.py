@@ -76,7 +76,9 @@ def main():
         out.append("The torch elementwise/reduce kernels are bench.py's own `isfinite` sanity check after the timed "
                    "region and its input upload; inside the timed region only EvalKernel launches.")
     open(os.path.join(ROOT, "profiles", "%s_ncu_summary.md" % tag), "w").write("\n".join(out) + "\n")
-    json.dump({"dram_bytes_per_launch": traffic, "source": os.path.basename(rep), "tag": tag},
+    commit = subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
+    json.dump({"dram_bytes_per_launch": traffic, "source": os.path.basename(rep), "tag": tag, "commit": commit, "workload": "anymal_trot",
+               "kernel": vals[hdr.index("Kernel Name")] if "Kernel Name" in hdr else "EvalKernel"},
               open(os.path.join(ROOT, "profiles", "traffic.json"), "w"))
     print("\n".join(out))
 

@@ -100,7 +100,7 @@ towr_b200_batch_eval towr_b200_batch_eval_device towr_b200_batch_status towr_b20
 towr_b200_batch_stream towr_b200_trajectory_width towr_b200_trajectory_samples towr_b200_batch_sample_trajectory
 towr_b200_batch_sample_trajectory_device towr_b200_trajectory_write_csv towr_b200_batch_eval_cost
 towr_b200_batch_eval_cost_device towr_b200_eval_cost_static towr_b200_batch_n_dynamic
-towr_b200_batch_dynamic_index towr_b200_batch_constant_values towr_b200_batch_dynamic_transfer_entries""".split()
+towr_b200_batch_dynamic_index towr_b200_batch_constant_values towr_b200_batch_dynamic_transfer_entries towr_b200_batch_kernel_info towr_b200_host_alloc towr_b200_host_free""".split()
 
 
 def lib():
@@ -154,6 +154,7 @@ def lib():
     L.towr_b200_batch_sample_trajectory.argtypes = [vp, C.c_int, C.c_double, dp, dp]
     L.towr_b200_batch_sample_trajectory_device.argtypes = [vp, C.c_int, C.c_double, vp, vp, vp]
     L.towr_b200_trajectory_write_csv.argtypes = [vp, dp, C.c_int, C.c_char_p]
+    L.towr_b200_batch_kernel_info.argtypes = [vp, C.c_char_p, C.c_int]
     L.towr_b200_batch_launch_count.argtypes = [vp]
     L.towr_b200_batch_launch_count.restype = C.c_longlong
     L.towr_b200_batch_stream.argtypes = [vp]
@@ -371,6 +372,12 @@ class Batch:
         s = np.empty(n, np.int32)
         _check(self._L.towr_b200_batch_status(self._h, n, _ip(s)))
         return s
+
+    @property
+    def kernel_info(self):
+        buf = C.create_string_buffer(512)
+        _check(self._L.towr_b200_batch_kernel_info(self._h, buf, 512))
+        return buf.value.decode()
 
     @property
     def launches(self):

@@ -729,7 +729,27 @@ int towr_b200_trajectory_write_csv(const towr_b200_structure* st, const double* 
   });
 }
 
+int towr_b200_host_alloc(size_t bytes, void** out) {
+  return Guard([&] {
+    if (!out) throw std::runtime_error("null argument");
+    *out = nullptr;
+    if (towr_b200_device_count() < 1) throw CudaError("no CUDA device visible");
+    Check(cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocPortable), "cudaHostAlloc");
+  });
+}
+void towr_b200_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
 long long towr_b200_batch_launch_count(const towr_b200_batch* b) { return b ? b->launches : 0; }
+int towr_b200_batch_kernel_info(const towr_b200_batch* b, char* buf, int n) {
+  return Guard([&] {
+    if (!b || !buf || n < 1) throw std::runtime_error("bad argument");
+    std::snprintf(buf, static_cast<size_t>(n), "tb::EvalKernel<lanes=%d, optimised_durations=%d, streams=%d, ring=%d, curvature=%d>: "
+                  "%d CTAs x %d threads, %zu B shared, %d segments", b->var.lanes, b->dp.blob.rt, b->var.streams, b->var.ring ? 1 : 0,
+                  b->dp.curvature_dims != 0, b->max_ctas, 256 * b->var.lanes * b->var.streams,
+                  tb::EvalSharedBytes(b->dp, b->var.lanes, b->var.streams, b->var.ring), b->dp.n_segments);
+  });
+}
 void* towr_b200_batch_stream(const towr_b200_batch* b) { return b ? static_cast<void*>(b->stream) : nullptr; }
 
 }  // extern "C"
