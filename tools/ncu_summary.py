@@ -2,7 +2,7 @@
 """Summarise an ncu report (run here, no GPU needed) into profiles/: key metrics of the evaluation kernel,
 per-launch DRAM traffic (profiles/traffic.json, read by bench.py) and the launch list shares.
 
-    python tools/ncu_summary.py gpurun_out/prof_r01.ncu-rep gpurun_out/launches_r01.csv r01
+    python tools/ncu_summary.py gpurun_out/prof_r01.ncu-rep gpurun_out/launches_r01.csv r01 [commit of the captured build]
 """
 import csv
 import io
@@ -30,8 +30,9 @@ def main():
     rows = list(csv.reader(io.StringIO(raw)))
     hdr, units, vals = rows[0], rows[1], rows[2]
     out = ["# ncu summary %s — %s" % (tag, vals[hdr.index("Kernel Name")] if "Kernel Name" in hdr else "kernel"), "",
-           "Source: `ncu --set full --clock-control none --import-source on -k regex:EvalKernel -s 1 -c 1` on "
-           "`python bench.py --steps 3 --warmup 1 --e2e-steps 1 --no-cpu-baseline` (B200, batch 4096 ANYmal trot).", "",
+           "Source: `ncu --set full --clock-control none --import-source on -k regex:EvalKernel -s 3 -c 1` on "
+           "`python bench.py --steps 3 --warmup 3 --e2e-steps 1 --no-cpu-baseline --no-extra` (B200, batch 4096 ANYmal trot; "
+           "tools/run_round_gpu.sh).", "",
            "| metric | value | unit |", "|---|---|---|"]
     got = {}
     for k in KEYS:
@@ -76,7 +77,7 @@ def main():
         out.append("The torch elementwise/reduce kernels are bench.py's own `isfinite` sanity check after the timed "
                    "region and its input upload; inside the timed region only EvalKernel launches.")
     open(os.path.join(ROOT, "profiles", "%s_ncu_summary.md" % tag), "w").write("\n".join(out) + "\n")
-    commit = subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
+    commit = sys.argv[4] if len(sys.argv) > 4 else subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
     json.dump({"dram_bytes_per_launch": traffic, "source": os.path.basename(rep), "tag": tag, "commit": commit, "workload": "anymal_trot",
                "kernel": vals[hdr.index("Kernel Name")] if "Kernel Name" in hdr else "EvalKernel"},
               open(os.path.join(ROOT, "profiles", "traffic.json"), "w"))

@@ -240,7 +240,7 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
       tb::DeviceProgram t{};
       t.blob = h.blob;
       t.g_capacity = g_cap;
-      return static_cast<long long>(tb::EvalSharedBytes(t, v.lanes, v.streams, v.ring)) + 1024;   // + the kernel's static shared memory
+      return static_cast<long long>(tb::EvalSharedBytes(t, v.lanes, v.streams, v.mode())) + 1024;   // + the kernel's static shared memory
     };
     // rebuilds the program with at most `cap` G slots per segment (more, smaller segments); true when `v` then fits
     auto rebuild = [&](long long cap, const tb::EvalVariant& v) {
@@ -271,6 +271,7 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
       if (std::strcmp(kenv, "ring") == 0) want = tb::EvalVariant{1, 1, true, 0};
       else if (std::strcmp(kenv, "streams") == 0) want = tb::EvalVariant{1, 2, false, 0};
       else if (std::strcmp(kenv, "streamsring") == 0) want = tb::EvalVariant{1, 2, true, 0};
+      else if (std::strcmp(kenv, "split") == 0) want = tb::EvalVariant{2, 1, false, 0, true};
       else throw std::runtime_error(std::string("unknown TOWR_B200_KERNEL: ") + kenv);
     }
     if (const char* env = std::getenv("TOWR_B200_SKEW")) want.skew = std::atoi(env);
@@ -280,7 +281,7 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     // optimised durations: 4.40 ms with 2 lanes / 17 segments against 6.69 ms with 1 lane / 14 segments).
     if (!std::getenv("TOWR_B200_GCAP") && !b->hp_local && (forced_variant || !forced) && need(*hpp, hpp->g_capacity, want) > optin) {
       const int default_cap = hpp->g_capacity;
-      long long cap = (optin - need(*hpp, 0, want) - 6144) / (8LL * want.lanes * want.streams);   // tables grow a little with the segment count
+      long long cap = (optin - need(*hpp, 0, want) - 6144) / (8LL * want.lanes * want.streams * (want.split ? 2 : 1));   // tables grow a little with the segment count
       for (int attempt = 0; attempt < 4 && (forced_variant || cap * 100 >= 45LL * default_cap); ++attempt, cap = cap * 31 / 32)
         if (rebuild(cap, want)) break;
     }
@@ -323,8 +324,8 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
       throw std::runtime_error("unsupported: structure class needs more shared memory per CTA than the device has");
     if (std::getenv("TOWR_B200_DEBUG"))
       std::fprintf(stderr, "batch: %d lane(s) x %d stream(s)%s, skew %d, %zu B shared (blob %d B, G capacity %d), %d CTAs, %d segments\n",
-                   b->var.lanes, b->var.streams, b->var.ring ? ", bulk-store ring" : "", b->var.skew,
-                   tb::EvalSharedBytes(dp, b->var.lanes, b->var.streams, b->var.ring), dp.blob.bytes, dp.g_capacity, b->max_ctas,
+                   b->var.lanes, b->var.streams, b->var.ring ? ", bulk-store ring" : b->var.split ? ", producer/consumer split" : "", b->var.skew,
+                   tb::EvalSharedBytes(dp, b->var.lanes, b->var.streams, b->var.mode()), dp.blob.bytes, dp.g_capacity, b->max_ctas,
                    dp.n_segments);
     *out = b.release();
   });
@@ -744,10 +745,11 @@ long long towr_b200_batch_launch_count(const towr_b200_batch* b) { return b ? b-
 int towr_b200_batch_kernel_info(const towr_b200_batch* b, char* buf, int n) {
   return Guard([&] {
     if (!b || !buf || n < 1) throw std::runtime_error("bad argument");
-    std::snprintf(buf, static_cast<size_t>(n), "tb::EvalKernel<lanes=%d, optimised_durations=%d, streams=%d, ring=%d, curvature=%d>: "
-                  "%d CTAs x %d threads, %zu B shared, %d segments", b->var.lanes, b->dp.blob.rt, b->var.streams, b->var.ring ? 1 : 0,
-                  b->dp.curvature_dims != 0, b->max_ctas, 256 * b->var.lanes * b->var.streams,
-                  tb::EvalSharedBytes(b->dp, b->var.lanes, b->var.streams, b->var.ring), b->dp.n_segments);
+    std::snprintf(buf, static_cast<size_t>(n), "tb::EvalKernel%s<lanes=%d, optimised_durations=%d, streams=%d, ring=%d, curvature=%d>: "
+                  "%d CTAs x %d threads, %zu B shared, %d segments", b->var.split ? "Split" : "", b->var.lanes, b->dp.blob.rt,
+                  b->var.streams, b->var.ring ? 1 : 0, b->dp.curvature_dims != 0, b->max_ctas,
+                  (b->var.split ? 384 : 256) * b->var.lanes * b->var.streams,
+                  tb::EvalSharedBytes(b->dp, b->var.lanes, b->var.streams, b->var.mode()), b->dp.n_segments);
   });
 }
 void* towr_b200_batch_stream(const towr_b200_batch* b) { return b ? static_cast<void*>(b->stream) : nullptr; }

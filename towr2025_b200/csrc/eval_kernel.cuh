@@ -58,8 +58,8 @@ __device__ __forceinline__ void Products(uint32_t w, const char* Gb, const char*
 
 // FULL: all P problem lanes of the group exist (no per-store predicate).
 // nf[p] accumulates value * 0 per problem lane: NaN exactly when a stored value is not finite (status bit 2).
-template <int P, bool FULL, int NT, bool GG = false>
-__device__ __forceinline__ void StageB(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[DescAhead<GG>::value][kDescBatch],
+template <int P, bool FULL, int NT, bool GG = false, int A = DescAhead<GG>::value>
+__device__ __forceinline__ void StageB(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[A][kDescBatch],
                                        const double* G, const double* Bs, double* __restrict__ o, int nnz, int np,
                                        double (&nf)[P]) {
   constexpr int U = kDescBatch;
@@ -74,7 +74,6 @@ __device__ __forceinline__ void StageB(const uint32_t* __restrict__ ent, int lef
       if (FULL || p < np) TB_STORE_VALUE(op + static_cast<size_t>(p) * nnz, v[p]);
     }
   };
-  constexpr int A = DescAhead<GG>::value;
   while (true) {
 #pragma unroll
     for (int a = 0; a < A; ++a) {                         // batch in d[a]; refilled with the batch A further on

@@ -206,10 +206,11 @@ constexpr int kRingDepth = 2;
 constexpr int kRingUB = 8;
 constexpr int kRingBlock = 32 * kRingUB;
 // doubles one stream of `lanes` problem lanes needs next to the class tables (even: keeps 16-byte alignment)
-TB_PHD inline int StreamDoubles(const DeviceProgram& P, int lanes, bool ring) {
+// mode: 0 lock-step, 1 bulk-store ring, 2 split (producer / consumer warp groups: two G buffers)
+TB_PHD inline int StreamDoubles(const DeviceProgram& P, int lanes, int mode) {
   const int rt = P.blob.rt ? 8 * P.blob.n_polys + P.blob.n_pdur : 0;   // kRtd (device_math.cuh)
-  int n = lanes * (P.blob.n_node_values + 6 * P.blob.n_polys + rt + P.g_capacity);
-  if (ring) n += (kEntryThreads * lanes / 32) * kRingDepth * lanes * (kRingBlock + 2) + 2;
+  int n = lanes * (P.blob.n_node_values + 6 * P.blob.n_polys + rt + (mode == 2 ? 2 : 1) * P.g_capacity);
+  if (mode == 1) n += (kEntryThreads * lanes / 32) * kRingDepth * lanes * (kRingBlock + 2) + 2;
   return (n + 1) & ~1;
 }
 
