@@ -292,6 +292,11 @@ def run_ours(args, rank, world, local_rank):
     if not torch.cuda.is_available() or T.lib().towr_b200_device_count() < 1:
         raise SystemExit("bench.py: no CUDA device - the backend has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
+    # one rank per GPU: keep the rank's threads and its pinned staging buffers on the GPU's own NUMA node, so that N ranks
+    # do not share one socket's memory bandwidth (single-GPU runs stay unbound: the CPU baseline wants every core)
+    numa = {"node": T.device_numa_node(local_rank), "cpus_bound": 0}
+    if world > 1:
+        numa["cpus_bound"] = T.bind_thread_to_device_node(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     batch = args.batch
@@ -416,6 +421,8 @@ def run_ours(args, rank, world, local_rank):
                         "api": "towr_b200_batch_eval(EVAL_G | EVAL_JAC_DYNAMIC) (C ABI), pinned host buffers; result = full n x nnz "
                                "value arrays on the host (their constant entries filled once at set-up)",
                         "dynamic_entries": nd, "entries_copied": nd_moved, "stored_entries": st.nnz,
+                        "d2h_gbs_per_gpu": batch * (st.n_rows + nd_moved) * 8 * args.e2e_steps / e2e_s / 1e9,
+                        "host_placement": numa,
                         "full_transfer": {"value": world * batch * args.e2e_steps / e2e_full_s, "ms_per_step": e2e_full_s / args.e2e_steps * 1e3,
                                           "d2h_bytes_per_step": batch * (st.n_rows + st.nnz) * 8,
                                           "api": "towr_b200_batch_eval(EVAL_BOTH): every stored value crosses PCIe"}},

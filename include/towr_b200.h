@@ -200,6 +200,14 @@ long long towr_b200_batch_launch_count(const towr_b200_batch* b);
  * PCIe rate and asynchronously only from such memory (the callback coalescer stages its requests in it) */
 int towr_b200_host_alloc(size_t bytes, void** out);
 void towr_b200_host_free(void* p);
+/* Host placement for multi-GPU jobs (one process or solver-thread group per GPU): the NUMA node the device hangs off
+ * (/sys/bus/pci/devices/<bus id>/numa_node; -1 when the platform does not say), and a call that restricts the CALLING
+ * thread - and the threads and pinned allocations it makes afterwards - to that node's CPUs (sched_setaffinity).  Returns
+ * the number of CPUs bound to, 0 when there is nothing to bind to (single node, no information), < 0 on error.  Without
+ * it every rank's staging buffers land on the node the process happened to start on and eight GPUs share one socket's
+ * memory bandwidth (round 1: end-to-end scaling efficiency 0.22 at N = 8).  No counterpart in the reference (CPU only). */
+int towr_b200_device_numa_node(int device);
+int towr_b200_bind_thread_to_device_node(int device);
 /* human-readable description of the kernel instantiation and launch geometry this batch uses (for logs / bench.py) */
 int towr_b200_batch_kernel_info(const towr_b200_batch* b, char* buf, int n);
 /* the batch's own non-blocking cudaStream_t (the one towr_b200_batch_eval works on) */

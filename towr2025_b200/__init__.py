@@ -100,7 +100,8 @@ towr_b200_batch_eval towr_b200_batch_eval_device towr_b200_batch_status towr_b20
 towr_b200_batch_stream towr_b200_trajectory_width towr_b200_trajectory_samples towr_b200_batch_sample_trajectory
 towr_b200_batch_sample_trajectory_device towr_b200_trajectory_write_csv towr_b200_batch_eval_cost
 towr_b200_batch_eval_cost_device towr_b200_eval_cost_static towr_b200_batch_n_dynamic
-towr_b200_batch_dynamic_index towr_b200_batch_constant_values towr_b200_batch_dynamic_transfer_entries towr_b200_batch_kernel_info towr_b200_host_alloc towr_b200_host_free""".split()
+towr_b200_batch_dynamic_index towr_b200_batch_constant_values towr_b200_batch_dynamic_transfer_entries towr_b200_batch_kernel_info towr_b200_host_alloc towr_b200_host_free
+towr_b200_device_numa_node towr_b200_bind_thread_to_device_node""".split()
 
 
 def lib():
@@ -165,6 +166,24 @@ def lib():
 
 def exported_symbols():
     return list(_EXPORTS)
+
+
+def device_numa_node(device=0):
+    """NUMA node of the GPU (towr_b200_device_numa_node); -1 when the platform does not say."""
+    L = lib()
+    L.towr_b200_device_numa_node.argtypes = [C.c_int]
+    return int(L.towr_b200_device_numa_node(int(device)))
+
+
+def bind_thread_to_device_node(device=0):
+    """Restrict the calling thread (and what it starts or pins afterwards) to the CPUs of the GPU's NUMA node
+    (towr_b200_bind_thread_to_device_node).  Returns the number of CPUs bound to, 0 when there is nothing to bind to."""
+    L = lib()
+    L.towr_b200_bind_thread_to_device_node.argtypes = [C.c_int]
+    rc = int(L.towr_b200_bind_thread_to_device_node(int(device)))
+    if rc < 0:
+        raise TowrB200Error(rc, L.towr_b200_last_error().decode())
+    return rc
 
 
 def _check(rc):

@@ -1,5 +1,9 @@
 // capi.cu — the extern "C" boundary declared in include/towr_b200.h.
 #include <cuda_runtime.h>
+#include <sched.h>
+
+#include <cctype>
+#include <cerrno>
 
 #include <algorithm>
 #include <cstdio>
@@ -740,6 +744,48 @@ int towr_b200_host_alloc(size_t bytes, void** out) {
 }
 void towr_b200_host_free(void* p) {
   if (p) cudaFreeHost(p);
+}
+int towr_b200_device_numa_node(int device) {
+  char bus[32] = {0};
+  if (cudaDeviceGetPCIBusId(bus, sizeof(bus), device) != cudaSuccess) { cudaGetLastError(); return -1; }
+  for (char* c = bus; *c; ++c) *c = static_cast<char>(std::tolower(static_cast<unsigned char>(*c)));
+  const std::string path = std::string("/sys/bus/pci/devices/") + bus + "/numa_node";
+  int node = -1;
+  if (FILE* f = std::fopen(path.c_str(), "r")) {
+    if (std::fscanf(f, "%d", &node) != 1) node = -1;
+    std::fclose(f);
+  }
+  return node;
+}
+int towr_b200_bind_thread_to_device_node(int device) {
+  int result = 0;
+  const int rc = Guard([&] {
+    result = [&]() -> int {
+    const int node = towr_b200_device_numa_node(device);
+    if (node < 0) return 0;
+    const std::string path = "/sys/devices/system/node/node" + std::to_string(node) + "/cpulist";
+    FILE* f = std::fopen(path.c_str(), "r");
+    if (!f) return 0;
+    char buf[4096] = {0};
+    const bool ok = std::fgets(buf, sizeof(buf), f) != nullptr;
+    std::fclose(f);
+    if (!ok) return 0;
+    cpu_set_t set;
+    CPU_ZERO(&set);
+    int n = 0;
+    for (char* tok = std::strtok(buf, ",\n"); tok; tok = std::strtok(nullptr, ",\n")) {   // "0-15,32-47"
+      int a = 0, b = 0;
+      const int got = std::sscanf(tok, "%d-%d", &a, &b);
+      if (got < 1) continue;
+      if (got == 1) b = a;
+      for (int c = a; c <= b && c < CPU_SETSIZE; ++c) { CPU_SET(c, &set); ++n; }
+    }
+    if (n == 0) return 0;
+    if (sched_setaffinity(0, sizeof(set), &set) != 0) throw std::runtime_error(std::string("sched_setaffinity: ") + std::strerror(errno));
+    return n;
+    }();
+  });
+  return rc != TOWR_B200_OK ? rc : result;
 }
 long long towr_b200_batch_launch_count(const towr_b200_batch* b) { return b ? b->launches : 0; }
 int towr_b200_batch_kernel_info(const towr_b200_batch* b, char* buf, int n) {
