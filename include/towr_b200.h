@@ -52,9 +52,13 @@ enum { TOWR_B200_C_DYNAMIC = 0, TOWR_B200_C_ENDEFFECTOR_ROM, TOWR_B200_C_TOTAL_T
        TOWR_B200_C_BASE_ACC, TOWR_B200_C_BASE_HEIGHT };
 /* towr::RobotModel::Robot, include/towr/models/robot_model.h */
 enum { TOWR_B200_MONOPED = 0, TOWR_B200_BIPED, TOWR_B200_HYQ, TOWR_B200_ANYMAL };
-/* towr::HeightMap::TerrainID, include/towr/terrain/height_map.h; 7 = FiveStepStairs of test/hopper_example.cc:53-86 */
+/* towr::HeightMap::TerrainID, include/towr/terrain/height_map.h; 7 = FiveStepStairs of test/hopper_example.cc:53-86;
+ * 8 = a height map given as DATA in the spec (terrain_table_*): what a user's own HeightMap subclass is in the reference
+ * (hopper_example.cc:53-91 defines one), without editing an enum and recompiling kernels */
 enum { TOWR_B200_FLAT = 0, TOWR_B200_BLOCK, TOWR_B200_STAIRS, TOWR_B200_GAP, TOWR_B200_SLOPE, TOWR_B200_CHIMNEY,
-       TOWR_B200_CHIMNEY_LR, TOWR_B200_FIVE_STEP_STAIRS, TOWR_B200_TERRAIN_COUNT };
+       TOWR_B200_CHIMNEY_LR, TOWR_B200_FIVE_STEP_STAIRS, TOWR_B200_TERRAIN_TABLE, TOWR_B200_TERRAIN_COUNT };
+#define TOWR_B200_MAX_TERRAIN_KNOTS 16
+enum { TOWR_B200_TABLE_STEPS = 0, TOWR_B200_TABLE_RAMPS = 1 };
 /* towr::Parameters::CostName, include/towr/parameters.h:157-161 */
 enum { TOWR_B200_COST_FORCES = 0, TOWR_B200_COST_EE_MOTION = 1, TOWR_B200_COST_ENERGY = 2, TOWR_B200_COST_ANG_MOM = 3 };
 /* what to evaluate */
@@ -104,6 +108,17 @@ typedef struct towr_b200_spec {
   int enable_stance_tracking;
   int n_stance_positions[TOWR_B200_MAX_EE];
   double ee_stance_position[TOWR_B200_MAX_EE][TOWR_B200_MAX_STANCES][2];
+  /* terrain_ as data (terrain_id == TOWR_B200_TERRAIN_TABLE), per problem: a profile along x, constant in y, with knots
+   * terrain_table_x[0] < ... < terrain_table_x[n-1] (1 <= n <= TOWR_B200_MAX_TERRAIN_KNOTS) and heights terrain_table_h.
+   *   TABLE_STEPS: h = 0 for x < x[0], h[i] for x[i] <= x < x[i+1], h[n-1] from x[n-1] on; no slope
+   *                (GetHeightDerivWrtX = 0, like the reference's Stairs, height_map_examples.cc:66-80)
+   *   TABLE_RAMPS: h = h[0] for x < x[0], linear between knots with GetHeightDerivWrtX = (h[i+1]-h[i])/(x[i+1]-x[i]) for
+   *                x[i] <= x < x[i+1], h[n-1] and no slope from x[n-1] on (like Slope / Block, :43-63,115-145)
+   * Second derivatives are 0 (HeightMap's defaults).  A structure class created from a spec with a table terrain admits
+   * problems with any terrain of the same curvature; one created on an analytic terrain refuses table terrains
+   * (towr_b200_structure_accepts: the kernels that read the table are a separate instantiation). */
+  int terrain_table_n, terrain_table_mode;
+  double terrain_table_x[TOWR_B200_MAX_TERRAIN_KNOTS], terrain_table_h[TOWR_B200_MAX_TERRAIN_KNOTS];
 } towr_b200_spec;
 
 const char* towr_b200_last_error(void);
@@ -253,6 +268,11 @@ int towr_b200_batch_sample_trajectory(towr_b200_batch* b, int n, double dt, cons
 /* device buffers already on the batch's device; stream NULL = the default stream */
 int towr_b200_batch_sample_trajectory_device(towr_b200_batch* b, int n, double dt, const double* d_x, double* d_rows,
                                              void* stream);
+/* SplineHolder::<spline>->GetPoint(t) / PhaseDurations::IsContactPhase(t) at ARBITRARY global times (spline_holder.h:48-84,
+ * spline.cc:80-93, phase_durations.cc:113-118): the same rows as _sample_trajectory for the n_times times of `times`
+ * (each in [0, total time]; ERR_ARG otherwise), rows_out n x n_times x width.  Tables for the list are built per call. */
+int towr_b200_batch_sample_points(towr_b200_batch* b, int n, const double* times, int n_times, const double* x,
+                                  double* rows_out);
 /* one problem's rows in the reference's CSV format (header line, std::fixed, 6 decimals; save_data.cpp:24-46,68-116) */
 int towr_b200_trajectory_write_csv(const towr_b200_structure* st, const double* rows, int n_rows, const char* filename);
 

@@ -20,6 +20,8 @@
 #include <vector>
 
 #include "towr_b200.h"
+#include "towr_b200_formulation.hpp"
+#include "towr_b200_spline_holder.hpp"
 
 namespace towr_b200 {
 
@@ -38,6 +40,10 @@ inline void Check(int rc) {
 class NlpFormulation {
  public:
   NlpFormulation() { Check(towr_b200_spec_defaults(&spec_)); }
+  // from the reference's own member layout (towr_b200_formulation.hpp: initial_base_, final_base_, initial_ee_W_, model_,
+  // terrain_, params_), or from a finished spec
+  explicit NlpFormulation(const ref::NlpFormulation& f) : spec_(ToSpec(f)) {}
+  explicit NlpFormulation(const towr_b200_spec& s) : spec_(s) {}
   // towr::RobotModel(Robot) ; towr::GaitGenerator::SetCombo + GetPhaseDurations / GetContactSchedule
   void SetRobot(int robot) { Check(towr_b200_spec_robot(&spec_, robot)); }
   void SetGait(int combo, double total_time) { Check(towr_b200_spec_gait(&spec_, combo, total_time)); }
@@ -210,6 +216,12 @@ class BatchedProblem {
     std::vector<double> rows(static_cast<size_t>(n_) * samples * GetTrajectoryWidth());
     Check(towr_b200_batch_sample_trajectory(batch_, n_, T_sample, x_.data(), rows.data()));
     return rows;
+  }
+  // towr::SplineHolder of problem p's current variables (what GetVariableSets hands back in the reference,
+  // nlp_formulation.cc:76-119): base_linear_, ee_motion_.at(ee), ... ->GetPoint(t), phase_durations_.at(ee)->IsContactPhase(t)
+  SplineHolder GetSplineHolder(int p) {
+    EnsureBatch();
+    return SplineHolder(batch_, st_, specs_[p], xp(p));
   }
   bool SaveTrajectoryToCSV(int p, const std::string& filename, double T_sample) {
     const std::vector<double> rows = SampleTrajectories(T_sample);

@@ -320,7 +320,37 @@ struct FiveStepStairs : HeightMap {   // test/hopper_example.cc:53-86
     return (step_number + 1) * step_height_;
   }
 };
+// User height map as data: knots x_[0] < ... < x_[n-1], heights h_.  steps_: h = 0 before the first knot, h_[i] on
+// [x_[i], x_[i+1]), h_.back() from the last knot on, no slope.  Otherwise ramps: h_[0] before the first knot, linear on
+// [x_[i], x_[i+1]) with that segment's slope as GetHeightDerivWrtX, h_.back() and no slope from the last knot on.
+struct TableTerrain : HeightMap {
+  bool steps_;
+  std::vector<double> x_, h_;
+  TableTerrain(bool steps, std::vector<double> x, std::vector<double> h) : steps_(steps), x_(std::move(x)), h_(std::move(h)) {}
+  int Interval(double x) const {      // -1: before the first knot; i: x_[i] <= x (< x_[i+1] when there is one)
+    int i = -1;
+    for (size_t k = 0; k < x_.size(); ++k)
+      if (x >= x_[k]) i = static_cast<int>(k);
+    return i;
+  }
+  double GetHeight(double x, double) const override {
+    const int i = Interval(x);
+    if (i < 0) return steps_ ? 0.0 : h_.front();
+    if (steps_ || i + 1 == static_cast<int>(x_.size())) return h_[i];
+    return h_[i] + GetHeightDerivWrtX(x, 0.0) * (x - x_[i]);
+  }
+  double GetHeightDerivWrtX(double x, double) const override {
+    const int i = Interval(x);
+    if (steps_ || i < 0 || i + 1 == static_cast<int>(x_.size())) return 0.0;
+    return (h_[i + 1] - h_[i]) / (x_[i + 1] - x_[i]);
+  }
+};
 }  // namespace
+
+std::shared_ptr<HeightMap> HeightMap::MakeTableTerrain(int mode, const std::vector<double>& x, const std::vector<double>& h) {
+  if (x.empty() || x.size() != h.size()) throw std::runtime_error("terrain table: bad knot count");
+  return std::make_shared<TableTerrain>(mode == 0, x, h);
+}
 
 // height_map.cc:38-51
 std::shared_ptr<HeightMap> HeightMap::MakeTerrain(int id) {

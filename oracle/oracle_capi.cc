@@ -37,7 +37,12 @@ static NlpFormulation MakeFormulation(const orc_spec& s) {
     kin->min_dev_.push_back(V3(s.min_dev[e][0], s.min_dev[e][1], s.min_dev[e][2]));
   }
   f.model_.kinematic_model_ = kin;
-  f.terrain_ = HeightMap::MakeTerrain(s.terrain_id);
+  if (s.terrain_id == 8)
+    f.terrain_ = HeightMap::MakeTableTerrain(s.terrain_table_mode,
+                                             std::vector<double>(s.terrain_table_x, s.terrain_table_x + s.terrain_table_n),
+                                             std::vector<double>(s.terrain_table_h, s.terrain_table_h + s.terrain_table_n));
+  else
+    f.terrain_ = HeightMap::MakeTerrain(s.terrain_id);
 
   Parameters& p = f.params_;
   p.constraints_.clear();

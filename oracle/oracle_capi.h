@@ -14,6 +14,7 @@ extern "C" {
 #define ORC_MAX_CONSTRAINTS 16
 #define ORC_MAX_COSTS 4
 #define ORC_MAX_STANCES 17
+#define ORC_MAX_TERRAIN_KNOTS 16
 
 /* The public members of towr::NlpFormulation (nlp_formulation.h:100-105) plus the
  * fields of towr::Parameters (parameters.h:135-336) the hot path reads. */
@@ -51,6 +52,10 @@ typedef struct orc_spec {
   int enable_stance_tracking;
   int n_stance_positions[ORC_MAX_EE];
   double ee_stance_position[ORC_MAX_EE][ORC_MAX_STANCES][2];
+  /* terrain_id 8: a user HeightMap given as data (a profile along x; mode 0 steps, 1 ramps) - the restatement of "derive
+   * from HeightMap and override GetHeight / GetHeightDerivWrtX" (test/hopper_example.cc:53-91) for a piecewise profile */
+  int terrain_table_n, terrain_table_mode;
+  double terrain_table_x[ORC_MAX_TERRAIN_KNOTS], terrain_table_h[ORC_MAX_TERRAIN_KNOTS];
 } orc_spec;
 
 /* Parameters::Parameters() defaults (parameters.cc:40-105), enable_stance_tracking=false. */

@@ -920,6 +920,32 @@ class FiveStepStairs(HeightMap):                                      # test/hop
         return (step + 1) * 0.15
 
 
+class TableTerrain(HeightMap):
+    """A user height map given as data (orc_spec::terrain_table_*, terrain id 8): profile along x.  mode 0: steps (0 before
+    the first knot, h[i] on [x[i], x[i+1]), h[-1] from the last knot on); mode 1: ramps (h[0] before the first knot, linear
+    between knots with the segment's slope as d h / d x, h[-1] and no slope from the last knot on)."""
+
+    def __init__(self, mode, xs, hs):
+        self.steps, self.xs, self.hs = mode == 0, np.asarray(xs, float), np.asarray(hs, float)
+
+    def _i(self, x):
+        return int(np.searchsorted(self.xs, x, side="right")) - 1
+
+    def height(self, x, y):
+        i = self._i(x)
+        if i < 0:
+            return 0.0 if self.steps else float(self.hs[0])
+        if self.steps or i + 1 == len(self.xs):
+            return float(self.hs[i])
+        return float(self.hs[i] + self.dx(x, y) * (x - self.xs[i]))
+
+    def dx(self, x, y):
+        i = self._i(x)
+        if self.steps or i < 0 or i + 1 == len(self.xs):
+            return 0.0
+        return float((self.hs[i + 1] - self.hs[i]) / (self.xs[i + 1] - self.xs[i]))
+
+
 TERRAINS = [FlatGround, Block, Stairs, Gap, Slope, Chimney, ChimneyLR, FiveStepStairs]
 
 
@@ -1666,7 +1692,11 @@ class Formulation:
         s = spec
         self.n_ee = n_ee = int(s.n_ee)
         arr = lambda a, *shape: np.array(np.ctypeslib.as_array(a), dtype=float).reshape(*shape) if not isinstance(a, np.ndarray) else a
-        self.terrain = TERRAINS[int(s.terrain_id)]()
+        if int(s.terrain_id) == 8:
+            n = int(s.terrain_table_n)
+            self.terrain = TableTerrain(int(s.terrain_table_mode), list(s.terrain_table_x)[:n], list(s.terrain_table_h)[:n])
+        else:
+            self.terrain = TERRAINS[int(s.terrain_id)]()
         self.model = SingleRigidBodyDynamics(float(s.mass), [float(v) for v in s.inertia], n_ee)
         self.kin = {"nominal": [np.array(list(s.nominal_stance[e])) for e in range(n_ee)],
                     "max_dev": [np.array(list(s.max_dev[e])) for e in range(n_ee)],

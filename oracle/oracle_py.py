@@ -17,7 +17,8 @@ MAX_EE, MAX_PHASES, MAX_CONSTRAINTS = 4, 32, 16
 # towr::Parameters::ConstraintName (parameters.h:142-153 order)
 Dynamic, EndeffectorRom, TotalTime, Terrain, TerrainHard, Force, Torque, Swing, BaseRom, BaseAcc, BaseHeight = range(11)
 Monoped, Biped, Hyq, Anymal = range(4)
-FlatID, BlockID, StairsID, GapID, SlopeID, ChimneyID, ChimneyLRID, FiveStepStairsID = range(8)
+FlatID, BlockID, StairsID, GapID, SlopeID, ChimneyID, ChimneyLRID, FiveStepStairsID, TableTerrainID = range(9)
+TABLE_STEPS, TABLE_RAMPS = 0, 1
 
 
 class Spec(C.Structure):
@@ -59,6 +60,8 @@ class Spec(C.Structure):
         ("enable_stance_tracking", C.c_int),
         ("n_stance_positions", C.c_int * MAX_EE),
         ("ee_stance_position", ((C.c_double * 2) * 17) * MAX_EE),
+        ("terrain_table_n", C.c_int), ("terrain_table_mode", C.c_int),
+        ("terrain_table_x", C.c_double * 16), ("terrain_table_h", C.c_double * 16),
     ]
 
 

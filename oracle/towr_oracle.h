@@ -300,6 +300,9 @@ class HeightMap {
   enum Direction { Normal, Tangent1, Tangent2 };
   virtual ~HeightMap() = default;
   static std::shared_ptr<HeightMap> MakeTerrain(int id);
+  // a user-defined height map given as data (orc_spec::terrain_table_*): what deriving from HeightMap and overriding
+  // GetHeight / GetHeightDerivWrtX is in the reference (test/hopper_example.cc:53-91), for a piecewise profile along x
+  static std::shared_ptr<HeightMap> MakeTableTerrain(int mode, const std::vector<double>& x, const std::vector<double>& h);
   virtual double GetHeight(double x, double y) const = 0;
   double GetDerivativeOfHeightWrt(int dim, double x, double y) const { return dim == 0 ? GetHeightDerivWrtX(x, y) : GetHeightDerivWrtY(x, y); }
   V3 GetNormalizedBasis(Direction basis, double x, double y) const { return normalized(GetBasis(basis, x, y, -1)); }

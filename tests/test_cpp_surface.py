@@ -16,7 +16,8 @@ def build(name="ifopt_surface"):
     os.makedirs(os.path.dirname(EXE), exist_ok=True)
     src = os.path.join(ROOT, "tests", "cpp", name + ".cc")
     lib_dir = os.path.join(ROOT, "towr2025_b200")
-    hdrs = [os.path.join(ROOT, "include", h) for h in ("towr_b200_ifopt.hpp", "towr_b200_coalescer.hpp", "towr_b200.h")]
+    hdrs = [os.path.join(ROOT, "include", h) for h in ("towr_b200_ifopt.hpp", "towr_b200_coalescer.hpp", "towr_b200.h",
+                                                       "towr_b200_formulation.hpp", "towr_b200_spline_holder.hpp")]
     newest = max([os.path.getmtime(src), os.path.getmtime(os.path.join(lib_dir, "libtowr_b200.so"))] +
                  [os.path.getmtime(h) for h in hdrs])
     if not os.path.exists(exe) or os.path.getmtime(exe) < newest:
@@ -114,3 +115,30 @@ def test_callback_coalescer_values_match_oracle_on_gpu():
     assert out.returncode == 0, out.stdout + out.stderr
     line = [l for l in out.stdout.splitlines() if l.startswith("oracle_checks")][0].split()
     assert int(line[1]) > 100 and float(line[3]) <= 1.0 and float(line[5]) <= 4.0
+
+
+def _hopper(mode):
+    out = subprocess.run([build("hopper_surface"), mode], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "ok" in out.stdout
+    return {l.split()[0]: l.split()[1:] for l in out.stdout.splitlines() if l.strip()}
+
+
+def test_hopper_example_through_reference_types_host(product, oracle):
+    """hopper_example.cc:93-150 stated with the reference's member names (towr_b200_formulation.hpp), ToSpec, the ifopt
+    mirror: sizes, x0, all bounds and the Jacobian pattern equal the oracle's entry by entry; ToSpec throws what the
+    reference throws (std::out_of_range without stance positions) and refuses what is not built."""
+    r = _hopper("host")
+    assert float(r["host_checks"][5]) <= 1.0
+
+
+@pytest.mark.gpu
+def test_hopper_example_through_reference_types_gpu(product, oracle):
+    """The same problem evaluated: g, every Jacobian value, eval_f / eval_grad_f and the SplineHolder view (GetPoint of
+    base / ee-motion / force / torque splines, IsContactPhase) against the oracle, entry by entry."""
+    r = _hopper("gpu")["gpu_checks"]
+    vals = dict(zip(r[0::2], r[1::2]))
+    assert float(vals["g"]) <= 1.0 and float(vals["jac"]) <= 4.0 and float(vals["cost"]) <= 1.0
+    assert float(vals["splines"]) <= 10.0      # the oracle's trajectory rows use std::pow (pow_ok band, tests/util.py)
+    assert int(vals["contact_mismatch"]) == 0 and int(vals["samples"]) == 24 and int(vals["phases"]) == 13
+    assert float(vals["duration_sum"]) == pytest.approx(4.6, abs=1e-12) and int(vals["force_v_threw"]) == 1

@@ -58,6 +58,29 @@ def test_gap_superset_pattern_matches_oracle(product, oracle, case):
     assert len(extras) > 1
 
 
+def test_table_terrain_reproduces_the_five_step_stairs(product):
+    """The hopper example's own HeightMap (FiveStepStairs, hopper_example.cc:53-91) written as a table of five steps gives
+    the same g and Jacobian values as the built-in terrain id 7, and per-problem tables differ within one batch."""
+    from util import set_terrain_table
+    T = product
+    a = T.make_spec(T.Monoped, T.C0, 2.4, goal=(1.0, 0.0, 0.0), terrain=T.FiveStepStairsID, extra_constraints=(T.Torque,))
+    b = T.make_spec(T.Monoped, T.C0, 2.4, goal=(1.0, 0.0, 0.0), extra_constraints=(T.Torque,))
+    set_terrain_table(b, T.TABLE_STEPS, [0.5, 0.8, 1.1, 1.4, 1.7], [0.15, 0.3, 0.45, 0.6, 0.75])
+    c = T.make_spec(T.Monoped, T.C0, 2.4, goal=(1.0, 0.0, 0.0), extra_constraints=(T.Torque,))
+    set_terrain_table(c, T.TABLE_STEPS, [0.5, 0.8], [0.3, 0.6])
+    st = T.Structure(b)
+    x0 = st.x0(a)
+    rng = np.random.default_rng(4)
+    x = x0 + rng.uniform(-0.013, 0.013, size=x0.shape)         # no node sits exactly on a step edge (there int((x - 0.5) / 0.3) and x >= knot may round differently)
+    batch = T.Batch(st, 3)
+    for i, s in enumerate((a, b, c)):
+        batch.set_problem(i, s)
+    g, v = batch.eval(np.stack([x, x, x]))
+    assert (batch.status() == 0).all()
+    assert np.array_equal(g[0], g[1]) and np.array_equal(v[0], v[1])
+    assert not np.array_equal(g[1], g[2])
+
+
 @pytest.mark.parametrize("optimise", [False, True], ids=["fixed", "durations"])
 def test_mixed_terrain_batch_block_gap_stairs(product, oracle, optimise):
     """BASELINE config 4 as written: HyQ gallop, terrain ids cycling Block / Gap / Stairs inside ONE batch.  The class is

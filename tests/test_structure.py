@@ -100,6 +100,37 @@ def test_gap_needs_a_class_that_declares_the_curvature_block(product):
             assert curv.accepts(T.make_spec(T.Hyq, T.C4, 2.4, terrain=terrain, optimize_durations=opt))
 
 
+def test_table_terrain_class_rules_and_validation(product, oracle):
+    """terrain_ as data (terrain id 8): a class created from a table spec has the SAME pattern as the class of an analytic
+    terrain (a piecewise-linear profile has no curvature) and admits analytic and table problems; a class created on an
+    analytic terrain refuses a table problem (its kernels do not read the table); bad tables are argument errors; x0 and
+    bounds follow the table's heights (final foothold on the terrain, nlp_formulation.cc:199-203)."""
+    from util import set_terrain_table
+    T, O = product, oracle
+    flat = T.make_spec(T.Biped, T.C0, 2.4, terrain=T.FlatID)
+    tab = T.make_spec(T.Biped, T.C0, 2.4)
+    set_terrain_table(tab, T.TABLE_RAMPS, [0.3, 0.9], [0.0, 0.25])
+    st_flat, st_tab = T.Structure(flat), T.Structure(tab)
+    assert st_tab.nnz == st_flat.nnz and np.array_equal(st_tab.pattern()[0], st_flat.pattern()[0])
+    assert st_tab.accepts(flat) and st_tab.accepts(tab)
+    assert not st_flat.accepts(tab)
+    with pytest.raises(T.TowrB200Error) as e:
+        st_flat.x0(tab)
+    assert e.value.code == -4 and "table" in str(e.value)
+    po = O.Problem(to_oracle_spec(O, tab))
+    assert np.array_equal(st_tab.x0(tab), po.x0())
+    for a, b in zip(st_tab.var_bounds(tab), po.var_bounds()):
+        assert np.array_equal(np.clip(a, -1e20, 1e20), np.clip(b, -1e20, 1e20))
+    assert not np.array_equal(st_tab.x0(tab), st_tab.x0(flat))          # the final footholds sit on the ramp
+    for bad in ((T.TABLE_STEPS, [0.5, 0.5], [0.1, 0.2]), (T.TABLE_STEPS, [], []), (7, [0.1], [0.1]),
+                (T.TABLE_RAMPS, [0.1, 0.2], [0.0, float("nan")])):
+        s = T.make_spec(T.Biped, T.C0, 2.4)
+        set_terrain_table(s, *bad)
+        with pytest.raises(T.TowrB200Error) as e:
+            T.Structure(s)
+        assert e.value.code == -1
+
+
 def test_library_exports_every_declared_symbol(product):
     """The C-ABI library loads without a GPU and exports everything include/towr_b200.h declares."""
     import os

@@ -99,6 +99,29 @@ def test_gpu_trajectory_matches_oracle(product, oracle, case):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("case", [TRAJ_CASES[0], TRAJ_CASES[-1]], ids=lambda c: c[0])
+def test_gpu_sample_points_at_arbitrary_times(product, oracle, case):
+    """towr_b200_batch_sample_points = SplineHolder::...->GetPoint(t) at any t: the rows for an unsorted list of times
+    taken from the oracle's grid must be the oracle's rows for those times; times outside [0, T] are refused."""
+    T, O = product, oracle
+    s = mk(T, case)
+    st = T.Structure(s)
+    x = np.stack([perturbed(st.x0(s), 300 + i, 0.02 if is_rt(case) else 0.1) for i in range(3)])
+    b = T.Batch(st, 3)
+    po = O.Problem(to_oracle_spec(O, s))
+    for i in range(3):
+        ref = po.sample_trajectory(x[i], 0.037)
+        pick = np.random.default_rng(i).permutation(ref.shape[0])[:17]
+        rows = b.sample_points(x[i:i + 1], ref[pick, 0])[0]
+        assert np.array_equal(rows[:, 0], ref[pick, 0])
+        assert (pow_ok if is_rt(case) else parity_ok)(rows, ref[pick])
+    with pytest.raises(T.TowrB200Error):
+        b.sample_points(x[:1], np.array([0.1, case[3] + 0.5]))
+    with pytest.raises(T.TowrB200Error):
+        b.sample_points(x[:1], np.array([-0.1]))
+
+
+@pytest.mark.gpu
 def test_gpu_trajectory_full_batch_properties(product):
     """Batch 1024: identical x rows give identical trajectories; node interpolation holds on the device rows."""
     import torch

@@ -52,6 +52,11 @@ CASES = [
     # large class tables: the range-of-motion sets are split into sample groups, the batch lowers the G capacity
     ("anymal_trot_very_fine_dt", 3, 1, 2.0, (1.0, 0.0, 0.0), 0, (), False,
      {"dt_constraint_dynamic": 0.025, "dt_constraint_range_of_motion": 0.02, "dt_constraint_force": 0.005}),
+    # terrain given as data (terrain id 8, towr_b200_spec::terrain_table_*): (mode, knots x, heights); mode 0 steps, 1 ramps
+    ("biped_walk_table_steps", 1, 0, 2.4, (1.0, 0.0, 0.1), 8, (), False, {}, (0, [0.6, 1.0, 1.4], [0.1, 0.2, 0.3])),
+    ("anymal_trot_table_ramps_torque", 3, 1, 2.0, (1.0, 0.0, 0.0), 8, (TORQUE,), False, {},
+     (1, [0.4, 0.8, 1.2, 1.6], [0.0, 0.2, 0.2, 0.0])),
+    ("monoped_hop_table_ramps_durations", 0, 0, 2.4, (1.0, 0.0, 0.0), 8, (), True, {}, (1, [0.5, 1.0], [0.0, 0.3])),
 ]
 
 
@@ -175,7 +180,19 @@ def mk(M, case, goal=None):
                     optimize_durations=opt, extra_constraints=extra)
     for k, v in (case[8] if len(case) > 8 else {}).items():     # Parameters overrides (same field names in both specs)
         setattr(s, k, v)
+    if len(case) > 9:
+        set_terrain_table(s, *case[9])
     return s
+
+
+def set_terrain_table(s, mode, xs, hs):
+    """terrain_ as data: terrain id 8 with a profile along x (same fields in the product's and the oracle's spec)."""
+    s.terrain_id = 8
+    s.terrain_table_mode = mode
+    s.terrain_table_n = len(xs)
+    for i, (x, h) in enumerate(zip(xs, hs)):
+        s.terrain_table_x[i] = x
+        s.terrain_table_h[i] = h
 
 
 def perturbed(x0, seed, scale=0.1):

@@ -20,7 +20,8 @@ MAX_EE, MAX_PHASES, MAX_CONSTRAINTS = 4, 32, 16
 # towr::Parameters::ConstraintName
 Dynamic, EndeffectorRom, TotalTime, Terrain, TerrainHard, Force, Torque, Swing, BaseRom, BaseAcc, BaseHeight = range(11)
 Monoped, Biped, Hyq, Anymal = range(4)
-FlatID, BlockID, StairsID, GapID, SlopeID, ChimneyID, ChimneyLRID, FiveStepStairsID = range(8)
+FlatID, BlockID, StairsID, GapID, SlopeID, ChimneyID, ChimneyLRID, FiveStepStairsID, TableTerrainID = range(9)
+TABLE_STEPS, TABLE_RAMPS = 0, 1
 EVAL_G, EVAL_JAC, EVAL_BOTH, EVAL_JAC_DYNAMIC = 1, 2, 3, 4
 C0, C1, C2, C3, C4 = range(5)
 
@@ -65,6 +66,8 @@ class Spec(C.Structure):
         ("enable_stance_tracking", C.c_int),
         ("n_stance_positions", C.c_int * MAX_EE),
         ("ee_stance_position", ((C.c_double * 2) * 17) * MAX_EE),
+        ("terrain_table_n", C.c_int), ("terrain_table_mode", C.c_int),
+        ("terrain_table_x", C.c_double * 16), ("terrain_table_h", C.c_double * 16),
     ]
 
     def copy(self):
@@ -101,7 +104,7 @@ towr_b200_batch_stream towr_b200_trajectory_width towr_b200_trajectory_samples t
 towr_b200_batch_sample_trajectory_device towr_b200_trajectory_write_csv towr_b200_batch_eval_cost
 towr_b200_batch_eval_cost_device towr_b200_eval_cost_static towr_b200_batch_n_dynamic
 towr_b200_batch_dynamic_index towr_b200_batch_constant_values towr_b200_batch_dynamic_transfer_entries towr_b200_batch_kernel_info towr_b200_host_alloc towr_b200_host_free
-towr_b200_device_numa_node towr_b200_bind_thread_to_device_node""".split()
+towr_b200_device_numa_node towr_b200_bind_thread_to_device_node towr_b200_batch_sample_points""".split()
 
 
 def lib():
@@ -154,6 +157,7 @@ def lib():
     L.towr_b200_trajectory_samples.argtypes = [vp, C.c_double]
     L.towr_b200_batch_sample_trajectory.argtypes = [vp, C.c_int, C.c_double, dp, dp]
     L.towr_b200_batch_sample_trajectory_device.argtypes = [vp, C.c_int, C.c_double, vp, vp, vp]
+    L.towr_b200_batch_sample_points.argtypes = [vp, C.c_int, dp, C.c_int, dp, dp]
     L.towr_b200_trajectory_write_csv.argtypes = [vp, dp, C.c_int, C.c_char_p]
     L.towr_b200_batch_kernel_info.argtypes = [vp, C.c_char_p, C.c_int]
     L.towr_b200_batch_launch_count.argtypes = [vp]
@@ -352,6 +356,15 @@ class Batch:
         n = x.shape[0]
         rows = np.empty((n, self.structure.trajectory_samples(dt), self.structure.trajectory_width()))
         _check(self._L.towr_b200_batch_sample_trajectory(self._h, n, float(dt), _dp(x), _dp(rows)))
+        return rows
+
+    def sample_points(self, x, times):
+        """SplineHolder GetPoint / IsContactPhase rows at arbitrary global times (towr_b200_batch_sample_points):
+        (n, len(times), width)."""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        times = np.ascontiguousarray(times, dtype=np.float64)
+        rows = np.empty((x.shape[0], times.shape[0], self.structure.trajectory_width()))
+        _check(self._L.towr_b200_batch_sample_points(self._h, x.shape[0], _dp(times), times.shape[0], _dp(x), _dp(rows)))
         return rows
 
     def sample_trajectory_device(self, n, dt, d_x, d_rows, stream=None):

@@ -197,6 +197,9 @@ int towr_b200_structure_accepts(const towr_b200_structure* st, const towr_b200_s
     if (tb::TerrainCurvatureDims(s->terrain_id) & ~st->hp.curvature_dims)
       throw StructureError("the problem's terrain has curvature (Gap) and this structure class does not declare the curvature block: "
                            "create the class from a spec on that terrain");
+    if (s->terrain_id == TOWR_B200_TERRAIN_TABLE && st->hp.curvature_dims == 0)
+      throw StructureError("the problem's terrain is given as a table and this structure class was created on an analytic terrain: "
+                           "create the class from a spec with a table terrain (or on Gap)");
     if (tb::StructureSignature(*s, st->hp.curvature_dims) != st->hp.signature)
       throw StructureError("spec belongs to a different structure class");
   });
@@ -361,7 +364,7 @@ namespace {
 // every problem of the batch on a terrain without slope: the terrain basis is a constant too
 bool FlatBasis(const towr_b200_batch* b) {
   for (const tb::ProblemConst& pc : b->pc_host)
-    if (tb::TerrainHasSlope(pc.terrain_id)) return false;
+    if (tb::TerrainHasSlope(pc.terrain_id, pc.table)) return false;
   return true;
 }
 const std::vector<int>& DynIndex(const towr_b200_batch* b) {
@@ -620,11 +623,8 @@ const T* UploadVec(std::vector<void*>& owned, const std::vector<T>& v) {
   return d;
 }
 
-const towr_b200_batch::Traj& TrajFor(towr_b200_batch* b, double dt) {
-  auto it = b->traj.find(dt);
-  if (it != b->traj.end()) return *it->second;
-  auto t = std::make_unique<towr_b200_batch::Traj>();
-  tb::BuildTrajTables(b->st->hp, b->st->spec, dt, t->host);
+// uploads t->host (filled by the caller) and checks that the sampler's tables fit an SM
+void UploadTraj(towr_b200_batch* b, towr_b200_batch::Traj* t) {
   const tb::TrajTables& h = t->host;
   tb::TrajDevice& d = t->dev;
   d.n_vars = h.n_vars; d.n_ee = h.n_ee; d.width = h.width; d.n_samples = h.n_samples;
@@ -645,6 +645,16 @@ const towr_b200_batch::Traj& TrajFor(towr_b200_batch* b, double dt) {
   Check(cudaGetDeviceProperties(&prop, b->device), "cudaGetDeviceProperties");
   if (tb::TrajSharedBytes(d) > prop.sharedMemPerBlockOptin)
     throw std::runtime_error("unsupported: the problem's spline tables exceed the SM's shared memory");
+}
+
+void SampleHost(towr_b200_batch* b, const towr_b200_batch::Traj& t, int n, const double* x, double* rows_out);
+
+const towr_b200_batch::Traj& TrajFor(towr_b200_batch* b, double dt) {
+  auto it = b->traj.find(dt);
+  if (it != b->traj.end()) return *it->second;
+  auto t = std::make_unique<towr_b200_batch::Traj>();
+  tb::BuildTrajTables(b->st->hp, b->st->spec, dt, t->host);
+  UploadTraj(b, t.get());
   if (b->traj.size() >= towr_b200_batch::kMaxTrajTables) {
     // evict one cached sampling period (its kernels have completed: the sampler entry points synchronise or run on a
     // caller stream the caller is responsible for; be safe and drain the device first)
@@ -677,7 +687,28 @@ int towr_b200_batch_sample_trajectory(towr_b200_batch* b, int n, double dt, cons
     if (!x || !rows_out) throw std::runtime_error("null host buffer");
     if (n == 0) return;
     Check(cudaSetDevice(b->device), "cudaSetDevice");
-    const towr_b200_batch::Traj& t = TrajFor(b, dt);
+    SampleHost(b, TrajFor(b, dt), n, x, rows_out);
+  });
+}
+
+int towr_b200_batch_sample_points(towr_b200_batch* b, int n, const double* times, int n_times, const double* x,
+                                  double* rows_out) {
+  return Guard([&] {
+    if (!b || n < 0 || n > b->n) throw std::runtime_error("bad problem count");
+    if (!times || n_times < 0 || !x || !rows_out) throw std::runtime_error("null host buffer");
+    if (n == 0 || n_times == 0) return;
+    Check(cudaSetDevice(b->device), "cudaSetDevice");
+    towr_b200_batch::Traj t;                             // not cached: the time list is the caller's
+    tb::BuildTrajTablesAt(b->st->hp, b->st->spec, std::vector<double>(times, times + n_times), t.host);
+    UploadTraj(b, &t);
+    SampleHost(b, t, n, x, rows_out);                    // synchronises before t's tables are freed
+  });
+}
+
+}  // extern "C"
+namespace {
+void SampleHost(towr_b200_batch* b, const towr_b200_batch::Traj& t, int n, const double* x, double* rows_out) {
+  {
     const size_t per = static_cast<size_t>(t.dev.n_samples) * t.dev.width;
     if (!b->x_dev) {
       Check(cudaMalloc(&b->x_dev, sizeof(double) * b->dp.n_vars * b->n), "cudaMalloc(staging)");
@@ -701,8 +732,10 @@ int towr_b200_batch_sample_trajectory(towr_b200_batch* b, int n, double dt, cons
     b->launches += 1;
     Check(cudaMemcpyAsync(rows_out, b->traj_out_dev, sizeof(double) * per * n, cudaMemcpyDeviceToHost, b->stream), "D2H rows");
     Check(cudaStreamSynchronize(b->stream), "sample_trajectory");
-  });
+  }
 }
+}  // namespace
+extern "C" {
 
 int towr_b200_trajectory_write_csv(const towr_b200_structure* st, const double* rows, int n_rows, const char* filename) {
   return Guard([&] {

@@ -38,17 +38,30 @@ struct Derived {           // quantities several variable sets share
   V3 ee_final[kMaxEE];     // final foothold, on the terrain
 };
 
+TerrainTable SpecTable(const towr_b200_spec& s) {
+  TerrainTable t{};
+  if (s.terrain_id != TOWR_B200_TERRAIN_TABLE) return t;
+  t.n = s.terrain_table_n;
+  t.mode = s.terrain_table_mode;
+  for (int i = 0; i < t.n && i < kMaxTerrainKnots; ++i) { t.x[i] = s.terrain_table_x[i]; t.h[i] = s.terrain_table_h[i]; }
+  return t;
+}
+// terrain_->GetHeight etc. of the problem's own height map
+TerrainSample SpecTerrain(const towr_b200_spec& s, double x, double y) {
+  return s.terrain_id == TOWR_B200_TERRAIN_TABLE ? EvalTerrainTable(SpecTable(s), x) : EvalTerrain(s.terrain_id, x, y);
+}
+
 Derived Derive(const towr_b200_spec& s) {
   Derived d;
   d.T = TotalTime(s);
   const double x = s.final_base_lin[0], y = s.final_base_lin[1];
-  d.base_final_pos = V3{{x, y, EvalTerrain(s.terrain_id, x, y).h - s.nominal_stance[0][2]}};
+  d.base_final_pos = V3{{x, y, SpecTerrain(s, x, y).h - s.nominal_stance[0][2]}};
   double R[3][3];
   EulerToR(V3{{0.0, 0.0, s.final_base_ang[2]}}, R);
   for (int e = 0; e < s.n_ee; ++e) {
     V3 off = MatVec(R, mk(s.nominal_stance[e]), false);
     double ex = s.final_base_lin[0] + off.v[0], ey = s.final_base_lin[1] + off.v[1];
-    d.ee_final[e] = V3{{ex, ey, EvalTerrain(s.terrain_id, ex, ey).h}};
+    d.ee_final[e] = V3{{ex, ey, SpecTerrain(s, ex, ey).h}};
   }
   return d;
 }
@@ -225,6 +238,7 @@ void FillProblemConst(const towr_b200_spec& s, ProblemConst& pc) {
   for (int i = 0; i < 9; ++i) pc.I[i] = I[i];
   pc.terrain_id = s.terrain_id;
   pc.pad = 0;
+  pc.table = SpecTable(s);
 }
 
 void ProblemConstantValues(const HostProgram& hp, double mass, double torque_k_friction, bool flat_basis, double* vals) {

@@ -30,6 +30,17 @@ struct ItemCtx {
   int n_ee;
 };
 
+// the problem's height map at (x, y).  Terrains given as data (terrain id 8, ProblemConst::table) are read only by the
+// CURV instantiations: a class that admits them is built with that flag (TerrainClassBits, terrain.h), so the analytic
+// terrains' kernels carry no table code
+template <class L>
+__device__ __forceinline__ TerrainSample TerrainAt(const ItemCtx<L>& cx, double x, double y) {
+  if constexpr (L::CURV) {
+    if (cx.pc->terrain_id == kTerrainTableId) return EvalTerrainTable(cx.pc->table, x);
+  }
+  return EvalTerrain(cx.pc->terrain_id, x, y);
+}
+
 // column j of PhaseDurations::GetJacobianOfPos (phase_durations.cc:126-154): d pos / d (phase duration j)
 __device__ __forceinline__ void DurationColumn(int j, int cur, int n_phases, const double dxdT[3], const double xd[3], double c[3]) {
   const bool in_last = cur == n_phases - 1;
@@ -427,6 +438,7 @@ __device__ __forceinline__ void ForceBasisScales(const TerrainSample& ts, int di
 template <class L, int ROWS>
 __device__ __forceinline__ void ItemCurvature(const ItemCtx<L>& cx, const ItemC& it) {
   const int dims = it.sub, nd = CurvDimCount(dims), E = cx.n_ee;
+  if (nd == 0) return;                                  // a class that only admits table terrains declares no block
   Pt3 p, f, tau;
   RtPoint rp;
   if constexpr (L::RT) {
@@ -438,7 +450,7 @@ __device__ __forceinline__ void ItemCurvature(const ItemCtx<L>& cx, const ItemC&
     EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 1, f);
     if (ROWS == 4) EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 2, tau);
   }
-  const TerrainSample ts = EvalTerrain(cx.pc->terrain_id, p.p[0], p.p[1]);
+  const TerrainSample ts = TerrainAt(cx, p.p[0], p.p[1]);
   double* G = cx.G + it.gslot * L::GS;
   int n_w = 0, n_sched = 0;
   if constexpr (L::RT) {
@@ -501,7 +513,7 @@ __device__ __forceinline__ void ItemForce(const ItemCtx<L>& cx, const ItemC& it)
     EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, p);
     EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 1, f);
   }
-  const TerrainSample ts = EvalTerrain(cx.pc->terrain_id, p.p[0], p.p[1]);
+  const TerrainSample ts = TerrainAt(cx, p.p[0], p.p[1]);
   double n[3], t1[3], t2[3];
   TerrainBasis(ts, n, t1, t2);
   const double mu = kFrictionCoeff;
@@ -552,7 +564,7 @@ __device__ __forceinline__ void ItemForceNode(const ItemCtx<L>& cx, const ItemC&
   const double* fn = cx.nodes + it.s0 * 6 * L::NS;
   const double* pn = cx.nodes + it.aux * 6 * L::NS;
   const double f[3] = {fn[0], fn[L::NS], fn[2 * L::NS]};
-  const TerrainSample ts = EvalTerrain(cx.pc->terrain_id, pn[0], pn[L::NS]);
+  const TerrainSample ts = TerrainAt(cx, pn[0], pn[L::NS]);
   double n[3], t1[3], t2[3];
   TerrainBasis(ts, n, t1, t2);
   const double mu = kFrictionCoeff;
@@ -607,7 +619,7 @@ __device__ __forceinline__ void ItemTorque(const ItemCtx<L>& cx, const ItemC& it
     EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 1, f);
     EvalSpline<kNeedPos, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + 2, tau);
   }
-  const TerrainSample ts = EvalTerrain(cx.pc->terrain_id, p.p[0], p.p[1]);
+  const TerrainSample ts = TerrainAt(cx, p.p[0], p.p[1]);
   double n[3], t1[3], t2[3];
   TerrainBasis(ts, n, t1, t2);
   const double mu = kFrictionCoeff, kf = cx.T.B[it.b0];
@@ -678,7 +690,7 @@ template <class L>
 __device__ __forceinline__ void ItemHeightNode(const ItemCtx<L>& cx, const ItemC& it, double offset) {
   const double* n = cx.nodes + it.s0 * 6 * L::NS;
   const double px = n[0], py = n[L::NS], pz = n[2 * L::NS];
-  const TerrainSample ts = EvalTerrain(cx.pc->terrain_id, px, py);
+  const TerrainSample ts = TerrainAt(cx, px, py);
   double* G = cx.G + it.gslot * L::GS;
   TB_G(0) = -ts.hx;
   TB_G(1) = -ts.hy;

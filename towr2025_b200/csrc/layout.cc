@@ -168,6 +168,15 @@ void ValidateSpec(const towr_b200_spec& s) {
       s.torque_polynomials_per_stance_phase < 1)
     throw std::runtime_error("polynomials per phase must be >= 1");
   if (s.terrain_id < 0 || s.terrain_id >= TOWR_B200_TERRAIN_COUNT) throw std::runtime_error("unknown terrain id");
+  if (s.terrain_id == TOWR_B200_TERRAIN_TABLE) {
+    if (s.terrain_table_n < 1 || s.terrain_table_n > TOWR_B200_MAX_TERRAIN_KNOTS) throw std::runtime_error("terrain table: 1..16 knots");
+    if (s.terrain_table_mode != TOWR_B200_TABLE_STEPS && s.terrain_table_mode != TOWR_B200_TABLE_RAMPS)
+      throw std::runtime_error("terrain table: mode must be TABLE_STEPS or TABLE_RAMPS");
+    for (int i = 0; i < s.terrain_table_n; ++i) {
+      if (!std::isfinite(s.terrain_table_x[i]) || !std::isfinite(s.terrain_table_h[i])) throw std::runtime_error("terrain table: non-finite knot");
+      if (i > 0 && !(s.terrain_table_x[i] > s.terrain_table_x[i - 1])) throw std::runtime_error("terrain table: knots must increase in x");
+    }
+  }
   if (s.n_costs < 0 || s.n_costs > TOWR_B200_MAX_COSTS) throw std::runtime_error("bad n_costs");
   for (int c = 0; c < s.n_costs; ++c) {
     if (s.cost_ids[c] == TOWR_B200_COST_ENERGY || s.cost_ids[c] == TOWR_B200_COST_ANG_MOM)
@@ -182,7 +191,7 @@ void BuildLayout(const towr_b200_spec& s, HostProgram& hp) {
   hp.n_ee = s.n_ee;
   hp.total_time = TotalTime(s);
   hp.optimize_durations = OptimizesDurations(s);
-  hp.curvature_dims = TerrainCurvatureDims(s.terrain_id);
+  hp.curvature_dims = TerrainClassBits(s.terrain_id);   // curvature dims | kClassTableTerrain
   const int E = s.n_ee;
   const std::vector<double> base_T = BasePolyDurations(s);
   const int n_base_nodes = static_cast<int>(base_T.size()) + 1;

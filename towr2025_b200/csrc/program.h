@@ -24,6 +24,8 @@ struct alignas(16) uint4 { unsigned int x, y, z, w; };
 #endif
 #include <vector>
 
+#include "terrain.h"
+
 namespace tb {
 
 // ---- device-visible records (plain data, shared by host and device code) ---------------------------------------
@@ -219,6 +221,7 @@ struct ProblemConst {   // per-problem constants read by the kernels
   double I[9];          // body inertia tensor, row-major, off-diagonals negated (single_rigid_body_dynamics.cc:36-44)
   int terrain_id;
   int pad;
+  TerrainTable table;   // terrain_id == kTerrainTableId: the problem's height profile (terrain.h)
 };
 
 // ---- host-side description ------------------------------------------------------------------------------------

@@ -23,6 +23,34 @@ struct TerrainSample {
   double hxx, hxy, hyx, hyy;
 };
 
+// A height map given as data (towr_b200_spec::terrain_table_*, terrain id 8): a profile along x, constant in y.
+constexpr int kTerrainTableId = 8, kMaxTerrainKnots = 16;
+struct TerrainTable {
+  int n, mode;               // mode 0: steps, 1: ramps
+  double x[kMaxTerrainKnots], h[kMaxTerrainKnots];
+};
+// steps: h = 0 before x[0], h[i] on [x[i], x[i+1]), h[n-1] from x[n-1] on.  ramps: h[0] before x[0], linear on
+// [x[i], x[i+1]) with h_x = (h[i+1] - h[i]) / (x[i+1] - x[i]), h[n-1] from x[n-1] on.  Second derivatives 0.
+TB_HD TerrainSample EvalTerrainTable(const TerrainTable& t, double x) {
+  TerrainSample s;
+  s.h = 0.0; s.hx = 0.0; s.hy = 0.0; s.hxx = 0.0; s.hxy = 0.0; s.hyx = 0.0; s.hyy = 0.0;
+  if (t.n < 1) return s;
+  if (x < t.x[0]) {
+    if (t.mode == 1) s.h = t.h[0];
+    return s;
+  }
+  int i = 0;
+  while (i + 1 < t.n && x >= t.x[i + 1]) ++i;       // x in [x[i], x[i+1]) or beyond the last knot
+  if (t.mode == 1 && i + 1 < t.n) {
+    const double slope = (t.h[i + 1] - t.h[i]) / (t.x[i + 1] - t.x[i]);
+    s.h = t.h[i] + slope * (x - t.x[i]);
+    s.hx = slope;
+  } else {
+    s.h = t.h[i];
+  }
+  return s;
+}
+
 TB_HD TerrainSample EvalTerrain(int id, double x, double y) {
   TerrainSample s;
   s.h = 0.0; s.hx = 0.0; s.hy = 0.0; s.hxx = 0.0; s.hxy = 0.0; s.hyx = 0.0; s.hyy = 0.0;
@@ -97,6 +125,11 @@ TB_HD int TerrainCurvatureDims(int id) { return id == 3 ? 1 : 0; }   // Gap: h_x
 
 // false: h_x = h_y = 0 everywhere (piecewise constant height): normal and tangents are the same constants at every (x, y)
 TB_HD bool TerrainHasSlope(int id) { return !(id == 0 || id == 2 || id == 7); }   // Flat, Stairs, FiveStepStairs
+TB_HD bool TerrainHasSlope(int id, const TerrainTable& t) { return id == kTerrainTableId ? t.mode == 1 : TerrainHasSlope(id); }
+// bit 2 of a class's curvature_dims: the class admits table terrains (its kernels are the CURV instantiations, the only
+// ones that read the table); bits 0, 1 as TerrainCurvatureDims
+constexpr int kClassTableTerrain = 4;
+TB_HD int TerrainClassBits(int id) { return id == kTerrainTableId ? kClassTableTerrain : TerrainCurvatureDims(id); }
 
 // normalised normal / tangents at (x,y): n = (-hx,-hy,1)/|.|, t1 = (1,0,hx)/|.|, t2 = (0,1,hy)/|.|
 // v.normalized() = v / sqrt(v.v) with the squared norm summed left to right

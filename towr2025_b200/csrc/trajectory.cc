@@ -25,14 +25,24 @@ std::vector<double> TrajectoryTimes(const HostProgram& hp, double dt) {
 }
 
 void BuildTrajTables(const HostProgram& hp, const towr_b200_spec& s, double dt, TrajTables& o) {
+  BuildTrajTablesAt(hp, s, TrajectoryTimes(hp, dt), o);
+  o.dt = dt;
+}
+
+void BuildTrajTablesAt(const HostProgram& hp, const towr_b200_spec& s, const std::vector<double>& times, TrajTables& o) {
   o = TrajTables{};
   o.n_vars = hp.n_vars;
   o.n_ee = hp.n_ee;
   o.width = TrajectoryWidth(hp.n_ee);
   o.rt = hp.optimize_durations;
   o.total_time = hp.total_time;
-  o.dt = dt;
-  o.times = TrajectoryTimes(hp, dt);
+  o.dt = 0.0;
+  // Spline::GetSegmentID asserts t_global >= 0 and runs off the end of the spline beyond its total time (spline.cc:48-66)
+  const VarSet* lin = hp.Find(kBaseLin);
+  const double T_total = std::accumulate(lin->poly_T.begin(), lin->poly_T.end(), 0.0);
+  for (double t : times)
+    if (!(t >= 0.0) || !(t <= T_total + 1e-9)) throw std::runtime_error("sample time outside [0, total time]");
+  o.times = times;
   o.n_samples = static_cast<int>(o.times.size());
   auto add = [&](const VarSet& v, int out_col, int n_out, int foot) {
     TrajSplineRec r{};

@@ -58,6 +58,8 @@ inline int TrajectoryWidth(int n_ee) { return 19 + 25 * n_ee; }
 // sample times of SaveTrajectoryToCSV: t = 0, t += dt while t <= T_total + 1e-9 (save_data.cpp:55,118)
 std::vector<double> TrajectoryTimes(const HostProgram& hp, double dt);
 void BuildTrajTables(const HostProgram& hp, const towr_b200_spec& s, double dt, TrajTables& out);
+// the same for an explicit list of global times in [0, T_total] (SplineHolder::...->GetPoint(t) at arbitrary t)
+void BuildTrajTablesAt(const HostProgram& hp, const towr_b200_spec& s, const std::vector<double>& times, TrajTables& out);
 size_t TrajSharedBytes(const TrajDevice& t);
 #ifdef __CUDACC__
 cudaError_t LaunchSampleTrajectory(const TrajDevice& t, const double* x, double* out, int n_problems, int sms,
