@@ -27,12 +27,21 @@ extern "C" const char* emu_last_error() { return g_err.c_str(); }
 
 // x: n_vars; g: n_rows; vals: nnz.  Mirrors the kernel's stages for one problem (P = 1).
 template <bool RT, bool CURV>
+static void EmuPart(const HostProgram& hp, const ProgramPart& part, const towr_b200_spec* s, const double* x, double* g, double* vals);
+
+// every part of the class's program (pack.cc): one kernel launch each on the device, disjoint rows and entries
+template <bool RT, bool CURV>
 static void EmuEval(const HostProgram& hp, const towr_b200_spec* s, const double* x, double* g, double* vals) {
-  const BlobLayout& L = hp.blob;
+  for (const ProgramPart& part : hp.parts) EmuPart<RT, CURV>(hp, part, s, x, g, vals);
+}
+
+template <bool RT, bool CURV>
+static void EmuPart(const HostProgram& hp, const ProgramPart& part, const towr_b200_spec* s, const double* x, double* g, double* vals) {
+  const BlobLayout& L = part.blob;
   ProblemConst pc;
   FillProblemConst(*s, pc);
   ItemCtx<Lockstep<1, RT, CURV>> cx;
-  cx.T = MakeTables(hp.blob_data.data(), L);
+  cx.T = MakeTables(part.blob_data.data(), L);
   cx.n_ee = hp.n_ee;
   std::vector<double> nodes(L.n_node_values), coef(6 * L.n_polys), G(hp.g_capacity), rtd(kRtd * L.n_polys), pdur(L.n_pdur + 1);
   for (int i = 0; i < L.n_node_values; ++i) nodes[i] = cx.T.node_src[i] != 0xFFFF ? x[cx.T.node_src[i]] : 0.0;
@@ -88,7 +97,7 @@ static void EmuEval(const HostProgram& hp, const towr_b200_spec* s, const double
   }
   cx.nodes = nodes.data(); cx.coef = coef.data(); cx.G = G.data(); cx.g = g; cx.pc = &pc;
   cx.rtd = rtd.data(); cx.pdur = pdur.data();
-  for (const SegmentRec& sg : hp.segments) {
+  for (const SegmentRec& sg : part.segments) {
     std::fill(G.begin(), G.end(), std::nan(""));
     G[kGOne] = 1.0; G[kGMass] = pc.mass; G[kGMinusOne] = -1.0;
     for (int i = 0; i < sg.n_items; ++i) RunItem<Lockstep<1, RT, CURV>>(cx, cx.T.items[sg.item0 + i]);   // level-0 items come first

@@ -57,6 +57,36 @@ def test_emulated_kernel_segment_capacity(product, oracle, emu, monkeypatch):
     assert np.array_equal(ref[0], alt[0]) and np.array_equal(ref[1], alt[1])
 
 
+def fine_dt_spec(M, robot, combo, T_total, dt, optimise=False):
+    """BASELINE config 5's sampling convention (tools/mixed_sweep.py): dynamic dt, range of motion 0.8 dt, force 0.2 dt."""
+    s = M.make_spec(robot, combo, T_total, optimize_durations=optimise)
+    s.dt_constraint_dynamic = dt
+    s.dt_constraint_range_of_motion = 0.8 * dt
+    s.dt_constraint_force = 0.2 * dt
+    return s
+
+
+def test_emulated_kernel_program_parts(product, oracle, emu, monkeypatch):
+    """Classes whose tables exceed one SM are split into parts (pack.cc: runs of segments with their own tables, one launch
+    each).  A forced split of a small class must not change a bit; a class that needs the split (monoped, dt 0.01: 87 071
+    stored entries, more than 8191 B constants) must match the oracle."""
+    T, O = product, oracle
+    s = T.make_spec(T.Anymal, T.C1, 2.0, goal=(1.1, 0.1, 0.2), optimize_durations=True)
+    st = T.Structure(s)
+    x = perturbed(st.x0(s), 5, 0.02)
+    ref = emu_eval(emu, s, st, x)
+    monkeypatch.setenv("TOWR_B200_MAX_BLOB", "24000")
+    alt = emu_eval(emu, s, st, x)
+    monkeypatch.delenv("TOWR_B200_MAX_BLOB")
+    assert np.array_equal(ref[0], alt[0]) and np.array_equal(ref[1], alt[1])
+    s = fine_dt_spec(T, T.Monoped, T.C0, 2.4, 0.01)
+    st = T.Structure(s)
+    assert st.nnz == 87071
+    x = perturbed(st.x0(s), 6, 0.05)
+    g, v = emu_eval(emu, s, st, x)
+    check_against_oracle(O, fine_dt_spec(O, O.Monoped, 0, 2.4, 0.01), st, x, g, v, False)
+
+
 def test_emulated_kernel_reproduces_committed_fixtures(product, emu):
     """tests/golden/*.npz (oracle outputs frozen by tests/golden/make_golden.py)."""
     import glob

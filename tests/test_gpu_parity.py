@@ -58,6 +58,42 @@ def test_gap_superset_pattern_matches_oracle(product, oracle, case):
     assert len(extras) > 1
 
 
+@pytest.mark.parametrize("which", ["anymal_dt0.02", "biped_dt0.01_durations"])
+def test_multi_part_classes_match_oracle(product, oracle, which, monkeypatch):
+    """Classes split into parts (pack.cc; BASELINE config 5's fine sampling steps): several launches per evaluation, values
+    against the oracle; and a small class forced into parts is bit-identical to its single-part evaluation."""
+    from test_emu import fine_dt_spec
+    from util import to_oracle_spec
+    T, O = product, oracle
+    if which == "anymal_dt0.02":
+        s, rt = fine_dt_spec(T, T.Anymal, T.C1, 2.0, 0.02), False
+    else:
+        s, rt = fine_dt_spec(T, T.Biped, T.C0, 2.4, 0.01, optimise=True), True
+    st = T.Structure(s)
+    n = 5
+    x = np.stack([perturbed(st.x0(s), 60 + i, 0.02 if rt else 0.08) for i in range(n)])
+    b = T.Batch(st, n)
+    b.set_all(s)
+    assert "parts" in b.kernel_info
+    g, v = b.eval(x)
+    assert (b.status() == 0).all()
+    for i in (0, n - 1):
+        check_against_oracle(O, to_oracle_spec(O, s), st, x[i], g[i], v[i], rt)
+    small = T.make_spec(T.Anymal, T.C1, 2.0, optimize_durations=rt)
+    st1 = T.Structure(small)
+    xs = np.stack([perturbed(st1.x0(small), 80 + i, 0.02) for i in range(7)])
+    b1 = T.Batch(st1, 7)
+    b1.set_all(small)
+    ref = b1.eval(xs)
+    monkeypatch.setenv("TOWR_B200_MAX_BLOB", "24000")
+    st2 = T.Structure(small)
+    b2 = T.Batch(st2, 7)
+    b2.set_all(small)
+    assert "parts" in b2.kernel_info
+    alt = b2.eval(xs)
+    assert np.array_equal(ref[0], alt[0]) and np.array_equal(ref[1], alt[1])
+
+
 def test_table_terrain_reproduces_the_five_step_stairs(product):
     """The hopper example's own HeightMap (FiveStepStairs, hopper_example.cc:53-91) written as a table of five steps gives
     the same g and Jacobian values as the built-in terrain id 7, and per-problem tables differ within one batch."""

@@ -90,7 +90,18 @@ struct towr_b200_batch {
   // H2D of the constants or a status read-out is ordered after it
   cudaEvent_t device_eval_done = nullptr;
   bool device_eval_pending = false;
-  tb::DeviceProgram dp{};
+  tb::DeviceProgram dp{};                 // part 0 (sizes, flags); classes with large tables have further parts
+  std::vector<tb::DeviceProgram> dps;     // one per ProgramPart (pack.cc): one kernel launch each per evaluation
+  // evaluates problems 0..n-1 of the given device arrays: every part's kernel, in order, on `s`
+  cudaError_t LaunchAll(const tb::ProblemConst* pcs, int what, const double* x, double* g, double* vals, int* status, int n,
+                        cudaStream_t s) {
+    for (const tb::DeviceProgram& part : dps) {
+      cudaError_t e = tb::LaunchEval(part, pcs, what, x, g, vals, status, n, var, max_ctas, s);
+      if (e != cudaSuccess) return e;
+      launches += 1;
+    }
+    return cudaSuccess;
+  }
   std::vector<void*> owned;            // device allocations
   std::vector<tb::ProblemConst> pc_host;
   tb::ProblemConst* pc_dev = nullptr;
@@ -244,10 +255,14 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     const tb::HostProgram* hpp = &st->hp;
     const long long optin = static_cast<long long>(prop.sharedMemPerBlockOptin);
     auto need = [](const tb::HostProgram& h, int g_cap, const tb::EvalVariant& v) {
-      tb::DeviceProgram t{};
-      t.blob = h.blob;
-      t.g_capacity = g_cap;
-      return static_cast<long long>(tb::EvalSharedBytes(t, v.lanes, v.streams, v.mode())) + 1024;   // + the kernel's static shared memory
+      long long worst = 0;
+      for (const tb::ProgramPart& part : h.parts) {
+        tb::DeviceProgram t{};
+        t.blob = part.blob;
+        t.g_capacity = g_cap;
+        worst = std::max(worst, static_cast<long long>(tb::EvalSharedBytes(t, v.lanes, v.streams, v.mode())) + 1024);   // + the kernel's static shared memory
+      }
+      return worst;
     };
     // rebuilds the program with at most `cap` G slots per segment (more, smaller segments); true when `v` then fits
     auto rebuild = [&](long long cap, const tb::EvalVariant& v) {
@@ -299,11 +314,17 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     dp.total_time = hp.total_time;
     dp.g_capacity = hp.g_capacity;
     dp.curvature_dims = hp.curvature_dims;
-    dp.blob = hp.blob;
     auto keep = [&](auto* p) { b->owned.push_back(const_cast<void*>(static_cast<const void*>(p))); return p; };
-    dp.blob_data = keep(Upload(hp.blob_data));
     dp.entries = keep(Upload(hp.entries_dev));
-    dp.segments = keep(Upload(hp.segments));
+    for (const tb::ProgramPart& part : hp.parts) {
+      tb::DeviceProgram d = dp;                            // the sizes and flags are the class's
+      d.n_segments = static_cast<int>(part.segments.size());
+      d.blob = part.blob;
+      d.blob_data = keep(Upload(part.blob_data));
+      d.segments = keep(Upload(part.segments));
+      b->dps.push_back(d);
+    }
+    dp = b->dps.front();
     b->pc_host.assign(n_problems, tb::ProblemConst{});
     Check(cudaMalloc(&b->pc_dev, sizeof(tb::ProblemConst) * n_problems), "cudaMalloc(consts)");
     keep(b->pc_dev);
@@ -313,7 +334,8 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     auto try_variant = [&](const tb::EvalVariant& v) {
       if (b->var.lanes || !tb::EvalVariantBuilt(dp, v)) return;
       if (need(hp, hp.g_capacity, v) > optin) return;
-      const int occ = tb::EvalOccupancy(dp, v);
+      int occ = 1 << 30;
+      for (const tb::DeviceProgram& part : b->dps) occ = std::min(occ, tb::EvalOccupancy(part, v));
       if (occ < 1) return;
       b->var = v;
       b->max_ctas = prop.multiProcessorCount * occ;
@@ -424,10 +446,9 @@ int towr_b200_batch_eval_device(towr_b200_batch* b, int n, int what, const doubl
       b->SyncConsts();
       Check(cudaStreamSynchronize(b->stream), "sync consts");
     }
-    Check(tb::LaunchEval(b->dp, b->pc_dev, what, d_x, d_g, d_jac_values, b->status_dev, n, b->var, b->max_ctas, s), "launch");
+    Check(b->LaunchAll(b->pc_dev, what, d_x, d_g, d_jac_values, b->status_dev, n, s), "launch");
     Check(cudaEventRecord(b->device_eval_done, s), "record eval_device");
     b->device_eval_pending = true;
-    b->launches += 1;
   });
 }
 
@@ -484,9 +505,8 @@ int towr_b200_batch_eval(towr_b200_batch* b, const int* ids, int n, int what, co
       cudaStream_t st = (k & 1) ? b->stream2 : b->stream;
       const size_t o = static_cast<size_t>(c0);
       Check(cudaMemcpyAsync(b->x_dev + o * dp.n_vars, x + o * dp.n_vars, sizeof(double) * dp.n_vars * m, cudaMemcpyHostToDevice, st), "H2D x");
-      Check(tb::LaunchEval(dp, pcs + c0, kernel_what, b->x_dev + o * dp.n_vars, want_g ? b->g_dev + o * dp.n_rows : nullptr,
-                           (want_jac || want_dyn) ? b->v_dev + o * dp.nnz : nullptr, b->status_dev + c0, m, b->var, b->max_ctas, st), "launch");
-      b->launches += 1;
+      Check(b->LaunchAll(pcs + c0, kernel_what, b->x_dev + o * dp.n_vars, want_g ? b->g_dev + o * dp.n_rows : nullptr,
+                         (want_jac || want_dyn) ? b->v_dev + o * dp.nnz : nullptr, b->status_dev + c0, m, st), "launch");
       if (want_g)
         Check(cudaMemcpyAsync(g_out + o * dp.n_rows, b->g_dev + o * dp.n_rows, sizeof(double) * dp.n_rows * m, cudaMemcpyDeviceToHost, st), "D2H g");
       if (want_jac)
@@ -829,6 +849,10 @@ int towr_b200_batch_kernel_info(const towr_b200_batch* b, char* buf, int n) {
                   b->var.streams, b->var.ring ? 1 : 0, b->dp.curvature_dims != 0, b->max_ctas,
                   (b->var.split ? 384 : 256) * b->var.lanes * b->var.streams,
                   tb::EvalSharedBytes(b->dp, b->var.lanes, b->var.streams, b->var.mode()), b->dp.n_segments);
+    if (b->dps.size() > 1) {                               // classes with large tables: one launch per part
+      const size_t used = std::strlen(buf);
+      std::snprintf(buf + used, static_cast<size_t>(n) - used, " in the first of %zu parts (one launch each)", b->dps.size());
+    }
   });
 }
 void* towr_b200_batch_stream(const towr_b200_batch* b) { return b ? static_cast<void*>(b->stream) : nullptr; }

@@ -257,6 +257,14 @@ enum RowBoundKind { kBoundZero = 0, kBoundTerrainSwing, kBoundRom, kBoundForceNo
                     kBoundBaseHeight, kBoundTotalDuration, kBoundNone, kBoundTorqueX, kBoundTorqueY };
 struct RowBound { int kind, ee, dim; };
 
+// a run of consecutive segments with its own class tables (pack.cc): classes with few samples have one
+struct ProgramPart {
+  BlobLayout blob{};
+  std::vector<unsigned char> blob_data;
+  std::vector<SegmentRec> segments;    // item0 relative to this part's items, entry0 absolute
+  int g_capacity = 0;                  // max g_size over its segments
+};
+
 struct HostProgram {
   int n_vars = 0, n_rows = 0, nnz = 0, n_ee = 0;
   bool optimize_durations = false;
@@ -276,10 +284,12 @@ struct HostProgram {
   std::vector<RtSpline> rt_splines;
   std::vector<RtFoot> rt_feet;
   std::vector<uint32_t> poly_meta;
-  // packed for the device (pack.cc)
+  // packed for the device (pack.cc): one ProgramPart per kernel launch of an evaluation.  blob / blob_data mirror
+  // parts[0]; segments is the concatenation of the parts' (padded) segment lists
+  std::vector<ProgramPart> parts;
   BlobLayout blob{};
   std::vector<unsigned char> blob_data;
-  std::vector<uint32_t> entries_dev;    // byte-offset form of entries
+  std::vector<uint32_t> entries_dev;    // byte-offset form of entries (B offsets local to the entry's part)
   // storage positions of the entries whose value depends on x (ascending).  The others are G[kGOne | kGMinusOne | kGMass]
   // * B: constant for a problem (ProblemConstantValues); the host interface can leave them off the bus
   std::vector<int> dyn_index;
