@@ -15,14 +15,7 @@ def _clip(a):
     return np.clip(a, -1e20, 1e20)     # ifopt::inf = 1e20; the C++ oracle reports +-infinity where the reference uses it
 
 
-# TerrainConstraintHard (Parameters::TerrainHard = 4, terrain_constraint_hard.cc): restated by both legs, not yet a product class
-TERRAIN_HARD_CASES = [
-    ("biped_walk_terrainhard_block", 1, 0, 2.4, (1.1, 0.0, 0.1), 1, (4,)),
-    ("monoped_hop_terrainhard_slope_durations", 0, 0, 2.4, (1.3, 0.0, 0.0), 4, (4,), True),
-]
-
-
-@pytest.mark.parametrize("case", CASES + GAP_CASES + TERRAIN_HARD_CASES, ids=lambda c: c[0])
+@pytest.mark.parametrize("case", CASES + GAP_CASES, ids=lambda c: c[0])
 def test_cpp_oracle_matches_numpy_restatement(oracle, case):
     O = oracle
     s = mk(O, case)

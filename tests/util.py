@@ -60,6 +60,17 @@ CASES = [
 ]
 
 
+# TerrainConstraintHard (Parameters::TerrainHard = 4, terrain_constraint_hard.cc; biped_example.cc:173-174 enables it with
+# Torque): one row per (range-of-motion sample, foot)
+TERRAIN_HARD = 4
+TERRAIN_HARD_CASES = [
+    ("biped_walk_terrainhard_block", 1, 0, 2.4, (1.1, 0.0, 0.1), 1, (TERRAIN_HARD,)),
+    ("monoped_hop_terrainhard_slope_durations", 0, 0, 2.4, (1.3, 0.0, 0.0), 4, (TERRAIN_HARD,), True),
+    ("biped_walk_terrainhard_torque_flat", 1, 0, 2.4, (1.0, 0.0, 0.0), 0, (TORQUE, TERRAIN_HARD)),      # biped_example.cc:173-174
+    ("anymal_trot_terrainhard_durations_chimney", 3, 1, 2.0, (1.2, 0.0, 0.0), 5, (TERRAIN_HARD,), True),
+]
+CASES += TERRAIN_HARD_CASES
+
 # Terrain with curvature (Gap, id 3): the class declares the force / torque constraint's ee-motion block for every sample
 # (superset); the reference / oracle store such an entry only where its scale is non-zero (value-dependent pattern).
 GAP = 3

@@ -697,6 +697,95 @@ __device__ __forceinline__ void ItemHeightNode(const ItemCtx<L>& cx, const ItemC
   if (cx.g) cx.g[it.row * L::RS] = (it.type == kItemBaseHeightNode) ? (pz - ts.h) - offset : pz - ts.h;
 }
 
+// TerrainConstraintHard (terrain_constraint_hard.cc:50-132), one row per (sample, foot):
+//   g = (p_z - h(p)) - min(k |v_tan|, k),   v_tan = (v.t1, v.t2) with the normalised tangents, k = 0.02
+//   d g / d(column of dimension d) = c_d J_pos - (k td_d) J_vel:  c_Z = 1, c_X = -h_x, c_Y = -h_y; the velocity term only
+//   while |v_tan| > 1e-6 and k |v_tan| < 0.05 - 1e-6 (:112-128), td = (v.t1 t1 + v.t2 t2) / |v_tan|.
+// The reference forms the row as J_pos.row(Z), then -= h_x J_pos.row(X), -= h_y J_pos.row(Y), then -= (k td_d) J_vel.row(d):
+// a column of dimension X holds 0 - h_x J_pos = -(h_x J_pos), then minus the velocity product.
+// Fixed durations: B[b0 + 3 j ..] = J_pos, J_vel, dimension of stored column j (sub columns) -> G[j].
+// Optimised durations: every column of the set; pos / vel weight sums of the active polynomial in scratch, G[c] finished.
+template <class L>
+__device__ __forceinline__ void ItemTerrainHard(const ItemCtx<L>& cx, const ItemC& it) {
+  constexpr double k_coeff = 0.02;
+  Pt3 p;
+  RtPoint rp;
+  if constexpr (L::RT) rp = EvalSplineRt<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0, p);
+  else EvalSpline<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, it.s0, p);
+  const TerrainSample ts = TerrainAt(cx, p.p[0], p.p[1]);
+  double n[3], t1[3], t2[3];
+  TerrainBasis(ts, n, t1, t2);
+  const double vt1 = (p.v[0] * t1[0] + p.v[1] * t1[1]) + p.v[2] * t1[2];
+  const double vt2 = (p.v[0] * t2[0] + p.v[1] * t2[1]) + p.v[2] * t2[2];
+  const double mag = sqrt(vt1 * vt1 + vt2 * vt2);
+  if (cx.g) {
+    const double delta_z = p.p[2] - ts.h;
+    const double a = k_coeff * mag;
+    cx.g[it.row * L::RS] = delta_z - (a < k_coeff ? a : k_coeff);       // std::min(k |v_tan|, k)
+  }
+  const double slope[3] = {ts.hx, ts.hy, 0.0};
+  double kv[3] = {0.0, 0.0, 0.0};
+  bool vel_term = false;
+  if (mag > 1e-6 && k_coeff * mag < 0.05 - 1e-6) {
+    vel_term = true;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) kv[d] = k_coeff * ((vt1 * t1[d] + vt2 * t2[d]) / mag);
+  }
+  auto finish = [&](int d, double jp, double jv) {
+    double v = d == 2 ? jp : -(slope[d] * jp);
+    if (vel_term) v = v - kv[d] * jv;
+    return v;
+  };
+  double* G = cx.G + it.gslot * L::GS;
+  if constexpr (L::RT) {
+    const RtSpline sm = cx.T.rt_splines[it.ee];
+    double* Wp = G + sm.n_cols * L::GS;
+    double* Wv = Wp + sm.n_cols * L::GS;
+    for (int c = 0; c < sm.n_cols; ++c) { Wp[c * L::GS] = 0.0; Wv[c * L::GS] = 0.0; }
+    const double* q = cx.rtd + rp.poly * kRtd * L::NS;
+    const double t = rp.t, T = rp.T, T2 = q[kRtT2 * L::NS], T3 = q[kRtT3 * L::NS];
+    const double r1 = q[kRtR1 * L::NS], r2 = q[kRtR2 * L::NS], r3 = q[kRtR3 * L::NS];
+    const double tt2 = t * t, tt3 = Cube(t);
+    double bp[4], bv[4];                                 // polynomial.cc:106-175, by side * 2 + node derivative
+    bp[0] = ExactDiv(2 * tt3, T3, r3) - ExactDiv(3 * tt2, T2, r2) + 1;
+    bp[1] = t - ExactDiv(2 * tt2, T, r1) + ExactDiv(tt3, T2, r2);
+    bp[2] = ExactDiv(3 * tt2, T2, r2) - ExactDiv(2 * tt3, T3, r3);
+    bp[3] = ExactDiv(tt3, T2, r2) - ExactDiv(tt2, T, r1);
+    bv[0] = ExactDiv(6 * tt2, T3, r3) - ExactDiv(6 * t, T2, r2);
+    bv[1] = ExactDiv(3 * tt2, T2, r2) - ExactDiv(4 * t, T, r1) + 1;
+    bv[2] = ExactDiv(6 * t, T2, r2) - ExactDiv(6 * tt2, T3, r3);
+    bv[3] = ExactDiv(3 * tt2, T2, r2) - ExactDiv(2 * t, T, r1);
+    const int n0 = cx.T.polys[rp.poly] & 0xFFFF;
+    unsigned touched = 0;                                // columns of the active polynomial (at most 12, by first hit)
+    int col_of[12], dim_of[12];
+#pragma unroll
+    for (int side = 0; side < 2; ++side)
+#pragma unroll
+      for (int deriv = 0; deriv < 2; ++deriv)
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+          const unsigned src = cx.T.node_src[(n0 + side) * 6 + deriv * 3 + d];
+          if (src != 0xFFFFu) {
+            const int c = static_cast<int>(src) - sm.col0;
+            Wp[c * L::GS] = Wp[c * L::GS] + bp[side * 2 + deriv];
+            Wv[c * L::GS] = Wv[c * L::GS] + bv[side * 2 + deriv];
+            col_of[touched] = c;
+            dim_of[touched] = d;
+            ++touched;
+          }
+        }
+    for (int c = 0; c < sm.n_cols; ++c) G[c * L::GS] = 0.0;
+    for (unsigned i = 0; i < touched; ++i) {
+      const int c = col_of[i];
+      G[c * L::GS] = finish(dim_of[i], Wp[c * L::GS], Wv[c * L::GS]);
+    }
+  } else {
+    const double* Bc = cx.T.B + it.b0;
+    for (int j = 0; j < it.sub; ++j)
+      TB_G(j) = finish(static_cast<int>(Bc[3 * j + 2]), Bc[3 * j], Bc[3 * j + 1]);
+  }
+}
+
 // SwingConstraint (swing_constraint.cc:54-78)
 template <class L>
 __device__ __forceinline__ void ItemSwingNode(const ItemCtx<L>& cx, const ItemC& it) {
@@ -753,6 +842,7 @@ __device__ __forceinline__ void RunItem(const ItemCtx<L>& cx, const ItemC& it) {
     case kItemRomPre: ItemRomPre<L>(cx, it); break;
     case kItemRomFoot: ItemRomFoot<L>(cx, it); break;
     case kItemForce: ItemForce<L>(cx, it); break;
+    case kItemTerrainHard: ItemTerrainHard<L>(cx, it); break;
     case kItemTorque: ItemTorque<L>(cx, it); break;
     case kItemForceNode: ItemForceNode<L>(cx, it); break;
     case kItemBaseRom: ItemBaseRom<L>(cx, it); break;

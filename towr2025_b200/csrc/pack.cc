@@ -22,8 +22,9 @@ int Align16(int v) { return (v + 15) & ~15; }
 
 // B constants an item reads by position from ItemRec::b0 (structure.cc): the dynamic sample's 16 Hermite basis values
 // (every item derived from the sample carries the same b0), the torque constraint's k_friction
-int ItemBRun(int type) {
+int ItemBRun(int type, int sub) {
   switch (type) {
+    case kItemTerrainHard: return 3 * sub;               // (J_pos, J_vel, dim) per stored column; 0 with optimised durations
     case kItemDynPre: case kItemDynFoot: case kItemDynWrench: case kItemDynJlin: case kItemDynCol: return 16;
     case kItemTorque: return 1;
     default: return 0;
@@ -99,7 +100,7 @@ void PackRange(HostProgram& hp, const std::vector<SegmentRec>& wide, int seg0, i
     c.sub = static_cast<uint8_t>(it.sub);
     c.ee = static_cast<uint8_t>(it.ee);
     c.n_ee = static_cast<uint8_t>(it.n_ee);
-    const int run = ItemBRun(it.type);
+    const int run = ItemBRun(it.type, it.sub);
     const int b0 = run ? local_run(it.b0, run) : 0;
     if (it.gslot > 0xFFFF || it.aux > 0xFFFF) throw std::runtime_error("item slot out of range");
     if (b0 > 0xFFFF) throw Unfit("B runs beyond 65535 entries");
@@ -130,6 +131,7 @@ void PackRange(HostProgram& hp, const std::vector<SegmentRec>& wide, int seg0, i
         add_sample(it.s[kSTorque + it.ee]);
         break;
       case kItemRomFoot: add_sample(it.s[kSMotion + it.ee]); break;
+      case kItemTerrainHard: add_sample(it.s[kSMotion + it.ee]); break;
       case kItemForce:
         add_sample(it.s[kSMotion + it.ee]);
         add_sample(it.s[kSForce + it.ee]);

@@ -55,6 +55,7 @@ enum ItemType : int {
   kItemBaseRom,         // base_motion_constraint.cc:60-85         6 rows per sample (base euler angles, base position)
   kItemTorque,          // torque_constraint_discretized.cc:105-235  4 rows per (sample, foot)
   kItemDynFoot,         // per (dynamic sample, foot): f_e, c - p_e slots and the foot's torque term f_e x (c - p_e) + tau_e
+  kItemTerrainHard,     // terrain_constraint_hard.cc:50-132         1 row per (sample, foot), finished ee-motion columns
   // level 1: read the scratch slots of a level-0 item (ItemC::aux)
   kItemDynWrench,       // dynamic_constraint.cc:63-148: the 6 g rows of a dynamic sample (feet summed in order)
   kItemDynJlin,         // row (sub) of the finished base-lin angular block -sum_e Cross(f_e) J_pos of a dynamic sample
@@ -67,7 +68,7 @@ constexpr int kItemPad = 16;   // items of one kind are padded to a multiple of 
 inline int ItemCostRank(int type) {
   switch (type) {
     case kItemDynPre: case kItemDynCol: return 0;
-    case kItemForce: case kItemTorque: case kItemForceNode: case kItemRomFoot: return 1;
+    case kItemForce: case kItemTorque: case kItemForceNode: case kItemRomFoot: case kItemTerrainHard: return 1;
     case kItemDynFoot: case kItemRomPre: return 2;
     case kItemDynJlin: case kItemBaseRom: return 3;
     case kItemDynWrench: return 4;

@@ -260,6 +260,7 @@ class Builder {
   void EmitForceNodes(int ee);
   void EmitTorqueDisc(int ee);
   void EmitBaseRom();
+  void EmitTerrainHard(int ee);
   void EmitRomSplit();
   void EmitTotalDuration(int ee);
   void EmitSwing(int ee);
@@ -882,6 +883,58 @@ void Builder::EmitSwing(int ee) {
   EndSet();
 }
 
+// TerrainConstraintHard (terrain_constraint_hard.cc:34-132), one row per sample of dt_constraint_range_of_motion_
+// (nlp_formulation.cc:476-488): g = p_z - h(p) - min(k |v_tangent|, k).  Only the ee-motion block exists (the reference
+// gives no ee-schedule block).  A row stores the union of J_pos rows Z, X, Y and - structurally, whether or not the
+// velocity term is active - the same columns of J_vel: every variable of the active polynomial's two nodes (all variables
+// of the set with optimised durations).  The value of a column of dimension d is
+//   c_d J_pos - (k td_d) J_vel,  c_Z = 1, c_X = -h_x, c_Y = -h_y,  td = (v.t1 t1 + v.t2 t2) / |v_tangent| or 0,
+// two products, so the item finishes it: fixed durations read (J_pos, J_vel, d) per column from a B run, optimised
+// durations accumulate the run-time Hermite weights (ItemTerrainHard, items.cuh).  Entries are G[slot] * 1.
+void Builder::EmitTerrainHard(int ee) {
+  const VarSet& mo = Set(kEEMotion, ee);
+  const std::vector<double> ts = SampleTimes(hp_.total_time, s_.dt_constraint_range_of_motion);
+  const int one = AddB(1.0);
+  const int per_item_rt = (3 * mo.n_vars) | 1;            // finished values, then scratch: pos and vel weight sums
+  const int chunk = std::max(1, 960 / (rt() ? per_item_rt : 12));
+  for (size_t k = 0; k < ts.size(); ++k) {
+    if (k % chunk == 0) {
+      if (k == 0) { BeginGroup(); BeginSet("terrainhard-" + std::to_string(ee), static_cast<int>(ts.size())); }
+      else BeginGroup(static_cast<int>(k));
+    }
+    ItemRec it = NewItem(kItemTerrainHard);
+    it.ee = static_cast<short>(ee);
+    it.row[0] = set_row0_ + static_cast<int>(k);
+    Bound(static_cast<int>(k), kBoundBaseHeight);          // (0, 1e20), terrain_constraint_hard.cc:72-77
+    if (rt()) {
+      it.gslot = AllocG(per_item_rt);
+      it.s[kSMotion + ee] = AtRt(0, ee, ts[k]);
+      it.sub = 0;
+      hp_.items.push_back(it);
+      for (auto& c : AllCols(mo)) {
+        Term tm; tm.g = it.gslot + c.first; tm.b = one;
+        Add(static_cast<int>(k), mo.col0 + c.first, tm);
+      }
+      continue;
+    }
+    SplineAt am = At(mo, ts[k]);
+    it.s[kSMotion + ee] = am.sample;
+    const std::vector<ColBasis> cols = Columns(mo, am.poly, am.t_local);
+    if (cols.size() > 12) throw std::runtime_error("unsupported: more than 12 ee-motion columns at one sample");
+    std::vector<double> run;
+    for (const ColBasis& c : cols) { run.push_back(c.v[0]); run.push_back(c.v[1]); run.push_back(static_cast<double>(c.dim)); }
+    it.b0 = AddBRun(run);
+    it.sub = static_cast<short>(cols.size());
+    it.gslot = AllocG(static_cast<int>(cols.size()) | 1);
+    hp_.items.push_back(it);
+    for (size_t j = 0; j < cols.size(); ++j) {
+      Term tm; tm.g = it.gslot + static_cast<int>(j); tm.b = one;
+      Add(static_cast<int>(k), mo.col0 + cols[j].idx, tm);
+    }
+  }
+  EndSet();
+}
+
 void Builder::Run() {
   hp_.n_rows = 0;
   for (int i = 0; i < s_.n_constraints; ++i) {
@@ -917,7 +970,8 @@ void Builder::Run() {
         for (int e = 0; e < s_.n_ee; ++e) EmitTotalDuration(e);
         break;
       case TOWR_B200_C_TERRAIN_HARD:
-        throw std::runtime_error("unsupported: constraint " + std::to_string(s_.constraints[i]) + " not built yet");
+        for (int e = 0; e < s_.n_ee; ++e) EmitTerrainHard(e);
+        break;
       default: throw std::runtime_error("constraint not defined!");   // nlp_formulation.cc:396
     }
   }
