@@ -723,17 +723,17 @@ __device__ __forceinline__ void ItemTerrainHard(const ItemCtx<L>& cx, const Item
     const double a = k_coeff * mag;
     cx.g[it.row * L::RS] = delta_z - (a < k_coeff ? a : k_coeff);       // std::min(k |v_tan|, k)
   }
-  const double slope[3] = {ts.hx, ts.hy, 0.0};
-  double kv[3] = {0.0, 0.0, 0.0};
+  double kv0 = 0.0, kv1 = 0.0, kv2 = 0.0;
   bool vel_term = false;
   if (mag > 1e-6 && k_coeff * mag < 0.05 - 1e-6) {
     vel_term = true;
-#pragma unroll
-    for (int d = 0; d < 3; ++d) kv[d] = k_coeff * ((vt1 * t1[d] + vt2 * t2[d]) / mag);
+    kv0 = k_coeff * ((vt1 * t1[0] + vt2 * t2[0]) / mag);
+    kv1 = k_coeff * ((vt1 * t1[1] + vt2 * t2[1]) / mag);
+    kv2 = k_coeff * ((vt1 * t1[2] + vt2 * t2[2]) / mag);
   }
-  auto finish = [&](int d, double jp, double jv) {
-    double v = d == 2 ? jp : -(slope[d] * jp);
-    if (vel_term) v = v - kv[d] * jv;
+  auto finish = [&](int d, double jp, double jv) {       // selects, not indexed arrays: no local memory
+    double v = d == 2 ? jp : -((d == 0 ? ts.hx : ts.hy) * jp);
+    if (vel_term) v = v - (d == 0 ? kv0 : d == 1 ? kv1 : kv2) * jv;
     return v;
   };
   double* G = cx.G + it.gslot * L::GS;

@@ -2,6 +2,8 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <cstddef>
+
 #include "items.cuh"
 #include "kernels.h"
 
@@ -63,6 +65,22 @@ template <int NT, int A, int U>
 __device__ __forceinline__ void LoadDescriptorRing(const uint32_t* __restrict__ ent, int left, uint32_t (&d)[A][U]) {
 #pragma unroll
   for (int a = 0; a < A; ++a) LoadDescriptors<NT, U>(ent + a * U * NT, left - a * U * NT, d[a]);
+}
+
+// Per-problem constants of the P problems of a group into shared memory, 8 bytes per thread.  The height table behind
+// the fixed fields (program.h: ProblemConst::table, 264 of the record's 352 bytes) is only read for problems on a table
+// terrain, so only those copy it.
+template <int P, int NT>
+__device__ __forceinline__ void FetchProblemConsts(ProblemConst* dst, const ProblemConst* __restrict__ pcs, int base_n, int n_problems,
+                                                   int tid) {
+  constexpr int kWords = static_cast<int>(sizeof(ProblemConst) / 8), kFixed = static_cast<int>(offsetof(ProblemConst, table) / 8);
+  static_assert(sizeof(ProblemConst) % 8 == 0 && offsetof(ProblemConst, table) % 8 == 0, "ProblemConst is copied in 8-byte words");
+  for (int i = tid; i < P * kWords; i += NT) {
+    const int p = i / kWords, w = i - p * kWords;
+    const ProblemConst* src = pcs + min(base_n + p, n_problems - 1);
+    if (w < kFixed || src->terrain_id == kTerrainTableId)
+      reinterpret_cast<double*>(dst + p)[w] = reinterpret_cast<const double*>(src)[w];
+  }
 }
 
 // 8-byte asynchronous global -> shared copy; src_bytes = 0 writes zeros (cp.async zero-fill)
