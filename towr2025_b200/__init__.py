@@ -157,7 +157,8 @@ def lib():
     L.towr_b200_trajectory_samples.argtypes = [vp, C.c_double]
     L.towr_b200_batch_sample_trajectory.argtypes = [vp, C.c_int, C.c_double, dp, dp]
     L.towr_b200_batch_sample_trajectory_device.argtypes = [vp, C.c_int, C.c_double, vp, vp, vp]
-    L.towr_b200_batch_sample_points.argtypes = [vp, C.c_int, dp, C.c_int, dp, dp]
+    if hasattr(L, "towr_b200_batch_sample_points"):      # absent only in older builds loaded through TOWR_B200_LIB (A/B runs)
+        L.towr_b200_batch_sample_points.argtypes = [vp, C.c_int, dp, C.c_int, dp, dp]
     L.towr_b200_trajectory_write_csv.argtypes = [vp, dp, C.c_int, C.c_char_p]
     L.towr_b200_batch_kernel_info.argtypes = [vp, C.c_char_p, C.c_int]
     L.towr_b200_batch_launch_count.argtypes = [vp]

@@ -235,7 +235,7 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
       CpAsync8(nodes + i, xn + (src != 0xFFFFu ? src : 0u), src != 0xFFFFu ? 8 : 0);
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
-    FetchProblemConsts<P, NT>(pc_s, pcs, base_n, n_problems, tid);
+    FetchProblemConsts<P, NT, CURV>(pc_s, pcs, base_n, n_problems, tid);
   };
   if (first < n_problems) fetch_group(first);
   // skew > 0: later streams (S > 1) or odd CTAs (S = 1) start `skew` clocks late, so that not every SM of the chip is in

@@ -107,7 +107,7 @@ EvalKernelSplit(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __
       CpAsync8(nodes + i, xn + (src != 0xFFFFu ? src : 0u), src != 0xFFFFu ? 8 : 0);
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
-    FetchProblemConsts<P, NTP>(pc_s, pcs, base_n, n_problems, tid);
+    FetchProblemConsts<P, NTP, CURV>(pc_s, pcs, base_n, n_problems, tid);
   };
   if (first < n_problems) fetch_group(first);
   int seq = 0;

@@ -842,7 +842,9 @@ __device__ __forceinline__ void RunItem(const ItemCtx<L>& cx, const ItemC& it) {
     case kItemRomPre: ItemRomPre<L>(cx, it); break;
     case kItemRomFoot: ItemRomFoot<L>(cx, it); break;
     case kItemForce: ItemForce<L>(cx, it); break;
-    case kItemTerrainHard: ItemTerrainHard<L>(cx, it); break;
+    case kItemTerrainHard:                               // classes with this set run the CURV instantiations (kClassTerrainHard)
+      if constexpr (L::CURV) ItemTerrainHard<L>(cx, it);
+      break;
     case kItemTorque: ItemTorque<L>(cx, it); break;
     case kItemForceNode: ItemForceNode<L>(cx, it); break;
     case kItemBaseRom: ItemBaseRom<L>(cx, it); break;

@@ -70,10 +70,12 @@ __device__ __forceinline__ void LoadDescriptorRing(const uint32_t* __restrict__ 
 // Per-problem constants of the P problems of a group into shared memory, 8 bytes per thread.  The height table behind
 // the fixed fields (program.h: ProblemConst::table, 264 of the record's 352 bytes) is only read for problems on a table
 // terrain, so only those copy it.
-template <int P, int NT>
+// TABLES = false (kernels of classes on analytic terrains): the fixed fields only, no look at the terrain id.
+template <int P, int NT, bool TABLES>
 __device__ __forceinline__ void FetchProblemConsts(ProblemConst* dst, const ProblemConst* __restrict__ pcs, int base_n, int n_problems,
                                                    int tid) {
-  constexpr int kWords = static_cast<int>(sizeof(ProblemConst) / 8), kFixed = static_cast<int>(offsetof(ProblemConst, table) / 8);
+  constexpr int kFixed = static_cast<int>(offsetof(ProblemConst, table) / 8);
+  constexpr int kWords = TABLES ? static_cast<int>(sizeof(ProblemConst) / 8) : kFixed;
   static_assert(sizeof(ProblemConst) % 8 == 0 && offsetof(ProblemConst, table) % 8 == 0, "ProblemConst is copied in 8-byte words");
   for (int i = tid; i < P * kWords; i += NT) {
     const int p = i / kWords, w = i - p * kWords;
