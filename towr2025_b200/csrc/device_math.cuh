@@ -15,6 +15,13 @@ struct Pt3 { double p[3], v[3], a[3]; };
 
 enum { kNeedPos = 1, kNeedVel = 2, kNeedAcc = 4 };
 
+// 1: the caller zeroes a segment's whole G buffer cooperatively before stage A (the evaluation kernels, classes with
+// optimised durations), so the items skip their serial zero fill of the all-column weight vectors - 60 to 100 shared-memory
+// stores per vector and thread.  0 (host emulation): every item zeroes what it owns, G starts as NaN to catch stray reads.
+#ifndef TB_PREZERO_G
+#define TB_PREZERO_G 0
+#endif
+
 // class tables in shared memory (BlobLayout, program.h)
 struct Tables {
   const double* B;
@@ -147,7 +154,8 @@ __device__ __forceinline__ RtPoint EvalSplineRt(const Tables& tb_, const double*
 template <int GS, int NS>
 __device__ __forceinline__ void WriteHermiteWeights(const Tables& tb_, const double* __restrict__ rtd, const RtSpline& sp,
                                                     const RtPoint& r, double* W) {
-  for (int c = 0; c < sp.n_cols; ++c) W[c * GS] = 0.0;
+  if (!TB_PREZERO_G)
+    for (int c = 0; c < sp.n_cols; ++c) W[c * GS] = 0.0;
   const double* q = rtd + r.poly * kRtd * NS;
   const double t = r.t, T = r.T, T2 = q[kRtT2 * NS], T3 = q[kRtT3 * NS];
   const double r1 = q[kRtR1 * NS], r2 = q[kRtR2 * NS], r3 = q[kRtR3 * NS];

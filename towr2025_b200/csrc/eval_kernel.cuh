@@ -346,6 +346,10 @@ EvalKernel(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __restr
 
     for (int s = 0; s < Pg.n_segments; ++s) {
       const SegmentRec sg = cx.T.segments[s];
+      if constexpr (RT && TB_PREZERO_G) {                // the all-column weight vectors start from 0 (device_math.cuh)
+        for (int i = tid; i < sg.g_size * P; i += NT) G[i] = 0.0;
+        StreamSync<S, NT>(sidx);
+      }
       // ---- stage A, level 0 then level 1: thread -> (item, problem lane)
       if (tid < P) { G[kGOne * P + tid] = 1.0; G[kGMass * P + tid] = pc_s[tid].mass; G[kGMinusOne * P + tid] = -1.0; }
       // a level with more (item, lane) pairs than threads runs in rounds of NT / P items.  The kinds are ordered longest

@@ -197,6 +197,10 @@ EvalKernelSplit(const __grid_constant__ DeviceProgram Pg, const ProblemConst* __
       double* G = G0 + static_cast<size_t>(b) * Pg.g_capacity * P;
       if (JAC && seq >= 2) BarSync(kBarEmpty + b, NTALL);   // the consumers have drained this buffer's previous segment
       cx.G = G + pl;
+      if constexpr (RT && TB_PREZERO_G) {
+        for (int i = tid; i < sg.g_size * P; i += NTP) G[i] = 0.0;
+        BarSync(kBarProducers, NTP);
+      }
       if (tid < P) { G[kGOne * P + tid] = 1.0; G[kGMass * P + tid] = pc_s[tid].mass; G[kGMinusOne * P + tid] = -1.0; }
       auto run_level = [&](int first_item, int count) {
         constexpr int kPerRound = NTP / P;

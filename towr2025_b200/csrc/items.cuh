@@ -741,7 +741,8 @@ __device__ __forceinline__ void ItemTerrainHard(const ItemCtx<L>& cx, const Item
     const RtSpline sm = cx.T.rt_splines[it.ee];
     double* Wp = G + sm.n_cols * L::GS;
     double* Wv = Wp + sm.n_cols * L::GS;
-    for (int c = 0; c < sm.n_cols; ++c) { Wp[c * L::GS] = 0.0; Wv[c * L::GS] = 0.0; }
+    if (!TB_PREZERO_G)
+      for (int c = 0; c < sm.n_cols; ++c) { Wp[c * L::GS] = 0.0; Wv[c * L::GS] = 0.0; }
     const double* q = cx.rtd + rp.poly * kRtd * L::NS;
     const double t = rp.t, T = rp.T, T2 = q[kRtT2 * L::NS], T3 = q[kRtT3 * L::NS];
     const double r1 = q[kRtR1 * L::NS], r2 = q[kRtR2 * L::NS], r3 = q[kRtR3 * L::NS];
@@ -774,7 +775,8 @@ __device__ __forceinline__ void ItemTerrainHard(const ItemCtx<L>& cx, const Item
             ++touched;
           }
         }
-    for (int c = 0; c < sm.n_cols; ++c) G[c * L::GS] = 0.0;
+    if (!TB_PREZERO_G)
+      for (int c = 0; c < sm.n_cols; ++c) G[c * L::GS] = 0.0;
     for (unsigned i = 0; i < touched; ++i) {
       const int c = col_of[i];
       G[c * L::GS] = finish(dim_of[i], Wp[c * L::GS], Wv[c * L::GS]);

@@ -10,6 +10,7 @@
 #if defined(TB_TIMING) && TB_CURV == 0 && (TB_LANES * 1000 + TB_RT * 100 + TB_STREAMS * 10 + TB_RING) == TB_TIMING_CODE
 #define TB_TIMING_HERE
 #endif
+#define TB_PREZERO_G 1   // the kernels zero each segment's G buffer cooperatively (device_math.cuh)
 #include "eval_kernel_split.cuh"
 
 namespace tb {
