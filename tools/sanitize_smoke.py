@@ -31,6 +31,34 @@ def main():
             rows = b.sample_trajectory(x, 0.05)
             assert np.isfinite(f).all() and np.isfinite(gr).all() and np.isfinite(rows).all()
             print("ok", robot, dur, st.nnz, flush=True)
+    if fixed_only or os.environ.get("TOWR_B200_KERNEL", "lockstep") != "lockstep":
+        return
+    # the extended instantiations and the multi-part path: Gap, a table terrain, TerrainHard, a fine-dt class, the
+    # dynamic-only transfer, arbitrary-time sampling, the allocation-free cost entry point's batch twin
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from util import set_terrain_table
+    extra = []
+    s = T.make_spec(T.Hyq, T.C4, 2.4, terrain=T.GapID, optimize_durations=True)
+    extra.append(("gap", s))
+    s = T.make_spec(T.Biped, T.C0, 2.4, extra_constraints=(T.Torque, T.TerrainHard))
+    set_terrain_table(s, T.TABLE_RAMPS, [0.4, 0.9, 1.3], [0.0, 0.2, 0.1])
+    extra.append(("table+terrainhard", s))
+    s = T.make_spec(T.Monoped, T.C0, 2.4)
+    s.dt_constraint_dynamic, s.dt_constraint_range_of_motion, s.dt_constraint_force = 0.01, 0.008, 0.002
+    extra.append(("parts", s))
+    for name, s in extra:
+        st = T.Structure(s)
+        n = 5
+        b = T.Batch(st, n, 0)
+        b.set_all(s)
+        x = np.tile(st.x0(s), (n, 1)) + np.random.default_rng(2).uniform(-0.01, 0.01, (n, st.n_vars))
+        g, v = b.eval(x)
+        base = np.stack([b.constant_values(i) for i in range(n)])
+        g2, v2 = b.eval(x, T.EVAL_G | T.EVAL_JAC_DYNAMIC, jac_out=base)
+        assert np.array_equal(v, v2) and np.array_equal(g, g2) and (b.status() == 0).all()
+        rows = b.sample_points(x, np.array([0.0, 0.37, 1.234]))
+        assert np.isfinite(rows).all()
+        print("ok", name, st.nnz, b.kernel_info, flush=True)
 
 
 if __name__ == "__main__":
