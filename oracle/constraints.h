@@ -186,4 +186,21 @@ class ForceConstraint : public ConstraintSet {
   std::vector<int> pure_stance_force_node_ids_;
 };
 
+// constraints/torque_constraint.cc:34-159 (node-based; used when dt_constraint_torque_ <= 0, nlp_formulation.cc:543-567)
+class TorqueConstraint : public ConstraintSet {
+ public:
+  TorqueConstraint(const std::shared_ptr<HeightMap>& terrain, double tx_min, double tx_max, double ty_min, double ty_max,
+                   double k_friction, int ee);
+  void InitVariableDependedQuantities(const std::shared_ptr<Variables>& x) override;
+  Vec GetValues() const override;
+  VecBound GetBounds() const override;
+  void FillJacobianBlock(const std::string& var_set, SpMat& jac) const override;
+ private:
+  std::shared_ptr<NodesVariablesPhaseBased> ee_torque_, ee_motion_, ee_force_;
+  std::shared_ptr<HeightMap> terrain_;
+  double tx_min_, tx_max_, ty_min_, ty_max_, k_friction_, mu_;
+  int n_constraints_per_node_, ee_;
+  std::vector<int> pure_stance_torque_node_ids_;
+};
+
 }  // namespace orc

@@ -303,4 +303,100 @@ void ForceConstraint::FillJacobianBlock(const std::string& var_set, SpMat& jac) 
   }
 }
 
+// ------------------------------------------------------------------ TorqueConstraint (node-based)
+// torque_constraint.cc:34-51
+TorqueConstraint::TorqueConstraint(const std::shared_ptr<HeightMap>& terrain, double tx_min, double tx_max, double ty_min,
+                                   double ty_max, double k_friction, int ee)
+    : ConstraintSet(-1, "torque-ee-torque_" + std::to_string(ee)) {
+  terrain_ = terrain;
+  tx_min_ = tx_min; tx_max_ = tx_max; ty_min_ = ty_min; ty_max_ = ty_max;
+  k_friction_ = k_friction;
+  mu_ = terrain->GetFrictionCoeff();
+  ee_ = ee;
+  n_constraints_per_node_ = 3;
+}
+// :53-62
+void TorqueConstraint::InitVariableDependedQuantities(const std::shared_ptr<Variables>& x) {
+  ee_torque_ = x->GetComponent<NodesVariablesPhaseBased>("ee-torque_" + std::to_string(ee_));
+  ee_motion_ = x->GetComponent<NodesVariablesPhaseBased>("ee-motion_" + std::to_string(ee_));
+  ee_force_ = x->GetComponent<NodesVariablesPhaseBased>("ee-force_" + std::to_string(ee_));
+  pure_stance_torque_node_ids_ = ee_torque_->GetIndicesOfNonConstantNodes();
+  SetRows(static_cast<int>(pure_stance_torque_node_ids_.size()) * n_constraints_per_node_);
+}
+// :64-92
+Vec TorqueConstraint::GetValues() const {
+  Vec g(GetRows());
+  int row = 0;
+  const auto& torque_nodes = ee_torque_->GetNodes();
+  for (int t_node_id : pure_stance_torque_node_ids_) {
+    int phase = ee_torque_->GetPhase(t_node_id);
+    V3 p = ee_motion_->GetValueAtStartOfPhase(phase);
+    V3 tau = torque_nodes.at(t_node_id).p;
+    V3 n = terrain_->GetNormalizedBasis(HeightMap::Normal, p.x(), p.y());
+    V3 t1 = terrain_->GetNormalizedBasis(HeightMap::Tangent1, p.x(), p.y());
+    V3 t2 = terrain_->GetNormalizedBasis(HeightMap::Tangent2, p.x(), p.y());
+    g[row++] = dot(tau, t1);
+    g[row++] = dot(tau, t2);
+    g[row++] = dot(tau, n);
+  }
+  return g;
+}
+// :94-112 - the friction-moment bound uses the force at the start of the phase AS IT IS when the bounds are asked for
+VecBound TorqueConstraint::GetBounds() const {
+  VecBound bounds;
+  for (int t_node_id : pure_stance_torque_node_ids_) {
+    int phase = ee_torque_->GetPhase(t_node_id);
+    V3 f = ee_force_->GetValueAtStartOfPhase(phase);
+    V3 p = ee_motion_->GetValueAtStartOfPhase(phase);
+    V3 n = terrain_->GetNormalizedBasis(HeightMap::Normal, p.x(), p.y());
+    double f_n = dot(f, n);
+    bounds.push_back(Bounds(tx_min_, tx_max_));
+    bounds.push_back(Bounds(ty_min_, ty_max_));
+    double tz_limit = k_friction_ * mu_ * f_n;
+    bounds.push_back(Bounds(-tz_limit, tz_limit));
+  }
+  return bounds;
+}
+// :114-157 - the ee-motion block uses the torque at the START of the phase (:141), not the row's node; no ee-force block
+void TorqueConstraint::FillJacobianBlock(const std::string& var_set, SpMat& jac) const {
+  if (var_set == ee_torque_->GetName()) {
+    int row = 0;
+    for (int t_node_id : pure_stance_torque_node_ids_) {
+      int phase = ee_torque_->GetPhase(t_node_id);
+      V3 p = ee_motion_->GetValueAtStartOfPhase(phase);
+      V3 n = terrain_->GetNormalizedBasis(HeightMap::Normal, p.x(), p.y());
+      V3 t1 = terrain_->GetNormalizedBasis(HeightMap::Tangent1, p.x(), p.y());
+      V3 t2 = terrain_->GetNormalizedBasis(HeightMap::Tangent2, p.x(), p.y());
+      for (int dim : {X, Y, Z}) {
+        int idx = ee_torque_->GetOptIndex(NVI{t_node_id, kPos, dim});
+        int rr = row;
+        jac.coeffRef(rr++, idx) = t1(dim);
+        jac.coeffRef(rr++, idx) = t2(dim);
+        jac.coeffRef(rr++, idx) = n(dim);
+      }
+      row += n_constraints_per_node_;
+    }
+  }
+  if (var_set == ee_motion_->GetName()) {
+    int row = 0;
+    for (int t_node_id : pure_stance_torque_node_ids_) {
+      int phase = ee_torque_->GetPhase(t_node_id);
+      int ee_node_id = ee_motion_->GetNodeIDAtStartOfPhase(phase);
+      V3 p = ee_motion_->GetValueAtStartOfPhase(phase);
+      V3 tau = ee_torque_->GetValueAtStartOfPhase(phase);
+      for (int dim : {0, 1}) {
+        V3 dt1 = terrain_->GetDerivativeOfNormalizedBasisWrt(HeightMap::Tangent1, dim, p.x(), p.y());
+        V3 dt2 = terrain_->GetDerivativeOfNormalizedBasisWrt(HeightMap::Tangent2, dim, p.x(), p.y());
+        V3 dn = terrain_->GetDerivativeOfNormalizedBasisWrt(HeightMap::Normal, dim, p.x(), p.y());
+        int idx = ee_motion_->GetOptIndex(NVI{ee_node_id, kPos, dim});
+        int rr = row;
+        jac.coeffRef(rr++, idx) = dot(tau, dt1);
+        jac.coeffRef(rr++, idx) = dot(tau, dt2);
+        jac.coeffRef(rr++, idx) = dot(tau, dn);
+      }
+      row += n_constraints_per_node_;
+    }
+  }
+}
+
 }  // namespace orc

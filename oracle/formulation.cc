@@ -258,7 +258,9 @@ std::vector<std::shared_ptr<ConstraintSet>> NlpFormulation::GetConstraint(Parame
                                                                     params_.torque_ty_min_, params_.torque_ty_max_,
                                                                     params_.torque_k_friction_, ee, spline_holder_for_costs_));
         else
-          throw std::runtime_error("oracle: node-based TorqueConstraint (dt_constraint_torque_ <= 0) not restated");
+          c.push_back(std::make_shared<TorqueConstraint>(terrain_, params_.torque_tx_min_, params_.torque_tx_max_,
+                                                         params_.torque_ty_min_, params_.torque_ty_max_,
+                                                         params_.torque_k_friction_, ee));
       }
       break;
     case Parameters::Swing:

@@ -1529,6 +1529,70 @@ class ForceConstraint(ConstraintSet):
         return None
 
 
+class TorqueConstraint(ConstraintSet):
+    """constraints/torque_constraint.cc:34-159 (node-based; used when dt_constraint_torque_ <= 0).  Three rows per stance
+    torque node.  The friction-moment bound is evaluated with the force at the start of the node's phase as it is when
+    the bounds are asked for (:94-112); the ee-motion block uses the torque at the START of the phase (:141); the
+    ee-force block is empty (:155-157)."""
+
+    def __init__(self, terrain, tx_min, tx_max, ty_min, ty_max, k_friction, ee):
+        self.name = "torque-ee-torque_%d" % ee
+        self.terrain, self.mu, self.ee = terrain, terrain.mu, ee
+        self.lim, self.kf = (tx_min, tx_max, ty_min, ty_max), k_friction
+
+    def link(self, variables):
+        self.ee_torque = variables["ee-torque_%d" % self.ee]
+        self.ee_motion = variables["ee-motion_%d" % self.ee]
+        self.ee_force = variables["ee-force_%d" % self.ee]
+        self.node_ids = self.ee_torque.non_constant_nodes()
+        self.n_rows = len(self.node_ids) * 3
+
+    def _frame(self, t_node):
+        phase = self.ee_torque.phase_of(t_node)
+        p = self.ee_motion.value_at_start_of_phase(phase)
+        return phase, p, [self.terrain.normalized_basis(b, p[X], p[Y]) for b in (1, 2, 0)]    # t1, t2, n
+
+    def values(self):
+        g = []
+        for t_node in self.node_ids:
+            phase, p, frame = self._frame(t_node)
+            tau = self.ee_torque.nodes[t_node, kPos]
+            g += [tau @ b for b in frame]
+        return np.array(g)
+
+    def bounds(self):
+        out = []
+        for t_node in self.node_ids:
+            phase, p, frame = self._frame(t_node)
+            f = self.ee_force.value_at_start_of_phase(phase)
+            tz_limit = self.kf * self.mu * (f @ frame[2])
+            out += [(self.lim[0], self.lim[1]), (self.lim[2], self.lim[3]), (-tz_limit, tz_limit)]
+        return out
+
+    def block(self, var_set):
+        if var_set.name == self.ee_torque.name:
+            entries = {}
+            for i, t_node in enumerate(self.node_ids):
+                phase, p, frame = self._frame(t_node)
+                for dim in (X, Y, Z):
+                    idx = self.ee_torque.opt_index(t_node, kPos, dim)
+                    for r in range(3):
+                        entries[(3 * i + r, idx)] = frame[r][dim]
+            return Sp.from_entries((self.n_rows, var_set.rows()), entries)
+        if var_set.name == self.ee_motion.name:
+            entries = {}
+            for i, t_node in enumerate(self.node_ids):
+                phase, p, frame = self._frame(t_node)
+                ee_node = self.ee_motion.node_at_start_of_phase(phase)
+                tau = self.ee_torque.value_at_start_of_phase(phase)
+                for dim in (X, Y):
+                    idx = self.ee_motion.opt_index(ee_node, kPos, dim)
+                    for r, b in enumerate((1, 2, 0)):
+                        entries[(3 * i + r, idx)] = tau @ self.terrain.d_normalized_basis(b, dim, p[X], p[Y])
+            return Sp.from_entries((self.n_rows, var_set.rows()), entries)
+        return None
+
+
 class SwingConstraint(ConstraintSet):
     """constraints/swing_constraint.cc:35-106; t_swing_avg_ = 0.3 (swing_constraint.h:68)."""
     t_swing_avg = 0.3
@@ -1854,7 +1918,10 @@ class Formulation:
             elif cid == C_TORQUE:
                 for ee in range(n_ee):
                     if float(s.dt_constraint_torque) <= 0.0:
-                        raise NotImplementedError("node-based TorqueConstraint")
+                        self.con_sets.append(TorqueConstraint(self.terrain, float(s.torque_tx_min), float(s.torque_tx_max),
+                                                              float(s.torque_ty_min), float(s.torque_ty_max),
+                                                              float(s.torque_k_friction), ee))
+                        continue
                     self.con_sets.append(TorqueConstraintDiscretized(self.terrain, T, float(s.dt_constraint_torque),
                                                                      float(s.torque_tx_min), float(s.torque_tx_max),
                                                                      float(s.torque_ty_min), float(s.torque_ty_max),

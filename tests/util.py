@@ -70,6 +70,11 @@ TERRAIN_HARD_CASES = [
     ("anymal_trot_terrainhard_durations_chimney", 3, 1, 2.0, (1.2, 0.0, 0.0), 5, (TERRAIN_HARD,), True),
 ]
 CASES += TERRAIN_HARD_CASES
+# node-based TorqueConstraint (Parameters::dt_constraint_torque_ <= 0, torque_constraint.cc)
+CASES += [
+    ("biped_walk_torque_nodes_block", 1, 0, 2.4, (1.1, 0.0, 0.1), 1, (TORQUE,), False, {"dt_constraint_torque": -1.0}),
+    ("anymal_trot_torque_nodes_slope_durations", 3, 1, 2.0, (1.0, 0.0, 0.0), 4, (TORQUE,), True, {"dt_constraint_torque": -1.0}),
+]
 
 # Terrain with curvature (Gap, id 3): the class declares the force / torque constraint's ee-motion block for every sample
 # (superset); the reference / oracle store such an entry only where its scale is non-zero (value-dependent pattern).
@@ -79,6 +84,7 @@ GAP_CASES = [
     ("hyq_gallop_gap_durations", 2, 4, 2.4, (1.5, 0.1, -0.2), GAP, (), True),                 # BASELINE config 4
     ("biped_walk_gap_torque", 1, 0, 2.4, (1.4, 0.0, 0.1), GAP, (TORQUE,)),
     ("monoped_hop_gap_torque_durations", 0, 0, 2.4, (1.3, 0.0, 0.0), GAP, (TORQUE,), True),
+    ("biped_walk_gap_torque_nodes", 1, 0, 2.4, (1.4, 0.0, 0.1), GAP, (TORQUE,), False, {"dt_constraint_torque": -1.0}),
 ]
 
 

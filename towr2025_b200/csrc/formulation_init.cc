@@ -204,6 +204,12 @@ void ProblemVarBounds(const HostProgram& hp, const towr_b200_spec& s, double* L,
 }
 
 void ProblemConBounds(const HostProgram& hp, const towr_b200_spec& s, double* L, double* U) {
+  std::vector<double> x0;                                // the initial guess, built when a bound depends on it
+  auto node_pos = [&](const VarSet& v, int node, int dim) {   // a node's position in the initial guess (0: not optimised)
+    if (x0.empty()) { x0.resize(hp.n_vars); ProblemX0(hp, s, x0.data()); }
+    const int idx = v.OptIndex(node, 0, dim);
+    return idx < 0 ? 0.0 : x0[v.col0 + idx];
+  };
   for (int r = 0; r < hp.n_rows; ++r) {
     const RowBound& b = hp.row_bounds[r];
     double lo = 0.0, up = 0.0;
@@ -225,6 +231,20 @@ void ProblemConBounds(const HostProgram& hp, const towr_b200_spec& s, double* L,
       case kBoundNone: lo = -kNoBound; up = +kNoBound; break;
       case kBoundTorqueX: lo = s.torque_tx_min; up = s.torque_tx_max; break;     // torque_constraint_discretized.cc:131-139
       case kBoundTorqueY: lo = s.torque_ty_min; up = s.torque_ty_max; break;
+      case kBoundTorqueNodeZ: {                          // torque_constraint.cc:94-112, evaluated on the initial guess
+        const VarSet& fo = *hp.Find(kEEForce, b.ee);
+        const VarSet& mo = *hp.Find(kEEMotion, b.ee);
+        const int fnode = fo.PolyAtStartOfPhase(b.dim), pnode = mo.PolyAtStartOfPhase(b.dim);
+        const double f[3] = {node_pos(fo, fnode, 0), node_pos(fo, fnode, 1), node_pos(fo, fnode, 2)};
+        const TerrainSample ts = SpecTerrain(s, node_pos(mo, pnode, 0), node_pos(mo, pnode, 1));
+        double n[3], t1[3], t2[3];
+        TerrainBasis(ts, n, t1, t2);
+        const double f_n = (f[0] * n[0] + f[1] * n[1]) + f[2] * n[2];
+        const double tz_limit = s.torque_k_friction * kFrictionCoeff * f_n;
+        lo = -tz_limit;
+        up = tz_limit;
+        break;
+      }
     }
     L[r] = lo;
     U[r] = up;

@@ -788,6 +788,40 @@ __device__ __forceinline__ void ItemTerrainHard(const ItemCtx<L>& cx, const Item
   }
 }
 
+// Node-based TorqueConstraint (torque_constraint.cc:64-157): s0 = the stance torque node, aux = the ee-motion node at the
+// start of its phase (the foothold), b0 = the torque node at the start of the phase.  G: t1[3], t2[3], n[3], then
+// (tau_s . d b / d x, tau_s . d b / d y) for b = t1, t2, n with tau_s the start-of-phase torque (:141).
+template <class L>
+__device__ __forceinline__ void ItemTorqueNode(const ItemCtx<L>& cx, const ItemC& it) {
+  const double* tn = cx.nodes + it.s0 * 6 * L::NS;
+  const double* pn = cx.nodes + it.aux * 6 * L::NS;
+  const double* sn = cx.nodes + it.b0 * 6 * L::NS;
+  const double tau[3] = {tn[0], tn[L::NS], tn[2 * L::NS]};
+  const double tau_s[3] = {sn[0], sn[L::NS], sn[2 * L::NS]};
+  const TerrainSample ts = TerrainAt(cx, pn[0], pn[L::NS]);
+  double n[3], t1[3], t2[3];
+  TerrainBasis(ts, n, t1, t2);
+  double* G = cx.G + it.gslot * L::GS;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) { TB_G(d) = t1[d]; TB_G(3 + d) = t2[d]; TB_G(6 + d) = n[d]; }
+#pragma unroll
+  for (int dim = 0; dim < 2; ++dim) {
+    double dn[3], dt1[3], dt2[3];
+    TerrainBasisDeriv(ts, 0, dim, dn);
+    TerrainBasisDeriv(ts, 1, dim, dt1);
+    TerrainBasisDeriv(ts, 2, dim, dt2);
+    TB_G(9 + 0 + dim) = (tau_s[0] * dt1[0] + tau_s[1] * dt1[1]) + tau_s[2] * dt1[2];
+    TB_G(9 + 2 + dim) = (tau_s[0] * dt2[0] + tau_s[1] * dt2[1]) + tau_s[2] * dt2[2];
+    TB_G(9 + 4 + dim) = (tau_s[0] * dn[0] + tau_s[1] * dn[1]) + tau_s[2] * dn[2];
+  }
+  if (cx.g) {
+    double* gr = cx.g + it.row * L::RS;
+    gr[0] = (tau[0] * t1[0] + tau[1] * t1[1]) + tau[2] * t1[2];
+    gr[L::RS] = (tau[0] * t2[0] + tau[1] * t2[1]) + tau[2] * t2[2];
+    gr[2 * L::RS] = (tau[0] * n[0] + tau[1] * n[1]) + tau[2] * n[2];
+  }
+}
+
 // SwingConstraint (swing_constraint.cc:54-78)
 template <class L>
 __device__ __forceinline__ void ItemSwingNode(const ItemCtx<L>& cx, const ItemC& it) {
@@ -846,6 +880,9 @@ __device__ __forceinline__ void RunItem(const ItemCtx<L>& cx, const ItemC& it) {
     case kItemForce: ItemForce<L>(cx, it); break;
     case kItemTerrainHard:                               // classes with this set run the CURV instantiations (kClassTerrainHard)
       if constexpr (L::CURV) ItemTerrainHard<L>(cx, it);
+      break;
+    case kItemTorqueNode:
+      if constexpr (L::CURV) ItemTorqueNode<L>(cx, it);
       break;
     case kItemTorque: ItemTorque<L>(cx, it); break;
     case kItemForceNode: ItemForceNode<L>(cx, it); break;

@@ -193,7 +193,8 @@ void BuildLayout(const towr_b200_spec& s, HostProgram& hp) {
   hp.optimize_durations = OptimizesDurations(s);
   hp.curvature_dims = TerrainClassBits(s.terrain_id);   // curvature dims | kClassTableTerrain | kClassTerrainHard
   for (int i = 0; i < s.n_constraints; ++i)
-    if (s.constraints[i] == TOWR_B200_C_TERRAIN_HARD) hp.curvature_dims |= kClassTerrainHard;
+    if (s.constraints[i] == TOWR_B200_C_TERRAIN_HARD || (s.constraints[i] == TOWR_B200_C_TORQUE && !(s.dt_constraint_torque > 0.0)))
+      hp.curvature_dims |= kClassTerrainHard;
   const int E = s.n_ee;
   const std::vector<double> base_T = BasePolyDurations(s);
   const int n_base_nodes = static_cast<int>(base_T.size()) + 1;

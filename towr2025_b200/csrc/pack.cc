@@ -101,7 +101,7 @@ void PackRange(HostProgram& hp, const std::vector<SegmentRec>& wide, int seg0, i
     c.ee = static_cast<uint8_t>(it.ee);
     c.n_ee = static_cast<uint8_t>(it.n_ee);
     const int run = ItemBRun(it.type, it.sub);
-    const int b0 = run ? local_run(it.b0, run) : 0;
+    const int b0 = run ? local_run(it.b0, run) : (it.type == kItemTorqueNode ? it.b0 : 0);   // TorqueNode: a node slot
     if (it.gslot > 0xFFFF || it.aux > 0xFFFF) throw std::runtime_error("item slot out of range");
     if (b0 > 0xFFFF) throw Unfit("B runs beyond 65535 entries");
     c.gslot = static_cast<uint16_t>(it.gslot);

@@ -56,6 +56,7 @@ enum ItemType : int {
   kItemTorque,          // torque_constraint_discretized.cc:105-235  4 rows per (sample, foot)
   kItemDynFoot,         // per (dynamic sample, foot): f_e, c - p_e slots and the foot's torque term f_e x (c - p_e) + tau_e
   kItemTerrainHard,     // terrain_constraint_hard.cc:50-132         1 row per (sample, foot), finished ee-motion columns
+  kItemTorqueNode,      // torque_constraint.cc:64-157               3 rows per stance torque node (node-based variant)
   // level 1: read the scratch slots of a level-0 item (ItemC::aux)
   kItemDynWrench,       // dynamic_constraint.cc:63-148: the 6 g rows of a dynamic sample (feet summed in order)
   kItemDynJlin,         // row (sub) of the finished base-lin angular block -sum_e Cross(f_e) J_pos of a dynamic sample
@@ -68,7 +69,7 @@ constexpr int kItemPad = 16;   // items of one kind are padded to a multiple of 
 inline int ItemCostRank(int type) {
   switch (type) {
     case kItemDynPre: case kItemDynCol: return 0;
-    case kItemForce: case kItemTorque: case kItemForceNode: case kItemRomFoot: case kItemTerrainHard: return 1;
+    case kItemForce: case kItemTorque: case kItemForceNode: case kItemRomFoot: case kItemTerrainHard: case kItemTorqueNode: return 1;
     case kItemDynFoot: case kItemRomPre: return 2;
     case kItemDynJlin: case kItemBaseRom: return 3;
     case kItemDynWrench: return 4;
@@ -255,7 +256,8 @@ struct ConSet { std::string name; int row0, n_rows; };
 
 // what ConstraintSet::GetBounds returns for one row (values depend on per-problem model data)
 enum RowBoundKind { kBoundZero = 0, kBoundTerrainSwing, kBoundRom, kBoundForceNormal, kBoundLE0, kBoundGE0,
-                    kBoundBaseHeight, kBoundTotalDuration, kBoundNone, kBoundTorqueX, kBoundTorqueY };
+                    kBoundBaseHeight, kBoundTotalDuration, kBoundNone, kBoundTorqueX, kBoundTorqueY,
+                    kBoundTorqueNodeZ };   // +- k mu f_n with the start-of-phase force of the initial guess; dim = phase
 struct RowBound { int kind, ee, dim; };
 
 // a run of consecutive segments with its own class tables (pack.cc): classes with few samples have one

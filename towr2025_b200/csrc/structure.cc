@@ -261,6 +261,7 @@ class Builder {
   void EmitTorqueDisc(int ee);
   void EmitBaseRom();
   void EmitTerrainHard(int ee);
+  void EmitTorqueNodes(int ee);
   void EmitRomSplit();
   void EmitTotalDuration(int ee);
   void EmitSwing(int ee);
@@ -935,6 +936,47 @@ void Builder::EmitTerrainHard(int ee) {
   EndSet();
 }
 
+// Node-based TorqueConstraint (torque_constraint.cc:34-159), three rows per stance torque node: tau . t1, tau . t2, tau . n
+// with the basis at the foothold of the node's phase.  ee-torque block: the basis components (:121-133); ee-motion block:
+// tau_s . d(t1, t2, n)/d(x, y) with tau_s the torque at the START of the phase (:141), stored whatever its value; no
+// ee-force block (:155-157).  Rows 0, 1 bounded by the torque limits, row 2 by +- k mu f_n (kBoundTorqueNodeZ).
+void Builder::EmitTorqueNodes(int ee) {
+  const VarSet& mo = Set(kEEMotion, ee);
+  const VarSet& to = Set(kEETorque, ee);
+  const std::vector<int> nodes = to.NonConstantNodes();
+  const int one = AddB(1.0);
+  BeginGroup();
+  BeginSet("torque-" + to.name, static_cast<int>(nodes.size()) * 3);
+  int row = 0;
+  for (int node : nodes) {
+    const int phase = to.PhaseOfNode(node);
+    const int ee_node = mo.PolyAtStartOfPhase(phase);
+    ItemRec it = NewItem(kItemTorqueNode);
+    it.ee = static_cast<short>(ee);
+    it.row[0] = set_row0_ + row;
+    it.s[0] = to.node_slot0 + node;
+    it.aux = mo.node_slot0 + ee_node;
+    it.b0 = to.node_slot0 + to.PolyAtStartOfPhase(phase);  // node slot, not a B run (pack.cc passes it through)
+    it.gslot = AllocG(15);
+    hp_.items.push_back(it);
+    Bound(row + 0, kBoundTorqueX, ee);
+    Bound(row + 1, kBoundTorqueY, ee);
+    Bound(row + 2, kBoundTorqueNodeZ, ee, phase);
+    for (int dim = 0; dim < 3; ++dim) {
+      const int idx = to.OptIndex(node, 0, dim);
+      if (idx < 0) throw std::runtime_error("torque constraint touches a node value that is not optimised");
+      for (int i = 0; i < 3; ++i) { Term tm; tm.g = it.gslot + 3 * i + dim; tm.b = one; tm.code = kCodeTorque + (i == 2 ? 6 : 3 * i) + dim; Add(row + i, to.col0 + idx, tm, true); }
+    }
+    for (int dim = 0; dim < 2; ++dim) {
+      const int idx = mo.OptIndex(ee_node, 0, dim);
+      if (idx < 0) throw std::runtime_error("torque constraint touches a foothold that is not optimised");
+      for (int i = 0; i < 3; ++i) { Term tm; tm.g = it.gslot + 9 + 2 * i + dim; tm.b = one; Add(row + i, mo.col0 + idx, tm, true); }
+    }
+    row += 3;
+  }
+  EndSet();
+}
+
 void Builder::Run() {
   hp_.n_rows = 0;
   for (int i = 0; i < s_.n_constraints; ++i) {
@@ -961,8 +1003,10 @@ void Builder::Run() {
         break;
       case TOWR_B200_C_BASE_HEIGHT: EmitBaseHeight(); break;
       case TOWR_B200_C_TORQUE:
-        if (!(s_.dt_constraint_torque > 0.0)) throw std::runtime_error("unsupported: node-based TorqueConstraint");
-        for (int e = 0; e < s_.n_ee; ++e) EmitTorqueDisc(e);
+        for (int e = 0; e < s_.n_ee; ++e) {
+          if (s_.dt_constraint_torque > 0.0) EmitTorqueDisc(e);
+          else EmitTorqueNodes(e);                          // nlp_formulation.cc:543-567
+        }
         break;
       case TOWR_B200_C_BASE_ROM: EmitBaseRom(); break;
       case TOWR_B200_C_TOTAL_TIME:

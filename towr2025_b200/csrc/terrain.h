@@ -129,8 +129,9 @@ TB_HD bool TerrainHasSlope(int id, const TerrainTable& t) { return id == kTerrai
 // bit 2 of a class's curvature_dims: the class admits table terrains (its kernels are the CURV instantiations, the only
 // ones that read the table); bits 0, 1 as TerrainCurvatureDims
 constexpr int kClassTableTerrain = 4;
-// bit 3: the class has a TerrainConstraintHard set; its item is compiled into the CURV instantiations only, so that the
-// kernels of the default constraint list do not carry its code (0.6 % of their run time, measured)
+// bit 3: the class has a TerrainConstraintHard or a node-based TorqueConstraint set; their items are compiled into the
+// CURV instantiations only, so that the kernels of the default constraint list do not carry their code (TerrainHard alone
+// was 0.6 % of their run time, measured)
 constexpr int kClassTerrainHard = 8;
 TB_HD int TerrainClassBits(int id) { return id == kTerrainTableId ? kClassTableTerrain : TerrainCurvatureDims(id); }
 
