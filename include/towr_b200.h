@@ -119,6 +119,9 @@ typedef struct towr_b200_spec {
    * (towr_b200_structure_accepts: the kernels that read the table are a separate instantiation). */
   int terrain_table_n, terrain_table_mode;
   double terrain_table_x[TOWR_B200_MAX_TERRAIN_KNOTS], terrain_table_h[TOWR_B200_MAX_TERRAIN_KNOTS];
+  /* time-discretised costs (parameters.h:245-247, parameters.cc:69-71): sampling period and torque weight of EnergyCost
+   * (costs/energy_cost.cc), sampling period of AngularMomentumCost.  Class properties, like the cost list itself. */
+  double dt_cost_energy, energy_cost_torque_weight, dt_cost_ang_mom;
 } towr_b200_spec;
 
 const char* towr_b200_last_error(void);
@@ -230,10 +233,14 @@ void* towr_b200_batch_stream(const towr_b200_batch* b);
 
 /* ---- the other two Ipopt callbacks: eval_f / eval_grad_f --------------------------------------------------------------
  * Replaces ifopt::Problem::EvaluateCostFunction / EvaluateCostFunctionGradient over the cost terms of
- * NlpFormulation::GetCosts (towr/src/nlp_formulation.cc:605-681) for the NodeCost families (towr/src/costs/node_cost.cc:
- * 36-76): ForcesCostID and EEMotionCostID, as test/hopper_example.cc:147-148 enables them.  spec.n_costs = 0 (the
- * reference's default, parameters.cc:90) gives f = 0 and a zero gradient.  what: bit 0 = f (n doubles), bit 1 = dense
- * gradient (n x n_vars doubles).  EnergyCostID / AngMomCostID make towr_b200_structure_create fail as unsupported. */
+ * NlpFormulation::GetCosts (towr/src/nlp_formulation.cc:605-681): the NodeCost families (towr/src/costs/node_cost.cc:
+ * 36-76) ForcesCostID and EEMotionCostID, as test/hopper_example.cc:147-148 enables them, and the time-discretised
+ * EnergyCostID (towr/src/costs/energy_cost.cc: weight dt sum_t sum_ee |f|^2 + torque_weight |tau|^2, with the gradient
+ * wrt force / torque nodes and, for optimised durations, the ee-schedule) and AngMomCostID
+ * (towr/src/costs/angular_momentum_cost.cc: weight dt sum_t |R I_b R^T omega|^2, gradient wrt base-ang nodes; I_b is the
+ * batch problem's inertia), sampled with spec.dt_cost_energy / dt_cost_ang_mom.  spec.n_costs = 0 (the reference's
+ * default, parameters.cc:90) gives f = 0 and a zero gradient.  what: bit 0 = f (n doubles), bit 1 = dense gradient
+ * (n x n_vars doubles).  Not built: EEBasePosCost (enable_swing_ee_base_pos_tracking, off by default). */
 int towr_b200_batch_eval_cost(towr_b200_batch* b, int n, int what, const double* x, double* f_out, double* grad_out);
 int towr_b200_batch_eval_cost_device(towr_b200_batch* b, int n, int what, const double* d_x, double* d_f, double* d_grad,
                                      void* stream);
@@ -242,15 +249,18 @@ int towr_b200_batch_eval_cost_device(towr_b200_batch* b, int n, int what, const 
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
  * it).  Same kernel and results as towr_b200_batch_eval_cost_device, but it needs no batch and performs no cudaMalloc /
  * cudaFree or any other device allocation: the kernel's work tables (column pointers and weights of the class's cost
- * terms) go into a fixed file-scope device array of the library (about 144 KB, held by every GPU that loads the library
+ * terms) go into a fixed file-scope device array of the library (about 208 KB, held by every GPU that loads the library
  * until the process exits) by two cudaMemcpyAsync on `stream`.  Limits: n_vars <= TOWR_B200_STATIC_COST_MAX_VARS and at
- * most TOWR_B200_STATIC_COST_MAX_WEIGHTS (variable, node value) weights, else TOWR_B200_ERR_ARG with a message naming
- * the limit.  d_x (n x n_vars), d_f (n) and d_grad (n x n_vars) are device memory on `device`, as for the _device entry
+ * most TOWR_B200_STATIC_COST_MAX_WEIGHTS (variable, node value) weights, and at most
+ * TOWR_B200_STATIC_COST_MAX_SAMPLED_BYTES of EnergyCost / AngularMomentumCost tables, else TOWR_B200_ERR_ARG with a
+ * message naming the limit.  Without a batch there are no per-problem constants: AngularMomentumCost uses the inertia
+ * of the spec the structure was created from.  d_x (n x n_vars), d_f (n) and d_grad (n x n_vars) are device memory on `device`, as for the _device entry
  * point.  ALL calls share the one array, which keeps the last call's tables (each call rewrites the part it uses;
  * nothing in it has to start at zero): calls that overlap on the GPU - different streams, or threads - race; order
  * them on one stream. */
 #define TOWR_B200_STATIC_COST_MAX_VARS 4096
 #define TOWR_B200_STATIC_COST_MAX_WEIGHTS 16384
+#define TOWR_B200_STATIC_COST_MAX_SAMPLED_BYTES 65536   /* class tables of EnergyCost / AngularMomentumCost */
 int towr_b200_eval_cost_static(const towr_b200_structure* st, int device, int n, int what, const double* d_x, double* d_f,
                                double* d_grad, void* stream);
 

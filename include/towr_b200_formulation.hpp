@@ -126,6 +126,9 @@ class Parameters {
     dt_constraint_base_motion_ = d.dt_constraint_base_motion;
     dt_constraint_force_ = d.dt_constraint_force;
     dt_constraint_torque_ = d.dt_constraint_torque;
+    dt_cost_energy_ = d.dt_cost_energy;                    // parameters.cc:69-71
+    energy_cost_torque_weight_ = d.energy_cost_torque_weight;
+    dt_cost_ang_mom_ = d.dt_cost_ang_mom;
     bound_phase_duration_ = std::make_pair(d.bound_phase_duration[0], d.bound_phase_duration[1]);
     for (int i = 0; i < d.n_constraints; ++i) constraints_.push_back(static_cast<ConstraintName>(d.constraints[i]));
     bounds_final_lin_pos_ = bounds_final_lin_vel_ = bounds_final_ang_pos_ = bounds_final_ang_vel_ = {X, Y, Z};
@@ -140,6 +143,7 @@ class Parameters {
   CostWeights costs_;
   double dt_constraint_dynamic_, dt_constraint_range_of_motion_, dt_constraint_base_motion_;
   double dt_constraint_force_, dt_constraint_torque_;
+  double dt_cost_energy_, energy_cost_torque_weight_, dt_cost_ang_mom_;   // parameters.h:245-247
   double duration_base_polynomial_;
   int ee_polynomials_per_swing_phase_, force_polynomials_per_stance_phase_, torque_polynomials_per_stance_phase_;
   double force_limit_in_normal_direction_;
@@ -242,6 +246,9 @@ inline towr_b200_spec ToSpec(const ref::NlpFormulation& f) {
   s.dt_constraint_base_motion = P.dt_constraint_base_motion_;
   s.dt_constraint_force = P.dt_constraint_force_;
   s.dt_constraint_torque = P.dt_constraint_torque_;
+  s.dt_cost_energy = P.dt_cost_energy_;
+  s.energy_cost_torque_weight = P.energy_cost_torque_weight_;
+  s.dt_cost_ang_mom = P.dt_cost_ang_mom_;
   s.duration_base_polynomial = P.duration_base_polynomial_;
   s.ee_polynomials_per_swing_phase = P.ee_polynomials_per_swing_phase_;
   s.force_polynomials_per_stance_phase = P.force_polynomials_per_stance_phase_;

@@ -203,4 +203,14 @@ class TorqueConstraint : public ConstraintSet {
   std::vector<int> pure_stance_torque_node_ids_;
 };
 
+
+// costs/energy_cost.cc, costs/angular_momentum_cost.cc (costs.cc)
+std::vector<double> CostSampleTimes(const SplineHolder& s, double dt);
+double EnergyCostValue(const SplineHolder& s, double weight, double torque_weight, double dt);
+void EnergyCostFillBlock(const SplineHolder& s, double weight, double torque_weight, double dt, const std::string& var_set,
+                         double* block);
+double AngMomCostValue(const SplineHolder& s, const SingleRigidBodyDynamics& model, double weight, double dt);
+void AngMomCostFillBlock(const SplineHolder& s, const SingleRigidBodyDynamics& model, double weight, double dt,
+                         const std::string& var_set, double* block);
+
 }  // namespace orc

@@ -27,6 +27,9 @@ Parameters::Parameters() {
   dt_constraint_base_motion_ = duration_base_polynomial_ / 4.;
   dt_constraint_force_ = 0.02;
   dt_constraint_torque_ = 0.02;
+  dt_cost_energy_ = 0.02;               // parameters.cc:69-71
+  energy_cost_torque_weight_ = 1.0;
+  dt_cost_ang_mom_ = 0.02;
   bound_phase_duration_ = std::make_pair(0.2, 1.0);
   constraints_ = {Terrain, Dynamic, BaseAcc, EndeffectorRom, Force, Swing, BaseHeight};
   bounds_final_lin_pos_ = {X, Y, Z};

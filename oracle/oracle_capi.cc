@@ -65,6 +65,9 @@ static NlpFormulation MakeFormulation(const orc_spec& s) {
   p.torque_ty_min_ = s.torque_ty_min; p.torque_ty_max_ = s.torque_ty_max;
   p.torque_k_friction_ = s.torque_k_friction;
   p.bound_phase_duration_ = {s.bound_phase_duration[0], s.bound_phase_duration[1]};
+  p.dt_cost_energy_ = s.dt_cost_energy;
+  p.energy_cost_torque_weight_ = s.energy_cost_torque_weight;
+  p.dt_cost_ang_mom_ = s.dt_cost_ang_mom;
   p.enable_stance_tracking = s.enable_stance_tracking != 0;   // orc_spec_defaults: off
   p.ee_stance_position_.clear();
   for (int e = 0; e < E; ++e) {
@@ -119,6 +122,9 @@ void orc_spec_defaults(orc_spec* s) {
   s->torque_k_friction = d.torque_k_friction_;
   s->bound_phase_duration[0] = d.bound_phase_duration_.first;
   s->bound_phase_duration[1] = d.bound_phase_duration_.second;
+  s->dt_cost_energy = d.dt_cost_energy_;
+  s->energy_cost_torque_weight = d.energy_cost_torque_weight_;
+  s->dt_cost_ang_mom = d.dt_cost_ang_mom_;
   for (int i = 0; i < 3; ++i) s->bounds_final_lin_pos[i] = s->bounds_final_lin_vel[i] = s->bounds_final_ang_pos[i] = s->bounds_final_ang_vel[i] = 1;
 }
 
@@ -454,8 +460,10 @@ std::vector<NodeCostDef> CostTerms(const orc_problem* p) {
         terms.push_back({"ee-motion_" + std::to_string(ee), kVel, 1, weight});
         terms.push_back({"ee-motion_" + std::to_string(ee), kVel, 2, 0.5 * weight});
       }
+    } else if (pr.first == 2 || pr.first == 3) {
+      // EnergyCostID / AngMomCostID (:636-643): time-discretised terms, summed by SampledCost* below
     } else {
-      throw std::runtime_error("unsupported: EnergyCost / AngularMomentumCost are not restated");
+      throw std::runtime_error("cost not defined!");     // :644
     }
   }
   return terms;
@@ -477,6 +485,11 @@ double orc_eval_f(orc_problem* p, const double* x) {
     }
     total += cost;
   }
+  const Parameters& pa = p->formulation.params_;
+  for (const auto& pr : p->costs) {
+    if (pr.first == 2) total += EnergyCostValue(p->splines, pr.second, pa.energy_cost_torque_weight_, pa.dt_cost_energy_);
+    if (pr.first == 3) total += AngMomCostValue(p->splines, *p->formulation.model_.dynamic_model_, pr.second, pa.dt_cost_ang_mom_);
+  }
   return total;
 }
 
@@ -497,6 +510,19 @@ void orc_eval_grad_f(orc_problem* p, const double* x, double* grad) {
               grad[col0 + i] += t.weight * 2.0 * val;
             }
       }
+      col0 += vs->GetRows();
+    }
+  }
+  const Parameters& pa = p->formulation.params_;
+  for (const auto& pr : p->costs) {
+    if (pr.first != 2 && pr.first != 3) continue;
+    int col0 = 0;
+    for (auto& vs : p->nlp.Vars()->GetComponents()) {     // ifopt::Composite::GetJacobian: one block per variable set
+      if (pr.first == 2)
+        EnergyCostFillBlock(p->splines, pr.second, pa.energy_cost_torque_weight_, pa.dt_cost_energy_, vs->GetName(), grad + col0);
+      else
+        AngMomCostFillBlock(p->splines, *p->formulation.model_.dynamic_model_, pr.second, pa.dt_cost_ang_mom_, vs->GetName(),
+                            grad + col0);
       col0 += vs->GetRows();
     }
   }

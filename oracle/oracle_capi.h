@@ -56,6 +56,8 @@ typedef struct orc_spec {
    * from HeightMap and override GetHeight / GetHeightDerivWrtX" (test/hopper_example.cc:53-91) for a piecewise profile */
   int terrain_table_n, terrain_table_mode;
   double terrain_table_x[ORC_MAX_TERRAIN_KNOTS], terrain_table_h[ORC_MAX_TERRAIN_KNOTS];
+  /* Parameters::dt_cost_energy_, energy_cost_torque_weight_, dt_cost_ang_mom_ (parameters.h:245-247) */
+  double dt_cost_energy, energy_cost_torque_weight, dt_cost_ang_mom;
 } orc_spec;
 
 /* Parameters::Parameters() defaults (parameters.cc:40-105), enable_stance_tracking=false. */

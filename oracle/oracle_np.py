@@ -1722,6 +1722,108 @@ class NodeCost:
         return g
 
 
+def cost_sample_times(T, dt):
+    """EnergyCost::GetSampleTimes (energy_cost.cc:52-66) == AngularMomentumCost::GetSampleTimes (:51-65)."""
+    if dt <= 0.0:
+        return [0.0, T]
+    ts, t = [], 0.0
+    while t <= T + 1e-9:
+        ts.append(t)
+        t += dt
+    return ts
+
+
+class EnergyCost:
+    """costs/energy_cost.cc:38-163: sum over samples of weight * dt * sum_ee (|f|^2 + torque_weight |tau|^2)."""
+
+    def __init__(self, splines, weight, torque_weight, dt):
+        self.sh, self.weight, self.torque_weight, self.dt = splines, weight, torque_weight, dt
+
+    def link(self, variables):
+        pass
+
+    def times(self):
+        return cost_sample_times(self.sh.base_linear.total_time(), self.dt)
+
+    def cost(self):                                                   # :68-90
+        if self.weight <= 0.0:
+            return 0.0
+        c = 0.0
+        for t in self.times():
+            inst = 0.0
+            for ee in range(len(self.sh.ee_force)):
+                f = self.sh.ee_force[ee].point(t)[kPos]
+                tau = self.sh.ee_torque[ee].point(t)[kPos]
+                inst += float(f @ f) + self.torque_weight * float(tau @ tau)
+            c += self.weight * inst * (self.dt if self.dt > 0.0 else 1.0)
+        return c
+
+    def gradient(self, var_set):                                      # :92-161
+        g = np.zeros(var_set.rows())
+        if self.weight <= 0.0:
+            return g
+        wdt = self.weight * (self.dt if self.dt > 0.0 else 1.0)
+        for t in self.times():
+            for ee in range(len(self.sh.ee_force)):
+                f = self.sh.ee_force[ee].point(t)[kPos]
+                tau = self.sh.ee_torque[ee].point(t)[kPos]
+                if var_set.name == "ee-force_%d" % ee:
+                    g += ((2.0 * wdt) * f) @ self.sh.ee_force[ee].jacobian_wrt_nodes(t, kPos).dense()
+                if var_set.name == "ee-torque_%d" % ee and self.torque_weight != 0.0:
+                    g += ((2.0 * wdt * self.torque_weight) * tau) @ self.sh.ee_torque[ee].jacobian_wrt_nodes(t, kPos).dense()
+                if var_set.name == "ee-schedule%d" % ee:
+                    g += ((2.0 * wdt) * f) @ self.sh.ee_force[ee].jacobian_of_pos_wrt_durations(t).dense()
+                    if self.torque_weight != 0.0:
+                        g += ((2.0 * wdt * self.torque_weight) * tau) @ self.sh.ee_torque[ee].jacobian_of_pos_wrt_durations(t).dense()
+        return g
+
+
+class AngularMomentumCost:
+    """costs/angular_momentum_cost.cc:39-208, SingleRigidBodyDynamics branch: sum of weight * dt * |R I_b R^T omega|^2."""
+
+    def __init__(self, splines, model, weight, dt):
+        self.sh, self.I_b, self.weight, self.dt = splines, model.I_b.dense(), weight, dt
+
+    def link(self, variables):
+        pass
+
+    def times(self):
+        return cost_sample_times(self.sh.base_linear.total_time(), self.dt)
+
+    def cost(self):                                                   # :67-101
+        if self.weight <= 0.0:
+            return 0.0
+        conv = self.sh.angular_converter
+        wdt = self.weight * (self.dt if self.dt > 0.0 else 1.0)
+        c = 0.0
+        for t in self.times():
+            R = conv.rotation(t)
+            v = (R @ self.I_b @ R.T) @ conv.angular_velocity(t)
+            c += wdt * float(v @ v)
+        return c
+
+    def gradient(self, var_set):                                      # :103-206
+        g = np.zeros(var_set.rows())
+        if self.weight <= 0.0 or var_set.name != "base-ang":
+            return g
+        conv = self.sh.angular_converter
+        wdt = self.weight * (self.dt if self.dt > 0.0 else 1.0)
+        for t in self.times():
+            R = conv.rotation(t)
+            omega = conv.angular_velocity(t)
+            v = (R @ self.I_b @ R.T) @ omega
+            m = (2.0 * wdt) * v
+            u = R.T @ omega
+            v2 = self.I_b @ u
+            J_R_v2 = conv.d_rot_vec_mult(t, v2, False).dense()
+            term_a = conv.d_rot_vec_mult(t, omega, True).dense()
+            term_b = R.T @ conv.d_ang_vel_wrt_nodes(t).dense()
+            J2 = R @ (self.I_b @ (term_a + term_b))
+            g += m @ J_R_v2
+            g += m @ J2
+        return g
+
+
 # ------------------------------------------------------------------------------------------------ formulation
 class SplineHolder:
     """helpers/spline_holder.cc:35-69."""
@@ -1744,7 +1846,7 @@ class SplineHolder:
 
 # towr::Parameters::ConstraintName (parameters.h:142-153)
 C_DYNAMIC, C_EE_ROM, C_TOTAL_TIME, C_TERRAIN, C_TERRAIN_HARD, C_FORCE, C_TORQUE, C_SWING, C_BASE_ROM, C_BASE_ACC, C_BASE_HEIGHT = range(11)
-COST_FORCES, COST_EE_MOTION = 0, 1
+COST_FORCES, COST_EE_MOTION, COST_ENERGY, COST_ANG_MOM = 0, 1, 2, 3
 
 
 class Formulation:
@@ -1952,8 +2054,12 @@ class Formulation:
                 for ee in range(n_ee):
                     self.costs += [NodeCost("ee-motion_%d" % ee, kVel, X, w), NodeCost("ee-motion_%d" % ee, kVel, Y, w),
                                    NodeCost("ee-motion_%d" % ee, kVel, Z, 0.5 * w)]
+            elif cid == COST_ENERGY:                                      # :636-639
+                self.costs.append(EnergyCost(sh, w, float(s.energy_cost_torque_weight), float(s.dt_cost_energy)))
+            elif cid == COST_ANG_MOM:                                     # :640-643
+                self.costs.append(AngularMomentumCost(sh, self.model, w, float(s.dt_cost_ang_mom)))
             else:
-                raise NotImplementedError("cost %d" % cid)
+                raise RuntimeError("cost not defined!")
         for c in self.costs:
             c.link(by_name)
 

@@ -62,6 +62,7 @@ class Spec(C.Structure):
         ("ee_stance_position", ((C.c_double * 2) * 17) * MAX_EE),
         ("terrain_table_n", C.c_int), ("terrain_table_mode", C.c_int),
         ("terrain_table_x", C.c_double * 16), ("terrain_table_h", C.c_double * 16),
+        ("dt_cost_energy", C.c_double), ("energy_cost_torque_weight", C.c_double), ("dt_cost_ang_mom", C.c_double),
     ]
 
 

@@ -273,6 +273,7 @@ class SingleRigidBodyDynamics {
   SpMat GetJacobianWrtEEPos(const SpMat& jac_ee_pos, int ee) const;
   double m() const { return m_; }
   double g() const { return g_; }
+  M3 GetInertiaB() const { return toDense(I_b); }   // single_rigid_body_dynamics.h:97
   int GetEECount() const { return static_cast<int>(ee_pos_.size()); }
  private:
   double m_, g_;
@@ -381,6 +382,7 @@ struct Parameters {
   std::vector<ConstraintName> constraints_;
   double dt_constraint_dynamic_, dt_constraint_range_of_motion_, dt_constraint_base_motion_;
   double dt_constraint_force_, dt_constraint_torque_;
+  double dt_cost_energy_, energy_cost_torque_weight_, dt_cost_ang_mom_;   // parameters.h:245-247
   double duration_base_polynomial_;
   int ee_polynomials_per_swing_phase_, force_polynomials_per_stance_phase_, torque_polynomials_per_stance_phase_;
   double force_limit_in_normal_direction_;

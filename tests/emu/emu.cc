@@ -123,3 +123,53 @@ extern "C" int emu_eval(const towr_b200_spec* s, const double* x, double* g, dou
     return -1;
   }
 }
+
+// ---- eval_f / eval_grad_f: the NodeCost column table (cost_kernel.cu CostKernel) and the time-discretised terms
+// (sampled_cost.cuh) replayed serially for one problem
+#include "../../towr2025_b200/csrc/sampled_cost.cuh"
+
+extern "C" int emu_eval_cost(const towr_b200_spec* s, const double* x, double* f_out, double* grad) {
+  try {
+    HostProgram hp;
+    BuildProgram(*s, hp);
+    CostTables ct;
+    BuildCostTables(hp, *s, ct);
+    double fsum = 0.0;
+    for (int c = 0; c < ct.n_vars; ++c) {
+      double g = 0.0;
+      for (int k = ct.col_ptr[c]; k < ct.col_ptr[c + 1]; ++k) {
+        const double w = ct.weights[k], val = x[c];
+        g = g + (w * 2.0) * val;
+        fsum = fsum + w * (val * val);
+      }
+      grad[c] = g;
+    }
+    *f_out = fsum;
+    SampledCost sc;
+    BuildSampledCost(hp, *s, sc);
+    if (sc.blob.empty()) return 0;
+    const SampledView V = MakeSampledView(sc.blob.data());
+    const SampledHeader& H = *V.h;
+    std::vector<double> work((sc.shared_bytes - H.bytes) / sizeof(double) + 8);
+    const SampledWork W = SampledCarve(H, reinterpret_cast<unsigned char*>(work.data()));
+    ProblemConst pc;
+    FillProblemConst(*s, pc);
+    for (int i = 0; i < 6 * H.n_nodes; ++i) SampledNode(V, W, x, i);
+    if (H.rt) for (int e = 0; e < H.n_ee; ++e) SampledPhaseDurations(V, W, x, e);
+    for (int poly = 0; poly < H.n_polys; ++poly) SampledPolyDuration(V, W, poly);
+    for (int i = 0; i < 3 * H.n_polys; ++i) SampledCoeff(V, W, i);
+    for (int ti = 0; ti < H.n_terms; ++ti) {
+      const SampledTerm tm = V.terms[ti];
+      for (int it = 0; it < tm.n_splines * tm.n_samples; ++it) SampledItem(V, W, tm, pc.I, it);
+      for (int k = 0; k < tm.n_samples; ++k) SampledSummand(V, W, tm, k);
+      double c = 0.0;
+      for (int k = 0; k < tm.n_samples; ++k) c += W.inst[k];
+      *f_out = *f_out + c;
+      for (int j = 0; j < tm.n_jobs; ++j) SampledJobGradient(V, W, tm, grad, j);
+    }
+    return 0;
+  } catch (const std::exception& e) {
+    g_err = e.what();
+    return -1;
+  }
+}

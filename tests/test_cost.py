@@ -1,12 +1,16 @@
-"""eval_f / eval_grad_f: the NodeCost terms of NlpFormulation::GetCosts (nlp_formulation.cc:605-681, costs/node_cost.cc),
-as test/hopper_example.cc:147-148 enables them.  Oracle known answers on the CPU, CUDA path against the oracle on the GPU."""
+"""eval_f / eval_grad_f: the cost terms of NlpFormulation::GetCosts (nlp_formulation.cc:605-681): NodeCost
+(costs/node_cost.cc) as test/hopper_example.cc:147-148 enables it, and the time-discretised EnergyCost
+(costs/energy_cost.cc) and AngularMomentumCost (costs/angular_momentum_cost.cc).  Oracle known answers and the kernel
+arithmetic replayed on the host (tests/emu) on the CPU, CUDA path against the oracle on the GPU."""
+import ctypes as C
+
 import numpy as np
 import pytest
 
 from test_hopper_example import hopper_spec
 from util import CASES, mk, perturbed, to_oracle_spec, tol_ratio
 
-FORCES, EE_MOTION, ENERGY = 0, 1, 2
+FORCES, EE_MOTION, ENERGY, ANG_MOM = 0, 1, 2, 3
 
 
 def with_costs(s, costs):
@@ -48,13 +52,87 @@ def test_oracle_cost_known_answers(product, oracle):
 
 def test_cost_spec_errors(product):
     T = product
-    with pytest.raises(T.TowrB200Error) as e:
-        T.Structure(with_costs(mk(T, CASES[4]), [(ENERGY, 1.0)]))
-    assert e.value.code == -2                                  # unsupported
     with pytest.raises(T.TowrB200Error):
         T.Structure(with_costs(mk(T, CASES[4]), [(7, 1.0)]))   # "cost not defined!" (nlp_formulation.cc:644)
     a = T.Structure(with_costs(mk(T, CASES[4]), [(FORCES, 1.0)]))
     assert not a.accepts(mk(T, CASES[4]))                      # the cost list is part of the structure class
+    e = T.Structure(with_costs(mk(T, CASES[4]), [(ENERGY, 1.0)]))
+    other = with_costs(mk(T, CASES[4]), [(ENERGY, 1.0)])
+    assert e.accepts(other)
+    other.dt_cost_energy = 0.05                                # ... and so are the sampling period and the torque weight
+    assert not e.accepts(other)
+    s = with_costs(mk(T, CASES[4]), [(ENERGY, 1.0)])
+    s.dt_cost_energy = float("nan")
+    with pytest.raises(T.TowrB200Error):
+        T.Structure(s)
+    s = mk(T, CASES[4])
+    assert s.dt_cost_energy == 0.02 and s.energy_cost_torque_weight == 1.0 and s.dt_cost_ang_mom == 0.02   # parameters.cc:69-71
+
+
+# (case, cost list, dt_cost_energy, energy_cost_torque_weight, dt_cost_ang_mom)
+SAMPLED = [
+    ("monoped_hop", [(ENERGY, 1e-3)], None, None, None),
+    ("monoped_hop", [(ANG_MOM, 0.5)], None, None, None),
+    ("anymal_trot", [(FORCES, 1e-9), (EE_MOTION, 1e-4), (ENERGY, 1e-3), (ANG_MOM, 0.7)], None, None, None),
+    ("biped_walk_durations", [(ENERGY, 1e-3), (ANG_MOM, 0.7)], None, None, None),
+    ("anymal_trot_durations", [(ENERGY, 1e-3), (ANG_MOM, 0.7), (FORCES, 1e-5)], 0.03, 0.0, 0.05),   # no torque term (:119)
+    ("monoped_hop_torque", [(ENERGY, 2.0), (ANG_MOM, 0.0)], 0.0, 0.5, None),   # dt <= 0: t = 0 and T only (:55-59); weight 0: no term
+]
+
+
+def sampled_spec(T, name, costs, dt_energy, torque_weight, dt_ang_mom):
+    s = with_costs(mk(T, [c for c in CASES if c[0] == name][0]), costs)
+    if dt_energy is not None:
+        s.dt_cost_energy = dt_energy
+    if torque_weight is not None:
+        s.energy_cost_torque_weight = torque_weight
+    if dt_ang_mom is not None:
+        s.dt_cost_ang_mom = dt_ang_mom
+    return s
+
+
+def test_oracle_sampled_cost_gradient_is_consistent(product, oracle):
+    """EnergyCost / AngularMomentumCost: the gradient (incl. the ee-schedule columns) matches central differences of f."""
+    T, O = product, oracle
+    s = sampled_spec(T, "biped_walk_durations", [(ENERGY, 1e-3), (ANG_MOM, 0.7)], None, None, None)
+    st = T.Structure(s)
+    p = O.Problem(to_oracle_spec(O, s))
+    x = perturbed(st.x0(s), 2, 0.05)
+    g = p.eval_grad_f(x)
+    off = np.concatenate([[0], np.cumsum([r for _, r in st.var_sets()])])
+    names = [n for n, _ in st.var_sets()]
+    for n in ("base-ang", "ee-force_0", "ee-torque_1", "ee-schedule0"):
+        i = names.index(n)
+        assert np.abs(g[off[i]:off[i + 1]]).max() > 0, n
+    for n in ("base-lin", "ee-motion_0"):
+        i = names.index(n)
+        assert (g[off[i]:off[i + 1]] == 0.0).all(), n
+    rng = np.random.default_rng(0)
+    for c in rng.choice(np.nonzero(g)[0], 12, replace=False):
+        h = 1e-6
+        xp, xm = x.copy(), x.copy()
+        xp[c] += h
+        xm[c] -= h
+        fd = (p.eval_f(xp) - p.eval_f(xm)) / (2 * h)
+        assert abs(fd - g[c]) <= 1e-6 * max(1.0, abs(g[c]))
+
+
+@pytest.mark.parametrize("case", SAMPLED, ids=lambda c: c[0] + "".join("_%d" % cid for cid, _ in c[1]))
+def test_emulated_cost_kernels_match_oracle(product, oracle, emu, case):
+    """The device code of both cost kernels (NodeCost table, sampled_cost.cuh) replayed serially on the host."""
+    T, O = product, oracle
+    s = sampled_spec(T, *case)
+    st = T.Structure(s)
+    p = O.Problem(to_oracle_spec(O, s))
+    DP = C.POINTER(C.c_double)
+    for seed in (0, 5):
+        x = perturbed(st.x0(s), 70 + seed, 0.05 if seed else 0.0)
+        f, g = np.zeros(1), np.zeros(st.n_vars)
+        rc = emu.emu_eval_cost(C.byref(s), x.ctypes.data_as(DP), f.ctypes.data_as(DP), g.ctypes.data_as(DP))
+        assert rc == 0, emu.emu_last_error()
+        assert tol_ratio(f, np.array([p.eval_f(x)])) <= 1.0
+        assert tol_ratio(g, p.eval_grad_f(x)) <= 1.0
+        assert f[0] > 0.0 or seed == 0
 
 
 @pytest.mark.gpu
@@ -81,6 +159,40 @@ def test_gpu_cost_matches_oracle(product, oracle, name):
     # the constraint path is unchanged by the cost list
     gg, vv = b.eval(x)
     assert np.isfinite(gg).all() and np.isfinite(vv).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", SAMPLED, ids=lambda c: c[0] + "".join("_%d" % cid for cid, _ in c[1]))
+def test_gpu_sampled_costs_match_oracle(product, oracle, case):
+    """EnergyCost / AngularMomentumCost on the GPU; problem 1 has its own inertia (AngularMomentumCost reads the
+    batch problem's I_b)."""
+    T, O = product, oracle
+    s = sampled_spec(T, *case)
+    st = T.Structure(s)
+    n = 5
+    x = np.stack([perturbed(st.x0(s), 70 + i, 0.05 if i else 0.0) for i in range(n)])
+    b = T.Batch(st, n)
+    b.set_all(s)
+    s1 = sampled_spec(T, *case)
+    s1.inertia[0] *= 1.5
+    s1.inertia[4] += 0.05
+    b.set_problem(1, s1)
+    f, g = b.eval_cost(x)
+    f1, _ = b.eval_cost(x, 1)
+    _, g2 = b.eval_cost(x, 2)
+    assert np.array_equal(f, f1) and np.array_equal(g, g2)
+    for i in range(n):
+        p = O.Problem(to_oracle_spec(O, s1 if i == 1 else s))
+        assert tol_ratio(np.array([f[i]]), np.array([p.eval_f(x[i])])) <= 1.0, i
+        assert tol_ratio(g[i], p.eval_grad_f(x[i])) <= 1.0, i
+    # device entry point on the caller's buffers and stream
+    import torch
+    dx = torch.from_numpy(x).cuda()
+    df = torch.full((n,), float("nan"), dtype=torch.float64, device="cuda")
+    dg = torch.full((n, st.n_vars), float("nan"), dtype=torch.float64, device="cuda")
+    b.eval_cost_device(n, 3, dx.data_ptr(), df.data_ptr(), dg.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert np.array_equal(df.cpu().numpy(), f) and np.array_equal(dg.cpu().numpy(), g)
 
 
 @pytest.mark.gpu

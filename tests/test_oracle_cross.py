@@ -49,13 +49,20 @@ def test_cpp_oracle_matches_numpy_restatement(oracle, case):
         assert nnz[0] != nnz[1], "the Gap case should exercise a value-dependent pattern"
 
 
-def test_costs_match_numpy_restatement(oracle):
-    """eval_f / eval_grad_f: NodeCost terms of hopper_example.cc:147-148 (ForcesCostID, EEMotionCostID)."""
+@pytest.mark.parametrize("robot,optimise,costs", [
+    (0, True, ((0, 1e-3), (1, 1e-2))),                       # hopper_example.cc:147-148 (ForcesCostID, EEMotionCostID)
+    (0, True, ((2, 1e-3), (3, 0.7))),                        # EnergyCostID, AngMomCostID with the ee-schedule gradient
+    (1, False, ((2, 1e-3), (3, 0.7), (0, 1e-3))),
+    (3, True, ((2, 1e-3), (3, 0.7))),
+], ids=["monoped_nodecost", "monoped_sampled_durations", "biped_sampled", "anymal_sampled_durations"])
+def test_costs_match_numpy_restatement(oracle, robot, optimise, costs):
+    """eval_f / eval_grad_f: NodeCost (node_cost.cc), EnergyCost (energy_cost.cc), AngularMomentumCost
+    (angular_momentum_cost.cc)."""
     O = oracle
-    s = O.make_spec(O.Monoped, 0, 2.4, optimize_durations=True, extra_constraints=(O.Torque,))
-    s.n_costs = 2
-    s.cost_ids[0], s.cost_weights[0] = 0, 1e-3
-    s.cost_ids[1], s.cost_weights[1] = 1, 1e-2
+    s = O.make_spec(robot, 0, 2.4, optimize_durations=optimise, extra_constraints=(O.Torque,))
+    s.n_costs = len(costs)
+    for i, (cid, w) in enumerate(costs):
+        s.cost_ids[i], s.cost_weights[i] = cid, w
     p, f = O.Problem(s), N.Formulation(s)
     x = perturbed(p.x0(), 3, 0.05)
     assert tol_ratio(np.array([f.eval_f(x)]), np.array([p.eval_f(x)])) <= 1.0

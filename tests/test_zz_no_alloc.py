@@ -12,11 +12,15 @@ from util import perturbed, tol_ratio
 pytestmark = pytest.mark.gpu
 
 
-def _with_costs(T, robot, combo, total_time, optimise):
+def _with_costs(T, robot, combo, total_time, optimise, sampled=False):
     s = T.make_spec(robot, combo, total_time, optimize_durations=optimise)
     s.n_costs = 2                                  # as test/hopper_example.cc:147-148
     s.cost_ids[0], s.cost_weights[0] = 0, 1e-3     # ForcesCostID
     s.cost_ids[1], s.cost_weights[1] = 1, 1e-2     # EEMotionCostID
+    if sampled:                                    # the time-discretised terms: their tables live in the static array too
+        s.n_costs = 4
+        s.cost_ids[2], s.cost_weights[2] = 2, 1e-3     # EnergyCostID
+        s.cost_ids[3], s.cost_weights[3] = 3, 0.5      # AngMomCostID
     return s
 
 
@@ -24,8 +28,11 @@ def test_static_cost_matches_batch_entry_point_twice(product):
     import torch
     T = product
     stream = torch.cuda.current_stream().cuda_stream
-    for robot, combo, total_time, optimise, n in ((T.Anymal, T.C1, 2.0, False, 33), (T.Monoped, T.C0, 2.4, True, 7)):
-        s = _with_costs(T, robot, combo, total_time, optimise)
+    for robot, combo, total_time, optimise, n, sampled in ((T.Anymal, T.C1, 2.0, False, 33, False),
+                                                           (T.Monoped, T.C0, 2.4, True, 7, False),
+                                                           (T.Biped, T.C0, 2.4, True, 9, True),
+                                                           (T.Anymal, T.C1, 2.0, False, 5, True)):
+        s = _with_costs(T, robot, combo, total_time, optimise, sampled)
         st = T.Structure(s)
         x = np.stack([perturbed(st.x0(s), 40 + i, 0.05) for i in range(n)])
         b = T.Batch(st, n)

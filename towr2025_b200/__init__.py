@@ -68,6 +68,7 @@ class Spec(C.Structure):
         ("ee_stance_position", ((C.c_double * 2) * 17) * MAX_EE),
         ("terrain_table_n", C.c_int), ("terrain_table_mode", C.c_int),
         ("terrain_table_x", C.c_double * 16), ("terrain_table_h", C.c_double * 16),
+        ("dt_cost_energy", C.c_double), ("energy_cost_torque_weight", C.c_double), ("dt_cost_ang_mom", C.c_double),
     ]
 
     def copy(self):
@@ -378,6 +379,11 @@ class Batch:
         (a cudaStream_t as int; None/0 = CUDA's default stream)."""
         _check(self._L.towr_b200_batch_eval_device(self._h, n, what, C.c_void_p(d_x), C.c_void_p(d_g or 0),
                                                     C.c_void_p(d_vals or 0), C.c_void_p(stream or 0)))
+
+    def eval_cost_device(self, n, what, d_x, d_f, d_grad, stream=None):
+        """Device-pointer eval_f / eval_grad_f (towr_b200_batch_eval_cost_device); asynchronous on `stream`."""
+        _check(self._L.towr_b200_batch_eval_cost_device(self._h, n, what, C.c_void_p(d_x), C.c_void_p(d_f or 0),
+                                                         C.c_void_p(d_grad or 0), C.c_void_p(stream or 0)))
 
     @property
     def n_dynamic(self):

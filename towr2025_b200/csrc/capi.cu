@@ -128,6 +128,8 @@ struct towr_b200_batch {
   // cost tables (cost.h), built at the first eval_cost call
   bool cost_ready = false;
   tb::CostDevice cost_dev{};
+  const unsigned char* sampled_dev = nullptr;   // EnergyCost / AngularMomentumCost tables (cost.h), nullptr: none
+  size_t sampled_shared = 0;
   double *cost_f_dev = nullptr, *cost_grad_dev = nullptr;
 
   void SyncConsts() {
@@ -552,6 +554,12 @@ void EnsureCost(towr_b200_batch* b) {
   b->cost_dev.n_vars = h.n_vars;
   b->cost_dev.col_ptr = up(h.col_ptr);
   b->cost_dev.weights = up(h.weights);
+  tb::SampledCost sc;
+  tb::BuildSampledCost(b->st->hp, b->st->spec, sc);
+  if (!sc.blob.empty()) {
+    b->sampled_dev = up(sc.blob);
+    b->sampled_shared = sc.shared_bytes;
+  }
   b->cost_ready = true;
 }
 }  // namespace
@@ -569,6 +577,15 @@ int towr_b200_batch_eval_cost_device(towr_b200_batch* b, int n, int what, const 
     Check(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device), "device attribute");
     Check(tb::LaunchCost(b->cost_dev, what, d_x, d_f, d_grad, n, 16 * sms, static_cast<cudaStream_t>(stream)), "launch");
     b->launches += 1;
+    if (b->sampled_dev) {
+      if (b->pc_dirty) {                        // per-problem inertia: the batch's constants
+        b->SyncConsts();
+        Check(cudaStreamSynchronize(b->stream), "sync consts");
+      }
+      Check(tb::LaunchSampledCost(b->sampled_dev, b->sampled_shared, b->pc_dev, what, d_x, d_f, d_grad, n, sms,
+                                  static_cast<cudaStream_t>(stream)), "launch");
+      b->launches += 1;
+    }
   });
 }
 
@@ -594,6 +611,12 @@ int towr_b200_batch_eval_cost(towr_b200_batch* b, int n, int what, const double*
     Check(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device), "device attribute");
     Check(tb::LaunchCost(b->cost_dev, what, b->x_dev, b->cost_f_dev, b->cost_grad_dev, n, 16 * sms, b->stream), "launch");
     b->launches += 1;
+    if (b->sampled_dev) {
+      b->SyncConsts();
+      Check(tb::LaunchSampledCost(b->sampled_dev, b->sampled_shared, b->pc_dev, what, b->x_dev, b->cost_f_dev,
+                                  b->cost_grad_dev, n, sms, b->stream), "launch");
+      b->launches += 1;
+    }
     if (what & 1) Check(cudaMemcpyAsync(f_out, b->cost_f_dev, sizeof(double) * n, cudaMemcpyDeviceToHost, b->stream), "D2H f");
     if (what & 2)
       Check(cudaMemcpyAsync(grad_out, b->cost_grad_dev, sizeof(double) * b->dp.n_vars * n, cudaMemcpyDeviceToHost, b->stream), "D2H gradient");
@@ -611,8 +634,10 @@ int towr_b200_eval_cost_static(const towr_b200_structure* st, int device, int n,
     if (towr_b200_device_count() < 1) throw CudaError("no CUDA device visible: this backend has no CPU fallback");
     tb::CostTables h;                                   // host tables only
     tb::BuildCostTables(st->hp, st->spec, h);
+    tb::SampledCost sc;
+    tb::BuildSampledCost(st->hp, st->spec, sc);
     const char* why = "";
-    const cudaError_t err = tb::LaunchCostStatic(h, device, what, d_x, d_f, d_grad, n, static_cast<cudaStream_t>(stream), &why);
+    const cudaError_t err = tb::LaunchCostStatic(h, sc, device, what, d_x, d_f, d_grad, n, static_cast<cudaStream_t>(stream), &why);
     if (err == cudaErrorInvalidValue && *why) throw std::runtime_error(std::string("eval_cost_static: ") + why);
     if (err != cudaSuccess) throw CudaError(std::string("eval_cost_static") + (*why ? std::string(" (") + why + ")" : std::string()) + ": " + cudaGetErrorString(err));
   });

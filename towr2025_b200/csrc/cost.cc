@@ -1,6 +1,9 @@
 // cost.cc — host tables of the cost kernel (cost.h).
 #include "cost.h"
 
+#include <algorithm>
+#include <cstring>
+#include <numeric>
 #include <stdexcept>
 
 namespace tb {
@@ -26,8 +29,10 @@ void BuildCostTables(const HostProgram& hp, const towr_b200_spec& s, CostTables&
         terms.push_back({kEEMotion, ee, 1, 1, weight});
         terms.push_back({kEEMotion, ee, 1, 2, 0.5 * weight});
       }
+    } else if (s.cost_ids[c] == TOWR_B200_COST_ENERGY || s.cost_ids[c] == TOWR_B200_COST_ANG_MOM) {
+      // time-discretised terms: BuildSampledCost
     } else {
-      throw std::runtime_error("unsupported: EnergyCost / AngularMomentumCost are not built");
+      throw std::runtime_error("cost not defined!");         // nlp_formulation.cc:644
     }
   }
   o.n_terms = static_cast<int>(terms.size());
@@ -44,6 +49,175 @@ void BuildCostTables(const HostProgram& hp, const towr_b200_spec& s, CostTables&
     o.weights.insert(o.weights.end(), ws.begin(), ws.end());
     o.col_ptr.push_back(static_cast<int>(o.weights.size()));
   }
+}
+
+namespace {
+template <class T>
+int Append(std::vector<unsigned char>& blob, const std::vector<T>& v) {
+  while (blob.size() % 8) blob.push_back(0);
+  const int off = static_cast<int>(blob.size());
+  const unsigned char* p = reinterpret_cast<const unsigned char*>(v.data());
+  blob.insert(blob.end(), p, p + sizeof(T) * v.size());
+  return off;
+}
+}  // namespace
+
+void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCost& out) {
+  out = SampledCost{};
+  std::vector<SampledTerm> terms;
+  std::vector<SampledSpline> splines;
+  std::vector<SampledFoot> feet;
+  std::vector<SampledJob> jobs;
+  std::vector<uint16_t> node_src, poly_spline;
+  std::vector<double> poly_T, times;
+  std::vector<uint32_t> poly_meta;
+  int n_nodes = 0, n_polys = 0, n_phases = 0;
+  const bool rt = hp.optimize_durations;
+  const VarSet* lin = hp.Find(kBaseLin);
+  // Spline::GetTotalTime of base_linear_ (helpers/spline.cc:119-123)
+  const double T_total = std::accumulate(lin->poly_T.begin(), lin->poly_T.end(), 0.0);
+  auto sample_times = [&](double dt) {      // GetSampleTimes (energy_cost.cc:52-66, angular_momentum_cost.cc:51-65)
+    std::vector<double> ts;
+    if (dt <= 0.0) return std::vector<double>{0.0, T_total};
+    for (double t = 0.0; t <= T_total + 1e-9; t += dt) {
+      ts.push_back(t);
+      if (ts.size() > 100000) throw std::runtime_error("unsupported: cost sampling period too small");
+    }
+    return ts;
+  };
+  auto add_spline = [&](const VarSet& v, int foot, bool is_torque, double scale, double mscale) {
+    SampledSpline r{};
+    r.node0 = n_nodes;
+    r.poly0 = n_polys;
+    r.n_polys = v.n_polys();
+    r.foot = foot;
+    r.rt = (foot >= 0 && rt) ? 1 : 0;
+    r.is_torque = is_torque ? 1 : 0;
+    r.scale = scale;
+    r.mscale = mscale;
+    std::vector<int> src(static_cast<size_t>(v.n_nodes) * 6, 0xFFFF);
+    for (int idx = 0; idx < v.n_vars; ++idx)
+      for (const NodeRef& nr : v.refs[idx]) src[nr.node * 6 + nr.deriv * 3 + nr.dim] = v.col0 + idx;
+    for (int x : src) node_src.push_back(static_cast<uint16_t>(x));
+    for (int p = 0; p < v.n_polys(); ++p) {
+      poly_T.push_back(v.poly_T[p]);
+      poly_spline.push_back(static_cast<uint16_t>(splines.size()));
+      poly_meta.push_back(r.rt ? (static_cast<uint32_t>(v.poly_phase[p]) | (static_cast<uint32_t>(v.polys_in_phase[p]) << 8) |
+                                  (static_cast<uint32_t>(v.poly_in_phase[p]) << 16))
+                               : kPolyFixed);
+    }
+    n_nodes += v.n_nodes;
+    n_polys += v.n_polys();
+    splines.push_back(r);
+  };
+  auto node_jobs = [&](const VarSet& v, int spline_in_term) {
+    for (int idx = 0; idx < v.n_vars; ++idx) {
+      if (v.refs[idx].size() != 1) throw std::runtime_error("unsupported: a cost variable that writes several node values");
+      const NodeRef& nr = v.refs[idx][0];
+      SampledJob j{};
+      j.col = v.col0 + idx;
+      j.kind = kJobNode;
+      j.spline = static_cast<uint16_t>(spline_in_term);
+      j.node = static_cast<uint16_t>(nr.node);
+      j.deriv_dim = static_cast<uint16_t>(nr.deriv * 4 + nr.dim);
+      jobs.push_back(j);
+    }
+  };
+  int max_items = 0, max_samples = 0;
+  for (int c = 0; c < s.n_costs; ++c) {
+    const double weight = s.cost_weights[c];
+    const bool energy = s.cost_ids[c] == TOWR_B200_COST_ENERGY, ang_mom = s.cost_ids[c] == TOWR_B200_COST_ANG_MOM;
+    if (!energy && !ang_mom) continue;
+    if (weight <= 0.0) continue;                               // GetCost / FillJacobianBlock return at once (:70, :94)
+    const double dt = energy ? s.dt_cost_energy : s.dt_cost_ang_mom;
+    SampledTerm t{};
+    t.kind = energy ? kSampledEnergy : kSampledAngMom;
+    t.spline0 = static_cast<int>(splines.size());
+    t.time0 = static_cast<int>(times.size());
+    t.job0 = static_cast<int>(jobs.size());
+    t.weight = weight;
+    t.dtf = dt > 0.0 ? dt : 1.0;
+    const std::vector<double> ts = sample_times(dt);
+    times.insert(times.end(), ts.begin(), ts.end());
+    t.n_samples = static_cast<int>(ts.size());
+    const double wdt = weight * t.dtf;
+    if (energy) {
+      const double tw = s.energy_cost_torque_weight;
+      for (int e = 0; e < hp.n_ee; ++e) {
+        const VarSet* vf = hp.Find(kEEForce, e);
+        const VarSet* vt = hp.Find(kEETorque, e);
+        add_spline(*vf, e, false, 1.0, 2.0 * wdt);
+        add_spline(*vt, e, true, tw, 2.0 * wdt * tw);
+        node_jobs(*vf, 2 * e);
+        if (tw != 0.0) node_jobs(*vt, 2 * e + 1);              // energy_cost.cc:119
+        if (rt) {                                              // id::EESchedule(ee) exists only then (:129-157)
+          const VarSet* vs = hp.Find(kEESchedule, e);
+          for (int ph = 0; ph < vs->n_vars; ++ph) {
+            SampledJob j{};
+            j.col = vs->col0 + ph;
+            j.kind = kJobSchedule;
+            j.spline = static_cast<uint16_t>(2 * e);
+            j.node = static_cast<uint16_t>(ph);
+            j.deriv_dim = tw != 0.0 ? 1 : 0;
+            jobs.push_back(j);
+          }
+        }
+      }
+    } else {
+      const VarSet* va = hp.Find(kBaseAng);
+      add_spline(*va, -1, false, 1.0, 2.0 * wdt);
+      node_jobs(*va, 0);
+    }
+    t.n_splines = static_cast<int>(splines.size()) - t.spline0;
+    t.n_jobs = static_cast<int>(jobs.size()) - t.job0;
+    max_items = std::max(max_items, t.n_splines * t.n_samples);
+    max_samples = std::max(max_samples, t.n_samples);
+    terms.push_back(t);
+  }
+  if (terms.empty()) return;
+  for (int e = 0; e < hp.n_ee; ++e) {
+    SampledFoot f{};
+    f.phase0 = n_phases;
+    f.n_phases = s.n_phases[e];
+    f.col0 = rt ? hp.Find(kEESchedule, e)->col0 : 0;
+    for (int i = 0; i < s.n_phases[e]; ++i) f.total += s.phase_durations[e][i];   // phase_durations.cc:40-50
+    feet.push_back(f);
+    n_phases += s.n_phases[e];
+  }
+  SampledHeader h{};
+  h.n_vars = hp.n_vars;
+  h.n_ee = hp.n_ee;
+  h.rt = rt ? 1 : 0;
+  h.n_terms = static_cast<int>(terms.size());
+  h.n_splines = static_cast<int>(splines.size());
+  h.n_nodes = n_nodes;
+  h.n_polys = n_polys;
+  h.n_phases = n_phases;
+  h.n_times = static_cast<int>(times.size());
+  h.n_jobs = static_cast<int>(jobs.size());
+  h.max_items = max_items;
+  h.max_samples = max_samples;
+  // body inertia as SingleRigidBodyDynamics builds it (single_rigid_body_dynamics.cc:36-44): off-diagonals negated
+  const double* in = s.inertia;   // Ixx, Iyy, Izz, Ixy, Ixz, Iyz
+  const double I[9] = {in[0], -in[3], -in[4], -in[3], in[1], -in[5], -in[4], -in[5], in[2]};
+  std::memcpy(h.I, I, sizeof(I));
+  std::vector<unsigned char>& blob = out.blob;
+  blob.assign(sizeof(SampledHeader), 0);
+  h.off_terms = Append(blob, terms);
+  h.off_splines = Append(blob, splines);
+  h.off_feet = Append(blob, feet);
+  h.off_poly_T = Append(blob, poly_T);
+  h.off_times = Append(blob, times);
+  h.off_jobs = Append(blob, jobs);
+  h.off_poly_meta = Append(blob, poly_meta);
+  h.off_node_src = Append(blob, node_src);
+  h.off_poly_spline = Append(blob, poly_spline);
+  while (blob.size() % 16) blob.push_back(0);
+  h.bytes = static_cast<int>(blob.size());
+  std::memcpy(blob.data(), &h, sizeof(h));
+  out.shared_bytes = SampledSharedBytes(h);
+  if (out.shared_bytes > kSampledMaxShared)
+    throw std::runtime_error("unsupported: the cost samples of this class exceed one SM's shared memory (larger dt_cost_*)");
 }
 
 }  // namespace tb

@@ -7,6 +7,7 @@
 #include <mutex>
 
 #include "cost.h"
+#include "sampled_cost.cuh"
 
 namespace tb {
 
@@ -56,6 +57,81 @@ cudaError_t LaunchCost(const CostDevice& c, int what, const double* x, double* f
   return cudaGetLastError();
 }
 
+// ---- time-discretised cost terms (EnergyCost, AngularMomentumCost): arithmetic in sampled_cost.cuh ------------------
+// One CTA per problem (grid-stride), class tables (cost.h blob) staged in shared memory once per CTA.  Per term:
+//   1. item = (spline, sample): segment and local time on the problem's own polynomial durations (spline.cc:48-78), the
+//      spline's value there, and what the gradient needs of it (the row vector m of energy_cost.cc:112 / the chain-rule
+//      factors of angular_momentum_cost.cc:144-203);
+//   2. f: thread k forms sample k's summand in the reference's order, one thread adds the samples in time order;
+//   3. gradient: one thread per column walks the samples in time order, like the reference's accumulation into
+//      jac.coeffRef(0, col) over its sample loop.
+// Adds to f / grad written by CostKernel earlier on the same stream.
+constexpr int kSampledThreads = 256;
+
+__global__ void __launch_bounds__(kSampledThreads)
+SampledCostKernel(const unsigned char* __restrict__ blob_g, const ProblemConst* __restrict__ pcs, int what,
+                  const double* __restrict__ x, double* __restrict__ f_out, double* __restrict__ grad_out, int n_problems) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int tid = threadIdx.x;
+  const int blob_bytes = reinterpret_cast<const SampledHeader*>(blob_g)->bytes;
+  for (int i = tid; i < blob_bytes / 16; i += kSampledThreads)
+    reinterpret_cast<int4*>(smem)[i] = __ldg(reinterpret_cast<const int4*>(blob_g) + i);
+  __syncthreads();
+  const SampledView V = MakeSampledView(smem);
+  const SampledHeader& H = *V.h;
+  const SampledWork W = SampledCarve(H, smem + ((H.bytes + 15) & ~15));
+  for (int prob = blockIdx.x; prob < n_problems; prob += gridDim.x) {
+    const double* xp = x + static_cast<size_t>(prob) * H.n_vars;
+    for (int i = tid; i < 6 * H.n_nodes; i += kSampledThreads) SampledNode(V, W, xp, i);
+    if (H.rt && tid < H.n_ee) SampledPhaseDurations(V, W, xp, tid);
+    __syncthreads();
+    for (int poly = tid; poly < H.n_polys; poly += kSampledThreads) SampledPolyDuration(V, W, poly);
+    __syncthreads();
+    for (int i = tid; i < 3 * H.n_polys; i += kSampledThreads) SampledCoeff(V, W, i);
+    __syncthreads();
+    double I[9];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) I[i] = pcs ? __ldg(&pcs[prob].I[i]) : H.I[i];
+    for (int ti = 0; ti < H.n_terms; ++ti) {
+      const SampledTerm tm = V.terms[ti];
+      for (int it = tid; it < tm.n_splines * tm.n_samples; it += kSampledThreads) SampledItem(V, W, tm, I, it);
+      __syncthreads();
+      if (what & 1) {
+        for (int k = tid; k < tm.n_samples; k += kSampledThreads) SampledSummand(V, W, tm, k);
+        __syncthreads();
+        if (tid == 0) {
+          double c = 0.0;
+          for (int k = 0; k < tm.n_samples; ++k) c += W.inst[k];   // cost += ... over the samples in time order
+          f_out[prob] = f_out[prob] + c;
+        }
+      }
+      if (what & 2) {
+        double* gp = grad_out + static_cast<size_t>(prob) * H.n_vars;
+        for (int j = tid; j < tm.n_jobs; j += kSampledThreads) SampledJobGradient(V, W, tm, gp, j);
+      }
+      __syncthreads();
+    }
+  }
+}
+
+cudaError_t LaunchSampledCost(const unsigned char* blob_dev, size_t shared_bytes, const ProblemConst* pcs, int what,
+                              const double* x, double* f, double* grad, int n_problems, int sms, cudaStream_t stream) {
+  if (n_problems <= 0 || !blob_dev) return cudaSuccess;
+  cudaError_t err = cudaFuncSetAttribute(SampledCostKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(shared_bytes));
+  if (err != cudaSuccess) return err;
+  int occ = 1;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, SampledCostKernel, kSampledThreads, shared_bytes) != cudaSuccess ||
+      occ < 1) {
+    cudaGetLastError();
+    occ = 1;
+  }
+  const int max_ctas = sms * occ;
+  const int grid = n_problems < max_ctas ? n_problems : max_ctas;
+  SampledCostKernel<<<grid, kSampledThreads, shared_bytes, stream>>>(blob_dev, pcs, what, x, f, grad, n_problems);
+  return cudaGetLastError();
+}
+
 // ---- allocation-free variant (towr_b200_eval_cost_static, include/towr_b200.h) --------------------------------------
 // The work tables of the cost kernel (column pointers and weights), which towr_b200_batch_eval_cost[_device] keeps in
 // cudaMalloc'ed memory, live here in a file-scope device array: every GPU that loads the library holds these
@@ -64,7 +140,8 @@ cudaError_t LaunchCost(const CostDevice& c, int what, const double* x, double* f
 constexpr int kCostStaticMaxVars = TOWR_B200_STATIC_COST_MAX_VARS;
 constexpr int kCostStaticMaxWeights = TOWR_B200_STATIC_COST_MAX_WEIGHTS;
 constexpr size_t kCostStaticWeightsOff = ((sizeof(int) * (kCostStaticMaxVars + 1)) + 255) & ~static_cast<size_t>(255);
-constexpr size_t kCostStaticBytes = kCostStaticWeightsOff + sizeof(double) * kCostStaticMaxWeights;
+constexpr size_t kCostStaticSampledOff = (kCostStaticWeightsOff + sizeof(double) * kCostStaticMaxWeights + 255) & ~static_cast<size_t>(255);
+constexpr size_t kCostStaticBytes = kCostStaticSampledOff + TOWR_B200_STATIC_COST_MAX_SAMPLED_BYTES;
 static __device__ __align__(256) unsigned char g_cost_static[kCostStaticBytes];
 
 constexpr int kMaxDevices = 64;
@@ -72,12 +149,16 @@ static unsigned char* g_cost_static_addr[kMaxDevices];     // device address of 
 static int g_cost_static_sms[kMaxDevices];
 static std::mutex g_cost_static_mu;
 
-cudaError_t LaunchCostStatic(const CostTables& h, int device, int what, const double* x, double* f, double* grad,
-                             int n_problems, cudaStream_t stream, const char** why) {
+cudaError_t LaunchCostStatic(const CostTables& h, const SampledCost& sc, int device, int what, const double* x, double* f,
+                             double* grad, int n_problems, cudaStream_t stream, const char** why) {
   *why = "";
   if (device < 0 || device >= kMaxDevices) { *why = "device index out of range"; return cudaErrorInvalidDevice; }
   if (h.n_vars > kCostStaticMaxVars || static_cast<int>(h.weights.size()) > kCostStaticMaxWeights) {
     *why = "the class exceeds TOWR_B200_STATIC_COST_MAX_VARS / _MAX_WEIGHTS";
+    return cudaErrorInvalidValue;
+  }
+  if (sc.blob.size() > TOWR_B200_STATIC_COST_MAX_SAMPLED_BYTES) {
+    *why = "the class's EnergyCost / AngularMomentumCost tables exceed TOWR_B200_STATIC_COST_MAX_SAMPLED_BYTES";
     return cudaErrorInvalidValue;
   }
   cudaError_t err = cudaSetDevice(device);
@@ -111,7 +192,13 @@ cudaError_t LaunchCostStatic(const CostTables& h, int device, int what, const do
   c.n_vars = h.n_vars;
   c.col_ptr = col_ptr;
   c.weights = weights;
-  return LaunchCost(c, what, x, f, grad, n_problems, 16 * sms, stream);
+  err = LaunchCost(c, what, x, f, grad, n_problems, 16 * sms, stream);
+  if (err != cudaSuccess || sc.blob.empty()) return err;
+  // the time-discretised terms: tables after the weights, inertia from the class spec (no per-problem constants here)
+  unsigned char* blob = base + kCostStaticSampledOff;
+  err = cudaMemcpyAsync(blob, sc.blob.data(), sc.blob.size(), cudaMemcpyHostToDevice, stream);
+  if (err != cudaSuccess) return err;
+  return LaunchSampledCost(blob, sc.shared_bytes, nullptr, what, x, f, grad, n_problems, sms, stream);
 }
 
 }  // namespace tb

@@ -137,6 +137,9 @@ void SpecDefaults(towr_b200_spec* s) {
   s->dt_constraint_torque = 0.02;
   s->bound_phase_duration[0] = 0.2;
   s->bound_phase_duration[1] = 1.0;
+  s->dt_cost_energy = 0.02;               // parameters.cc:69-71
+  s->energy_cost_torque_weight = 1.0;
+  s->dt_cost_ang_mom = 0.02;
   for (int i = 0; i < 3; ++i)
     s->bounds_final_lin_pos[i] = s->bounds_final_lin_vel[i] = s->bounds_final_ang_pos[i] = s->bounds_final_ang_vel[i] = 1;
 }

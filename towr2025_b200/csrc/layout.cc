@@ -179,10 +179,12 @@ void ValidateSpec(const towr_b200_spec& s) {
   }
   if (s.n_costs < 0 || s.n_costs > TOWR_B200_MAX_COSTS) throw std::runtime_error("bad n_costs");
   for (int c = 0; c < s.n_costs; ++c) {
-    if (s.cost_ids[c] == TOWR_B200_COST_ENERGY || s.cost_ids[c] == TOWR_B200_COST_ANG_MOM)
-      throw std::runtime_error("unsupported: EnergyCost / AngularMomentumCost are not built");
-    if (s.cost_ids[c] != TOWR_B200_COST_FORCES && s.cost_ids[c] != TOWR_B200_COST_EE_MOTION)
+    if (s.cost_ids[c] < TOWR_B200_COST_FORCES || s.cost_ids[c] > TOWR_B200_COST_ANG_MOM)
       throw std::runtime_error("cost not defined!");   // nlp_formulation.cc:644
+    if (s.cost_ids[c] == TOWR_B200_COST_ENERGY && (!std::isfinite(s.dt_cost_energy) || !std::isfinite(s.energy_cost_torque_weight)))
+      throw std::runtime_error("EnergyCost: non-finite dt_cost_energy / energy_cost_torque_weight");
+    if (s.cost_ids[c] == TOWR_B200_COST_ANG_MOM && !std::isfinite(s.dt_cost_ang_mom))
+      throw std::runtime_error("AngularMomentumCost: non-finite dt_cost_ang_mom");
   }
 }
 

@@ -1048,7 +1048,11 @@ std::string StructureSignature(const towr_b200_spec& s, int curvature_dims) {
     << s.torque_polynomials_per_stance_phase;
   for (int i = 0; i < s.n_constraints; ++i)
     if (s.constraints[i] == TOWR_B200_C_TORQUE) o << "|kf" << s.torque_k_friction;   // baked into the class tables
-  for (int c = 0; c < s.n_costs; ++c) o << "|cost" << s.cost_ids[c] << ":" << s.cost_weights[c];   // class-level weight table
+  for (int c = 0; c < s.n_costs; ++c) {                                                            // class-level cost tables
+    o << "|cost" << s.cost_ids[c] << ":" << s.cost_weights[c];
+    if (s.cost_ids[c] == TOWR_B200_COST_ENERGY) o << ":" << s.dt_cost_energy << ":" << s.energy_cost_torque_weight;
+    if (s.cost_ids[c] == TOWR_B200_COST_ANG_MOM) o << ":" << s.dt_cost_ang_mom;
+  }
   return o.str();
 }
 
