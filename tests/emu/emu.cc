@@ -126,6 +126,8 @@ extern "C" int emu_eval(const towr_b200_spec* s, const double* x, double* g, dou
 
 // ---- eval_f / eval_grad_f: the NodeCost column table (cost_kernel.cu CostKernel) and the time-discretised terms
 // (sampled_cost.cuh) replayed serially for one problem
+static inline int atomicMin(int* p, int v) { const int o = *p; if (v < o) *p = v; return o; }
+static inline int atomicMax(int* p, int v) { const int o = *p; if (v > o) *p = v; return o; }
 #include "../../towr2025_b200/csrc/sampled_cost.cuh"
 
 extern "C" int emu_eval_cost(const towr_b200_spec* s, const double* x, double* f_out, double* grad) {
@@ -156,18 +158,30 @@ extern "C" int emu_eval_cost(const towr_b200_spec* s, const double* x, double* f
     FillProblemConst(*s, pc);
     for (int i = 0; i < 6 * H.n_nodes; ++i) SampledNode(V, W, x, i);
     if (H.rt) for (int e = 0; e < H.n_ee; ++e) SampledPhaseDurations(V, W, x, e);
-    for (int poly = 0; poly < H.n_polys; ++poly) SampledPolyDuration(V, W, poly);
-    for (int i = 0; i < 3 * H.n_polys; ++i) SampledCoeff(V, W, i);
-    for (int ti = 0; ti < H.n_terms; ++ti) {
-      const SampledTerm tm = V.terms[ti];
-      for (int it = 0; it < tm.n_splines * tm.n_samples; ++it) SampledItem(V, W, tm, pc.I, it);
-      for (int k = 0; k < tm.n_samples; ++k) SampledSummand(V, W, tm, k);
-      double c = 0.0;
-      for (int k = 0; k < tm.n_samples; ++k) c += W.inst[k];
-      *f_out = *f_out + c;
-      for (int j = 0; j < tm.n_jobs; ++j) SampledJobGradient(V, W, tm, grad, j);
-    }
+    for (int poly = 0; poly < H.n_polys + H.n_phase_slots; ++poly) SampledPolyRecord(V, W, poly);
+    for (int i = 0; i < 3 * H.n_polys + H.n_splines; ++i) SampledCoeff(V, W, i);
+    for (int it = 0; it < H.n_items; ++it) SampledItem(V, W, pc.I, it);
+    for (int k = 0; k < H.n_times; ++k) SampledSummand(V, W, k);
+    for (int q = 0; q < H.n_phase_slots; ++q) SampledPhaseSum(V, W, q);
+    for (int ti = 0; ti < H.n_terms; ++ti) SampledTermSum(V, W, ti);
+    for (int j = 0; j < H.n_jobs; ++j) SampledJobGradient(V, W, grad, j);
+    for (int ti = 0; ti < H.n_terms; ++ti) *f_out = *f_out + W.fterm[ti];
     return 0;
+  } catch (const std::exception& e) {
+    g_err = e.what();
+    return -1;
+  }
+}
+
+// shared memory one CTA of the sampled-cost kernel needs for this class (cost.h: SampledSharedBytes), blob bytes in *blob
+extern "C" long emu_cost_shared_bytes(const towr_b200_spec* s, int* blob) {
+  try {
+    HostProgram hp;
+    BuildProgram(*s, hp);
+    SampledCost sc;
+    BuildSampledCost(hp, *s, sc);
+    if (blob) *blob = static_cast<int>(sc.blob.size());
+    return static_cast<long>(sc.shared_bytes);
   } catch (const std::exception& e) {
     g_err = e.what();
     return -1;

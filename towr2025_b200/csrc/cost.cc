@@ -1,5 +1,6 @@
 // cost.cc — host tables of the cost kernel (cost.h).
 #include "cost.h"
+#include "structure.h"
 
 #include <algorithm>
 #include <cstring>
@@ -68,10 +69,10 @@ void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCos
   std::vector<SampledSpline> splines;
   std::vector<SampledFoot> feet;
   std::vector<SampledJob> jobs;
-  std::vector<uint16_t> node_src, poly_spline;
-  std::vector<double> poly_T, times;
+  std::vector<uint16_t> node_src, poly_spline, fix_seg;
+  std::vector<double> poly_T, times, fix_t;
   std::vector<uint32_t> poly_meta;
-  int n_nodes = 0, n_polys = 0, n_phases = 0;
+  int n_nodes = 0, n_polys = 0, n_phases = 0, n_phase_slots = 0;
   const bool rt = hp.optimize_durations;
   const VarSet* lin = hp.Find(kBaseLin);
   // Spline::GetTotalTime of base_linear_ (helpers/spline.cc:119-123)
@@ -93,6 +94,8 @@ void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCos
     r.foot = foot;
     r.rt = (foot >= 0 && rt) ? 1 : 0;
     r.is_torque = is_torque ? 1 : 0;
+    r.ps0 = n_phase_slots;
+    if (r.rt) n_phase_slots += s.n_phases[foot];
     r.scale = scale;
     r.mscale = mscale;
     std::vector<int> src(static_cast<size_t>(v.n_nodes) * 6, 0xFFFF);
@@ -110,20 +113,26 @@ void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCos
     n_polys += v.n_polys();
     splines.push_back(r);
   };
-  auto node_jobs = [&](const VarSet& v, int spline_in_term) {
+  auto node_jobs = [&](const VarSet& v, int spline_in_term, int term) {
+    // one job per (node, dim): the variables that hold the node's position and velocity value there
+    std::vector<int> col(static_cast<size_t>(v.n_nodes) * 6, -1);
     for (int idx = 0; idx < v.n_vars; ++idx) {
       if (v.refs[idx].size() != 1) throw std::runtime_error("unsupported: a cost variable that writes several node values");
       const NodeRef& nr = v.refs[idx][0];
+      col[nr.node * 6 + nr.deriv * 3 + nr.dim] = v.col0 + idx;
+    }
+    for (int node = 0; node < v.n_nodes; ++node) {
       SampledJob j{};
-      j.col = v.col0 + idx;
-      j.kind = kJobNode;
+      bool any = false;
+      for (int i = 0; i < 6; ++i) { j.col[i] = col[node * 6 + i]; any = any || j.col[i] >= 0; }
+      if (!any) continue;
+      j.kind = static_cast<uint16_t>(kJobNode | (term << 8));
       j.spline = static_cast<uint16_t>(spline_in_term);
-      j.node = static_cast<uint16_t>(nr.node);
-      j.deriv_dim = static_cast<uint16_t>(nr.deriv * 4 + nr.dim);
+      j.node = static_cast<uint16_t>(node);
       jobs.push_back(j);
     }
   };
-  int max_items = 0, max_samples = 0;
+  int n_items = 0, item_doubles = 0;
   for (int c = 0; c < s.n_costs; ++c) {
     const double weight = s.cost_weights[c];
     const bool energy = s.cost_ids[c] == TOWR_B200_COST_ENERGY, ang_mom = s.cost_ids[c] == TOWR_B200_COST_ANG_MOM;
@@ -135,6 +144,10 @@ void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCos
     t.spline0 = static_cast<int>(splines.size());
     t.time0 = static_cast<int>(times.size());
     t.job0 = static_cast<int>(jobs.size());
+    t.item0 = n_items;
+    t.scratch0 = item_doubles;
+    t.rec = energy ? (rt ? 6 : 4) : 8;
+    const int term = static_cast<int>(terms.size());
     t.weight = weight;
     t.dtf = dt > 0.0 ? dt : 1.0;
     const std::vector<double> ts = sample_times(dt);
@@ -148,17 +161,17 @@ void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCos
         const VarSet* vt = hp.Find(kEETorque, e);
         add_spline(*vf, e, false, 1.0, 2.0 * wdt);
         add_spline(*vt, e, true, tw, 2.0 * wdt * tw);
-        node_jobs(*vf, 2 * e);
-        if (tw != 0.0) node_jobs(*vt, 2 * e + 1);              // energy_cost.cc:119
+        node_jobs(*vf, 2 * e, term);
+        if (tw != 0.0) node_jobs(*vt, 2 * e + 1, term);             // energy_cost.cc:119
         if (rt) {                                              // id::EESchedule(ee) exists only then (:129-157)
           const VarSet* vs = hp.Find(kEESchedule, e);
           for (int ph = 0; ph < vs->n_vars; ++ph) {
             SampledJob j{};
-            j.col = vs->col0 + ph;
-            j.kind = kJobSchedule;
+            j.col[0] = vs->col0 + ph;
+            j.kind = static_cast<uint16_t>(kJobSchedule | (term << 8));
             j.spline = static_cast<uint16_t>(2 * e);
             j.node = static_cast<uint16_t>(ph);
-            j.deriv_dim = tw != 0.0 ? 1 : 0;
+            j.aux = tw != 0.0 ? 1 : 0;
             jobs.push_back(j);
           }
         }
@@ -166,15 +179,27 @@ void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCos
     } else {
       const VarSet* va = hp.Find(kBaseAng);
       add_spline(*va, -1, false, 1.0, 2.0 * wdt);
-      node_jobs(*va, 0);
+      node_jobs(*va, 0, term);
     }
     t.n_splines = static_cast<int>(splines.size()) - t.spline0;
     t.n_jobs = static_cast<int>(jobs.size()) - t.job0;
-    max_items = std::max(max_items, t.n_splines * t.n_samples);
-    max_samples = std::max(max_samples, t.n_samples);
+    // fixed durations: segment and local time of every (spline, sample) are class constants (spline.cc:48-78)
+    t.fix0 = splines[t.spline0].rt ? -1 : static_cast<int>(fix_t.size());
+    for (int sidx = t.spline0; t.fix0 >= 0 && sidx < static_cast<int>(splines.size()); ++sidx) {
+      const SampledSpline& sp = splines[sidx];
+      const std::vector<double> d(poly_T.begin() + sp.poly0, poly_T.begin() + sp.poly0 + sp.n_polys);
+      for (double tg : ts) {
+        const int id = SegmentId(tg, d);
+        fix_seg.push_back(static_cast<uint16_t>(id));
+        fix_t.push_back(LocalTime(tg, id, d));
+      }
+    }
+    n_items += t.n_splines * t.n_samples;
+    item_doubles += t.rec * t.n_splines * t.n_samples;
     terms.push_back(t);
   }
   if (terms.empty()) return;
+  if (terms.size() > 8) throw std::runtime_error("unsupported: more than 8 time-discretised cost terms");   // one warp each (cost_kernel.cu)
   for (int e = 0; e < hp.n_ee; ++e) {
     SampledFoot f{};
     f.phase0 = n_phases;
@@ -195,8 +220,9 @@ void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCos
   h.n_phases = n_phases;
   h.n_times = static_cast<int>(times.size());
   h.n_jobs = static_cast<int>(jobs.size());
-  h.max_items = max_items;
-  h.max_samples = max_samples;
+  h.n_phase_slots = n_phase_slots;
+  h.n_items = n_items;
+  h.item_doubles = item_doubles;
   // body inertia as SingleRigidBodyDynamics builds it (single_rigid_body_dynamics.cc:36-44): off-diagonals negated
   const double* in = s.inertia;   // Ixx, Iyy, Izz, Ixy, Ixz, Iyz
   const double I[9] = {in[0], -in[3], -in[4], -in[3], in[1], -in[5], -in[4], -in[5], in[2]};
@@ -212,6 +238,8 @@ void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCos
   h.off_poly_meta = Append(blob, poly_meta);
   h.off_node_src = Append(blob, node_src);
   h.off_poly_spline = Append(blob, poly_spline);
+  h.off_fix_t = Append(blob, fix_t);
+  h.off_fix_seg = Append(blob, fix_seg);
   while (blob.size() % 16) blob.push_back(0);
   h.bytes = static_cast<int>(blob.size());
   std::memcpy(blob.data(), &h, sizeof(h));

@@ -32,25 +32,34 @@ void BuildCostTables(const HostProgram& hp, const towr_b200_spec& s, CostTables&
 // copied to the device once and staged into shared memory by the kernel.
 enum SampledKind { kSampledEnergy = 0, kSampledAngMom = 1 };
 struct SampledTerm {     // one cost term
-  int kind, spline0, n_splines, time0, n_samples, job0, n_jobs, pad;
+  int kind, spline0, n_splines, time0, n_samples, job0, n_jobs;
+  int item0;             // first item (spline, sample) of the term among all terms' items
+  int fix0;              // first entry of the term in fix_t / fix_seg (-1: optimised durations, found at run time)
+  int scratch0;          // first double of the term's item arrays in the kernel's item scratch
+  int rec;               // doubles kept per item: energy 4 (value, local time; 6 with optimised durations), ang-mom 8
   double weight, dtf;    // weight_, (dt_ > 0 ? dt_ : 1)
 };
 struct SampledSpline {   // a spline the term samples (force / torque of a foot, or base-ang)
   int node0, poly0, n_polys, foot, rt, is_torque;
+  int ps0, pad;          // optimised durations: first (spline, phase) slot of the spline (phase sums, sample ranges)
   double scale;          // 1, or torque_weight_ for a torque spline (energy_cost.cc:84)
   double mscale;         // 2 wdt, or 2 wdt torque_weight_ (energy_cost.cc:112,121)
 };
 struct SampledFoot { int phase0, n_phases, col0, pad; double total; };
 enum SampledJobKind { kJobNode = 0, kJobSchedule = 1 };
-struct SampledJob {      // one gradient column
-  int col;
-  uint16_t kind, spline;         // spline: index within the term (kJobSchedule: the foot's force spline; its torque spline
-  uint16_t node, deriv_dim;      //         follows it); kJobNode: node, deriv * 4 + dim; kJobSchedule: node = phase,
-};                               //         deriv_dim = 1 when the torque spline contributes too
+struct SampledJob {      // kJobNode: the columns of one node's values, col[deriv * 3 + dim] (-1: not optimised);
+  int col[6];            // kJobSchedule: col[0] = the ee-schedule column
+  uint16_t kind, spline; // kind: SampledJobKind | term << 8.  spline: index within the term (kJobSchedule: the foot's
+  uint16_t node, aux;    // force spline; its torque spline follows it).  kJobNode: node; kJobSchedule: node = phase,
+};                       // aux = 1 when the torque spline contributes too
 struct SampledHeader {
-  int n_vars, n_ee, rt, n_terms, n_splines, n_nodes, n_polys, n_phases, n_times, n_jobs, max_items, max_samples;
+  int n_vars, n_ee, rt, n_terms, n_splines, n_nodes, n_polys, n_phases, n_times, n_jobs;
+  int n_phase_slots;           // (spline, phase) pairs of the splines with optimised durations
+  int n_items, item_doubles;   // items (spline, sample) of all terms; doubles of their arrays (rec each)
   int off_terms, off_splines, off_feet, off_node_src, off_poly_T, off_poly_meta, off_poly_spline, off_times, off_jobs;
-  int bytes;
+  int off_fix_t, off_fix_seg;  // per item of a term whose splines have class-constant durations (SampledTerm::fix0 + item):
+                               // local time and polynomial (spline.cc:48-78)
+  int bytes;             // all of it is staged in shared memory
   double I[9];           // the class spec's inertia (used when a call has no per-problem constants)
 };
 struct SampledCost {     // host side
@@ -58,12 +67,14 @@ struct SampledCost {     // host side
   size_t shared_bytes = 0;
 };
 constexpr int kSampledRec = 7;   // doubles per node / coefficient record in shared memory (6 used; odd stride, fewer bank conflicts)
+constexpr int kSampledPolyRec = 9;   // doubles per polynomial record (T, T^2, T^3, T^4, their reciprocals, end time)
 constexpr size_t kSampledMaxShared = 200 * 1024;
 inline size_t SampledSharedBytes(const SampledHeader& h) {
   const size_t blob = (static_cast<size_t>(h.bytes) + 15) & ~static_cast<size_t>(15);
-  const size_t doubles = static_cast<size_t>(kSampledRec) * (h.n_nodes + h.n_polys) + h.n_polys + h.n_phases +
-                         8 * static_cast<size_t>(h.max_items) + h.max_samples + 4;
-  return blob + sizeof(double) * doubles + sizeof(int) * static_cast<size_t>(h.max_items);
+  const size_t doubles = static_cast<size_t>(kSampledRec) * (h.n_nodes + h.n_polys) + static_cast<size_t>(kSampledPolyRec) * h.n_polys +
+                         h.n_phases + static_cast<size_t>(h.item_doubles) + h.n_times + 8 + 2 * static_cast<size_t>(h.n_phase_slots);
+  return blob + sizeof(double) * doubles +
+         sizeof(int) * (static_cast<size_t>(h.n_items) + 2 * static_cast<size_t>(h.n_polys) + 2 * static_cast<size_t>(h.n_phase_slots) + 4);
 }
 // throws "unsupported" when a term's samples do not fit one SM's shared memory
 void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCost& out);

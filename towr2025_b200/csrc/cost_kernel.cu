@@ -58,17 +58,26 @@ cudaError_t LaunchCost(const CostDevice& c, int what, const double* x, double* f
 }
 
 // ---- time-discretised cost terms (EnergyCost, AngularMomentumCost): arithmetic in sampled_cost.cuh ------------------
-// One CTA per problem (grid-stride), class tables (cost.h blob) staged in shared memory once per CTA.  Per term:
+// One CTA per problem (grid-stride), class tables (cost.h blob) staged in shared memory once per CTA.  Steps:
 //   1. item = (spline, sample): segment and local time on the problem's own polynomial durations (spline.cc:48-78), the
 //      spline's value there, and what the gradient needs of it (the row vector m of energy_cost.cc:112 / the chain-rule
 //      factors of angular_momentum_cost.cc:144-203);
-//   2. f: thread k forms sample k's summand in the reference's order, one thread adds the samples in time order;
-//   3. gradient: one thread per column walks the samples in time order, like the reference's accumulation into
-//      jac.coeffRef(0, col) over its sample loop.
+//   2. f: one thread per sample forms its summand in the reference's order, one thread per term adds them in time order;
+//   3. gradient: one thread per column walks the samples of the column's two polynomials in time order, like the
+//      reference's accumulation into jac.coeffRef(0, col) over its sample loop.
+// All terms of the class go through each step together (one barrier per step).
 // Adds to f / grad written by CostKernel earlier on the same stream.
 constexpr int kSampledThreads = 256;
 
-__global__ void __launch_bounds__(kSampledThreads)
+// make cost_timing: per-step clocks of CTA 0's first problem (tools/cost_timing.py); not in the product build
+#ifdef TB_COST_TIMING
+__device__ long long g_cost_clocks[16];
+#define TB_COST_CLK(i) do { if (blockIdx.x == 0 && threadIdx.x == 0 && prob == 0) g_cost_clocks[i] = clock64(); } while (0)
+#else
+#define TB_COST_CLK(i) do { } while (0)
+#endif
+
+__global__ void __launch_bounds__(kSampledThreads, 2)
 SampledCostKernel(const unsigned char* __restrict__ blob_g, const ProblemConst* __restrict__ pcs, int what,
                   const double* __restrict__ x, double* __restrict__ f_out, double* __restrict__ grad_out, int n_problems) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -82,34 +91,46 @@ SampledCostKernel(const unsigned char* __restrict__ blob_g, const ProblemConst* 
   const SampledWork W = SampledCarve(H, smem + ((H.bytes + 15) & ~15));
   for (int prob = blockIdx.x; prob < n_problems; prob += gridDim.x) {
     const double* xp = x + static_cast<size_t>(prob) * H.n_vars;
+    TB_COST_CLK(0);
+#pragma unroll 4
     for (int i = tid; i < 6 * H.n_nodes; i += kSampledThreads) SampledNode(V, W, xp, i);
     if (H.rt && tid < H.n_ee) SampledPhaseDurations(V, W, xp, tid);
     __syncthreads();
-    for (int poly = tid; poly < H.n_polys; poly += kSampledThreads) SampledPolyDuration(V, W, poly);
+    TB_COST_CLK(1);
+    for (int poly = tid; poly < H.n_polys + H.n_phase_slots; poly += kSampledThreads) SampledPolyRecord(V, W, poly);
     __syncthreads();
-    for (int i = tid; i < 3 * H.n_polys; i += kSampledThreads) SampledCoeff(V, W, i);
+    TB_COST_CLK(2);
+    for (int i = tid; i < 3 * H.n_polys + H.n_splines; i += kSampledThreads) SampledCoeff(V, W, i);
     __syncthreads();
+    TB_COST_CLK(3);
     double I[9];
 #pragma unroll
     for (int i = 0; i < 9; ++i) I[i] = pcs ? __ldg(&pcs[prob].I[i]) : H.I[i];
-    for (int ti = 0; ti < H.n_terms; ++ti) {
-      const SampledTerm tm = V.terms[ti];
-      for (int it = tid; it < tm.n_splines * tm.n_samples; it += kSampledThreads) SampledItem(V, W, tm, I, it);
-      __syncthreads();
-      if (what & 1) {
-        for (int k = tid; k < tm.n_samples; k += kSampledThreads) SampledSummand(V, W, tm, k);
-        __syncthreads();
-        if (tid == 0) {
-          double c = 0.0;
-          for (int k = 0; k < tm.n_samples; ++k) c += W.inst[k];   // cost += ... over the samples in time order
-          f_out[prob] = f_out[prob] + c;
-        }
-      }
-      if (what & 2) {
-        double* gp = grad_out + static_cast<size_t>(prob) * H.n_vars;
-        for (int j = tid; j < tm.n_jobs; j += kSampledThreads) SampledJobGradient(V, W, tm, gp, j);
-      }
-      __syncthreads();
+    for (int it = tid; it < H.n_items; it += kSampledThreads) SampledItem(V, W, I, it);
+    __syncthreads();
+    TB_COST_CLK(4);
+    // summands (threads from the front) and, for the ee-schedule gradient, phase sums (threads from the back)
+    if (what & 1)
+      for (int k = tid; k < H.n_times; k += kSampledThreads) SampledSummand(V, W, k);
+    if (what & 2)
+      for (int q = kSampledThreads - 1 - tid; q < H.n_phase_slots; q += kSampledThreads) SampledPhaseSum(V, W, q);
+    __syncthreads();
+    TB_COST_CLK(5);
+    // one thread per term adds its samples in time order: the last lanes of the last warps, which have the fewest jobs
+    if ((what & 1) && (tid & 31) == 31 && (kSampledThreads / 32 - 1 - (tid >> 5)) < H.n_terms)
+      SampledTermSum(V, W, kSampledThreads / 32 - 1 - (tid >> 5));
+    TB_COST_CLK(6);
+    if (what & 2) {
+      double* gp = grad_out + static_cast<size_t>(prob) * H.n_vars;
+      for (int j = tid; j < H.n_jobs; j += kSampledThreads) SampledJobGradient(V, W, gp, j);
+    }
+    TB_COST_CLK(7);
+    __syncthreads();
+    TB_COST_CLK(8);
+    if ((what & 1) && tid == 0) {
+      double f = f_out[prob];
+      for (int ti = 0; ti < H.n_terms; ++ti) f = f + W.fterm[ti];   // the terms in the order of params_.costs_
+      f_out[prob] = f;
     }
   }
 }
@@ -202,3 +223,9 @@ cudaError_t LaunchCostStatic(const CostTables& h, const SampledCost& sc, int dev
 }
 
 }  // namespace tb
+
+#ifdef TB_COST_TIMING
+extern "C" int tb_cost_clocks(long long* out) {
+  return cudaMemcpyFromSymbol(out, tb::g_cost_clocks, sizeof(long long) * 16) == cudaSuccess ? 0 : -1;
+}
+#endif

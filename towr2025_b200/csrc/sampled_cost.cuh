@@ -19,18 +19,9 @@ struct SampledView {
   const uint32_t* poly_meta;
   const uint16_t* node_src;
   const uint16_t* poly_spline;
+  const double* fix_t;
+  const uint16_t* fix_seg;
 };
-
-// d (pos | vel)(t) / d (node value) of a cubic Hermite polynomial (polynomial.cc:106-234); side 0 start, 1 end
-__device__ __forceinline__ double HermiteWeight(int dxdt, int side, int deriv, double t, double T) {
-  const double t2 = t * t, t3 = Cube(t), T2 = T * T, T3 = Cube(T);
-  if (dxdt == 0) {
-    if (side == 0) return deriv == 0 ? (2 * t3) / T3 - (3 * t2) / T2 + 1 : t - (2 * t2) / T + t3 / T2;
-    return deriv == 0 ? (3 * t2) / T2 - (2 * t3) / T3 : t3 / T2 - t2 / T;
-  }
-  if (side == 0) return deriv == 0 ? (6 * t2) / T3 - (6 * t) / T2 : (3 * t2) / T2 - (4 * t) / T + 1;
-  return deriv == 0 ? (6 * t) / T2 - (6 * t2) / T3 : (3 * t2) / T2 - (2 * t) / T;
-}
 
 __device__ __forceinline__ void Mat3Mul(const double A[9], const double B[9], double C[9]) {
 #pragma unroll
@@ -43,9 +34,42 @@ __device__ __forceinline__ double Dot3(const double a[3], const double b[3]) { r
 
 // shared-memory work arrays of one CTA (one problem at a time), carved by SampledCarve
 struct SampledWork {
-  double *nodes, *coef, *pT, *pdur, *itl, *im, *ix, *ie, *inst;
-  int* iseg;             // per item: polynomial within the spline | phase << 16
+  double *nodes, *coef, *prec, *pdur, *items, *inst, *fterm, *psum;
+  int *iseg, *k0, *k1;   // iseg per item: polynomial within the spline | phase << 16; k0 / k1 per polynomial: its samples
+  int *pk0, *pk1;        // per (spline, phase) slot: the samples that fall into the phase
 };
+// per-polynomial record (kSampledPolyRec doubles): T, T^2, T^3, T^4, their correctly rounded reciprocals (ExactDiv) and,
+// for optimised durations, the polynomial's end time within its spline (accumulated like Spline::GetSegmentID's `t += d`)
+enum { kPrT = 0, kPrT2, kPrT3, kPrR1, kPrR2, kPrR3, kPrR4, kPrT4, kPrEnd };
+
+// the item arrays of one term (N = n_splines * n_samples items, tm.rec doubles each):
+//   energy:  P[3N] the spline's value, t[N] local time, with optimised durations also AB[2N] = m . dx/dT, m . vel
+//   ang-mom: P[3N] d summand / d euler angle, t[N], X[3N] d summand / d euler rate, e[N] |L|^2
+struct SampledTermArrays { double *P, *t, *X; };
+__device__ __forceinline__ SampledTermArrays TermArrays(const SampledWork& W, const SampledTerm& tm) {
+  const int N = tm.n_splines * tm.n_samples;
+  SampledTermArrays A;
+  A.P = W.items + tm.scratch0;
+  A.t = A.P + 3 * N;
+  A.X = A.t + N;
+  return A;
+}
+
+// d (pos | vel)(t) / d (node value) of a cubic Hermite polynomial (polynomial.cc:106-234) from the polynomial's record;
+// side 0 start node, 1 end node; deriv: the node's position or velocity
+__device__ __forceinline__ double HermiteWeight(int dxdt, int side, int deriv, double t, const double* q) {
+  const double T = q[kPrT], T2 = q[kPrT2], T3 = q[kPrT3], r1 = q[kPrR1], r2 = q[kPrR2], r3 = q[kPrR3];
+  const double t2 = t * t;
+  if (dxdt == 0) {
+    const double t3 = Cube(t);
+    if (side == 0)
+      return deriv == 0 ? ExactDiv(2 * t3, T3, r3) - ExactDiv(3 * t2, T2, r2) + 1 : t - ExactDiv(2 * t2, T, r1) + ExactDiv(t3, T2, r2);
+    return deriv == 0 ? ExactDiv(3 * t2, T2, r2) - ExactDiv(2 * t3, T3, r3) : ExactDiv(t3, T2, r2) - ExactDiv(t2, T, r1);
+  }
+  if (side == 0)
+    return deriv == 0 ? ExactDiv(6 * t2, T3, r3) - ExactDiv(6 * t, T2, r2) : ExactDiv(3 * t2, T2, r2) - ExactDiv(4 * t, T, r1) + 1;
+  return deriv == 0 ? ExactDiv(6 * t, T2, r2) - ExactDiv(6 * t2, T3, r3) : ExactDiv(3 * t2, T2, r2) - ExactDiv(2 * t, T, r1);
+}
 
 __device__ __forceinline__ SampledView MakeSampledView(const unsigned char* blob) {
   SampledView V;
@@ -60,6 +84,8 @@ __device__ __forceinline__ SampledView MakeSampledView(const unsigned char* blob
   V.poly_meta = reinterpret_cast<const uint32_t*>(blob + H.off_poly_meta);
   V.node_src = reinterpret_cast<const uint16_t*>(blob + H.off_node_src);
   V.poly_spline = reinterpret_cast<const uint16_t*>(blob + H.off_poly_spline);
+  V.fix_t = reinterpret_cast<const double*>(blob + H.off_fix_t);
+  V.fix_seg = reinterpret_cast<const uint16_t*>(blob + H.off_fix_seg);
   return V;
 }
 
@@ -68,24 +94,27 @@ __device__ __forceinline__ SampledWork SampledCarve(const SampledHeader& H, unsi
   SampledWork W;
   W.nodes = reinterpret_cast<double*>(base);
   W.coef = W.nodes + kSampledRec * H.n_nodes;            // c[3], d[3] of every polynomial (polynomial.cc:97-104)
-  W.pT = W.coef + kSampledRec * H.n_polys;
-  W.pdur = W.pT + H.n_polys;
-  W.itl = W.pdur + H.n_phases;                           // per item: local time
-  W.im = W.itl + H.max_items;                            //   3: energy m(r) / ang-mom d cost / d euler angle
-  W.ix = W.im + 3 * H.max_items;                         //   3: energy (m . dx/dT, m . vel, -) / ang-mom d cost / d euler rate
-  W.ie = W.ix + 3 * H.max_items;                         //   squared norm
-  W.inst = W.ie + H.max_items;                           // per sample: the summand of f
-  W.iseg = reinterpret_cast<int*>(W.inst + H.max_samples + 4);
+  W.prec = W.coef + kSampledRec * H.n_polys;
+  W.pdur = W.prec + kSampledPolyRec * H.n_polys;
+  W.items = W.pdur + H.n_phases;
+  W.inst = W.items + H.item_doubles;                     // per sample of every term: the summand of f
+  W.fterm = W.inst + H.n_times;
+  W.psum = W.fterm + 8;                                  // per (spline, phase) slot: sum of m . dx/dT, sum of m . vel
+  W.iseg = reinterpret_cast<int*>(W.psum + 2 * H.n_phase_slots);
+  W.k0 = W.iseg + H.n_items;
+  W.k1 = W.k0 + H.n_polys;
+  W.pk0 = W.k1 + H.n_polys;
+  W.pk1 = W.pk0 + H.n_phase_slots;
   return W;
 }
 
-// ---- set-up of one problem; a barrier separates the four steps
-// node value i of 6 * n_nodes (nodes_variables.cc:68-76)
+// ---- set-up of one problem; a barrier separates the three steps
+// step A: node value i of 6 * n_nodes (nodes_variables.cc:68-76) ...
 __device__ __forceinline__ void SampledNode(const SampledView& V, const SampledWork& W, const double* __restrict__ xp, int i) {
   const unsigned src = V.node_src[i];
   W.nodes[(i / 6) * kSampledRec + i % 6] = src != 0xFFFFu ? __ldg(xp + src) : 0.0;
 }
-// phase durations of foot e (phase_durations.cc:78-100), optimised durations only
+// ... and the phase durations of foot e (phase_durations.cc:78-100), optimised durations only
 __device__ __forceinline__ void SampledPhaseDurations(const SampledView& V, const SampledWork& W, const double* __restrict__ xp, int e) {
   const SampledFoot ft = V.feet[e];
   double sum = 0.0;
@@ -96,88 +125,137 @@ __device__ __forceinline__ void SampledPhaseDurations(const SampledView& V, cons
   }
   W.pdur[ft.phase0 + ft.n_phases - 1] = ft.total - sum;
 }
-// polynomial durations (nodes_variables_phase_based.cc:75-86)
-__device__ __forceinline__ void SampledPolyDuration(const SampledView& V, const SampledWork& W, int poly) {
+// step B, poly in [0, n_polys + n_phase_slots): polynomial durations (nodes_variables_phase_based.cc:75-86), their powers
+// and reciprocals; the last indices clear the phase slots' sample ranges
+__device__ __forceinline__ void SampledPolyRecord(const SampledView& V, const SampledWork& W, int poly) {
+  if (poly >= V.h->n_polys) {
+    W.pk0[poly - V.h->n_polys] = 0x7FFFFFFF;
+    W.pk1[poly - V.h->n_polys] = 0;
+    return;
+  }
   const uint32_t pm = V.poly_meta[poly];
-  W.pT[poly] = pm == kPolyFixed ? V.poly_T[poly]
-                                : W.pdur[V.feet[V.splines[V.poly_spline[poly]].foot].phase0 + (pm & 0xFF)] /
-                                      static_cast<double>((pm >> 8) & 0xFF);
+  const double T = pm == kPolyFixed ? V.poly_T[poly]
+                                    : W.pdur[V.feet[V.splines[V.poly_spline[poly]].foot].phase0 + (pm & 0xFF)] /
+                                          static_cast<double>((pm >> 8) & 0xFF);
+  double* q = W.prec + kSampledPolyRec * poly;
+  const double T2 = T * T, T3 = Cube(T), T4 = Pow4(T);
+  q[kPrT] = T; q[kPrT2] = T2; q[kPrT3] = T3; q[kPrT4] = T4;
+  q[kPrR1] = 1.0 / T; q[kPrR2] = 1.0 / T2; q[kPrR3] = 1.0 / T3; q[kPrR4] = 1.0 / T4;
+  W.k0[poly] = 0x7FFFFFFF;
+  W.k1[poly] = 0;
 }
-// Hermite coefficients c, d of (polynomial, dim) i (polynomial.cc:97-104)
+// step C, i in [0, 3 n_polys + n_splines): Hermite coefficients c, d of (polynomial, dim) i (polynomial.cc:97-104); the
+// last n_splines indices: end times of a spline's polynomials (optimised durations)
 __device__ __forceinline__ void SampledCoeff(const SampledView& V, const SampledWork& W, int i) {
+  if (i >= 3 * V.h->n_polys) {
+    const SampledSpline& sp = V.splines[i - 3 * V.h->n_polys];
+    if (!sp.rt) return;
+    double acc = 0.0;
+    for (int j = 0; j < sp.n_polys; ++j) {
+      double* q = W.prec + kSampledPolyRec * (sp.poly0 + j);
+      acc += q[kPrT];
+      q[kPrEnd] = acc;
+    }
+    return;
+  }
   const int poly = i / 3, d = i - 3 * poly;
   const SampledSpline& sp = V.splines[V.poly_spline[poly]];
   const double* n0 = W.nodes + kSampledRec * (sp.node0 + (poly - sp.poly0));
   const double p0 = n0[d], v0 = n0[3 + d], p1 = n0[kSampledRec + d], v1 = n0[kSampledRec + 3 + d];
-  const double T = W.pT[poly], T2 = T * T, T3 = Cube(T);
-  W.coef[kSampledRec * poly + d] = -(3.0 * (p0 - p1) + T * (2.0 * v0 + v1)) / T2;
-  W.coef[kSampledRec * poly + 3 + d] = (2.0 * (p0 - p1) + T * (v0 + v1)) / T3;
+  const double* q = W.prec + kSampledPolyRec * poly;
+  const double T = q[kPrT];
+  W.coef[kSampledRec * poly + d] = ExactDiv(-(3.0 * (p0 - p1) + T * (2.0 * v0 + v1)), q[kPrT2], q[kPrR2]);
+  W.coef[kSampledRec * poly + 3 + d] = ExactDiv(2.0 * (p0 - p1) + T * (v0 + v1), q[kPrT3], q[kPrR3]);
 }
 
-// ---- step 1: item `it` = (spline, sample) of term tm; I: the problem's body inertia
-__device__ __forceinline__ void SampledItem(const SampledView& V, const SampledWork& W, const SampledTerm& tm, const double I[9], int it) {
-  const SampledHeader& H = *V.h;
-  double *nodes = W.nodes, *coef = W.coef, *pT = W.pT, *pdur = W.pdur, *itl = W.itl, *im = W.im, *ix = W.ix, *ie = W.ie;
-  int* iseg = W.iseg;
+// the term an index of a concatenated per-term range belongs to (items, samples, jobs)
+__device__ __forceinline__ int TermOfItem(const SampledView& V, int it) {
+  int ti = 0;
+  while (ti + 1 < V.h->n_terms && it >= V.terms[ti + 1].item0) ++ti;
+  return ti;
+}
+__device__ __forceinline__ int TermOfSample(const SampledView& V, int k) {
+  int ti = 0;
+  while (ti + 1 < V.h->n_terms && k >= V.terms[ti + 1].time0) ++ti;
+  return ti;
+}
+
+// ---- step 1: item `git` (all terms) = (spline, sample) of a term; I: the problem's body inertia
+__device__ __forceinline__ void SampledItem(const SampledView& V, const SampledWork& W, const double I[9], int git) {
+  const SampledTerm& tm = V.terms[TermOfItem(V, git)];
+  const SampledTermArrays A = TermArrays(W, tm);
+  const int it = git - tm.item0;
   const int K = tm.n_samples;
-  const double wdt = tm.weight * tm.dtf;
-  (void)H; (void)pdur; (void)wdt;
   const int s = it / K, k = it - s * K;
   const SampledSpline& sp = V.splines[tm.spline0 + s];
   const double tg = V.times[tm.time0 + k];
-  int id = sp.n_polys - 1;                         // Spline::GetSegmentID / GetLocalTime (spline.cc:48-78)
-  double acc = 0.0;
-  for (int j = 0; j < sp.n_polys; ++j) {
-    acc += pT[sp.poly0 + j];
-    if (acc >= tg - 1e-10) { id = j; break; }
+  int id;                                            // Spline::GetSegmentID / GetLocalTime (spline.cc:48-78)
+  double t;
+  if (!sp.rt) {                                      // class constants
+    id = V.fix_seg[tm.fix0 + it];
+    t = V.fix_t[tm.fix0 + it];
+  } else {                                           // on the problem's own durations
+    const double* pr = W.prec + kSampledPolyRec * sp.poly0;
+    const double lim = tg - 1e-10;
+    id = sp.n_polys - 1;
+#pragma unroll 4
+    for (int j = 0; j < sp.n_polys; ++j)
+      if (pr[j * kSampledPolyRec + kPrEnd] >= lim) { id = j; break; }
+    t = tg;
+    for (int j = 0; j < id; ++j) t -= pr[j * kSampledPolyRec];
   }
-  double t = tg;
-  for (int j = 0; j < id; ++j) t -= pT[sp.poly0 + j];
   const int poly = sp.poly0 + id;
+  atomicMin(W.k0 + poly, k);                         // the polynomial's samples are k0 .. k1 - 1 (time order)
+  atomicMax(W.k1 + poly, k + 1);
+  const double* q = W.prec + kSampledPolyRec * poly;
   const double t2 = t * t, t3 = Cube(t);
-  const double* n0 = nodes + kSampledRec * (sp.node0 + id);
+  const double* n0 = W.nodes + kSampledRec * (sp.node0 + id);
   double pos[3], vel[3];
 #pragma unroll
-  for (int d = 0; d < 3; ++d) {                    // Polynomial::GetPoint (polynomial.cc:47-61)
-    const double a = n0[d], b = n0[3 + d], c = coef[kSampledRec * poly + d], dd = coef[kSampledRec * poly + 3 + d];
+  for (int d = 0; d < 3; ++d) {                      // Polynomial::GetPoint (polynomial.cc:47-61)
+    const double a = n0[d], b = n0[3 + d], c = W.coef[kSampledRec * poly + d], dd = W.coef[kSampledRec * poly + 3 + d];
     pos[d] = ((a + t * b) + t2 * c) + t3 * dd;
     vel[d] = (b + (2 * t) * c) + (3 * t2) * dd;
   }
+  A.t[it] = t;
   int phase = 0;
-  itl[it] = t;
   if (tm.kind == kSampledEnergy) {
-    ie[it] = Dot3(pos, pos);                       // squaredNorm (energy_cost.cc:84)
-    double m[3];
 #pragma unroll
-    for (int d = 0; d < 3; ++d) { m[d] = sp.mscale * pos[d]; im[3 * it + d] = m[d]; }   // :112, :121
+    for (int d = 0; d < 3; ++d) A.P[3 * it + d] = pos[d];
     if (sp.rt) {
+      double m[3];
+#pragma unroll
+      for (int d = 0; d < 3; ++d) m[d] = sp.mscale * pos[d];   // energy_cost.cc:112, :121
       // PhaseSpline::GetJacobianOfPosWrtDurations (phase_spline.cc:67-93): dx/dT of the active polynomial
       // (polynomial.cc:236-257) through its share of the phase, and the phase the global time falls into
       const uint32_t pm = V.poly_meta[poly];
       const int nin = (pm >> 8) & 0xFF, prev = (pm >> 16) & 0xFF;
-      const double T = pT[poly], T2 = T * T, T3 = Cube(T), T4 = Pow4(T);
+      const double T = q[kPrT], T2 = q[kPrT2], T3 = q[kPrT3], T4 = q[kPrT4], r2 = q[kPrR2], r3 = q[kPrR3], r4 = q[kPrR4];
       const double inner = 1.0 / nin;
       double dxdT[3];
 #pragma unroll
       for (int d = 0; d < 3; ++d) {
         const double x0 = n0[d], v0 = n0[3 + d], x1 = n0[kSampledRec + d], v1 = n0[kSampledRec + 3 + d];
-        const double dx = (((t3 * (v0 + v1)) / T3 - (t2 * (2.0 * v0 + v1)) / T2) -
-                           ((3 * t3) * (((2.0 * x0 - 2.0 * x1) + T * v0) + T * v1)) / T4) +
-                          ((2 * t2) * (((3.0 * x0 - 3.0 * x1) + (2 * T) * v0) + T * v1)) / T3;
+        const double dx = ((ExactDiv(t3 * (v0 + v1), T3, r3) - ExactDiv(t2 * (2.0 * v0 + v1), T2, r2)) -
+                           ExactDiv((3 * t3) * (((2.0 * x0 - 2.0 * x1) + T * v0) + T * v1), T4, r4)) +
+                          ExactDiv((2 * t2) * (((3.0 * x0 - 3.0 * x1) + (2 * T) * v0) + T * v1), T3, r3);
         dxdT[d] = inner * (dx - prev * vel[d]);
       }
       const SampledFoot ft = V.feet[sp.foot];
       phase = ft.n_phases - 1;
       double pacc = 0.0;
       for (int j = 0; j < ft.n_phases; ++j) {
-        pacc += pdur[ft.phase0 + j];
+        pacc += W.pdur[ft.phase0 + j];
         if (pacc >= tg - 1e-10) { phase = j; break; }
       }
-      ix[3 * it] = Dot3(m, dxdT);
-      ix[3 * it + 1] = Dot3(m, vel);
+      A.X[2 * it] = Dot3(m, dxdT);
+      A.X[2 * it + 1] = Dot3(m, vel);
+      atomicMin(W.pk0 + sp.ps0 + phase, k);           // the phase's samples are pk0 .. pk1 - 1 (time order)
+      atomicMax(W.pk1 + sp.ps0 + phase, k + 1);
     }
   } else {
     // AngularMomentumCost (angular_momentum_cost.cc:67-101, 103-206): L = R I_b R^T omega, omega = M(euler) euler_rate
+    const double wdt = tm.weight * tm.dtf;
     const Trig tr = MakeTrig(pos);
     double R[9], RI[9], Rt[9], Iw[9];
     RotationMatrix(tr, R);
@@ -194,12 +272,16 @@ __device__ __forceinline__ void SampledItem(const SampledView& V, const SampledW
     omega[1] = Mm[3] * vel[0] + Mm[4] * vel[1];
     omega[2] = Mm[6] * vel[0] + vel[2];
     MatVec3(Iw, omega, L);
-    ie[it] = Dot3(L, L);
-    double m[3], u[3], v2[3];
+    A.X[3 * tm.n_samples + it] = Dot3(L, L);
+    double m[3], u[3], v2[3], mRI[3], mIw[3];
 #pragma unroll
     for (int d = 0; d < 3; ++d) m[d] = (2.0 * wdt) * L[d];
     MatTVec3(R, omega, u);
     MatVec3(I, u, v2);
+    // m . (R I_b q) = (m^T R I_b) . q and m . (I_w c) = (m^T I_w) . c: the row vectors once per sample instead of a
+    // 3 x n product per Jacobian (angular_momentum_cost.cc:196-203 forms J2 = R (I_b term_u), then m * J2)
+    MatTVec3(RI, m, mRI);
+    MatTVec3(Iw, m, mIw);
     // d omega / d euler_j = (dM / d euler_j) euler_rate  (euler_converter.cc:168-198)
     const double dw[3][3] = {
         {0.0, 0.0, 0.0},
@@ -207,80 +289,133 @@ __device__ __forceinline__ void SampledItem(const SampledView& V, const SampledW
         {-tr.cy * tr.sz * vel[0] - tr.cz * vel[1], tr.cy * tr.cz * vel[0] - tr.sz * vel[1], 0.0}};
 #pragma unroll
     for (int j = 0; j < 3; ++j) {
-      double D[9], a1[3], a2[3], a3[3], q[3], Iq[3], dL[3], col[3];
+      double D[9], a1[3], a2[3], a3[3], qv[3], col[3];
       RotationMatrixDeriv(tr, j, D);
-      MatVec3(D, v2, a1);                          // d(R v2)/d euler_j at fixed v2      (:170, J_R_v2)
-      MatTVec3(D, omega, a2);                      // d(R^T omega)/d euler_j at fixed omega (:171, term_a)
-      MatTVec3(R, dw[j], a3);                      // R^T d omega / d euler_j             (term_b)
+      MatVec3(D, v2, a1);                            // d(R v2)/d euler_j at fixed v2      (:170, J_R_v2)
+      MatTVec3(D, omega, a2);                        // d(R^T omega)/d euler_j at fixed omega (:171, term_a)
+      MatTVec3(R, dw[j], a3);                        // R^T d omega / d euler_j             (term_b)
 #pragma unroll
-      for (int d = 0; d < 3; ++d) q[d] = a2[d] + a3[d];
-      MatVec3(I, q, Iq);
-      MatVec3(R, Iq, dL);                          // J2 = R (I_b term_u)
-      im[3 * it + j] = Dot3(m, a1) + Dot3(m, dL);
+      for (int d = 0; d < 3; ++d) qv[d] = a2[d] + a3[d];
+      A.P[3 * it + j] = Dot3(m, a1) + Dot3(mRI, qv);
       col[0] = Mm[j]; col[1] = Mm[3 + j]; col[2] = Mm[6 + j];   // d omega / d euler_rate_j
-      MatTVec3(R, col, a3);
-      MatVec3(I, a3, Iq);
-      MatVec3(R, Iq, dL);
-      ix[3 * it + j] = Dot3(m, dL);
+      A.X[3 * it + j] = Dot3(mIw, col);
     }
   }
-  iseg[it] = id | (phase << 16);
+  W.iseg[git] = id | (phase << 16);
 }
 
-// ---- step 2: the summand of sample k (energy_cost.cc:80-87, angular_momentum_cost.cc:97)
-__device__ __forceinline__ void SampledSummand(const SampledView& V, const SampledWork& W, const SampledTerm& tm, int k) {
-  const double* ie = W.ie;
-  double* inst = W.inst;
-  const int K = tm.n_samples;
-  const double wdt = tm.weight * tm.dtf;
+// ---- step 2b: phase slot `slot` of a spline with optimised durations: the sums of m . dx/dT and m . vel over the samples
+// of the phase, in time order.  PhaseDurations::GetJacobianOfPos (phase_durations.cc:126-154) gives column ph of the
+// ee-schedule +dx/dT for the samples of phase ph and -vel for those of every later phase (-vel - dx/dT in the last one).
+__device__ __forceinline__ void SampledPhaseSum(const SampledView& V, const SampledWork& W, int slot) {
+  int si = 0;
+  while (si + 1 < V.h->n_splines && (!V.splines[si].rt || slot >= V.splines[si].ps0 + V.feet[V.splines[si].foot].n_phases)) ++si;
+  int ti = 0;
+  while (ti + 1 < V.h->n_terms && si >= V.terms[ti + 1].spline0) ++ti;
+  const SampledTerm& tm = V.terms[ti];
+  const SampledTermArrays A = TermArrays(W, tm);
+  const int s = si - tm.spline0, K = tm.n_samples;
+  double sa = 0.0, sb = 0.0;
+  for (int k = W.pk0[slot]; k < W.pk1[slot]; ++k) {
+    sa += A.X[2 * (s * K + k)];
+    sb += A.X[2 * (s * K + k) + 1];
+  }
+  W.psum[2 * slot] = sa;
+  W.psum[2 * slot + 1] = sb;
+}
+
+// ---- step 2: the summand of sample `gk` (all terms; energy_cost.cc:80-87, angular_momentum_cost.cc:97)
+__device__ __forceinline__ void SampledSummand(const SampledView& V, const SampledWork& W, int gk) {
+  const SampledTerm& tm = V.terms[TermOfSample(V, gk)];
+  const SampledTermArrays A = TermArrays(W, tm);
+  const int K = tm.n_samples, k = gk - tm.time0;
   double v;
   if (tm.kind == kSampledEnergy) {
     double in = 0.0;
-    for (int e = 0; e < tm.n_splines / 2; ++e)   // inst += f.squaredNorm() + torque_weight_*tau.squaredNorm()  (:84)
-      in += ie[(2 * e) * K + k] + V.splines[tm.spline0 + 2 * e + 1].scale * ie[(2 * e + 1) * K + k];
-    v = tm.weight * in * tm.dtf;                 // :87
+    for (int e = 0; e < tm.n_splines / 2; ++e) {     // inst += f.squaredNorm() + torque_weight_*tau.squaredNorm()  (:84)
+      const double* f = A.P + 3 * ((2 * e) * K + k);
+      const double* tau = A.P + 3 * ((2 * e + 1) * K + k);
+      in += Dot3(f, f) + V.splines[tm.spline0 + 2 * e + 1].scale * Dot3(tau, tau);
+    }
+    v = tm.weight * in * tm.dtf;                     // :87
   } else {
-    v = wdt * ie[k];                             // angular_momentum_cost.cc:97
+    v = (tm.weight * tm.dtf) * A.X[3 * K + k];       // angular_momentum_cost.cc:97
   }
-  inst[k] = v;
+  W.inst[gk] = v;
+}
+// f of term ti: the samples added in time order
+__device__ __forceinline__ void SampledTermSum(const SampledView& V, const SampledWork& W, int ti) {
+  const SampledTerm& tm = V.terms[ti];
+  double c = 0.0;
+  for (int k = 0; k < tm.n_samples; ++k) c += W.inst[tm.time0 + k];
+  W.fterm[ti] = c;
 }
 
-// ---- step 3: gradient column of job j, added to gp (the problem's dense gradient)
-__device__ __forceinline__ void SampledJobGradient(const SampledView& V, const SampledWork& W, const SampledTerm& tm, double* __restrict__ gp, int j) {
-  const double *pT = W.pT, *itl = W.itl, *im = W.im, *ix = W.ix;
-  const int* iseg = W.iseg;
+// ---- step 3: gradient columns of job j (all terms), added to gp (the problem's dense gradient)
+__device__ __forceinline__ void SampledJobGradient(const SampledView& V, const SampledWork& W, double* __restrict__ gp, int j) {
+  const SampledJob jb = V.jobs[j];
+  const SampledTerm& tm = V.terms[jb.kind >> 8];
+  const SampledTermArrays A = TermArrays(W, tm);
   const int K = tm.n_samples;
-  const SampledJob jb = V.jobs[tm.job0 + j];
-  double g = 0.0;
-  if (jb.kind == kJobNode) {
-    const int s = jb.spline, node = jb.node, deriv = jb.deriv_dim >> 2, dim = jb.deriv_dim & 3;
+  if ((jb.kind & 0xFF) == kJobNode) {
+    // the samples of the two polynomials that meet in the node, in time order: the reference's accumulation into
+    // jac.coeffRef(0, col) over its sample loop.  gpos / gvel: the columns of the node's position / velocity values
+    const int s = jb.spline, node = jb.node;
     const SampledSpline& sp = V.splines[tm.spline0 + s];
-    for (int k = 0; k < K; ++k) {
-      const int it = s * K + k;
-      const int id = iseg[it] & 0xFFFF;
-      if (id != node && id + 1 != node) continue;
-      const int side = id == node ? 0 : 1;
-      const double t = itl[it], T = pT[sp.poly0 + id];
-      if (tm.kind == kSampledEnergy)
-        g += im[3 * it + dim] * HermiteWeight(0, side, deriv, t, T);
-      else
-        g += im[3 * it + dim] * HermiteWeight(0, side, deriv, t, T) + ix[3 * it + dim] * HermiteWeight(1, side, deriv, t, T);
+    double gpos[3] = {0.0, 0.0, 0.0}, gvel[3] = {0.0, 0.0, 0.0};
+    for (int side = 1; side >= 0; --side) {          // end node of polynomial node-1, then start node of polynomial node
+      const int id = node - side;
+      if (id < 0 || id >= sp.n_polys) continue;
+      const int ka = W.k0[sp.poly0 + id], kb = W.k1[sp.poly0 + id];
+      const double* q = W.prec + kSampledPolyRec * (sp.poly0 + id);
+      const double T = q[kPrT], T2 = q[kPrT2], T3 = q[kPrT3], r1 = q[kPrR1], r2 = q[kPrR2], r3 = q[kPrR3];
+      for (int k = ka; k < kb; ++k) {
+        const int it = s * K + k;
+        const double t = A.t[it], t2 = t * t, t3 = Cube(t);
+        // d pos / d (node position, node velocity)  (polynomial.cc:106-160, kPos)
+        const double a = ExactDiv(2 * t3, T3, r3), b = ExactDiv(3 * t2, T2, r2), d = ExactDiv(t3, T2, r2);
+        const double wp = side == 0 ? a - b + 1 : b - a;
+        const double wv = side == 0 ? t - ExactDiv(2 * t2, T, r1) + d : d - ExactDiv(t2, T, r1);
+        if (tm.kind == kSampledEnergy) {             // m(r) * J(r, col), m = (2 wdt [torque_weight]) * value  (:112-123)
+#pragma unroll
+          for (int dim = 0; dim < 3; ++dim) {
+            const double m = sp.mscale * A.P[3 * it + dim];
+            gpos[dim] += m * wp;
+            gvel[dim] += m * wv;
+          }
+        } else {                                     // ... and d vel / d (node position, node velocity)  (kVel)
+          const double e = ExactDiv(6 * t2, T3, r3), f = ExactDiv(6 * t, T2, r2), c = ExactDiv(3 * t2, T2, r2);
+          const double up = side == 0 ? e - f : f - e;
+          const double uv = side == 0 ? c - ExactDiv(4 * t, T, r1) + 1 : c - ExactDiv(2 * t, T, r1);
+#pragma unroll
+          for (int dim = 0; dim < 3; ++dim) {
+            const double da = A.P[3 * it + dim], dr = A.X[3 * it + dim];
+            gpos[dim] += da * wp + dr * up;
+            gvel[dim] += da * wv + dr * uv;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int dim = 0; dim < 3; ++dim) {
+      if (jb.col[dim] >= 0) gp[jb.col[dim]] = gp[jb.col[dim]] + gpos[dim];
+      if (jb.col[3 + dim] >= 0) gp[jb.col[3 + dim]] = gp[jb.col[3 + dim]] + gvel[dim];
     }
   } else {
-    // PhaseDurations::GetJacobianOfPos (phase_durations.cc:126-154), column `ph`
+    // column `ph` of the foot's ee-schedule from the phase sums (SampledPhaseSum): force spline, then torque spline
     const int ph = jb.node;
-    const SampledFoot ft = V.feet[V.splines[tm.spline0 + jb.spline].foot];
-    for (int k = 0; k < K; ++k)
-      for (int q = 0; q <= jb.deriv_dim; ++q) {
-        const int it = (jb.spline + q) * K + k;
-        const int cur = iseg[it] >> 16;
-        const bool last = cur == ft.n_phases - 1;
-        const double A = ix[3 * it], B = ix[3 * it + 1];
-        if (ph == cur && !last) g += A;
-        if (ph < cur) g += last ? -B - A : -B;
-      }
+    double g = 0.0;
+    for (int q = 0; q <= jb.aux; ++q) {
+      const SampledSpline& sp = V.splines[tm.spline0 + jb.spline + q];
+      const int last = V.feet[sp.foot].n_phases - 1;
+      const double* ps = W.psum + 2 * sp.ps0;
+      double c = ps[2 * ph];                         // phase ph itself (never the last phase: it has no column)
+      for (int later = ph + 1; later <= last; ++later) c -= ps[2 * later + 1];
+      c -= ps[2 * last];
+      g += c;
+    }
+    gp[jb.col[0]] = gp[jb.col[0]] + g;
   }
-  gp[jb.col] = gp[jb.col] + g;
 }
 
 }  // namespace tb
