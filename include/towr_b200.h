@@ -122,6 +122,12 @@ typedef struct towr_b200_spec {
   /* time-discretised costs (parameters.h:245-247, parameters.cc:69-71): sampling period and torque weight of EnergyCost
    * (costs/energy_cost.cc), sampling period of AngularMomentumCost.  Class properties, like the cost list itself. */
   double dt_cost_energy, energy_cost_torque_weight, dt_cost_ang_mom;
+  /* params_.enable_swing_ee_base_pos_tracking, swing_ee_base_pos_tracking_weight_, dt_cost_swing_ee_base_pos_tracking_
+   * (parameters.h:233-235; off by default): one EEBasePosCost per foot (nlp_formulation.cc:612-626, costs/
+   * ee_base_pos_cost.cc) that keeps the swinging foot near its initial position in the base frame.  The switch, weight and
+   * period are class properties; the reference position comes from each problem's initial_base_ / initial_ee_W. */
+  int enable_swing_ee_base_pos_tracking;
+  double swing_ee_base_pos_tracking_weight, dt_cost_swing_ee_base_pos_tracking;
 } towr_b200_spec;
 
 const char* towr_b200_last_error(void);
@@ -240,7 +246,8 @@ void* towr_b200_batch_stream(const towr_b200_batch* b);
  * (towr/src/costs/angular_momentum_cost.cc: weight dt sum_t |R I_b R^T omega|^2, gradient wrt base-ang nodes; I_b is the
  * batch problem's inertia), sampled with spec.dt_cost_energy / dt_cost_ang_mom.  spec.n_costs = 0 (the reference's
  * default, parameters.cc:90) gives f = 0 and a zero gradient.  what: bit 0 = f (n doubles), bit 1 = dense gradient
- * (n x n_vars doubles).  Not built: EEBasePosCost (enable_swing_ee_base_pos_tracking, off by default). */
+ * (n x n_vars doubles).  spec.enable_swing_ee_base_pos_tracking adds one EEBasePosCost per foot
+ * (towr/src/costs/ee_base_pos_cost.cc) after the listed costs, as GetCosts does: every cost term of the reference is built. */
 int towr_b200_batch_eval_cost(towr_b200_batch* b, int n, int what, const double* x, double* f_out, double* grad_out);
 int towr_b200_batch_eval_cost_device(towr_b200_batch* b, int n, int what, const double* d_x, double* d_f, double* d_grad,
                                      void* stream);
@@ -254,7 +261,7 @@ int towr_b200_batch_eval_cost_device(towr_b200_batch* b, int n, int what, const 
  * most TOWR_B200_STATIC_COST_MAX_WEIGHTS (variable, node value) weights, and at most
  * TOWR_B200_STATIC_COST_MAX_SAMPLED_BYTES of EnergyCost / AngularMomentumCost tables, else TOWR_B200_ERR_ARG with a
  * message naming the limit.  Without a batch there are no per-problem constants: AngularMomentumCost uses the inertia
- * of the spec the structure was created from.  d_x (n x n_vars), d_f (n) and d_grad (n x n_vars) are device memory on `device`, as for the _device entry
+ * and EEBasePosCost the initial base / foot positions of the spec the structure was created from.  d_x (n x n_vars), d_f (n) and d_grad (n x n_vars) are device memory on `device`, as for the _device entry
  * point.  ALL calls share the one array, which keeps the last call's tables (each call rewrites the part it uses;
  * nothing in it has to start at zero): calls that overlap on the GPU - different streams, or threads - race; order
  * them on one stream. */

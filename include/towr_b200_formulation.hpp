@@ -150,6 +150,8 @@ class Parameters {
   bool enable_stance_tracking = true;                   // the fork's default (parameters.h:225)
   bool enable_stance_rpy_tracking = true;
   bool enable_swing_ee_base_pos_tracking = false;
+  double swing_ee_base_pos_tracking_weight_ = 1e-2;     // parameters.h:234-235
+  double dt_cost_swing_ee_base_pos_tracking_ = 0.05;
   bool constrain_base_pitch_ = false;
   double torque_tx_min_, torque_tx_max_, torque_ty_min_, torque_ty_max_, torque_k_friction_;
   std::vector<double> ee_swing_height_min_, ee_swing_height_max_;
@@ -207,7 +209,6 @@ inline towr_b200_spec ToSpec(const ref::NlpFormulation& f) {
   // members without a counterpart in the backend
   if (P.angular_rep_ != ref::Parameters::EulerZYX) throw std::runtime_error("unsupported: RotationVector base orientation");
   if (P.constrain_base_pitch_) throw std::runtime_error("unsupported: constrain_base_pitch_");
-  if (P.enable_swing_ee_base_pos_tracking) throw std::runtime_error("unsupported: EEBasePosCost");
   if (!P.ee_swing_height_min_.empty() || !P.ee_swing_height_max_.empty()) throw std::runtime_error("unsupported: per-foot swing height bounds");
   if (!P.rom_swing_relax_dims_.empty()) throw std::runtime_error("unsupported: rom_swing_relax_dims_");
   if (P.n_base_waypoints_ != 0) throw std::runtime_error("unsupported: base waypoints");
@@ -249,6 +250,9 @@ inline towr_b200_spec ToSpec(const ref::NlpFormulation& f) {
   s.dt_cost_energy = P.dt_cost_energy_;
   s.energy_cost_torque_weight = P.energy_cost_torque_weight_;
   s.dt_cost_ang_mom = P.dt_cost_ang_mom_;
+  s.enable_swing_ee_base_pos_tracking = P.enable_swing_ee_base_pos_tracking ? 1 : 0;
+  s.swing_ee_base_pos_tracking_weight = P.swing_ee_base_pos_tracking_weight_;
+  s.dt_cost_swing_ee_base_pos_tracking = P.dt_cost_swing_ee_base_pos_tracking_;
   s.duration_base_polynomial = P.duration_base_polynomial_;
   s.ee_polynomials_per_swing_phase = P.ee_polynomials_per_swing_phase_;
   s.force_polynomials_per_stance_phase = P.force_polynomials_per_stance_phase_;

@@ -209,6 +209,9 @@ std::vector<double> CostSampleTimes(const SplineHolder& s, double dt);
 double EnergyCostValue(const SplineHolder& s, double weight, double torque_weight, double dt);
 void EnergyCostFillBlock(const SplineHolder& s, double weight, double torque_weight, double dt, const std::string& var_set,
                          double* block);
+double EEBasePosCostValue(const SplineHolder& s, int ee, const V3& p_ref_B, double weight, double dt);
+void EEBasePosCostFillBlock(const SplineHolder& s, int ee, const V3& p_ref_B, double weight, double dt,
+                            const std::string& var_set, double* block);
 double AngMomCostValue(const SplineHolder& s, const SingleRigidBodyDynamics& model, double weight, double dt);
 void AngMomCostFillBlock(const SplineHolder& s, const SingleRigidBodyDynamics& model, double weight, double dt,
                          const std::string& var_set, double* block);

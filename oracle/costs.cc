@@ -70,6 +70,49 @@ void EnergyCostFillBlock(const SplineHolder& s, double weight, double torque_wei
   }
 }
 
+// EEBasePosCost::GetCost (ee_base_pos_cost.cc:67-96): swing samples only, no dt factor
+double EEBasePosCostValue(const SplineHolder& s, int ee, const V3& p_ref_B, double weight, double dt) {
+  if (weight <= 0.0) return 0.0;
+  double cost = 0.0;
+  const EulerConverter& base_ang = *s.angular_converter_;
+  for (double t : CostSampleTimes(s, dt)) {
+    if (s.phase_durations_.at(ee)->IsContactPhase(t)) continue;
+    const V3 p_base = s.base_linear_->GetPoint(t).p;
+    const V3 p_ee = s.ee_motion_.at(ee)->GetPoint(t).p;
+    const V3 r_W = p_ee - p_base;
+    const M3 b_R_w = toDense(base_ang.GetRotationMatrixBaseToWorld(t)).transpose();
+    const V3 p_B = b_R_w * r_W;
+    const V3 e = p_B - p_ref_B;
+    cost += weight * squaredNorm(e);
+  }
+  return cost;
+}
+
+// EEBasePosCost::FillJacobianBlock (ee_base_pos_cost.cc:98-160); the ee-schedule block is left out there too (:154-157)
+void EEBasePosCostFillBlock(const SplineHolder& s, int ee, const V3& p_ref_B, double weight, double dt,
+                            const std::string& var_set, double* block) {
+  if (weight <= 0.0) return;
+  const EulerConverter& base_ang = *s.angular_converter_;
+  for (double t : CostSampleTimes(s, dt)) {
+    if (s.phase_durations_.at(ee)->IsContactPhase(t)) continue;
+    const V3 p_base = s.base_linear_->GetPoint(t).p;
+    const V3 p_ee = s.ee_motion_.at(ee)->GetPoint(t).p;
+    const V3 r_W = p_ee - p_base;
+    const M3 b_R_w = toDense(base_ang.GetRotationMatrixBaseToWorld(t)).transpose();
+    const V3 p_B = b_R_w * r_W;
+    const V3 e = p_B - p_ref_B;
+    const double m[3] = {(2.0 * weight) * e(0), (2.0 * weight) * e(1), (2.0 * weight) * e(2)};
+    double mW[3], mWn[3];
+    for (int c = 0; c < 3; ++c) {
+      mW[c] = m[0] * b_R_w.m[0][c] + m[1] * b_R_w.m[1][c] + m[2] * b_R_w.m[2][c];            // m * b_R_w
+      mWn[c] = (-m[0]) * b_R_w.m[0][c] + (-m[1]) * b_R_w.m[1][c] + (-m[2]) * b_R_w.m[2][c];   // -m * b_R_w
+    }
+    if (var_set == "ee-motion_" + std::to_string(ee)) AddRows(s.ee_motion_.at(ee)->GetJacobianWrtNodes(t, kPos), mW, block);
+    if (var_set == "base-lin") AddRows(s.base_linear_->GetJacobianWrtNodes(t, kPos), mWn, block);
+    if (var_set == "base-ang") AddRows(base_ang.DerivOfRotVecMult(t, r_W, true), m, block);
+  }
+}
+
 static M3 Mul(const M3& A, const M3& B) {
   M3 C;
   for (int i = 0; i < 3; ++i)

@@ -23,6 +23,7 @@ struct orc_problem {
   SplineHolder splines;
   Problem nlp;
   Vec x0;
+  std::vector<V3> swing_ref_B;                 // EEBasePosCost reference positions, one per foot when the cost is on
 };
 
 static NlpFormulation MakeFormulation(const orc_spec& s) {
@@ -68,6 +69,9 @@ static NlpFormulation MakeFormulation(const orc_spec& s) {
   p.dt_cost_energy_ = s.dt_cost_energy;
   p.energy_cost_torque_weight_ = s.energy_cost_torque_weight;
   p.dt_cost_ang_mom_ = s.dt_cost_ang_mom;
+  p.enable_swing_ee_base_pos_tracking = s.enable_swing_ee_base_pos_tracking != 0;
+  p.swing_ee_base_pos_tracking_weight_ = s.swing_ee_base_pos_tracking_weight;
+  p.dt_cost_swing_ee_base_pos_tracking_ = s.dt_cost_swing_ee_base_pos_tracking;
   p.enable_stance_tracking = s.enable_stance_tracking != 0;   // orc_spec_defaults: off
   p.ee_stance_position_.clear();
   for (int e = 0; e < E; ++e) {
@@ -97,6 +101,12 @@ static void Build(orc_problem* p, const orc_spec& s) {
   for (auto& v : p->formulation.GetVariableSets(p->splines)) p->nlp.AddVariableSet(v);
   for (auto& c : p->formulation.GetConstraints(p->splines)) p->nlp.AddConstraintSet(c);
   p->x0 = p->nlp.GetVariableValues();
+  // GetCosts (nlp_formulation.cc:612-626): r_B0 = b_R_w0 (initial_ee_W - initial_base.lin.p)
+  const NlpFormulation& f = p->formulation;
+  if (f.params_.enable_swing_ee_base_pos_tracking && f.params_.swing_ee_base_pos_tracking_weight_ > 0.0) {
+    const M3 b_R_w0 = EulerConverter::GetRotationMatrixBaseToWorldDense(f.initial_base_.ang.p).transpose();
+    for (int ee = 0; ee < f.params_.GetEECount(); ++ee) p->swing_ref_B.push_back(b_R_w0 * (f.initial_ee_W_.at(ee) - f.initial_base_.lin.p));
+  }
 }
 
 extern "C" {
@@ -125,6 +135,9 @@ void orc_spec_defaults(orc_spec* s) {
   s->dt_cost_energy = d.dt_cost_energy_;
   s->energy_cost_torque_weight = d.energy_cost_torque_weight_;
   s->dt_cost_ang_mom = d.dt_cost_ang_mom_;
+  s->enable_swing_ee_base_pos_tracking = d.enable_swing_ee_base_pos_tracking ? 1 : 0;
+  s->swing_ee_base_pos_tracking_weight = d.swing_ee_base_pos_tracking_weight_;
+  s->dt_cost_swing_ee_base_pos_tracking = d.dt_cost_swing_ee_base_pos_tracking_;
   for (int i = 0; i < 3; ++i) s->bounds_final_lin_pos[i] = s->bounds_final_lin_vel[i] = s->bounds_final_ang_pos[i] = s->bounds_final_ang_vel[i] = 1;
 }
 
@@ -490,6 +503,9 @@ double orc_eval_f(orc_problem* p, const double* x) {
     if (pr.first == 2) total += EnergyCostValue(p->splines, pr.second, pa.energy_cost_torque_weight_, pa.dt_cost_energy_);
     if (pr.first == 3) total += AngMomCostValue(p->splines, *p->formulation.model_.dynamic_model_, pr.second, pa.dt_cost_ang_mom_);
   }
+  for (size_t ee = 0; ee < p->swing_ref_B.size(); ++ee)     // GetCosts, nlp_formulation.cc:612-626: after the listed costs
+    total += EEBasePosCostValue(p->splines, static_cast<int>(ee), p->swing_ref_B[ee], pa.swing_ee_base_pos_tracking_weight_,
+                                pa.dt_cost_swing_ee_base_pos_tracking_);
   return total;
 }
 
@@ -523,6 +539,14 @@ void orc_eval_grad_f(orc_problem* p, const double* x, double* grad) {
       else
         AngMomCostFillBlock(p->splines, *p->formulation.model_.dynamic_model_, pr.second, pa.dt_cost_ang_mom_, vs->GetName(),
                             grad + col0);
+      col0 += vs->GetRows();
+    }
+  }
+  for (size_t ee = 0; ee < p->swing_ref_B.size(); ++ee) {
+    int col0 = 0;
+    for (auto& vs : p->nlp.Vars()->GetComponents()) {
+      EEBasePosCostFillBlock(p->splines, static_cast<int>(ee), p->swing_ref_B[ee], pa.swing_ee_base_pos_tracking_weight_,
+                             pa.dt_cost_swing_ee_base_pos_tracking_, vs->GetName(), grad + col0);
       col0 += vs->GetRows();
     }
   }

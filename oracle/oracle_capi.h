@@ -58,6 +58,10 @@ typedef struct orc_spec {
   double terrain_table_x[ORC_MAX_TERRAIN_KNOTS], terrain_table_h[ORC_MAX_TERRAIN_KNOTS];
   /* Parameters::dt_cost_energy_, energy_cost_torque_weight_, dt_cost_ang_mom_ (parameters.h:245-247) */
   double dt_cost_energy, energy_cost_torque_weight, dt_cost_ang_mom;
+  /* Parameters::enable_swing_ee_base_pos_tracking, swing_ee_base_pos_tracking_weight_, dt_cost_swing_ee_base_pos_tracking_
+   * (parameters.h:233-235) */
+  int enable_swing_ee_base_pos_tracking;
+  double swing_ee_base_pos_tracking_weight, dt_cost_swing_ee_base_pos_tracking;
 } orc_spec;
 
 /* Parameters::Parameters() defaults (parameters.cc:40-105), enable_stance_tracking=false. */

@@ -1778,6 +1778,46 @@ class EnergyCost:
         return g
 
 
+class EEBasePosCost:
+    """costs/ee_base_pos_cost.cc:38-160: during swing, weight * |b_R_w (p_ee - p_base) - p_ref_B|^2 per sample (no dt factor)."""
+
+    def __init__(self, splines, ee, p_ref_B, weight, dt):
+        self.sh, self.ee, self.p_ref_B, self.weight, self.dt = splines, ee, np.asarray(p_ref_B, dtype=float), weight, dt
+
+    def link(self, variables):
+        pass
+
+    def _swing_samples(self):
+        for t in cost_sample_times(self.sh.base_linear.total_time(), self.dt):
+            if self.sh.phase_durations[self.ee].is_contact_phase(t):      # :78-80
+                continue
+            r_W = self.sh.ee_motion[self.ee].point(t)[kPos] - self.sh.base_linear.point(t)[kPos]
+            b_R_w = self.sh.angular_converter.rotation(t).T
+            yield t, r_W, b_R_w, b_R_w @ r_W - self.p_ref_B
+
+    def cost(self):                                                   # :67-96
+        if self.weight <= 0.0:
+            return 0.0
+        c = 0.0
+        for _, _, _, e in self._swing_samples():
+            c += self.weight * float(e @ e)
+        return c
+
+    def gradient(self, var_set):                                      # :98-160 (no ee-schedule block, :154-157)
+        g = np.zeros(var_set.rows())
+        if self.weight <= 0.0:
+            return g
+        for t, r_W, b_R_w, e in self._swing_samples():
+            m = (2.0 * self.weight) * e
+            if var_set.name == "ee-motion_%d" % self.ee:
+                g += (m @ b_R_w) @ self.sh.ee_motion[self.ee].jacobian_wrt_nodes(t, kPos).dense()
+            if var_set.name == "base-lin":
+                g += (-m @ b_R_w) @ self.sh.base_linear.jacobian_wrt_nodes(t, kPos).dense()
+            if var_set.name == "base-ang":
+                g += m @ self.sh.angular_converter.d_rot_vec_mult(t, r_W, True).dense()
+        return g
+
+
 class AngularMomentumCost:
     """costs/angular_momentum_cost.cc:39-208, SingleRigidBodyDynamics branch: sum of weight * dt * |R I_b R^T omega|^2."""
 
@@ -2060,6 +2100,13 @@ class Formulation:
                 self.costs.append(AngularMomentumCost(sh, self.model, w, float(s.dt_cost_ang_mom)))
             else:
                 raise RuntimeError("cost not defined!")
+        # :612-626: one EEBasePosCost per foot, reference r_B0 = b_R_w0 (initial_ee_W - initial_base.lin.p)
+        if int(s.enable_swing_ee_base_pos_tracking) and float(s.swing_ee_base_pos_tracking_weight) > 0.0:
+            b_R_w0 = rotation_base_to_world(self.initial_base_ang[kPos]).T
+            for ee in range(n_ee):
+                r_B0 = b_R_w0 @ (self.initial_ee_W[ee] - self.initial_base_lin[kPos])
+                self.costs.append(EEBasePosCost(sh, ee, r_B0, float(s.swing_ee_base_pos_tracking_weight),
+                                                float(s.dt_cost_swing_ee_base_pos_tracking)))
         for c in self.costs:
             c.link(by_name)
 

@@ -63,6 +63,8 @@ class Spec(C.Structure):
         ("terrain_table_n", C.c_int), ("terrain_table_mode", C.c_int),
         ("terrain_table_x", C.c_double * 16), ("terrain_table_h", C.c_double * 16),
         ("dt_cost_energy", C.c_double), ("energy_cost_torque_weight", C.c_double), ("dt_cost_ang_mom", C.c_double),
+        ("enable_swing_ee_base_pos_tracking", C.c_int), ("swing_ee_base_pos_tracking_weight", C.c_double),
+        ("dt_cost_swing_ee_base_pos_tracking", C.c_double),
     ]
 
 

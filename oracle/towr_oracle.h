@@ -383,6 +383,8 @@ struct Parameters {
   double dt_constraint_dynamic_, dt_constraint_range_of_motion_, dt_constraint_base_motion_;
   double dt_constraint_force_, dt_constraint_torque_;
   double dt_cost_energy_, energy_cost_torque_weight_, dt_cost_ang_mom_;   // parameters.h:245-247
+  bool enable_swing_ee_base_pos_tracking = false;                          // parameters.h:233-235
+  double swing_ee_base_pos_tracking_weight_ = 1e-2, dt_cost_swing_ee_base_pos_tracking_ = 0.05;
   double duration_base_polynomial_;
   int ee_polynomials_per_swing_phase_, force_polynomials_per_stance_phase_, torque_polynomials_per_stance_phase_;
   double force_limit_in_normal_direction_;

@@ -67,6 +67,13 @@ def test_cost_spec_errors(product):
         T.Structure(s)
     s = mk(T, CASES[4])
     assert s.dt_cost_energy == 0.02 and s.energy_cost_torque_weight == 1.0 and s.dt_cost_ang_mom == 0.02   # parameters.cc:69-71
+    assert (s.enable_swing_ee_base_pos_tracking, s.swing_ee_base_pos_tracking_weight, s.dt_cost_swing_ee_base_pos_tracking) == \
+        (0, 1e-2, 0.05)                                        # parameters.h:233-235
+    plain = T.Structure(mk(T, CASES[4]))
+    swing = sampled_spec(T, "monoped_hop", [], None, None, None, (0.3, None))
+    assert not plain.accepts(swing) and T.Structure(swing).accepts(swing)
+    swing.swing_ee_base_pos_tracking_weight = 0.0              # weight 0: no cost term is made (nlp_formulation.cc:614)
+    assert plain.accepts(swing)
 
 
 # (case, cost list, dt_cost_energy, energy_cost_torque_weight, dt_cost_ang_mom)
@@ -77,11 +84,22 @@ SAMPLED = [
     ("biped_walk_durations", [(ENERGY, 1e-3), (ANG_MOM, 0.7)], None, None, None),
     ("anymal_trot_durations", [(ENERGY, 1e-3), (ANG_MOM, 0.7), (FORCES, 1e-5)], 0.03, 0.0, 0.05),   # no torque term (:119)
     ("monoped_hop_torque", [(ENERGY, 2.0), (ANG_MOM, 0.0)], 0.0, 0.5, None),   # dt <= 0: t = 0 and T only (:55-59); weight 0: no term
+    # EEBasePosCost (params_.enable_swing_ee_base_pos_tracking, nlp_formulation.cc:612-626): 6th element = (weight, dt)
+    ("monoped_hop", [], None, None, None, (0.3, None)),
+    ("anymal_trot", [(ENERGY, 1e-3), (ANG_MOM, 0.7)], None, None, None, (0.3, None)),
+    ("biped_walk_durations", [(FORCES, 1e-5)], None, None, None, (1e-2, 0.03)),
+    ("anymal_trot_durations", [], None, None, None, (0.3, 0.03)),
 ]
 
 
-def sampled_spec(T, name, costs, dt_energy, torque_weight, dt_ang_mom):
+def sampled_spec(T, name, costs, dt_energy, torque_weight, dt_ang_mom, swing=None):
     s = with_costs(mk(T, [c for c in CASES if c[0] == name][0]), costs)
+    if swing is not None:
+        s.enable_swing_ee_base_pos_tracking = 1
+        s.swing_ee_base_pos_tracking_weight = swing[0]
+        if swing[1] is not None:
+            s.dt_cost_swing_ee_base_pos_tracking = swing[1]
+        s.initial_base_ang[1], s.initial_base_ang[2] = -0.1, 0.2      # a reference frame that is not the world frame
     if dt_energy is not None:
         s.dt_cost_energy = dt_energy
     if torque_weight is not None:
@@ -117,7 +135,7 @@ def test_oracle_sampled_cost_gradient_is_consistent(product, oracle):
         assert abs(fd - g[c]) <= 1e-6 * max(1.0, abs(g[c]))
 
 
-@pytest.mark.parametrize("case", SAMPLED, ids=lambda c: c[0] + "".join("_%d" % cid for cid, _ in c[1]))
+@pytest.mark.parametrize("case", SAMPLED, ids=lambda c: c[0] + "".join("_%d" % cid for cid, _ in c[1]) + ("_swing" if len(c) > 5 else ""))
 def test_emulated_cost_kernels_match_oracle(product, oracle, emu, case):
     """The device code of both cost kernels (NodeCost table, sampled_cost.cuh) replayed serially on the host."""
     T, O = product, oracle
@@ -162,7 +180,7 @@ def test_gpu_cost_matches_oracle(product, oracle, name):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("case", SAMPLED, ids=lambda c: c[0] + "".join("_%d" % cid for cid, _ in c[1]))
+@pytest.mark.parametrize("case", SAMPLED, ids=lambda c: c[0] + "".join("_%d" % cid for cid, _ in c[1]) + ("_swing" if len(c) > 5 else ""))
 def test_gpu_sampled_costs_match_oracle(product, oracle, case):
     """EnergyCost / AngularMomentumCost on the GPU; problem 1 has its own inertia (AngularMomentumCost reads the
     batch problem's I_b)."""
@@ -176,6 +194,8 @@ def test_gpu_sampled_costs_match_oracle(product, oracle, case):
     s1 = sampled_spec(T, *case)
     s1.inertia[0] *= 1.5
     s1.inertia[4] += 0.05
+    s1.initial_base_ang[2] = -0.3                  # ... and its own EEBasePosCost reference positions
+    s1.initial_ee_W[0][1] += 0.02
     b.set_problem(1, s1)
     f, g = b.eval_cost(x)
     f1, _ = b.eval_cost(x, 1)

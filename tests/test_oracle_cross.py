@@ -54,12 +54,20 @@ def test_cpp_oracle_matches_numpy_restatement(oracle, case):
     (0, True, ((2, 1e-3), (3, 0.7))),                        # EnergyCostID, AngMomCostID with the ee-schedule gradient
     (1, False, ((2, 1e-3), (3, 0.7), (0, 1e-3))),
     (3, True, ((2, 1e-3), (3, 0.7))),
-], ids=["monoped_nodecost", "monoped_sampled_durations", "biped_sampled", "anymal_sampled_durations"])
+    (0, True, ("swing",)),                                   # EEBasePosCost alone, then with a listed cost
+    (3, False, ((2, 1e-3), "swing")),
+], ids=["monoped_nodecost", "monoped_sampled_durations", "biped_sampled", "anymal_sampled_durations", "monoped_swing_durations",
+        "anymal_swing"])
 def test_costs_match_numpy_restatement(oracle, robot, optimise, costs):
     """eval_f / eval_grad_f: NodeCost (node_cost.cc), EnergyCost (energy_cost.cc), AngularMomentumCost
-    (angular_momentum_cost.cc)."""
+    (angular_momentum_cost.cc), EEBasePosCost (ee_base_pos_cost.cc)."""
     O = oracle
     s = O.make_spec(robot, 0, 2.4, optimize_durations=optimise, extra_constraints=(O.Torque,))
+    if "swing" in costs:
+        s.enable_swing_ee_base_pos_tracking = 1
+        s.swing_ee_base_pos_tracking_weight = 0.3
+        s.initial_base_ang[1], s.initial_base_ang[2] = -0.1, 0.2
+        costs = tuple(c for c in costs if c != "swing")
     s.n_costs = len(costs)
     for i, (cid, w) in enumerate(costs):
         s.cost_ids[i], s.cost_weights[i] = cid, w

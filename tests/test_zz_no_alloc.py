@@ -21,6 +21,9 @@ def _with_costs(T, robot, combo, total_time, optimise, sampled=False):
         s.n_costs = 4
         s.cost_ids[2], s.cost_weights[2] = 2, 1e-3     # EnergyCostID
         s.cost_ids[3], s.cost_weights[3] = 3, 0.5      # AngMomCostID
+        s.enable_swing_ee_base_pos_tracking = 1        # EEBasePosCost, reference positions of the class spec
+        s.swing_ee_base_pos_tracking_weight = 0.3
+        s.initial_base_ang[2] = 0.2
     return s
 
 

@@ -57,6 +57,11 @@ CASES = [
     ("anymal_trot_table_ramps_torque", 3, 1, 2.0, (1.0, 0.0, 0.0), 8, (TORQUE,), False, {},
      (1, [0.4, 0.8, 1.2, 1.6], [0.0, 0.2, 0.2, 0.0])),
     ("monoped_hop_table_ramps_durations", 0, 0, 2.4, (1.0, 0.0, 0.0), 8, (), True, {}, (1, [0.5, 1.0], [0.0, 0.3])),
+    # hand-made phase timings instead of a GaitGenerator combo ("phases": per foot; the first phase is a stance): the
+    # reference's hand-built monoped formulations, test/yaw_spin_example.cc:51-61 (stance 0.6, flight 0.5, stance 0.6, a half
+    # turn in yaw, the default constraint families :163-170) and test/squat_jump_example.cc with optimised timings
+    ("monoped_yaw_spin_example", 0, 0, 1.7, (0.0, 0.0, 3.141592653589793), 0, (), False, {"phases": [[0.6, 0.5, 0.6]]}),
+    ("monoped_squat_jump_durations", 0, 0, 1.5, (0.3, 0.0, 0.0), 0, (), True, {"phases": [[0.5, 0.4, 0.6]]}),
 ]
 
 
@@ -196,6 +201,13 @@ def mk(M, case, goal=None):
     s = M.make_spec(case[1], case[2], case[3], goal=goal if goal is not None else case[4], terrain=case[5],
                     optimize_durations=opt, extra_constraints=extra)
     for k, v in (case[8] if len(case) > 8 else {}).items():     # Parameters overrides (same field names in both specs)
+        if k == "phases":                                       # params_.ee_phase_durations_, ee_in_contact_at_start_
+            for e, durations in enumerate(v):
+                s.n_phases[e] = len(durations)
+                s.in_contact_at_start[e] = 1
+                for i, d in enumerate(durations):
+                    s.phase_durations[e][i] = d
+            continue
         setattr(s, k, v)
     if len(case) > 9:
         set_terrain_table(s, *case[9])

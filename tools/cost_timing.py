@@ -11,8 +11,11 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import towr2025_b200 as T
 
 
-def run(name, robot, combo, total_time, optimise, costs, n=4096, steps=20, warmup=5):
+def run(name, robot, combo, total_time, optimise, costs, n=4096, steps=20, warmup=5, swing=False):
     s = T.make_spec(robot, combo, total_time, optimize_durations=optimise)
+    if swing:                                    # one EEBasePosCost per foot
+        s.enable_swing_ee_base_pos_tracking = 1
+        name += " + swing tracking"
     s.n_costs = len(costs)
     for i, (cid, w) in enumerate(costs):
         s.cost_ids[i], s.cost_weights[i] = cid, w
@@ -51,6 +54,8 @@ if __name__ == "__main__":
     run("anymal_trot", T.Anymal, T.C1, 2.0, False, [(0, 1e-3), (1, 1e-2), (2, 1e-3), (3, 0.5)])
     run("anymal_trot_durations", T.Anymal, T.C1, 2.0, True, [(0, 1e-3), (1, 1e-2), (2, 1e-3), (3, 0.5)])
     run("monoped_hop_durations", T.Monoped, T.C0, 2.4, True, [(2, 1e-3), (3, 0.5)])
+    run("anymal_trot", T.Anymal, T.C1, 2.0, False, [(0, 1e-3), (1, 1e-2), (2, 1e-3), (3, 0.5)], swing=True)
+    run("anymal_trot_durations", T.Anymal, T.C1, 2.0, True, [(0, 1e-3), (1, 1e-2), (2, 1e-3), (3, 0.5)], swing=True)
     if "--split" in sys.argv:
         run("anymal_trot", T.Anymal, T.C1, 2.0, False, [(2, 1e-3)])
         run("anymal_trot", T.Anymal, T.C1, 2.0, False, [(3, 0.5)])

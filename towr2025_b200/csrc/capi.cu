@@ -128,14 +128,18 @@ struct towr_b200_batch {
   // cost tables (cost.h), built at the first eval_cost call
   bool cost_ready = false;
   tb::CostDevice cost_dev{};
-  const unsigned char* sampled_dev = nullptr;   // EnergyCost / AngularMomentumCost tables (cost.h), nullptr: none
+  const unsigned char* sampled_dev = nullptr;   // EnergyCost / AngularMomentumCost / EEBasePosCost tables (cost.h), nullptr: none
   size_t sampled_shared = 0;
+  // EEBasePosCost reference positions per problem (cost.h: SwingReferenceB), kept only by classes with that cost
+  std::vector<double> pref_host;
+  double* pref_dev = nullptr;
   double *cost_f_dev = nullptr, *cost_grad_dev = nullptr;
 
   void SyncConsts() {
     if (!pc_dirty) return;
     if (device_eval_pending) Check(cudaStreamWaitEvent(stream, device_eval_done, 0), "order consts after eval_device");
     Check(cudaMemcpyAsync(pc_dev, pc_host.data(), sizeof(tb::ProblemConst) * n, cudaMemcpyHostToDevice, stream), "H2D consts");
+    if (pref_dev) Check(cudaMemcpyAsync(pref_dev, pref_host.data(), sizeof(double) * pref_host.size(), cudaMemcpyHostToDevice, stream), "H2D consts");
     pc_dirty = false;
   }
   ~towr_b200_batch() {
@@ -330,6 +334,11 @@ int towr_b200_batch_create(const towr_b200_structure* st, int n_problems, int de
     b->pc_host.assign(n_problems, tb::ProblemConst{});
     Check(cudaMalloc(&b->pc_dev, sizeof(tb::ProblemConst) * n_problems), "cudaMalloc(consts)");
     keep(b->pc_dev);
+    if (tb::HasSwingTracking(st->spec)) {
+      b->pref_host.assign(12 * static_cast<size_t>(n_problems), 0.0);
+      Check(cudaMalloc(&b->pref_dev, sizeof(double) * b->pref_host.size()), "cudaMalloc(consts)");
+      keep(b->pref_dev);
+    }
     Check(cudaMalloc(&b->status_dev, sizeof(int) * n_problems), "cudaMalloc(status)");
     keep(b->status_dev);
     Check(cudaMemset(b->status_dev, 0, sizeof(int) * n_problems), "cudaMemset(status)");
@@ -369,6 +378,7 @@ int towr_b200_batch_set_problem(towr_b200_batch* b, int i, const towr_b200_spec*
     if (!b || i < 0 || i >= b->n) throw std::runtime_error("problem index out of range");
     if (towr_b200_structure_accepts(b->st, s) != 0) throw StructureError(g_err);
     tb::FillProblemConst(*s, b->pc_host[i]);
+    if (b->pref_dev) tb::SwingReferenceB(*s, b->pref_host.data() + 12 * static_cast<size_t>(i));
     b->pc_dirty = true;
   });
 }
@@ -379,6 +389,8 @@ int towr_b200_batch_set_all_problems(towr_b200_batch* b, const towr_b200_spec* s
     tb::ProblemConst pc;
     tb::FillProblemConst(*s, pc);
     for (auto& p : b->pc_host) p = pc;
+    if (b->pref_dev)
+      for (int i = 0; i < b->n; ++i) tb::SwingReferenceB(*s, b->pref_host.data() + 12 * static_cast<size_t>(i));
     b->pc_dirty = true;
   });
 }
@@ -582,9 +594,12 @@ int towr_b200_batch_eval_cost_device(towr_b200_batch* b, int n, int what, const 
         b->SyncConsts();
         Check(cudaStreamSynchronize(b->stream), "sync consts");
       }
-      Check(tb::LaunchSampledCost(b->sampled_dev, b->sampled_shared, b->pc_dev, what, d_x, d_f, d_grad, n, sms,
+      Check(tb::LaunchSampledCost(b->sampled_dev, b->sampled_shared, b->pc_dev, b->pref_dev, what, d_x, d_f, d_grad, n, sms,
                                   static_cast<cudaStream_t>(stream)), "launch");
       b->launches += 1;
+      // the kernel reads the batch's constants on the caller's stream: a later set_problem must not overwrite them first
+      Check(cudaEventRecord(b->device_eval_done, static_cast<cudaStream_t>(stream)), "record eval_cost_device");
+      b->device_eval_pending = true;
     }
   });
 }
@@ -613,7 +628,7 @@ int towr_b200_batch_eval_cost(towr_b200_batch* b, int n, int what, const double*
     b->launches += 1;
     if (b->sampled_dev) {
       b->SyncConsts();
-      Check(tb::LaunchSampledCost(b->sampled_dev, b->sampled_shared, b->pc_dev, what, b->x_dev, b->cost_f_dev,
+      Check(tb::LaunchSampledCost(b->sampled_dev, b->sampled_shared, b->pc_dev, b->pref_dev, what, b->x_dev, b->cost_f_dev,
                                   b->cost_grad_dev, n, sms, b->stream), "launch");
       b->launches += 1;
     }

@@ -132,21 +132,44 @@ void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCos
       jobs.push_back(j);
     }
   };
-  int n_items = 0, item_doubles = 0;
+  // variables that write several node values (the stance variables of ee-motion): one job per column
+  auto column_jobs = [&](const VarSet& v, int spline_in_term, int term) {
+    for (int idx = 0; idx < v.n_vars; ++idx) {
+      if (v.refs[idx].empty() || v.refs[idx].size() > 5) throw std::runtime_error("unsupported: cost variable with 0 or > 5 node values");
+      SampledJob j{};
+      j.col[0] = v.col0 + idx;
+      j.kind = static_cast<uint16_t>(kJobColumn | (term << 8));
+      j.spline = static_cast<uint16_t>(spline_in_term);
+      j.aux = static_cast<uint16_t>(v.refs[idx].size());
+      for (size_t r = 0; r < v.refs[idx].size(); ++r)
+        j.col[1 + r] = v.refs[idx][r].node | (v.refs[idx][r].deriv << 16) | (v.refs[idx][r].dim << 20);
+      jobs.push_back(j);
+    }
+  };
+  struct TermDef { int kind; double weight, dt; int foot; };
+  std::vector<TermDef> defs;
   for (int c = 0; c < s.n_costs; ++c) {
-    const double weight = s.cost_weights[c];
-    const bool energy = s.cost_ids[c] == TOWR_B200_COST_ENERGY, ang_mom = s.cost_ids[c] == TOWR_B200_COST_ANG_MOM;
-    if (!energy && !ang_mom) continue;
+    if (s.cost_ids[c] == TOWR_B200_COST_ENERGY) defs.push_back({kSampledEnergy, s.cost_weights[c], s.dt_cost_energy, -1});
+    if (s.cost_ids[c] == TOWR_B200_COST_ANG_MOM) defs.push_back({kSampledAngMom, s.cost_weights[c], s.dt_cost_ang_mom, -1});
+  }
+  if (HasSwingTracking(s))                                     // after the listed costs (nlp_formulation.cc:612-626)
+    for (int e = 0; e < hp.n_ee; ++e)
+      defs.push_back({kSampledEEBasePos, s.swing_ee_base_pos_tracking_weight, s.dt_cost_swing_ee_base_pos_tracking, e});
+  int n_items = 0, item_doubles = 0;
+  for (const TermDef& def : defs) {
+    const double weight = def.weight;
     if (weight <= 0.0) continue;                               // GetCost / FillJacobianBlock return at once (:70, :94)
-    const double dt = energy ? s.dt_cost_energy : s.dt_cost_ang_mom;
+    const bool energy = def.kind == kSampledEnergy;
+    const double dt = def.dt;
     SampledTerm t{};
-    t.kind = energy ? kSampledEnergy : kSampledAngMom;
+    t.kind = def.kind;
+    t.foot = def.foot;
     t.spline0 = static_cast<int>(splines.size());
     t.time0 = static_cast<int>(times.size());
     t.job0 = static_cast<int>(jobs.size());
     t.item0 = n_items;
     t.scratch0 = item_doubles;
-    t.rec = energy ? (rt ? 6 : 4) : 8;
+    t.rec = energy ? (rt ? 6 : 4) : def.kind == kSampledAngMom ? 8 : 9;
     const int term = static_cast<int>(terms.size());
     t.weight = weight;
     t.dtf = dt > 0.0 ? dt : 1.0;
@@ -176,35 +199,89 @@ void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCos
           }
         }
       }
-    } else {
+    } else if (def.kind == kSampledAngMom) {
       const VarSet* va = hp.Find(kBaseAng);
       add_spline(*va, -1, false, 1.0, 2.0 * wdt);
       node_jobs(*va, 0, term);
+    } else {
+      // EEBasePosCost (ee_base_pos_cost.cc): the foot's motion spline, base-lin, base-ang; the gradient reaches their
+      // node variables (:123-152), not the ee-schedule (:154-157)
+      const VarSet* vm = hp.Find(kEEMotion, def.foot);
+      const VarSet* vl = hp.Find(kBaseLin);
+      const VarSet* va = hp.Find(kBaseAng);
+      add_spline(*vm, def.foot, false, 1.0, 2.0 * weight);     // m = (2.0*weight_) * e  (:121)
+      add_spline(*vl, -1, false, 1.0, 2.0 * weight);
+      add_spline(*va, -1, false, 1.0, 2.0 * weight);
+      if (vm->n_polys() >= 4096 || vl->n_polys() >= 4096) throw std::runtime_error("unsupported: more than 4095 polynomials in a spline");
+      column_jobs(*vm, 0, term);
+      node_jobs(*vl, 1, term);
+      node_jobs(*va, 2, term);
     }
     t.n_splines = static_cast<int>(splines.size()) - t.spline0;
+    t.item_splines = energy ? t.n_splines : 1;
     t.n_jobs = static_cast<int>(jobs.size()) - t.job0;
     // fixed durations: segment and local time of every (spline, sample) are class constants (spline.cc:48-78)
-    t.fix0 = splines[t.spline0].rt ? -1 : static_cast<int>(fix_t.size());
-    for (int sidx = t.spline0; t.fix0 >= 0 && sidx < static_cast<int>(splines.size()); ++sidx) {
-      const SampledSpline& sp = splines[sidx];
+    for (int sidx = t.spline0; sidx < static_cast<int>(splines.size()); ++sidx) {
+      SampledSpline& sp = splines[sidx];
+      sp.fix0 = -1;
+      if (sp.rt) continue;
+      sp.fix0 = static_cast<int>(fix_t.size());
       const std::vector<double> d(poly_T.begin() + sp.poly0, poly_T.begin() + sp.poly0 + sp.n_polys);
+      std::vector<double> pd;
+      if (sp.foot >= 0) pd.assign(s.phase_durations[sp.foot], s.phase_durations[sp.foot] + s.n_phases[sp.foot]);
       for (double tg : ts) {
         const int id = SegmentId(tg, d);
-        fix_seg.push_back(static_cast<uint16_t>(id));
+        int contact = 0;
+        if (sp.foot >= 0) {                                    // PhaseDurations::IsContactPhase (phase_durations.cc:113-118)
+          const int ph = SegmentId(tg, pd);
+          contact = ((ph % 2 == 0) ? s.in_contact_at_start[sp.foot] != 0 : s.in_contact_at_start[sp.foot] == 0) ? 1 : 0;
+        }
+        if (id >= 0x8000) throw std::runtime_error("unsupported: more than 32767 polynomials in a spline");
+        fix_seg.push_back(static_cast<uint16_t>(id | (contact << 15)));
         fix_t.push_back(LocalTime(tg, id, d));
       }
     }
-    n_items += t.n_splines * t.n_samples;
-    item_doubles += t.rec * t.n_splines * t.n_samples;
+    n_items += t.item_splines * t.n_samples;
+    item_doubles += t.rec * t.item_splines * t.n_samples;
     terms.push_back(t);
   }
   if (terms.empty()) return;
+  // Columns that several jobs write (base-ang: AngularMomentumCost and every foot's EEBasePosCost; base-lin: every
+  // foot's): those jobs park their sums and one thread per column adds them in job = term order, which is also the order
+  // in which ifopt adds the terms' gradients.
+  std::vector<int> comb_col, comb_ptr(1, 0), comb_src;
+  int n_scratch = 0;
+  {
+    auto n_cols = [](const SampledJob& j) { return (j.kind & 0xFF) == kJobNode ? 6 : 1; };
+    std::vector<int> writers(static_cast<size_t>(hp.n_vars), 0);
+    for (const SampledJob& j : jobs)
+      for (int i = 0; i < n_cols(j); ++i)
+        if (j.col[i] >= 0) ++writers[j.col[i]];
+    std::vector<std::vector<int>> src(static_cast<size_t>(hp.n_vars));
+    for (SampledJob& j : jobs) {
+      j.slot = -1;
+      bool shared = false;
+      for (int i = 0; i < n_cols(j); ++i) shared = shared || (j.col[i] >= 0 && writers[j.col[i]] > 1);
+      if (!shared) continue;
+      j.slot = n_scratch;
+      for (int i = 0; i < n_cols(j); ++i)
+        if (j.col[i] >= 0) src[j.col[i]].push_back(n_scratch + i);
+      n_scratch += n_cols(j);
+    }
+    for (int c = 0; c < hp.n_vars; ++c) {
+      if (src[c].empty()) continue;
+      comb_col.push_back(c);
+      comb_src.insert(comb_src.end(), src[c].begin(), src[c].end());
+      comb_ptr.push_back(static_cast<int>(comb_src.size()));
+    }
+  }
   if (terms.size() > 8) throw std::runtime_error("unsupported: more than 8 time-discretised cost terms");   // one warp each (cost_kernel.cu)
   for (int e = 0; e < hp.n_ee; ++e) {
     SampledFoot f{};
     f.phase0 = n_phases;
     f.n_phases = s.n_phases[e];
     f.col0 = rt ? hp.Find(kEESchedule, e)->col0 : 0;
+    f.contact_at_start = s.in_contact_at_start[e] != 0;
     for (int i = 0; i < s.n_phases[e]; ++i) f.total += s.phase_durations[e][i];   // phase_durations.cc:40-50
     feet.push_back(f);
     n_phases += s.n_phases[e];
@@ -221,12 +298,15 @@ void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCos
   h.n_times = static_cast<int>(times.size());
   h.n_jobs = static_cast<int>(jobs.size());
   h.n_phase_slots = n_phase_slots;
+  h.n_scratch = n_scratch;
+  h.n_comb = static_cast<int>(comb_col.size());
   h.n_items = n_items;
   h.item_doubles = item_doubles;
   // body inertia as SingleRigidBodyDynamics builds it (single_rigid_body_dynamics.cc:36-44): off-diagonals negated
   const double* in = s.inertia;   // Ixx, Iyy, Izz, Ixy, Ixz, Iyz
   const double I[9] = {in[0], -in[3], -in[4], -in[3], in[1], -in[5], -in[4], -in[5], in[2]};
   std::memcpy(h.I, I, sizeof(I));
+  SwingReferenceB(s, h.p_ref_B);
   std::vector<unsigned char>& blob = out.blob;
   blob.assign(sizeof(SampledHeader), 0);
   h.off_terms = Append(blob, terms);
@@ -238,6 +318,9 @@ void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCos
   h.off_poly_meta = Append(blob, poly_meta);
   h.off_node_src = Append(blob, node_src);
   h.off_poly_spline = Append(blob, poly_spline);
+  h.off_comb_col = Append(blob, comb_col);
+  h.off_comb_ptr = Append(blob, comb_ptr);
+  h.off_comb_src = Append(blob, comb_src);
   h.off_fix_t = Append(blob, fix_t);
   h.off_fix_seg = Append(blob, fix_seg);
   while (blob.size() % 16) blob.push_back(0);

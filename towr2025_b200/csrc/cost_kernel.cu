@@ -78,8 +78,8 @@ __device__ long long g_cost_clocks[16];
 #endif
 
 __global__ void __launch_bounds__(kSampledThreads, 2)
-SampledCostKernel(const unsigned char* __restrict__ blob_g, const ProblemConst* __restrict__ pcs, int what,
-                  const double* __restrict__ x, double* __restrict__ f_out, double* __restrict__ grad_out, int n_problems) {
+SampledCostKernel(const unsigned char* __restrict__ blob_g, const ProblemConst* __restrict__ pcs,
+                  const double* __restrict__ pref, int what, const double* __restrict__ x, double* __restrict__ f_out, double* __restrict__ grad_out, int n_problems) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int tid = threadIdx.x;
   const int blob_bytes = reinterpret_cast<const SampledHeader*>(blob_g)->bytes;
@@ -106,7 +106,8 @@ SampledCostKernel(const unsigned char* __restrict__ blob_g, const ProblemConst* 
     double I[9];
 #pragma unroll
     for (int i = 0; i < 9; ++i) I[i] = pcs ? __ldg(&pcs[prob].I[i]) : H.I[i];
-    for (int it = tid; it < H.n_items; it += kSampledThreads) SampledItem(V, W, I, it);
+    const double* p_ref_B = pref ? pref + 12 * static_cast<size_t>(prob) : H.p_ref_B;
+    for (int it = tid; it < H.n_items; it += kSampledThreads) SampledItem(V, W, I, p_ref_B, it);
     __syncthreads();
     TB_COST_CLK(4);
     // summands (threads from the front) and, for the ee-schedule gradient, phase sums (threads from the back)
@@ -126,6 +127,11 @@ SampledCostKernel(const unsigned char* __restrict__ blob_g, const ProblemConst* 
     }
     TB_COST_CLK(7);
     __syncthreads();
+    if ((what & 2) && H.n_comb > 0) {                  // columns that several terms write: parked sums, added in term order
+      double* gp = grad_out + static_cast<size_t>(prob) * H.n_vars;
+      for (int i = tid; i < H.n_comb; i += kSampledThreads) SampledCombine(V, W, gp, i);
+      __syncthreads();                                 // the scratch is reused by the next problem's jobs
+    }
     TB_COST_CLK(8);
     if ((what & 1) && tid == 0) {
       double f = f_out[prob];
@@ -135,8 +141,8 @@ SampledCostKernel(const unsigned char* __restrict__ blob_g, const ProblemConst* 
   }
 }
 
-cudaError_t LaunchSampledCost(const unsigned char* blob_dev, size_t shared_bytes, const ProblemConst* pcs, int what,
-                              const double* x, double* f, double* grad, int n_problems, int sms, cudaStream_t stream) {
+cudaError_t LaunchSampledCost(const unsigned char* blob_dev, size_t shared_bytes, const ProblemConst* pcs, const double* pref,
+                              int what, const double* x, double* f, double* grad, int n_problems, int sms, cudaStream_t stream) {
   if (n_problems <= 0 || !blob_dev) return cudaSuccess;
   cudaError_t err = cudaFuncSetAttribute(SampledCostKernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(shared_bytes));
@@ -149,7 +155,7 @@ cudaError_t LaunchSampledCost(const unsigned char* blob_dev, size_t shared_bytes
   }
   const int max_ctas = sms * occ;
   const int grid = n_problems < max_ctas ? n_problems : max_ctas;
-  SampledCostKernel<<<grid, kSampledThreads, shared_bytes, stream>>>(blob_dev, pcs, what, x, f, grad, n_problems);
+  SampledCostKernel<<<grid, kSampledThreads, shared_bytes, stream>>>(blob_dev, pcs, pref, what, x, f, grad, n_problems);
   return cudaGetLastError();
 }
 
@@ -215,11 +221,11 @@ cudaError_t LaunchCostStatic(const CostTables& h, const SampledCost& sc, int dev
   c.weights = weights;
   err = LaunchCost(c, what, x, f, grad, n_problems, 16 * sms, stream);
   if (err != cudaSuccess || sc.blob.empty()) return err;
-  // the time-discretised terms: tables after the weights, inertia from the class spec (no per-problem constants here)
+  // the time-discretised terms: tables after the weights, inertia and swing reference positions from the class spec (no per-problem constants here)
   unsigned char* blob = base + kCostStaticSampledOff;
   err = cudaMemcpyAsync(blob, sc.blob.data(), sc.blob.size(), cudaMemcpyHostToDevice, stream);
   if (err != cudaSuccess) return err;
-  return LaunchSampledCost(blob, sc.shared_bytes, nullptr, what, x, f, grad, n_problems, sms, stream);
+  return LaunchSampledCost(blob, sc.shared_bytes, nullptr, nullptr, what, x, f, grad, n_problems, sms, stream);
 }
 
 }  // namespace tb

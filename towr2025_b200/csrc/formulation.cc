@@ -140,6 +140,9 @@ void SpecDefaults(towr_b200_spec* s) {
   s->dt_cost_energy = 0.02;               // parameters.cc:69-71
   s->energy_cost_torque_weight = 1.0;
   s->dt_cost_ang_mom = 0.02;
+  s->enable_swing_ee_base_pos_tracking = 0;            // parameters.h:233-235
+  s->swing_ee_base_pos_tracking_weight = 1e-2;
+  s->dt_cost_swing_ee_base_pos_tracking = 0.05;
   for (int i = 0; i < 3; ++i)
     s->bounds_final_lin_pos[i] = s->bounds_final_lin_vel[i] = s->bounds_final_ang_pos[i] = s->bounds_final_ang_vel[i] = 1;
 }

@@ -7,6 +7,7 @@
 #include <stdexcept>
 
 #include "structure.h"
+#include "cost.h"
 #include "terrain.h"
 
 namespace tb {
@@ -249,6 +250,18 @@ void ProblemConBounds(const HostProgram& hp, const towr_b200_spec& s, double* L,
     L[r] = lo;
     U[r] = up;
   }
+}
+
+// NlpFormulation::GetCosts (nlp_formulation.cc:616-620): the foot's initial position in the initial base frame
+void SwingReferenceB(const towr_b200_spec& s, double out[12]) {
+  double R[3][3];
+  EulerToR(V3{{s.initial_base_ang[0], s.initial_base_ang[1], s.initial_base_ang[2]}}, R);
+  for (int e = 0; e < 4; ++e)
+    for (int i = 0; i < 3; ++i) {
+      const double r[3] = {s.initial_ee_W[e][0] - s.initial_base_lin[0], s.initial_ee_W[e][1] - s.initial_base_lin[1],
+                           s.initial_ee_W[e][2] - s.initial_base_lin[2]};
+      out[3 * e + i] = e < s.n_ee ? (R[0][i] * r[0] + R[1][i] * r[1]) + R[2][i] * r[2] : 0.0;   // row i of R^T
+    }
 }
 
 void FillProblemConst(const towr_b200_spec& s, ProblemConst& pc) {

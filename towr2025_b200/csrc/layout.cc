@@ -178,6 +178,9 @@ void ValidateSpec(const towr_b200_spec& s) {
     }
   }
   if (s.n_costs < 0 || s.n_costs > TOWR_B200_MAX_COSTS) throw std::runtime_error("bad n_costs");
+  if (s.enable_swing_ee_base_pos_tracking &&
+      (!std::isfinite(s.swing_ee_base_pos_tracking_weight) || !std::isfinite(s.dt_cost_swing_ee_base_pos_tracking)))
+    throw std::runtime_error("EEBasePosCost: non-finite weight / sampling period");
   for (int c = 0; c < s.n_costs; ++c) {
     if (s.cost_ids[c] < TOWR_B200_COST_FORCES || s.cost_ids[c] > TOWR_B200_COST_ANG_MOM)
       throw std::runtime_error("cost not defined!");   // nlp_formulation.cc:644

@@ -21,6 +21,7 @@ struct SampledView {
   const uint16_t* poly_spline;
   const double* fix_t;
   const uint16_t* fix_seg;
+  const int *comb_col, *comb_ptr, *comb_src;
 };
 
 __device__ __forceinline__ void Mat3Mul(const double A[9], const double B[9], double C[9]) {
@@ -34,7 +35,7 @@ __device__ __forceinline__ double Dot3(const double a[3], const double b[3]) { r
 
 // shared-memory work arrays of one CTA (one problem at a time), carved by SampledCarve
 struct SampledWork {
-  double *nodes, *coef, *prec, *pdur, *items, *inst, *fterm, *psum;
+  double *nodes, *coef, *prec, *pdur, *items, *inst, *fterm, *psum, *scratch;
   int *iseg, *k0, *k1;   // iseg per item: polynomial within the spline | phase << 16; k0 / k1 per polynomial: its samples
   int *pk0, *pk1;        // per (spline, phase) slot: the samples that fall into the phase
 };
@@ -42,12 +43,14 @@ struct SampledWork {
 // for optimised durations, the polynomial's end time within its spline (accumulated like Spline::GetSegmentID's `t += d`)
 enum { kPrT = 0, kPrT2, kPrT3, kPrR1, kPrR2, kPrR3, kPrR4, kPrT4, kPrEnd };
 
-// the item arrays of one term (N = n_splines * n_samples items, tm.rec doubles each):
-//   energy:  P[3N] the spline's value, t[N] local time, with optimised durations also AB[2N] = m . dx/dT, m . vel
-//   ang-mom: P[3N] d summand / d euler angle, t[N], X[3N] d summand / d euler rate, e[N] |L|^2
+// the item arrays of one term (N = item_splines * n_samples items, tm.rec doubles each):
+//   energy:      P[3N] the spline's value, t[N] local time, with optimised durations also X[2N] = m . dx/dT, m . vel
+//   ang-mom:     P[3N] d summand / d euler angle, t[N], X[3N] d summand / d euler rate, then e[N] = |L|^2
+//   ee-base-pos: P[3N] m b_R_w (the row vector of ee_base_pos_cost.cc:125), t[N] local time in the foot's motion
+//                spline, X[3N] d summand / d euler angle, then tb[N] local time in the base splines, e[N] = |e|^2
 struct SampledTermArrays { double *P, *t, *X; };
 __device__ __forceinline__ SampledTermArrays TermArrays(const SampledWork& W, const SampledTerm& tm) {
-  const int N = tm.n_splines * tm.n_samples;
+  const int N = tm.item_splines * tm.n_samples;
   SampledTermArrays A;
   A.P = W.items + tm.scratch0;
   A.t = A.P + 3 * N;
@@ -86,6 +89,9 @@ __device__ __forceinline__ SampledView MakeSampledView(const unsigned char* blob
   V.poly_spline = reinterpret_cast<const uint16_t*>(blob + H.off_poly_spline);
   V.fix_t = reinterpret_cast<const double*>(blob + H.off_fix_t);
   V.fix_seg = reinterpret_cast<const uint16_t*>(blob + H.off_fix_seg);
+  V.comb_col = reinterpret_cast<const int*>(blob + H.off_comb_col);
+  V.comb_ptr = reinterpret_cast<const int*>(blob + H.off_comb_ptr);
+  V.comb_src = reinterpret_cast<const int*>(blob + H.off_comb_src);
   return V;
 }
 
@@ -100,7 +106,8 @@ __device__ __forceinline__ SampledWork SampledCarve(const SampledHeader& H, unsi
   W.inst = W.items + H.item_doubles;                     // per sample of every term: the summand of f
   W.fterm = W.inst + H.n_times;
   W.psum = W.fterm + 8;                                  // per (spline, phase) slot: sum of m . dx/dT, sum of m . vel
-  W.iseg = reinterpret_cast<int*>(W.psum + 2 * H.n_phase_slots);
+  W.scratch = W.psum + 2 * H.n_phase_slots;              // sums of the jobs whose columns other terms write too
+  W.iseg = reinterpret_cast<int*>(W.scratch + H.n_scratch);
   W.k0 = W.iseg + H.n_items;
   W.k1 = W.k0 + H.n_polys;
   W.pk0 = W.k1 + H.n_polys;
@@ -180,30 +187,122 @@ __device__ __forceinline__ int TermOfSample(const SampledView& V, int k) {
   return ti;
 }
 
+// Spline::GetSegmentID / GetLocalTime (spline.cc:48-78) of sample k (global time tg) in spline sp: a table read where the
+// durations are class constants, the reference's search and one-by-one subtraction on the problem's own durations
+// otherwise.  Returns the polynomial within the spline; bit 15: the foot is in contact (class-constant durations only).
+__device__ __forceinline__ int LocateSample(const SampledView& V, const SampledWork& W, const SampledSpline& sp, int k, double tg,
+                                            double* t_local) {
+  if (!sp.rt) {
+    *t_local = V.fix_t[sp.fix0 + k];
+    return V.fix_seg[sp.fix0 + k];
+  }
+  const double* pr = W.prec + kSampledPolyRec * sp.poly0;
+  const double lim = tg - 1e-10;
+  int id = sp.n_polys - 1;
+#pragma unroll 4
+  for (int j = 0; j < sp.n_polys; ++j)
+    if (pr[j * kSampledPolyRec + kPrEnd] >= lim) { id = j; break; }
+  double t = tg;
+  for (int j = 0; j < id; ++j) t -= pr[j * kSampledPolyRec];
+  *t_local = t;
+  return id;
+}
+// the phase of foot ft the global time falls into, on the problem's own phase durations (phase_durations.cc:113-118)
+__device__ __forceinline__ int PhaseAt(const SampledWork& W, const SampledFoot& ft, double tg) {
+  int phase = ft.n_phases - 1;
+  double pacc = 0.0;
+  for (int j = 0; j < ft.n_phases; ++j) {
+    pacc += W.pdur[ft.phase0 + j];
+    if (pacc >= tg - 1e-10) { phase = j; break; }
+  }
+  return phase;
+}
+// Polynomial::GetPoint (polynomial.cc:47-61), position only
+__device__ __forceinline__ void SplinePos(const SampledWork& W, const SampledSpline& sp, int id, double t, double pos[3]) {
+  const double t2 = t * t, t3 = Cube(t);
+  const double* n0 = W.nodes + kSampledRec * (sp.node0 + id);
+  const double* cf = W.coef + kSampledRec * (sp.poly0 + id);
+#pragma unroll
+  for (int d = 0; d < 3; ++d) pos[d] = ((n0[d] + t * n0[3 + d]) + t2 * cf[d]) + t3 * cf[3 + d];
+}
+
+// EEBasePosCost (ee_base_pos_cost.cc:67-160), one item per sample: e = b_R_w (p_ee - p_base) - p_ref_B during swing
+__device__ __forceinline__ void SampledItemEEBasePos(const SampledView& V, const SampledWork& W, const SampledTerm& tm,
+                                                     const double* __restrict__ p_ref_B, int git) {
+  const SampledTermArrays A = TermArrays(W, tm);
+  const int K = tm.n_samples, k = git - tm.item0;
+  const SampledSpline& sm = V.splines[tm.spline0];       // the foot's motion, base-lin, base-ang
+  const SampledSpline& sl = V.splines[tm.spline0 + 1];
+  const SampledSpline& sa = V.splines[tm.spline0 + 2];
+  const double tg = V.times[tm.time0 + k];
+  double t_m, t_b;
+  int id_m = LocateSample(V, W, sm, k, tg, &t_m);
+  const int id_b = LocateSample(V, W, sl, k, tg, &t_b) & 0x7FFF;   // base-lin and base-ang share their durations
+  bool contact;
+  if (!sm.rt) {
+    contact = (id_m & 0x8000) != 0;
+    id_m &= 0x7FFF;
+  } else {                                               // PhaseDurations::IsContactPhase (phase_durations.cc:113-118)
+    const SampledFoot ft = V.feet[sm.foot];
+    const int ph = PhaseAt(W, ft, tg);
+    contact = (ph % 2 == 0) ? ft.contact_at_start != 0 : ft.contact_at_start == 0;
+  }
+  atomicMin(W.k0 + sm.poly0 + id_m, k);
+  atomicMax(W.k1 + sm.poly0 + id_m, k + 1);
+  atomicMin(W.k0 + sl.poly0 + id_b, k);
+  atomicMax(W.k1 + sl.poly0 + id_b, k + 1);
+  atomicMin(W.k0 + sa.poly0 + id_b, k);
+  atomicMax(W.k1 + sa.poly0 + id_b, k + 1);
+  W.iseg[git] = id_m | (id_b << 12) | (contact ? 0 : 1 << 24);   // bit 24: a swing sample (the only ones that count, :78-80)
+  A.t[k] = t_m;
+  double* tb_ = A.X + 3 * K;
+  double* e2 = tb_ + K;
+  tb_[k] = t_b;
+  if (contact) {
+    e2[k] = 0.0;
+    return;
+  }
+  double p_ee[3], p_base[3], eul[3], r_W[3], p_B[3], e[3], m[3], mW[3];
+  SplinePos(W, sm, id_m, t_m, p_ee);
+  SplinePos(W, sl, id_b, t_b, p_base);
+  SplinePos(W, sa, id_b, t_b, eul);
+#pragma unroll
+  for (int d = 0; d < 3; ++d) r_W[d] = p_ee[d] - p_base[d];
+  const Trig tr = MakeTrig(eul);
+  double R[9];
+  RotationMatrix(tr, R);
+  MatTVec3(R, r_W, p_B);                                 // b_R_w = w_R_b^T
+#pragma unroll
+  for (int d = 0; d < 3; ++d) { e[d] = p_B[d] - p_ref_B[3 * tm.foot + d]; m[d] = sm.mscale * e[d]; }
+  e2[k] = Dot3(e, e);
+  MatVec3(R, m, mW);                                     // (m b_R_w)(c) = sum_r m(r) R(c, r)   (:125)
+#pragma unroll
+  for (int d = 0; d < 3; ++d) A.P[3 * k + d] = mW[d];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {                          // m . d(b_R_w r_W)/d euler_j  (DerivOfRotVecMult, inverse; :143-150)
+    double D[9], a[3];
+    RotationMatrixDeriv(tr, j, D);
+    MatTVec3(D, r_W, a);
+    A.X[3 * k + j] = Dot3(m, a);
+  }
+}
+
 // ---- step 1: item `git` (all terms) = (spline, sample) of a term; I: the problem's body inertia
-__device__ __forceinline__ void SampledItem(const SampledView& V, const SampledWork& W, const double I[9], int git) {
+__device__ __forceinline__ void SampledItem(const SampledView& V, const SampledWork& W, const double I[9],
+                                            const double* __restrict__ p_ref_B, int git) {
   const SampledTerm& tm = V.terms[TermOfItem(V, git)];
+  if (tm.kind == kSampledEEBasePos) {
+    SampledItemEEBasePos(V, W, tm, p_ref_B, git);
+    return;
+  }
   const SampledTermArrays A = TermArrays(W, tm);
   const int it = git - tm.item0;
   const int K = tm.n_samples;
   const int s = it / K, k = it - s * K;
   const SampledSpline& sp = V.splines[tm.spline0 + s];
   const double tg = V.times[tm.time0 + k];
-  int id;                                            // Spline::GetSegmentID / GetLocalTime (spline.cc:48-78)
   double t;
-  if (!sp.rt) {                                      // class constants
-    id = V.fix_seg[tm.fix0 + it];
-    t = V.fix_t[tm.fix0 + it];
-  } else {                                           // on the problem's own durations
-    const double* pr = W.prec + kSampledPolyRec * sp.poly0;
-    const double lim = tg - 1e-10;
-    id = sp.n_polys - 1;
-#pragma unroll 4
-    for (int j = 0; j < sp.n_polys; ++j)
-      if (pr[j * kSampledPolyRec + kPrEnd] >= lim) { id = j; break; }
-    t = tg;
-    for (int j = 0; j < id; ++j) t -= pr[j * kSampledPolyRec];
-  }
+  const int id = LocateSample(V, W, sp, k, tg, &t) & 0x7FFF;
   const int poly = sp.poly0 + id;
   atomicMin(W.k0 + poly, k);                         // the polynomial's samples are k0 .. k1 - 1 (time order)
   atomicMax(W.k1 + poly, k + 1);
@@ -241,13 +340,7 @@ __device__ __forceinline__ void SampledItem(const SampledView& V, const SampledW
                           ExactDiv((2 * t2) * (((3.0 * x0 - 3.0 * x1) + (2 * T) * v0) + T * v1), T3, r3);
         dxdT[d] = inner * (dx - prev * vel[d]);
       }
-      const SampledFoot ft = V.feet[sp.foot];
-      phase = ft.n_phases - 1;
-      double pacc = 0.0;
-      for (int j = 0; j < ft.n_phases; ++j) {
-        pacc += W.pdur[ft.phase0 + j];
-        if (pacc >= tg - 1e-10) { phase = j; break; }
-      }
+      phase = PhaseAt(W, V.feet[sp.foot], tg);
       A.X[2 * it] = Dot3(m, dxdT);
       A.X[2 * it + 1] = Dot3(m, vel);
       atomicMin(W.pk0 + sp.ps0 + phase, k);           // the phase's samples are pk0 .. pk1 - 1 (time order)
@@ -338,8 +431,10 @@ __device__ __forceinline__ void SampledSummand(const SampledView& V, const Sampl
       in += Dot3(f, f) + V.splines[tm.spline0 + 2 * e + 1].scale * Dot3(tau, tau);
     }
     v = tm.weight * in * tm.dtf;                     // :87
-  } else {
+  } else if (tm.kind == kSampledAngMom) {
     v = (tm.weight * tm.dtf) * A.X[3 * K + k];       // angular_momentum_cost.cc:97
+  } else {
+    v = tm.weight * A.X[4 * K + k];                  // ee_base_pos_cost.cc:92; 0 for the samples in contact (skipped there)
   }
   W.inst[gk] = v;
 }
@@ -351,12 +446,71 @@ __device__ __forceinline__ void SampledTermSum(const SampledView& V, const Sampl
   W.fterm[ti] = c;
 }
 
+// a job's sum for its i-th column: added to the gradient, or parked for SampledCombine when other terms write the column too
+__device__ __forceinline__ void EmitColumn(const SampledJob& jb, const SampledWork& W, double* __restrict__ gp, int i, double v) {
+  if (jb.col[i] < 0) return;
+  if (jb.slot < 0) gp[jb.col[i]] = gp[jb.col[i]] + v;
+  else W.scratch[jb.slot + i] = v;
+}
+// ---- step 4: column i of the shared columns: the parked sums added in term order
+__device__ __forceinline__ void SampledCombine(const SampledView& V, const SampledWork& W, double* __restrict__ gp, int i) {
+  double g = gp[V.comb_col[i]];
+  for (int k = V.comb_ptr[i]; k < V.comb_ptr[i + 1]; ++k) g = g + W.scratch[V.comb_src[k]];
+  gp[V.comb_col[i]] = g;
+}
+
 // ---- step 3: gradient columns of job j (all terms), added to gp (the problem's dense gradient)
 __device__ __forceinline__ void SampledJobGradient(const SampledView& V, const SampledWork& W, double* __restrict__ gp, int j) {
   const SampledJob jb = V.jobs[j];
   const SampledTerm& tm = V.terms[jb.kind >> 8];
   const SampledTermArrays A = TermArrays(W, tm);
   const int K = tm.n_samples;
+  if (tm.kind == kSampledEEBasePos) {
+    // EEBasePosCost: swing samples only (:78-80, :112-114); base-lin gets -m b_R_w, base-ang m . d(b_R_w r_W)/d euler
+    // (:133-150), the foot's motion variables m b_R_w (:123-131); position weights only, no ee-schedule block
+    const SampledSpline& sp = V.splines[tm.spline0 + jb.spline];
+    const int* seg = W.iseg + tm.item0;
+    const double* tb_ = A.X + 3 * K;
+    if ((jb.kind & 0xFF) == kJobNode) {
+      double gpos[3] = {0.0, 0.0, 0.0}, gvel[3] = {0.0, 0.0, 0.0};
+      for (int side = 1; side >= 0; --side) {
+        const int id = jb.node - side;
+        if (id < 0 || id >= sp.n_polys) continue;
+        const double* q = W.prec + kSampledPolyRec * (sp.poly0 + id);
+        for (int k = W.k0[sp.poly0 + id]; k < W.k1[sp.poly0 + id]; ++k) {
+          if (!(seg[k] >> 24 & 1)) continue;
+          const double wp = HermiteWeight(0, side, 0, tb_[k], q), wv = HermiteWeight(0, side, 1, tb_[k], q);
+#pragma unroll
+          for (int dim = 0; dim < 3; ++dim) {
+            const double v = jb.spline == 1 ? -A.P[3 * k + dim] : A.X[3 * k + dim];
+            gpos[dim] += v * wp;
+            gvel[dim] += v * wv;
+          }
+        }
+      }
+#pragma unroll
+      for (int dim = 0; dim < 3; ++dim) {
+        EmitColumn(jb, W, gp, dim, gpos[dim]);
+        EmitColumn(jb, W, gp, 3 + dim, gvel[dim]);
+      }
+    } else {                                         // kJobColumn: a variable of the foot's motion, its node values in order
+      double g = 0.0;
+      for (int r = 0; r < jb.aux; ++r) {
+        const int node = jb.col[1 + r] & 0xFFFF, deriv = (jb.col[1 + r] >> 16) & 0xF, dim = (jb.col[1 + r] >> 20) & 0xF;
+        for (int side = 1; side >= 0; --side) {
+          const int id = node - side;
+          if (id < 0 || id >= sp.n_polys) continue;
+          const double* q = W.prec + kSampledPolyRec * (sp.poly0 + id);
+          for (int k = W.k0[sp.poly0 + id]; k < W.k1[sp.poly0 + id]; ++k) {
+            if (!(seg[k] >> 24 & 1)) continue;
+            g += A.P[3 * k + dim] * HermiteWeight(0, side, deriv, A.t[k], q);
+          }
+        }
+      }
+      EmitColumn(jb, W, gp, 0, g);
+    }
+    return;
+  }
   if ((jb.kind & 0xFF) == kJobNode) {
     // the samples of the two polynomials that meet in the node, in time order: the reference's accumulation into
     // jac.coeffRef(0, col) over its sample loop.  gpos / gvel: the columns of the node's position / velocity values
@@ -398,8 +552,8 @@ __device__ __forceinline__ void SampledJobGradient(const SampledView& V, const S
     }
 #pragma unroll
     for (int dim = 0; dim < 3; ++dim) {
-      if (jb.col[dim] >= 0) gp[jb.col[dim]] = gp[jb.col[dim]] + gpos[dim];
-      if (jb.col[3 + dim] >= 0) gp[jb.col[3 + dim]] = gp[jb.col[3 + dim]] + gvel[dim];
+      EmitColumn(jb, W, gp, dim, gpos[dim]);
+      EmitColumn(jb, W, gp, 3 + dim, gvel[dim]);
     }
   } else {
     // column `ph` of the foot's ee-schedule from the phase sums (SampledPhaseSum): force spline, then torque spline
@@ -414,7 +568,7 @@ __device__ __forceinline__ void SampledJobGradient(const SampledView& V, const S
       c -= ps[2 * last];
       g += c;
     }
-    gp[jb.col[0]] = gp[jb.col[0]] + g;
+    EmitColumn(jb, W, gp, 0, g);
   }
 }
 

@@ -1053,6 +1053,8 @@ std::string StructureSignature(const towr_b200_spec& s, int curvature_dims) {
     if (s.cost_ids[c] == TOWR_B200_COST_ENERGY) o << ":" << s.dt_cost_energy << ":" << s.energy_cost_torque_weight;
     if (s.cost_ids[c] == TOWR_B200_COST_ANG_MOM) o << ":" << s.dt_cost_ang_mom;
   }
+  if (s.enable_swing_ee_base_pos_tracking && s.swing_ee_base_pos_tracking_weight > 0.0)
+    o << "|swingpos" << s.swing_ee_base_pos_tracking_weight << ":" << s.dt_cost_swing_ee_base_pos_tracking;
   return o.str();
 }
 
