@@ -36,6 +36,12 @@ extern "C" {
 #define TOWR_B200_MAX_PHASES 32
 #define TOWR_B200_MAX_CONSTRAINTS 16
 #define TOWR_B200_MAX_COSTS 4
+#define TOWR_B200_MAX_NODE_COSTS 32
+#define TOWR_B200_MAX_EE_LINEAR 4
+#define TOWR_B200_MAX_EE_LINEAR_TERMS 4
+/* variable sets a NodeCost term can name (variable_names.h: base-lin, base-ang, ee-motion_, ee-ang_, ee-force_, ee-torque_) */
+enum { TOWR_B200_NODES_BASE_LIN = 0, TOWR_B200_NODES_BASE_ANG = 1, TOWR_B200_NODES_EE_MOTION = 2, TOWR_B200_NODES_EE_ANG = 3,
+       TOWR_B200_NODES_EE_FORCE = 4, TOWR_B200_NODES_EE_TORQUE = 5 };
 #define TOWR_B200_MAX_STANCES 17   /* stance phases of one foot: (MAX_PHASES + 1) / 2 */
 
 typedef enum towr_b200_status {
@@ -128,6 +134,26 @@ typedef struct towr_b200_spec {
    * period are class properties; the reference position comes from each problem's initial_base_ / initial_ee_W. */
   int enable_swing_ee_base_pos_tracking;
   double swing_ee_base_pos_tracking_weight, dt_cost_swing_ee_base_pos_tracking;
+  /* Individual NodeCost terms (towr::NodeCost(nodes_id, deriv, dim, weight), costs/node_cost.cc:36-45), for callers that
+   * add them one by one instead of through a cost family: the reference's hand-built formulations do
+   * (test/squat_jump_example.cc:205-211, yaw_spin_example.cc:171-176, procedural_example.cc:243-249).  Term i:
+   * weight * (node value)^2 over the nodes of variable set node_cost_set[i] (TOWR_B200_NODES_*; foot node_cost_ee[i] for
+   * the ee sets), derivative node_cost_deriv[i] (0 position, 1 velocity), dimension node_cost_dim[i].  Added after the
+   * families of cost_ids.  Class properties. */
+  int n_node_costs;
+  int node_cost_set[TOWR_B200_MAX_NODE_COSTS], node_cost_ee[TOWR_B200_MAX_NODE_COSTS];
+  int node_cost_deriv[TOWR_B200_MAX_NODE_COSTS], node_cost_dim[TOWR_B200_MAX_NODE_COSTS];
+  double node_cost_weight[TOWR_B200_MAX_NODE_COSTS];
+  /* params_.ee_linear_constraints_ (parameters.h:315-327; constraints/ee_linear_constraint.cc): definition i keeps
+   * |sum_j coeff_j * spline_{ee_j}(t).at(deriv)(dim_j)| <= tolerance at t = 0, dt, ...; target 0 = the feet's motion splines,
+   * 1 = their angle splines; deriv 0 = kPos, 1 = kVel.  Appended after the constraints of `constraints`
+   * (nlp_formulation.cc:373-375).  Class properties (the tolerance too: it is a row bound of the class's definition). */
+  int n_ee_linear;
+  int ee_linear_target[TOWR_B200_MAX_EE_LINEAR], ee_linear_deriv[TOWR_B200_MAX_EE_LINEAR], ee_linear_n_terms[TOWR_B200_MAX_EE_LINEAR];
+  int ee_linear_term_ee[TOWR_B200_MAX_EE_LINEAR][TOWR_B200_MAX_EE_LINEAR_TERMS];
+  int ee_linear_term_dim[TOWR_B200_MAX_EE_LINEAR][TOWR_B200_MAX_EE_LINEAR_TERMS];
+  double ee_linear_term_coeff[TOWR_B200_MAX_EE_LINEAR][TOWR_B200_MAX_EE_LINEAR_TERMS];
+  double ee_linear_tolerance[TOWR_B200_MAX_EE_LINEAR], ee_linear_dt[TOWR_B200_MAX_EE_LINEAR];
 } towr_b200_spec;
 
 const char* towr_b200_last_error(void);

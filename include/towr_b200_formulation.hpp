@@ -160,8 +160,19 @@ class Parameters {
   std::vector<int> rom_swing_relax_dims_;
   enum AngularRepresentation { EulerZYX, RotationVector };
   AngularRepresentation angular_rep_ = EulerZYX;
-  // counts only: a non-empty list is refused by ToSpec (base waypoints, EELinearConstraint are not evaluated)
-  int n_base_waypoints_ = 0, n_ee_linear_constraints_ = 0;
+  // parameters.h:315-327
+  struct EELinearConstraintDef {
+    struct Term { int ee; int dim; double coeff; };
+    enum Target { Motion, Angle };
+    Target target = Motion;
+    Dx deriv = kPos;
+    std::vector<Term> terms;
+    double tolerance = 0.0;
+    double dt = 0.1;
+  };
+  std::vector<EELinearConstraintDef> ee_linear_constraints_;
+  // count only: a non-empty list is refused by ToSpec (base waypoints are not evaluated)
+  int n_base_waypoints_ = 0;
 
   void OptimizePhaseDurations() { constraints_.push_back(TotalTime); }          // parameters.cc:107-111
   int GetPhaseCount(EEID ee) const { return static_cast<int>(ee_phase_durations_.at(ee).size()); }
@@ -212,7 +223,7 @@ inline towr_b200_spec ToSpec(const ref::NlpFormulation& f) {
   if (!P.ee_swing_height_min_.empty() || !P.ee_swing_height_max_.empty()) throw std::runtime_error("unsupported: per-foot swing height bounds");
   if (!P.rom_swing_relax_dims_.empty()) throw std::runtime_error("unsupported: rom_swing_relax_dims_");
   if (P.n_base_waypoints_ != 0) throw std::runtime_error("unsupported: base waypoints");
-  if (P.n_ee_linear_constraints_ != 0) throw std::runtime_error("unsupported: EELinearConstraint");
+  if (static_cast<int>(P.ee_linear_constraints_.size()) > TOWR_B200_MAX_EE_LINEAR) throw std::length_error("too many EELinearConstraint definitions");
   if (P.enable_stance_rpy_tracking)
     for (const auto& v : P.ee_stance_rpy_)
       if (!v.empty()) throw std::runtime_error("unsupported: ee_stance_rpy_ tracking");
@@ -247,6 +258,21 @@ inline towr_b200_spec ToSpec(const ref::NlpFormulation& f) {
   s.dt_constraint_base_motion = P.dt_constraint_base_motion_;
   s.dt_constraint_force = P.dt_constraint_force_;
   s.dt_constraint_torque = P.dt_constraint_torque_;
+  s.n_ee_linear = static_cast<int>(P.ee_linear_constraints_.size());      // the backend refuses Angle targets / optimised durations
+  for (int i = 0; i < s.n_ee_linear; ++i) {
+    const ref::Parameters::EELinearConstraintDef& d = P.ee_linear_constraints_[i];
+    if (static_cast<int>(d.terms.size()) > TOWR_B200_MAX_EE_LINEAR_TERMS) throw std::length_error("too many EELinearConstraint terms");
+    s.ee_linear_target[i] = d.target == ref::Parameters::EELinearConstraintDef::Angle ? 1 : 0;
+    s.ee_linear_deriv[i] = static_cast<int>(d.deriv);
+    s.ee_linear_n_terms[i] = static_cast<int>(d.terms.size());
+    for (size_t j = 0; j < d.terms.size(); ++j) {
+      s.ee_linear_term_ee[i][j] = d.terms[j].ee;
+      s.ee_linear_term_dim[i][j] = d.terms[j].dim;
+      s.ee_linear_term_coeff[i][j] = d.terms[j].coeff;
+    }
+    s.ee_linear_tolerance[i] = d.tolerance;
+    s.ee_linear_dt[i] = d.dt;
+  }
   s.dt_cost_energy = P.dt_cost_energy_;
   s.energy_cost_torque_weight = P.energy_cost_torque_weight_;
   s.dt_cost_ang_mom = P.dt_cost_ang_mom_;

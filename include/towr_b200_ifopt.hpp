@@ -63,6 +63,17 @@ class NlpFormulation {
     spec_.cost_ids[spec_.n_costs] = name;
     spec_.cost_weights[spec_.n_costs++] = weight;
   }
+  // nlp.AddCostSet(std::make_shared<NodeCost>(nodes_id, deriv, dim, weight))   (node_cost.cc:36-45; the reference's
+  // hand-built examples, test/squat_jump_example.cc:205-211); nodes: TOWR_B200_NODES_*, ee: the foot of an ee set
+  void AddNodeCost(int nodes, int ee, int deriv, int dim, double weight) {
+    if (spec_.n_node_costs >= TOWR_B200_MAX_NODE_COSTS) throw std::runtime_error("too many NodeCost terms");
+    const int i = spec_.n_node_costs++;
+    spec_.node_cost_set[i] = nodes;
+    spec_.node_cost_ee[i] = ee;
+    spec_.node_cost_deriv[i] = deriv;
+    spec_.node_cost_dim[i] = dim;
+    spec_.node_cost_weight[i] = weight;
+  }
   towr_b200_spec& params() { return spec_; }
   const towr_b200_spec& params() const { return spec_; }
 

@@ -426,4 +426,33 @@ void BaseMotionConstraint::UpdateJacobianAtInstance(double t, int k, const std::
   if (var_set == id::base_lin_nodes) jac.setMiddleRows(GetRow(k, LX), base_linear_->GetJacobianWrtNodes(t, kPos));
 }
 
+
+// ---- constraints/ee_linear_constraint.cc:5-48
+EELinearConstraint::EELinearConstraint(const std::vector<Term>& terms, const std::vector<std::shared_ptr<NodeSpline>>& splines,
+                                       const std::vector<std::string>& var_names, Dx deriv, double tolerance, double T, double dt)
+    : TimeDiscretizationConstraint(T, dt, "ee-linear"), terms_(terms), splines_(splines), var_names_(var_names), deriv_(deriv),
+      tolerance_(tolerance) {
+  SetRows(GetNumberOfNodes());
+}
+// :20-29
+void EELinearConstraint::UpdateConstraintAtInstance(double t, int k, Vec& g) const {
+  double val = 0.0;
+  for (const auto& term : terms_) {
+    auto pt = splines_.at(term.ee)->GetPoint(t);
+    double v = (deriv_ == kPos) ? pt.p(term.dim) : pt.v(term.dim);
+    val += term.coeff * v;
+  }
+  g[k] = val;
+}
+// :31-34
+void EELinearConstraint::UpdateBoundsAtInstance(double, int k, VecBound& bounds) const { bounds.at(k) = Bounds(-tolerance_, tolerance_); }
+// :36-48; jac.row(k) += coeff * jac_nodes.row(dim): Eigen's sparse row sum stores the union of both patterns
+void EELinearConstraint::UpdateJacobianAtInstance(double t, int k, const std::string& var_set, SpMat& jac) const {
+  for (const auto& term : terms_)
+    if (var_set == var_names_.at(term.ee)) {
+      SpMat jac_nodes = splines_.at(term.ee)->GetJacobianWrtNodes(t, deriv_);
+      jac.setRow(k, jac.row(k) + term.coeff * jac_nodes.row(term.dim));
+    }
+}
+
 }  // namespace orc

@@ -95,6 +95,23 @@ class BaseMotionConstraint : public TimeDiscretizationConstraint {
   VecBound node_bounds_;
 };
 
+// constraints/ee_linear_constraint.cc:5-48
+class EELinearConstraint : public TimeDiscretizationConstraint {
+ public:
+  struct Term { int ee; int dim; double coeff; };
+  EELinearConstraint(const std::vector<Term>& terms, const std::vector<std::shared_ptr<NodeSpline>>& splines,
+                     const std::vector<std::string>& var_names, Dx deriv, double tolerance, double T, double dt);
+ private:
+  void UpdateConstraintAtInstance(double t, int k, Vec& g) const override;
+  void UpdateBoundsAtInstance(double t, int k, VecBound& b) const override;
+  void UpdateJacobianAtInstance(double t, int k, const std::string& var_set, SpMat& jac) const override;
+  std::vector<Term> terms_;
+  std::vector<std::shared_ptr<NodeSpline>> splines_;
+  std::vector<std::string> var_names_;
+  Dx deriv_;
+  double tolerance_;
+};
+
 // constraints/terrain_constraint.cc:36-111
 class TerrainConstraint : public ConstraintSet {
  public:

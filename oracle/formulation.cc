@@ -207,6 +207,16 @@ std::vector<std::shared_ptr<ConstraintSet>> NlpFormulation::GetConstraints(const
   std::vector<std::shared_ptr<ConstraintSet>> constraints;
   for (auto name : params_.constraints_)
     for (auto& c : GetConstraint(name, s)) constraints.push_back(c);
+  for (const auto& def : params_.ee_linear_constraints_) {            // :373-375, MakeEELinearConstraint :682-704
+    std::vector<EELinearConstraint::Term> terms;
+    for (const auto& t : def.terms) terms.push_back({t.ee, t.dim, t.coeff});
+    const bool motion = def.target == Parameters::EELinearConstraintDef::Motion;
+    const auto& splines = motion ? s.ee_motion_ : s.ee_ang_;
+    std::vector<std::string> var_names;
+    for (int ee = 0; ee < params_.GetEECount(); ++ee) var_names.push_back((motion ? "ee-motion_" : "ee-ang_") + std::to_string(ee));
+    constraints.push_back(std::make_shared<EELinearConstraint>(terms, splines, var_names, def.deriv, def.tolerance,
+                                                               params_.GetTotalTime(), def.dt));
+  }
   return constraints;
 }
 

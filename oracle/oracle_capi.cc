@@ -24,6 +24,8 @@ struct orc_problem {
   Problem nlp;
   Vec x0;
   std::vector<V3> swing_ref_B;                 // EEBasePosCost reference positions, one per foot when the cost is on
+  struct NodeCostSpec { int set, ee, deriv, dim; double weight; };
+  std::vector<NodeCostSpec> node_costs;        // individual NodeCost terms of the spec
 };
 
 static NlpFormulation MakeFormulation(const orc_spec& s) {
@@ -72,6 +74,17 @@ static NlpFormulation MakeFormulation(const orc_spec& s) {
   p.enable_swing_ee_base_pos_tracking = s.enable_swing_ee_base_pos_tracking != 0;
   p.swing_ee_base_pos_tracking_weight_ = s.swing_ee_base_pos_tracking_weight;
   p.dt_cost_swing_ee_base_pos_tracking_ = s.dt_cost_swing_ee_base_pos_tracking;
+  p.ee_linear_constraints_.clear();
+  for (int i = 0; i < s.n_ee_linear && i < ORC_MAX_EE_LINEAR; ++i) {
+    Parameters::EELinearConstraintDef def;
+    def.target = s.ee_linear_target[i] ? Parameters::EELinearConstraintDef::Angle : Parameters::EELinearConstraintDef::Motion;
+    def.deriv = s.ee_linear_deriv[i] ? kVel : kPos;
+    for (int j = 0; j < s.ee_linear_n_terms[i] && j < ORC_MAX_EE_LINEAR_TERMS; ++j)
+      def.terms.push_back({s.ee_linear_term_ee[i][j], s.ee_linear_term_dim[i][j], s.ee_linear_term_coeff[i][j]});
+    def.tolerance = s.ee_linear_tolerance[i];
+    def.dt = s.ee_linear_dt[i];
+    p.ee_linear_constraints_.push_back(def);
+  }
   p.enable_stance_tracking = s.enable_stance_tracking != 0;   // orc_spec_defaults: off
   p.ee_stance_position_.clear();
   for (int e = 0; e < E; ++e) {
@@ -98,6 +111,12 @@ static NlpFormulation MakeFormulation(const orc_spec& s) {
 static void Build(orc_problem* p, const orc_spec& s) {
   p->formulation = MakeFormulation(s);
   for (int c = 0; c < s.n_costs && c < ORC_MAX_COSTS; ++c) p->costs.emplace_back(s.cost_ids[c], s.cost_weights[c]);
+  for (int c = 0; c < s.n_node_costs && c < ORC_MAX_NODE_COSTS; ++c) {
+    if (s.node_cost_set[c] < 0 || s.node_cost_set[c] > 5 || s.node_cost_deriv[c] < 0 || s.node_cost_deriv[c] > 1 ||
+        s.node_cost_dim[c] < 0 || s.node_cost_dim[c] > 2 || (s.node_cost_set[c] >= 2 && (s.node_cost_ee[c] < 0 || s.node_cost_ee[c] >= s.n_ee)))
+      throw std::runtime_error("bad NodeCost term");
+    p->node_costs.push_back({s.node_cost_set[c], s.node_cost_ee[c], s.node_cost_deriv[c], s.node_cost_dim[c], s.node_cost_weight[c]});
+  }
   for (auto& v : p->formulation.GetVariableSets(p->splines)) p->nlp.AddVariableSet(v);
   for (auto& c : p->formulation.GetConstraints(p->splines)) p->nlp.AddConstraintSet(c);
   p->x0 = p->nlp.GetVariableValues();
@@ -478,6 +497,11 @@ std::vector<NodeCostDef> CostTerms(const orc_problem* p) {
     } else {
       throw std::runtime_error("cost not defined!");     // :644
     }
+  }
+  static const char* const kSetNames[6] = {"base-lin", "base-ang", "ee-motion_", "ee-ang_", "ee-force_", "ee-torque_"};
+  for (const auto& nc : p->node_costs) {          // nlp.AddCostSet(std::make_shared<NodeCost>(...)), squat_jump_example.cc:205-211
+    const std::string id = nc.set < 2 ? std::string(kSetNames[nc.set]) : kSetNames[nc.set] + std::to_string(nc.ee);
+    terms.push_back({id, nc.deriv == 0 ? kPos : kVel, nc.dim, nc.weight});
   }
   return terms;
 }

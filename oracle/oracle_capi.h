@@ -13,6 +13,9 @@ extern "C" {
 #define ORC_MAX_PHASES 32
 #define ORC_MAX_CONSTRAINTS 16
 #define ORC_MAX_COSTS 4
+#define ORC_MAX_NODE_COSTS 32
+#define ORC_MAX_EE_LINEAR 4
+#define ORC_MAX_EE_LINEAR_TERMS 4
 #define ORC_MAX_STANCES 17
 #define ORC_MAX_TERRAIN_KNOTS 16
 
@@ -62,6 +65,19 @@ typedef struct orc_spec {
    * (parameters.h:233-235) */
   int enable_swing_ee_base_pos_tracking;
   double swing_ee_base_pos_tracking_weight, dt_cost_swing_ee_base_pos_tracking;
+  /* individual NodeCost(nodes_id, deriv, dim, weight) terms (node_cost.cc:36-45), as the hand-built examples add them
+   * (test/squat_jump_example.cc:205-211); set: 0 base-lin, 1 base-ang, 2 ee-motion_, 3 ee-ang_, 4 ee-force_, 5 ee-torque_ */
+  int n_node_costs;
+  int node_cost_set[ORC_MAX_NODE_COSTS], node_cost_ee[ORC_MAX_NODE_COSTS];
+  int node_cost_deriv[ORC_MAX_NODE_COSTS], node_cost_dim[ORC_MAX_NODE_COSTS];
+  double node_cost_weight[ORC_MAX_NODE_COSTS];
+  /* Parameters::ee_linear_constraints_ (parameters.h:315-327): target 0 Motion / 1 Angle, deriv 0 kPos / 1 kVel */
+  int n_ee_linear;
+  int ee_linear_target[ORC_MAX_EE_LINEAR], ee_linear_deriv[ORC_MAX_EE_LINEAR], ee_linear_n_terms[ORC_MAX_EE_LINEAR];
+  int ee_linear_term_ee[ORC_MAX_EE_LINEAR][ORC_MAX_EE_LINEAR_TERMS];
+  int ee_linear_term_dim[ORC_MAX_EE_LINEAR][ORC_MAX_EE_LINEAR_TERMS];
+  double ee_linear_term_coeff[ORC_MAX_EE_LINEAR][ORC_MAX_EE_LINEAR_TERMS];
+  double ee_linear_tolerance[ORC_MAX_EE_LINEAR], ee_linear_dt[ORC_MAX_EE_LINEAR];
 } orc_spec;
 
 /* Parameters::Parameters() defaults (parameters.cc:40-105), enable_stance_tracking=false. */

@@ -1201,6 +1201,35 @@ class BaseMotionConstraint(TimeDiscretizationConstraint):
         return Sp.vstack([Sp.zeros(3, n), self.s.base_linear.jacobian_wrt_nodes(t, kPos)])
 
 
+class EELinearConstraint(TimeDiscretizationConstraint):
+    """constraints/ee_linear_constraint.cc:5-48: |sum_j coeff_j * spline_{ee_j}(t).at(deriv)(dim_j)| <= tolerance."""
+    rows_per_instance = 1
+
+    def __init__(self, terms, splines, var_names, deriv, tolerance, T, dt):
+        super().__init__(T, dt, "ee-linear")
+        self.terms, self.splines, self.var_names, self.deriv, self.tolerance = terms, splines, var_names, deriv, tolerance
+        self.finish()
+
+    def instance_values(self, t, k):                                  # :20-29
+        val = 0.0
+        for (ee, dim, coeff) in self.terms:
+            val += coeff * self.splines[ee].point(t)[self.deriv][dim]
+        return np.array([val])
+
+    def instance_bounds(self, t, k):                                  # :31-34
+        return [(-self.tolerance, self.tolerance)]
+
+    def depends_on(self, name):
+        return any(name == self.var_names[ee] for (ee, _, _) in self.terms)
+
+    def instance_block(self, t, k, name, n):                          # :36-48: jac.row(k) += coeff * jac_nodes.row(dim)
+        row = Sp.zeros(1, n)
+        for (ee, dim, coeff) in self.terms:
+            if name == self.var_names[ee]:
+                row = row + coeff * self.splines[ee].jacobian_wrt_nodes(t, self.deriv).row(dim)
+        return row
+
+
 def _accumulate_linear_form(J, b, dst_row, entries):                  # force_constraint_discretized.cc:36-49
     r, c, v = J.stored()
     for i in range(len(r)):
@@ -2078,6 +2107,14 @@ class Formulation:
                 self.con_sets.append(BaseHeightConstraint(self.terrain, 0.4, "base-lin"))
             else:
                 raise RuntimeError("constraint not defined!")
+        for i in range(int(s.n_ee_linear)):                           # :373-375, MakeEELinearConstraint :682-704
+            motion = int(s.ee_linear_target[i]) == 0
+            terms = [(int(s.ee_linear_term_ee[i][j]), int(s.ee_linear_term_dim[i][j]), float(s.ee_linear_term_coeff[i][j]))
+                     for j in range(int(s.ee_linear_n_terms[i]))]
+            self.con_sets.append(EELinearConstraint(
+                terms, sh.ee_motion if motion else sh.ee_ang,
+                [("ee-motion_%d" if motion else "ee-ang_%d") % ee for ee in range(n_ee)],
+                kVel if int(s.ee_linear_deriv[i]) else kPos, float(s.ee_linear_tolerance[i]), T, float(s.ee_linear_dt[i])))
         for c in self.con_sets:
             c.link(by_name)
         # GetCosts :604-681 (NodeCost terms only)
@@ -2100,6 +2137,12 @@ class Formulation:
                 self.costs.append(AngularMomentumCost(sh, self.model, w, float(s.dt_cost_ang_mom)))
             else:
                 raise RuntimeError("cost not defined!")
+        # individual NodeCost terms, as the hand-built examples add them (test/squat_jump_example.cc:205-211)
+        set_names = ("base-lin", "base-ang", "ee-motion_%d", "ee-ang_%d", "ee-force_%d", "ee-torque_%d")
+        for i in range(int(s.n_node_costs)):
+            k = int(s.node_cost_set[i])
+            name = set_names[k] if k < 2 else set_names[k] % int(s.node_cost_ee[i])
+            self.costs.append(NodeCost(name, int(s.node_cost_deriv[i]), int(s.node_cost_dim[i]), float(s.node_cost_weight[i])))
         # :612-626: one EEBasePosCost per foot, reference r_B0 = b_R_w0 (initial_ee_W - initial_base.lin.p)
         if int(s.enable_swing_ee_base_pos_tracking) and float(s.swing_ee_base_pos_tracking_weight) > 0.0:
             b_R_w0 = rotation_base_to_world(self.initial_base_ang[kPos]).T

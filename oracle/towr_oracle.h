@@ -395,6 +395,16 @@ struct Parameters {
   std::pair<double, double> bound_phase_duration_;
   Bounds base_rom_ax, base_rom_ay, base_rom_lz;
   std::vector<std::vector<std::vector<double>>> ee_stance_position_;
+  struct EELinearConstraintDef {        // parameters.h:315-327
+    struct Term { int ee; int dim; double coeff; };
+    enum Target { Motion, Angle };
+    Target target = Motion;
+    Dx deriv = kPos;
+    std::vector<Term> terms;
+    double tolerance = 0.0;
+    double dt = 0.1;
+  };
+  std::vector<EELinearConstraintDef> ee_linear_constraints_;
   void OptimizePhaseDurations() { constraints_.push_back(TotalTime); }
   Vec GetBasePolyDurations() const;
   int GetPhaseCount(int ee) const { return static_cast<int>(ee_phase_durations_.at(ee).size()); }

@@ -109,6 +109,50 @@ def sampled_spec(T, name, costs, dt_energy, torque_weight, dt_ang_mom, swing=Non
     return s
 
 
+def with_node_costs(s, terms):
+    """Individual NodeCost(nodes_id, deriv, dim, weight) terms: (set, foot, deriv, dim, weight)."""
+    s.n_node_costs = len(terms)
+    for i, (k, ee, deriv, dim, w) in enumerate(terms):
+        s.node_cost_set[i], s.node_cost_ee[i], s.node_cost_deriv[i], s.node_cost_dim[i], s.node_cost_weight[i] = k, ee, deriv, dim, w
+    return s
+
+
+def squat_jump_costs(s, w=1e-3):
+    """test/squat_jump_example.cc:205-211: NodeCost on the force and the torque node positions, every dimension."""
+    EE_FORCE, EE_TORQUE = 4, 5
+    return with_node_costs(s, [(k, 0, 0, d, w) for d in range(3) for k in (EE_FORCE, EE_TORQUE)])
+
+
+def test_individual_node_costs(product, oracle, emu):
+    """NodeCost terms named one by one (the reference's hand-built examples) in the oracle and in the kernel arithmetic;
+    a cost family equals its expansion into individual terms (nlp_formulation.cc:648-681)."""
+    T, O = product, oracle
+    DP = C.POINTER(C.c_double)
+    case = [c for c in CASES if c[0] == "monoped_squat_jump_durations"][0]
+    s = squat_jump_costs(mk(T, case))
+    st = T.Structure(s)
+    assert not T.Structure(mk(T, case)).accepts(s)              # the terms are part of the class
+    p = O.Problem(to_oracle_spec(O, s))
+    x = perturbed(st.x0(s), 4, 0.05)
+    f, g = np.zeros(1), np.zeros(st.n_vars)
+    assert emu.emu_eval_cost(C.byref(s), x.ctypes.data_as(DP), f.ctypes.data_as(DP), g.ctypes.data_as(DP)) == 0
+    assert f[0] > 0 and tol_ratio(f, np.array([p.eval_f(x)])) <= 1.0 and tol_ratio(g, p.eval_grad_f(x)) <= 1.0
+    # ForcesCostID(w) = force / torque positions at w and velocities at 0.1 w; EEMotionCostID(w) = velocities at w, w, 0.5 w
+    w = 1e-3
+    fam = O.Problem(to_oracle_spec(O, with_costs(mk(T, case), [(FORCES, w), (EE_MOTION, w)])))
+    terms = [(k, 0, deriv, d, w if deriv == 0 else 0.1 * w) for d in range(3) for deriv in (0, 1) for k in (4, 5)]
+    terms += [(2, 0, 1, 0, w), (2, 0, 1, 1, w), (2, 0, 1, 2, 0.5 * w)]
+    one = O.Problem(to_oracle_spec(O, with_node_costs(mk(T, case), terms)))
+    assert tol_ratio(np.array([one.eval_f(x)]), np.array([fam.eval_f(x)])) <= 1.0
+    assert tol_ratio(one.eval_grad_f(x), fam.eval_grad_f(x)) <= 1.0
+    bad = with_node_costs(mk(T, case), [(6, 0, 0, 0, 1.0)])
+    with pytest.raises(T.TowrB200Error):
+        T.Structure(bad)
+    bad = with_node_costs(mk(T, case), [(4, 1, 0, 0, 1.0)])    # the monoped has one foot
+    with pytest.raises(T.TowrB200Error):
+        T.Structure(bad)
+
+
 def test_oracle_sampled_cost_gradient_is_consistent(product, oracle):
     """EnergyCost / AngularMomentumCost: the gradient (incl. the ee-schedule columns) matches central differences of f."""
     T, O = product, oracle
@@ -154,14 +198,17 @@ def test_emulated_cost_kernels_match_oracle(product, oracle, emu, case):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", ["hopper_example", "anymal_trot", "biped_walk_durations"])
+@pytest.mark.parametrize("name", ["hopper_example", "anymal_trot", "biped_walk_durations", "monoped_squat_jump_durations"])
 def test_gpu_cost_matches_oracle(product, oracle, name):
     T, O = product, oracle
     if name == "hopper_example":
         s = hopper_spec(T)
     else:
         s = mk(T, [c for c in CASES if c[0] == name][0])
-    with_costs(s, [(FORCES, 1e-9), (EE_MOTION, 1e-4)])
+    if name == "monoped_squat_jump_durations":
+        squat_jump_costs(s)                                    # individual NodeCost terms, squat_jump_example.cc:205-211
+    else:
+        with_costs(s, [(FORCES, 1e-9), (EE_MOTION, 1e-4)])
     st = T.Structure(s)
     p = O.Problem(to_oracle_spec(O, s))
     n = 6

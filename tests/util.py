@@ -62,6 +62,12 @@ CASES = [
     # turn in yaw, the default constraint families :163-170) and test/squat_jump_example.cc with optimised timings
     ("monoped_yaw_spin_example", 0, 0, 1.7, (0.0, 0.0, 3.141592653589793), 0, (), False, {"phases": [[0.6, 0.5, 0.6]]}),
     ("monoped_squat_jump_durations", 0, 0, 1.5, (0.3, 0.0, 0.0), 0, (), True, {"phases": [[0.5, 0.4, 0.6]]}),
+    # EELinearConstraint (params_.ee_linear_constraints_, parameters.h:315-327): (target, deriv, [(ee, dim, coeff)], tolerance, dt)
+    ("biped_walk_ee_linear", 1, 0, 2.4, (1.0, 0.0, 0.1), 0, (), False,
+     {"ee_linear": [(0, 0, [(0, 0, 1.0), (1, 0, -1.0)], 0.3, 0.1),                        # |x_left - x_right| <= 0.3
+                    (0, 1, [(0, 2, 0.5), (1, 2, 0.5), (0, 1, 2.0), (0, 2, -0.25)], 0.2, 0.07)]}),   # velocities, a foot named twice
+    ("anymal_trot_ee_linear_block", 3, 1, 2.0, (1.0, 0.1, 0.0), 1, (TORQUE,), False,
+     {"ee_linear": [(0, 0, [(0, 1, 1.0), (1, 1, 1.0), (2, 1, -1.0), (3, 1, -1.0)], 0.05, 0.05)]}),
 ]
 
 
@@ -208,10 +214,23 @@ def mk(M, case, goal=None):
                 for i, d in enumerate(durations):
                     s.phase_durations[e][i] = d
             continue
+        if k == "ee_linear":
+            set_ee_linear(s, v)
+            continue
         setattr(s, k, v)
     if len(case) > 9:
         set_terrain_table(s, *case[9])
     return s
+
+
+def set_ee_linear(s, defs):
+    """params_.ee_linear_constraints_: (target, deriv, [(ee, dim, coeff)], tolerance, dt) per definition."""
+    s.n_ee_linear = len(defs)
+    for i, (target, deriv, terms, tol, dt) in enumerate(defs):
+        s.ee_linear_target[i], s.ee_linear_deriv[i], s.ee_linear_n_terms[i] = target, deriv, len(terms)
+        for j, (ee, dim, coeff) in enumerate(terms):
+            s.ee_linear_term_ee[i][j], s.ee_linear_term_dim[i][j], s.ee_linear_term_coeff[i][j] = ee, dim, coeff
+        s.ee_linear_tolerance[i], s.ee_linear_dt[i] = tol, dt
 
 
 def set_terrain_table(s, mode, xs, hs):

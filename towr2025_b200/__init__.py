@@ -71,6 +71,11 @@ class Spec(C.Structure):
         ("dt_cost_energy", C.c_double), ("energy_cost_torque_weight", C.c_double), ("dt_cost_ang_mom", C.c_double),
         ("enable_swing_ee_base_pos_tracking", C.c_int), ("swing_ee_base_pos_tracking_weight", C.c_double),
         ("dt_cost_swing_ee_base_pos_tracking", C.c_double),
+        ("n_node_costs", C.c_int), ("node_cost_set", C.c_int * 32), ("node_cost_ee", C.c_int * 32),
+        ("node_cost_deriv", C.c_int * 32), ("node_cost_dim", C.c_int * 32), ("node_cost_weight", C.c_double * 32),
+        ("n_ee_linear", C.c_int), ("ee_linear_target", C.c_int * 4), ("ee_linear_deriv", C.c_int * 4),
+        ("ee_linear_n_terms", C.c_int * 4), ("ee_linear_term_ee", (C.c_int * 4) * 4), ("ee_linear_term_dim", (C.c_int * 4) * 4),
+        ("ee_linear_term_coeff", (C.c_double * 4) * 4), ("ee_linear_tolerance", C.c_double * 4), ("ee_linear_dt", C.c_double * 4),
     ]
 
     def copy(self):

@@ -36,6 +36,9 @@ void BuildCostTables(const HostProgram& hp, const towr_b200_spec& s, CostTables&
       throw std::runtime_error("cost not defined!");         // nlp_formulation.cc:644
     }
   }
+  for (int c = 0; c < s.n_node_costs; ++c)                    // individual NodeCost(nodes_id, deriv, dim, weight) terms
+    terms.push_back({s.node_cost_set[c], s.node_cost_set[c] < kEEMotion ? -1 : s.node_cost_ee[c], s.node_cost_deriv[c],
+                     s.node_cost_dim[c], s.node_cost_weight[c]});
   o.n_terms = static_cast<int>(terms.size());
   std::vector<std::vector<double>> per_col(static_cast<size_t>(hp.n_vars));
   for (const Term& t : terms) {

@@ -232,6 +232,7 @@ void ProblemConBounds(const HostProgram& hp, const towr_b200_spec& s, double* L,
       case kBoundNone: lo = -kNoBound; up = +kNoBound; break;
       case kBoundTorqueX: lo = s.torque_tx_min; up = s.torque_tx_max; break;     // torque_constraint_discretized.cc:131-139
       case kBoundTorqueY: lo = s.torque_ty_min; up = s.torque_ty_max; break;
+      case kBoundEELinear: lo = -s.ee_linear_tolerance[b.dim]; up = s.ee_linear_tolerance[b.dim]; break;   // ee_linear_constraint.cc:31-34
       case kBoundTorqueNodeZ: {                          // torque_constraint.cc:94-112, evaluated on the initial guess
         const VarSet& fo = *hp.Find(kEEForce, b.ee);
         const VarSet& mo = *hp.Find(kEEMotion, b.ee);

@@ -788,6 +788,25 @@ __device__ __forceinline__ void ItemTerrainHard(const ItemCtx<L>& cx, const Item
   }
 }
 
+// EELinearConstraint (ee_linear_constraint.cc:20-29), one row per sample: g = sum over the terms of coeff * value of the
+// term's foot spline in one dimension (position or velocity).  sub terms; samples s0 .. s0 + sub - 1 in term order;
+// B[b0 + 3 j ..] = coeff, dimension, derivative.  The Jacobian entries are class constants (fixed durations only).
+template <class L>
+__device__ __forceinline__ void ItemEELinear(const ItemCtx<L>& cx, const ItemC& it) {
+  if (!cx.g) return;
+  const double* Bc = cx.T.B + it.b0;
+  double val = 0.0;
+  for (int j = 0; j < it.sub; ++j) {
+    Pt3 p;
+    EvalSpline<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + j, p);
+    const int dim = static_cast<int>(Bc[3 * j + 1]);
+    const double pv = dim == 0 ? p.p[0] : dim == 1 ? p.p[1] : p.p[2];
+    const double vv = dim == 0 ? p.v[0] : dim == 1 ? p.v[1] : p.v[2];
+    val += Bc[3 * j] * (Bc[3 * j + 2] != 0.0 ? vv : pv);
+  }
+  cx.g[it.row * L::RS] = val;
+}
+
 // Node-based TorqueConstraint (torque_constraint.cc:64-157): s0 = the stance torque node, aux = the ee-motion node at the
 // start of its phase (the foothold), b0 = the torque node at the start of the phase.  G: t1[3], t2[3], n[3], then
 // (tau_s . d b / d x, tau_s . d b / d y) for b = t1, t2, n with tau_s the start-of-phase torque (:141).
@@ -883,6 +902,9 @@ __device__ __forceinline__ void RunItem(const ItemCtx<L>& cx, const ItemC& it) {
       break;
     case kItemTorqueNode:
       if constexpr (L::CURV) ItemTorqueNode<L>(cx, it);
+      break;
+    case kItemEELinear:
+      if constexpr (L::CURV && !L::RT) ItemEELinear<L>(cx, it);
       break;
     case kItemTorque: ItemTorque<L>(cx, it); break;
     case kItemForceNode: ItemForceNode<L>(cx, it); break;

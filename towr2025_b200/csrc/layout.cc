@@ -178,6 +178,29 @@ void ValidateSpec(const towr_b200_spec& s) {
     }
   }
   if (s.n_costs < 0 || s.n_costs > TOWR_B200_MAX_COSTS) throw std::runtime_error("bad n_costs");
+  if (s.n_ee_linear < 0 || s.n_ee_linear > TOWR_B200_MAX_EE_LINEAR) throw std::runtime_error("bad n_ee_linear");
+  for (int i = 0; i < s.n_ee_linear; ++i) {
+    if (s.ee_linear_n_terms[i] < 1 || s.ee_linear_n_terms[i] > TOWR_B200_MAX_EE_LINEAR_TERMS) throw std::runtime_error("EELinearConstraint: 1..4 terms");
+    if (s.ee_linear_deriv[i] < 0 || s.ee_linear_deriv[i] > 1) throw std::runtime_error("EELinearConstraint: deriv must be kPos or kVel");
+    if (!(s.ee_linear_dt[i] > 0.0) || !std::isfinite(s.ee_linear_dt[i]) || !std::isfinite(s.ee_linear_tolerance[i]))
+      throw std::runtime_error("EELinearConstraint: bad dt / tolerance");
+    for (int j = 0; j < s.ee_linear_n_terms[i]; ++j)
+      if (s.ee_linear_term_ee[i][j] < 0 || s.ee_linear_term_ee[i][j] >= s.n_ee || s.ee_linear_term_dim[i][j] < 0 ||
+          s.ee_linear_term_dim[i][j] > 2 || !std::isfinite(s.ee_linear_term_coeff[i][j]))
+        throw std::runtime_error("EELinearConstraint: bad term (foot, dimension or coefficient)");
+    if (s.ee_linear_target[i] != 0) throw std::runtime_error("unsupported: EELinearConstraint on the ee-angle splines (Motion only)");
+    for (int c = 0; c < s.n_constraints; ++c)
+      if (s.constraints[c] == TOWR_B200_C_TOTAL_TIME)
+        throw std::runtime_error("unsupported: EELinearConstraint with optimised phase durations");
+  }
+  if (s.n_node_costs < 0 || s.n_node_costs > TOWR_B200_MAX_NODE_COSTS) throw std::runtime_error("bad n_node_costs");
+  for (int c = 0; c < s.n_node_costs; ++c) {
+    const int set = s.node_cost_set[c];
+    if (set < TOWR_B200_NODES_BASE_LIN || set > TOWR_B200_NODES_EE_TORQUE || s.node_cost_deriv[c] < 0 || s.node_cost_deriv[c] > 1 ||
+        s.node_cost_dim[c] < 0 || s.node_cost_dim[c] > 2 || !std::isfinite(s.node_cost_weight[c]) ||
+        (set >= TOWR_B200_NODES_EE_MOTION && (s.node_cost_ee[c] < 0 || s.node_cost_ee[c] >= s.n_ee)))
+      throw std::runtime_error("bad NodeCost term (set, foot, derivative, dimension or weight)");
+  }
   if (s.enable_swing_ee_base_pos_tracking &&
       (!std::isfinite(s.swing_ee_base_pos_tracking_weight) || !std::isfinite(s.dt_cost_swing_ee_base_pos_tracking)))
     throw std::runtime_error("EEBasePosCost: non-finite weight / sampling period");
@@ -200,6 +223,7 @@ void BuildLayout(const towr_b200_spec& s, HostProgram& hp) {
   for (int i = 0; i < s.n_constraints; ++i)
     if (s.constraints[i] == TOWR_B200_C_TERRAIN_HARD || (s.constraints[i] == TOWR_B200_C_TORQUE && !(s.dt_constraint_torque > 0.0)))
       hp.curvature_dims |= kClassTerrainHard;
+  if (s.n_ee_linear > 0) hp.curvature_dims |= kClassTerrainHard;   // ItemEELinear lives in the extended instantiations too
   const int E = s.n_ee;
   const std::vector<double> base_T = BasePolyDurations(s);
   const int n_base_nodes = static_cast<int>(base_T.size()) + 1;

@@ -27,6 +27,7 @@ int ItemBRun(int type, int sub) {
     case kItemTerrainHard: return 3 * sub;               // (J_pos, J_vel, dim) per stored column; 0 with optimised durations
     case kItemDynPre: case kItemDynFoot: case kItemDynWrench: case kItemDynJlin: case kItemDynCol: return 16;
     case kItemTorque: return 1;
+    case kItemEELinear: return 3 * sub;                  // (coeff, dimension, derivative) per term
     default: return 0;
   }
 }
@@ -132,6 +133,9 @@ void PackRange(HostProgram& hp, const std::vector<SegmentRec>& wide, int seg0, i
         break;
       case kItemRomFoot: add_sample(it.s[kSMotion + it.ee]); break;
       case kItemTerrainHard: add_sample(it.s[kSMotion + it.ee]); break;
+      case kItemEELinear:
+        for (int j = 0; j < it.sub; ++j) add_sample(it.s[j]);   // one sample per term, in term order
+        break;
       case kItemForce:
         add_sample(it.s[kSMotion + it.ee]);
         add_sample(it.s[kSForce + it.ee]);

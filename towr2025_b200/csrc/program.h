@@ -57,6 +57,7 @@ enum ItemType : int {
   kItemDynFoot,         // per (dynamic sample, foot): f_e, c - p_e slots and the foot's torque term f_e x (c - p_e) + tau_e
   kItemTerrainHard,     // terrain_constraint_hard.cc:50-132         1 row per (sample, foot), finished ee-motion columns
   kItemTorqueNode,      // torque_constraint.cc:64-157               3 rows per stance torque node (node-based variant)
+  kItemEELinear,        // ee_linear_constraint.cc:20-29             1 row per sample: sum of coeff * (foot spline value)
   // level 1: read the scratch slots of a level-0 item (ItemC::aux)
   kItemDynWrench,       // dynamic_constraint.cc:63-148: the 6 g rows of a dynamic sample (feet summed in order)
   kItemDynJlin,         // row (sub) of the finished base-lin angular block -sum_e Cross(f_e) J_pos of a dynamic sample
@@ -257,7 +258,8 @@ struct ConSet { std::string name; int row0, n_rows; };
 // what ConstraintSet::GetBounds returns for one row (values depend on per-problem model data)
 enum RowBoundKind { kBoundZero = 0, kBoundTerrainSwing, kBoundRom, kBoundForceNormal, kBoundLE0, kBoundGE0,
                     kBoundBaseHeight, kBoundTotalDuration, kBoundNone, kBoundTorqueX, kBoundTorqueY,
-                    kBoundTorqueNodeZ };   // +- k mu f_n with the start-of-phase force of the initial guess; dim = phase
+                    kBoundTorqueNodeZ,     // +- k mu f_n with the start-of-phase force of the initial guess; dim = phase
+                    kBoundEELinear };      // +- tolerance of EELinearConstraint definition `dim`
 struct RowBound { int kind, ee, dim; };
 
 // a run of consecutive segments with its own class tables (pack.cc): classes with few samples have one

@@ -262,6 +262,7 @@ class Builder {
   void EmitBaseRom();
   void EmitTerrainHard(int ee);
   void EmitTorqueNodes(int ee);
+  void EmitEELinear(int def);
   void EmitRomSplit();
   void EmitTotalDuration(int ee);
   void EmitSwing(int ee);
@@ -850,6 +851,51 @@ void Builder::EmitBaseRom() {
   EndSet();
 }
 
+// EELinearConstraint (ee_linear_constraint.cc:5-48, MakeEELinearConstraint nlp_formulation.cc:682-704), definition `def`:
+// one row per sample of its own dt, g = sum_j coeff_j * spline_{ee_j}(t).at(deriv)(dim_j), bounds +- tolerance; the row of
+// the Jacobian is sum_j coeff_j * (row dim_j of the foot's GetJacobianWrtNodes(t, deriv)), accumulated term by term
+// (`jac.row(k) += ...`): with class-constant durations every entry is a class constant.
+void Builder::EmitEELinear(int def) {
+  const int n_terms = s_.ee_linear_n_terms[def], deriv = s_.ee_linear_deriv[def];
+  const std::vector<double> ts = SampleTimes(hp_.total_time, s_.ee_linear_dt[def]);
+  BeginGroup();
+  BeginSet("ee-linear", static_cast<int>(ts.size()));
+  for (size_t k = 0; k < ts.size(); ++k) {
+    ItemRec it = NewItem(kItemEELinear);
+    it.row[0] = set_row0_ + static_cast<int>(k);
+    it.sub = static_cast<short>(n_terms);
+    std::vector<double> brun(3 * static_cast<size_t>(n_terms));
+    std::vector<std::pair<int, double>> row;               // column -> value, in order of first appearance
+    for (int j = 0; j < n_terms; ++j) {
+      const int ee = s_.ee_linear_term_ee[def][j], dim = s_.ee_linear_term_dim[def][j];
+      const double coeff = s_.ee_linear_term_coeff[def][j];
+      const VarSet& mo = Set(kEEMotion, ee);
+      const SplineAt am = At(mo, ts[k]);
+      it.s[j] = am.sample;
+      brun[3 * j] = coeff;
+      brun[3 * j + 1] = dim;
+      brun[3 * j + 2] = deriv;
+      for (const ColBasis& c : Columns(mo, am.poly, am.t_local)) {
+        if (c.dim != dim) continue;
+        const int col = mo.col0 + c.idx;
+        const double v = coeff * c.v[deriv];
+        bool found = false;
+        for (auto& e : row)
+          if (e.first == col) { e.second = e.second + v; found = true; }
+        if (!found) row.emplace_back(col, 0.0 + v);
+      }
+    }
+    it.b0 = AddBRun(brun);
+    hp_.items.push_back(it);
+    Bound(static_cast<int>(k), kBoundEELinear, 0, def);
+    for (const auto& e : row) {
+      Term tm; tm.g = kGOne; tm.b = AddB(e.second);
+      Add(static_cast<int>(k), e.first, tm);
+    }
+  }
+  EndSet();
+}
+
 // SwingConstraint (swing_constraint.cc:54-108): per swing node and dim in {x,y} a position and a velocity row
 void Builder::EmitSwing(int ee) {
   const VarSet& mo = Set(kEEMotion, ee);
@@ -1019,6 +1065,7 @@ void Builder::Run() {
       default: throw std::runtime_error("constraint not defined!");   // nlp_formulation.cc:396
     }
   }
+  for (int i = 0; i < s_.n_ee_linear; ++i) EmitEELinear(i);          // nlp_formulation.cc:373-375
   CloseSegment();
   hp_.nnz = static_cast<int>(hp_.entries.size());
 }
@@ -1053,6 +1100,14 @@ std::string StructureSignature(const towr_b200_spec& s, int curvature_dims) {
     if (s.cost_ids[c] == TOWR_B200_COST_ENERGY) o << ":" << s.dt_cost_energy << ":" << s.energy_cost_torque_weight;
     if (s.cost_ids[c] == TOWR_B200_COST_ANG_MOM) o << ":" << s.dt_cost_ang_mom;
   }
+  for (int i = 0; i < s.n_ee_linear; ++i) {
+    o << "|eelin" << s.ee_linear_target[i] << ":" << s.ee_linear_deriv[i] << ":" << s.ee_linear_tolerance[i] << ":" << s.ee_linear_dt[i];
+    for (int j = 0; j < s.ee_linear_n_terms[i]; ++j)
+      o << ":" << s.ee_linear_term_ee[i][j] << "," << s.ee_linear_term_dim[i][j] << "," << s.ee_linear_term_coeff[i][j];
+  }
+  for (int c = 0; c < s.n_node_costs; ++c)
+    o << "|nc" << s.node_cost_set[c] << ":" << (s.node_cost_set[c] < 2 ? -1 : s.node_cost_ee[c]) << ":" << s.node_cost_deriv[c] << ":"
+      << s.node_cost_dim[c] << ":" << s.node_cost_weight[c];
   if (s.enable_swing_ee_base_pos_tracking && s.swing_ee_base_pos_tracking_weight > 0.0)
     o << "|swingpos" << s.swing_ee_base_pos_tracking_weight << ":" << s.dt_cost_swing_ee_base_pos_tracking;
   return o.str();
