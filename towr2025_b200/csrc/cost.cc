@@ -1,4 +1,4 @@
-// cost.cc — host tables of the cost kernel (cost.h).
+// cost.cc — host tables of the two cost kernels (cost.h): the NodeCost weight table and the blob of the time-discretised terms.
 #include "cost.h"
 #include "structure.h"
 

@@ -1,4 +1,5 @@
-// cost.h — cost terms of a structure class (NodeCost, costs/node_cost.cc) as a column-compressed weight table.
+// cost.h — cost terms of a structure class: NodeCost (costs/node_cost.cc) as a column-compressed weight table, and the
+// time-discretised terms (EnergyCost, AngularMomentumCost, EEBasePosCost) as one blob of class tables (SampledCost).
 #pragma once
 #include <cstdint>
 #include <vector>

@@ -2,6 +2,8 @@
 // costs/node_cost.cc:36-76): f = sum over terms of weight * value^2 over the nodes of a set, gradient entry
 // weight * 2 * value at every optimised variable that writes such a node value (a stance variable that writes two
 // nodes is counted twice, as in the reference).  One CTA per problem; thread c owns column c of the dense gradient.
+// A second kernel (SampledCostKernel, below) adds the time-discretised terms: EnergyCost, AngularMomentumCost,
+// EEBasePosCost (costs/energy_cost.cc, angular_momentum_cost.cc, ee_base_pos_cost.cc).
 #include <cuda_runtime.h>
 
 #include <mutex>

@@ -1,5 +1,6 @@
 // sampled_cost.cuh — per-problem arithmetic of the time-discretised cost terms (cost.h): EnergyCost
-// (costs/energy_cost.cc:38-163) and AngularMomentumCost (costs/angular_momentum_cost.cc:39-208).  The kernel
+// (costs/energy_cost.cc:38-163), AngularMomentumCost (costs/angular_momentum_cost.cc:39-208) and EEBasePosCost
+// (costs/ee_base_pos_cost.cc:38-160).  The kernel
 // (cost_kernel.cu) strides these functions over a CTA's threads with a barrier between the steps; tests/emu replays them
 // serially on the host.
 #pragma once
@@ -31,7 +32,6 @@ __device__ __forceinline__ void Mat3Mul(const double A[9], const double B[9], do
     for (int j = 0; j < 3; ++j) C[3 * i + j] = (A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j]) + A[3 * i + 2] * B[6 + j];
 }
 __device__ __forceinline__ double Dot3(const double a[3], const double b[3]) { return (a[0] * b[0] + a[1] * b[1]) + a[2] * b[2]; }
-
 
 // shared-memory work arrays of one CTA (one problem at a time), carved by SampledCarve
 struct SampledWork {
