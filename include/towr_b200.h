@@ -147,7 +147,8 @@ typedef struct towr_b200_spec {
   /* params_.ee_linear_constraints_ (parameters.h:315-327; constraints/ee_linear_constraint.cc): definition i keeps
    * |sum_j coeff_j * spline_{ee_j}(t).at(deriv)(dim_j)| <= tolerance at t = 0, dt, ...; target 0 = the feet's motion splines,
    * 1 = their angle splines; deriv 0 = kPos, 1 = kVel.  Appended after the constraints of `constraints`
-   * (nlp_formulation.cc:373-375).  Class properties (the tolerance too: it is a row bound of the class's definition). */
+   * (nlp_formulation.cc:373-375), fixed or optimised durations.  Class properties (the tolerance too: it is a row bound of
+ * the class's definition). */
   int n_ee_linear;
   int ee_linear_target[TOWR_B200_MAX_EE_LINEAR], ee_linear_deriv[TOWR_B200_MAX_EE_LINEAR], ee_linear_n_terms[TOWR_B200_MAX_EE_LINEAR];
   int ee_linear_term_ee[TOWR_B200_MAX_EE_LINEAR][TOWR_B200_MAX_EE_LINEAR_TERMS];

@@ -158,8 +158,7 @@ def test_no_cpu_fallback(product):
 
 
 def test_ee_linear_constraint_rules(product):
-    """EELinearConstraint is built for the feet's motion splines with class-constant durations; the other variants of
-    parameters.h:315-327 are refused as unsupported, malformed definitions as argument errors."""
+    """EELinearConstraint definitions (parameters.h:315-327) are part of the class; malformed ones are argument errors."""
     from util import set_ee_linear
     T = product
     base = [c for c in CASES if c[0] == "biped_walk_ee_linear"][0]
@@ -167,18 +166,8 @@ def test_ee_linear_constraint_rules(product):
     st = T.Structure(ok)
     assert [n for n, _ in st.con_sets()][-2:] == ["ee-linear", "ee-linear"]      # every definition's set has this name (:14)
     assert not T.Structure(mk(T, [c for c in CASES if c[0] == "biped_walk_stairs"][0])).accepts(ok)
-    s = mk(T, base)
-    set_ee_linear(s, [(1, 0, [(0, 0, 1.0)], 0.1, 0.1)])                        # Angle target
-    with pytest.raises(T.TowrB200Error) as e:
-        T.Structure(s)
-    assert e.value.code == -2
-    s = mk(T, [c for c in CASES if c[0] == "biped_walk_durations"][0])
-    set_ee_linear(s, [(0, 0, [(0, 0, 1.0)], 0.1, 0.1)])                        # optimised durations
-    with pytest.raises(T.TowrB200Error) as e:
-        T.Structure(s)
-    assert e.value.code == -2
     for bad in ([(0, 0, [(2, 0, 1.0)], 0.1, 0.1)], [(0, 0, [(0, 3, 1.0)], 0.1, 0.1)], [(0, 0, [(0, 0, 1.0)], 0.1, 0.0)],
-                [(0, 2, [(0, 0, 1.0)], 0.1, 0.1)]):
+                [(0, 2, [(0, 0, 1.0)], 0.1, 0.1)], [(2, 0, [(0, 0, 1.0)], 0.1, 0.1)]):
         s = mk(T, base)
         set_ee_linear(s, bad)
         with pytest.raises(T.TowrB200Error):

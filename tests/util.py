@@ -68,6 +68,14 @@ CASES = [
                     (0, 1, [(0, 2, 0.5), (1, 2, 0.5), (0, 1, 2.0), (0, 2, -0.25)], 0.2, 0.07)]}),   # velocities, a foot named twice
     ("anymal_trot_ee_linear_block", 3, 1, 2.0, (1.0, 0.1, 0.0), 1, (TORQUE,), False,
      {"ee_linear": [(0, 0, [(0, 1, 1.0), (1, 1, 1.0), (2, 1, -1.0), (3, 1, -1.0)], 0.05, 0.05)]}),
+    ("biped_walk_ee_linear_durations", 1, 0, 2.4, (1.0, 0.0, 0.1), 0, (), True,
+     {"ee_linear": [(0, 0, [(0, 0, 1.0), (1, 0, -1.0)], 0.3, 0.1),
+                    (0, 1, [(0, 2, 0.5), (1, 2, 0.5), (0, 1, 2.0), (0, 2, -0.25)], 0.2, 0.07)]}),
+    # ... on the feet's angle splines (target 1: the ee-ang sets are staged only for such classes)
+    ("hyq_trot_ee_linear_angle", 2, 1, 2.0, (0.8, 0.0, 0.2), 0, (), False,
+     {"ee_linear": [(1, 0, [(0, 2, 1.0), (3, 2, -1.0)], 0.1, 0.1), (0, 0, [(1, 1, 1.0), (2, 1, 1.0)], 0.4, 0.08)]}),
+    ("monoped_hop_ee_linear_angle_durations", 0, 0, 2.4, (1.0, 0.0, 0.0), 0, (), True,
+     {"ee_linear": [(1, 1, [(0, 0, 1.0), (0, 1, -2.0)], 0.5, 0.05)]}),
 ]
 
 

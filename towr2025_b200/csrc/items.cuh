@@ -788,23 +788,76 @@ __device__ __forceinline__ void ItemTerrainHard(const ItemCtx<L>& cx, const Item
   }
 }
 
-// EELinearConstraint (ee_linear_constraint.cc:20-29), one row per sample: g = sum over the terms of coeff * value of the
+// EELinearConstraint (ee_linear_constraint.cc:20-48), one row per sample: g = sum over the terms of coeff * value of the
 // term's foot spline in one dimension (position or velocity).  sub terms; samples s0 .. s0 + sub - 1 in term order;
-// B[b0 + 3 j ..] = coeff, dimension, derivative.  The Jacobian entries are class constants (fixed durations only).
+// B[b0 + 4 j ..] = coeff, dimension, derivative, G offset of the foot's column block.
+// Fixed durations: the Jacobian entries are class constants, the item only forms g.
+// Optimised durations: G[gslot + offset + c] = sum of coeff * (run-time Hermite weight) over the terms that reach column c
+// of the foot's set: the columns of the active polynomial's two nodes in the term's dimension; every other stored column
+// stays 0 (`jac.row(k) += coeff * jac_nodes.row(dim)` on the pre-filled structure).
 template <class L>
 __device__ __forceinline__ void ItemEELinear(const ItemCtx<L>& cx, const ItemC& it) {
-  if (!cx.g) return;
   const double* Bc = cx.T.B + it.b0;
+  double* G = cx.G + it.gslot * L::GS;
+  if constexpr (L::RT) {
+    if (!TB_PREZERO_G)
+      for (int j = 0; j < it.sub; ++j) {
+        const RtSpline sm = cx.T.rt_splines[cx.T.samples[it.s0 + j] & 0xFFFF];
+        double* Gf = G + static_cast<int>(Bc[4 * j + 3]) * L::GS;
+        for (int c = 0; c < sm.n_cols; ++c) Gf[c * L::GS] = 0.0;
+      }
+  }
   double val = 0.0;
   for (int j = 0; j < it.sub; ++j) {
+    const double coeff = Bc[4 * j];
+    const int dim = static_cast<int>(Bc[4 * j + 1]);
+    const bool vel = Bc[4 * j + 2] != 0.0;
     Pt3 p;
-    EvalSpline<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + j, p);
-    const int dim = static_cast<int>(Bc[3 * j + 1]);
+    if constexpr (L::RT) {
+      const RtPoint rp = EvalSplineRt<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, cx.rtd, it.s0 + j, p);
+      const RtSpline sm = cx.T.rt_splines[cx.T.samples[it.s0 + j] & 0xFFFF];
+      double* Gf = G + static_cast<int>(Bc[4 * j + 3]) * L::GS;
+      const double* q = cx.rtd + rp.poly * kRtd * L::NS;
+      const double t = rp.t, T = rp.T, T2 = q[kRtT2 * L::NS], T3 = q[kRtT3 * L::NS];
+      const double r1 = q[kRtR1 * L::NS], r2 = q[kRtR2 * L::NS], r3 = q[kRtR3 * L::NS];
+      const double tt2 = t * t, tt3 = Cube(t);
+      double w[4];                                       // polynomial.cc:106-175, by side * 2 + node derivative
+      if (!vel) {
+        w[0] = ExactDiv(2 * tt3, T3, r3) - ExactDiv(3 * tt2, T2, r2) + 1;
+        w[1] = t - ExactDiv(2 * tt2, T, r1) + ExactDiv(tt3, T2, r2);
+        w[2] = ExactDiv(3 * tt2, T2, r2) - ExactDiv(2 * tt3, T3, r3);
+        w[3] = ExactDiv(tt3, T2, r2) - ExactDiv(tt2, T, r1);
+      } else {
+        w[0] = ExactDiv(6 * tt2, T3, r3) - ExactDiv(6 * t, T2, r2);
+        w[1] = ExactDiv(3 * tt2, T2, r2) - ExactDiv(4 * t, T, r1) + 1;
+        w[2] = ExactDiv(6 * t, T2, r2) - ExactDiv(6 * tt2, T3, r3);
+        w[3] = ExactDiv(3 * tt2, T2, r2) - ExactDiv(2 * t, T, r1);
+      }
+      const int n0 = cx.T.polys[rp.poly] & 0xFFFF;
+      // one value per column first (a stance variable writes both nodes of its polynomial: node_spline.cc:84-112 sums the
+      // two weights into the Jacobian entry), then coeff * that value joins the row
+      int cols[4];
+      double sum[4];
+      int n = 0;
+#pragma unroll
+      for (int sd = 0; sd < 4; ++sd) {
+        const unsigned src = cx.T.node_src[(n0 + (sd >> 1)) * 6 + (sd & 1) * 3 + dim];
+        if (src == 0xFFFFu) continue;
+        const int c = static_cast<int>(src) - sm.col0;
+        int hit = -1;
+        for (int i = 0; i < n; ++i) hit = cols[i] == c ? i : hit;
+        if (hit < 0) { cols[n] = c; sum[n] = 0.0 + w[sd]; ++n; }
+        else sum[hit] = sum[hit] + w[sd];
+      }
+      for (int i = 0; i < n; ++i) Gf[cols[i] * L::GS] = Gf[cols[i] * L::GS] + coeff * sum[i];
+    } else {
+      EvalSpline<kNeedPos | kNeedVel, L::NS>(cx.T, cx.nodes, cx.coef, it.s0 + j, p);
+    }
     const double pv = dim == 0 ? p.p[0] : dim == 1 ? p.p[1] : p.p[2];
     const double vv = dim == 0 ? p.v[0] : dim == 1 ? p.v[1] : p.v[2];
-    val += Bc[3 * j] * (Bc[3 * j + 2] != 0.0 ? vv : pv);
+    val += coeff * (vel ? vv : pv);
   }
-  cx.g[it.row * L::RS] = val;
+  if (cx.g) cx.g[it.row * L::RS] = val;
 }
 
 // Node-based TorqueConstraint (torque_constraint.cc:64-157): s0 = the stance torque node, aux = the ee-motion node at the
@@ -904,7 +957,7 @@ __device__ __forceinline__ void RunItem(const ItemCtx<L>& cx, const ItemC& it) {
       if constexpr (L::CURV) ItemTorqueNode<L>(cx, it);
       break;
     case kItemEELinear:
-      if constexpr (L::CURV && !L::RT) ItemEELinear<L>(cx, it);
+      if constexpr (L::CURV) ItemEELinear<L>(cx, it);
       break;
     case kItemTorque: ItemTorque<L>(cx, it); break;
     case kItemForceNode: ItemForceNode<L>(cx, it); break;

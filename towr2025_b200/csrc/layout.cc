@@ -188,10 +188,7 @@ void ValidateSpec(const towr_b200_spec& s) {
       if (s.ee_linear_term_ee[i][j] < 0 || s.ee_linear_term_ee[i][j] >= s.n_ee || s.ee_linear_term_dim[i][j] < 0 ||
           s.ee_linear_term_dim[i][j] > 2 || !std::isfinite(s.ee_linear_term_coeff[i][j]))
         throw std::runtime_error("EELinearConstraint: bad term (foot, dimension or coefficient)");
-    if (s.ee_linear_target[i] != 0) throw std::runtime_error("unsupported: EELinearConstraint on the ee-angle splines (Motion only)");
-    for (int c = 0; c < s.n_constraints; ++c)
-      if (s.constraints[c] == TOWR_B200_C_TOTAL_TIME)
-        throw std::runtime_error("unsupported: EELinearConstraint with optimised phase durations");
+    if (s.ee_linear_target[i] != 0 && s.ee_linear_target[i] != 1) throw std::runtime_error("EELinearConstraint: target must be Motion or Angle");
   }
   if (s.n_node_costs < 0 || s.n_node_costs > TOWR_B200_MAX_NODE_COSTS) throw std::runtime_error("bad n_node_costs");
   for (int c = 0; c < s.n_node_costs; ++c) {
@@ -257,14 +254,17 @@ void BuildLayout(const towr_b200_spec& s, HostProgram& hp) {
       vs.push_back(std::move(v));
     }
 
-  // columns, node slots, polynomial records.  ee-ang splines feed no constraint on this path: not staged.
+  // columns, node slots, polynomial records.  The ee-ang splines feed no constraint on this path unless an
+  // EELinearConstraint definition targets them (parameters.h:319-320): staged only then.
+  bool needs_ee_ang = false;
+  for (int i = 0; i < s.n_ee_linear; ++i) needs_ee_ang = needs_ee_ang || s.ee_linear_target[i] == 1;
   int col = 0, node_slot = 0;
   hp.polys.clear();
   hp.node_src.clear();
   for (VarSet& v : vs) {
     v.col0 = col;
     col += v.n_vars;
-    if (v.kind == kEESchedule || v.kind == kEEAng) continue;
+    if (v.kind == kEESchedule || (v.kind == kEEAng && !needs_ee_ang)) continue;
     v.node_slot0 = node_slot;
     v.poly0 = static_cast<int>(hp.polys.size());
     std::vector<int> src(static_cast<size_t>(v.n_nodes) * 6, -1);
@@ -290,9 +290,10 @@ void BuildLayout(const towr_b200_spec& s, HostProgram& hp) {
   hp.rt_feet.clear();
   hp.poly_meta.assign(hp.polys.size(), kPolyFixed);
   if (hp.optimize_durations) {
-    const int kinds[3] = {kEEMotion, kEEForce, kEETorque};
-    hp.rt_splines.resize(3 * static_cast<size_t>(E));
-    for (int k = 0; k < 3; ++k)
+    const int kinds[4] = {kEEMotion, kEEForce, kEETorque, kEEAng};
+    const int n_kinds = needs_ee_ang ? 4 : 3;
+    hp.rt_splines.resize(n_kinds * static_cast<size_t>(E));
+    for (int k = 0; k < n_kinds; ++k)
       for (int e = 0; e < E; ++e) {
         const VarSet& v = *hp.Find(kinds[k], e);
         hp.rt_splines[k * E + e] = RtSpline{v.poly0, v.n_polys(), v.col0, v.n_vars};

@@ -27,7 +27,7 @@ int ItemBRun(int type, int sub) {
     case kItemTerrainHard: return 3 * sub;               // (J_pos, J_vel, dim) per stored column; 0 with optimised durations
     case kItemDynPre: case kItemDynFoot: case kItemDynWrench: case kItemDynJlin: case kItemDynCol: return 16;
     case kItemTorque: return 1;
-    case kItemEELinear: return 3 * sub;                  // (coeff, dimension, derivative) per term
+    case kItemEELinear: return 4 * sub;                  // (coeff, dimension, derivative, G offset of the foot's block) per term
     default: return 0;
   }
 }

@@ -160,7 +160,8 @@ struct ItemC {          // 16 bytes
 // RomFoot [motion], Force [motion, force], Torque [motion, force, torque], BaseRom [lin, ang]
 // ---- classes with optimised phase durations (PhaseSpline path, phase_spline.cc / phase_durations.cc): which
 // polynomial a sample time falls into, its local time and the Hermite weights are per-problem quantities
-struct RtSpline {       // one PhaseSpline: index kind*E + foot, kind 0 = ee-motion, 1 = ee-force, 2 = ee-torque
+struct RtSpline {       // one PhaseSpline: index kind*E + foot, kind 0 = ee-motion, 1 = ee-force, 2 = ee-torque, 3 = ee-ang
+                        // (kind 3 only in classes with an EELinearConstraint on the angle splines)
   int poly0, n_polys;   // global polynomial range
   int col0, n_cols;     // its variable set's columns
 };

@@ -854,27 +854,55 @@ void Builder::EmitBaseRom() {
 // EELinearConstraint (ee_linear_constraint.cc:5-48, MakeEELinearConstraint nlp_formulation.cc:682-704), definition `def`:
 // one row per sample of its own dt, g = sum_j coeff_j * spline_{ee_j}(t).at(deriv)(dim_j), bounds +- tolerance; the row of
 // the Jacobian is sum_j coeff_j * (row dim_j of the foot's GetJacobianWrtNodes(t, deriv)), accumulated term by term
-// (`jac.row(k) += ...`): with class-constant durations every entry is a class constant.
+// (`jac.row(k) += ...`): with class-constant durations every entry is a class constant; with optimised durations the item
+// finishes the columns of the active polynomials from run-time Hermite weights (ItemEELinear).
 void Builder::EmitEELinear(int def) {
   const int n_terms = s_.ee_linear_n_terms[def], deriv = s_.ee_linear_deriv[def];
+  const bool angle = s_.ee_linear_target[def] == 1;                   // s.ee_ang_ instead of s.ee_motion_ (nlp_formulation.cc:692-699)
+  const int set_kind = angle ? kEEAng : kEEMotion;
   const std::vector<double> ts = SampleTimes(hp_.total_time, s_.ee_linear_dt[def]);
-  BeginGroup();
-  BeginSet("ee-linear", static_cast<int>(ts.size()));
+  const int one = AddB(1.0);
+  // optimised durations: one block of G slots per foot the definition names (every column of the foot's set), offsets
+  // within the item; the row stores, per term, the set's columns of the term's dimension (the pre-filled structure of
+  // PhaseSpline, phase_spline.cc:45-51, row dim of GetJacobianWrtNodes)
+  std::vector<int> foot_off(kMaxEE, -1);
+  int per_item_rt = 0;
+  for (int j = 0; j < n_terms; ++j) {
+    const int ee = s_.ee_linear_term_ee[def][j];
+    if (foot_off[ee] < 0) { foot_off[ee] = per_item_rt; per_item_rt += Set(set_kind, ee).n_vars; }
+  }
+  per_item_rt |= 1;
+  const int chunk = std::max(1, 960 / (rt() ? per_item_rt : 1));
   for (size_t k = 0; k < ts.size(); ++k) {
+    if (k == 0) { BeginGroup(); BeginSet("ee-linear", static_cast<int>(ts.size())); }
+    else if (rt() && k % chunk == 0) BeginGroup(static_cast<int>(k));   // a new group of items: bounded G use per group
     ItemRec it = NewItem(kItemEELinear);
     it.row[0] = set_row0_ + static_cast<int>(k);
     it.sub = static_cast<short>(n_terms);
-    std::vector<double> brun(3 * static_cast<size_t>(n_terms));
+    Bound(static_cast<int>(k), kBoundEELinear, 0, def);
+    std::vector<double> brun(4 * static_cast<size_t>(n_terms));
     std::vector<std::pair<int, double>> row;               // column -> value, in order of first appearance
+    if (rt()) it.gslot = AllocG(per_item_rt);
     for (int j = 0; j < n_terms; ++j) {
       const int ee = s_.ee_linear_term_ee[def][j], dim = s_.ee_linear_term_dim[def][j];
       const double coeff = s_.ee_linear_term_coeff[def][j];
-      const VarSet& mo = Set(kEEMotion, ee);
+      const VarSet& mo = Set(set_kind, ee);
+      brun[4 * j] = coeff;
+      brun[4 * j + 1] = dim;
+      brun[4 * j + 2] = deriv;
+      brun[4 * j + 3] = rt() ? foot_off[ee] : 0;
+      if (rt()) {
+        it.s[j] = AtRt(angle ? 3 : 0, ee, ts[k]);
+        for (auto& c : AllCols(mo)) {
+          if (c.second != dim) continue;
+          bool found = false;
+          for (auto& e : row) found = found || e.first == mo.col0 + c.first;
+          if (!found) row.emplace_back(mo.col0 + c.first, static_cast<double>(it.gslot + foot_off[ee] + c.first));
+        }
+        continue;
+      }
       const SplineAt am = At(mo, ts[k]);
       it.s[j] = am.sample;
-      brun[3 * j] = coeff;
-      brun[3 * j + 1] = dim;
-      brun[3 * j + 2] = deriv;
       for (const ColBasis& c : Columns(mo, am.poly, am.t_local)) {
         if (c.dim != dim) continue;
         const int col = mo.col0 + c.idx;
@@ -887,9 +915,10 @@ void Builder::EmitEELinear(int def) {
     }
     it.b0 = AddBRun(brun);
     hp_.items.push_back(it);
-    Bound(static_cast<int>(k), kBoundEELinear, 0, def);
     for (const auto& e : row) {
-      Term tm; tm.g = kGOne; tm.b = AddB(e.second);
+      Term tm;
+      if (rt()) { tm.g = static_cast<int>(e.second); tm.b = one; }      // the item's finished value of that column
+      else { tm.g = kGOne; tm.b = AddB(e.second); }
       Add(static_cast<int>(k), e.first, tm);
     }
   }
