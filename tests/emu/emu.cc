@@ -147,28 +147,29 @@ extern "C" int emu_eval_cost(const towr_b200_spec* s, const double* x, double* f
       grad[c] = g;
     }
     *f_out = fsum;
-    SampledCost sc;
-    BuildSampledCost(hp, *s, sc);
-    if (sc.blob.empty()) return 0;
-    const SampledView V = MakeSampledView(sc.blob.data());
-    const SampledHeader& H = *V.h;
-    std::vector<double> work((sc.shared_bytes - H.bytes) / sizeof(double) + 8);
-    const SampledWork W = SampledCarve(H, reinterpret_cast<unsigned char*>(work.data()));
-    ProblemConst pc;
-    FillProblemConst(*s, pc);
-    for (int i = 0; i < 6 * H.n_nodes; ++i) SampledNode(V, W, x, i);
-    if (H.rt) for (int e = 0; e < H.n_ee; ++e) SampledPhaseDurations(V, W, x, e);
-    for (int poly = 0; poly < H.n_polys + H.n_phase_slots; ++poly) SampledPolyRecord(V, W, poly);
-    for (int i = 0; i < 3 * H.n_polys + H.n_splines; ++i) SampledCoeff(V, W, i);
-    double pref[12];
-    SwingReferenceB(*s, pref);
-    for (int it = 0; it < H.n_items; ++it) SampledItem(V, W, pc.I, pref, it);
-    for (int k = 0; k < H.n_times; ++k) SampledSummand(V, W, k);
-    for (int q = 0; q < H.n_phase_slots; ++q) SampledPhaseSum(V, W, q);
-    for (int ti = 0; ti < H.n_terms; ++ti) SampledTermSum(V, W, ti);
-    for (int j = 0; j < H.n_jobs; ++j) SampledJobGradient(V, W, grad, j);
-    for (int i = 0; i < H.n_comb; ++i) SampledCombine(V, W, grad, i);
-    for (int ti = 0; ti < H.n_terms; ++ti) *f_out = *f_out + W.fterm[ti];
+    std::vector<SampledCost> parts;                        // one kernel launch each on the device, in term order
+    BuildSampledCostParts(hp, *s, parts);
+    for (const SampledCost& sc : parts) {
+      const SampledView V = MakeSampledView(sc.blob.data());
+      const SampledHeader& H = *V.h;
+      std::vector<double> work((sc.shared_bytes - H.bytes) / sizeof(double) + 8);
+      const SampledWork W = SampledCarve(H, reinterpret_cast<unsigned char*>(work.data()));
+      ProblemConst pc;
+      FillProblemConst(*s, pc);
+      for (int i = 0; i < 6 * H.n_nodes; ++i) SampledNode(V, W, x, i);
+      if (H.rt) for (int e = 0; e < H.n_ee; ++e) SampledPhaseDurations(V, W, x, e);
+      for (int poly = 0; poly < H.n_polys + H.n_phase_slots; ++poly) SampledPolyRecord(V, W, poly);
+      for (int i = 0; i < 3 * H.n_polys + H.n_splines; ++i) SampledCoeff(V, W, i);
+      double pref[12];
+      SwingReferenceB(*s, pref);
+      for (int it = 0; it < H.n_items; ++it) SampledItem(V, W, pc.I, pref, it);
+      for (int k = 0; k < H.n_times; ++k) SampledSummand(V, W, k);
+      for (int q = 0; q < H.n_phase_slots; ++q) SampledPhaseSum(V, W, q);
+      for (int ti = 0; ti < H.n_terms; ++ti) SampledTermSum(V, W, ti);
+      for (int j = 0; j < H.n_jobs; ++j) SampledJobGradient(V, W, grad, j);
+      for (int i = 0; i < H.n_comb; ++i) SampledCombine(V, W, grad, i);
+      for (int ti = 0; ti < H.n_terms; ++ti) *f_out = *f_out + W.fterm[ti];
+    }
     return 0;
   } catch (const std::exception& e) {
     g_err = e.what();
@@ -181,10 +182,12 @@ extern "C" long emu_cost_shared_bytes(const towr_b200_spec* s, int* blob) {
   try {
     HostProgram hp;
     BuildProgram(*s, hp);
-    SampledCost sc;
-    BuildSampledCost(hp, *s, sc);
-    if (blob) *blob = static_cast<int>(sc.blob.size());
-    return static_cast<long>(sc.shared_bytes);
+    std::vector<SampledCost> parts;
+    BuildSampledCostParts(hp, *s, parts);
+    long worst = 0;
+    if (blob) *blob = static_cast<int>(parts.size());   // number of launches
+    for (const SampledCost& sc : parts) worst = std::max(worst, static_cast<long>(sc.shared_bytes));
+    return worst;
   } catch (const std::exception& e) {
     g_err = e.what();
     return -1;

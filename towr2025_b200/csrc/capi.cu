@@ -128,8 +128,9 @@ struct towr_b200_batch {
   // cost tables (cost.h), built at the first eval_cost call
   bool cost_ready = false;
   tb::CostDevice cost_dev{};
-  const unsigned char* sampled_dev = nullptr;   // EnergyCost / AngularMomentumCost / EEBasePosCost tables (cost.h), nullptr: none
-  size_t sampled_shared = 0;
+  // EnergyCost / AngularMomentumCost / EEBasePosCost tables (cost.h): one entry per launch, in term order
+  struct SampledPart { const unsigned char* dev; size_t shared; };
+  std::vector<SampledPart> sampled;
   // EEBasePosCost reference positions per problem (cost.h: SwingReferenceB), kept only by classes with that cost
   std::vector<double> pref_host;
   double* pref_dev = nullptr;
@@ -566,12 +567,9 @@ void EnsureCost(towr_b200_batch* b) {
   b->cost_dev.n_vars = h.n_vars;
   b->cost_dev.col_ptr = up(h.col_ptr);
   b->cost_dev.weights = up(h.weights);
-  tb::SampledCost sc;
-  tb::BuildSampledCost(b->st->hp, b->st->spec, sc);
-  if (!sc.blob.empty()) {
-    b->sampled_dev = up(sc.blob);
-    b->sampled_shared = sc.shared_bytes;
-  }
+  std::vector<tb::SampledCost> parts;
+  tb::BuildSampledCostParts(b->st->hp, b->st->spec, parts);
+  for (const tb::SampledCost& sc : parts) b->sampled.push_back({up(sc.blob), sc.shared_bytes});
   b->cost_ready = true;
 }
 }  // namespace
@@ -589,14 +587,16 @@ int towr_b200_batch_eval_cost_device(towr_b200_batch* b, int n, int what, const 
     Check(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device), "device attribute");
     Check(tb::LaunchCost(b->cost_dev, what, d_x, d_f, d_grad, n, 16 * sms, static_cast<cudaStream_t>(stream)), "launch");
     b->launches += 1;
-    if (b->sampled_dev) {
+    if (!b->sampled.empty()) {
       if (b->pc_dirty) {                        // per-problem inertia: the batch's constants
         b->SyncConsts();
         Check(cudaStreamSynchronize(b->stream), "sync consts");
       }
-      Check(tb::LaunchSampledCost(b->sampled_dev, b->sampled_shared, b->pc_dev, b->pref_dev, what, d_x, d_f, d_grad, n, sms,
-                                  static_cast<cudaStream_t>(stream)), "launch");
-      b->launches += 1;
+      for (const auto& part : b->sampled) {
+        Check(tb::LaunchSampledCost(part.dev, part.shared, b->pc_dev, b->pref_dev, what, d_x, d_f, d_grad, n, sms,
+                                    static_cast<cudaStream_t>(stream)), "launch");
+        b->launches += 1;
+      }
       // the kernel reads the batch's constants on the caller's stream: a later set_problem must not overwrite them first
       Check(cudaEventRecord(b->device_eval_done, static_cast<cudaStream_t>(stream)), "record eval_cost_device");
       b->device_eval_pending = true;
@@ -626,9 +626,9 @@ int towr_b200_batch_eval_cost(towr_b200_batch* b, int n, int what, const double*
     Check(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, b->device), "device attribute");
     Check(tb::LaunchCost(b->cost_dev, what, b->x_dev, b->cost_f_dev, b->cost_grad_dev, n, 16 * sms, b->stream), "launch");
     b->launches += 1;
-    if (b->sampled_dev) {
-      b->SyncConsts();
-      Check(tb::LaunchSampledCost(b->sampled_dev, b->sampled_shared, b->pc_dev, b->pref_dev, what, b->x_dev, b->cost_f_dev,
+    if (!b->sampled.empty()) b->SyncConsts();
+    for (const auto& part : b->sampled) {
+      Check(tb::LaunchSampledCost(part.dev, part.shared, b->pc_dev, b->pref_dev, what, b->x_dev, b->cost_f_dev,
                                   b->cost_grad_dev, n, sms, b->stream), "launch");
       b->launches += 1;
     }
@@ -649,8 +649,8 @@ int towr_b200_eval_cost_static(const towr_b200_structure* st, int device, int n,
     if (towr_b200_device_count() < 1) throw CudaError("no CUDA device visible: this backend has no CPU fallback");
     tb::CostTables h;                                   // host tables only
     tb::BuildCostTables(st->hp, st->spec, h);
-    tb::SampledCost sc;
-    tb::BuildSampledCost(st->hp, st->spec, sc);
+    std::vector<tb::SampledCost> sc;
+    tb::BuildSampledCostParts(st->hp, st->spec, sc);
     const char* why = "";
     const cudaError_t err = tb::LaunchCostStatic(h, sc, device, what, d_x, d_f, d_grad, n, static_cast<cudaStream_t>(stream), &why);
     if (err == cudaErrorInvalidValue && *why) throw std::runtime_error(std::string("eval_cost_static: ") + why);

@@ -66,7 +66,41 @@ int Append(std::vector<unsigned char>& blob, const std::vector<T>& v) {
 }
 }  // namespace
 
-void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCost& out) {
+std::vector<SampledTermDef> SampledTermDefs(const HostProgram& hp, const towr_b200_spec& s) {
+  std::vector<SampledTermDef> defs;
+  for (int c = 0; c < s.n_costs; ++c) {
+    if (s.cost_ids[c] == TOWR_B200_COST_ENERGY) defs.push_back({kSampledEnergy, s.cost_weights[c], s.dt_cost_energy, -1});
+    if (s.cost_ids[c] == TOWR_B200_COST_ANG_MOM) defs.push_back({kSampledAngMom, s.cost_weights[c], s.dt_cost_ang_mom, -1});
+  }
+  if (HasSwingTracking(s))                                     // after the listed costs (nlp_formulation.cc:612-626)
+    for (int e = 0; e < hp.n_ee; ++e)
+      defs.push_back({kSampledEEBasePos, s.swing_ee_base_pos_tracking_weight, s.dt_cost_swing_ee_base_pos_tracking, e});
+  std::vector<SampledTermDef> live;
+  for (const SampledTermDef& d : defs)
+    if (d.weight > 0.0) live.push_back(d);                     // GetCost / FillJacobianBlock return at once otherwise (:70, :94)
+  return live;
+}
+
+void BuildSampledCostParts(const HostProgram& hp, const towr_b200_spec& s, std::vector<SampledCost>& out) {
+  out.clear();
+  const std::vector<SampledTermDef> defs = SampledTermDefs(hp, s);
+  const int n = static_cast<int>(defs.size());
+  int first = 0;
+  while (first < n) {
+    SampledCost part;
+    int count = n - first;
+    BuildSampledCost(hp, s, defs, first, count, part, count > 1);
+    while (count > 1 && part.shared_bytes > kSampledTwoCtaShared) {   // the longest run of terms that leaves room for two CTAs
+      --count;
+      BuildSampledCost(hp, s, defs, first, count, part, count > 1);
+    }
+    out.push_back(std::move(part));
+    first += count;
+  }
+}
+
+void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, const std::vector<SampledTermDef>& all_defs, int first,
+                      int count, SampledCost& out, bool size_only_ok) {
   out = SampledCost{};
   std::vector<SampledTerm> terms;
   std::vector<SampledSpline> splines;
@@ -149,17 +183,9 @@ void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCos
       jobs.push_back(j);
     }
   };
-  struct TermDef { int kind; double weight, dt; int foot; };
-  std::vector<TermDef> defs;
-  for (int c = 0; c < s.n_costs; ++c) {
-    if (s.cost_ids[c] == TOWR_B200_COST_ENERGY) defs.push_back({kSampledEnergy, s.cost_weights[c], s.dt_cost_energy, -1});
-    if (s.cost_ids[c] == TOWR_B200_COST_ANG_MOM) defs.push_back({kSampledAngMom, s.cost_weights[c], s.dt_cost_ang_mom, -1});
-  }
-  if (HasSwingTracking(s))                                     // after the listed costs (nlp_formulation.cc:612-626)
-    for (int e = 0; e < hp.n_ee; ++e)
-      defs.push_back({kSampledEEBasePos, s.swing_ee_base_pos_tracking_weight, s.dt_cost_swing_ee_base_pos_tracking, e});
+  const std::vector<SampledTermDef> defs(all_defs.begin() + first, all_defs.begin() + first + count);
   int n_items = 0, item_doubles = 0;
-  for (const TermDef& def : defs) {
+  for (const SampledTermDef& def : defs) {
     const double weight = def.weight;
     if (weight <= 0.0) continue;                               // GetCost / FillJacobianBlock return at once (:70, :94)
     const bool energy = def.kind == kSampledEnergy;
@@ -330,7 +356,7 @@ void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCos
   h.bytes = static_cast<int>(blob.size());
   std::memcpy(blob.data(), &h, sizeof(h));
   out.shared_bytes = SampledSharedBytes(h);
-  if (out.shared_bytes > kSampledMaxShared)
+  if (out.shared_bytes > kSampledMaxShared && !size_only_ok)
     throw std::runtime_error("unsupported: the cost samples of this class exceed one SM's shared memory (larger dt_cost_*)");
 }
 

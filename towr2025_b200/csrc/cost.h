@@ -72,10 +72,14 @@ struct SampledHeader {
   double I[9];           // the class spec's inertia (used when a call has no per-problem constants)
   double p_ref_B[12];    // ... and its EEBasePosCost reference positions, 3 per foot
 };
-struct SampledCost {     // host side
-  std::vector<unsigned char> blob;   // empty: the class has no time-discretised cost term
+struct SampledCost {     // host side: the tables of one launch
+  std::vector<unsigned char> blob;
   size_t shared_bytes = 0;
 };
+// one term of the class, in the order ifopt adds them: the EnergyCost / AngularMomentumCost entries of params_.costs_, then
+// one EEBasePosCost per foot (nlp_formulation.cc:605-626)
+struct SampledTermDef { int kind; double weight, dt; int foot; };
+std::vector<SampledTermDef> SampledTermDefs(const HostProgram& hp, const towr_b200_spec& s);
 constexpr int kSampledRec = 7;   // doubles per node / coefficient record in shared memory (6 used; odd stride, fewer bank conflicts)
 constexpr int kSampledPolyRec = 9;   // doubles per polynomial record (T, T^2, T^3, T^4, their reciprocals, end time)
 constexpr size_t kSampledMaxShared = 200 * 1024;
@@ -86,8 +90,16 @@ inline size_t SampledSharedBytes(const SampledHeader& h) {
   return blob + sizeof(double) * doubles +
          sizeof(int) * (static_cast<size_t>(h.n_items) + 2 * static_cast<size_t>(h.n_polys) + 2 * static_cast<size_t>(h.n_phase_slots) + 4);
 }
-// throws "unsupported" when a term's samples do not fit one SM's shared memory
-void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, SampledCost& out);
+// shared memory per CTA up to which two CTAs of the kernel fit one SM (227 KB, 1 KB reserved per CTA)
+constexpr size_t kSampledTwoCtaShared = 112 * 1024;
+// tables of the terms defs[first, first + count); throws "unsupported" when they do not fit one SM's shared memory
+// (size_only_ok: do not throw, the caller looks at out.shared_bytes and retries with fewer terms)
+void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, const std::vector<SampledTermDef>& defs, int first,
+                      int count, SampledCost& out, bool size_only_ok = false);
+// the class's terms as one launch, or - where that would leave one CTA per SM - as several launches of consecutive terms
+// that each leave room for two (run in order on one stream: f and the gradient accumulate in term order either way);
+// empty: the class has no time-discretised cost term
+void BuildSampledCostParts(const HostProgram& hp, const towr_b200_spec& s, std::vector<SampledCost>& out);
 // true when the class has EEBasePosCost terms (params_.enable_swing_ee_base_pos_tracking with a positive weight)
 inline bool HasSwingTracking(const towr_b200_spec& s) { return s.enable_swing_ee_base_pos_tracking && s.swing_ee_base_pos_tracking_weight > 0.0; }
 // r_B0 = b_R_w0 (initial_ee_W - initial_base.lin.p) per foot (nlp_formulation.cc:616-620); formulation_init.cc
@@ -97,7 +109,7 @@ cudaError_t LaunchCost(const CostDevice& c, int what, const double* x, double* f
                        cudaStream_t stream);
 // allocation-free variant: the tables go into a file-scope device array of cost_kernel.cu (no cudaMalloc / cudaFree);
 // *why names the limit or call that failed
-cudaError_t LaunchCostStatic(const CostTables& h, const SampledCost& sc, int device, int what, const double* x, double* f,
+cudaError_t LaunchCostStatic(const CostTables& h, const std::vector<SampledCost>& sc, int device, int what, const double* x, double* f,
                              double* grad, int n_problems, cudaStream_t stream, const char** why);
 // adds the time-discretised terms to f / grad written by LaunchCost (same stream, after it).  pcs: the batch's
 // per-problem constants (inertia), or nullptr to use the class spec's

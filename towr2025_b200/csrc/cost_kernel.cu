@@ -178,7 +178,7 @@ static unsigned char* g_cost_static_addr[kMaxDevices];     // device address of 
 static int g_cost_static_sms[kMaxDevices];
 static std::mutex g_cost_static_mu;
 
-cudaError_t LaunchCostStatic(const CostTables& h, const SampledCost& sc, int device, int what, const double* x, double* f,
+cudaError_t LaunchCostStatic(const CostTables& h, const std::vector<SampledCost>& sc, int device, int what, const double* x, double* f,
                              double* grad, int n_problems, cudaStream_t stream, const char** why) {
   *why = "";
   if (device < 0 || device >= kMaxDevices) { *why = "device index out of range"; return cudaErrorInvalidDevice; }
@@ -186,7 +186,9 @@ cudaError_t LaunchCostStatic(const CostTables& h, const SampledCost& sc, int dev
     *why = "the class exceeds TOWR_B200_STATIC_COST_MAX_VARS / _MAX_WEIGHTS";
     return cudaErrorInvalidValue;
   }
-  if (sc.blob.size() > TOWR_B200_STATIC_COST_MAX_SAMPLED_BYTES) {
+  size_t sampled_bytes = 0;
+  for (const SampledCost& part : sc) sampled_bytes += (part.blob.size() + 255) & ~static_cast<size_t>(255);
+  if (sampled_bytes > TOWR_B200_STATIC_COST_MAX_SAMPLED_BYTES) {
     *why = "the class's EnergyCost / AngularMomentumCost tables exceed TOWR_B200_STATIC_COST_MAX_SAMPLED_BYTES";
     return cudaErrorInvalidValue;
   }
@@ -222,12 +224,17 @@ cudaError_t LaunchCostStatic(const CostTables& h, const SampledCost& sc, int dev
   c.col_ptr = col_ptr;
   c.weights = weights;
   err = LaunchCost(c, what, x, f, grad, n_problems, 16 * sms, stream);
-  if (err != cudaSuccess || sc.blob.empty()) return err;
-  // the time-discretised terms: tables after the weights, inertia and swing reference positions from the class spec (no per-problem constants here)
+  // the time-discretised terms: tables after the weights (one blob per launch), inertia and swing reference positions from
+  // the class spec (no per-problem constants here)
   unsigned char* blob = base + kCostStaticSampledOff;
-  err = cudaMemcpyAsync(blob, sc.blob.data(), sc.blob.size(), cudaMemcpyHostToDevice, stream);
-  if (err != cudaSuccess) return err;
-  return LaunchSampledCost(blob, sc.shared_bytes, nullptr, nullptr, what, x, f, grad, n_problems, sms, stream);
+  for (const SampledCost& part : sc) {
+    if (err != cudaSuccess) return err;
+    err = cudaMemcpyAsync(blob, part.blob.data(), part.blob.size(), cudaMemcpyHostToDevice, stream);
+    if (err != cudaSuccess) return err;
+    err = LaunchSampledCost(blob, part.shared_bytes, nullptr, nullptr, what, x, f, grad, n_problems, sms, stream);
+    blob += (part.blob.size() + 255) & ~static_cast<size_t>(255);
+  }
+  return err;
 }
 
 }  // namespace tb
