@@ -164,7 +164,6 @@ extern "C" int emu_eval_cost(const towr_b200_spec* s, const double* x, double* f
       SwingReferenceB(*s, pref);
       for (int it = 0; it < H.n_items; ++it) SampledItem(V, W, pc.I, pref, it);
       for (int k = 0; k < H.n_times; ++k) SampledSummand(V, W, k);
-      for (int q = 0; q < H.n_phase_slots; ++q) SampledPhaseSum(V, W, q);
       for (int ti = 0; ti < H.n_terms; ++ti) SampledTermSum(V, W, ti);
       for (int j = 0; j < H.n_jobs; ++j) SampledJobGradient(V, W, grad, j);
       for (int i = 0; i < H.n_comb; ++i) SampledCombine(V, W, grad, i);

@@ -105,3 +105,4 @@ def test_emulated_kernel_reproduces_committed_fixtures(product, emu):
         assert st.nnz == int(z["nnz"])
         assert np.array_equal(rows[z["jac_idx"]], z["jac_rows"]) and np.array_equal(cols[z["jac_idx"]], z["jac_cols"])
         assert tol_ratio(g, z["g"]) <= 1.0 and tol_ratio(v[z["jac_idx"]], z["jac_vals"]) <= 1.0
+

@@ -1,0 +1,152 @@
+"""Random formulations against the oracle: hand-made phase timings (2-6 phases per foot, a first phase in stance or in
+swing, feet that differ), random terrain, constraint subset, sampling steps, EELinearConstraint definitions and costs.
+TEST INFRASTRUCTURE.  Default: the host emulation of the device arithmetic (tests/emu, no GPU); `gpu`: the CUDA path.
+
+    python tools/fuzz_parity.py [gpu] [n_cases] [seed]
+"""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import towr2025_b200 as T                      # noqa: E402
+from oracle import oracle_py as O              # noqa: E402  (checker)
+from util import check_against_oracle, cost_gradient_ok, perturbed, to_oracle_spec, tol_ratio, set_ee_linear, set_terrain_table   # noqa: E402
+
+DP = C.POINTER(C.c_double)
+
+
+def random_spec(rng):
+    robot = int(rng.integers(0, 4))
+    n_ee = (1, 2, 4, 4)[robot]
+    total = float(rng.choice([1.2, 1.7, 2.0, 2.4]))
+    optimise = bool(rng.integers(0, 2))
+    s = T.make_spec(robot, 0, total, goal=(float(rng.uniform(0.2, 1.2)), float(rng.uniform(-0.2, 0.2)), float(rng.uniform(-0.5, 0.5))),
+                    terrain=0, optimize_durations=optimise)
+    # SwingConstraint reads the neighbours of every swing node (swing_constraint.cc:66-70): a motion that starts or ends
+    # in swing runs off the node vector there, in the reference too.  Mostly stance-first-and-last; else without Swing.
+    ends_in_stance = rng.random() < 0.8
+    for e in range(n_ee):                                   # params_.ee_phase_durations_, ee_in_contact_at_start_
+        n = int(rng.choice([3, 5])) if ends_in_stance else int(rng.integers(2, 7))
+        d = rng.uniform(0.25, 1.0, size=n)
+        d = d / d.sum() * total
+        s.n_phases[e] = n
+        s.in_contact_at_start[e] = 1 if ends_in_stance else int(rng.integers(0, 2))
+        for i in range(n):
+            s.phase_durations[e][i] = float(d[i])
+    terrain = int(rng.integers(0, 9))
+    if terrain == 8:
+        xs = np.unique(np.round(np.sort(rng.uniform(0.1, 1.5, size=int(rng.integers(1, 5)))), 2))
+        set_terrain_table(s, int(rng.integers(0, 2)), [float(v) for v in xs], [float(v) for v in rng.uniform(0.0, 0.3, size=len(xs))])
+    else:
+        s.terrain_id = terrain
+    cons = [T.Terrain, T.Dynamic, T.BaseAcc, T.EndeffectorRom, T.Force, T.Swing, T.BaseHeight]
+    keep = [c for c in cons if rng.random() < 0.85 and (ends_in_stance or c != T.Swing)]
+    for extra in (T.Torque, T.BaseRom, T.TerrainHard):
+        if rng.random() < 0.3:
+            keep.append(extra)
+    rng.shuffle(keep)
+    if optimise:
+        keep.append(T.TotalTime)
+    s.n_constraints = len(keep)
+    for i, c in enumerate(keep):
+        s.constraints[i] = int(c)
+    s.dt_constraint_dynamic = float(rng.choice([0.1, 0.07, 0.05]))
+    s.dt_constraint_range_of_motion = float(rng.choice([0.08, 0.11, 0.04]))
+    s.dt_constraint_force = float(rng.choice([0.02, 0.05, -1.0]))
+    s.dt_constraint_torque = float(rng.choice([0.02, 0.06, -1.0]))
+    s.dt_constraint_base_motion = float(rng.choice([0.025, 0.04]))
+    if rng.random() < 0.4:
+        defs = []
+        for _ in range(int(rng.integers(1, 3))):
+            terms = [(int(rng.integers(0, n_ee)), int(rng.integers(0, 3)), float(rng.uniform(-2, 2))) for _ in range(int(rng.integers(1, 5)))]
+            defs.append((int(rng.integers(0, 2)), int(rng.integers(0, 2)), terms, float(rng.uniform(0.01, 0.5)), float(rng.choice([0.1, 0.06]))))
+        set_ee_linear(s, defs)
+    costs = [(int(c), float(rng.uniform(1e-4, 1.0))) for c in range(4) if rng.random() < 0.4]
+    s.n_costs = len(costs)
+    for i, (c, w) in enumerate(costs):
+        s.cost_ids[i], s.cost_weights[i] = c, w
+    if rng.random() < 0.3:
+        s.enable_swing_ee_base_pos_tracking = 1
+        s.initial_base_ang[2] = float(rng.uniform(-0.5, 0.5))
+    return s
+
+
+def describe(s):
+    n_ee = s.n_ee
+    return "robot_ee=%d T-phases=%s start=%s terrain=%d cons=%s dur=%s eelin=%d costs=%s swing=%d" % (
+        n_ee, [int(s.n_phases[e]) for e in range(n_ee)], [int(s.in_contact_at_start[e]) for e in range(n_ee)], s.terrain_id,
+        [int(s.constraints[i]) for i in range(s.n_constraints)], any(int(s.constraints[i]) == int(T.TotalTime) for i in range(s.n_constraints)),
+        s.n_ee_linear, [int(s.cost_ids[i]) for i in range(s.n_costs)], s.enable_swing_ee_base_pos_tracking)
+
+
+def main():
+    gpu = "gpu" in sys.argv
+    nums = [a for a in sys.argv[1:] if a.lstrip("-").isdigit()]
+    n_cases = int(nums[0]) if nums else 60
+    seed = int(nums[1]) if len(nums) > 1 else 1
+    rng = np.random.default_rng(seed)
+    E = None
+    if not gpu:
+        import subprocess
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "tests", "emu")], stdout=subprocess.DEVNULL)
+        E = C.CDLL(os.path.join(ROOT, "tests", "emu", "_build", "libemu.so"))
+        E.emu_last_error.restype = C.c_char_p
+    done = skipped = 0
+    worst = 0.0
+    for case in range(n_cases):
+        s = random_spec(rng)
+        try:
+            st = T.Structure(s)
+        except T.TowrB200Error as e:
+            skipped += 1
+            print("case %d refused (%s): %s" % (case, str(e)[:90], describe(s)))
+            continue
+        try:
+            p = O.Problem(to_oracle_spec(O, s))
+        except RuntimeError as e:
+            raise SystemExit("case %d: the product accepts what the oracle refuses (%s): %s" % (case, e, describe(s)))
+        ok = (st.n_vars, st.n_rows) == (len(p.x0()), sum(n for _, n in p.con_sets()))
+        gap = s.terrain_id == 3
+        optimise = any(int(s.constraints[i]) == int(T.TotalTime) for i in range(s.n_constraints))
+        x0 = st.x0(s)
+        ok = ok and tol_ratio(x0, p.x0()) <= 1.0
+        xs = [perturbed(x0, 100 + case, 0.03), x0]
+        r_o, c_o, _ = p.eval_jac(xs[0])
+        rows, cols = st.pattern()
+        if not gap:
+            ok = ok and len(rows) == len(r_o) and np.array_equal(rows, r_o) and np.array_equal(cols, c_o)
+        if gpu:
+            b = T.Batch(st, len(xs))
+            b.set_all(s)
+            g_all, v_all = b.eval(np.stack(xs))
+            f_all, gr_all = b.eval_cost(np.stack(xs))
+        for i, x in enumerate(xs):
+            if gpu:
+                g, v, f, gr = g_all[i], v_all[i], f_all[i], gr_all[i]
+            else:
+                g, v = np.zeros(st.n_rows), np.zeros(st.nnz)
+                assert E.emu_eval(C.byref(s), x.ctypes.data_as(DP), g.ctypes.data_as(DP), v.ctypes.data_as(DP)) == 0, E.emu_last_error()
+                fa, gr = np.zeros(1), np.zeros(st.n_vars)
+                assert E.emu_eval_cost(C.byref(s), x.ctypes.data_as(DP), fa.ctypes.data_as(DP), gr.ctypes.data_as(DP)) == 0, E.emu_last_error()
+                f = fa[0]
+            try:                                             # strict band; optimised durations as in the parity tests
+                check_against_oracle(O, to_oracle_spec(O, s), st, x, g, v, optimise, superset=gap)
+                jac_ok = g_ok = True
+            except AssertionError as err:
+                print("case %d: %s" % (case, err))
+                jac_ok = g_ok = False
+            c_ok = tol_ratio(np.array([f]), np.array([p.eval_f(x)])) <= 1.0 and cost_gradient_ok(st, gr, p.eval_grad_f(x))
+            if not (ok and jac_ok and g_ok and c_ok):
+                raise SystemExit("case %d x%d FAILED (structure %s, jac %s, g %s, cost %s): %s" % (case, i, ok, jac_ok, g_ok, c_ok, describe(s)))
+        done += 1
+    print("fuzz_parity (%s): %d random formulations match the oracle, %d refused as unsupported; seed %d" %
+          ("CUDA path" if gpu else "host emulation", done, skipped, seed))
+
+
+if __name__ == "__main__":
+    main()

@@ -198,7 +198,7 @@ void BuildSampledCost(const HostProgram& hp, const towr_b200_spec& s, const std:
     t.job0 = static_cast<int>(jobs.size());
     t.item0 = n_items;
     t.scratch0 = item_doubles;
-    t.rec = energy ? (rt ? 6 : 4) : def.kind == kSampledAngMom ? 8 : 9;
+    t.rec = energy ? (rt ? 10 : 4) : def.kind == kSampledAngMom ? 8 : 9;
     const int term = static_cast<int>(terms.size());
     t.weight = weight;
     t.dtf = dt > 0.0 ? dt : 1.0;

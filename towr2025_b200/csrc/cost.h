@@ -37,14 +37,14 @@ struct SampledTerm {     // one cost term
   int item0;             // first item of the term among all terms' items
   int item_splines;      // items per sample: one per spline (energy) or one for the whole sample (ang-mom, ee-base-pos)
   int scratch0;          // first double of the term's item arrays in the kernel's item scratch
-  int rec;               // doubles kept per item: energy 4 (value, local time; 6 with optimised durations), ang-mom 8,
+  int rec;               // doubles kept per item: energy 4 (value, local time; 10 with optimised durations), ang-mom 8,
                          // ee-base-pos 9
   int foot, pad;         // ee-base-pos: the foot (EEBasePosCost::ee_)
   double weight, dtf;    // weight_, (dt_ > 0 ? dt_ : 1)
 };
 struct SampledSpline {   // a spline the term samples (force / torque of a foot, or base-ang)
   int node0, poly0, n_polys, foot, rt, is_torque;
-  int ps0;               // optimised durations: first (spline, phase) slot of the spline (phase sums, sample ranges)
+  int ps0;               // optimised durations: first (spline, phase) slot of the spline (first sample of each phase)
   int fix0;              // class-constant durations: the spline's first entry in fix_t / fix_seg (one per sample); -1 else
   double scale;          // 1, or torque_weight_ for a torque spline (energy_cost.cc:84)
   double mscale;         // 2 wdt, or 2 wdt torque_weight_ (energy_cost.cc:112,121)
@@ -86,9 +86,9 @@ constexpr size_t kSampledMaxShared = 200 * 1024;
 inline size_t SampledSharedBytes(const SampledHeader& h) {
   const size_t blob = (static_cast<size_t>(h.bytes) + 15) & ~static_cast<size_t>(15);
   const size_t doubles = static_cast<size_t>(kSampledRec) * (h.n_nodes + h.n_polys) + static_cast<size_t>(kSampledPolyRec) * h.n_polys +
-                         h.n_phases + static_cast<size_t>(h.item_doubles) + h.n_times + 8 + 2 * static_cast<size_t>(h.n_phase_slots) + h.n_scratch;
+                         h.n_phases + static_cast<size_t>(h.item_doubles) + h.n_times + 8 + h.n_scratch;
   return blob + sizeof(double) * doubles +
-         sizeof(int) * (static_cast<size_t>(h.n_items) + 2 * static_cast<size_t>(h.n_polys) + 2 * static_cast<size_t>(h.n_phase_slots) + 4);
+         sizeof(int) * (static_cast<size_t>(h.n_items) + 2 * static_cast<size_t>(h.n_polys) + static_cast<size_t>(h.n_phase_slots) + 4);
 }
 // shared memory per CTA up to which two CTAs of the kernel fit one SM (227 KB, 1 KB reserved per CTA)
 constexpr size_t kSampledTwoCtaShared = 112 * 1024;

@@ -112,12 +112,10 @@ SampledCostKernel(const unsigned char* __restrict__ blob_g, const ProblemConst* 
     for (int it = tid; it < H.n_items; it += kSampledThreads) SampledItem(V, W, I, p_ref_B, it);
     __syncthreads();
     TB_COST_CLK(4);
-    // summands (threads from the front) and, for the ee-schedule gradient, phase sums (threads from the back)
-    if (what & 1)
+    if (what & 1) {
       for (int k = tid; k < H.n_times; k += kSampledThreads) SampledSummand(V, W, k);
-    if (what & 2)
-      for (int q = kSampledThreads - 1 - tid; q < H.n_phase_slots; q += kSampledThreads) SampledPhaseSum(V, W, q);
-    __syncthreads();
+      __syncthreads();
+    }
     TB_COST_CLK(5);
     // one thread per term adds its samples in time order: the last lanes of the last warps, which have the fewest jobs
     if ((what & 1) && (tid & 31) == 31 && (kSampledThreads / 32 - 1 - (tid >> 5)) < H.n_terms)

@@ -41,10 +41,15 @@ struct Unfit : std::runtime_error {   // this range of segments does not fit the
 void PackRange(HostProgram& hp, const std::vector<SegmentRec>& wide, int seg0, int seg1, ProgramPart& part) {
   // distinct local times and durations
   std::vector<double> times, durs;
-  std::map<uint64_t, int> time_ix, dur_ix;
-  auto intern = [](std::map<uint64_t, int>& ix, std::vector<double>& tab, double a, double b, double c) {
-    uint64_t key;
-    std::memcpy(&key, &a, 8);
+  // records are shared by value of ALL three doubles: a run-time sample (global time, 0, 0) and a fixed-duration sample
+  // whose local time has the same bits (local time, t^2, t^3) are different records
+  using Key3 = std::array<uint64_t, 3>;
+  std::map<Key3, int> time_ix, dur_ix;
+  auto intern = [](std::map<Key3, int>& ix, std::vector<double>& tab, double a, double b, double c) {
+    Key3 key;
+    std::memcpy(&key[0], &a, 8);
+    std::memcpy(&key[1], &b, 8);
+    std::memcpy(&key[2], &c, 8);
     auto it = ix.find(key);
     if (it != ix.end()) return it->second;
     int i = static_cast<int>(tab.size() / 3);

@@ -35,16 +35,16 @@ __device__ __forceinline__ double Dot3(const double a[3], const double b[3]) { r
 
 // shared-memory work arrays of one CTA (one problem at a time), carved by SampledCarve
 struct SampledWork {
-  double *nodes, *coef, *prec, *pdur, *items, *inst, *fterm, *psum, *scratch;
+  double *nodes, *coef, *prec, *pdur, *items, *inst, *fterm, *scratch;
   int *iseg, *k0, *k1;   // iseg per item: polynomial within the spline | phase << 16; k0 / k1 per polynomial: its samples
-  int *pk0, *pk1;        // per (spline, phase) slot: the samples that fall into the phase
+  int* pk0;              // per (spline, phase) slot: the first sample that falls into the phase
 };
 // per-polynomial record (kSampledPolyRec doubles): T, T^2, T^3, T^4, their correctly rounded reciprocals (ExactDiv) and,
 // for optimised durations, the polynomial's end time within its spline (accumulated like Spline::GetSegmentID's `t += d`)
 enum { kPrT = 0, kPrT2, kPrT3, kPrR1, kPrR2, kPrR3, kPrR4, kPrT4, kPrEnd };
 
 // the item arrays of one term (N = item_splines * n_samples items, tm.rec doubles each):
-//   energy:      P[3N] the spline's value, t[N] local time, with optimised durations also X[2N] = m . dx/dT, m . vel
+//   energy:      P[3N] the spline's value, t[N] local time, with optimised durations also X[6N] = dx/dT[3], vel[3]
 //   ang-mom:     P[3N] d summand / d euler angle, t[N], X[3N] d summand / d euler rate, then e[N] = |L|^2
 //   ee-base-pos: P[3N] m b_R_w (the row vector of ee_base_pos_cost.cc:125), t[N] local time in the foot's motion
 //                spline, X[3N] d summand / d euler angle, then tb[N] local time in the base splines, e[N] = |e|^2
@@ -105,13 +105,11 @@ __device__ __forceinline__ SampledWork SampledCarve(const SampledHeader& H, unsi
   W.items = W.pdur + H.n_phases;
   W.inst = W.items + H.item_doubles;                     // per sample of every term: the summand of f
   W.fterm = W.inst + H.n_times;
-  W.psum = W.fterm + 8;                                  // per (spline, phase) slot: sum of m . dx/dT, sum of m . vel
-  W.scratch = W.psum + 2 * H.n_phase_slots;              // sums of the jobs whose columns other terms write too
+  W.scratch = W.fterm + 8;                               // sums of the jobs whose columns other terms write too
   W.iseg = reinterpret_cast<int*>(W.scratch + H.n_scratch);
   W.k0 = W.iseg + H.n_items;
   W.k1 = W.k0 + H.n_polys;
   W.pk0 = W.k1 + H.n_polys;
-  W.pk1 = W.pk0 + H.n_phase_slots;
   return W;
 }
 
@@ -137,7 +135,6 @@ __device__ __forceinline__ void SampledPhaseDurations(const SampledView& V, cons
 __device__ __forceinline__ void SampledPolyRecord(const SampledView& V, const SampledWork& W, int poly) {
   if (poly >= V.h->n_polys) {
     W.pk0[poly - V.h->n_polys] = 0x7FFFFFFF;
-    W.pk1[poly - V.h->n_polys] = 0;
     return;
   }
   const uint32_t pm = V.poly_meta[poly];
@@ -322,9 +319,6 @@ __device__ __forceinline__ void SampledItem(const SampledView& V, const SampledW
 #pragma unroll
     for (int d = 0; d < 3; ++d) A.P[3 * it + d] = pos[d];
     if (sp.rt) {
-      double m[3];
-#pragma unroll
-      for (int d = 0; d < 3; ++d) m[d] = sp.mscale * pos[d];   // energy_cost.cc:112, :121
       // PhaseSpline::GetJacobianOfPosWrtDurations (phase_spline.cc:67-93): dx/dT of the active polynomial
       // (polynomial.cc:236-257) through its share of the phase, and the phase the global time falls into
       const uint32_t pm = V.poly_meta[poly];
@@ -341,10 +335,9 @@ __device__ __forceinline__ void SampledItem(const SampledView& V, const SampledW
         dxdT[d] = inner * (dx - prev * vel[d]);
       }
       phase = PhaseAt(W, V.feet[sp.foot], tg);
-      A.X[2 * it] = Dot3(m, dxdT);
-      A.X[2 * it + 1] = Dot3(m, vel);
-      atomicMin(W.pk0 + sp.ps0 + phase, k);           // the phase's samples are pk0 .. pk1 - 1 (time order)
-      atomicMax(W.pk1 + sp.ps0 + phase, k + 1);
+#pragma unroll
+      for (int d = 0; d < 3; ++d) { A.X[6 * it + d] = dxdT[d]; A.X[6 * it + 3 + d] = vel[d]; }
+      atomicMin(W.pk0 + sp.ps0 + phase, k);           // the phase's samples start at pk0 (time order)
     }
   } else {
     // AngularMomentumCost (angular_momentum_cost.cc:67-101, 103-206): L = R I_b R^T omega, omega = M(euler) euler_rate
@@ -395,26 +388,6 @@ __device__ __forceinline__ void SampledItem(const SampledView& V, const SampledW
     }
   }
   W.iseg[git] = id | (phase << 16);
-}
-
-// ---- step 2b: phase slot `slot` of a spline with optimised durations: the sums of m . dx/dT and m . vel over the samples
-// of the phase, in time order.  PhaseDurations::GetJacobianOfPos (phase_durations.cc:126-154) gives column ph of the
-// ee-schedule +dx/dT for the samples of phase ph and -vel for those of every later phase (-vel - dx/dT in the last one).
-__device__ __forceinline__ void SampledPhaseSum(const SampledView& V, const SampledWork& W, int slot) {
-  int si = 0;
-  while (si + 1 < V.h->n_splines && (!V.splines[si].rt || slot >= V.splines[si].ps0 + V.feet[V.splines[si].foot].n_phases)) ++si;
-  int ti = 0;
-  while (ti + 1 < V.h->n_terms && si >= V.terms[ti + 1].spline0) ++ti;
-  const SampledTerm& tm = V.terms[ti];
-  const SampledTermArrays A = TermArrays(W, tm);
-  const int s = si - tm.spline0, K = tm.n_samples;
-  double sa = 0.0, sb = 0.0;
-  for (int k = W.pk0[slot]; k < W.pk1[slot]; ++k) {
-    sa += A.X[2 * (s * K + k)];
-    sb += A.X[2 * (s * K + k) + 1];
-  }
-  W.psum[2 * slot] = sa;
-  W.psum[2 * slot + 1] = sb;
 }
 
 // ---- step 2: the summand of sample `gk` (all terms; energy_cost.cc:80-87, angular_momentum_cost.cc:97)
@@ -556,18 +529,34 @@ __device__ __forceinline__ void SampledJobGradient(const SampledView& V, const S
       EmitColumn(jb, W, gp, 3 + dim, gvel[dim]);
     }
   } else {
-    // column `ph` of the foot's ee-schedule from the phase sums (SampledPhaseSum): force spline, then torque spline
+    // column `ph` of the foot's ee-schedule (energy_cost.cc:129-157): per sample in time order, force spline then torque
+    // spline, m(r) * J(r, ph) for r = 0, 1, 2 with J = GetJacobianOfPosWrtDurations = PhaseDurations::GetJacobianOfPos
+    // (phase_durations.cc:126-154): +dx/dT in the column of the sample's own phase (unless that is the last phase), -vel
+    // in the columns of all earlier phases (-vel, then -= dx/dT when the sample is in the last phase).  The same
+    // operations in the same order as the reference: these sums cancel, a regrouped sum leaves the 1e-12 band.
     const int ph = jb.node;
+    const SampledSpline& sf = V.splines[tm.spline0 + jb.spline];
+    const int last = V.feet[sf.foot].n_phases - 1;
+    int k_first = K;                                   // samples of earlier phases contribute nothing to this column
+    for (int c = ph; c <= last; ++c) k_first = W.pk0[sf.ps0 + c] < k_first ? W.pk0[sf.ps0 + c] : k_first;
     double g = 0.0;
-    for (int q = 0; q <= jb.aux; ++q) {
-      const SampledSpline& sp = V.splines[tm.spline0 + jb.spline + q];
-      const int last = V.feet[sp.foot].n_phases - 1;
-      const double* ps = W.psum + 2 * sp.ps0;
-      double c = ps[2 * ph];                         // phase ph itself (never the last phase: it has no column)
-      for (int later = ph + 1; later <= last; ++later) c -= ps[2 * later + 1];
-      c -= ps[2 * last];
-      g += c;
-    }
+    for (int k = k_first; k < K; ++k)
+      for (int q = 0; q <= jb.aux; ++q) {
+        const SampledSpline& sp = V.splines[tm.spline0 + jb.spline + q];
+        const int it = (jb.spline + q) * K + k;
+        const int cur = W.iseg[tm.item0 + it] >> 16;
+        if (ph > cur) continue;
+        const double* dxdT = A.X + 6 * it;
+        const double* vel = dxdT + 3;
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+          const double m = sp.mscale * A.P[3 * it + r];
+          double J;
+          if (ph == cur) J = dxdT[r];                  // never the last phase: it has no column
+          else J = cur == last ? (-1 * vel[r]) - dxdT[r] : -1 * vel[r];
+          g += m * J;
+        }
+      }
     EmitColumn(jb, W, gp, 0, g);
   }
 }
