@@ -44,7 +44,8 @@ struct SampledWork {
 enum { kPrT = 0, kPrT2, kPrT3, kPrR1, kPrR2, kPrR3, kPrR4, kPrT4, kPrEnd };
 
 // the item arrays of one term (N = item_splines * n_samples items, tm.rec doubles each):
-//   energy:      P[3N] the spline's value, t[N] local time, with optimised durations also X[6N] = dx/dT[3], vel[3]
+//   energy:      P[3N] the spline's value, t[N] local time, with optimised durations also X[6N]: the sample's products
+//                m(r) * J(r, col) for the ee-schedule column of its own phase [3] and for every earlier column [3]
 //   ang-mom:     P[3N] d summand / d euler angle, t[N], X[3N] d summand / d euler rate, then e[N] = |L|^2
 //   ee-base-pos: P[3N] m b_R_w (the row vector of ee_base_pos_cost.cc:125), t[N] local time in the foot's motion
 //                spline, X[3N] d summand / d euler angle, then tb[N] local time in the base splines, e[N] = |e|^2
@@ -334,9 +335,17 @@ __device__ __forceinline__ void SampledItem(const SampledView& V, const SampledW
                           ExactDiv((2 * t2) * (((3.0 * x0 - 3.0 * x1) + (2 * T) * v0) + T * v1), T3, r3);
         dxdT[d] = inner * (dx - prev * vel[d]);
       }
-      phase = PhaseAt(W, V.feet[sp.foot], tg);
+      const SampledFoot ft = V.feet[sp.foot];
+      phase = PhaseAt(W, ft, tg);
+      // PhaseDurations::GetJacobianOfPos (phase_durations.cc:126-154): +dx/dT in the column of the sample's own phase, -vel
+      // in every earlier column (-vel, then -= dx/dT when the sample is in the last phase); times m(r) (energy_cost.cc:112)
+      const bool in_last = phase == ft.n_phases - 1;
 #pragma unroll
-      for (int d = 0; d < 3; ++d) { A.X[6 * it + d] = dxdT[d]; A.X[6 * it + 3 + d] = vel[d]; }
+      for (int d = 0; d < 3; ++d) {
+        const double m = sp.mscale * pos[d];
+        A.X[6 * it + d] = m * dxdT[d];
+        A.X[6 * it + 3 + d] = m * (in_last ? (-1 * vel[d]) - dxdT[d] : -1 * vel[d]);
+      }
       atomicMin(W.pk0 + sp.ps0 + phase, k);           // the phase's samples start at pk0 (time order)
     }
   } else {
@@ -530,33 +539,33 @@ __device__ __forceinline__ void SampledJobGradient(const SampledView& V, const S
     }
   } else {
     // column `ph` of the foot's ee-schedule (energy_cost.cc:129-157): per sample in time order, force spline then torque
-    // spline, m(r) * J(r, ph) for r = 0, 1, 2 with J = GetJacobianOfPosWrtDurations = PhaseDurations::GetJacobianOfPos
-    // (phase_durations.cc:126-154): +dx/dT in the column of the sample's own phase (unless that is the last phase), -vel
-    // in the columns of all earlier phases (-vel, then -= dx/dT when the sample is in the last phase).  The same
-    // operations in the same order as the reference: these sums cancel, a regrouped sum leaves the 1e-12 band.
+    // spline, m(r) * J(r, ph) for r = 0, 1, 2 with J = GetJacobianOfPosWrtDurations (the products are formed in the item
+    // step).  The same operations in the same order as the reference: these sums cancel, a regrouped sum leaves the
+    // 1e-12 band.
     const int ph = jb.node;
     const SampledSpline& sf = V.splines[tm.spline0 + jb.spline];
     const int last = V.feet[sf.foot].n_phases - 1;
     int k_first = K;                                   // samples of earlier phases contribute nothing to this column
     for (int c = ph; c <= last; ++c) k_first = W.pk0[sf.ps0 + c] < k_first ? W.pk0[sf.ps0 + c] : k_first;
     double g = 0.0;
-    for (int k = k_first; k < K; ++k)
-      for (int q = 0; q <= jb.aux; ++q) {
-        const SampledSpline& sp = V.splines[tm.spline0 + jb.spline + q];
-        const int it = (jb.spline + q) * K + k;
-        const int cur = W.iseg[tm.item0 + it] >> 16;
-        if (ph > cur) continue;
-        const double* dxdT = A.X + 6 * it;
-        const double* vel = dxdT + 3;
-#pragma unroll
-        for (int r = 0; r < 3; ++r) {
-          const double m = sp.mscale * A.P[3 * it + r];
-          double J;
-          if (ph == cur) J = dxdT[r];                  // never the last phase: it has no column
-          else J = cur == last ? (-1 * vel[r]) - dxdT[r] : -1 * vel[r];
-          g += m * J;
-        }
-      }
+    const int* seg = W.iseg + tm.item0;
+    // the products of the item step: own-phase column or earlier column; a later column gets m(r) * 0
+    auto add = [&](int it) {
+      const int cur = seg[it] >> 16;
+      const double* X = A.X + 6 * it + (ph == cur ? 0 : 3);
+      const bool in = ph <= cur;
+      g += in ? X[0] : 0.0;
+      g += in ? X[1] : 0.0;
+      g += in ? X[2] : 0.0;
+    };
+    const int it_f = jb.spline * K, it_t = it_f + K;
+    if (jb.aux) {
+#pragma unroll 4
+      for (int k = k_first; k < K; ++k) { add(it_f + k); add(it_t + k); }   // force spline, then torque spline (:131-156)
+    } else {
+#pragma unroll 4
+      for (int k = k_first; k < K; ++k) add(it_f + k);
+    }
     EmitColumn(jb, W, gp, 0, g);
   }
 }
