@@ -60,6 +60,18 @@ def random_spec(rng):
     s.dt_constraint_force = float(rng.choice([0.02, 0.05, -1.0]))
     s.dt_constraint_torque = float(rng.choice([0.02, 0.06, -1.0]))
     s.dt_constraint_base_motion = float(rng.choice([0.025, 0.04]))
+    if rng.random() < 0.4:                                   # spline resolution (parameters.cc:61-66)
+        s.duration_base_polynomial = float(rng.choice([0.1, 0.15, 0.07]))
+        s.force_polynomials_per_stance_phase = int(rng.choice([2, 3, 4]))
+        s.torque_polynomials_per_stance_phase = int(rng.choice([2, 3, 4]))
+        s.ee_polynomials_per_swing_phase = int(rng.choice([2, 3]))
+    if rng.random() < 0.3:                                   # stance tracking: bounds only (nlp_formulation.cc:218-231)
+        s.enable_stance_tracking = 1
+        for e in range(n_ee):
+            s.n_stance_positions[e] = 4
+            for k in range(4):
+                s.ee_stance_position[e][k][0] = float(rng.uniform(-0.3, 1.2))
+                s.ee_stance_position[e][k][1] = float(rng.uniform(-0.3, 0.3))
     if rng.random() < 0.4:
         defs = []
         for _ in range(int(rng.integers(1, 3))):
@@ -115,6 +127,9 @@ def main():
         optimise = any(int(s.constraints[i]) == int(T.TotalTime) for i in range(s.n_constraints))
         x0 = st.x0(s)
         ok = ok and tol_ratio(x0, p.x0()) <= 1.0
+        clip = lambda a: np.clip(a, -1e20, 1e20)           # ifopt::inf
+        for mine, ref in zip(st.var_bounds(s) + st.con_bounds(s), p.var_bounds() + p.con_bounds()):
+            ok = ok and tol_ratio(clip(mine), clip(ref)) <= 1.0
         xs = [perturbed(x0, 100 + case, 0.03), x0]
         r_o, c_o, _ = p.eval_jac(xs[0])
         rows, cols = st.pattern()
@@ -125,6 +140,10 @@ def main():
             b.set_all(s)
             g_all, v_all = b.eval(np.stack(xs))
             f_all, gr_all = b.eval_cost(np.stack(xs))
+            dt = float(rng.choice([0.05, 0.013]))            # SaveTrajectoryToCSV's sampling loop (save_data.cpp:54-119)
+            rows = b.sample_trajectory(np.stack(xs), dt)
+            for i, x in enumerate(xs):
+                ok = ok and tol_ratio(rows[i], p.sample_trajectory(x, dt)) <= 1.0
         for i, x in enumerate(xs):
             if gpu:
                 g, v, f, gr = g_all[i], v_all[i], f_all[i], gr_all[i]
