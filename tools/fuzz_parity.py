@@ -140,6 +140,34 @@ def main():
             b.set_all(s)
             g_all, v_all = b.eval(np.stack(xs))
             f_all, gr_all = b.eval_cost(np.stack(xs))
+            # the dynamic-only transfer (constants once, x-dependent entries per eval) equals the full result bit for bit
+            full = np.stack([b.constant_values(i) for i in range(len(xs))])
+            b.eval(np.stack(xs), T.EVAL_JAC_DYNAMIC, jac_out=full)
+            ok = ok and np.array_equal(full, v_all)
+            # a second problem of the class with its own robot (mass, inertia, kinematic box) and terrain of the same
+            # kind: per-problem constants, checked against its own oracle problem
+            s_b = T.Spec()
+            C.memmove(C.byref(s_b), C.byref(s), C.sizeof(s))
+            s_b.mass *= 1.3
+            s_b.inertia[0] *= 1.2
+            s_b.inertia[5] += 0.01
+            for e in range(s.n_ee):
+                s_b.nominal_stance[e][0] += 0.02
+                s_b.max_dev[e][2] *= 1.1
+            if st.accepts(s_b):
+                b.set_problem(1, s_b)
+                g_b, v_b = b.eval(np.stack(xs))
+                f_b, gr_b = b.eval_cost(np.stack(xs))
+                try:
+                    check_against_oracle(O, to_oracle_spec(O, s_b), st, xs[1], g_b[1], v_b[1], optimise, superset=gap)
+                except AssertionError as err:
+                    print("case %d (second robot): %s" % (case, err))
+                    ok = False
+                p_b = O.Problem(to_oracle_spec(O, s_b))
+                ok = ok and tol_ratio(np.array([f_b[1]]), np.array([p_b.eval_f(xs[1])])) <= 1.0
+                ok = ok and cost_gradient_ok(st, gr_b[1], p_b.eval_grad_f(xs[1]))
+                ok = ok and np.array_equal(g_b[0], g_all[0]) and np.array_equal(v_b[0], v_all[0])
+                b.set_problem(1, s)
             dt = float(rng.choice([0.05, 0.013]))            # SaveTrajectoryToCSV's sampling loop (save_data.cpp:54-119)
             rows = b.sample_trajectory(np.stack(xs), dt)
             for i, x in enumerate(xs):
