@@ -185,8 +185,11 @@ def parity_ok(a, b, mask=None):
     (d(I_w wd + w x I_w w)/d euler nodes) as A_pos*B_pos + A_vel*B_vel + A_acc*B_acc from dense 3x3 partials, the reference
     sums about ten sparse row products in Eigen's order (single_rigid_body_dynamics.cc:124-166).  Where those terms cancel
     the two associations differ by a few 1e-16 of the LARGEST term, which can exceed 1e-12 of the (small) result: measured
-    over 20 classes x 8 x: 6 of 160128 entries of that block outside the strict band, worst 2.4 x.
-    Entries under the mask may therefore reach REGROUPED_BAND x the strict band; nothing else may leave it."""
+    over 33 classes x 8 x: 13 of 246240 entries of that block outside the strict band, worst 2.4 x.
+    Entries under the mask may therefore reach REGROUPED_BAND x the strict band - or, where the block's entries are large,
+    the absolute floor ATOL taken relative to the block's largest entry: a monoped with an unbalanced inertia tensor at
+    its initial guess (zero angular velocity) has an exact 0 in the kernel where the reference's sum leaves 2.3e-13, the
+    rounding residue of terms near 1e3 beside entries of 94 (tools/fuzz_parity.py).  Nothing else may leave the strict band."""
     a, b = np.asarray(a), np.asarray(b)
     assert a.shape == b.shape and np.isfinite(a).all() and np.isfinite(b).all()
     if a.size == 0:
@@ -194,7 +197,18 @@ def parity_ok(a, b, mask=None):
     ratio = np.abs(a - b) / (ATOL + RTOL * np.abs(b))
     if mask is None:
         return bool(ratio.max() <= 1.0)
-    return bool((ratio[~mask] <= 1.0).all() and (ratio[mask] <= REGROUPED_BAND).all())
+    excused = _regrouped_floor(a, b, mask)
+    return bool((ratio[~mask] <= 1.0).all() and ((ratio <= REGROUPED_BAND) | excused)[mask].all())
+
+
+def _regrouped_floor(a, b, mask):
+    """Entries of the regrouped block that agree within the band whose absolute floor is relative to the block's largest
+    entry (see parity_ok)."""
+    ok = np.zeros(a.shape, bool)
+    if mask.any():
+        scale = max(1.0, float(np.abs(b[mask]).max()))
+        ok[mask] = np.abs(a[mask] - b[mask]) <= ATOL * scale + RTOL * np.abs(b[mask])
+    return ok
 
 
 POW_BAND, POW_FRACTION = 10.0, 5e-3
@@ -212,6 +226,8 @@ def pow_ok(a, b, mask=None):
     if a.size == 0:
         return True
     ratio = np.abs(a - b) / (ATOL + RTOL * np.abs(b))
+    if mask is not None:
+        ratio = np.where(_regrouped_floor(a, b, mask), 0.0, ratio)       # the regrouped block's own floor (parity_ok)
     lim = np.where(mask, max(REGROUPED_BAND, POW_BAND), POW_BAND) if mask is not None else POW_BAND
     out = ratio > (np.where(mask, REGROUPED_BAND, 1.0) if mask is not None else 1.0)
     return bool((ratio <= lim).all() and out.mean() <= POW_FRACTION)

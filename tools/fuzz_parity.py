@@ -88,6 +88,19 @@ def random_spec(rng):
     return s
 
 
+def second_robot(s):
+    """The same formulation for a robot with its own mass, inertia and kinematic box (per-problem constants of a class)."""
+    s_b = T.Spec()
+    C.memmove(C.byref(s_b), C.byref(s), C.sizeof(s))
+    s_b.mass *= 1.3
+    s_b.inertia[0] *= 1.2
+    s_b.inertia[5] += 0.01
+    for e in range(s.n_ee):
+        s_b.nominal_stance[e][0] += 0.02
+        s_b.max_dev[e][2] *= 1.1
+    return s_b
+
+
 def describe(s):
     n_ee = s.n_ee
     return "robot_ee=%d T-phases=%s start=%s terrain=%d cons=%s dur=%s eelin=%d costs=%s swing=%d" % (
@@ -146,14 +159,7 @@ def main():
             ok = ok and np.array_equal(full, v_all)
             # a second problem of the class with its own robot (mass, inertia, kinematic box) and terrain of the same
             # kind: per-problem constants, checked against its own oracle problem
-            s_b = T.Spec()
-            C.memmove(C.byref(s_b), C.byref(s), C.sizeof(s))
-            s_b.mass *= 1.3
-            s_b.inertia[0] *= 1.2
-            s_b.inertia[5] += 0.01
-            for e in range(s.n_ee):
-                s_b.nominal_stance[e][0] += 0.02
-                s_b.max_dev[e][2] *= 1.1
+            s_b = second_robot(s)
             if st.accepts(s_b):
                 b.set_problem(1, s_b)
                 g_b, v_b = b.eval(np.stack(xs))
@@ -172,6 +178,15 @@ def main():
             rows = b.sample_trajectory(np.stack(xs), dt)
             for i, x in enumerate(xs):
                 ok = ok and tol_ratio(rows[i], p.sample_trajectory(x, dt)) <= 1.0
+        if not gpu:                                          # the second robot as a class of its own (the emulation has no batch)
+            s_b = second_robot(s)
+            g, v = np.zeros(st.n_rows), np.zeros(st.nnz)
+            assert E.emu_eval(C.byref(s_b), x0.ctypes.data_as(DP), g.ctypes.data_as(DP), v.ctypes.data_as(DP)) == 0, E.emu_last_error()
+            try:
+                check_against_oracle(O, to_oracle_spec(O, s_b), st, x0, g, v, optimise, superset=gap)
+            except AssertionError as err:
+                print("case %d (second robot): %s" % (case, err))
+                ok = False
         for i, x in enumerate(xs):
             if gpu:
                 g, v, f, gr = g_all[i], v_all[i], f_all[i], gr_all[i]
