@@ -160,12 +160,18 @@ def main():
             # a second problem of the class with its own robot (mass, inertia, kinematic box) and terrain of the same
             # kind: per-problem constants, checked against its own oracle problem
             s_b = second_robot(s)
+            other = int(rng.integers(0, 8))                  # ... on another terrain, where the class admits it
+            keep_terrain = s_b.terrain_id
+            s_b.terrain_id = other
+            if not st.accepts(s_b):
+                s_b.terrain_id = keep_terrain
+            gap_b = gap or s_b.terrain_id == 3
             if st.accepts(s_b):
                 b.set_problem(1, s_b)
                 g_b, v_b = b.eval(np.stack(xs))
                 f_b, gr_b = b.eval_cost(np.stack(xs))
                 try:
-                    check_against_oracle(O, to_oracle_spec(O, s_b), st, xs[1], g_b[1], v_b[1], optimise, superset=gap)
+                    check_against_oracle(O, to_oracle_spec(O, s_b), st, xs[1], g_b[1], v_b[1], optimise, superset=gap_b)
                 except AssertionError as err:
                     print("case %d (second robot): %s" % (case, err))
                     ok = False
