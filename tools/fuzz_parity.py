@@ -15,7 +15,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 import towr2025_b200 as T                      # noqa: E402
 from oracle import oracle_py as O              # noqa: E402  (checker)
-from util import check_against_oracle, cost_gradient_ok, perturbed, to_oracle_spec, tol_ratio, set_ee_linear, set_terrain_table   # noqa: E402
+from util import check_against_oracle, cost_gradient_ok, parity_ok, pow_ok, perturbed, to_oracle_spec, tol_ratio, set_ee_linear, set_terrain_table   # noqa: E402
 
 DP = C.POINTER(C.c_double)
 
@@ -101,6 +101,12 @@ def second_robot(s):
     return s_b
 
 
+def note(ok, passed, what):
+    if not passed:
+        print("  failed check: " + what, flush=True)
+    return ok and passed
+
+
 def describe(s):
     n_ee = s.n_ee
     return "robot_ee=%d T-phases=%s start=%s terrain=%d cons=%s dur=%s eelin=%d costs=%s swing=%d" % (
@@ -156,7 +162,7 @@ def main():
             # the dynamic-only transfer (constants once, x-dependent entries per eval) equals the full result bit for bit
             full = np.stack([b.constant_values(i) for i in range(len(xs))])
             b.eval(np.stack(xs), T.EVAL_JAC_DYNAMIC, jac_out=full)
-            ok = ok and np.array_equal(full, v_all)
+            ok = note(ok, np.array_equal(full, v_all), 'dynamic-only transfer')
             # a second problem of the class with its own robot (mass, inertia, kinematic box) and terrain of the same
             # kind: per-problem constants, checked against its own oracle problem
             s_b = second_robot(s)
@@ -176,14 +182,19 @@ def main():
                     print("case %d (second robot): %s" % (case, err))
                     ok = False
                 p_b = O.Problem(to_oracle_spec(O, s_b))
-                ok = ok and tol_ratio(np.array([f_b[1]]), np.array([p_b.eval_f(xs[1])])) <= 1.0
-                ok = ok and cost_gradient_ok(st, gr_b[1], p_b.eval_grad_f(xs[1]))
-                ok = ok and np.array_equal(g_b[0], g_all[0]) and np.array_equal(v_b[0], v_all[0])
+                ok = note(ok, tol_ratio(np.array([f_b[1]]), np.array([p_b.eval_f(xs[1])])) <= 1.0, 'second problem: f')
+                ok = note(ok, cost_gradient_ok(st, gr_b[1], p_b.eval_grad_f(xs[1])), 'second problem: cost gradient')
+                ok = note(ok, np.array_equal(g_b[0], g_all[0]) and np.array_equal(v_b[0], v_all[0]), 'first problem changed by the second')
                 b.set_problem(1, s)
             dt = float(rng.choice([0.05, 0.013]))            # SaveTrajectoryToCSV's sampling loop (save_data.cpp:54-119)
             rows = b.sample_trajectory(np.stack(xs), dt)
-            for i, x in enumerate(xs):
-                ok = ok and tol_ratio(rows[i], p.sample_trajectory(x, dt)) <= 1.0
+            for i, x in enumerate(xs):                       # as tests/test_trajectory.py: strict against exact powers
+                if optimise:
+                    with O.pow_mode(1):
+                        ok = note(ok, parity_ok(rows[i], p.sample_trajectory(x, dt)), 'trajectory sampler (exact-power oracle)')
+                    ok = note(ok, pow_ok(rows[i], p.sample_trajectory(x, dt)), 'trajectory sampler (std::pow oracle)')
+                else:
+                    ok = note(ok, parity_ok(rows[i], p.sample_trajectory(x, dt)), 'trajectory sampler')
         if not gpu:                                          # the second robot as a class of its own (the emulation has no batch)
             s_b = second_robot(s)
             g, v = np.zeros(st.n_rows), np.zeros(st.nnz)
