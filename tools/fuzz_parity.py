@@ -79,6 +79,18 @@ def random_spec(rng):
             defs.append((int(rng.integers(0, 2)), int(rng.integers(0, 2)), terms, float(rng.uniform(0.01, 0.5)), float(rng.choice([0.1, 0.06]))))
         set_ee_linear(s, defs)
     costs = [(int(c), float(rng.uniform(1e-4, 1.0))) for c in range(4) if rng.random() < 0.4]
+    if rng.random() < 0.15 and len(costs) < 4:               # a family listed twice: its columns get two writers
+        costs.append((int(rng.choice([2, 3])), float(rng.uniform(1e-3, 0.5))))
+    s.dt_cost_energy = float(rng.choice([0.02, 0.05, 0.0]))
+    s.energy_cost_torque_weight = float(rng.choice([1.0, 0.0, 0.3]))
+    s.dt_cost_ang_mom = float(rng.choice([0.02, 0.07]))
+    s.dt_cost_swing_ee_base_pos_tracking = float(rng.choice([0.05, 0.03]))
+    if rng.random() < 0.3:                                   # individual NodeCost terms (node_cost.cc:36-45)
+        terms = [(int(rng.integers(0, 6)), int(rng.integers(0, n_ee)), int(rng.integers(0, 2)), int(rng.integers(0, 3)),
+                  float(rng.uniform(1e-4, 1.0))) for _ in range(int(rng.integers(1, 6)))]
+        s.n_node_costs = len(terms)
+        for i, (k, ee, deriv, dim, w) in enumerate(terms):
+            s.node_cost_set[i], s.node_cost_ee[i], s.node_cost_deriv[i], s.node_cost_dim[i], s.node_cost_weight[i] = k, ee, deriv, dim, w
     s.n_costs = len(costs)
     for i, (c, w) in enumerate(costs):
         s.cost_ids[i], s.cost_weights[i] = c, w
