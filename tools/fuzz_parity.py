@@ -2,7 +2,10 @@
 swing, feet that differ), random terrain, constraint subset, sampling steps, EELinearConstraint definitions and costs.
 TEST INFRASTRUCTURE.  Default: the host emulation of the device arithmetic (tests/emu, no GPU); `gpu`: the CUDA path.
 
-    python tools/fuzz_parity.py [gpu] [n_cases] [seed]
+    python tools/fuzz_parity.py [gpu | cross] [n_cases] [seed]
+
+`cross`: the same random formulations through the two oracle legs instead (oracle/*.cc against oracle/oracle_np.py):
+structure, bounds, g, the stored-entry pattern and values, f and its gradient.
 """
 import ctypes as C
 import os
@@ -127,7 +130,42 @@ def describe(s):
         s.n_ee_linear, [int(s.cost_ids[i]) for i in range(s.n_costs)], s.enable_swing_ee_base_pos_tracking)
 
 
+def cross_check(n_cases, seed):
+    from oracle import oracle_np as N
+    rng = np.random.default_rng(seed)
+    clip = lambda a: np.clip(a, -1e20, 1e20)
+    for case in range(n_cases):
+        s = to_oracle_spec(O, random_spec(rng))
+        p, f = O.Problem(s), N.Formulation(s)
+        why = []
+        if [(v.name, v.rows()) for v in f.var_sets] != p.var_sets() or [(c.name, c.n_rows) for c in f.con_sets] != p.con_sets():
+            why.append("sets")
+        x0 = p.x0()
+        if tol_ratio(f.x0(), x0) > 1.0:
+            why.append("x0")
+        for a, b in zip(f.var_bounds() + f.con_bounds(), p.var_bounds() + p.con_bounds()):
+            if tol_ratio(clip(a), clip(b)) > 1.0:
+                why.append("bounds")
+        x = perturbed(x0, 100 + case, 0.03)
+        if tol_ratio(f.eval_g(x), p.eval_g(x)) > 1.0:
+            why.append("g")
+        r, c, v = f.eval_jac(x)
+        ro, co, vo = p.eval_jac(x)
+        if len(r) != len(ro) or not (np.array_equal(r, ro) and np.array_equal(c, co)):
+            why.append("pattern")
+        elif tol_ratio(v, vo) > 1.0:
+            why.append("jacobian values")
+        if tol_ratio(np.array([f.eval_f(x)]), np.array([p.eval_f(x)])) > 1.0 or tol_ratio(f.eval_grad_f(x), p.eval_grad_f(x)) > 1.0:
+            why.append("costs")
+        if why:
+            raise SystemExit("cross case %d FAILED (%s): %s" % (case, ", ".join(why), describe(s)))
+    print("fuzz_parity (oracle legs): the C++ and the numpy restatement agree on %d random formulations; seed %d" % (n_cases, seed))
+
+
 def main():
+    if "cross" in sys.argv:
+        nums = [a for a in sys.argv[1:] if a.lstrip("-").isdigit()]
+        return cross_check(int(nums[0]) if nums else 20, int(nums[1]) if len(nums) > 1 else 1)
     gpu = "gpu" in sys.argv
     nums = [a for a in sys.argv[1:] if a.lstrip("-").isdigit()]
     n_cases = int(nums[0]) if nums else 60
