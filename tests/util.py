@@ -185,7 +185,7 @@ def parity_ok(a, b, mask=None):
     (d(I_w wd + w x I_w w)/d euler nodes) as A_pos*B_pos + A_vel*B_vel + A_acc*B_acc from dense 3x3 partials, the reference
     sums about ten sparse row products in Eigen's order (single_rigid_body_dynamics.cc:124-166).  Where those terms cancel
     the two associations differ by a few 1e-16 of the LARGEST term, which can exceed 1e-12 of the (small) result: measured
-    over 33 classes x 8 x: 13 of 246240 entries of that block outside the strict band, worst 2.4 x.
+    over 37 classes x 8 x: 14 of 270720 entries of that block outside the strict band, worst 2.4 x.
     Entries under the mask may therefore reach REGROUPED_BAND x the strict band - or, where the block's entries are large,
     the absolute floor ATOL taken relative to the block's largest entry: a monoped with an unbalanced inertia tensor at
     its initial guess (zero angular velocity) has an exact 0 in the kernel where the reference's sum leaves 2.3e-13, the
