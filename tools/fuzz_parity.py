@@ -245,6 +245,11 @@ def main():
                     ok = note(ok, pow_ok(rows[i], p.sample_trajectory(x, dt)), 'trajectory sampler (std::pow oracle)')
                 else:
                     ok = note(ok, parity_ok(rows[i], p.sample_trajectory(x, dt)), 'trajectory sampler')
+                if not ok:                                   # where: sample, column (save_data.cpp:68-112 order), values
+                    ref = p.sample_trajectory(x, dt)
+                    bad = np.argwhere(np.abs(rows[i] - ref) > 1e-14 + 1e-12 * np.abs(ref))
+                    print("  dt %g, %d entries differ; first: %s" % (dt, len(bad), [(int(a), int(c), float(rows[i][a, c]), float(ref[a, c])) for a, c in bad[:6]]))
+                    print("  columns that differ:", sorted(set(int(c) for _, c in bad)))
         if not gpu:                                          # the second robot as a class of its own (the emulation has no batch)
             s_b = second_robot(s)
             g, v = np.zeros(st.n_rows), np.zeros(st.nnz)

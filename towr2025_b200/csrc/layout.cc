@@ -276,8 +276,8 @@ void BuildLayout(const towr_b200_spec& s, HostProgram& hp) {
       pr.node0 = node_slot + p;
       pr.pad = 0;
       pr.T = v.poly_T[p];
-      pr.T2 = std::pow(pr.T, 2);
-      pr.T3 = std::pow(pr.T, 3);
+      pr.T2 = RuntimePow(pr.T, 2);
+      pr.T3 = RuntimePow(pr.T, 3);
       hp.polys.push_back(pr);
     }
     node_slot += v.n_nodes;

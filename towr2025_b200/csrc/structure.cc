@@ -33,9 +33,14 @@ std::vector<double> SampleTimes(double T, double dt) {
   return ts;
 }
 
+double RuntimePow(double x, int n) {
+  volatile int e = n;          // not a compile-time constant: no folding into x * x
+  return std::pow(x, static_cast<double>(e));
+}
+
 void HermiteBasis(double T, double t, double o[12]) {
-  const double t2 = std::pow(t, 2), t3 = std::pow(t, 3);
-  const double T2 = std::pow(T, 2), T3 = std::pow(T, 3);
+  const double t2 = RuntimePow(t, 2), t3 = RuntimePow(t, 3);
+  const double T2 = RuntimePow(T, 2), T3 = RuntimePow(T, 3);
   // position
   o[0] = (2 * t3) / T3 - (3 * t2) / T2 + 1;   o[1] = t - (2 * t2) / T + t3 / T2;
   o[2] = (3 * t2) / T2 - (2 * t3) / T3;       o[3] = t3 / T2 - t2 / T;
@@ -108,8 +113,8 @@ class Builder {
     r.poly = set.poly0 + a.poly;
     r.pad = 0;
     r.t = a.t_local;
-    r.t2 = std::pow(a.t_local, 2);
-    r.t3 = std::pow(a.t_local, 3);
+    r.t2 = RuntimePow(a.t_local, 2);
+    r.t3 = RuntimePow(a.t_local, 3);
     a.sample = static_cast<int>(hp_.samples.size());
     hp_.samples.push_back(r);
     return a;

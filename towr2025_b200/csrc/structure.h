@@ -21,6 +21,12 @@ std::vector<double> SampleTimes(double T, double dt);
 void HermiteBasis(double T, double t, double out[12]);
 // segment lookup with the 1e-10 junction rule (spline.cc:48-78)
 int SegmentId(double t_global, const std::vector<double>& durations);
+// std::pow(x, n) evaluated by libm at run time.  The reference takes most powers with an exponent that is a run-time
+// value (polynomial.cc:67-69: std::pow(t, c)), and glibc's pow(x, 2.0) is not always x * x - but g++ folds a literal
+// std::pow(x, 2) into x * x.  The class tables must hold the same bits as the oracle's powers (one ulp of t^2 shows as 6e-14
+// where a contact force of 0.007 N is the rest of terms near 400; tools/fuzz_parity.py), so every power of the host
+// builder goes through here.
+double RuntimePow(double x, int n);
 double LocalTime(double t_global, int id, const std::vector<double>& durations);
 // g_cap > 0 overrides the G slots per segment (the batch lowers it when a class's tables leave less shared memory)
 void BuildProgram(const towr_b200_spec& s, HostProgram& hp, int g_cap = 0);

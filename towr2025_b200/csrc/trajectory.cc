@@ -60,8 +60,8 @@ void BuildTrajTablesAt(const HostProgram& hp, const towr_b200_spec& s, const std
     for (int p = 0; p < v.n_polys(); ++p) {
       const double T = v.poly_T[p];
       o.poly_T.push_back(T);
-      o.poly_T.push_back(std::pow(T, 2));
-      o.poly_T.push_back(std::pow(T, 3));
+      o.poly_T.push_back(RuntimePow(T, 2));
+      o.poly_T.push_back(RuntimePow(T, 3));
       o.poly_spline.push_back(static_cast<uint16_t>(o.splines.size()));
       o.poly_meta.push_back(r.rt ? (static_cast<uint32_t>(v.poly_phase[p]) | (static_cast<uint32_t>(v.polys_in_phase[p]) << 8))
                                  : kPolyFixed);
@@ -76,8 +76,8 @@ void BuildTrajTablesAt(const HostProgram& hp, const towr_b200_spec& s, const std
       for (int i = 0; i < id; ++i) tl -= v.poly_T[i];
       o.samp_poly.push_back(static_cast<uint32_t>(r.poly0 + id));
       o.samp_t.push_back(tl);
-      o.samp_t.push_back(std::pow(tl, 2));
-      o.samp_t.push_back(std::pow(tl, 3));
+      o.samp_t.push_back(RuntimePow(tl, 2));
+      o.samp_t.push_back(RuntimePow(tl, 3));
     }
     o.n_nodes += v.n_nodes;
     o.n_polys += v.n_polys();
