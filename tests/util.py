@@ -233,6 +233,21 @@ def pow_ok(a, b, mask=None):
     return bool((ratio <= lim).all() and out.mean() <= POW_FRACTION)
 
 
+def check_cost_against_oracle(O, p, st, x, f, grad, rt):
+    """f and its gradient of one problem against oracle problem p.  Fixed durations: f in the strict band, the gradient
+    by cost_gradient_ok.  Optimised durations, like check_against_oracle: those against the oracle with correctly rounded
+    powers (O.pow_mode(1)), and pow_ok against the oracle's default std::pow mode (an end-of-stance force of 1e-14 N differs
+    by its own size between the two power functions)."""
+    for mode in ((1, 0) if rt else (0,)):
+        with O.pow_mode(mode):
+            fo, go = p.eval_f(x), p.eval_grad_f(x)
+        if mode == 1 or not rt:
+            assert tol_ratio(np.array([f]), np.array([fo])) <= 1.0, "f, oracle pow mode %d" % mode
+            assert cost_gradient_ok(st, grad, go), "cost gradient, oracle pow mode %d" % mode
+        else:
+            assert pow_ok(np.array([f]), np.array([fo])) and (cost_gradient_ok(st, grad, go) or pow_ok(grad, go)), "costs, std::pow oracle"
+
+
 def check_against_oracle(O, ospec, st, x, g, v, rt, superset=False):
     """g and the Jacobian values of one problem against the oracle.  Fixed durations: strict band (parity_ok).  Optimised
     durations: strict band against the oracle with correctly rounded powers (O.pow_mode(1)) AND pow_ok against the
