@@ -236,8 +236,9 @@ def pow_ok(a, b, mask=None):
 def check_cost_against_oracle(O, p, st, x, f, grad, rt):
     """f and its gradient of one problem against oracle problem p.  Fixed durations: f in the strict band, the gradient
     by cost_gradient_ok.  Optimised durations, like check_against_oracle: those against the oracle with correctly rounded
-    powers (O.pow_mode(1)), and pow_ok against the oracle's default std::pow mode (an end-of-stance force of 1e-14 N differs
-    by its own size between the two power functions)."""
+    powers (O.pow_mode(1)), and every entry within POW_BAND x the band of the oracle's default std::pow mode (an
+    end-of-stance force of 1e-14 N differs by its own size between the two power functions; pow_ok's allowance of a small
+    FRACTION of such entries suits the long constraint vectors, not a gradient block of two ee-schedule variables)."""
     for mode in ((1, 0) if rt else (0,)):
         with O.pow_mode(mode):
             fo, go = p.eval_f(x), p.eval_grad_f(x)
@@ -245,7 +246,8 @@ def check_cost_against_oracle(O, p, st, x, f, grad, rt):
             assert tol_ratio(np.array([f]), np.array([fo])) <= 1.0, "f, oracle pow mode %d" % mode
             assert cost_gradient_ok(st, grad, go), "cost gradient, oracle pow mode %d" % mode
         else:
-            assert pow_ok(np.array([f]), np.array([fo])) and (cost_gradient_ok(st, grad, go) or pow_ok(grad, go)), "costs, std::pow oracle"
+            assert tol_ratio(np.array([f]), np.array([fo])) <= POW_BAND, "f, std::pow oracle"
+            assert cost_gradient_ok(st, grad, go) or tol_ratio(grad, go) <= POW_BAND, "cost gradient, std::pow oracle"
 
 
 def check_against_oracle(O, ospec, st, x, g, v, rt, superset=False):
