@@ -199,7 +199,7 @@ def main():
         clip = lambda a: np.clip(a, -1e20, 1e20)           # ifopt::inf
         for mine, ref in zip(st.var_bounds(s) + st.con_bounds(s), p.var_bounds() + p.con_bounds()):
             ok = ok and tol_ratio(clip(mine), clip(ref)) <= 1.0
-        xs = [perturbed(x0, 100 + case, 0.03), x0]
+        xs = [perturbed(x0, 100 + case, float(os.environ.get("FUZZ_SCALE", "0.03"))), x0]   # FUZZ_SCALE: size of the perturbation
         r_o, c_o, _ = p.eval_jac(xs[0])
         rows, cols = st.pattern()
         if not gap:
